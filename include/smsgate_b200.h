@@ -1,0 +1,174 @@
+/*
+ * smsgate_b200 — C ABI of the B200 bulk-replay library.
+ *
+ * The reference (vpuhoff/smsgate) is pure Python and has no FFI seam; its seam
+ * is a handful of Python functions.  Each entry point below names the reference
+ * code it stands in for (paths relative to the reference root).  The Python
+ * drop-in (smsgate_b200/*.py) binds these with ctypes; INTEGRATION.md shows the
+ * stub a maintainer of the reference would add.
+ *
+ * Conventions
+ *   - Every function returns 0 on success or a negative SMSGATE_E_* code and
+ *     never throws; smsgate_last_error() gives the text.  Per-message problems
+ *     are data (flags / status / decimal error bits), not errors.
+ *   - A context is bound to one GPU and one CUDA stream and is not re-entrant;
+ *     different contexts are independent.
+ *   - "d_" pointers are device memory owned by the caller; "h_" pointers are
+ *     host memory.  Hot calls allocate nothing: scratch lives in the context
+ *     and is sized by smsgate_reserve().
+ *   - A batch is Arrow-style: int64 offsets[n+1] + uint8 bytes[offsets[n]],
+ *     UTF-8, offsets[0] may be non-zero, `bytes` must be 16-byte aligned.
+ */
+#ifndef SMSGATE_B200_H
+#define SMSGATE_B200_H
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define SMSGATE_ABI_VERSION 1
+
+/* error codes */
+#define SMSGATE_OK 0
+#define SMSGATE_E_CUDA (-1)
+#define SMSGATE_E_ARG (-2)
+#define SMSGATE_E_NOMEM (-3)
+#define SMSGATE_E_STATE (-4)
+#define SMSGATE_E_LIMIT (-5)
+
+/* flags[] bits written by the scan */
+#define SMSGATE_F_WORKER_SKIP 0x01 /* services/parser_worker/worker.py:112-121 */
+#define SMSGATE_F_PARSER_OTP 0x02  /* libs/gemini_parser.py:198-200 */
+#define SMSGATE_F_MODIFIED 0x04    /* clean/mask changed the body (libs/gemini_parser.py:202-203) */
+#define SMSGATE_F_BODY_DATE 0x08   /* the body carries a usable dd.mm.yy[yy] (libs/gemini_parser.py:73-100) */
+#define SMSGATE_F_NON_ASCII 0x10
+
+/* status[] values: where the reference would have sent the message */
+#define SMSGATE_ST_UPSERT 0             /* sms.parsed, truthy merchant: upserted (services/pb_writer/writer.py:70-74) */
+#define SMSGATE_ST_PARSED_NO_MERCHANT 1 /* sms.parsed, writer acks without upsert (writer.py:70,75) */
+#define SMSGATE_ST_SKIPPED_FILTER 2     /* worker skip filter: acked, nothing published (worker.py:112-126) */
+#define SMSGATE_ST_CACHE_MISS 3         /* would call Gemini (libs/gemini_parser.py:210-222); offline: DLQ set */
+#define SMSGATE_ST_UNMATCHED 4          /* parse_sms_llm returned None -> sms.failed (worker.py:151-158) */
+#define SMSGATE_ST_BROKEN 5             /* BrokenMessage: acked, dropped (worker.py:136-140) */
+#define SMSGATE_ST_FUTURE_DATE 6        /* parsed.date > now -> sms.failed (worker.py:174-180) */
+#define SMSGATE_ST_FAILED_EXC 7         /* any other exception -> sms.failed (worker.py:141-149) */
+
+/* per cache entry flags supplied by the loader (see smsgate_cache_load) */
+#define SMSGATE_E_IS_DICT 0x0001
+#define SMSGATE_E_HAS_TXN 0x0002
+#define SMSGATE_E_SCHEMA_OK 0x0004
+#define SMSGATE_E_CARD_STR 0x0008
+#define SMSGATE_E_MERCHANT 0x0010
+#define SMSGATE_E_DATE_STRICT 0x0020
+#define SMSGATE_E_DATE_HOST 0x0040
+#define SMSGATE_E_DATE_NOBODY 0x0080
+#define SMSGATE_E_DATE_TZ 0x0100
+#define SMSGATE_E_DATE_KEY 0x0200
+
+/* dec_flags[] layout: bits 0-1 amount error, 2-3 balance error, bit 4 amount sign, bit 5 balance sign */
+#define SMSGATE_DEC_OK 0
+#define SMSGATE_DEC_SYNTAX 1   /* parse_ambiguous_decimal raises ValueError */
+#define SMSGATE_DEC_OVERFLOW 2 /* |coefficient| > INT64_MAX: representation limit of this library */
+
+typedef struct smsgate_ctx smsgate_ctx;
+
+/* Per-message outputs.  Any pointer may be NULL to skip that column, except
+ * that later stages need the columns of earlier ones when run separately.
+ * Device pointers for the *_device calls, host pointers for smsgate_replay_host. */
+typedef struct smsgate_outputs {
+    uint8_t* msg_id;      /* [n*20] SHA-1(body) digest bytes (services/xml_watcher/watcher.py:45) */
+    uint8_t* cache_key;   /* [n*32] SHA-256(fixed_body) digest bytes (libs/gemini_parser.py:207) */
+    uint8_t* flags;       /* [n] SMSGATE_F_* */
+    int32_t* body_date;   /* [n] y<<9|m<<5|d lifted from the body, 0 if none */
+    int32_t* fixed_len;   /* [n] byte length of fixed_body */
+    uint8_t* fixed_bytes; /* [same size as the input bytes] fixed_body of message i at offsets[i],
+                             valid only where flags has SMSGATE_F_MODIFIED; raw_body otherwise is the body */
+    int32_t* slot;        /* [n] index of the matching cache entry, -1 on a miss */
+    uint8_t* status;      /* [n] SMSGATE_ST_* */
+    int64_t* amount_coef; /* [n] |coefficient| of parse_ambiguous_decimal(str(amount)) (libs/decimal_utils.py:4-63) */
+    int64_t* balance_coef;
+    int32_t* amount_exp;  /* [n] Decimal exponent */
+    int32_t* balance_exp;
+    uint8_t* dec_flags;   /* [n] */
+    int64_t* date;        /* [n] resolved naive datetime, packed y<<46|m<<42|d<<37|H<<32|M<<26|S<<20|us; 0 if none */
+    uint8_t* card;        /* [n*16] first four characters of the normalised card, UTF-8, zero padded */
+    uint8_t* card_len;    /* [n] bytes used in card */
+    uint8_t* survivor;    /* [n] 1 = last occurrence of its msg_id among upserts: the record that survives */
+    uint8_t* first_seen;  /* [n] 1 = first occurrence: an insert rather than a patch */
+    int64_t* last_idx;    /* [n] global index of the surviving occurrence, -1 if the message is not upserted */
+} smsgate_outputs;
+
+/* ---- lifecycle ---------------------------------------------------------- */
+int smsgate_abi_version(void);
+/* Create a context on CUDA device `device`.  cuda_stream is a cudaStream_t
+ * (or NULL for a stream the context creates).  No reference counterpart. */
+int smsgate_create(int device, void* cuda_stream, smsgate_ctx** out);
+void smsgate_destroy(smsgate_ctx* ctx);
+/* Text of the last error on this context (or of the last failed create when ctx is NULL). */
+const char* smsgate_last_error(const smsgate_ctx* ctx);
+/* Size the context's scratch (dedup table, staging for the host call) for
+ * batches of up to max_msgs messages / max_bytes body bytes.  Allocates. */
+int smsgate_reserve(smsgate_ctx* ctx, int64_t max_msgs, int64_t max_bytes);
+/* Kernels launched by this context since creation (for bench accounting). */
+int64_t smsgate_launch_count(const smsgate_ctx* ctx);
+
+/* ---- the Gemini response cache ------------------------------------------
+ * Replaces `cache = diskcache.Cache(".gemini_cache")` + `cache_key in cache` +
+ * `cache[cache_key]` (libs/gemini_parser.py:33, :208-209) by a device hash
+ * table.  All pointers are HOST memory; the call copies and builds.
+ *   keys        [m*32]   SHA-256 digests (the hex keys of the cache, decoded)
+ *   val_offsets [4*m+1]  Arrow offsets into val_bytes; entry e owns strings
+ *                        4e..4e+3 = str(amount), str(balance), date, card
+ *   eflags      [m]      SMSGATE_E_* (schema facts the loader established)
+ *   date_packed [m]      packed datetime for SMSGATE_E_DATE_HOST / _NOBODY entries
+ */
+int smsgate_cache_load(smsgate_ctx* ctx, int64_t m, const uint8_t* h_keys, const int32_t* h_val_offsets,
+                       const uint8_t* h_val_bytes, const uint16_t* h_eflags, const int64_t* h_date_packed);
+int64_t smsgate_cache_size(const smsgate_ctx* ctx);
+
+/* ---- batch helpers (host buffers in and out) ----------------------------- */
+/* libs.decimal_utils.parse_ambiguous_decimal over n strings (libs/decimal_utils.py:4-63).
+ * flags[i]: bits 0-1 SMSGATE_DEC_*, bit 4 sign. */
+int smsgate_decimal_batch(smsgate_ctx* ctx, int64_t n, const int32_t* h_offsets, const uint8_t* h_bytes,
+                          int64_t* h_coef, int32_t* h_exp, uint8_t* h_flags);
+/* datetime.strptime(s, '%d.%m.%y %H:%M') for the ASCII subset evaluated on the
+ * GPU (libs/gemini_parser.py:116); out[i] = packed datetime or -1 when the
+ * string needs the reference's strptime/dateutil chain on the host. */
+int smsgate_strict_date_batch(smsgate_ctx* ctx, int64_t n, const int32_t* h_offsets, const uint8_t* h_bytes,
+                              int64_t* h_packed);
+
+/* ---- the replay stages, device pointers ----------------------------------- */
+/* Stage 1 — keys and scans: msg_id (watcher.py:45), worker skip filter
+ * (worker.py:112-121), parser OTP filter (gemini_parser.py:198-200), clean +
+ * card masking (:202-203, :121-137), cache key (:207), body date (:73-100).
+ * Writes msg_id, cache_key, flags, body_date, fixed_len, fixed_bytes. */
+int smsgate_scan_keys(smsgate_ctx* ctx, const uint8_t* d_bytes, const int64_t* d_offsets, int64_t n,
+                      const smsgate_outputs* out);
+/* Stage 2 — cache join, amounts, date, card, routing (gemini_parser.py:208-247,
+ * decimal_utils.py:4-63, worker.py:136-189, writer.py:65-84).  Reads
+ * cache_key, flags, body_date; writes slot, status, amount_*, balance_*,
+ * dec_flags, date, card, card_len.  now_packed is the frozen `datetime.now()`. */
+int smsgate_join_route(smsgate_ctx* ctx, int64_t n, int64_t now_packed, const smsgate_outputs* out);
+/* Stage 3 — upsert-by-msg_id (libs/pocketbase.py:168-200,
+ * services/pb_writer/upsert.py:19-31): among messages with status UPSERT the
+ * last occurrence of a msg_id survives, the first one is the insert.  Reads
+ * msg_id, status; writes survivor, first_seen, last_idx (= base_index + local). */
+int smsgate_dedup(smsgate_ctx* ctx, int64_t n, int64_t base_index, const smsgate_outputs* out);
+/* All three stages on one batch. */
+int smsgate_replay_device(smsgate_ctx* ctx, const uint8_t* d_bytes, const int64_t* d_offsets, int64_t n,
+                          int64_t now_packed, int64_t base_index, const smsgate_outputs* out);
+
+/* ---- the replay, host buffers --------------------------------------------
+ * What `_iter_sms` -> worker -> parse_sms_llm -> pb_writer do for a whole
+ * backup, called with the batch in host memory: copies in, runs the three
+ * stages, copies every non-NULL output column back and synchronises.
+ * total_bytes = h_offsets[n].  Needs smsgate_reserve() to have covered n. */
+int smsgate_replay_host(smsgate_ctx* ctx, const uint8_t* h_bytes, const int64_t* h_offsets, int64_t n,
+                        int64_t now_packed, int64_t base_index, const smsgate_outputs* h_out);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* SMSGATE_B200_H */

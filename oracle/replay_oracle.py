@@ -325,12 +325,11 @@ def replay_one(body: str, sender: str, raw_date: str, cache, now: _dt.datetime,
                          parser_otp=parser_otp(body), fixed=fixed, hit=False,
                          status=ST_SKIPPED_FILTER, body_date=pack_date(body_date(body)))
     hexkey = ck.hex()
-    out.hit = hexkey in cache
-    if out.hit:
-        resp0 = cache[hexkey]
-        if isinstance(resp0, dict):
-            out.amount = decimal_triplet(str(resp0.get("amount")))
-            out.balance = decimal_triplet(str(resp0.get("balance")))
+    out.hit = hexkey in cache                                     # gemini_parser.py:208
+    resp0 = cache[hexkey] if out.hit else None                    # :209
+    if isinstance(resp0, dict):
+        out.amount = decimal_triplet(str(resp0.get("amount")))
+        out.balance = decimal_triplet(str(resp0.get("balance")))
     if out.worker_skip:                                           # worker.py:112-126
         return out
     if out.parser_otp:                                            # gemini_parser.py:198-200
@@ -340,8 +339,7 @@ def replay_one(body: str, sender: str, raw_date: str, cache, now: _dt.datetime,
         out.status = ST_CACHE_MISS
         return out
     try:
-        parsed = parse_hit(mid.hex(), sender, device_id, raw_date, body, fixed,
-                           copy_resp(cache[hexkey]))
+        parsed = parse_hit(mid.hex(), sender, device_id, raw_date, body, fixed, copy_resp(resp0))
     except BrokenMessage:                                         # worker.py:136-140
         out.status = ST_BROKEN
         return out

@@ -1,0 +1,96 @@
+"""ctypes binding of include/smsgate_b200.h.
+
+There is no CPU implementation behind this module: if the CUDA library is
+missing or no B200-class GPU is visible, loading / creating a context raises.
+"""
+from __future__ import annotations
+
+import ctypes as C
+import os
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, "libsmsgate_b200.so")
+
+ABI_VERSION = 1
+
+# flags / status / entry flags — mirror the header
+F_WORKER_SKIP, F_PARSER_OTP, F_MODIFIED, F_BODY_DATE, F_NON_ASCII = 0x01, 0x02, 0x04, 0x08, 0x10
+(ST_UPSERT, ST_PARSED_NO_MERCHANT, ST_SKIPPED_FILTER, ST_CACHE_MISS, ST_UNMATCHED, ST_BROKEN,
+ ST_FUTURE_DATE, ST_FAILED_EXC) = range(8)
+STATUS_NAMES = ("UPSERT", "PARSED_NO_MERCHANT", "SKIPPED_FILTER", "CACHE_MISS", "UNMATCHED", "BROKEN",
+                "FUTURE_DATE", "FAILED_EXC")
+DLQ_STATUSES = (ST_CACHE_MISS, ST_UNMATCHED, ST_FUTURE_DATE, ST_FAILED_EXC)
+E_IS_DICT, E_HAS_TXN, E_SCHEMA_OK, E_CARD_STR, E_MERCHANT = 0x1, 0x2, 0x4, 0x8, 0x10
+E_DATE_STRICT, E_DATE_HOST, E_DATE_NOBODY, E_DATE_TZ, E_DATE_KEY = 0x20, 0x40, 0x80, 0x100, 0x200
+DEC_OK, DEC_SYNTAX, DEC_OVERFLOW = 0, 1, 2
+
+# (column name, numpy dtype string, elements per message)
+COLUMNS = (
+    ("msg_id", "u1", 20), ("cache_key", "u1", 32), ("flags", "u1", 1), ("body_date", "i4", 1),
+    ("fixed_len", "i4", 1), ("fixed_bytes", "u1", 0), ("slot", "i4", 1), ("status", "u1", 1),
+    ("amount_coef", "i8", 1), ("balance_coef", "i8", 1), ("amount_exp", "i4", 1), ("balance_exp", "i4", 1),
+    ("dec_flags", "u1", 1), ("date", "i8", 1), ("card", "u1", 16), ("card_len", "u1", 1),
+    ("survivor", "u1", 1), ("first_seen", "u1", 1), ("last_idx", "i8", 1),
+)
+
+
+class Outputs(C.Structure):
+    _fields_ = [(name, C.c_void_p) for name, _, _ in COLUMNS]
+
+
+class LibraryMissing(RuntimeError):
+    pass
+
+
+_lib = None
+
+
+def lib():
+    """The loaded shared library.  Raises LibraryMissing when it has not been
+    built (`python -m smsgate_b200.build`): there is no fallback."""
+    global _lib
+    if _lib is not None:
+        return _lib
+    if not os.path.exists(LIB_PATH):
+        raise LibraryMissing(f"{LIB_PATH} is not built; run `python -m smsgate_b200.build` "
+                             "(the bulk-replay path has no CPU implementation)")
+    L = C.CDLL(LIB_PATH)
+    vp, i64, i32 = C.c_void_p, C.c_int64, C.c_int
+    sigs = {
+        "smsgate_abi_version": (i32, []),
+        "smsgate_create": (i32, [i32, vp, C.POINTER(vp)]),
+        "smsgate_destroy": (None, [vp]),
+        "smsgate_last_error": (C.c_char_p, [vp]),
+        "smsgate_reserve": (i32, [vp, i64, i64]),
+        "smsgate_launch_count": (i64, [vp]),
+        "smsgate_cache_load": (i32, [vp, i64, vp, vp, vp, vp, vp]),
+        "smsgate_cache_size": (i64, [vp]),
+        "smsgate_decimal_batch": (i32, [vp, i64, vp, vp, vp, vp, vp]),
+        "smsgate_strict_date_batch": (i32, [vp, i64, vp, vp, vp]),
+        "smsgate_scan_keys": (i32, [vp, vp, vp, i64, C.POINTER(Outputs)]),
+        "smsgate_join_route": (i32, [vp, i64, i64, C.POINTER(Outputs)]),
+        "smsgate_dedup": (i32, [vp, i64, i64, C.POINTER(Outputs)]),
+        "smsgate_replay_device": (i32, [vp, vp, vp, i64, i64, i64, C.POINTER(Outputs)]),
+        "smsgate_replay_host": (i32, [vp, vp, vp, i64, i64, i64, C.POINTER(Outputs)]),
+    }
+    for name, (res, args) in sigs.items():
+        fn = getattr(L, name)          # AttributeError if the library does not export it
+        fn.restype = res
+        fn.argtypes = args
+    if L.smsgate_abi_version() != ABI_VERSION:
+        raise LibraryMissing("libsmsgate_b200.so was built from a different header; rebuild it")
+    L._exported = tuple(sigs)
+    _lib = L
+    return L
+
+
+class SmsgateError(RuntimeError):
+    def __init__(self, code: int, text: str):
+        super().__init__(f"smsgate_b200 error {code}: {text}")
+        self.code = code
+
+
+def check(ctx, rc: int) -> None:
+    if rc != 0:
+        msg = lib().smsgate_last_error(ctx)
+        raise SmsgateError(rc, msg.decode("utf-8", "replace") if msg else "")

@@ -1,0 +1,326 @@
+"""Generates scan_tables.h: the byte-class table and the three dense automata
+the scan kernel walks once per body byte.
+
+  CI  Aho-Corasick automaton over the UPPER-CASED symbol stream for the nine
+      needles of the worker skip-filter (services/parser_worker/worker.py:112-121).
+      One absorbing accept state.
+  CS  automaton over RAW bytes for the case-sensitive needles: the parser's OTP
+      list (libs/gemini_parser.py:198) and the worker's `Daily limit exceeded`
+      (worker.py:120), plus the byte pair C2 A0 (U+00A0, which `clean` rewrites,
+      libs/gemini_parser.py:202).  Sticky facts ride in the state number:
+      bit 0 of the block index = "Daily limit exceeded" seen, bit 1 = NBSP seen;
+      one absorbing pair of states = parser needle seen.
+  DM  product of two KMP automata over code-point classes {other, digit, '.',
+      '*'}: the body-date forms dd.mm.yy / dd.mm.yyyy (libs/gemini_parser.py:73-76)
+      and the card form dddd***dddd (libs/gemini_parser.py:131).  Sticky flags
+      in the high bits of each entry: B found, A found, card found.
+
+Run `python smsgate_b200/csrc/gen_tables.py` after changing a needle; the
+header is committed so the build needs no Python.
+"""
+from __future__ import annotations
+
+import os
+import re
+import sys
+from collections import deque
+
+CI_NEEDLES = ["OTP", "CODE:", "NOT ENOUGH FUNDS", "INSUFFICIENT FUNDS", "CREDIT PAYMENT",
+              "C2C RECEIVED", "PASS:", "PASS=", "PERSON TO PERSON"]
+CS_PARSER = ["OTP", "CODE:", "PASS:", "PASS=", "Daily limit exceeded:"]
+CS_WORKER = "Daily limit exceeded"
+NBSP = b"\xc2\xa0"
+
+STRIDE = 32            # classes per CI / CS row
+DM_STRIDE = 8
+
+# upper()-expansions that contain ASCII (probed over all of Unicode 15.0)
+UPPER_SPECIALS = {
+    0x00DF: "SS", 0x0131: "I", 0x0149: "\x00N", 0x017F: "S", 0x01F0: "J\x00",
+    0x1E96: "H\x00", 0x1E97: "T\x00", 0x1E98: "W\x00", 0x1E99: "Y\x00", 0x1E9A: "A\x00",
+    0xFB00: "FF", 0xFB01: "FI", 0xFB02: "FL", 0xFB03: "FFI", 0xFB04: "FFL", 0xFB05: "ST", 0xFB06: "ST",
+}  # "\x00" stands for a non-ASCII output character
+
+
+def digit_runs():
+    cps = [cp for cp in range(0x110000) if re.match(r"\d", chr(cp))]
+    runs = []
+    for cp in cps:
+        if runs and cp == runs[-1][1] + 1:
+            runs[-1][1] = cp
+        else:
+            runs.append([cp, cp])
+    return [(a, b - a + 1) for a, b in runs]
+
+
+def aho(needles, alphabet):
+    """Dense goto table of the Aho-Corasick automaton; returns (next, accepting-set)."""
+    goto = [{}]
+    out = [set()]
+    for n in needles:
+        s = 0
+        for ch in n:
+            if ch not in goto[s]:
+                goto.append({})
+                out.append(set())
+                goto[s][ch] = len(goto) - 1
+            s = goto[s][ch]
+        out[s].add(n)
+    fail = [0] * len(goto)
+    q = deque()
+    for ch, t in goto[0].items():
+        q.append(t)
+    dense = [dict() for _ in goto]
+    order = [0]
+    while q:
+        r = q.popleft()
+        order.append(r)
+        for ch, t in goto[r].items():
+            q.append(t)
+            f = fail[r]
+            while f and ch not in goto[f]:
+                f = fail[f]
+            fail[t] = goto[f].get(ch, 0) if goto[f].get(ch, 0) != t else 0
+            out[t] |= out[fail[t]]
+    for s in order:
+        for ch in alphabet:
+            if ch in goto[s]:
+                dense[s][ch] = goto[s][ch]
+            else:
+                dense[s][ch] = dense[fail[s]][ch] if s else 0
+    return dense, out
+
+
+def build_ci():
+    alphabet = sorted(set("".join(CI_NEEDLES)))
+    cls = {ch: i + 2 for i, ch in enumerate(alphabet)}      # 0 = OTHER, 1 = KEEP (continuation byte)
+    assert len(cls) + 2 <= STRIDE
+    dense, out = aho(CI_NEEDLES, alphabet)
+    n = len(dense)
+    ACC = n                                                # absorbing
+    table = [[0] * STRIDE for _ in range(n + 1)]
+    for s in range(n):
+        for c in range(STRIDE):
+            table[s][c] = 0
+        table[s][1] = s
+        for ch, c in cls.items():
+            t = dense[s][ch]
+            table[s][c] = ACC if out[t] else t
+    for c in range(STRIDE):
+        table[ACC][c] = ACC
+    return table, cls, ACC
+
+
+def build_cs():
+    needles = CS_PARSER + [CS_WORKER]
+    alphabet = sorted(set("".join(needles)))
+    cls = {ch: i + 1 for i, ch in enumerate(alphabet)}     # 0 = OTHER
+    c_c2 = len(cls) + 1
+    c_a0 = len(cls) + 2
+    assert c_a0 < STRIDE
+    dense, out = aho(needles, alphabet)
+    n = len(dense)
+    # state id = block * L + local; block = W | N << 1 carries the sticky facts.
+    # local 0..n-1 = automaton states, local n = "root, previous byte was C2"
+    # (C2 is in no needle, so it always falls back to the root).
+    L = n + 1
+    ACC0 = 4 * L            # parser needle seen, NBSP not seen
+    ACC1 = 4 * L + 1        # parser needle seen, NBSP seen
+    ACC0C = 4 * L + 2       # parser needle seen, previous byte was C2
+    nstates = 4 * L + 3
+    assert nstates <= 256
+    sym_of = {k: ch for ch, k in cls.items()}
+    table = [[0] * STRIDE for _ in range(nstates)]
+    for blk in range(4):
+        W, N = blk & 1, blk >> 1
+        for loc in range(L):
+            s = 0 if loc == n else loc
+            after_c2 = loc == n
+            sid = blk * L + loc
+            for c in range(STRIDE):
+                sym = sym_of.get(c)
+                t = dense[s][sym] if sym is not None else 0
+                w2, n2 = W, N
+                if c == c_a0 and after_c2:
+                    n2 = 1
+                if CS_WORKER in out[t]:
+                    w2 = 1
+                if any(x in CS_PARSER for x in out[t]):
+                    table[sid][c] = ACC1 if n2 else ACC0
+                else:
+                    table[sid][c] = (w2 | n2 << 1) * L + (n if c == c_c2 else t)
+    for c in range(STRIDE):
+        table[ACC0][c] = ACC0
+        table[ACC1][c] = ACC1
+        table[ACC0C][c] = ACC0
+    table[ACC0][c_c2] = ACC0C
+    table[ACC0C][c_c2] = ACC0C
+    table[ACC0C][c_a0] = ACC1
+    return table, cls, c_c2, c_a0, L, ACC0, ACC1, ACC0C
+
+
+def kmp(pattern, classes):
+    """Dense KMP automaton; state = matched prefix length, len(pattern) is reported
+    by the caller.  After a full match the search restarts from scratch (regex
+    `sub`/`search` semantics: non-overlapping)."""
+    m = len(pattern)
+    nxt = [[0] * len(classes) for _ in range(m + 1)]
+    for s in range(m + 1):
+        for ci, c in enumerate(classes):
+            if s == m:
+                text = c                      # restart after a complete match
+            else:
+                text = pattern[:s] + c
+            k = min(len(text), m)
+            while k > 0 and text[-k:] != pattern[:k]:
+                k -= 1
+            nxt[s][ci] = k
+    return nxt
+
+
+def build_dm():
+    # class ids: 0 other, 1 digit, 2 '.', 3 '*', 4 keep
+    classes = ["o", "d", ".", "*"]
+    date = kmp("dd.dd.dddd", classes)        # state 8 = short form complete, 10 = long form complete
+    card = kmp("dddd***dddd", classes)       # 11 = card form complete
+    # date part: (progress 0..10, foundB, foundA): after A nothing more is needed.
+    # card part: (progress 0..10, found)
+    states = {}
+    rows = []
+
+    def sid(key):
+        if key not in states:
+            states[key] = len(rows)
+            rows.append(None)
+        return states[key]
+
+    start = (0, 0, 0, 0, 0)
+    sid(start)
+    work = [start]
+    trans = {}
+    while work:
+        key = work.pop()
+        dp, fb, fa, cp, fc = key
+        row = []
+        for ci in range(4):
+            ndp, nfb, nfa = dp, fb, fa
+            if not fa:
+                ndp = date[dp][ci]
+                if ndp >= 8:
+                    nfb = 1
+                if ndp == 10:
+                    nfa = 1
+                    ndp = 0
+            ncp, nfc = cp, fc
+            if not fc:
+                ncp = card[cp][ci]
+                if ncp == 11:
+                    nfc = 1
+                    ncp = 0
+            nk = (ndp, nfb, nfa, ncp, nfc)
+            if nk not in states:
+                sid(nk)
+                work.append(nk)
+            row.append(nk)
+        trans[key] = row
+    n = len(rows)
+    table = [[0] * DM_STRIDE for _ in range(n)]
+    FLAG_B, FLAG_A, FLAG_C = 0x2000, 0x4000, 0x8000
+
+    def enc(key):
+        dp, fb, fa, cp, fc = key
+        v = states[key] * DM_STRIDE
+        assert v < 0x2000
+        return v | (FLAG_B if fb else 0) | (FLAG_A if fa else 0) | (FLAG_C if fc else 0)
+
+    for key, s in states.items():
+        for ci in range(4):
+            table[s][ci] = enc(trans[key][ci])
+        table[s][4] = enc(key)                               # keep
+        for ci in range(5, DM_STRIDE):
+            table[s][ci] = enc(key)
+    return table, n
+
+
+def lead_len(b):
+    if b < 0x80:
+        return 1
+    if 0xC2 <= b <= 0xDF:
+        return 2
+    if 0xE0 <= b <= 0xEF:
+        return 3
+    if 0xF0 <= b <= 0xF4:
+        return 4
+    return 0
+
+
+def main():
+    ci, ci_cls, CI_ACC = build_ci()
+    cs, cs_cls, c_c2, c_a0, CS_L, ACC0, ACC1, ACC0C = build_cs()
+    dm, dm_n = build_dm()
+    runs = digit_runs()
+
+    special_leads = set()
+    for cp in UPPER_SPECIALS:
+        special_leads.add(chr(cp).encode()[0])
+    for a, n in runs:
+        for cp in (a, a + n - 1):
+            if cp >= 0x80:
+                special_leads.add(chr(cp).encode()[0])
+        # a run never straddles a lead byte boundary in practice; assert it
+        if a >= 0x80:
+            assert chr(a).encode()[0] == chr(a + n - 1).encode()[0] or n == 50
+    special_leads.add(0xE2)                                 # U+2022 bullet
+
+    # byte class word: bits 0-4 CI class, 5-9 CS class, 10-12 DM class, bit 15 = special lead
+    cls_word = []
+    for b in range(256):
+        ch = chr(b)
+        if b < 0x80:
+            up = ch.upper()
+            cic = ci_cls.get(up, 0)
+            csc = cs_cls.get(ch, 0)
+            dmc = 1 if ch.isdigit() else 2 if ch == "." else 3 if ch == "*" else 0
+            sp = 0
+        elif b < 0xC0:
+            cic, csc, dmc, sp = 1, (c_a0 if b == 0xA0 else 0), 4, 0
+        else:
+            cic, csc, dmc = 0, (c_c2 if b == 0xC2 else 0), 0
+            sp = 1 if b in special_leads else 0
+        cls_word.append(cic | csc << 5 | dmc << 10 | sp << 15)
+
+    here = os.path.dirname(os.path.abspath(__file__))
+    with open(os.path.join(here, "scan_tables.h"), "w") as f:
+        w = f.write
+        w("// GENERATED by gen_tables.py — do not edit.\n#pragma once\n#include <stdint.h>\n\n")
+        w(f"#define SCAN_STRIDE {STRIDE}\n#define DM_STRIDE {DM_STRIDE}\n")
+        w(f"#define CI_STATES {len(ci)}\n#define CI_ACCEPT {CI_ACC}\n")
+        w(f"#define CS_STATES {len(cs)}\n#define CS_BLOCK {CS_L}\n#define CS_ACC0 {ACC0}\n#define CS_ACC1 {ACC1}\n#define CS_ACC0C {ACC0C}\n")
+        w(f"#define DM_STATES {dm_n}\n#define DM_FLAG_B 0x2000\n#define DM_FLAG_A 0x4000\n#define DM_FLAG_C 0x8000\n#define DM_ROW_MASK 0x1ff8\n")
+        for ch, c in sorted(ci_cls.items(), key=lambda kv: kv[1]):
+            name = {" ": "SP", ":": "COLON", "=": "EQ"}.get(ch, ch)
+            w(f"#define CI_CLS_{name} {c}\n")
+        w("#define CI_CLS_OTHER 0\n#define CI_CLS_KEEP 1\n")
+        w("#define DM_CLS_OTHER 0\n#define DM_CLS_DIGIT 1\n#define DM_CLS_DOT 2\n#define DM_CLS_STAR 3\n#define DM_CLS_KEEP 4\n\n")
+
+        def arr(name, ctype, rows):
+            flat = [v for r in rows for v in r]
+            w(f"static const {ctype} {name}[{len(flat)}] = {{\n")
+            for i in range(0, len(flat), 24):
+                w("  " + ",".join(str(v) for v in flat[i:i + 24]) + ",\n")
+            w("};\n\n")
+
+        arr("H_BYTE_CLASS", "uint16_t", [cls_word])
+        arr("H_CI_NEXT", "uint8_t", ci)
+        arr("H_CS_NEXT", "uint8_t", cs)
+        arr("H_DM_NEXT", "uint16_t", dm)
+        w(f"#define N_DIGIT_RUNS {len(runs)}\n")
+        arr("H_DIGIT_RUN_START", "uint32_t", [[a for a, _ in runs]])
+        arr("H_DIGIT_RUN_LEN", "uint8_t", [[n for _, n in runs]])
+        arr("H_CARD_KMP", "uint8_t", kmp("dddd***dddd", ["o", "d", ".", "*"]))
+    print("CI states", len(ci), "CS states", len(cs), "DM states", dm_n,
+          "special leads", sorted(hex(b) for b in special_leads))
+
+
+if __name__ == "__main__":
+    sys.exit(main())

@@ -1,0 +1,800 @@
+// smsgate_b200 — CUDA kernels (sm_100a) and the C ABI declared in
+// include/smsgate_b200.h.  No torch types, no host fallback: every entry
+// point launches kernels or fails with an error code.
+//
+// Kernels
+//   k_scan_keys     one thread per message over a shared-memory tile that a
+//                   single cp.async.bulk (TMA 1-D) copy stages per CTA: skip
+//                   filters, body date, clean+mask rewrite, SHA-1, SHA-256.
+//                   Integer-ALU bound (SHA rounds), see DESIGN.md.
+//   k_cache_build   inserts the cache entries into an open-addressing table.
+//   k_join_route    probe + decimal canonicalisation + date/card + routing.
+//   k_dedup_insert / k_dedup_resolve   upsert-by-msg_id.
+//   k_decimal_batch / k_strict_date_batch   the two batch helpers.
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include <stdio.h>
+#include <string.h>
+#include <new>
+#include <string>
+
+#include "../../include/smsgate_b200.h"
+#include "join_core.cuh"
+#include "scan_core.cuh"
+
+// ------------------------------------------------------------------ tables in global memory
+struct DeviceTables {
+    uint16_t byte_class[256];
+    uint16_t dm_next[DM_STATES * DM_STRIDE];
+    uint32_t digit_run_start[N_DIGIT_RUNS];
+    uint8_t ci_next[CI_STATES * SCAN_STRIDE];
+    uint8_t cs_next[CS_STATES * SCAN_STRIDE];
+    uint8_t digit_run_len[N_DIGIT_RUNS];
+    uint8_t card_kmp[48];
+};
+static_assert(sizeof(DeviceTables) % 16 == 0, "tables are copied 16 bytes at a time");
+
+// ------------------------------------------------------------------ PTX helpers (TMA 1-D bulk copy + mbarrier)
+__device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
+__device__ __forceinline__ void mbar_init(uint64_t* bar, uint32_t count) {
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count));
+}
+__device__ __forceinline__ void fence_proxy_async() { asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); }
+__device__ __forceinline__ void mbar_expect_tx(uint64_t* bar, uint32_t bytes) {
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void tma_load_1d(void* dst, const void* src, uint32_t bytes, uint64_t* bar) {
+    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(
+                     smem_u32(dst)),
+                 "l"(src), "r"(bytes), "r"(smem_u32(bar))
+                 : "memory");
+}
+__device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
+    asm volatile(
+        "{\n"
+        ".reg .pred p;\n"
+        "WAIT_LOOP:\n"
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n"
+        "@p bra DONE;\n"
+        "bra WAIT_LOOP;\n"
+        "DONE:\n"
+        "}\n" ::"r"(smem_u32(bar)),
+        "r"(parity)
+        : "memory");
+}
+
+// ------------------------------------------------------------------ stage 1: keys + scans
+constexpr int K1_THREADS = 256;
+constexpr int K1_STAGE = 44 * 1024;       // staged body bytes per CTA tile
+constexpr int K1_PAD = 32;                // slack read by the unaligned word reader
+
+struct __align__(16) K1Smem {
+    DeviceTables tab;
+    uint8_t stage[K1_STAGE + K1_PAD];
+    uint64_t mbar;
+};
+
+struct ScanOut {
+    uint8_t* msg_id;
+    uint8_t* cache_key;
+    uint8_t* flags;
+    int32_t* body_date;
+    int32_t* fixed_len;
+    uint8_t* fixed_bytes;
+};
+
+__device__ __forceinline__ void k1_store(const ScanOut& o, int64_t i, const uint32_t h1[5], const uint32_t h2[8],
+                                         const ScanResult& sr, int flen) {
+    if (o.msg_id) {
+        uint32_t* p = (uint32_t*)(o.msg_id + i * 20);
+#pragma unroll
+        for (int k = 0; k < 5; ++k) p[k] = __byte_perm(h1[k], 0, 0x0123);
+    }
+    if (o.cache_key) {
+        uint4* p = (uint4*)(o.cache_key + i * 32);
+        p[0] = make_uint4(__byte_perm(h2[0], 0, 0x0123), __byte_perm(h2[1], 0, 0x0123), __byte_perm(h2[2], 0, 0x0123),
+                          __byte_perm(h2[3], 0, 0x0123));
+        p[1] = make_uint4(__byte_perm(h2[4], 0, 0x0123), __byte_perm(h2[5], 0, 0x0123), __byte_perm(h2[6], 0, 0x0123),
+                          __byte_perm(h2[7], 0, 0x0123));
+    }
+    if (o.flags) o.flags[i] = (uint8_t)sr.flags;
+    if (o.body_date) o.body_date[i] = sr.body_date;
+    if (o.fixed_len) o.fixed_len[i] = flen;
+}
+
+__global__ void __launch_bounds__(K1_THREADS, 4)
+k_scan_keys(const uint8_t* __restrict__ bytes, const int64_t* __restrict__ offsets, int64_t n,
+            const DeviceTables* __restrict__ gtab, ScanOut out) {
+    extern __shared__ __align__(16) uint8_t smem_raw[];
+    K1Smem& S = *reinterpret_cast<K1Smem*>(smem_raw);
+    const int tid = threadIdx.x;
+
+    {   // tables -> shared, 16 bytes per thread per step
+        const uint4* src = reinterpret_cast<const uint4*>(gtab);
+        uint4* dst = reinterpret_cast<uint4*>(&S.tab);
+        for (int k = tid; k < (int)(sizeof(DeviceTables) / 16); k += K1_THREADS) dst[k] = src[k];
+    }
+    if (tid == 0) {
+        mbar_init(&S.mbar, 1);
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    __syncthreads();
+    ScanTables T;
+    T.byte_class = S.tab.byte_class;
+    T.ci_next = S.tab.ci_next;
+    T.cs_next = S.tab.cs_next;
+    T.dm_next = S.tab.dm_next;
+    T.digit_run_start = S.tab.digit_run_start;
+    T.digit_run_len = S.tab.digit_run_len;
+    T.card_kmp = S.tab.card_kmp;
+
+    uint32_t parity = 0;
+    const int64_t ntiles = (n + K1_THREADS - 1) / K1_THREADS;
+    for (int64_t tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
+        const int64_t t0 = tile * K1_THREADS;
+        const int64_t t1 = (t0 + K1_THREADS < n) ? t0 + K1_THREADS : n;
+        int64_t s = t0;
+        while (s < t1) {
+            // ---- how many messages starting at s fit the staging buffer
+            const int64_t lo = offsets[s];
+            const int64_t base = lo & ~(int64_t)15;
+            const int64_t mine = s + tid;
+            int64_t my_lo = 0, my_hi = 0;
+            bool fits = false;
+            if (mine < t1) {
+                my_lo = offsets[mine];
+                my_hi = offsets[mine + 1];
+                fits = (my_hi - base) <= K1_STAGE;
+            }
+            const int cnt = __syncthreads_count(fits);       // offsets are monotone: a prefix fits
+            if (cnt == 0) {
+                // a single body larger than the staging buffer: one thread walks it in global memory
+                if (tid == 0) {
+                    const uint8_t* m = bytes + my_lo;
+                    const int len = (int)(my_hi - my_lo);
+                    ScanResult sr = sg_scan_body(m, len, T);
+                    uint32_t h1[5], h2[8];
+                    sg_sha1(m, len, h1);
+                    int flen = len;
+                    const uint8_t* fm = m;
+                    if ((sr.flags & SG_F_MODIFIED) && out.fixed_bytes) {
+                        uint8_t* w = out.fixed_bytes + my_lo;
+                        for (int k = 0; k < len; ++k) w[k] = m[k];
+                        flen = sg_rewrite_fixed(w, len, T);
+                        fm = w;
+                    }
+                    sg_sha256(fm, flen, h2);
+                    k1_store(out, s, h1, h2, sr, flen);
+                }
+                s += 1;
+                __syncthreads();
+                continue;
+            }
+            const int64_t e = s + cnt;
+            const int64_t hi = offsets[e];
+            // ---- stage [base, hi): one bulk copy for the 16-byte-aligned part, plain loads for the tail
+            const int64_t bulk_end = hi & ~(int64_t)15;
+            const uint32_t bulk = (uint32_t)(bulk_end > base ? bulk_end - base : 0);
+            if (tid == 0 && bulk) {
+                fence_proxy_async();                             // earlier generic writes to the stage are ordered first
+                mbar_expect_tx(&S.mbar, bulk);
+                tma_load_1d(S.stage, bytes + base, bulk, &S.mbar);
+            }
+            {
+                const int64_t tail0 = (bulk_end > base) ? bulk_end : base;
+                if (tail0 + tid < hi && tid < 16) S.stage[tail0 - base + tid] = bytes[tail0 + tid];
+            }
+            if (bulk) mbar_wait(&S.mbar, parity);
+            if (bulk) parity ^= 1;
+            __syncthreads();
+
+            bool modified = false;
+            if (fits) {
+                uint8_t* m = S.stage + (my_lo - base);
+                const int len = (int)(my_hi - my_lo);
+                ScanResult sr = sg_scan_body(m, len, T);
+                uint32_t h1[5], h2[8];
+                sg_sha1(m, len, h1);
+                int flen = len;
+                if (sr.flags & SG_F_MODIFIED) { flen = sg_rewrite_fixed(m, len, T); modified = true; }
+                sg_sha256(m, flen, h2);
+                k1_store(out, mine, h1, h2, sr, flen);
+            }
+            const int any_mod = __syncthreads_or(modified);
+            if (any_mod && out.fixed_bytes) {
+                // tile -> fixed_bytes[lo, hi): the rewritten bodies sit at their original offsets
+                for (int64_t p = lo + tid; p < hi; p += K1_THREADS) out.fixed_bytes[p] = S.stage[p - base];
+            }
+            __syncthreads();
+            s = e;
+        }
+    }
+}
+
+// ------------------------------------------------------------------ cache table
+// slots: int2 {entry index or -1, 32-bit fingerprint}; keys stay in their own array.
+__device__ __forceinline__ uint64_t key_hash(const uint8_t* k) { return *reinterpret_cast<const uint64_t*>(k); }
+__device__ __forceinline__ uint32_t key_fp(const uint8_t* k) { return *reinterpret_cast<const uint32_t*>(k + 8); }
+
+__global__ void k_cache_build(const uint8_t* __restrict__ keys, int64_t m, int2* __restrict__ table, uint64_t mask,
+                              int* __restrict__ dup_count) {
+    const int64_t e = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+    if (e >= m) return;
+    const uint8_t* k = keys + e * 32;
+    uint64_t pos = key_hash(k) & mask;
+    const uint32_t fp = key_fp(k);
+    for (;;) {
+        int* slot = &table[pos].x;
+        const int prev = atomicCAS(slot, -1, (int)e);
+        if (prev == -1) {
+            table[pos].y = (int)fp;
+            return;
+        }
+        // duplicate key in the input: keep the later entry out, count it
+        const uint4* a = reinterpret_cast<const uint4*>(keys + (int64_t)prev * 32);
+        const uint4* b = reinterpret_cast<const uint4*>(k);
+        const uint4 a0 = a[0], a1 = a[1], b0 = b[0], b1 = b[1];
+        if (a0.x == b0.x && a0.y == b0.y && a0.z == b0.z && a0.w == b0.w && a1.x == b1.x && a1.y == b1.y &&
+            a1.z == b1.z && a1.w == b1.w) {
+            atomicAdd(dup_count, 1);
+            return;
+        }
+        pos = (pos + 1) & mask;
+    }
+}
+// fingerprints are written after the CAS; a second tiny pass makes them visible for every slot
+__global__ void k_cache_fix_fp(const uint8_t* __restrict__ keys, int2* __restrict__ table, uint64_t cap) {
+    const uint64_t p = blockIdx.x * (uint64_t)blockDim.x + threadIdx.x;
+    if (p >= cap) return;
+    const int e = table[p].x;
+    if (e >= 0) table[p].y = (int)key_fp(keys + (int64_t)e * 32);
+}
+
+struct CacheView {
+    const uint8_t* keys;
+    const int2* table;
+    uint64_t mask;
+    const int32_t* val_offsets;
+    const uint8_t* val_bytes;
+    const uint16_t* eflags;
+    const int64_t* date_packed;
+    int64_t m;
+};
+
+struct JoinOut {
+    int32_t* slot;
+    uint8_t* status;
+    int64_t* amount_coef;
+    int64_t* balance_coef;
+    int32_t* amount_exp;
+    int32_t* balance_exp;
+    uint8_t* dec_flags;
+    int64_t* date;
+    uint8_t* card;
+    uint8_t* card_len;
+};
+
+__global__ void __launch_bounds__(256)
+k_join_route(int64_t n, const uint8_t* __restrict__ cache_key, const uint8_t* __restrict__ flags,
+             const int32_t* __restrict__ body_date, int64_t now_packed, CacheView C, JoinOut out) {
+    const int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const uint4* kp = reinterpret_cast<const uint4*>(cache_key + i * 32);
+    const uint4 k0 = kp[0], k1 = kp[1];
+    int e = -1;
+    if (C.m > 0) {
+        uint64_t pos = (((uint64_t)k0.y << 32) | k0.x) & C.mask;
+        const int fp = (int)k0.z;
+        for (;;) {
+            const int2 sl = C.table[pos];
+            if (sl.x < 0) break;
+            if (sl.y == fp) {
+                const uint4* a = reinterpret_cast<const uint4*>(C.keys + (int64_t)sl.x * 32);
+                const uint4 a0 = a[0], a1 = a[1];
+                if (a0.x == k0.x && a0.y == k0.y && a0.z == k0.z && a0.w == k0.w && a1.x == k1.x && a1.y == k1.y &&
+                    a1.z == k1.z && a1.w == k1.w) {
+                    e = sl.x;
+                    break;
+                }
+            }
+            pos = (pos + 1) & C.mask;
+        }
+    }
+    EntryView ev;
+    ev.amount = ev.balance = ev.date = ev.card = nullptr;
+    ev.amount_len = ev.balance_len = ev.date_len = ev.card_len = 0;
+    ev.eflags = 0;
+    ev.date_packed = 0;
+    if (e >= 0) {
+        const int32_t* o = C.val_offsets + (int64_t)e * 4;
+        const int32_t o0 = o[0], o1 = o[1], o2 = o[2], o3 = o[3], o4 = o[4];
+        ev.amount = C.val_bytes + o0; ev.amount_len = o1 - o0;
+        ev.balance = C.val_bytes + o1; ev.balance_len = o2 - o1;
+        ev.date = C.val_bytes + o2; ev.date_len = o3 - o2;
+        ev.card = C.val_bytes + o3; ev.card_len = o4 - o3;
+        ev.eflags = C.eflags[e];
+        ev.date_packed = C.date_packed[e];
+    }
+    const RouteResult r = sg_route(flags[i], body_date[i], e >= 0, ev, now_packed);
+    if (out.slot) out.slot[i] = e;
+    if (out.status) out.status[i] = (uint8_t)r.status;
+    if (out.amount_coef) out.amount_coef[i] = r.amount.coef;
+    if (out.balance_coef) out.balance_coef[i] = r.balance.coef;
+    if (out.amount_exp) out.amount_exp[i] = r.amount.exp;
+    if (out.balance_exp) out.balance_exp[i] = r.balance.exp;
+    if (out.dec_flags)
+        out.dec_flags[i] = (uint8_t)(r.amount.err | (r.balance.err << 2) | (r.amount.sign << 4) | (r.balance.sign << 5));
+    if (out.date) out.date[i] = r.date;
+    if (out.card) {
+        uint4 c;
+        memcpy(&c, r.card, 16);
+        *reinterpret_cast<uint4*>(out.card + i * 16) = c;
+    }
+    if (out.card_len) out.card_len[i] = (uint8_t)r.card_bytes;
+}
+
+// ------------------------------------------------------------------ dedup (upsert-by-msg_id)
+struct DedupScratch {
+    int32_t* owner;    // [cap] local index of the message that claimed the slot, -1 = empty
+    int32_t* first;    // [cap] min local index with this key
+    int32_t* last;     // [cap] max local index with this key
+    int32_t* slot_of;  // [n]   slot of message i, -1 = not an upsert
+    uint64_t mask;
+};
+
+__device__ __forceinline__ bool id20_equal(const uint8_t* a, const uint8_t* b) {
+    const uint32_t* x = reinterpret_cast<const uint32_t*>(a);
+    const uint32_t* y = reinterpret_cast<const uint32_t*>(b);
+    return x[0] == y[0] && x[1] == y[1] && x[2] == y[2] && x[3] == y[3] && x[4] == y[4];
+}
+
+__global__ void __launch_bounds__(256)
+k_dedup_insert(int64_t n, const uint8_t* __restrict__ msg_id, const uint8_t* __restrict__ status, DedupScratch D) {
+    const int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    if (status[i] != SG_ST_UPSERT) {
+        D.slot_of[i] = -1;
+        return;
+    }
+    const uint8_t* k = msg_id + i * 20;
+    const uint32_t* kw = reinterpret_cast<const uint32_t*>(k);
+    uint64_t pos = (((uint64_t)kw[1] << 32) | kw[0]) & D.mask;
+    for (;;) {
+        int prev = D.owner[pos];
+        if (prev == -1) prev = atomicCAS(&D.owner[pos], -1, (int)i);
+        if (prev == -1 || prev == (int)i || id20_equal(msg_id + (int64_t)prev * 20, k)) break;
+        pos = (pos + 1) & D.mask;
+    }
+    atomicMin(&D.first[pos], (int)i);
+    atomicMax(&D.last[pos], (int)i);
+    D.slot_of[i] = (int32_t)pos;
+}
+
+__global__ void __launch_bounds__(256)
+k_dedup_resolve(int64_t n, int64_t base_index, DedupScratch D, uint8_t* __restrict__ survivor,
+                uint8_t* __restrict__ first_seen, int64_t* __restrict__ last_idx) {
+    const int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const int32_t sl = D.slot_of[i];
+    uint8_t sv = 0, fs = 0;
+    int64_t li = -1;
+    if (sl >= 0) {
+        const int32_t l = D.last[sl], f = D.first[sl];
+        sv = (l == (int32_t)i);
+        fs = (f == (int32_t)i);
+        li = base_index + l;
+    }
+    if (survivor) survivor[i] = sv;
+    if (first_seen) first_seen[i] = fs;
+    if (last_idx) last_idx[i] = li;
+}
+
+// ------------------------------------------------------------------ batch helpers
+__global__ void k_decimal_batch(int64_t n, const int32_t* __restrict__ offsets, const uint8_t* __restrict__ bytes,
+                                int64_t* coef, int32_t* exp, uint8_t* flags) {
+    const int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const DecResult r = sg_parse_decimal(bytes + offsets[i], offsets[i + 1] - offsets[i]);
+    coef[i] = r.coef;
+    exp[i] = r.exp;
+    flags[i] = (uint8_t)(r.err | (r.sign << 4));
+}
+__global__ void k_strict_date_batch(int64_t n, const int32_t* __restrict__ offsets, const uint8_t* __restrict__ bytes,
+                                    int64_t* packed) {
+    const int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    packed[i] = sg_parse_strict_datetime(bytes + offsets[i], offsets[i + 1] - offsets[i]);
+}
+
+// ================================================================== host side / C ABI
+struct smsgate_ctx {
+    int device = 0;
+    cudaStream_t stream = nullptr;
+    bool own_stream = false;
+    int sm_count = 148;
+    std::string err;
+    int64_t launches = 0;
+    DeviceTables* d_tables = nullptr;
+    // cache
+    int64_t cache_m = 0;
+    uint8_t* c_keys = nullptr;
+    int2* c_table = nullptr;
+    uint64_t c_cap = 0;
+    int32_t* c_val_offsets = nullptr;
+    uint8_t* c_val_bytes = nullptr;
+    uint16_t* c_eflags = nullptr;
+    int64_t* c_date_packed = nullptr;
+    // scratch sized by reserve()
+    int64_t cap_msgs = 0, cap_bytes = 0;
+    int32_t *d_owner = nullptr, *d_first = nullptr, *d_last = nullptr, *d_slot_of = nullptr;
+    uint64_t dd_cap = 0;
+    // device mirror of a host batch (smsgate_replay_host)
+    uint8_t* s_bytes = nullptr;
+    int64_t* s_offsets = nullptr;
+    uint8_t* s_out = nullptr;     // one slab carved into the output columns
+    uint8_t* s_fixed = nullptr;
+};
+
+static thread_local std::string g_create_error;
+
+static int fail(smsgate_ctx* ctx, int code, const std::string& msg) {
+    if (ctx) ctx->err = msg; else g_create_error = msg;
+    return code;
+}
+#define CUDA_TRY(ctx, expr)                                                                       \
+    do {                                                                                          \
+        cudaError_t _e = (expr);                                                                  \
+        if (_e != cudaSuccess)                                                                    \
+            return fail(ctx, SMSGATE_E_CUDA, std::string(#expr) + ": " + cudaGetErrorString(_e)); \
+    } while (0)
+
+static uint64_t pow2_at_least(uint64_t x) {
+    uint64_t p = 1;
+    while (p < x) p <<= 1;
+    return p;
+}
+
+extern "C" int smsgate_abi_version(void) { return SMSGATE_ABI_VERSION; }
+
+extern "C" const char* smsgate_last_error(const smsgate_ctx* ctx) {
+    return ctx ? ctx->err.c_str() : g_create_error.c_str();
+}
+
+extern "C" int64_t smsgate_launch_count(const smsgate_ctx* ctx) { return ctx ? ctx->launches : 0; }
+extern "C" int64_t smsgate_cache_size(const smsgate_ctx* ctx) { return ctx ? ctx->cache_m : 0; }
+
+extern "C" int smsgate_create(int device, void* cuda_stream, smsgate_ctx** out) {
+    if (!out) return fail(nullptr, SMSGATE_E_ARG, "out is NULL");
+    *out = nullptr;
+    int count = 0;
+    cudaError_t e = cudaGetDeviceCount(&count);
+    if (e != cudaSuccess || count == 0)
+        return fail(nullptr, SMSGATE_E_CUDA,
+                    std::string("no CUDA device: ") + (e != cudaSuccess ? cudaGetErrorString(e) : "count is 0") +
+                        " (this library has no CPU path)");
+    if (device < 0 || device >= count) return fail(nullptr, SMSGATE_E_ARG, "device index out of range");
+    smsgate_ctx* ctx = new (std::nothrow) smsgate_ctx();
+    if (!ctx) return fail(nullptr, SMSGATE_E_NOMEM, "out of host memory");
+    ctx->device = device;
+    auto bail = [&](const char* what, cudaError_t ce) {
+        g_create_error = std::string(what) + ": " + cudaGetErrorString(ce);
+        delete ctx;
+        return SMSGATE_E_CUDA;
+    };
+    if ((e = cudaSetDevice(device)) != cudaSuccess) return bail("cudaSetDevice", e);
+    cudaDeviceProp prop;
+    if ((e = cudaGetDeviceProperties(&prop, device)) != cudaSuccess) return bail("cudaGetDeviceProperties", e);
+    if (prop.major < 10) {
+        g_create_error = "device is not sm_100 class (compute capability " + std::to_string(prop.major) + "." +
+                         std::to_string(prop.minor) + "); this library carries sm_100a code only";
+        delete ctx;
+        return SMSGATE_E_CUDA;
+    }
+    ctx->sm_count = prop.multiProcessorCount;
+    if (cuda_stream) ctx->stream = (cudaStream_t)cuda_stream;
+    else {
+        if ((e = cudaStreamCreateWithFlags(&ctx->stream, cudaStreamNonBlocking)) != cudaSuccess)
+            return bail("cudaStreamCreate", e);
+        ctx->own_stream = true;
+    }
+    DeviceTables* h = new DeviceTables();
+    memcpy(h->byte_class, H_BYTE_CLASS, sizeof(h->byte_class));
+    memcpy(h->dm_next, H_DM_NEXT, sizeof(h->dm_next));
+    memcpy(h->digit_run_start, H_DIGIT_RUN_START, sizeof(h->digit_run_start));
+    memcpy(h->ci_next, H_CI_NEXT, sizeof(h->ci_next));
+    memcpy(h->cs_next, H_CS_NEXT, sizeof(h->cs_next));
+    memcpy(h->digit_run_len, H_DIGIT_RUN_LEN, sizeof(h->digit_run_len));
+    memcpy(h->card_kmp, H_CARD_KMP, sizeof(h->card_kmp));
+    if ((e = cudaMalloc(&ctx->d_tables, sizeof(DeviceTables))) != cudaSuccess) { delete h; return bail("cudaMalloc tables", e); }
+    e = cudaMemcpy(ctx->d_tables, h, sizeof(DeviceTables), cudaMemcpyHostToDevice);
+    delete h;
+    if (e != cudaSuccess) return bail("cudaMemcpy tables", e);
+    if ((e = cudaFuncSetAttribute(k_scan_keys, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(K1Smem))) != cudaSuccess)
+        return bail("cudaFuncSetAttribute(k_scan_keys)", e);
+    *out = ctx;
+    return SMSGATE_OK;
+}
+
+static void free_cache(smsgate_ctx* c) {
+    cudaFree(c->c_keys); cudaFree(c->c_table); cudaFree(c->c_val_offsets); cudaFree(c->c_val_bytes);
+    cudaFree(c->c_eflags); cudaFree(c->c_date_packed);
+    c->c_keys = nullptr; c->c_table = nullptr; c->c_val_offsets = nullptr; c->c_val_bytes = nullptr;
+    c->c_eflags = nullptr; c->c_date_packed = nullptr;
+    c->cache_m = 0; c->c_cap = 0;
+}
+static void free_scratch(smsgate_ctx* c) {
+    cudaFree(c->d_owner); cudaFree(c->d_first); cudaFree(c->d_last); cudaFree(c->d_slot_of);
+    cudaFree(c->s_bytes); cudaFree(c->s_offsets); cudaFree(c->s_out); cudaFree(c->s_fixed);
+    c->d_owner = c->d_first = c->d_last = c->d_slot_of = nullptr;
+    c->s_bytes = nullptr; c->s_offsets = nullptr; c->s_out = nullptr; c->s_fixed = nullptr;
+    c->cap_msgs = c->cap_bytes = 0; c->dd_cap = 0;
+}
+
+extern "C" void smsgate_destroy(smsgate_ctx* ctx) {
+    if (!ctx) return;
+    cudaSetDevice(ctx->device);
+    cudaStreamSynchronize(ctx->stream);
+    free_cache(ctx);
+    free_scratch(ctx);
+    cudaFree(ctx->d_tables);
+    if (ctx->own_stream) cudaStreamDestroy(ctx->stream);
+    delete ctx;
+}
+
+// bytes of the output slab per message (smsgate_replay_host): see carve_slab()
+static const int64_t SLAB_PER_MSG = 20 + 32 + 1 + 4 + 4 + 4 + 1 + 8 + 8 + 4 + 4 + 1 + 8 + 16 + 1 + 1 + 1 + 8;
+
+extern "C" int smsgate_reserve(smsgate_ctx* ctx, int64_t max_msgs, int64_t max_bytes) {
+    if (!ctx) return SMSGATE_E_ARG;
+    if (max_msgs < 0 || max_bytes < 0) return fail(ctx, SMSGATE_E_ARG, "negative size");
+    if (max_msgs > 0x40000000ll) return fail(ctx, SMSGATE_E_LIMIT, "a batch holds at most 2^30 messages");
+    CUDA_TRY(ctx, cudaSetDevice(ctx->device));
+    if (max_msgs <= ctx->cap_msgs && max_bytes <= ctx->cap_bytes) return SMSGATE_OK;
+    CUDA_TRY(ctx, cudaStreamSynchronize(ctx->stream));
+    free_scratch(ctx);
+    const uint64_t cap = pow2_at_least((uint64_t)(max_msgs > 8 ? max_msgs : 8) * 2);
+    CUDA_TRY(ctx, cudaMalloc(&ctx->d_owner, cap * 4));
+    CUDA_TRY(ctx, cudaMalloc(&ctx->d_first, cap * 4));
+    CUDA_TRY(ctx, cudaMalloc(&ctx->d_last, cap * 4));
+    CUDA_TRY(ctx, cudaMalloc(&ctx->d_slot_of, (size_t)(max_msgs + 1) * 4));
+    CUDA_TRY(ctx, cudaMalloc(&ctx->s_bytes, (size_t)max_bytes + 64));
+    CUDA_TRY(ctx, cudaMalloc(&ctx->s_fixed, (size_t)max_bytes + 64));
+    CUDA_TRY(ctx, cudaMalloc(&ctx->s_offsets, (size_t)(max_msgs + 1) * 8));
+    CUDA_TRY(ctx, cudaMalloc(&ctx->s_out, (size_t)(max_msgs + 16) * SLAB_PER_MSG + 4096));
+    ctx->dd_cap = cap;
+    ctx->cap_msgs = max_msgs;
+    ctx->cap_bytes = max_bytes;
+    return SMSGATE_OK;
+}
+
+extern "C" int smsgate_cache_load(smsgate_ctx* ctx, int64_t m, const uint8_t* h_keys, const int32_t* h_val_offsets,
+                                  const uint8_t* h_val_bytes, const uint16_t* h_eflags, const int64_t* h_date_packed) {
+    if (!ctx) return SMSGATE_E_ARG;
+    if (m < 0 || (m > 0 && (!h_keys || !h_val_offsets || !h_eflags || !h_date_packed)))
+        return fail(ctx, SMSGATE_E_ARG, "cache_load: NULL array");
+    if (m > 0x3FFFFFFFll) return fail(ctx, SMSGATE_E_LIMIT, "cache holds at most 2^30 entries");
+    CUDA_TRY(ctx, cudaSetDevice(ctx->device));
+    CUDA_TRY(ctx, cudaStreamSynchronize(ctx->stream));
+    free_cache(ctx);
+    if (m == 0) return SMSGATE_OK;
+    const int64_t vbytes = h_val_offsets[4 * m];
+    if (vbytes < 0 || (vbytes > 0 && !h_val_bytes)) return fail(ctx, SMSGATE_E_ARG, "cache_load: bad value offsets");
+    const uint64_t cap = pow2_at_least((uint64_t)m * 2);
+    CUDA_TRY(ctx, cudaMalloc(&ctx->c_keys, (size_t)m * 32));
+    CUDA_TRY(ctx, cudaMalloc(&ctx->c_table, cap * sizeof(int2)));
+    CUDA_TRY(ctx, cudaMalloc(&ctx->c_val_offsets, (size_t)(4 * m + 1) * 4));
+    CUDA_TRY(ctx, cudaMalloc(&ctx->c_val_bytes, (size_t)vbytes + 16));
+    CUDA_TRY(ctx, cudaMalloc(&ctx->c_eflags, (size_t)m * 2));
+    CUDA_TRY(ctx, cudaMalloc(&ctx->c_date_packed, (size_t)m * 8));
+    cudaStream_t st = ctx->stream;
+    CUDA_TRY(ctx, cudaMemcpyAsync(ctx->c_keys, h_keys, (size_t)m * 32, cudaMemcpyHostToDevice, st));
+    CUDA_TRY(ctx, cudaMemcpyAsync(ctx->c_val_offsets, h_val_offsets, (size_t)(4 * m + 1) * 4, cudaMemcpyHostToDevice, st));
+    if (vbytes) CUDA_TRY(ctx, cudaMemcpyAsync(ctx->c_val_bytes, h_val_bytes, (size_t)vbytes, cudaMemcpyHostToDevice, st));
+    CUDA_TRY(ctx, cudaMemcpyAsync(ctx->c_eflags, h_eflags, (size_t)m * 2, cudaMemcpyHostToDevice, st));
+    CUDA_TRY(ctx, cudaMemcpyAsync(ctx->c_date_packed, h_date_packed, (size_t)m * 8, cudaMemcpyHostToDevice, st));
+    CUDA_TRY(ctx, cudaMemsetAsync(ctx->c_table, 0xFF, cap * sizeof(int2), st));
+    int* d_dup = nullptr;
+    CUDA_TRY(ctx, cudaMalloc(&d_dup, 4));
+    CUDA_TRY(ctx, cudaMemsetAsync(d_dup, 0, 4, st));
+    k_cache_build<<<(unsigned)((m + 255) / 256), 256, 0, st>>>(ctx->c_keys, m, ctx->c_table, cap - 1, d_dup);
+    k_cache_fix_fp<<<(unsigned)((cap + 255) / 256), 256, 0, st>>>(ctx->c_keys, ctx->c_table, cap);
+    ctx->launches += 2;
+    int dup = 0;
+    CUDA_TRY(ctx, cudaMemcpyAsync(&dup, d_dup, 4, cudaMemcpyDeviceToHost, st));
+    CUDA_TRY(ctx, cudaStreamSynchronize(st));
+    cudaFree(d_dup);
+    CUDA_TRY(ctx, cudaGetLastError());
+    if (dup) {
+        free_cache(ctx);
+        return fail(ctx, SMSGATE_E_ARG, "cache_load: " + std::to_string(dup) + " duplicate key(s)");
+    }
+    ctx->cache_m = m;
+    ctx->c_cap = cap;
+    return SMSGATE_OK;
+}
+
+// ---- batch helpers
+extern "C" int smsgate_decimal_batch(smsgate_ctx* ctx, int64_t n, const int32_t* h_offsets, const uint8_t* h_bytes,
+                                     int64_t* h_coef, int32_t* h_exp, uint8_t* h_flags) {
+    if (!ctx) return SMSGATE_E_ARG;
+    if (n < 0 || (n > 0 && (!h_offsets || !h_coef || !h_exp || !h_flags))) return fail(ctx, SMSGATE_E_ARG, "decimal_batch: NULL array");
+    if (n == 0) return SMSGATE_OK;
+    CUDA_TRY(ctx, cudaSetDevice(ctx->device));
+    const int64_t nb = h_offsets[n];
+    int32_t* d_off = nullptr; uint8_t* d_b = nullptr; int64_t* d_c = nullptr; int32_t* d_e = nullptr; uint8_t* d_f = nullptr;
+    cudaStream_t st = ctx->stream;
+    int rc = SMSGATE_OK;
+    cudaError_t e;
+#define HB_TRY(expr) if ((e = (expr)) != cudaSuccess) { rc = fail(ctx, SMSGATE_E_CUDA, std::string(#expr) + ": " + cudaGetErrorString(e)); goto done; }
+    HB_TRY(cudaMalloc(&d_off, (size_t)(n + 1) * 4));
+    HB_TRY(cudaMalloc(&d_b, (size_t)nb + 16));
+    HB_TRY(cudaMalloc(&d_c, (size_t)n * 8));
+    HB_TRY(cudaMalloc(&d_e, (size_t)n * 4));
+    HB_TRY(cudaMalloc(&d_f, (size_t)n));
+    HB_TRY(cudaMemcpyAsync(d_off, h_offsets, (size_t)(n + 1) * 4, cudaMemcpyHostToDevice, st));
+    if (nb) HB_TRY(cudaMemcpyAsync(d_b, h_bytes, (size_t)nb, cudaMemcpyHostToDevice, st));
+    k_decimal_batch<<<(unsigned)((n + 255) / 256), 256, 0, st>>>(n, d_off, d_b, d_c, d_e, d_f);
+    ctx->launches += 1;
+    HB_TRY(cudaMemcpyAsync(h_coef, d_c, (size_t)n * 8, cudaMemcpyDeviceToHost, st));
+    HB_TRY(cudaMemcpyAsync(h_exp, d_e, (size_t)n * 4, cudaMemcpyDeviceToHost, st));
+    HB_TRY(cudaMemcpyAsync(h_flags, d_f, (size_t)n, cudaMemcpyDeviceToHost, st));
+    HB_TRY(cudaStreamSynchronize(st));
+    HB_TRY(cudaGetLastError());
+done:
+    cudaFree(d_off); cudaFree(d_b); cudaFree(d_c); cudaFree(d_e); cudaFree(d_f);
+    return rc;
+}
+
+extern "C" int smsgate_strict_date_batch(smsgate_ctx* ctx, int64_t n, const int32_t* h_offsets, const uint8_t* h_bytes,
+                                         int64_t* h_packed) {
+    if (!ctx) return SMSGATE_E_ARG;
+    if (n < 0 || (n > 0 && (!h_offsets || !h_packed))) return fail(ctx, SMSGATE_E_ARG, "strict_date_batch: NULL array");
+    if (n == 0) return SMSGATE_OK;
+    CUDA_TRY(ctx, cudaSetDevice(ctx->device));
+    const int64_t nb = h_offsets[n];
+    int32_t* d_off = nullptr; uint8_t* d_b = nullptr; int64_t* d_p = nullptr;
+    cudaStream_t st = ctx->stream;
+    int rc = SMSGATE_OK;
+    cudaError_t e;
+    HB_TRY(cudaMalloc(&d_off, (size_t)(n + 1) * 4));
+    HB_TRY(cudaMalloc(&d_b, (size_t)nb + 16));
+    HB_TRY(cudaMalloc(&d_p, (size_t)n * 8));
+    HB_TRY(cudaMemcpyAsync(d_off, h_offsets, (size_t)(n + 1) * 4, cudaMemcpyHostToDevice, st));
+    if (nb) HB_TRY(cudaMemcpyAsync(d_b, h_bytes, (size_t)nb, cudaMemcpyHostToDevice, st));
+    k_strict_date_batch<<<(unsigned)((n + 255) / 256), 256, 0, st>>>(n, d_off, d_b, d_p);
+    ctx->launches += 1;
+    HB_TRY(cudaMemcpyAsync(h_packed, d_p, (size_t)n * 8, cudaMemcpyDeviceToHost, st));
+    HB_TRY(cudaStreamSynchronize(st));
+    HB_TRY(cudaGetLastError());
+done:
+    cudaFree(d_off); cudaFree(d_b); cudaFree(d_p);
+    return rc;
+#undef HB_TRY
+}
+
+// ---- stages
+extern "C" int smsgate_scan_keys(smsgate_ctx* ctx, const uint8_t* d_bytes, const int64_t* d_offsets, int64_t n,
+                                 const smsgate_outputs* out) {
+    if (!ctx) return SMSGATE_E_ARG;
+    if (n < 0 || !out || (n > 0 && (!d_bytes || !d_offsets))) return fail(ctx, SMSGATE_E_ARG, "scan_keys: NULL argument");
+    if (((uintptr_t)d_bytes & 15) != 0) return fail(ctx, SMSGATE_E_ARG, "scan_keys: bytes must be 16-byte aligned");
+    if (n == 0) return SMSGATE_OK;
+    CUDA_TRY(ctx, cudaSetDevice(ctx->device));
+    ScanOut so{out->msg_id, out->cache_key, out->flags, out->body_date, out->fixed_len, out->fixed_bytes};
+    const int64_t ntiles = (n + K1_THREADS - 1) / K1_THREADS;
+    const int64_t maxgrid = (int64_t)ctx->sm_count * 4;
+    const unsigned grid = (unsigned)(ntiles < maxgrid ? ntiles : maxgrid);
+    k_scan_keys<<<grid, K1_THREADS, sizeof(K1Smem), ctx->stream>>>(d_bytes, d_offsets, n, ctx->d_tables, so);
+    ctx->launches += 1;
+    CUDA_TRY(ctx, cudaGetLastError());
+    return SMSGATE_OK;
+}
+
+extern "C" int smsgate_join_route(smsgate_ctx* ctx, int64_t n, int64_t now_packed, const smsgate_outputs* out) {
+    if (!ctx) return SMSGATE_E_ARG;
+    if (n < 0 || !out) return fail(ctx, SMSGATE_E_ARG, "join_route: NULL argument");
+    if (n == 0) return SMSGATE_OK;
+    if (!out->cache_key || !out->flags || !out->body_date)
+        return fail(ctx, SMSGATE_E_ARG, "join_route needs the cache_key, flags and body_date columns of stage 1");
+    CUDA_TRY(ctx, cudaSetDevice(ctx->device));
+    CacheView C{ctx->c_keys, ctx->c_table, ctx->c_cap ? ctx->c_cap - 1 : 0, ctx->c_val_offsets, ctx->c_val_bytes,
+                ctx->c_eflags, ctx->c_date_packed, ctx->cache_m};
+    JoinOut jo{out->slot, out->status, out->amount_coef, out->balance_coef, out->amount_exp, out->balance_exp,
+               out->dec_flags, out->date, out->card, out->card_len};
+    k_join_route<<<(unsigned)((n + 255) / 256), 256, 0, ctx->stream>>>(n, out->cache_key, out->flags, out->body_date,
+                                                                        now_packed, C, jo);
+    ctx->launches += 1;
+    CUDA_TRY(ctx, cudaGetLastError());
+    return SMSGATE_OK;
+}
+
+extern "C" int smsgate_dedup(smsgate_ctx* ctx, int64_t n, int64_t base_index, const smsgate_outputs* out) {
+    if (!ctx) return SMSGATE_E_ARG;
+    if (n < 0 || !out) return fail(ctx, SMSGATE_E_ARG, "dedup: NULL argument");
+    if (n == 0) return SMSGATE_OK;
+    if (!out->msg_id || !out->status) return fail(ctx, SMSGATE_E_ARG, "dedup needs the msg_id and status columns");
+    if (n > ctx->cap_msgs) return fail(ctx, SMSGATE_E_STATE, "dedup: batch larger than smsgate_reserve() sized the scratch for");
+    CUDA_TRY(ctx, cudaSetDevice(ctx->device));
+    // table sized for this batch (power of two >= 2n) inside the reserved arrays
+    uint64_t cap = pow2_at_least((uint64_t)(n > 8 ? n : 8) * 2);
+    if (cap > ctx->dd_cap) cap = ctx->dd_cap;
+    cudaStream_t st = ctx->stream;
+    CUDA_TRY(ctx, cudaMemsetAsync(ctx->d_owner, 0xFF, cap * 4, st));
+    CUDA_TRY(ctx, cudaMemsetAsync(ctx->d_first, 0x7F, cap * 4, st));
+    CUDA_TRY(ctx, cudaMemsetAsync(ctx->d_last, 0xFF, cap * 4, st));
+    DedupScratch D{ctx->d_owner, ctx->d_first, ctx->d_last, ctx->d_slot_of, cap - 1};
+    const unsigned grid = (unsigned)((n + 255) / 256);
+    k_dedup_insert<<<grid, 256, 0, st>>>(n, out->msg_id, out->status, D);
+    k_dedup_resolve<<<grid, 256, 0, st>>>(n, base_index, D, out->survivor, out->first_seen, out->last_idx);
+    ctx->launches += 2;
+    CUDA_TRY(ctx, cudaGetLastError());
+    return SMSGATE_OK;
+}
+
+extern "C" int smsgate_replay_device(smsgate_ctx* ctx, const uint8_t* d_bytes, const int64_t* d_offsets, int64_t n,
+                                     int64_t now_packed, int64_t base_index, const smsgate_outputs* out) {
+    int rc = smsgate_scan_keys(ctx, d_bytes, d_offsets, n, out);
+    if (rc) return rc;
+    rc = smsgate_join_route(ctx, n, now_packed, out);
+    if (rc) return rc;
+    return smsgate_dedup(ctx, n, base_index, out);
+}
+
+// carve the context's device slab into the output columns (alignment: widest first)
+static void carve_slab(uint8_t* slab, int64_t n, uint8_t* fixed, smsgate_outputs* d) {
+    auto take = [&](size_t bytes) {
+        uint8_t* p = slab;
+        slab += (bytes + 255) & ~(size_t)255;
+        return p;
+    };
+    d->amount_coef = (int64_t*)take((size_t)n * 8);
+    d->balance_coef = (int64_t*)take((size_t)n * 8);
+    d->date = (int64_t*)take((size_t)n * 8);
+    d->last_idx = (int64_t*)take((size_t)n * 8);
+    d->cache_key = take((size_t)n * 32);
+    d->msg_id = take((size_t)n * 20);
+    d->card = take((size_t)n * 16);
+    d->body_date = (int32_t*)take((size_t)n * 4);
+    d->fixed_len = (int32_t*)take((size_t)n * 4);
+    d->slot = (int32_t*)take((size_t)n * 4);
+    d->amount_exp = (int32_t*)take((size_t)n * 4);
+    d->balance_exp = (int32_t*)take((size_t)n * 4);
+    d->flags = take((size_t)n);
+    d->status = take((size_t)n);
+    d->dec_flags = take((size_t)n);
+    d->card_len = take((size_t)n);
+    d->survivor = take((size_t)n);
+    d->first_seen = take((size_t)n);
+    d->fixed_bytes = fixed;
+}
+
+extern "C" int smsgate_replay_host(smsgate_ctx* ctx, const uint8_t* h_bytes, const int64_t* h_offsets, int64_t n,
+                                   int64_t now_packed, int64_t base_index, const smsgate_outputs* h_out) {
+    if (!ctx) return SMSGATE_E_ARG;
+    if (n < 0 || !h_out || (n > 0 && (!h_offsets))) return fail(ctx, SMSGATE_E_ARG, "replay_host: NULL argument");
+    if (n == 0) return SMSGATE_OK;
+    const int64_t first = h_offsets[0], total = h_offsets[n];
+    if (first != 0) return fail(ctx, SMSGATE_E_ARG, "replay_host: offsets[0] must be 0");
+    if (total < 0 || (total > 0 && !h_bytes)) return fail(ctx, SMSGATE_E_ARG, "replay_host: bad offsets");
+    if (n > ctx->cap_msgs || total > ctx->cap_bytes)
+        return fail(ctx, SMSGATE_E_STATE, "replay_host: batch larger than smsgate_reserve() sized the scratch for");
+    CUDA_TRY(ctx, cudaSetDevice(ctx->device));
+    cudaStream_t st = ctx->stream;
+    CUDA_TRY(ctx, cudaMemcpyAsync(ctx->s_offsets, h_offsets, (size_t)(n + 1) * 8, cudaMemcpyHostToDevice, st));
+    if (total) CUDA_TRY(ctx, cudaMemcpyAsync(ctx->s_bytes, h_bytes, (size_t)total, cudaMemcpyHostToDevice, st));
+    smsgate_outputs d;
+    carve_slab(ctx->s_out, n, ctx->s_fixed, &d);
+    int rc = smsgate_replay_device(ctx, ctx->s_bytes, ctx->s_offsets, n, now_packed, base_index, &d);
+    if (rc) return rc;
+#define BACK(col, bytes) \
+    if (h_out->col) CUDA_TRY(ctx, cudaMemcpyAsync(h_out->col, d.col, (size_t)(bytes), cudaMemcpyDeviceToHost, st))
+    BACK(msg_id, n * 20); BACK(cache_key, n * 32); BACK(flags, n); BACK(body_date, n * 4); BACK(fixed_len, n * 4);
+    BACK(slot, n * 4); BACK(status, n); BACK(amount_coef, n * 8); BACK(balance_coef, n * 8); BACK(amount_exp, n * 4);
+    BACK(balance_exp, n * 4); BACK(dec_flags, n); BACK(date, n * 8); BACK(card, n * 16); BACK(card_len, n);
+    BACK(survivor, n); BACK(first_seen, n); BACK(last_idx, n * 8);
+    if (h_out->fixed_bytes && total) BACK(fixed_bytes, total);
+#undef BACK
+    CUDA_TRY(ctx, cudaStreamSynchronize(st));
+    CUDA_TRY(ctx, cudaGetLastError());
+    return SMSGATE_OK;
+}

@@ -1,0 +1,182 @@
+"""Loader for the Gemini response cache: turns the reference's
+`diskcache.Cache(".gemini_cache")` (libs/gemini_parser.py:33) — a mapping
+hex(SHA-256(fixed_body)) -> response dict (schema :46-61) — into the flat
+arrays `smsgate_cache_load` builds the device hash table from.
+
+What is decided here, once per cache entry at load time, is only what does
+not depend on the message: which schema facts hold (the keys the reference
+indexes, the types pydantic would accept, libs/llm_core.py:9-19) and, for
+date strings outside the strict `dd.mm.yy HH:MM` form the GPU parses, what
+the reference's own `strptime` -> `dateutil` chain makes of them
+(libs/gemini_parser.py:106-119).  Amounts, balances, cards and strict dates
+stay strings and are evaluated per message on the GPU.
+"""
+from __future__ import annotations
+
+import datetime as _dt
+from dataclasses import dataclass, field
+from typing import Any, Mapping, Optional
+
+import numpy as np
+
+from . import _lib as L
+
+_TXN_VALUES = ("debit", "credit", "otp", "unknown")
+_NINE = ("txn_type", "date", "amount", "currency", "card", "merchant", "city", "address", "balance")
+_HEX = set("0123456789abcdef")
+
+
+def pack_datetime(d: _dt.datetime) -> int:
+    return ((d.year << 46) | (d.month << 42) | (d.day << 37) | (d.hour << 32) | (d.minute << 26)
+            | (d.second << 20) | d.microsecond)
+
+
+def unpack_datetime(p: int) -> _dt.datetime:
+    p = int(p)
+    return _dt.datetime(p >> 46, (p >> 42) & 15, (p >> 37) & 31, (p >> 32) & 31, (p >> 26) & 63,
+                        (p >> 20) & 63, p & 0xFFFFF)
+
+
+_dt_adapter = None
+
+
+def _host_date(value: Any):
+    """The reference's chain for a cached `date` the GPU does not parse:
+    strptime, else dateutil, else (date left as it was) what pydantic makes of
+    the raw value.  Returns (kind, datetime | None)."""
+    global _dt_adapter
+    try:
+        return "dt", _dt.datetime.strptime(value, "%d.%m.%y %H:%M")
+    except Exception:
+        pass
+    try:
+        from dateutil.parser import parse
+        return "dt", parse(value)
+    except Exception as e:
+        if "String does not contain a date" in str(e):
+            return "rawdate", None          # falls back to int(raw.date): raises for XML-sourced messages
+    try:
+        if _dt_adapter is None:
+            from pydantic import TypeAdapter
+            _dt_adapter = TypeAdapter(_dt.datetime)
+        return "nobody", _dt_adapter.validate_python(value)
+    except Exception:
+        return "bad", None
+
+
+def _str_or_none_ok(v: Any) -> bool:
+    return v is None or type(v) is str or (isinstance(v, str))
+
+
+@dataclass
+class CacheTable:
+    """Flat form of the response cache + the dicts for materialising ParsedSMS."""
+    keys: np.ndarray                 # uint8 [m, 32]
+    val_offsets: np.ndarray          # int32 [4m+1]
+    val_bytes: np.ndarray            # uint8
+    eflags: np.ndarray               # uint16 [m]
+    date_packed: np.ndarray          # int64 [m]
+    values: list                     # the cached objects, entry order
+    host_dates: dict = field(default_factory=dict)   # entry -> datetime (non-strict dates)
+    skipped: int = 0                 # keys that are not 64 lowercase hex chars (can never be probed)
+
+    @property
+    def m(self) -> int:
+        return len(self.values)
+
+
+def build_table(mapping: Mapping[str, Any], strict_date_batch) -> CacheTable:
+    """`strict_date_batch(list[str]) -> int64 array` is the GPU call
+    (ReplayEngine.strict_date_batch); entries it answers -1 for are resolved by
+    `_host_date`."""
+    keys, values = [], []
+    skipped = 0
+    for k, v in mapping.items() if hasattr(mapping, "items") else ((k, mapping[k]) for k in mapping):
+        if not (isinstance(k, str) and len(k) == 64 and set(k) <= _HEX):
+            skipped += 1
+            continue
+        keys.append(k)
+        values.append(v)
+    m = len(values)
+    eflags = np.zeros(m, dtype=np.uint16)
+    date_packed = np.zeros(m, dtype=np.int64)
+    parts: list = []
+    date_strs: list = []
+    date_idx: list = []
+    host_dates: dict = {}
+    for e, v in enumerate(values):
+        f = 0
+        amount = balance = date_s = card = ""
+        if isinstance(v, dict):
+            f |= L.E_IS_DICT
+            if "txn_type" in v:
+                f |= L.E_HAS_TXN
+            ok = all(k in v for k in _NINE)
+            if ok:
+                t = v["txn_type"]
+                ok = (isinstance(t, str) and (t in _TXN_VALUES)) and all(
+                    _str_or_none_ok(v[k]) for k in ("currency", "merchant", "city", "address"))
+            if ok:
+                f |= L.E_SCHEMA_OK
+            if "amount" in v:
+                amount = str(v["amount"])
+            if "balance" in v:
+                balance = str(v["balance"])
+            c = v.get("card")
+            if isinstance(c, str):
+                f |= L.E_CARD_STR
+                card = c
+            mer = v.get("merchant")
+            if isinstance(mer, str) and mer:
+                f |= L.E_MERCHANT
+            if "date" in v:
+                f |= L.E_DATE_KEY
+                d = v["date"]
+                if type(d) is str and d.isascii() and len(d) <= 32:
+                    date_s = d
+                    date_strs.append(d)
+                    date_idx.append(e)
+                else:
+                    kind, obj = _host_date(d)
+                    f |= _apply_host_date(kind, obj, e, date_packed, host_dates)
+        eflags[e] = f
+        parts.append(amount.encode("utf-8"))
+        parts.append(balance.encode("utf-8"))
+        parts.append(date_s.encode("utf-8"))
+        parts.append(card.encode("utf-8"))
+    if date_strs:
+        packed = strict_date_batch(date_strs)
+        for j, e in enumerate(date_idx):
+            if packed[j] > 0:
+                eflags[e] |= L.E_DATE_STRICT
+                date_packed[e] = packed[j]
+            else:
+                kind, obj = _host_date(values[e]["date"])
+                eflags[e] |= _apply_host_date(kind, obj, e, date_packed, host_dates)
+    val_offsets = np.zeros(4 * m + 1, dtype=np.int64)
+    if parts:
+        np.cumsum(np.fromiter((len(p) for p in parts), dtype=np.int64, count=len(parts)), out=val_offsets[1:])
+    if val_offsets[-1] >= 2 ** 31:
+        raise ValueError("cache value strings exceed 2 GiB")
+    key_arr = (np.frombuffer(bytes.fromhex("".join(keys)), dtype=np.uint8).reshape(m, 32).copy()
+               if m else np.zeros((0, 32), dtype=np.uint8))
+    return CacheTable(keys=key_arr, val_offsets=val_offsets.astype(np.int32),
+                      val_bytes=np.frombuffer(b"".join(parts), dtype=np.uint8).copy(), eflags=eflags,
+                      date_packed=date_packed, values=values, host_dates=host_dates, skipped=skipped)
+
+
+def _apply_host_date(kind: str, obj, e: int, date_packed: np.ndarray, host_dates: dict) -> int:
+    if kind == "dt" or kind == "nobody":
+        date_packed[e] = pack_datetime(obj)
+        host_dates[e] = obj
+        f = L.E_DATE_HOST if kind == "dt" else L.E_DATE_NOBODY
+        if obj.tzinfo is not None:
+            f |= L.E_DATE_TZ
+        return f
+    return 0
+
+
+def open_diskcache(path: str) -> Mapping[str, Any]:
+    """The on-disk cache as the reference opens it (diskcache 5.6.3, pickled dicts)."""
+    import diskcache
+    return diskcache.Cache(path)

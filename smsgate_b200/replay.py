@@ -1,0 +1,275 @@
+"""Bulk replay engine: the Python face of libsmsgate_b200.so.
+
+One `ReplayEngine` = one GPU = one C-ABI context.  It does what the reference
+does to every message of a backup between `_iter_sms` and the PocketBase /
+Postgres upsert (services/xml_watcher/watcher.py:35-54,
+services/parser_worker/worker.py:112-189, libs/gemini_parser.py:193-271,
+services/pb_writer/writer.py:65-84) for a whole batch at once, and hands the
+results back either as flat columns or, lazily, as the reference's own
+`ParsedSMS` objects.
+
+torch is used for device memory and streams only.
+"""
+from __future__ import annotations
+
+import ctypes as C
+import datetime as _dt
+from decimal import Decimal
+from typing import Any, Mapping, Optional, Sequence
+
+import numpy as np
+
+from . import _lib as L
+from .batch import Batch, ragged_from_strings
+from .gemini_cache import CacheTable, build_table, pack_datetime, unpack_datetime
+from .models import BrokenMessage, ParsedSMS
+
+
+class CacheMiss(RuntimeError):
+    """The body is not in the Gemini response cache; the reference would call
+    Gemini here (libs/gemini_parser.py:210-222), which is out of scope offline."""
+
+
+def _np_ptr(a: Optional[np.ndarray]):
+    return None if a is None else a.ctypes.data_as(C.c_void_p)
+
+
+class ReplayResult:
+    """Columns of one replayed batch (numpy, host) + lazy ParsedSMS views."""
+
+    def __init__(self, batch: Batch, cols: dict, table: Optional[CacheTable], base_index: int):
+        self.batch = batch
+        self.cols = cols
+        self.table = table
+        self.base_index = base_index
+
+    def __getattr__(self, name):
+        cols = self.__dict__.get("cols", {})
+        if name in cols:
+            return cols[name]
+        raise AttributeError(name)
+
+    @property
+    def n(self) -> int:
+        return self.batch.n
+
+    def msg_id_hex(self, i: int) -> str:
+        return self.cols["msg_id"][i].tobytes().hex()
+
+    def cache_key_hex(self, i: int) -> str:
+        return self.cols["cache_key"][i].tobytes().hex()
+
+    def fixed_body(self, i: int) -> str:
+        """fixed_body of message i (libs/gemini_parser.py:202-203) = ParsedSMS.raw_body."""
+        a = int(self.batch.body_offsets[i])
+        if self.cols["flags"][i] & L.F_MODIFIED:
+            return self.cols["fixed_bytes"][a:a + int(self.cols["fixed_len"][i])].tobytes().decode("utf-8")
+        return self.batch.body(i)
+
+    def decimal(self, which: str, i: int) -> Decimal:
+        fl = int(self.cols["dec_flags"][i])
+        err = (fl & 3) if which == "amount" else ((fl >> 2) & 3)
+        sign = (fl >> 4) & 1 if which == "amount" else (fl >> 5) & 1
+        if err == L.DEC_SYNTAX:
+            raise ValueError(f"{which} of message {i} is not a number")
+        if err == L.DEC_OVERFLOW:
+            raise OverflowError(f"{which} of message {i} has more than 18 significant digits")
+        coef = int(self.cols[which + "_coef"][i])
+        return Decimal((sign, tuple(int(ch) for ch in str(coef)), int(self.cols[which + "_exp"][i])))
+
+    def datetime(self, i: int) -> Optional[_dt.datetime]:
+        p = int(self.cols["date"][i])
+        if p == 0:
+            return None
+        e = int(self.cols["slot"][i])
+        if self.table is not None and e in self.table.host_dates and not (self.cols["flags"][i] & L.F_BODY_DATE):
+            return self.table.host_dates[e]        # keeps tzinfo / exact object of non-strict dates
+        return unpack_datetime(p)
+
+    def parsed(self, i: int, sender: Optional[str] = None, device_id: Optional[str] = "xml_backup",
+               msg_id: Optional[str] = None) -> Optional[ParsedSMS]:
+        """What `parse_sms_llm` returns (or raises) for message i."""
+        st = int(self.cols["status"][i])
+        if st == L.ST_CACHE_MISS:
+            raise CacheMiss(self.cache_key_hex(i))
+        if st == L.ST_BROKEN:
+            raise BrokenMessage("no card number in the message")
+        if st in (L.ST_SKIPPED_FILTER, L.ST_UNMATCHED):
+            return None
+        e = int(self.cols["slot"][i])
+        v = self.table.values[e]
+        if st == L.ST_FAILED_EXC and not (isinstance(v, dict) and "txn_type" in v):
+            raise KeyError("txn_type")
+        if sender is None:
+            sender = self.batch.senders[i] if self.batch.senders is not None else ""
+        address = v.get("address")
+        return ParsedSMS(
+            msg_id=msg_id if msg_id is not None else self.msg_id_hex(i), device_id=device_id, sender=sender,
+            date=self.datetime(i), raw_body=self.fixed_body(i), txn_type=v["txn_type"],
+            amount=self.decimal("amount", i), currency=v.get("currency"),
+            card=self.cols["card"][i, :int(self.cols["card_len"][i])].tobytes().decode("utf-8"),
+            merchant=v.get("merchant"), city=v.get("city"), address="" if address == "null" else address,
+            balance=self.decimal("balance", i), parser_version="llm-0.2.0")
+
+    def status_counts(self) -> dict:
+        c = np.bincount(self.cols["status"], minlength=8)
+        return {L.STATUS_NAMES[k]: int(c[k]) for k in range(8)}
+
+    def dlq_indices(self) -> np.ndarray:
+        """Messages the reference would publish to sms.failed (libs/nats_utils.py:28)."""
+        return np.nonzero(np.isin(self.cols["status"], L.DLQ_STATUSES))[0]
+
+    def survivor_indices(self) -> np.ndarray:
+        return np.nonzero(self.cols["survivor"])[0]
+
+    def upserts(self) -> dict:
+        """msg_id hex -> ParsedSMS of the record that remains after the replay."""
+        return {self.msg_id_hex(int(i)): self.parsed(int(i)) for i in self.survivor_indices()}
+
+
+class ReplayEngine:
+    def __init__(self, device: int = 0, use_torch_stream: bool = True):
+        self._lib = L.lib()
+        self._ctx = C.c_void_p()
+        self.device = device
+        stream = None
+        if use_torch_stream:
+            import torch
+            if not torch.cuda.is_available():
+                raise RuntimeError("smsgate_b200 needs a CUDA device (B200, sm_100a); there is no CPU path")
+            torch.cuda.set_device(device)
+            stream = C.c_void_p(torch.cuda.current_stream(device).cuda_stream)
+        rc = self._lib.smsgate_create(device, stream, C.byref(self._ctx))
+        if rc != 0:
+            raise L.SmsgateError(rc, (self._lib.smsgate_last_error(None) or b"").decode())
+        self.table: Optional[CacheTable] = None
+        self._pinned: dict = {}
+
+    # -- lifecycle ---------------------------------------------------------
+    def close(self):
+        if getattr(self, "_ctx", None) is not None and self._ctx.value:
+            self._lib.smsgate_destroy(self._ctx)
+            self._ctx = C.c_void_p()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def __enter__(self):
+        return self
+
+    def __exit__(self, *exc):
+        self.close()
+
+    def reserve(self, max_msgs: int, max_bytes: int) -> None:
+        L.check(self._ctx, self._lib.smsgate_reserve(self._ctx, int(max_msgs), int(max_bytes)))
+
+    @property
+    def launch_count(self) -> int:
+        return int(self._lib.smsgate_launch_count(self._ctx))
+
+    # -- cache -------------------------------------------------------------
+    def load_cache(self, cache: "Mapping[str, Any] | CacheTable") -> CacheTable:
+        table = cache if isinstance(cache, CacheTable) else build_table(cache, self.strict_date_batch)
+        keys = np.ascontiguousarray(table.keys)
+        L.check(self._ctx, self._lib.smsgate_cache_load(
+            self._ctx, table.m, _np_ptr(keys), _np_ptr(table.val_offsets), _np_ptr(table.val_bytes),
+            _np_ptr(table.eflags), _np_ptr(table.date_packed)))
+        self.table = table
+        return table
+
+    # -- batch helpers -----------------------------------------------------
+    def decimal_batch(self, strings: Sequence[str]):
+        """parse_ambiguous_decimal over many strings -> (coef int64, exp int32, flags uint8)."""
+        data, offsets = ragged_from_strings(strings, np.int32)
+        n = len(strings)
+        coef, exp, flags = np.zeros(n, np.int64), np.zeros(n, np.int32), np.zeros(n, np.uint8)
+        L.check(self._ctx, self._lib.smsgate_decimal_batch(self._ctx, n, _np_ptr(offsets), _np_ptr(data),
+                                                           _np_ptr(coef), _np_ptr(exp), _np_ptr(flags)))
+        return coef, exp, flags
+
+    def strict_date_batch(self, strings: Sequence[str]) -> np.ndarray:
+        data, offsets = ragged_from_strings(strings, np.int32)
+        n = len(strings)
+        out = np.zeros(n, np.int64)
+        L.check(self._ctx, self._lib.smsgate_strict_date_batch(self._ctx, n, _np_ptr(offsets), _np_ptr(data),
+                                                               _np_ptr(out)))
+        return out
+
+    # -- host-buffer replay (the end-to-end call) ----------------------------
+    def _host_columns(self, n: int, total: int, want: Sequence[str], pinned: bool) -> dict:
+        cols = {}
+        for name, dt, width in L.COLUMNS:
+            if name not in want:
+                continue
+            shape = (total,) if name == "fixed_bytes" else ((n, width) if width > 1 else (n,))
+            if pinned:
+                import torch
+                tdt = {"u1": torch.uint8, "i4": torch.int32, "i8": torch.int64}[dt]
+                key = (name, shape)
+                t = self._pinned.get(key)
+                if t is None:
+                    t = torch.empty(shape, dtype=tdt, pin_memory=True)
+                    self._pinned[key] = t
+                cols[name] = t.numpy()
+            else:
+                cols[name] = np.zeros(shape, dtype=np.dtype(dt))
+        return cols
+
+    ALL_COLUMNS = tuple(name for name, _, _ in L.COLUMNS)
+
+    def replay(self, batch: Batch, now: _dt.datetime, base_index: int = 0,
+               columns: Optional[Sequence[str]] = None, pinned: bool = False) -> ReplayResult:
+        """Replay a host-resident batch end to end (host->device copy, three
+        kernel stages, device->host copy of the requested columns)."""
+        n = batch.n
+        total = int(batch.body_offsets[-1]) if n else 0
+        self.reserve(max(n, 1), max(total, 1))
+        want = tuple(columns) if columns is not None else self.ALL_COLUMNS
+        cols = self._host_columns(n, total, want, pinned)
+        out = L.Outputs(**{k: (v.ctypes.data if v.size else None) for k, v in cols.items()})
+        body = np.ascontiguousarray(batch.body_bytes)
+        offs = np.ascontiguousarray(batch.body_offsets, dtype=np.int64)
+        L.check(self._ctx, self._lib.smsgate_replay_host(self._ctx, _np_ptr(body), _np_ptr(offs), n,
+                                                         pack_datetime(now), int(base_index), C.byref(out)))
+        return ReplayResult(batch, cols, self.table, base_index)
+
+    # -- device-pointer stages (torch tensors) -------------------------------
+    def device_columns(self, n: int, total: int, want: Optional[Sequence[str]] = None) -> dict:
+        import torch
+        want = tuple(want) if want is not None else self.ALL_COLUMNS
+        dev = torch.device("cuda", self.device)
+        cols = {}
+        for name, dt, width in L.COLUMNS:
+            if name not in want:
+                continue
+            tdt = {"u1": torch.uint8, "i4": torch.int32, "i8": torch.int64}[dt]
+            shape = (max(total, 1),) if name == "fixed_bytes" else ((n, width) if width > 1 else (n,))
+            cols[name] = torch.empty(shape, dtype=tdt, device=dev)
+        return cols
+
+    @staticmethod
+    def _dev_outputs(cols: dict) -> L.Outputs:
+        return L.Outputs(**{k: v.data_ptr() for k, v in cols.items()})
+
+    def scan_keys(self, d_bytes, d_offsets, cols: dict) -> None:
+        n = d_offsets.numel() - 1
+        out = self._dev_outputs(cols)
+        L.check(self._ctx, self._lib.smsgate_scan_keys(self._ctx, d_bytes.data_ptr(), d_offsets.data_ptr(), n,
+                                                       C.byref(out)))
+
+    def join_route(self, n: int, now: _dt.datetime, cols: dict) -> None:
+        out = self._dev_outputs(cols)
+        L.check(self._ctx, self._lib.smsgate_join_route(self._ctx, n, pack_datetime(now), C.byref(out)))
+
+    def dedup(self, n: int, base_index: int, cols: dict) -> None:
+        out = self._dev_outputs(cols)
+        L.check(self._ctx, self._lib.smsgate_dedup(self._ctx, n, int(base_index), C.byref(out)))
+
+    def replay_device(self, d_bytes, d_offsets, now: _dt.datetime, cols: dict, base_index: int = 0) -> None:
+        n = d_offsets.numel() - 1
+        out = self._dev_outputs(cols)
+        L.check(self._ctx, self._lib.smsgate_replay_device(self._ctx, d_bytes.data_ptr(), d_offsets.data_ptr(), n,
+                                                           pack_datetime(now), int(base_index), C.byref(out)))

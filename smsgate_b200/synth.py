@@ -87,11 +87,17 @@ def generate(n: int, *, seed: int = 0x5EED, otp_frac: float = 0.05, dup_frac: fl
 
     bodies, kinds = [], []
     cache: dict = {}
+    # one distinct (date, time) per message keeps bodies pairwise distinct; string tables avoid strftime per message
+    base_min = base_date.hour * 60 + base_date.minute
+    n_days = (base_min + min(n_distinct, 900_000)) // 1440 + n_distinct // 900_000 + 2
+    day0 = base_date.date()
+    d2_tab = [(day0 + _dt.timedelta(days=k)).strftime("%d.%m.%y") for k in range(n_days)]
+    d4_tab = [(day0 + _dt.timedelta(days=k)).strftime("%d.%m.%Y") for k in range(n_days)]
+    hm_tab = [f"{k // 60:02d}:{k % 60:02d}" for k in range(1440)]
     for i in range(n_distinct):
-        when = base_date + _dt.timedelta(minutes=int(i % 900_000), days=int(i // 900_000))
-        d2 = when.strftime("%d.%m.%y")
-        d4 = when.strftime("%d.%m.%Y")
-        hm = when.strftime("%H:%M")
+        tmin = base_min + i % 900_000
+        day = tmin // 1440 + i // 900_000
+        d2, d4, hm = d2_tab[day], d4_tab[day], hm_tab[tmin % 1440]
         m = f"{MERCHANT_WORDS[merch_i[i]]} {merch_no[i]}"
         city = CITIES[city_i[i]]
         ccy = CURRENCIES[ccy_i[i]]

@@ -1,0 +1,71 @@
+"""TEST ONLY: ctypes wrapper over tests/hostcheck/libhostcheck.so, the CPU build
+of the kernels' __host__ __device__ cores (see hostcheck.cpp).  It exists so the
+device logic can be checked in a container without a GPU; the product never
+loads it."""
+import ctypes as C
+
+import numpy as np
+
+from smsgate_b200 import build
+from smsgate_b200.batch import ragged_from_strings
+
+_lib = None
+
+
+def lib():
+    global _lib
+    if _lib is None:
+        _lib = C.CDLL(build.build_hostcheck())
+    return _lib
+
+
+def _p(a):
+    return a.ctypes.data_as(C.c_void_p)
+
+
+def scan(bodies):
+    data, offsets = ragged_from_strings(bodies)
+    n = len(bodies)
+    cols = dict(msg_id=np.zeros((n, 20), np.uint8), cache_key=np.zeros((n, 32), np.uint8),
+                flags=np.zeros(n, np.uint8), body_date=np.zeros(n, np.int32), fixed_len=np.zeros(n, np.int32),
+                fixed_bytes=np.zeros(max(len(data), 1), np.uint8))
+    data = np.concatenate([data, np.zeros(16, np.uint8)])
+    lib().hc_scan_keys(_p(data), _p(offsets), C.c_int64(n), _p(cols["msg_id"]), _p(cols["cache_key"]),
+                       _p(cols["flags"]), _p(cols["body_date"]), _p(cols["fixed_len"]), _p(cols["fixed_bytes"]))
+    cols["offsets"] = offsets
+    return cols
+
+
+def decimal(strings):
+    data, offsets = ragged_from_strings(strings, np.int32)
+    n = len(strings)
+    coef, exp, flags = np.zeros(n, np.int64), np.zeros(n, np.int32), np.zeros(n, np.uint8)
+    data = np.concatenate([data, np.zeros(16, np.uint8)])
+    lib().hc_decimal(C.c_int64(n), _p(offsets), _p(data), _p(coef), _p(exp), _p(flags))
+    return coef, exp, flags
+
+
+def strict_date(strings):
+    data, offsets = ragged_from_strings(strings, np.int32)
+    n = len(strings)
+    out = np.zeros(n, np.int64)
+    data = np.concatenate([data, np.zeros(16, np.uint8)])
+    lib().hc_strict_date(C.c_int64(n), _p(offsets), _p(data), _p(out))
+    return out
+
+
+def join_route(scan_cols, table, now_packed):
+    n = len(scan_cols["flags"])
+    cols = dict(slot=np.zeros(n, np.int32), status=np.zeros(n, np.uint8), amount_coef=np.zeros(n, np.int64),
+                balance_coef=np.zeros(n, np.int64), amount_exp=np.zeros(n, np.int32),
+                balance_exp=np.zeros(n, np.int32), dec_flags=np.zeros(n, np.uint8), date=np.zeros(n, np.int64),
+                card=np.zeros((n, 16), np.uint8), card_len=np.zeros(n, np.uint8))
+    keys = np.ascontiguousarray(table.keys)
+    vb = np.concatenate([table.val_bytes, np.zeros(16, np.uint8)])
+    lib().hc_join_route(C.c_int64(n), _p(scan_cols["cache_key"]), _p(scan_cols["flags"]), _p(scan_cols["body_date"]),
+                        C.c_int64(now_packed), C.c_int64(table.m), _p(keys), _p(table.val_offsets), _p(vb),
+                        _p(table.eflags), _p(table.date_packed), _p(cols["slot"]), _p(cols["status"]),
+                        _p(cols["amount_coef"]), _p(cols["balance_coef"]), _p(cols["amount_exp"]),
+                        _p(cols["balance_exp"]), _p(cols["dec_flags"]), _p(cols["date"]), _p(cols["card"]),
+                        _p(cols["card_len"]))
+    return cols

@@ -1,0 +1,128 @@
+"""The kernels' per-message cores (same source, compiled for the CPU by
+tests/hostcheck) against the golden vectors.  This pins the device LOGIC in a
+GPU-less container; tests/test_gpu_parity.py runs the real kernels."""
+import datetime as dt
+
+import numpy as np
+import pytest
+
+from oracle import replay_oracle as O
+from smsgate_b200 import _lib as L
+from smsgate_b200 import gemini_cache, synth
+from tests import _hostcheck as H
+
+STATUS = {n: i for i, n in enumerate(L.STATUS_NAMES)}
+
+
+def test_scan_matches_reference_vectors(golden):
+    cases = golden("keys.json")
+    bodies = [c["body"] for c in cases]
+    cols = H.scan(bodies)
+    off = cols["offsets"]
+    for i, c in enumerate(cases):
+        assert cols["msg_id"][i].tobytes().hex() == c["msg_id"], c["body"]
+        fl = int(cols["flags"][i])
+        assert bool(fl & L.F_WORKER_SKIP) == c["worker_skip"], c["body"]
+        assert bool(fl & L.F_PARSER_OTP) == c["parser_otp"], c["body"]
+        a = int(off[i])
+        fixed = cols["fixed_bytes"][a:a + int(cols["fixed_len"][i])].tobytes().decode()
+        assert fixed == c["fixed"], c["body"]
+        assert bool(fl & L.F_MODIFIED) == (c["fixed"] != c["body"]), c["body"]
+        assert cols["cache_key"][i].tobytes().hex() == c["cache_key"], c["body"]
+        want = 0 if c["body_date"] is None else O.pack_date(dt.date.fromisoformat(c["body_date"]))
+        assert int(cols["body_date"][i]) == want, c["body"]
+
+
+def test_decimals_match_reference_vectors(golden):
+    rows = golden("decimals.json")
+    coef, exp, flags = H.decimal([r[0] for r in rows])
+    for i, r in enumerate(rows):
+        err = int(flags[i]) & 3
+        if r[1] == "ValueError":
+            assert err == L.DEC_SYNTAX, r[0]
+        elif int(r[3]) > O.INT64_MAX:
+            assert err == L.DEC_OVERFLOW, r[0]
+        else:
+            assert (err, (int(flags[i]) >> 4) & 1, int(coef[i]), int(exp[i])) == (0, r[2], int(r[3]), r[4]), r[0]
+
+
+def test_strict_date_is_a_sound_subset_of_strptime():
+    import random
+    rnd = random.Random(3)
+    alphabet = "0123456789" * 4 + "..::  \t-/a"
+    cases = ["06.05.25 14:23", "6.5.25 4:23", "06.05.25  14:23", " 6.05.25 14:23", "06.05.25 14:23 ", "32.05.25 14:23",
+             "31.02.25 10:00", "29.02.24 23:59", "29.02.23 23:59", "01.01.69 00:00", "01.01.68 00:00", "00.05.25 10:00",
+             "06.00.25 10:00", "06.13.25 1:1", "06.05.25 24:00", "06.05.25 14:60", "06.05.25 7:5", "06.05.2025 14:23",
+             "31.12.99 23:59", "1.1.00 0:0", "31.04.25 10:00", "30.04.25 10:00", "06.05.25\t14:23", "06.05.25\n14:23",
+             "", "1", "06.05.25", "06.05.25 ", "06.05.25 1", "06.05.25 1:", "06.05.25 :1"]
+    for _ in range(3000):
+        d, m, y = rnd.randint(0, 40), rnd.randint(0, 15), rnd.randint(0, 99)
+        h, mi = rnd.randint(0, 30), rnd.randint(0, 70)
+        fmt = rnd.choice(["{:02d}.{:02d}.{:02d} {:02d}:{:02d}", "{}.{}.{:02d} {}:{}", "{:02d}.{}.{:02d}  {}:{:02d}"])
+        cases.append(fmt.format(d, m, y, h, mi))
+    for _ in range(2000):
+        cases.append("".join(rnd.choice(alphabet) for _ in range(rnd.randint(0, 16))))
+    got = H.strict_date(cases)
+    accepted = 0
+    for s, p in zip(cases, got):
+        try:
+            want = dt.datetime.strptime(s, "%d.%m.%y %H:%M")
+        except ValueError:
+            want = None
+        if p > 0:                         # whenever the GPU form accepts, it must agree with strptime
+            assert want is not None and gemini_cache.pack_datetime(want) == int(p), s
+            accepted += 1
+        elif want is not None:            # it may only decline strings outside the plain ASCII form
+            assert not s.isascii() or s != s.strip() or any(ch in s for ch in "\x0b\x0c\x1c\x1d\x1e\x1f"), s
+    assert accepted > 500
+
+
+def _table(mapping):
+    return gemini_cache.build_table(mapping, H.strict_date)
+
+
+def test_parse_matrix_status_and_fields(golden):
+    now = dt.datetime(2026, 1, 1)
+    for c in golden("parse_matrix.json"):
+        if c["raw_date"].lstrip("-").isdigit():
+            continue                      # device-source raw.date (unix seconds): not an XML-replay case
+        sc = H.scan([c["body"]])
+        key = sc["cache_key"][0].tobytes().hex()
+        table = _table({key: c["resp"]})
+        jr = H.join_route(sc, table, gemini_cache.pack_datetime(now))
+        assert int(jr["status"][0]) == STATUS[c["status"]], c["name"]
+        p = c["parsed"]
+        if p is None or c["status"] == "FAILED_EXC":
+            continue
+        got_date = gemini_cache.unpack_datetime(jr["date"][0])
+        assert got_date.isoformat() == p["date"], c["name"]
+        assert jr["card"][0, :int(jr["card_len"][0])].tobytes().decode() == p["card"], c["name"]
+        fl = int(jr["dec_flags"][0])
+        for which, sh, sg in (("amount", 0, 4), ("balance", 2, 5)):
+            sign, digits, exp = p[which]
+            if int(digits) > O.INT64_MAX:
+                assert (fl >> sh) & 3 == L.DEC_OVERFLOW
+            else:
+                assert ((fl >> sh) & 3, (fl >> sg) & 1, int(jr[which + "_coef"][0]), int(jr[which + "_exp"][0])) == \
+                    (0, sign, int(digits), exp), c["name"]
+
+
+@pytest.mark.parametrize("name", ["replay_plain.json", "replay_mixed.json"])
+def test_replay_against_reference_run(golden, name):
+    g = golden(name)
+    backup = synth.generate(g["n"], seed=g["seed"], **g["kwargs"])
+    now = dt.datetime.fromisoformat(g["now"])
+    sc = H.scan(backup.bodies)
+    table = _table(backup.cache)
+    jr = H.join_route(sc, table, gemini_cache.pack_datetime(now))
+    for i, r in enumerate(g["rows"]):
+        assert sc["msg_id"][i].tobytes().hex() == r["msg_id"]
+        assert int(jr["status"][i]) == STATUS[r["status"]], i
+        if r["cache_key"] is not None:
+            assert sc["cache_key"][i].tobytes().hex() == r["cache_key"]
+        p = r["parsed"]
+        if p is not None:
+            assert gemini_cache.unpack_datetime(jr["date"][i]).isoformat() == p["date"]
+            assert int(jr["amount_coef"][i]) == int(p["amount"][1]) and int(jr["amount_exp"][i]) == p["amount"][2]
+            assert int(jr["balance_coef"][i]) == int(p["balance"][1]) and int(jr["balance_exp"][i]) == p["balance"][2]
+            assert jr["card"][i, :int(jr["card_len"][i])].tobytes().decode() == p["card"]

@@ -1,0 +1,257 @@
+"""Parity of the CUDA path, called through the C ABI, against (a) the golden
+vectors produced by executing the reference, (b) the CPU oracle on seeded
+synthetic backups, (c) size-independent properties at BASELINE.json's 1 M size.
+Bit-exact everywhere: this path is integer / byte work."""
+import datetime as dt
+
+import numpy as np
+import pytest
+
+from oracle import replay_oracle as O
+from smsgate_b200 import _lib as L
+from smsgate_b200 import gemini_cache, synth
+from smsgate_b200.batch import Batch
+
+pytestmark = pytest.mark.gpu
+STATUS = {n: i for i, n in enumerate(L.STATUS_NAMES)}
+NOW = dt.datetime(2026, 1, 1)
+
+
+@pytest.fixture(scope="module")
+def engine():
+    from smsgate_b200.replay import ReplayEngine
+    eng = ReplayEngine(0)
+    yield eng
+    eng.close()
+
+
+def _run(engine, bodies, cache, now=NOW, senders=None):
+    engine.load_cache(cache)
+    batch = Batch.from_strings(bodies, senders or ["BANK"] * len(bodies), range(len(bodies)))
+    return engine.replay(batch, now)
+
+
+def test_keys_scans_rewrite_golden(engine, golden):
+    cases = golden("keys.json")
+    res = _run(engine, [c["body"] for c in cases], {})
+    for i, c in enumerate(cases):
+        assert res.msg_id_hex(i) == c["msg_id"], c["body"]
+        assert res.cache_key_hex(i) == c["cache_key"], c["body"]
+        fl = int(res.flags[i])
+        assert bool(fl & L.F_WORKER_SKIP) == c["worker_skip"], c["body"]
+        assert bool(fl & L.F_PARSER_OTP) == c["parser_otp"], c["body"]
+        assert res.fixed_body(i) == c["fixed"], c["body"]
+        assert bool(fl & L.F_MODIFIED) == (c["fixed"] != c["body"])
+        want = 0 if c["body_date"] is None else O.pack_date(dt.date.fromisoformat(c["body_date"]))
+        assert int(res.body_date[i]) == want, c["body"]
+
+
+def test_decimal_batch_golden(engine, golden):
+    rows = golden("decimals.json")
+    coef, exp, flags = engine.decimal_batch([r[0] for r in rows])
+    for i, r in enumerate(rows):
+        err = int(flags[i]) & 3
+        if r[1] == "ValueError":
+            assert err == L.DEC_SYNTAX, r[0]
+        elif int(r[3]) > O.INT64_MAX:
+            assert err == L.DEC_OVERFLOW, r[0]
+        else:
+            assert (err, (int(flags[i]) >> 4) & 1, int(coef[i]), int(exp[i])) == (0, r[2], int(r[3]), r[4]), r[0]
+
+
+def test_parse_matrix_golden(engine, golden):
+    for c in golden("parse_matrix.json"):
+        if c["raw_date"].lstrip("-").isdigit():
+            continue    # device-source raw.date; XML replay always carries an ISO string (watcher.py:52)
+        key = O.cache_key(O.fixed_body(c["body"])).hex()
+        res = _run(engine, [c["body"]], {key: c["resp"]})
+        assert int(res.status[0]) == STATUS[c["status"]], c["name"]
+        p = c["parsed"]
+        if p is None:
+            continue
+        if c["status"] == "FAILED_EXC":
+            continue
+        big = any(int(p[w][1]) > O.INT64_MAX for w in ("amount", "balance"))
+        if big:
+            with pytest.raises(OverflowError):
+                res.parsed(0)
+            continue
+        got = res.parsed(0, sender="BANK")
+        assert got.date.isoformat() == p["date"], c["name"]
+        assert got.raw_body == p["raw_body"]
+        assert got.txn_type.value == p["txn_type"]
+        for w in ("amount", "balance"):
+            s, digits, e = getattr(got, w).as_tuple()
+            assert [s, "".join(map(str, digits)), e] == p[w], c["name"]
+        for f in ("currency", "card", "merchant", "city", "address", "parser_version"):
+            assert getattr(got, f) == p[f], (c["name"], f)
+
+
+@pytest.mark.parametrize("name", ["replay_plain.json", "replay_mixed.json"])
+def test_replay_golden(engine, golden, name):
+    g = golden(name)
+    backup = synth.generate(g["n"], seed=g["seed"], **g["kwargs"])
+    now = dt.datetime.fromisoformat(g["now"])
+    engine.load_cache(backup.cache)
+    res = engine.replay(Batch.from_strings(backup.bodies, backup.senders, backup.date_ms), now)
+    for i, r in enumerate(g["rows"]):
+        assert res.msg_id_hex(i) == r["msg_id"]
+        assert int(res.status[i]) == STATUS[r["status"]], i
+        if r["cache_key"] is not None:
+            assert res.cache_key_hex(i) == r["cache_key"]
+        p = r["parsed"]
+        if p is not None:
+            got = res.parsed(i)
+            assert got.model_dump(mode="json")["date"] == p["date"]
+            assert got.raw_body == p["raw_body"] and got.card == p["card"] and got.sender == p["sender"]
+            assert str(got.amount) == str(O.Decimal((p["amount"][0], tuple(map(int, p["amount"][1])), p["amount"][2])))
+            assert got.currency == p["currency"] and got.merchant == p["merchant"] and got.address == p["address"]
+    ups = {res.msg_id_hex(int(i)): int(i) for i in res.survivor_indices()}
+    assert ups == g["upserts"]
+    first = {res.msg_id_hex(int(i)): int(i) for i in np.nonzero(res.first_seen)[0]}
+    assert first == g["first"]
+    for i in range(res.n):
+        if int(res.status[i]) == L.ST_UPSERT:
+            assert int(res.last_idx[i]) == g["upserts"][res.msg_id_hex(i)]
+        else:
+            assert int(res.last_idx[i]) == -1
+
+
+def _compare_with_oracle(res, backup, now):
+    raw_dates = [O.iso_utc_from_ms(ms) for ms in backup.date_ms]
+    ora = O.replay(backup.bodies, backup.senders, raw_dates, backup.cache, now)
+    n = len(backup.bodies)
+    assert res.n == n
+    want_ids = np.frombuffer(b"".join(o.msg_id for o in ora.outcomes), np.uint8).reshape(n, 20)
+    want_keys = np.frombuffer(b"".join(o.cache_key for o in ora.outcomes), np.uint8).reshape(n, 32)
+    assert np.array_equal(res.msg_id, want_ids)
+    assert np.array_equal(res.cache_key, want_keys)
+    assert np.array_equal(res.status, np.array([o.status for o in ora.outcomes], np.uint8))
+    assert np.array_equal((res.flags & L.F_WORKER_SKIP) != 0, np.array([o.worker_skip for o in ora.outcomes]))
+    assert np.array_equal((res.flags & L.F_PARSER_OTP) != 0, np.array([o.parser_otp for o in ora.outcomes]))
+    assert np.array_equal(res.body_date, np.array([o.body_date for o in ora.outcomes], np.int32))
+    assert np.array_equal(res.slot >= 0, np.array([o.hit for o in ora.outcomes]))
+    assert np.array_equal(res.survivor != 0, np.array(ora.survivor))
+    assert np.array_equal(res.first_seen != 0, np.array(ora.first_seen))
+    assert np.array_equal(res.last_idx, np.array(ora.last_idx, np.int64))
+    for i, o in enumerate(ora.outcomes):
+        if o.hit:
+            fl = int(res.dec_flags[i])
+            for w, sh, sg, want in (("amount", 0, 4, o.amount), ("balance", 2, 5, o.balance)):
+                assert (fl >> sh) & 3 == want[0], (i, w)
+                if want[0] == 0:
+                    assert ((fl >> sg) & 1, int(res.cols[w + "_coef"][i]), int(res.cols[w + "_exp"][i])) == want[1:]
+        if o.parsed is not None and o.status != O.ST_FAILED_EXC:
+            assert int(res.date[i]) == O.pack_datetime(o.parsed.date), i
+            assert res.fixed_body(i) == o.fixed
+            assert res.cols["card"][i, :int(res.card_len[i])].tobytes().decode() == o.parsed.card
+
+
+@pytest.mark.parametrize("kw", [
+    dict(n=20000, seed=11),
+    dict(n=20000, seed=12, dup_frac=0.5, hot_key_zipf=1.2),
+    dict(n=12000, seed=13, mixed_locale=True, miss_frac=0.3, dup_frac=0.1),
+])
+def test_synthetic_vs_oracle(engine, kw):
+    kw = dict(kw)
+    n = kw.pop("n")
+    backup = synth.generate(n, **kw)
+    engine.load_cache(backup.cache)
+    res = engine.replay(Batch.from_strings(backup.bodies, backup.senders, backup.date_ms), NOW)
+    _compare_with_oracle(res, backup, NOW)
+
+
+def test_edges_empty_ragged_giant(engine):
+    # empty batch
+    engine.load_cache({})
+    res = engine.replay(Batch.from_strings([], [], []), NOW)
+    assert res.n == 0
+    # bodies of every length around the SHA block and staging boundaries, empty bodies, one giant body
+    rng = np.random.Generator(np.random.PCG64(5))
+    alphabet = np.array(list("ABCDEFGHIJKLMNOPQRSTUVWXYZ 0123456789.:*,"))
+    bodies = ["", "a", ""]
+    for ln in list(range(0, 200)) + [255, 256, 257, 1000, 4095, 4096, 4097, 44 * 1024 - 1, 44 * 1024, 44 * 1024 + 1]:
+        bodies.append("".join(rng.choice(alphabet, ln)))
+    giant = "4083***7538 " + "".join(rng.choice(alphabet, 120_000)) + " 1111•••2222 OTP "
+    bodies += [giant, "tail after giant", giant[:50_000], "x" * 45_000 + "Daily limit exceeded: 10.06.2025"]
+    # 300 x 400 B bodies: a full tile of these overflows the 44 KB stage -> sub-batches
+    bodies += ["".join(rng.choice(alphabet, 400)) + str(i) for i in range(300)]
+    cache = {O.cache_key(O.fixed_body(b)).hex(): dict(synth_resp) for b, synth_resp in
+             ((b, dict(txn_type="debit", date="06.05.25 14:23", amount="1,00", currency="usd", card="1234",
+                       merchant="M", city=None, address=None, balance="2")) for b in bodies[::3])}
+    res = _run(engine, bodies, cache)
+    backup = synth.Backup(bodies=bodies, senders=["BANK"] * len(bodies), date_ms=list(range(len(bodies))), cache=cache)
+    _compare_with_oracle(res, backup, NOW)
+
+
+def test_stage_calls_match_fused_replay(engine):
+    """scan_keys / join_route / dedup called one by one on device tensors give
+    the same columns as replay_host."""
+    import torch
+    backup = synth.generate(5000, seed=21, dup_frac=0.2, mixed_locale=True, miss_frac=0.1)
+    engine.load_cache(backup.cache)
+    batch = Batch.from_strings(backup.bodies, backup.senders, backup.date_ms)
+    ref = engine.replay(batch, NOW, base_index=1000)
+    d_bytes = torch.from_numpy(batch.body_bytes.copy()).cuda()
+    d_off = torch.from_numpy(batch.body_offsets.copy()).cuda()
+    cols = engine.device_columns(batch.n, d_bytes.numel())
+    engine.reserve(batch.n, d_bytes.numel())
+    engine.scan_keys(d_bytes, d_off, cols)
+    engine.join_route(batch.n, NOW, cols)
+    engine.dedup(batch.n, 1000, cols)
+    torch.cuda.synchronize()
+    for name in ("msg_id", "cache_key", "flags", "body_date", "fixed_len", "slot", "status", "amount_coef",
+                 "balance_coef", "amount_exp", "balance_exp", "dec_flags", "date", "card", "card_len", "survivor",
+                 "first_seen", "last_idx"):
+        assert np.array_equal(cols[name].cpu().numpy(), ref.cols[name]), name
+    assert int(ref.last_idx.max()) >= 1000
+
+
+def test_full_size_properties(engine):
+    """BASELINE.json config 2 size (1 M messages, 100 % hit for non-OTP bodies):
+    properties that do not need the oracle at full size, plus a 2 000-message
+    sample checked against it."""
+    n = 1_000_000
+    backup = synth.generate(n, seed=0x5EED + 2)
+    engine.load_cache(backup.cache)
+    batch = Batch.from_strings(backup.bodies, backup.senders, backup.date_ms)
+    res = engine.replay(batch, NOW, columns=[c for c in engine.ALL_COLUMNS if c != "fixed_bytes"])
+    kinds = np.array(backup.kinds)
+    otp = kinds == "otp"
+    # every OTP shape is skipped by the worker filter, nothing else is
+    assert np.array_equal((res.flags & L.F_WORKER_SKIP) != 0, otp)
+    # every other body hits the cache
+    assert np.all(res.slot[~otp] >= 0)
+    # the join is a bijection onto the loaded entries
+    hit_slots = res.slot[res.slot >= 0]
+    assert len(np.unique(hit_slots)) == len(hit_slots) == len(backup.cache)
+    # keys are pairwise distinct (bodies are), so dedup keeps every upsert as both first and last
+    ups = res.status == L.ST_UPSERT
+    assert np.array_equal(res.survivor != 0, ups) and np.array_equal(res.first_seen != 0, ups)
+    assert np.array_equal(res.last_idx[ups], np.nonzero(ups)[0])
+    assert np.all(res.last_idx[~ups] == -1)
+    # idempotence: replaying the same batch gives the same columns
+    res2 = engine.replay(batch, NOW, columns=["msg_id", "cache_key", "status", "survivor"])
+    for c in ("msg_id", "cache_key", "status", "survivor"):
+        assert np.array_equal(res2.cols[c], res.cols[c])
+    # doubling the batch (every message twice): survivors are exactly the second copies
+    half = 100_000
+    bodies2 = backup.bodies[:half] * 2
+    res3 = engine.replay(Batch.from_strings(bodies2, ["B"] * (2 * half), range(2 * half)), NOW,
+                         columns=["msg_id", "status", "survivor", "first_seen", "last_idx"])
+    u = res3.status == L.ST_UPSERT
+    assert np.array_equal(res3.survivor[:half] != 0, np.zeros(half, bool))
+    assert np.array_equal(res3.survivor[half:] != 0, u[half:])
+    assert np.array_equal(res3.first_seen[:half] != 0, u[:half])
+    assert np.array_equal(res3.last_idx[:half][u[:half]], np.nonzero(u[:half])[0] + half)
+    # sample against the oracle
+    idx = np.random.Generator(np.random.PCG64(1)).choice(n, 2000, replace=False)
+    for i in idx:
+        i = int(i)
+        o = O.replay_one(backup.bodies[i], backup.senders[i], O.iso_utc_from_ms(backup.date_ms[i]), backup.cache, NOW)
+        assert res.msg_id_hex(i) == o.msg_id.hex() and res.cache_key_hex(i) == o.cache_key.hex()
+        assert int(res.status[i]) == o.status
+        if o.parsed is not None:
+            assert int(res.date[i]) == O.pack_datetime(o.parsed.date)
+            assert int(res.amount_coef[i]) == o.amount[2] and int(res.amount_exp[i]) == o.amount[3]
+            assert int(res.balance_coef[i]) == o.balance[2] and int(res.balance_exp[i]) == o.balance[3]
