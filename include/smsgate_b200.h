@@ -102,8 +102,9 @@ typedef struct smsgate_outputs {
 
 /* ---- lifecycle ---------------------------------------------------------- */
 int smsgate_abi_version(void);
-/* Create a context on CUDA device `device`.  cuda_stream is a cudaStream_t
- * (or NULL for a stream the context creates).  No reference counterpart. */
+/* Create a context on CUDA device `device`.  cuda_stream is the cudaStream_t
+ * every copy and kernel of this context is issued on (NULL = CUDA's default
+ * stream).  No reference counterpart. */
 int smsgate_create(int device, void* cuda_stream, smsgate_ctx** out);
 void smsgate_destroy(smsgate_ctx* ctx);
 /* Text of the last error on this context (or of the last failed create when ctx is NULL). */

@@ -491,12 +491,7 @@ extern "C" int smsgate_create(int device, void* cuda_stream, smsgate_ctx** out) 
         return SMSGATE_E_CUDA;
     }
     ctx->sm_count = prop.multiProcessorCount;
-    if (cuda_stream) ctx->stream = (cudaStream_t)cuda_stream;
-    else {
-        if ((e = cudaStreamCreateWithFlags(&ctx->stream, cudaStreamNonBlocking)) != cudaSuccess)
-            return bail("cudaStreamCreate", e);
-        ctx->own_stream = true;
-    }
+    ctx->stream = (cudaStream_t)cuda_stream;          // NULL is CUDA's default stream
     DeviceTables* h = new DeviceTables();
     memcpy(h->byte_class, H_BYTE_CLASS, sizeof(h->byte_class));
     memcpy(h->dm_next, H_DM_NEXT, sizeof(h->dm_next));
