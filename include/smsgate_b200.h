@@ -43,7 +43,6 @@ extern "C" {
 #define SMSGATE_F_PARSER_OTP 0x02  /* libs/gemini_parser.py:198-200 */
 #define SMSGATE_F_MODIFIED 0x04    /* clean/mask changed the body (libs/gemini_parser.py:202-203) */
 #define SMSGATE_F_BODY_DATE 0x08   /* the body carries a usable dd.mm.yy[yy] (libs/gemini_parser.py:73-100) */
-#define SMSGATE_F_NON_ASCII 0x10
 
 /* status[] values: where the reference would have sent the message */
 #define SMSGATE_ST_UPSERT 0             /* sms.parsed, truthy merchant: upserted (services/pb_writer/writer.py:70-74) */

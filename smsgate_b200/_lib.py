@@ -14,7 +14,7 @@ LIB_PATH = os.path.join(_HERE, "libsmsgate_b200.so")
 ABI_VERSION = 1
 
 # flags / status / entry flags — mirror the header
-F_WORKER_SKIP, F_PARSER_OTP, F_MODIFIED, F_BODY_DATE, F_NON_ASCII = 0x01, 0x02, 0x04, 0x08, 0x10
+F_WORKER_SKIP, F_PARSER_OTP, F_MODIFIED, F_BODY_DATE = 0x01, 0x02, 0x04, 0x08
 (ST_UPSERT, ST_PARSED_NO_MERCHANT, ST_SKIPPED_FILTER, ST_CACHE_MISS, ST_UNMATCHED, ST_BROKEN,
  ST_FUTURE_DATE, ST_FAILED_EXC) = range(8)
 STATUS_NAMES = ("UPSERT", "PARSED_NO_MERCHANT", "SKIPPED_FILTER", "CACHE_MISS", "UNMATCHED", "BROKEN",

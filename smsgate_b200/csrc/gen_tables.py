@@ -6,14 +6,19 @@ the scan kernel walks once per body byte.
       One absorbing accept state.
   CS  automaton over RAW bytes for the case-sensitive needles: the parser's OTP
       list (libs/gemini_parser.py:198) and the worker's `Daily limit exceeded`
-      (worker.py:120), plus the byte pair C2 A0 (U+00A0, which `clean` rewrites,
-      libs/gemini_parser.py:202).  Sticky facts ride in the state number:
-      bit 0 of the block index = "Daily limit exceeded" seen, bit 1 = NBSP seen;
-      one absorbing pair of states = parser needle seen.
+      (worker.py:120).  One sticky fact rides in the state number (second block
+      of states = "Daily limit exceeded" seen); one absorbing state = parser
+      needle seen.
   DM  product of two KMP automata over code-point classes {other, digit, '.',
       '*'}: the body-date forms dd.mm.yy / dd.mm.yyyy (libs/gemini_parser.py:73-76)
-      and the card form dddd***dddd (libs/gemini_parser.py:131).  Sticky flags
-      in the high bits of each entry: B found, A found, card found.
+      and the card form dddd***dddd (libs/gemini_parser.py:131).  Rows are
+      sorted by date progress (nothing / short form seen / long form seen) so
+      the kernel spots the two events with one compare per byte; whether the
+      card form was seen is read off the final row.
+
+All three tables hold, per (row, class), the BYTE OFFSET of the next row inside
+its own table (uint16), and the byte-class word holds each automaton's class
+already multiplied by the entry size, so one step is `next = tab[state + cls]`.
 
 Run `python smsgate_b200/csrc/gen_tables.py` after changing a needle; the
 header is committed so the build needs no Python.
@@ -115,48 +120,23 @@ def build_cs():
     needles = CS_PARSER + [CS_WORKER]
     alphabet = sorted(set("".join(needles)))
     cls = {ch: i + 1 for i, ch in enumerate(alphabet)}     # 0 = OTHER
-    c_c2 = len(cls) + 1
-    c_a0 = len(cls) + 2
-    assert c_a0 < STRIDE
+    assert len(cls) + 1 <= STRIDE
     dense, out = aho(needles, alphabet)
     n = len(dense)
-    # state id = block * L + local; block = W | N << 1 carries the sticky facts.
-    # local 0..n-1 = automaton states, local n = "root, previous byte was C2"
-    # (C2 is in no needle, so it always falls back to the root).
-    L = n + 1
-    ACC0 = 4 * L            # parser needle seen, NBSP not seen
-    ACC1 = 4 * L + 1        # parser needle seen, NBSP seen
-    ACC0C = 4 * L + 2       # parser needle seen, previous byte was C2
-    nstates = 4 * L + 3
-    assert nstates <= 256
+    # state id = W * n + automaton state (W = "Daily limit exceeded" seen), then the parser-hit state
+    ACC = 2 * n
     sym_of = {k: ch for ch, k in cls.items()}
-    table = [[0] * STRIDE for _ in range(nstates)]
-    for blk in range(4):
-        W, N = blk & 1, blk >> 1
-        for loc in range(L):
-            s = 0 if loc == n else loc
-            after_c2 = loc == n
-            sid = blk * L + loc
+    table = [[0] * STRIDE for _ in range(2 * n + 1)]
+    for W in range(2):
+        for s in range(n):
             for c in range(STRIDE):
                 sym = sym_of.get(c)
                 t = dense[s][sym] if sym is not None else 0
-                w2, n2 = W, N
-                if c == c_a0 and after_c2:
-                    n2 = 1
-                if CS_WORKER in out[t]:
-                    w2 = 1
-                if any(x in CS_PARSER for x in out[t]):
-                    table[sid][c] = ACC1 if n2 else ACC0
-                else:
-                    table[sid][c] = (w2 | n2 << 1) * L + (n if c == c_c2 else t)
+                w2 = 1 if (W or CS_WORKER in out[t]) else 0
+                table[W * n + s][c] = ACC if any(x in CS_PARSER for x in out[t]) else w2 * n + t
     for c in range(STRIDE):
-        table[ACC0][c] = ACC0
-        table[ACC1][c] = ACC1
-        table[ACC0C][c] = ACC0
-    table[ACC0][c_c2] = ACC0C
-    table[ACC0C][c_c2] = ACC0C
-    table[ACC0C][c_a0] = ACC1
-    return table, cls, c_c2, c_a0, L, ACC0, ACC1, ACC0C
+        table[ACC][c] = ACC
+    return table, cls, n, ACC
 
 
 def kmp(pattern, classes):
@@ -181,21 +161,10 @@ def kmp(pattern, classes):
 def build_dm():
     # class ids: 0 other, 1 digit, 2 '.', 3 '*', 4 keep
     classes = ["o", "d", ".", "*"]
-    date = kmp("dd.dd.dddd", classes)        # state 8 = short form complete, 10 = long form complete
+    date = kmp("dd.dd.dddd", classes)        # progress 8 = short form complete, 10 = long form complete
     card = kmp("dddd***dddd", classes)       # 11 = card form complete
-    # date part: (progress 0..10, foundB, foundA): after A nothing more is needed.
-    # card part: (progress 0..10, found)
-    states = {}
-    rows = []
-
-    def sid(key):
-        if key not in states:
-            states[key] = len(rows)
-            rows.append(None)
-        return states[key]
-
-    start = (0, 0, 0, 0, 0)
-    sid(start)
+    start = (0, 0, 0, 0, 0)                  # (date progress, B found, A found, card progress, card found)
+    seen = {start}
     work = [start]
     trans = {}
     while work:
@@ -218,28 +187,24 @@ def build_dm():
                     nfc = 1
                     ncp = 0
             nk = (ndp, nfb, nfa, ncp, nfc)
-            if nk not in states:
-                sid(nk)
+            if nk not in seen:
+                seen.add(nk)
                 work.append(nk)
             row.append(nk)
         trans[key] = row
-    n = len(rows)
-    table = [[0] * DM_STRIDE for _ in range(n)]
-    FLAG_B, FLAG_A, FLAG_C = 0x2000, 0x4000, 0x8000
-
-    def enc(key):
-        dp, fb, fa, cp, fc = key
-        v = states[key] * DM_STRIDE
-        assert v < 0x2000
-        return v | (FLAG_B if fb else 0) | (FLAG_A if fa else 0) | (FLAG_C if fc else 0)
-
-    for key, s in states.items():
+    order = sorted(seen, key=lambda k: (k[1] + k[2], k[4], k[0], k[3]))
+    assert order[0] == start
+    idx = {k: i for i, k in enumerate(order)}
+    first_b = min(i for i, k in enumerate(order) if k[1])
+    first_a = min(i for i, k in enumerate(order) if k[2])
+    table = [[0] * DM_STRIDE for _ in order]
+    for k, i in idx.items():
         for ci in range(4):
-            table[s][ci] = enc(trans[key][ci])
-        table[s][4] = enc(key)                               # keep
-        for ci in range(5, DM_STRIDE):
-            table[s][ci] = enc(key)
-    return table, n
+            table[i][ci] = idx[trans[k][ci]]
+        for ci in range(4, DM_STRIDE):
+            table[i][ci] = i                                 # keep
+    has_card = [1 if k[4] else 0 for k in order]
+    return table, len(order), first_b, first_a, has_card
 
 
 def lead_len(b):
@@ -256,52 +221,54 @@ def lead_len(b):
 
 def main():
     ci, ci_cls, CI_ACC = build_ci()
-    cs, cs_cls, c_c2, c_a0, CS_L, ACC0, ACC1, ACC0C = build_cs()
-    dm, dm_n = build_dm()
+    cs, cs_cls, CS_N, CS_ACC = build_cs()
+    dm, dm_n, dm_first_b, dm_first_a, dm_has_card = build_dm()
     runs = digit_runs()
 
-    special_leads = set()
+    special_leads = {0xC2, 0xE2}                            # U+00A0 and U+2022, rewritten by `clean`
     for cp in UPPER_SPECIALS:
         special_leads.add(chr(cp).encode()[0])
     for a, n in runs:
-        for cp in (a, a + n - 1):
-            if cp >= 0x80:
-                special_leads.add(chr(cp).encode()[0])
-        # a run never straddles a lead byte boundary in practice; assert it
         if a >= 0x80:
-            assert chr(a).encode()[0] == chr(a + n - 1).encode()[0] or n == 50
-    special_leads.add(0xE2)                                 # U+2022 bullet
+            special_leads.add(chr(a).encode()[0])
+            assert chr(a).encode()[0] == chr(a + n - 1).encode()[0]
 
-    # byte class word: bits 0-4 CI class, 5-9 CS class, 10-12 DM class, bit 15 = special lead
+    CI_ROW = STRIDE * 2          # bytes per row (uint16 entries)
+    CS_ROW = STRIDE * 2
+    DM_ROW = DM_STRIDE * 2
+    # byte class word: byte0 = CI class * 2, byte1 = CS class * 2, byte2 = DM class * 2, bit 31 = special lead
     cls_word = []
     for b in range(256):
         ch = chr(b)
         if b < 0x80:
-            up = ch.upper()
-            cic = ci_cls.get(up, 0)
+            cic = ci_cls.get(ch.upper(), 0)
             csc = cs_cls.get(ch, 0)
             dmc = 1 if ch.isdigit() else 2 if ch == "." else 3 if ch == "*" else 0
             sp = 0
         elif b < 0xC0:
-            cic, csc, dmc, sp = 1, (c_a0 if b == 0xA0 else 0), 4, 0
+            cic, csc, dmc, sp = 1, 0, 4, 0                  # continuation byte: CI / DM keep their state
         else:
-            cic, csc, dmc = 0, (c_c2 if b == 0xC2 else 0), 0
+            cic, csc, dmc = 0, 0, 0
             sp = 1 if b in special_leads else 0
-        cls_word.append(cic | csc << 5 | dmc << 10 | sp << 15)
+        cls_word.append((cic * 2) | (csc * 2) << 8 | (dmc * 2) << 16 | sp << 31)
 
     here = os.path.dirname(os.path.abspath(__file__))
     with open(os.path.join(here, "scan_tables.h"), "w") as f:
         w = f.write
-        w("// GENERATED by gen_tables.py — do not edit.\n#pragma once\n#include <stdint.h>\n\n")
+        w("// GENERATED by gen_tables.py - do not edit.\n#pragma once\n#include <stdint.h>\n\n")
         w(f"#define SCAN_STRIDE {STRIDE}\n#define DM_STRIDE {DM_STRIDE}\n")
-        w(f"#define CI_STATES {len(ci)}\n#define CI_ACCEPT {CI_ACC}\n")
-        w(f"#define CS_STATES {len(cs)}\n#define CS_BLOCK {CS_L}\n#define CS_ACC0 {ACC0}\n#define CS_ACC1 {ACC1}\n#define CS_ACC0C {ACC0C}\n")
-        w(f"#define DM_STATES {dm_n}\n#define DM_FLAG_B 0x2000\n#define DM_FLAG_A 0x4000\n#define DM_FLAG_C 0x8000\n#define DM_ROW_MASK 0x1ff8\n")
+        w(f"#define CI_STATES {len(ci)}\n#define CI_ROW_BYTES {CI_ROW}\n#define CI_ACCEPT_OFF {CI_ACC * CI_ROW}\n")
+        w(f"#define CS_STATES {len(cs)}\n#define CS_ROW_BYTES {CS_ROW}\n#define CS_DAILY_OFF {CS_N * CS_ROW}\n"
+          f"#define CS_ACCEPT_OFF {CS_ACC * CS_ROW}\n")
+        w(f"#define DM_STATES {dm_n}\n#define DM_ROW_BYTES {DM_ROW}\n#define DM_FIRST_B_OFF {dm_first_b * DM_ROW}\n"
+          f"#define DM_FIRST_A_OFF {dm_first_a * DM_ROW}\n")
         for ch, c in sorted(ci_cls.items(), key=lambda kv: kv[1]):
             name = {" ": "SP", ":": "COLON", "=": "EQ"}.get(ch, ch)
-            w(f"#define CI_CLS_{name} {c}\n")
-        w("#define CI_CLS_OTHER 0\n#define CI_CLS_KEEP 1\n")
-        w("#define DM_CLS_OTHER 0\n#define DM_CLS_DIGIT 1\n#define DM_CLS_DOT 2\n#define DM_CLS_STAR 3\n#define DM_CLS_KEEP 4\n\n")
+            w(f"#define CI_CLS_{name} {c * 2}\n")
+        w("#define CI_CLS_OTHER 0\n#define CI_CLS_KEEP 2\n")
+        w("#define DM_CLS_OTHER 0\n#define DM_CLS_DIGIT 2\n#define DM_CLS_DOT 4\n#define DM_CLS_STAR 6\n#define DM_CLS_KEEP 8\n")
+        w("// class ids for the card-form KMP table used by the rewrite (not pre-multiplied)\n")
+        w("#define KMP_CLS_OTHER 0\n#define KMP_CLS_DIGIT 1\n#define KMP_CLS_STAR 3\n\n")
 
         def arr(name, ctype, rows):
             flat = [v for r in rows for v in r]
@@ -310,15 +277,16 @@ def main():
                 w("  " + ",".join(str(v) for v in flat[i:i + 24]) + ",\n")
             w("};\n\n")
 
-        arr("H_BYTE_CLASS", "uint16_t", [cls_word])
-        arr("H_CI_NEXT", "uint8_t", ci)
-        arr("H_CS_NEXT", "uint8_t", cs)
-        arr("H_DM_NEXT", "uint16_t", dm)
+        arr("H_BYTE_CLASS", "uint32_t", [cls_word])
+        arr("H_CI_NEXT", "uint16_t", [[v * CI_ROW for v in r] for r in ci])
+        arr("H_CS_NEXT", "uint16_t", [[v * CS_ROW for v in r] for r in cs])
+        arr("H_DM_NEXT", "uint16_t", [[v * DM_ROW for v in r] for r in dm])
+        arr("H_DM_HAS_CARD", "uint8_t", [dm_has_card])
         w(f"#define N_DIGIT_RUNS {len(runs)}\n")
         arr("H_DIGIT_RUN_START", "uint32_t", [[a for a, _ in runs]])
         arr("H_DIGIT_RUN_LEN", "uint8_t", [[n for _, n in runs]])
         arr("H_CARD_KMP", "uint8_t", kmp("dddd***dddd", ["o", "d", ".", "*"]))
-    print("CI states", len(ci), "CS states", len(cs), "DM states", dm_n,
+    print("CI states", len(ci), "CS states", len(cs), "DM states", dm_n, "first_b", dm_first_b, "first_a", dm_first_a,
           "special leads", sorted(hex(b) for b in special_leads))
 
 

@@ -5,15 +5,49 @@
 #pragma once
 #include "sg_common.cuh"
 
-struct ScanTables {
-    const uint16_t* byte_class;   // [256]
-    const uint8_t* ci_next;       // [CI_STATES * SCAN_STRIDE]
-    const uint8_t* cs_next;       // [CS_STATES * SCAN_STRIDE]
-    const uint16_t* dm_next;      // [DM_STATES * DM_STRIDE]
-    const uint32_t* digit_run_start;
-    const uint8_t* digit_run_len;
-    const uint8_t* card_kmp;      // [12 * 4]
+// All lookup tables of the scan in one block (copied to shared memory once per CTA).
+struct DeviceTables {
+    uint32_t byte_class[256];                    // byte0 = CI class*2, byte1 = CS class*2, byte2 = DM class*2, bit31 = special lead
+    uint32_t digit_run_start[N_DIGIT_RUNS];
+    uint16_t ci_next[CI_STATES * SCAN_STRIDE];   // byte offset of the next row
+    uint16_t cs_next[CS_STATES * SCAN_STRIDE];
+    uint16_t dm_next[DM_STATES * DM_STRIDE];
+    uint8_t dm_has_card[DM_STATES];
+    uint8_t digit_run_len[N_DIGIT_RUNS];
+    uint8_t card_kmp[48];
 };
+static_assert(sizeof(DeviceTables) % 16 == 0, "tables are copied 16 bytes at a time");
+
+inline void sg_fill_tables(DeviceTables* h) {
+    for (int k = 0; k < 256; ++k) h->byte_class[k] = H_BYTE_CLASS[k];
+    for (int k = 0; k < N_DIGIT_RUNS; ++k) { h->digit_run_start[k] = H_DIGIT_RUN_START[k]; h->digit_run_len[k] = H_DIGIT_RUN_LEN[k]; }
+    for (int k = 0; k < CI_STATES * SCAN_STRIDE; ++k) h->ci_next[k] = H_CI_NEXT[k];
+    for (int k = 0; k < CS_STATES * SCAN_STRIDE; ++k) h->cs_next[k] = H_CS_NEXT[k];
+    for (int k = 0; k < DM_STATES * DM_STRIDE; ++k) h->dm_next[k] = H_DM_NEXT[k];
+    for (int k = 0; k < DM_STATES; ++k) h->dm_has_card[k] = H_DM_HAS_CARD[k];
+    for (int k = 0; k < 48; ++k) h->card_kmp[k] = H_CARD_KMP[k];
+}
+
+// A view of the tables: one pointer, so it travels in registers.
+struct ScanTables {
+    const DeviceTables* t;
+};
+#define T_BYTE_CLASS(T) ((T).t->byte_class)
+#define T_CI(T) (reinterpret_cast<const uint8_t*>((T).t->ci_next))
+#define T_CS(T) (reinterpret_cast<const uint8_t*>((T).t->cs_next))
+#define T_DM(T) (reinterpret_cast<const uint8_t*>((T).t->dm_next))
+
+// one automaton step: tables hold the byte offset of the next row, classes come pre-multiplied by 2
+SG_HD uint32_t sg_step(const uint8_t* tab, uint32_t state, uint32_t cls2) {
+    return *reinterpret_cast<const uint16_t*>(tab + state + cls2);
+}
+SG_HD uint32_t sg_byte(uint32_t w, int k) {
+#ifdef __CUDA_ARCH__
+    return __byte_perm(w, 0, 0x4440 | k);
+#else
+    return (w >> (8 * k)) & 0xFF;
+#endif
+}
 
 struct ScanResult {
     uint32_t flags;      // SG_F_*
@@ -63,14 +97,17 @@ SG_HD int sg_back_cps(const uint8_t* m, int pos, int k) {
 // already matched \d{2}\.\d{2}\.\d{2,4} with Unicode digits: day
 // 3[01]|[12]\d|0[1-9] and month 1[0-2]|0[1-9] need ASCII where the pattern
 // names ASCII digits, the year accepts any Nd digits, then calendar validity.
-SG_HD int32_t sg_body_date_at(const uint8_t* m, int len, int lead, int ncp, const ScanTables& T) {
+#if defined(__CUDACC__)
+__host__ __device__ __noinline__
+#endif
+static int32_t sg_body_date_at(const uint8_t* m, int len, int lead, int ncp, const ScanTables T) {
     uint64_t vals = 0;                                // 4 bits per code point, position k at bits 4k
     uint32_t ascm = 0;                                // bit k: code point k is ASCII
     int p = lead;
     for (int k = ncp - 1; k >= 0; --k) {
         uint32_t cp;
         sg_utf8_decode(m + p, len - p, &cp);
-        const int dv = sg_digit_value(cp, T.digit_run_start, T.digit_run_len);
+        const int dv = sg_digit_value(cp, T.t->digit_run_start, T.t->digit_run_len);
         vals |= (uint64_t)(dv & 15) << (4 * k);
         ascm |= (cp < 0x80 ? 1u : 0u) << k;
         if (k) p = sg_back_cps(m, p, 1);
@@ -98,53 +135,102 @@ SG_HD int32_t sg_body_date_at(const uint8_t* m, int len, int lead, int ncp, cons
     return (year << 9) | (mon << 5) | day;
 }
 
+// Running state of the three automata over one body.
+struct ScanState {
+    uint32_t ci, cs, dm;     // row byte offsets in their tables
+    uint32_t dm_event;       // next date-progress threshold the DM row offset has to reach
+    int posB, posA;          // offset of the byte that completed the short / long date form
+    uint32_t modified;       // U+00A0 or U+2022 seen
+};
+
+// A date-progress event (rows are sorted by progress): rare, at most twice per body.
+SG_HD void sg_scan_event(ScanState& st, int i) {
+    if (st.posB < 0) st.posB = i;
+    if (st.dm >= DM_FIRST_A_OFF) { st.posA = i; st.dm_event = 0xFFFFFFFFu; }
+    else st.dm_event = DM_FIRST_A_OFF;
+}
+
+// One byte, any value.  A special lead byte (may upper-case into ASCII, be a
+// Unicode digit, U+00A0 or U+2022) is decoded and its symbols fed explicitly;
+// continuation bytes keep the CI / DM state, other lead bytes reset it.
+#if defined(__CUDACC__)
+__host__ __device__ __noinline__
+#endif
+static ScanState sg_scan_byte_careful(const uint8_t* m, int len, int i, const ScanTables T, ScanState st) {
+    const uint32_t cw = T_BYTE_CLASS(T)[m[i]];
+    st.cs = sg_step(T_CS(T), st.cs, sg_byte(cw, 1));
+    if ((int32_t)cw < 0) {
+        uint32_t cp;
+        sg_utf8_decode(m + i, len - i, &cp);
+        uint32_t up[3];
+        const int nu = sg_upper_special(cp, up);
+        if (nu == 0) st.ci = sg_step(T_CI(T), st.ci, CI_CLS_OTHER);
+        for (int k = 0; k < nu; ++k) st.ci = sg_step(T_CI(T), st.ci, up[k]);
+        uint32_t dcls = DM_CLS_OTHER;
+        if (cp == 0x2022) { dcls = DM_CLS_STAR; st.modified = 1; }
+        else if (cp == 0xA0) st.modified = 1;
+        else if (sg_digit_value(cp, T.t->digit_run_start, T.t->digit_run_len) >= 0) dcls = DM_CLS_DIGIT;
+        st.dm = sg_step(T_DM(T), st.dm, dcls);
+    } else {
+        st.ci = sg_step(T_CI(T), st.ci, sg_byte(cw, 0));
+        st.dm = sg_step(T_DM(T), st.dm, sg_byte(cw, 2));
+    }
+    if (st.dm >= st.dm_event) sg_scan_event(st, i);
+    return st;
+}
+
 // One pass over the body: both skip filters, NBSP / bullet / card-form
 // detection (is fixed_body different?) and the first hits of the two body
 // date forms.  worker.py:112-121, gemini_parser.py:198-203, :73-100, :131.
+// Aligned 4-byte words that are pure ASCII take the branch-free fast path (three
+// table steps per byte); every other byte goes through sg_scan_byte_careful.
 SG_HD ScanResult sg_scan_body(const uint8_t* m, int len, const ScanTables& T) {
-    uint32_t ci = 0, cs = 0, dm = 0;
-    int nB = 0, nA = 0;              // bytes consumed before the short / long date form completed
-    uint32_t modified = 0, nonascii = 0;
-    for (int i = 0; i < len; ++i) {
-        const uint32_t b = m[i];
-        const uint32_t cw = T.byte_class[b];
-        cs = T.cs_next[cs * SCAN_STRIDE + ((cw >> 5) & 31)];
-        if (cw & 0x8000) {
-            // lead byte of a sequence that may upper-case into ASCII, be a
-            // Unicode digit, or be U+2022: decode and feed symbols explicitly.
-            uint32_t cp;
-            sg_utf8_decode(m + i, len - i, &cp);
-            uint32_t up[3];
-            const int nu = sg_upper_special(cp, up);
-            if (nu == 0) ci = T.ci_next[ci * SCAN_STRIDE + CI_CLS_OTHER];
-            for (int k = 0; k < nu; ++k) ci = T.ci_next[ci * SCAN_STRIDE + up[k]];
-            uint32_t dcls = DM_CLS_OTHER;
-            if (cp == 0x2022) { dcls = DM_CLS_STAR; modified = 1; }
-            else if (sg_digit_value(cp, T.digit_run_start, T.digit_run_len) >= 0) dcls = DM_CLS_DIGIT;
-            dm = T.dm_next[(dm & DM_ROW_MASK) | dcls];
-        } else {
-            ci = T.ci_next[ci * SCAN_STRIDE + (cw & 31)];
-            dm = T.dm_next[(dm & DM_ROW_MASK) | ((cw >> 10) & 7)];
+    ScanState st;
+    st.ci = st.cs = st.dm = 0;
+    st.dm_event = DM_FIRST_B_OFF;
+    st.posB = st.posA = -1;
+    st.modified = 0;
+    int i = 0;
+    const int head = (int)((4 - ((uintptr_t)m & 3)) & 3);
+    for (; i < len && i < head; ++i) st = sg_scan_byte_careful(m, len, i, T, st);
+    for (; i + 4 <= len; i += 4) {
+        const uint32_t w4 = *reinterpret_cast<const uint32_t*>(m + i);
+        if (w4 & 0x80808080u) {
+#pragma unroll 1
+            for (int k = 0; k < 4; ++k) st = sg_scan_byte_careful(m, len, i + k, T, st);
+            continue;
         }
-        nonascii |= b;
-        nB += (dm & DM_FLAG_B) ? 0 : 1;
-        nA += (dm & DM_FLAG_A) ? 0 : 1;
+        uint32_t ci = st.ci, cs = st.cs, dm = st.dm;
+        const uint32_t dm_before = dm;
+#pragma unroll
+        for (int k = 0; k < 4; ++k) {
+            const uint32_t cw = T_BYTE_CLASS(T)[sg_byte(w4, k)];
+            ci = sg_step(T_CI(T), ci, sg_byte(cw, 0));
+            cs = sg_step(T_CS(T), cs, sg_byte(cw, 1));
+            dm = sg_step(T_DM(T), dm, sg_byte(cw, 2));
+        }
+        st.ci = ci; st.cs = cs;
+        if (dm >= st.dm_event) {
+            // a date form completed inside this word: replay its four bytes one by one for the position
+            st.dm = dm_before;
+            for (int k = 0; k < 4; ++k) {
+                st.dm = sg_step(T_DM(T), st.dm, sg_byte(T_BYTE_CLASS(T)[sg_byte(w4, k)], 2));
+                if (st.dm >= st.dm_event) sg_scan_event(st, i + k);
+            }
+        } else st.dm = dm;
     }
+    for (; i < len; ++i) st = sg_scan_byte_careful(m, len, i, T, st);
+
     ScanResult r;
     r.flags = 0;
-    r.body_date = 0;
-    // CS state layout: block = W | N<<1 (CS_BLOCK states each), then the parser-hit states
-    const bool parser_hit = cs >= CS_ACC0;
-    const uint32_t blk = cs / CS_BLOCK;
-    const bool daily = !parser_hit && (blk & 1);
-    const bool nbsp = parser_hit ? (cs == CS_ACC1) : ((blk >> 1) & 1);
-    if (ci == CI_ACCEPT || daily || parser_hit) r.flags |= SG_F_WORKER_SKIP;
+    const bool parser_hit = st.cs == CS_ACCEPT_OFF;
+    const bool daily = st.cs >= CS_DAILY_OFF;              // includes the parser-hit state
+    if (st.ci == CI_ACCEPT_OFF || daily) r.flags |= SG_F_WORKER_SKIP;
     if (parser_hit) r.flags |= SG_F_PARSER_OTP;
-    if (modified || nbsp || (dm & DM_FLAG_C)) r.flags |= SG_F_MODIFIED;
-    if (nonascii & 0x80) r.flags |= SG_F_NON_ASCII;
+    if (st.modified || T.t->dm_has_card[st.dm / DM_ROW_BYTES]) r.flags |= SG_F_MODIFIED;
     int32_t bd = 0;
-    if (dm & DM_FLAG_A) bd = sg_body_date_at(m, len, nA, 10, T);
-    if (bd == 0 && (dm & DM_FLAG_B)) bd = sg_body_date_at(m, len, nB, 8, T);
+    if (st.posA >= 0) bd = sg_body_date_at(m, len, st.posA, 10, T);
+    if (bd == 0 && st.posB >= 0) bd = sg_body_date_at(m, len, st.posB, 8, T);
     r.body_date = bd;
     if (bd) r.flags |= SG_F_BODY_DATE;
     return r;
@@ -159,19 +245,25 @@ SG_HD int sg_rewrite_fixed(uint8_t* m, int len, const ScanTables& T) {
     int r = 0, w = 0;
     uint32_t k = 0;                                   // card-form KMP progress
     while (r < len) {
-        uint32_t cp;
-        const int n = sg_utf8_decode(m + r, len - r, &cp);
+        const uint32_t b = m[r];
         uint32_t cls;
-        if (cp == 0xA0) { m[w++] = ' '; cls = DM_CLS_OTHER; }
-        else if (cp == 0x2022) { m[w++] = '*'; cls = DM_CLS_STAR; }
-        else {
-            for (int j = 0; j < n; ++j) m[w + j] = m[r + j];
-            w += n;
-            cls = (cp == '*') ? DM_CLS_STAR
-                : (sg_digit_value(cp, T.digit_run_start, T.digit_run_len) >= 0) ? DM_CLS_DIGIT : DM_CLS_OTHER;
+        if (b < 0x80) {                               // ASCII: class straight from the byte-class word
+            m[w++] = (uint8_t)b;
+            ++r;
+            cls = sg_byte(T_BYTE_CLASS(T)[b], 2) >> 1;   // DM class ids 0 other, 1 digit, 2 '.', 3 '*'
+        } else {
+            uint32_t cp;
+            const int n = sg_utf8_decode(m + r, len - r, &cp);
+            if (cp == 0xA0) { m[w++] = ' '; cls = KMP_CLS_OTHER; }
+            else if (cp == 0x2022) { m[w++] = '*'; cls = KMP_CLS_STAR; }
+            else {
+                for (int j = 0; j < n; ++j) m[w + j] = m[r + j];
+                w += n;
+                cls = (sg_digit_value(cp, T.t->digit_run_start, T.t->digit_run_len) >= 0) ? KMP_CLS_DIGIT : KMP_CLS_OTHER;
+            }
+            r += n;
         }
-        r += n;
-        k = T.card_kmp[k * 4 + cls];
+        k = T.t->card_kmp[k * 4 + cls];
         if (k == 11) {
             const int g = sg_back_cps(m, w, 4);       // start of the captured group
             const int s = sg_back_cps(m, g - 3, 4);   // start of the match
@@ -231,16 +323,17 @@ struct WordReader {
     }
 };
 
-// Word `j` of the padded message (0x80, zeros, 64-bit bit length).
+// Word `j` of the padded message (0x80, zeros, 64-bit bit length), branch-free:
+// k = message bytes left at this word; k >= 4 keeps the word, 0 <= k < 4 keeps k
+// bytes and plants the 0x80 terminator, k < 0 is zero fill; the last two words
+// carry the bit length.
 SG_HD uint32_t sg_padded_word(const WordReader& R, int len, int j, int nwords) {
-    const int off = j * 4;
-    if (off + 4 <= len) return R.be(j);
-    uint32_t w = 0;
-    if (off <= len) {
-        const int keep = len - off;                   // 0..3 message bytes in this word
-        if (keep) w = R.be(j) & (0xFFFFFFFFu << (32 - 8 * keep));
-        w |= 0x80u << (24 - 8 * keep);
-    }
+    const int k = len - j * 4;
+    const uint32_t raw = R.be(j);
+    const uint32_t kk = (uint32_t)(k < 0 ? 0 : (k > 4 ? 4 : k));
+    const uint32_t keep = kk == 0 ? 0u : (0xFFFFFFFFu << (32 - 8 * kk));      // kk in 1..4
+    uint32_t w = raw & keep;
+    if (k >= 0 && k < 4) w |= 0x80000000u >> (8 * kk);
     if (j == nwords - 1) w |= (uint32_t)len << 3;
     if (j == nwords - 2) w |= (uint32_t)len >> 29;
     return w;
@@ -307,26 +400,30 @@ static __constant__ uint32_t c_k256[64] = SG_K256_INIT;   // constant-bank opera
 #endif
 
 SG_HD void sg_sha256_compress(uint32_t h[8], uint32_t w[16]) {
-    // round constants as immediates: the loop is fully unrolled
+    // 4 x 16 rounds: the 16-round body is unrolled (static schedule indices), the outer loop is not,
+    // which keeps the kernel's instruction footprint inside the instruction cache
     uint32_t a = h[0], b = h[1], c = h[2], d = h[3], e = h[4], f = h[5], g = h[6], hh = h[7];
+#pragma unroll 1
+    for (int r = 0; r < 64; r += 16) {
 #pragma unroll
-    for (int i = 0; i < 64; ++i) {
-        uint32_t wi;
-        if (i < 16) wi = w[i];
-        else {
-            const uint32_t w15 = w[(i - 15) & 15], w2 = w[(i - 2) & 15];
-            const uint32_t s0 = sg_rotr(w15, 7) ^ sg_rotr(w15, 18) ^ (w15 >> 3);
-            const uint32_t s1 = sg_rotr(w2, 17) ^ sg_rotr(w2, 19) ^ (w2 >> 10);
-            wi = w[i & 15] + s0 + w[(i - 7) & 15] + s1;
-            w[i & 15] = wi;
+        for (int j = 0; j < 16; ++j) {
+            uint32_t wi;
+            if (r == 0) wi = w[j];
+            else {
+                const uint32_t w15 = w[(j + 1) & 15], w2 = w[(j + 14) & 15];
+                const uint32_t s0 = sg_rotr(w15, 7) ^ sg_rotr(w15, 18) ^ (w15 >> 3);
+                const uint32_t s1 = sg_rotr(w2, 17) ^ sg_rotr(w2, 19) ^ (w2 >> 10);
+                wi = w[j] + s0 + w[(j + 9) & 15] + s1;
+                w[j] = wi;
+            }
+            const uint32_t S1 = sg_rotr(e, 6) ^ sg_rotr(e, 11) ^ sg_rotr(e, 25);
+            const uint32_t ch = (e & f) ^ (~e & g);
+            const uint32_t t1 = hh + S1 + ch + SG_K256[r + j] + wi;
+            const uint32_t S0 = sg_rotr(a, 2) ^ sg_rotr(a, 13) ^ sg_rotr(a, 22);
+            const uint32_t mj = (a & b) ^ (a & c) ^ (b & c);
+            const uint32_t t2 = S0 + mj;
+            hh = g; g = f; f = e; e = d + t1; d = c; c = b; b = a; a = t1 + t2;
         }
-        const uint32_t S1 = sg_rotr(e, 6) ^ sg_rotr(e, 11) ^ sg_rotr(e, 25);
-        const uint32_t ch = (e & f) ^ (~e & g);
-        const uint32_t t1 = hh + S1 + ch + SG_K256[i] + wi;
-        const uint32_t S0 = sg_rotr(a, 2) ^ sg_rotr(a, 13) ^ sg_rotr(a, 22);
-        const uint32_t mj = (a & b) ^ (a & c) ^ (b & c);
-        const uint32_t t2 = S0 + mj;
-        hh = g; g = f; f = e; e = d + t1; d = c; c = b; b = a; a = t1 + t2;
     }
     h[0] += a; h[1] += b; h[2] += c; h[3] += d; h[4] += e; h[5] += f; h[6] += g; h[7] += hh;
 }
@@ -349,3 +446,33 @@ SG_HD void sg_sha256(const uint8_t* m, int len, uint32_t h[8]) {
         sg_sha256_compress(h, w);
     }
 }
+
+// SHA-1 and SHA-256 of the same byte string in one walk: each 64-byte block is
+// loaded and byte-swapped once and fed to both compressions.
+SG_HD void sg_sha1_sha256(const uint8_t* m, int len, uint32_t h1[5], uint32_t h2[8]) {
+    h1[0] = 0x67452301u; h1[1] = 0xEFCDAB89u; h1[2] = 0x98BADCFEu; h1[3] = 0x10325476u; h1[4] = 0xC3D2E1F0u;
+    h2[0] = 0x6a09e667u; h2[1] = 0xbb67ae85u; h2[2] = 0x3c6ef372u; h2[3] = 0xa54ff53au;
+    h2[4] = 0x510e527fu; h2[5] = 0x9b05688cu; h2[6] = 0x1f83d9abu; h2[7] = 0x5be0cd19u;
+    WordReader R;
+    R.init(m);
+    const int nblk = sg_sha_blocks(len), nwords = nblk * 16;
+    for (int blk = 0; blk < nblk; ++blk) {
+        uint32_t w[16], v[16];
+        if ((blk + 1) * 64 <= len) {
+#pragma unroll
+            for (int j = 0; j < 16; ++j) w[j] = R.be(blk * 16 + j);
+        } else {
+#pragma unroll
+            for (int j = 0; j < 16; ++j) w[j] = sg_padded_word(R, len, blk * 16 + j, nwords);
+        }
+#pragma unroll
+        for (int j = 0; j < 16; ++j) v[j] = w[j];
+        sg_sha1_compress(h1, w);
+        sg_sha256_compress(h2, v);
+    }
+}
+
+#if defined(__CUDACC__)
+__host__ __device__ __noinline__
+#endif
+static void sg_sha256_outofline(const uint8_t* m, int len, uint32_t h[8]) { sg_sha256(m, len, h); }

@@ -22,18 +22,6 @@
 #include "join_core.cuh"
 #include "scan_core.cuh"
 
-// ------------------------------------------------------------------ tables in global memory
-struct DeviceTables {
-    uint16_t byte_class[256];
-    uint16_t dm_next[DM_STATES * DM_STRIDE];
-    uint32_t digit_run_start[N_DIGIT_RUNS];
-    uint8_t ci_next[CI_STATES * SCAN_STRIDE];
-    uint8_t cs_next[CS_STATES * SCAN_STRIDE];
-    uint8_t digit_run_len[N_DIGIT_RUNS];
-    uint8_t card_kmp[48];
-};
-static_assert(sizeof(DeviceTables) % 16 == 0, "tables are copied 16 bytes at a time");
-
 // ------------------------------------------------------------------ PTX helpers (TMA 1-D bulk copy + mbarrier)
 __device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
 __device__ __forceinline__ void mbar_init(uint64_t* bar, uint32_t count) {
@@ -64,14 +52,24 @@ __device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
 }
 
 // ------------------------------------------------------------------ stage 1: keys + scans
-constexpr int K1_THREADS = 256;
-constexpr int K1_STAGE = 44 * 1024;       // staged body bytes per CTA tile
+constexpr int K1_THREADS = 128;           // 4 warps
+constexpr int K1_TILE = 256;              // messages per tile: every thread owns one short and one long body
+constexpr int K1_STAGE = 36 * 1024;       // staged body bytes per CTA tile (4 CTAs per SM)
 constexpr int K1_PAD = 32;                // slack read by the unaligned word reader
+constexpr int K1_BUCKETS = 64;            // length buckets of 16 bytes for the in-tile sort
 
 struct __align__(16) K1Smem {
     DeviceTables tab;
     uint8_t stage[K1_STAGE + K1_PAD];
     uint64_t mbar;
+    int32_t m_off[K1_TILE];               // start of message t inside `stage`
+    int32_t m_len[K1_TILE];               // body length
+    int32_t m_flen[K1_TILE];              // fixed_body length
+    int32_t hist[K1_BUCKETS];
+    int32_t cursor[K1_BUCKETS];
+    uint16_t order[K1_TILE];              // tile-local message ids sorted by length bucket
+    uint16_t modlist[K1_TILE];            // messages whose body the clean/mask step changes
+    int32_t nmod;
 };
 
 struct ScanOut {
@@ -83,13 +81,16 @@ struct ScanOut {
     uint8_t* fixed_bytes;
 };
 
-__device__ __forceinline__ void k1_store(const ScanOut& o, int64_t i, const uint32_t h1[5], const uint32_t h2[8],
-                                         const ScanResult& sr, int flen) {
+__device__ __forceinline__ void k1_store_id(const ScanOut& o, int64_t i, const uint32_t h1[5], const ScanResult& sr) {
     if (o.msg_id) {
         uint32_t* p = (uint32_t*)(o.msg_id + i * 20);
 #pragma unroll
         for (int k = 0; k < 5; ++k) p[k] = __byte_perm(h1[k], 0, 0x0123);
     }
+    if (o.flags) o.flags[i] = (uint8_t)sr.flags;
+    if (o.body_date) o.body_date[i] = sr.body_date;
+}
+__device__ __forceinline__ void k1_store_key(const ScanOut& o, int64_t i, const uint32_t h2[8], int flen) {
     if (o.cache_key) {
         uint4* p = (uint4*)(o.cache_key + i * 32);
         p[0] = make_uint4(__byte_perm(h2[0], 0, 0x0123), __byte_perm(h2[1], 0, 0x0123), __byte_perm(h2[2], 0, 0x0123),
@@ -97,9 +98,29 @@ __device__ __forceinline__ void k1_store(const ScanOut& o, int64_t i, const uint
         p[1] = make_uint4(__byte_perm(h2[4], 0, 0x0123), __byte_perm(h2[5], 0, 0x0123), __byte_perm(h2[6], 0, 0x0123),
                           __byte_perm(h2[7], 0, 0x0123));
     }
-    if (o.flags) o.flags[i] = (uint8_t)sr.flags;
-    if (o.body_date) o.body_date[i] = sr.body_date;
     if (o.fixed_len) o.fixed_len[i] = flen;
+}
+
+// A body that does not fit the staging buffer: one thread walks it in global
+// memory.  Kept out of line so the hot loop's instruction footprint stays small.
+__device__ __noinline__ void k1_giant(const uint8_t* bytes, int64_t lo, int64_t hi, int64_t msg, const ScanTables T,
+                                      const ScanOut out) {
+    const uint8_t* m = bytes + lo;
+    const int len = (int)(hi - lo);
+    ScanResult sr = sg_scan_body(m, len, T);
+    uint32_t h1[5], h2[8];
+    sg_sha1(m, len, h1);
+    int flen = len;
+    const uint8_t* fm = m;
+    if ((sr.flags & SG_F_MODIFIED) && out.fixed_bytes) {
+        uint8_t* w = out.fixed_bytes + lo;
+        for (int k = 0; k < len; ++k) w[k] = m[k];
+        flen = sg_rewrite_fixed(w, len, T);
+        fm = w;
+    }
+    sg_sha256_outofline(fm, flen, h2);
+    k1_store_id(out, msg, h1, sr);
+    k1_store_key(out, msg, h2, flen);
 }
 
 __global__ void __launch_bounds__(K1_THREADS, 4)
@@ -120,52 +141,42 @@ k_scan_keys(const uint8_t* __restrict__ bytes, const int64_t* __restrict__ offse
     }
     __syncthreads();
     ScanTables T;
-    T.byte_class = S.tab.byte_class;
-    T.ci_next = S.tab.ci_next;
-    T.cs_next = S.tab.cs_next;
-    T.dm_next = S.tab.dm_next;
-    T.digit_run_start = S.tab.digit_run_start;
-    T.digit_run_len = S.tab.digit_run_len;
-    T.card_kmp = S.tab.card_kmp;
+    T.t = &S.tab;
 
     uint32_t parity = 0;
-    const int64_t ntiles = (n + K1_THREADS - 1) / K1_THREADS;
+    const int64_t ntiles = (n + K1_TILE - 1) / K1_TILE;
     for (int64_t tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
-        const int64_t t0 = tile * K1_THREADS;
-        const int64_t t1 = (t0 + K1_THREADS < n) ? t0 + K1_THREADS : n;
+        const int64_t t0 = tile * K1_TILE;
+        const int64_t t1 = (t0 + K1_TILE < n) ? t0 + K1_TILE : n;
         int64_t s = t0;
         while (s < t1) {
-            // ---- how many messages starting at s fit the staging buffer
+            // ---- how many messages starting at s fit the staging buffer (offsets are monotone: a prefix)
             const int64_t lo = offsets[s];
             const int64_t base = lo & ~(int64_t)15;
-            const int64_t mine = s + tid;
-            int64_t my_lo = 0, my_hi = 0;
-            bool fits = false;
-            if (mine < t1) {
-                my_lo = offsets[mine];
-                my_hi = offsets[mine + 1];
-                fits = (my_hi - base) <= K1_STAGE;
-            }
-            const int cnt = __syncthreads_count(fits);       // offsets are monotone: a prefix fits
-            if (cnt == 0) {
-                // a single body larger than the staging buffer: one thread walks it in global memory
-                if (tid == 0) {
-                    const uint8_t* m = bytes + my_lo;
-                    const int len = (int)(my_hi - my_lo);
-                    ScanResult sr = sg_scan_body(m, len, T);
-                    uint32_t h1[5], h2[8];
-                    sg_sha1(m, len, h1);
-                    int flen = len;
-                    const uint8_t* fm = m;
-                    if ((sr.flags & SG_F_MODIFIED) && out.fixed_bytes) {
-                        uint8_t* w = out.fixed_bytes + my_lo;
-                        for (int k = 0; k < len; ++k) w[k] = m[k];
-                        flen = sg_rewrite_fixed(w, len, T);
-                        fm = w;
-                    }
-                    sg_sha256(fm, flen, h2);
-                    k1_store(out, s, h1, h2, sr, flen);
+            int nfit = 0;
+            int64_t my_lo[2], my_hi[2];
+            bool fits[2];
+#pragma unroll
+            for (int h = 0; h < 2; ++h) {
+                const int64_t mine = s + tid + h * K1_THREADS;
+                fits[h] = false;
+                my_lo[h] = my_hi[h] = 0;
+                if (mine < t1) {
+                    my_lo[h] = offsets[mine];
+                    my_hi[h] = offsets[mine + 1];
+                    fits[h] = (my_hi[h] - base) <= K1_STAGE;
                 }
+                nfit += fits[h] ? 1 : 0;
+            }
+            if (tid < K1_BUCKETS) S.hist[tid] = 0;
+            if (tid == 0) S.nmod = 0;
+            // the first half is a prefix of the tile, so the count of fitting messages is exact
+            // only if the second half is counted after the first: do two block-wide counts
+            const int cnt0 = __syncthreads_count(fits[0]);
+            const int cnt1 = (cnt0 == K1_THREADS) ? __syncthreads_count(fits[1]) : 0;
+            const int cnt = cnt0 + cnt1;
+            if (cnt == 0) {
+                if (tid == 0) k1_giant(bytes, my_lo[0], my_hi[0], s, T, out);
                 s += 1;
                 __syncthreads();
                 continue;
@@ -176,34 +187,99 @@ k_scan_keys(const uint8_t* __restrict__ bytes, const int64_t* __restrict__ offse
             const int64_t bulk_end = hi & ~(int64_t)15;
             const uint32_t bulk = (uint32_t)(bulk_end > base ? bulk_end - base : 0);
             if (tid == 0 && bulk) {
-                fence_proxy_async();                             // earlier generic writes to the stage are ordered first
+                fence_proxy_async();                         // generic-proxy writes of the last tile come first
                 mbar_expect_tx(&S.mbar, bulk);
                 tma_load_1d(S.stage, bytes + base, bulk, &S.mbar);
             }
             {
                 const int64_t tail0 = (bulk_end > base) ? bulk_end : base;
-                if (tail0 + tid < hi && tid < 16) S.stage[tail0 - base + tid] = bytes[tail0 + tid];
+                if (tid < 16 && tail0 + tid < hi) S.stage[tail0 - base + tid] = bytes[tail0 + tid];
             }
-            if (bulk) mbar_wait(&S.mbar, parity);
-            if (bulk) parity ^= 1;
+            // ---- while the copy is in flight: sort the tile's messages by length (16-byte buckets) so that
+            //      the 32 lanes of a warp walk bodies of about the same length and SHA block count
+            int key[2] = {0, 0};
+#pragma unroll
+            for (int h = 0; h < 2; ++h) {
+                const int loc = tid + h * K1_THREADS;
+                if (loc < cnt) {
+                    const int len = (int)(my_hi[h] - my_lo[h]);
+                    S.m_off[loc] = (int)(my_lo[h] - base);
+                    S.m_len[loc] = len;
+                    S.m_flen[loc] = len;
+                    int k = len >> 4;
+                    k = k < K1_BUCKETS - 1 ? k : K1_BUCKETS - 1;
+                    key[h] = k;
+                    atomicAdd(&S.hist[k], 1);
+                }
+            }
+            __syncthreads();
+            if (tid < 32) {
+                const int a = S.hist[2 * tid], b = S.hist[2 * tid + 1];
+                int incl = a + b;
+#pragma unroll
+                for (int d = 1; d < 32; d <<= 1) {
+                    const int v = __shfl_up_sync(0xffffffffu, incl, d);
+                    if (tid >= d) incl += v;
+                }
+                const int excl = incl - (a + b);
+                S.cursor[2 * tid] = excl;
+                S.cursor[2 * tid + 1] = excl + a;
+            }
+            __syncthreads();
+#pragma unroll
+            for (int h = 0; h < 2; ++h) {
+                const int loc = tid + h * K1_THREADS;
+                if (loc < cnt) S.order[atomicAdd(&S.cursor[key[h]], 1)] = (uint16_t)loc;
+            }
+            if (bulk) {
+                mbar_wait(&S.mbar, parity);
+                parity ^= 1;
+            }
             __syncthreads();
 
-            bool modified = false;
-            if (fits) {
-                uint8_t* m = S.stage + (my_lo - base);
-                const int len = (int)(my_hi - my_lo);
-                ScanResult sr = sg_scan_body(m, len, T);
+            // thread `tid` owns rank tid (short half) and rank cnt-1-tid (long half): every warp gets one
+            // group of short and one group of long bodies, so warps finish each phase at about the same time
+            const int half = (cnt + 1) >> 1;
+            int rk[2];
+            rk[0] = tid < half ? tid : -1;
+            rk[1] = tid < cnt - half ? cnt - 1 - tid : -1;
+            // ---- phase A: scans, then SHA-1 and SHA-256 of the body in one walk.  For the bodies that
+            //      clean/mask changes the SHA-256 is discarded and redone in phase B.
+#pragma unroll 1
+            for (int h = 0; h < 2; ++h) {
+                if (rk[h] < 0) continue;
+                const int t = S.order[rk[h]];
+                const uint8_t* m = S.stage + S.m_off[t];
+                const int len = S.m_len[t];
+                const ScanResult sr = sg_scan_body(m, len, T);
                 uint32_t h1[5], h2[8];
-                sg_sha1(m, len, h1);
-                int flen = len;
-                if (sr.flags & SG_F_MODIFIED) { flen = sg_rewrite_fixed(m, len, T); modified = true; }
-                sg_sha256(m, flen, h2);
-                k1_store(out, mine, h1, h2, sr, flen);
+                sg_sha1_sha256(m, len, h1, h2);
+                k1_store_id(out, s + t, h1, sr);
+                if (sr.flags & SG_F_MODIFIED) S.modlist[atomicAdd(&S.nmod, 1)] = (uint16_t)t;
+                else k1_store_key(out, s + t, h2, len);
             }
-            const int any_mod = __syncthreads_or(modified);
-            if (any_mod && out.fixed_bytes) {
-                // tile -> fixed_bytes[lo, hi): the rewritten bodies sit at their original offsets
-                for (int64_t p = lo + tid; p < hi; p += K1_THREADS) out.fixed_bytes[p] = S.stage[p - base];
+            __syncthreads();
+            // ---- phase B: clean + mask in place and SHA-256 of the result, compacted onto the first lanes
+            const int nmod = S.nmod;
+            for (int j = tid; j < nmod; j += K1_THREADS) {
+                const int u = S.modlist[j];
+                uint8_t* m = S.stage + S.m_off[u];
+                const int flen = sg_rewrite_fixed(m, S.m_len[u], T);
+                S.m_flen[u] = flen;
+                uint32_t h2[8];
+                sg_sha256_outofline(m, flen, h2);
+                k1_store_key(out, s + u, h2, flen);
+            }
+            __syncthreads();
+            // ---- phase 4: rewritten bodies -> fixed_bytes at their original offsets, one warp per body
+            if (out.fixed_bytes) {
+                for (int j = tid >> 5; j < nmod; j += K1_THREADS / 32) {
+                    const int u = S.modlist[j];
+                    const int fl = S.m_flen[u];
+                    const uint8_t* src = S.stage + S.m_off[u];
+                    uint8_t* dst = out.fixed_bytes + base + S.m_off[u];
+                    for (int k = tid & 31; k < fl; k += 32) dst[k] = src[k];
+                }
             }
             __syncthreads();
             s = e;
@@ -493,13 +569,7 @@ extern "C" int smsgate_create(int device, void* cuda_stream, smsgate_ctx** out) 
     ctx->sm_count = prop.multiProcessorCount;
     ctx->stream = (cudaStream_t)cuda_stream;          // NULL is CUDA's default stream
     DeviceTables* h = new DeviceTables();
-    memcpy(h->byte_class, H_BYTE_CLASS, sizeof(h->byte_class));
-    memcpy(h->dm_next, H_DM_NEXT, sizeof(h->dm_next));
-    memcpy(h->digit_run_start, H_DIGIT_RUN_START, sizeof(h->digit_run_start));
-    memcpy(h->ci_next, H_CI_NEXT, sizeof(h->ci_next));
-    memcpy(h->cs_next, H_CS_NEXT, sizeof(h->cs_next));
-    memcpy(h->digit_run_len, H_DIGIT_RUN_LEN, sizeof(h->digit_run_len));
-    memcpy(h->card_kmp, H_CARD_KMP, sizeof(h->card_kmp));
+    sg_fill_tables(h);
     if ((e = cudaMalloc(&ctx->d_tables, sizeof(DeviceTables))) != cudaSuccess) { delete h; return bail("cudaMalloc tables", e); }
     e = cudaMemcpy(ctx->d_tables, h, sizeof(DeviceTables), cudaMemcpyHostToDevice);
     delete h;
@@ -676,7 +746,7 @@ extern "C" int smsgate_scan_keys(smsgate_ctx* ctx, const uint8_t* d_bytes, const
     if (n == 0) return SMSGATE_OK;
     CUDA_TRY(ctx, cudaSetDevice(ctx->device));
     ScanOut so{out->msg_id, out->cache_key, out->flags, out->body_date, out->fixed_len, out->fixed_bytes};
-    const int64_t ntiles = (n + K1_THREADS - 1) / K1_THREADS;
+    const int64_t ntiles = (n + K1_TILE - 1) / K1_TILE;
     const int64_t maxgrid = (int64_t)ctx->sm_count * 4;
     const unsigned grid = (unsigned)(ntiles < maxgrid ? ntiles : maxgrid);
     k_scan_keys<<<grid, K1_THREADS, sizeof(K1Smem), ctx->stream>>>(d_bytes, d_offsets, n, ctx->d_tables, so);

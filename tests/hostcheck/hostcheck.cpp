@@ -13,14 +13,11 @@
 #include "scan_core.cuh"
 
 static ScanTables host_tables() {
+    static DeviceTables tab;
+    static bool ready = false;
+    if (!ready) { sg_fill_tables(&tab); ready = true; }
     ScanTables T;
-    T.byte_class = H_BYTE_CLASS;
-    T.ci_next = H_CI_NEXT;
-    T.cs_next = H_CS_NEXT;
-    T.dm_next = H_DM_NEXT;
-    T.digit_run_start = H_DIGIT_RUN_START;
-    T.digit_run_len = H_DIGIT_RUN_LEN;
-    T.card_kmp = H_CARD_KMP;
+    T.t = &tab;
     return T;
 }
 
