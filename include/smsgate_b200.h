@@ -168,6 +168,37 @@ int smsgate_replay_device(smsgate_ctx* ctx, const uint8_t* d_bytes, const int64_
 int smsgate_replay_host(smsgate_ctx* ctx, const uint8_t* h_bytes, const int64_t* h_offsets, int64_t n,
                         int64_t now_packed, int64_t base_index, const smsgate_outputs* h_out);
 
+/* ---- upsert-by-msg_id for callers that must not allocate -------------------
+ * No counterpart in the reference (it has no device memory to manage).
+ *
+ * Same verdicts as smsgate_dedup (survivor / first_seen / last_idx from msg_id
+ * and status), but without a context and without a single allocation: no
+ * cudaMalloc, no cudaFree, no library call that allocates.  The hash table it
+ * needs is a fixed array compiled into the library, so this is the call for
+ * code that runs where the allocator is off limits - a replay loop whose memory
+ * was budgeted and handed out at start-up, a host process in which another
+ * component owns the CUDA allocator, a section that must not stall or fail in
+ * an allocation.  The caller passes device pointers for inputs and outputs
+ * (any output may be NULL) and the stream to run on.
+ *
+ * Limits and rules
+ *   - at most SMSGATE_DEDUP_STATIC_MAX messages per call; a larger n is refused
+ *     with SMSGATE_E_LIMIT and a message in errbuf (split the batch, or use
+ *     smsgate_dedup with smsgate_reserve);
+ *   - the built-in table takes about 28 MiB on every GPU that loads the library,
+ *     for the life of the process;
+ *   - the first call on a given device looks up the table's device address
+ *     (cudaGetSymbolAddress); make that first call outside any stream capture;
+ *   - all calls on one device share the table: each call resets the part it
+ *     uses, and two calls whose GPU work overlaps (different streams, different
+ *     threads) corrupt each other - serialise them;
+ *   - errbuf/errbuf_len (optional) receive the error text.
+ */
+#define SMSGATE_DEDUP_STATIC_MAX (1 << 20)
+int smsgate_dedup_static(int device, void* cuda_stream, int64_t n, int64_t base_index, const uint8_t* d_msg_id,
+                         const uint8_t* d_status, uint8_t* d_survivor, uint8_t* d_first_seen, int64_t* d_last_idx,
+                         char* errbuf, int errbuf_len);
+
 #ifdef __cplusplus
 }
 #endif

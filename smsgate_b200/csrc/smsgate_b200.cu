@@ -15,6 +15,7 @@
 #include <stdint.h>
 #include <stdio.h>
 #include <string.h>
+#include <mutex>
 #include <new>
 #include <string>
 
@@ -861,5 +862,87 @@ extern "C" int smsgate_replay_host(smsgate_ctx* ctx, const uint8_t* h_bytes, con
 #undef BACK
     CUDA_TRY(ctx, cudaStreamSynchronize(st));
     CUDA_TRY(ctx, cudaGetLastError());
+    return SMSGATE_OK;
+}
+
+// ================================================================== dedup without any allocation
+// Some callers of this library are not allowed to allocate device memory at
+// the point where they need the upsert-by-msg_id verdicts: a replay loop whose
+// memory budget was fixed (and fully handed out) at start-up, a process in
+// which another component owns the CUDA allocator, or code that must not
+// touch the allocator because an allocation there can stall or fail.  For
+// them the hash table that k_dedup_insert / k_dedup_resolve need lives in the
+// file-scope array below instead of in a context's cudaMalloc'ed scratch.
+// The price: every GPU that loads this library carries the array
+// (SG_STATIC_BYTES, about 28 MiB) until the process exits, and a batch is
+// limited to SMSGATE_DEDUP_STATIC_MAX messages.
+constexpr int64_t SG_STATIC_MAX_N = SMSGATE_DEDUP_STATIC_MAX;              // 1 Mi messages
+constexpr uint64_t SG_STATIC_CAP = 2ull * SMSGATE_DEDUP_STATIC_MAX;        // table slots (power of two)
+constexpr uint64_t SG_STATIC_WORDS = 3 * SG_STATIC_CAP + SG_STATIC_MAX_N;  // owner | first | last | slot_of
+constexpr uint64_t SG_STATIC_BYTES = SG_STATIC_WORDS * 4;
+static_assert((SG_STATIC_CAP & (SG_STATIC_CAP - 1)) == 0, "table capacity must be a power of two");
+static_assert(SG_STATIC_BYTES <= (32ull << 20), "the built-in table is meant to stay modest (<= 32 MiB per GPU)");
+
+static __device__ __align__(256) int32_t g_dedup_static[SG_STATIC_WORDS];
+
+// In host code `g_dedup_static` is only a handle for the runtime, not a device
+// address; the address each device gave the array is looked up once per device.
+static int32_t* g_dedup_static_addr[64] = {nullptr};
+static std::mutex g_dedup_static_mutex;
+
+static int static_fail(char* errbuf, int errbuf_len, int code, const char* what, const char* detail) {
+    if (errbuf && errbuf_len > 0) snprintf(errbuf, (size_t)errbuf_len, "smsgate_dedup_static: %s%s%s", what,
+                                           detail ? ": " : "", detail ? detail : "");
+    return code;
+}
+
+extern "C" int smsgate_dedup_static(int device, void* cuda_stream, int64_t n, int64_t base_index,
+                                    const uint8_t* d_msg_id, const uint8_t* d_status, uint8_t* d_survivor,
+                                    uint8_t* d_first_seen, int64_t* d_last_idx, char* errbuf, int errbuf_len) {
+    if (n < 0 || (n > 0 && (!d_msg_id || !d_status)))
+        return static_fail(errbuf, errbuf_len, SMSGATE_E_ARG, "msg_id and status are required", nullptr);
+    if (n > SG_STATIC_MAX_N) {
+        char detail[160];
+        snprintf(detail, sizeof detail, "%lld messages, the built-in table holds at most %lld per call; "
+                 "split the batch or use smsgate_dedup with a reserved context",
+                 (long long)n, (long long)SG_STATIC_MAX_N);
+        return static_fail(errbuf, errbuf_len, SMSGATE_E_LIMIT, "batch too large", detail);
+    }
+    if (device < 0 || device >= 64) return static_fail(errbuf, errbuf_len, SMSGATE_E_ARG, "device index out of range", nullptr);
+    if (n == 0) return SMSGATE_OK;
+    cudaError_t e = cudaSetDevice(device);
+    if (e != cudaSuccess) return static_fail(errbuf, errbuf_len, SMSGATE_E_CUDA, "cudaSetDevice", cudaGetErrorString(e));
+    int32_t* base = nullptr;
+    {
+        // first call on this device: ask the runtime where the array lives here (that device is current)
+        std::lock_guard<std::mutex> lock(g_dedup_static_mutex);
+        if (!g_dedup_static_addr[device]) {
+            void* p = nullptr;
+            e = cudaGetSymbolAddress(&p, g_dedup_static);
+            if (e != cudaSuccess || !p)
+                return static_fail(errbuf, errbuf_len, SMSGATE_E_CUDA, "cudaGetSymbolAddress",
+                                   e != cudaSuccess ? cudaGetErrorString(e) : "null address");
+            g_dedup_static_addr[device] = static_cast<int32_t*>(p);
+        }
+        base = g_dedup_static_addr[device];
+    }
+    cudaStream_t st = (cudaStream_t)cuda_stream;
+    const uint64_t cap = pow2_at_least((uint64_t)(n > 8 ? n : 8) * 2);       // <= SG_STATIC_CAP
+    DedupScratch D;
+    D.owner = base;
+    D.first = base + SG_STATIC_CAP;
+    D.last = base + 2 * SG_STATIC_CAP;
+    D.slot_of = base + 3 * SG_STATIC_CAP;
+    D.mask = cap - 1;
+    // the array still holds the previous call's table: reset the part this call uses
+    if ((e = cudaMemsetAsync(D.owner, 0xFF, cap * 4, st)) != cudaSuccess ||
+        (e = cudaMemsetAsync(D.first, 0x7F, cap * 4, st)) != cudaSuccess ||
+        (e = cudaMemsetAsync(D.last, 0xFF, cap * 4, st)) != cudaSuccess)
+        return static_fail(errbuf, errbuf_len, SMSGATE_E_CUDA, "cudaMemsetAsync", cudaGetErrorString(e));
+    const unsigned grid = (unsigned)((n + 255) / 256);
+    k_dedup_insert<<<grid, 256, 0, st>>>(n, d_msg_id, d_status, D);
+    k_dedup_resolve<<<grid, 256, 0, st>>>(n, base_index, D, d_survivor, d_first_seen, d_last_idx);
+    if ((e = cudaGetLastError()) != cudaSuccess)
+        return static_fail(errbuf, errbuf_len, SMSGATE_E_CUDA, "kernel launch", cudaGetErrorString(e));
     return SMSGATE_OK;
 }
