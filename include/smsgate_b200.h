@@ -160,6 +160,33 @@ int smsgate_dedup(smsgate_ctx* ctx, int64_t n, int64_t base_index, const smsgate
 int smsgate_replay_device(smsgate_ctx* ctx, const uint8_t* d_bytes, const int64_t* d_offsets, int64_t n,
                           int64_t now_packed, int64_t base_index, const smsgate_outputs* out);
 
+/* ---- global upsert-by-msg_id across GPUs -----------------------------------
+ * The reference gets global idempotency from one PocketBase/Postgres unique key
+ * on msg_id (db/models.py:16, services/pb_writer/upsert.py:19-31).  With the
+ * backup sharded by index over `world` GPUs the same guarantee needs ONE exchange:
+ * after smsgate_dedup on its shard, every rank exports one 32-byte record per
+ * locally distinct msg_id {key[20], first48, last48 (global indices)}, grouped by
+ * the rank that owns the key's 32-bit prefix ((prefix * world) >> 32); the records
+ * travel in one all-to-all (NCCL over NVLink, done by the caller, e.g.
+ * torch.distributed.all_to_all_single); the owner merges them and answers each
+ * record with {global first, global last}; the answers return on the mirrored
+ * all-to-all and smsgate_dedup_apply rewrites survivor / first_seen / last_idx. */
+#define SMSGATE_MAX_WORLD 64
+#define SMSGATE_RECORD_BYTES 32
+/* Writes the records (destination-contiguous) to d_records [<= n*32], the local slot
+ * of each record to d_rec_slot [<= n] and the per-destination counts to HOST
+ * h_counts[world].  Synchronises the stream (the counts are the split sizes). */
+int smsgate_dedup_export(smsgate_ctx* ctx, int64_t n, int64_t base_index, int world, const smsgate_outputs* out,
+                         uint8_t* d_records, int32_t* d_rec_slot, int64_t* h_counts);
+/* Size the owner-side merge table for up to max_records received records.  Allocates. */
+int smsgate_reserve_merge(smsgate_ctx* ctx, int64_t max_records);
+/* Owner side: merge n_recv received records, write {first, last} per record to d_verdicts [n_recv*2]. */
+int smsgate_dedup_merge(smsgate_ctx* ctx, int64_t n_recv, const uint8_t* d_records, int64_t* d_verdicts);
+/* Home side: d_verdicts [n_rec*2] in the order of the exported records; rewrites
+ * out->survivor, out->first_seen, out->last_idx of the n local messages. */
+int smsgate_dedup_apply(smsgate_ctx* ctx, int64_t n, int64_t base_index, int64_t n_rec, const int32_t* d_rec_slot,
+                        const int64_t* d_verdicts, const smsgate_outputs* out);
+
 /* ---- the replay, host buffers --------------------------------------------
  * What `_iter_sms` -> worker -> parse_sms_llm -> pb_writer do for a whole
  * backup, called with the batch in host memory: copies in, runs the three

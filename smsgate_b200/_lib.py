@@ -24,6 +24,8 @@ E_IS_DICT, E_HAS_TXN, E_SCHEMA_OK, E_CARD_STR, E_MERCHANT = 0x1, 0x2, 0x4, 0x8, 
 E_DATE_STRICT, E_DATE_HOST, E_DATE_NOBODY, E_DATE_TZ, E_DATE_KEY = 0x20, 0x40, 0x80, 0x100, 0x200
 DEC_OK, DEC_SYNTAX, DEC_OVERFLOW = 0, 1, 2
 DEDUP_STATIC_MAX = 1 << 20
+MAX_WORLD = 64
+RECORD_BYTES = 32
 E_LIMIT = -5
 
 # (column name, numpy dtype string, elements per message)
@@ -74,6 +76,10 @@ def lib():
         "smsgate_dedup": (i32, [vp, i64, i64, C.POINTER(Outputs)]),
         "smsgate_replay_device": (i32, [vp, vp, vp, i64, i64, i64, C.POINTER(Outputs)]),
         "smsgate_replay_host": (i32, [vp, vp, vp, i64, i64, i64, C.POINTER(Outputs)]),
+        "smsgate_dedup_export": (i32, [vp, i64, i64, i32, C.POINTER(Outputs), vp, vp, vp]),
+        "smsgate_reserve_merge": (i32, [vp, i64]),
+        "smsgate_dedup_merge": (i32, [vp, i64, vp, vp]),
+        "smsgate_dedup_apply": (i32, [vp, i64, i64, i64, vp, vp, C.POINTER(Outputs)]),
         "smsgate_dedup_static": (i32, [i32, vp, i64, i64, vp, vp, vp, vp, vp, C.c_char_p, i32]),
     }
     for name, (res, args) in sigs.items():

@@ -505,6 +505,13 @@ struct smsgate_ctx {
     int64_t cap_msgs = 0, cap_bytes = 0;
     int32_t *d_owner = nullptr, *d_first = nullptr, *d_last = nullptr, *d_slot_of = nullptr;
     uint64_t dd_cap = 0;
+    int64_t *d_gfirst = nullptr, *d_glast = nullptr;   // [dd_cap] global first / last index per local slot
+    int* d_counts = nullptr;                            // [SMSGATE_MAX_WORLD] export counters / cursors
+    // owner-side merge table (smsgate_reserve_merge)
+    int64_t mg_records = 0;
+    uint64_t mg_cap = 0;
+    int32_t *mg_owner = nullptr, *mg_slot_of = nullptr;
+    unsigned long long *mg_first = nullptr, *mg_last = nullptr;
     // device mirror of a host batch (smsgate_replay_host)
     uint8_t* s_bytes = nullptr;
     int64_t* s_offsets = nullptr;
@@ -590,6 +597,8 @@ static void free_cache(smsgate_ctx* c) {
 }
 static void free_scratch(smsgate_ctx* c) {
     cudaFree(c->d_owner); cudaFree(c->d_first); cudaFree(c->d_last); cudaFree(c->d_slot_of);
+    cudaFree(c->d_gfirst); cudaFree(c->d_glast); cudaFree(c->d_counts);
+    c->d_gfirst = c->d_glast = nullptr; c->d_counts = nullptr;
     cudaFree(c->s_bytes); cudaFree(c->s_offsets); cudaFree(c->s_out); cudaFree(c->s_fixed);
     c->d_owner = c->d_first = c->d_last = c->d_slot_of = nullptr;
     c->s_bytes = nullptr; c->s_offsets = nullptr; c->s_out = nullptr; c->s_fixed = nullptr;
@@ -602,6 +611,7 @@ extern "C" void smsgate_destroy(smsgate_ctx* ctx) {
     cudaStreamSynchronize(ctx->stream);
     free_cache(ctx);
     free_scratch(ctx);
+    cudaFree(ctx->mg_owner); cudaFree(ctx->mg_first); cudaFree(ctx->mg_last); cudaFree(ctx->mg_slot_of);
     cudaFree(ctx->d_tables);
     if (ctx->own_stream) cudaStreamDestroy(ctx->stream);
     delete ctx;
@@ -623,6 +633,9 @@ extern "C" int smsgate_reserve(smsgate_ctx* ctx, int64_t max_msgs, int64_t max_b
     CUDA_TRY(ctx, cudaMalloc(&ctx->d_first, cap * 4));
     CUDA_TRY(ctx, cudaMalloc(&ctx->d_last, cap * 4));
     CUDA_TRY(ctx, cudaMalloc(&ctx->d_slot_of, (size_t)(max_msgs + 1) * 4));
+    CUDA_TRY(ctx, cudaMalloc(&ctx->d_gfirst, cap * 8));
+    CUDA_TRY(ctx, cudaMalloc(&ctx->d_glast, cap * 8));
+    CUDA_TRY(ctx, cudaMalloc(&ctx->d_counts, sizeof(int) * SMSGATE_MAX_WORLD));
     CUDA_TRY(ctx, cudaMalloc(&ctx->s_bytes, (size_t)max_bytes + 64));
     CUDA_TRY(ctx, cudaMalloc(&ctx->s_fixed, (size_t)max_bytes + 64));
     CUDA_TRY(ctx, cudaMalloc(&ctx->s_offsets, (size_t)(max_msgs + 1) * 8));
@@ -861,6 +874,216 @@ extern "C" int smsgate_replay_host(smsgate_ctx* ctx, const uint8_t* h_bytes, con
     if (h_out->fixed_bytes && total) BACK(fixed_bytes, total);
 #undef BACK
     CUDA_TRY(ctx, cudaStreamSynchronize(st));
+    CUDA_TRY(ctx, cudaGetLastError());
+    return SMSGATE_OK;
+}
+
+// ================================================================== global dedup across GPUs
+// Messages are sharded by index; after the local dedup every locally distinct
+// msg_id becomes one 32-byte record {key[20], first48, last48} (global indices)
+// routed to the rank that owns its key prefix.  The owner merges the records of
+// all ranks and answers each with the global first / last index.
+struct __align__(16) KeyRecord {
+    uint32_t key[5];
+    uint32_t first_lo;
+    uint32_t last_lo;
+    uint16_t first_hi;
+    uint16_t last_hi;
+};
+static_assert(sizeof(KeyRecord) == 32, "exchange records are 32 bytes");
+
+__device__ __forceinline__ int key_owner(const uint8_t* k, int world) {
+    // the digest's first four bytes, big-endian, are its top 32 bits: range-partition them over `world`
+    const uint32_t p = ((uint32_t)k[0] << 24) | ((uint32_t)k[1] << 16) | ((uint32_t)k[2] << 8) | k[3];
+    return (int)(((uint64_t)p * (uint64_t)world) >> 32);
+}
+
+// pass 1: count representatives (the message that claimed its slot) per destination
+__global__ void __launch_bounds__(256)
+k_export_count(int64_t n, const uint8_t* __restrict__ msg_id, DedupScratch D, int world, int* __restrict__ counts) {
+    const int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const int32_t sl = D.slot_of[i];
+    if (sl < 0 || D.owner[sl] != (int32_t)i) return;
+    atomicAdd(&counts[key_owner(msg_id + i * 20, world)], 1);
+}
+// pass 2: scatter the records into destination-contiguous order
+__global__ void __launch_bounds__(256)
+k_export_scatter(int64_t n, int64_t base_index, const uint8_t* __restrict__ msg_id, DedupScratch D, int world,
+                 int* __restrict__ cursor, KeyRecord* __restrict__ records, int32_t* __restrict__ rec_slot) {
+    const int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const int32_t sl = D.slot_of[i];
+    if (sl < 0 || D.owner[sl] != (int32_t)i) return;
+    const uint8_t* k = msg_id + i * 20;
+    const int r = atomicAdd(&cursor[key_owner(k, world)], 1);
+    const uint32_t* kw = reinterpret_cast<const uint32_t*>(k);
+    const uint64_t f = (uint64_t)(base_index + D.first[sl]), l = (uint64_t)(base_index + D.last[sl]);
+    KeyRecord rec;
+    rec.key[0] = kw[0]; rec.key[1] = kw[1]; rec.key[2] = kw[2]; rec.key[3] = kw[3]; rec.key[4] = kw[4];
+    rec.first_lo = (uint32_t)f; rec.last_lo = (uint32_t)l;
+    rec.first_hi = (uint16_t)(f >> 32); rec.last_hi = (uint16_t)(l >> 32);
+    records[r] = rec;
+    rec_slot[r] = sl;
+}
+
+struct MergeScratch {
+    int32_t* owner;              // [cap] record index that claimed the slot
+    unsigned long long* first;   // [cap]
+    unsigned long long* last;    // [cap]
+    int32_t* slot_of;            // [n_recv]
+    uint64_t mask;
+};
+__global__ void __launch_bounds__(256)
+k_merge_insert(int64_t n, const KeyRecord* __restrict__ recs, MergeScratch M) {
+    const int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const KeyRecord r = recs[i];
+    uint64_t pos = (((uint64_t)r.key[1] << 32) | r.key[0]) & M.mask;
+    for (;;) {
+        int prev = M.owner[pos];
+        if (prev == -1) prev = atomicCAS(&M.owner[pos], -1, (int)i);
+        if (prev == -1 || prev == (int)i) break;
+        const KeyRecord o = recs[prev];
+        if (o.key[0] == r.key[0] && o.key[1] == r.key[1] && o.key[2] == r.key[2] && o.key[3] == r.key[3] &&
+            o.key[4] == r.key[4]) break;
+        pos = (pos + 1) & M.mask;
+    }
+    atomicMin(&M.first[pos], ((unsigned long long)r.first_hi << 32) | r.first_lo);
+    atomicMax(&M.last[pos], ((unsigned long long)r.last_hi << 32) | r.last_lo);
+    M.slot_of[i] = (int32_t)pos;
+}
+__global__ void __launch_bounds__(256)
+k_merge_verdict(int64_t n, MergeScratch M, int64_t* __restrict__ verdict /* [n][2] */) {
+    const int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const int32_t sl = M.slot_of[i];
+    verdict[2 * i] = (int64_t)M.first[sl];
+    verdict[2 * i + 1] = (int64_t)M.last[sl];
+}
+// back home: verdict r belongs to local slot rec_slot[r]
+__global__ void __launch_bounds__(256)
+k_apply_scatter(int64_t n_rec, const int32_t* __restrict__ rec_slot, const int64_t* __restrict__ verdict,
+                int64_t* __restrict__ gfirst, int64_t* __restrict__ glast) {
+    const int64_t r = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+    if (r >= n_rec) return;
+    const int32_t sl = rec_slot[r];
+    gfirst[sl] = verdict[2 * r];
+    glast[sl] = verdict[2 * r + 1];
+}
+__global__ void __launch_bounds__(256)
+k_apply_resolve(int64_t n, int64_t base_index, const int32_t* __restrict__ slot_of,
+                const int64_t* __restrict__ gfirst, const int64_t* __restrict__ glast,
+                uint8_t* __restrict__ survivor, uint8_t* __restrict__ first_seen, int64_t* __restrict__ last_idx) {
+    const int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const int32_t sl = slot_of[i];
+    uint8_t sv = 0, fs = 0;
+    int64_t li = -1;
+    if (sl >= 0) {
+        const int64_t g = base_index + i;
+        li = glast[sl];
+        sv = (li == g);
+        fs = (gfirst[sl] == g);
+    }
+    if (survivor) survivor[i] = sv;
+    if (first_seen) first_seen[i] = fs;
+    if (last_idx) last_idx[i] = li;
+}
+
+extern "C" int smsgate_dedup_export(smsgate_ctx* ctx, int64_t n, int64_t base_index, int world,
+                                    const smsgate_outputs* out, uint8_t* d_records, int32_t* d_rec_slot,
+                                    int64_t* h_counts) {
+    if (!ctx) return SMSGATE_E_ARG;
+    if (n < 0 || world < 1 || world > SMSGATE_MAX_WORLD || !out || !h_counts)
+        return fail(ctx, SMSGATE_E_ARG, "dedup_export: bad argument");
+    for (int w = 0; w < world; ++w) h_counts[w] = 0;
+    if (n == 0) return SMSGATE_OK;
+    if (n > ctx->cap_msgs) return fail(ctx, SMSGATE_E_STATE, "dedup_export: run smsgate_dedup on this batch first");
+    if (!out->msg_id || !d_records || !d_rec_slot) return fail(ctx, SMSGATE_E_ARG, "dedup_export: NULL array");
+    CUDA_TRY(ctx, cudaSetDevice(ctx->device));
+    cudaStream_t st = ctx->stream;
+    uint64_t cap = pow2_at_least((uint64_t)(n > 8 ? n : 8) * 2);
+    if (cap > ctx->dd_cap) cap = ctx->dd_cap;
+    DedupScratch D{ctx->d_owner, ctx->d_first, ctx->d_last, ctx->d_slot_of, cap - 1};
+    const unsigned grid = (unsigned)((n + 255) / 256);
+    CUDA_TRY(ctx, cudaMemsetAsync(ctx->d_counts, 0, sizeof(int) * SMSGATE_MAX_WORLD, st));
+    k_export_count<<<grid, 256, 0, st>>>(n, out->msg_id, D, world, ctx->d_counts);
+    int counts[SMSGATE_MAX_WORLD];
+    CUDA_TRY(ctx, cudaMemcpyAsync(counts, ctx->d_counts, sizeof(int) * world, cudaMemcpyDeviceToHost, st));
+    CUDA_TRY(ctx, cudaStreamSynchronize(st));        // the split sizes are needed on the host for the all-to-all
+    int cursor[SMSGATE_MAX_WORLD];
+    int run = 0;
+    for (int w = 0; w < world; ++w) { cursor[w] = run; run += counts[w]; h_counts[w] = counts[w]; }
+    CUDA_TRY(ctx, cudaMemcpyAsync(ctx->d_counts, cursor, sizeof(int) * world, cudaMemcpyHostToDevice, st));
+    k_export_scatter<<<grid, 256, 0, st>>>(n, base_index, out->msg_id, D, world, ctx->d_counts,
+                                           reinterpret_cast<KeyRecord*>(d_records), d_rec_slot);
+    ctx->launches += 2;
+    CUDA_TRY(ctx, cudaGetLastError());
+    // `cursor` is read by an async copy: make sure it has been consumed before this frame goes away
+    CUDA_TRY(ctx, cudaStreamSynchronize(st));
+    return SMSGATE_OK;
+}
+
+extern "C" int smsgate_reserve_merge(smsgate_ctx* ctx, int64_t max_records) {
+    if (!ctx) return SMSGATE_E_ARG;
+    if (max_records < 0 || max_records > 0x40000000ll) return fail(ctx, SMSGATE_E_LIMIT, "reserve_merge: at most 2^30 records");
+    if (max_records <= ctx->mg_records) return SMSGATE_OK;
+    CUDA_TRY(ctx, cudaSetDevice(ctx->device));
+    CUDA_TRY(ctx, cudaStreamSynchronize(ctx->stream));
+    cudaFree(ctx->mg_owner); cudaFree(ctx->mg_first); cudaFree(ctx->mg_last); cudaFree(ctx->mg_slot_of);
+    ctx->mg_owner = nullptr; ctx->mg_first = nullptr; ctx->mg_last = nullptr; ctx->mg_slot_of = nullptr;
+    ctx->mg_records = 0;
+    const uint64_t cap = pow2_at_least((uint64_t)(max_records > 8 ? max_records : 8) * 2);
+    CUDA_TRY(ctx, cudaMalloc(&ctx->mg_owner, cap * 4));
+    CUDA_TRY(ctx, cudaMalloc(&ctx->mg_first, cap * 8));
+    CUDA_TRY(ctx, cudaMalloc(&ctx->mg_last, cap * 8));
+    CUDA_TRY(ctx, cudaMalloc(&ctx->mg_slot_of, (size_t)(max_records + 1) * 4));
+    ctx->mg_cap = cap;
+    ctx->mg_records = max_records;
+    return SMSGATE_OK;
+}
+
+extern "C" int smsgate_dedup_merge(smsgate_ctx* ctx, int64_t n_recv, const uint8_t* d_records, int64_t* d_verdicts) {
+    if (!ctx) return SMSGATE_E_ARG;
+    if (n_recv < 0) return fail(ctx, SMSGATE_E_ARG, "dedup_merge: negative count");
+    if (n_recv == 0) return SMSGATE_OK;
+    if (!d_records || !d_verdicts) return fail(ctx, SMSGATE_E_ARG, "dedup_merge: NULL array");
+    if (n_recv > ctx->mg_records) return fail(ctx, SMSGATE_E_STATE, "dedup_merge: more records than smsgate_reserve_merge() sized the table for");
+    CUDA_TRY(ctx, cudaSetDevice(ctx->device));
+    cudaStream_t st = ctx->stream;
+    uint64_t cap = pow2_at_least((uint64_t)(n_recv > 8 ? n_recv : 8) * 2);
+    if (cap > ctx->mg_cap) cap = ctx->mg_cap;
+    CUDA_TRY(ctx, cudaMemsetAsync(ctx->mg_owner, 0xFF, cap * 4, st));
+    CUDA_TRY(ctx, cudaMemsetAsync(ctx->mg_first, 0x7F, cap * 8, st));
+    CUDA_TRY(ctx, cudaMemsetAsync(ctx->mg_last, 0x00, cap * 8, st));
+    MergeScratch M{ctx->mg_owner, ctx->mg_first, ctx->mg_last, ctx->mg_slot_of, cap - 1};
+    const unsigned grid = (unsigned)((n_recv + 255) / 256);
+    k_merge_insert<<<grid, 256, 0, st>>>(n_recv, reinterpret_cast<const KeyRecord*>(d_records), M);
+    k_merge_verdict<<<grid, 256, 0, st>>>(n_recv, M, d_verdicts);
+    ctx->launches += 2;
+    CUDA_TRY(ctx, cudaGetLastError());
+    return SMSGATE_OK;
+}
+
+extern "C" int smsgate_dedup_apply(smsgate_ctx* ctx, int64_t n, int64_t base_index, int64_t n_rec,
+                                   const int32_t* d_rec_slot, const int64_t* d_verdicts, const smsgate_outputs* out) {
+    if (!ctx) return SMSGATE_E_ARG;
+    if (n < 0 || n_rec < 0 || !out) return fail(ctx, SMSGATE_E_ARG, "dedup_apply: bad argument");
+    if (n == 0) return SMSGATE_OK;
+    if (n > ctx->cap_msgs) return fail(ctx, SMSGATE_E_STATE, "dedup_apply: run smsgate_dedup on this batch first");
+    if (n_rec > 0 && (!d_rec_slot || !d_verdicts)) return fail(ctx, SMSGATE_E_ARG, "dedup_apply: NULL array");
+    CUDA_TRY(ctx, cudaSetDevice(ctx->device));
+    cudaStream_t st = ctx->stream;
+    if (n_rec > 0) {
+        k_apply_scatter<<<(unsigned)((n_rec + 255) / 256), 256, 0, st>>>(n_rec, d_rec_slot, d_verdicts, ctx->d_gfirst,
+                                                                         ctx->d_glast);
+        ctx->launches += 1;
+    }
+    k_apply_resolve<<<(unsigned)((n + 255) / 256), 256, 0, st>>>(n, base_index, ctx->d_slot_of, ctx->d_gfirst,
+                                                                 ctx->d_glast, out->survivor, out->first_seen,
+                                                                 out->last_idx);
+    ctx->launches += 1;
     CUDA_TRY(ctx, cudaGetLastError());
     return SMSGATE_OK;
 }

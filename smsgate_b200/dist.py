@@ -1,0 +1,110 @@
+"""Global upsert-by-msg_id across the GPUs of one node.
+
+The reference gets global idempotency from a unique key on `msg_id`
+(db/models.py:16; services/pb_writer/upsert.py:19-31; libs/pocketbase.py:168-200).
+With the backup sharded by index over `world` ranks that becomes exactly one
+exchange step: records of locally distinct keys travel to the rank that owns the
+key's hash prefix, the owner decides first / last occurrence globally, the
+verdicts travel back.  torch.distributed is the plumbing
+(NCCL over NVLink on the GPUs; gloo in the CPU tests of this module's logic);
+the record building, merging and applying are CUDA kernels behind the C ABI
+(smsgate_dedup_export / _merge / _apply).
+"""
+from __future__ import annotations
+
+import ctypes as C
+from typing import List, Sequence
+
+import numpy as np
+
+from . import _lib as L
+
+
+def owner_of_prefix(prefix32: np.ndarray, world: int) -> np.ndarray:
+    """Owner rank of a key whose first four digest bytes, big-endian, are `prefix32`:
+    a range partition of the 32-bit prefix space (same formula as key_owner() in the kernels)."""
+    return ((prefix32.astype(np.uint64) * np.uint64(world)) >> np.uint64(32)).astype(np.int64)
+
+
+class ExchangePlan:
+    """Variable-size all-to-all of fixed-width rows plus its mirror image."""
+
+    def __init__(self, dist, device=None, group=None):
+        self.dist = dist
+        self.group = group
+        self.world = dist.get_world_size(group)
+        self.rank = dist.get_rank(group)
+        self.device = device
+
+    def exchange_counts(self, send_counts: Sequence[int]) -> List[int]:
+        import torch
+        s = torch.tensor(list(send_counts), dtype=torch.int64, device=self.device)
+        r = torch.empty_like(s)
+        self.dist.all_to_all_single(r, s, group=self.group)
+        return [int(x) for x in r.cpu().tolist()]
+
+    def rows(self, send, send_counts: Sequence[int], recv_counts: Sequence[int], out=None):
+        """send: tensor [sum(send_counts), width] grouped by destination rank.
+        Returns the tensor [sum(recv_counts), width] grouped by source rank."""
+        import torch
+        n_recv = int(sum(recv_counts))
+        if out is None:
+            out = torch.empty((n_recv,) + tuple(send.shape[1:]), dtype=send.dtype, device=send.device)
+        else:
+            out = out[:n_recv]
+        self.dist.all_to_all_single(out, send[:int(sum(send_counts))], output_split_sizes=list(recv_counts),
+                                    input_split_sizes=list(send_counts), group=self.group)
+        return out
+
+
+class GlobalDedup:
+    """One rank's side of the global dedup.  `run(cols, base_index)` expects
+    smsgate_dedup to have been called on the local batch and rewrites
+    cols['survivor'], cols['first_seen'], cols['last_idx'] with the global verdicts."""
+
+    def __init__(self, engine, dist, n_max: int, group=None):
+        import torch
+        self.engine = engine
+        self.torch = torch
+        dev = torch.device("cuda", engine.device)
+        self.plan = ExchangePlan(dist, device=dev, group=group)
+        self.records = torch.empty((max(n_max, 1), L.RECORD_BYTES), dtype=torch.uint8, device=dev)
+        self.rec_slot = torch.empty(max(n_max, 1), dtype=torch.int32, device=dev)
+        self.h_counts = np.zeros(self.plan.world, dtype=np.int64)
+        self._recv = None
+        self._verdicts = None
+        self._back = None
+        self.launches = 0
+        self.bytes_sent = 0
+
+    def _buf(self, name: str, rows: int, width: int, dtype):
+        t = getattr(self, name)
+        if t is None or t.shape[0] < rows:
+            t = self.torch.empty((max(rows, 1), width), dtype=dtype, device=self.records.device)
+            setattr(self, name, t)
+        return t
+
+    def run(self, cols: dict, base_index: int) -> None:
+        eng, lib, torch = self.engine, L.lib(), self.torch
+        n = cols["status"].numel()
+        out = eng._dev_outputs(cols)
+        l0 = eng.launch_count
+        L.check(eng._ctx, lib.smsgate_dedup_export(eng._ctx, n, int(base_index), self.plan.world, C.byref(out),
+                                                   self.records.data_ptr(), self.rec_slot.data_ptr(),
+                                                   self.h_counts.ctypes.data_as(C.c_void_p)))
+        send_counts = [int(x) for x in self.h_counts]
+        n_rec = sum(send_counts)
+        recv_counts = self.plan.exchange_counts(send_counts)
+        n_recv = sum(recv_counts)
+        recv = self.plan.rows(self.records, send_counts, recv_counts,
+                              out=self._buf("_recv", n_recv, L.RECORD_BYTES, torch.uint8))
+        L.check(eng._ctx, lib.smsgate_reserve_merge(eng._ctx, n_recv))
+        verdicts = self._buf("_verdicts", n_recv, 2, torch.int64)
+        L.check(eng._ctx, lib.smsgate_dedup_merge(eng._ctx, n_recv, recv.data_ptr(), verdicts.data_ptr()))
+        back = self.plan.rows(verdicts, recv_counts, send_counts, out=self._buf("_back", n_rec, 2, torch.int64))
+        L.check(eng._ctx, lib.smsgate_dedup_apply(eng._ctx, n, int(base_index), n_rec, self.rec_slot.data_ptr(),
+                                                  back.data_ptr(), C.byref(out)))
+        self.launches += 0          # the context counts its own launches
+        self.bytes_sent += n_rec * L.RECORD_BYTES + n_recv * 16
+        self.last_counts = (send_counts, recv_counts)
+        self.last_launches = eng.launch_count - l0

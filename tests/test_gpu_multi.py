@@ -1,0 +1,143 @@
+"""Global dedup kernels (export / merge / apply).
+
+1. One GPU playing R ranks: R contexts on cuda:0, each with its own shard; the
+   all-to-all is done by slicing tensors in this process.  Checks the three
+   kernels and the record layout against the oracle's global upsert.
+2. Two real ranks over NCCL when the box has two GPUs (skipped otherwise)."""
+import ctypes as C
+import datetime as dt
+import os
+import socket
+
+import numpy as np
+import pytest
+
+from oracle import replay_oracle as O
+from smsgate_b200 import _lib as L
+from smsgate_b200 import synth
+from smsgate_b200.batch import Batch
+
+pytestmark = pytest.mark.gpu
+NOW = dt.datetime(2026, 1, 1)
+
+
+def _global_oracle(backup):
+    raw = [O.iso_utc_from_ms(m) for m in backup.date_ms]
+    return O.replay(backup.bodies, backup.senders, raw, backup.cache, NOW)
+
+
+@pytest.mark.parametrize("world", [2, 3, 8])
+def test_ranks_emulated_on_one_gpu(world):
+    import torch
+
+    from smsgate_b200.replay import ReplayEngine
+    lib = L.lib()
+    n_per = 4000
+    backup = synth.generate(n_per * world, seed=300 + world, dup_frac=0.5, hot_key_zipf=1.2, miss_frac=0.05)
+    ora = _global_oracle(backup)
+    engines, cols, recs, slots, counts = [], [], [], [], []
+    base0 = (1 << 34)                                             # indices beyond 32 bits
+    for r in range(world):
+        eng = ReplayEngine(0)
+        eng.load_cache(backup.cache)
+        lo, hi = r * n_per, (r + 1) * n_per
+        b = Batch.from_strings(backup.bodies[lo:hi], backup.senders[lo:hi], backup.date_ms[lo:hi])
+        d_bytes = torch.from_numpy(b.body_bytes.copy()).cuda()
+        d_off = torch.from_numpy(b.body_offsets.copy()).cuda()
+        c = eng.device_columns(b.n, d_bytes.numel())
+        eng.reserve(b.n, d_bytes.numel())
+        eng.replay_device(d_bytes, d_off, NOW, c, base_index=base0 + lo)
+        rec = torch.empty((n_per, L.RECORD_BYTES), dtype=torch.uint8, device="cuda")
+        slot = torch.empty(n_per, dtype=torch.int32, device="cuda")
+        h_counts = np.zeros(world, np.int64)
+        out = eng._dev_outputs(c)
+        L.check(eng._ctx, lib.smsgate_dedup_export(eng._ctx, b.n, base0 + lo, world, C.byref(out), rec.data_ptr(),
+                                                   slot.data_ptr(), h_counts.ctypes.data_as(C.c_void_p)))
+        engines.append(eng); cols.append(c); recs.append(rec); slots.append(slot); counts.append(h_counts.copy())
+    torch.cuda.synchronize()
+    # all-to-all by slicing: owner o receives, from every rank r in order, r's bucket o
+    starts = [np.concatenate([[0], np.cumsum(c)]) for c in counts]
+    verdict_back = [torch.empty((int(counts[r].sum()), 2), dtype=torch.int64, device="cuda") for r in range(world)]
+    for o in range(world):
+        parts = [recs[r][int(starts[r][o]):int(starts[r][o + 1])] for r in range(world)]
+        recv = torch.cat(parts) if parts else torch.empty((0, 32), dtype=torch.uint8, device="cuda")
+        n_recv = recv.shape[0]
+        eng = engines[o]
+        L.check(eng._ctx, lib.smsgate_reserve_merge(eng._ctx, n_recv))
+        ver = torch.empty((max(n_recv, 1), 2), dtype=torch.int64, device="cuda")
+        L.check(eng._ctx, lib.smsgate_dedup_merge(eng._ctx, n_recv, recv.contiguous().data_ptr(), ver.data_ptr()))
+        torch.cuda.synchronize()
+        pos = 0
+        for r in range(world):
+            k = int(counts[r][o])
+            verdict_back[r][int(starts[r][o]):int(starts[r][o + 1])] = ver[pos:pos + k]
+            pos += k
+    got_s, got_f, got_l = [], [], []
+    for r in range(world):
+        eng = engines[r]
+        out = eng._dev_outputs(cols[r])
+        n_rec = int(counts[r].sum())
+        L.check(eng._ctx, lib.smsgate_dedup_apply(eng._ctx, n_per, base0 + r * n_per, n_rec, slots[r].data_ptr(),
+                                                  verdict_back[r].data_ptr(), C.byref(out)))
+        torch.cuda.synchronize()
+        got_s.append(cols[r]["survivor"].cpu().numpy())
+        got_f.append(cols[r]["first_seen"].cpu().numpy())
+        got_l.append(cols[r]["last_idx"].cpu().numpy())
+        eng.close()
+    assert np.array_equal(np.concatenate(got_s) != 0, np.array(ora.survivor))
+    assert np.array_equal(np.concatenate(got_f) != 0, np.array(ora.first_seen))
+    want_l = np.array([(-1 if x < 0 else base0 + x) for x in ora.last_idx], np.int64)
+    assert np.array_equal(np.concatenate(got_l), want_l)
+
+
+def _nccl_worker(rank, world, port, n_per, q):
+    import torch
+    import torch.distributed as dist
+
+    from smsgate_b200.dist import GlobalDedup
+    from smsgate_b200.replay import ReplayEngine
+    os.environ["MASTER_ADDR"] = "127.0.0.1"
+    os.environ["MASTER_PORT"] = str(port)
+    torch.cuda.set_device(rank)
+    dist.init_process_group("nccl", rank=rank, world_size=world, device_id=torch.device("cuda", rank))
+    try:
+        backup = synth.generate(n_per * world, seed=500, dup_frac=0.5, hot_key_zipf=1.2)
+        lo, hi = rank * n_per, (rank + 1) * n_per
+        b = Batch.from_strings(backup.bodies[lo:hi], backup.senders[lo:hi], backup.date_ms[lo:hi])
+        eng = ReplayEngine(rank)
+        eng.load_cache(backup.cache)
+        d_bytes = torch.from_numpy(b.body_bytes.copy()).cuda()
+        d_off = torch.from_numpy(b.body_offsets.copy()).cuda()
+        c = eng.device_columns(b.n, d_bytes.numel())
+        eng.reserve(b.n, d_bytes.numel())
+        eng.replay_device(d_bytes, d_off, NOW, c, base_index=lo)
+        GlobalDedup(eng, dist, b.n).run(c, lo)
+        torch.cuda.synchronize()
+        q.put((rank, c["survivor"].cpu().numpy(), c["first_seen"].cpu().numpy(), c["last_idx"].cpu().numpy()))
+        eng.close()
+    finally:
+        dist.destroy_process_group()
+
+
+@pytest.mark.timeout(600)
+def test_two_ranks_over_nccl():
+    import torch
+    if torch.cuda.device_count() < 2:
+        pytest.skip("needs two GPUs")
+    import torch.multiprocessing as mp
+    world, n_per = 2, 20000
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    s = socket.socket(); s.bind(("127.0.0.1", 0)); port = s.getsockname()[1]; s.close()
+    procs = [ctx.Process(target=_nccl_worker, args=(r, world, port, n_per, q)) for r in range(world)]
+    for p in procs:
+        p.start()
+    res = sorted((q.get(timeout=500) for _ in range(world)), key=lambda t: t[0])
+    for p in procs:
+        p.join(timeout=60)
+        assert p.exitcode == 0
+    backup = synth.generate(n_per * world, seed=500, dup_frac=0.5, hot_key_zipf=1.2)
+    ora = _global_oracle(backup)
+    assert np.array_equal(np.concatenate([r[1] for r in res]) != 0, np.array(ora.survivor))
+    assert np.array_equal(np.concatenate([r[2] for r in res]) != 0, np.array(ora.first_seen))
+    assert np.array_equal(np.concatenate([r[3] for r in res]), np.array(ora.last_idx, np.int64))
