@@ -274,7 +274,7 @@ def run_ours(args, rank, world, local_rank):
         torch.cuda.synchronize()
         e0, e1 = ev(), ev()
         e0.record()
-        res = eng.replay(hb, NOW, base_index=base_index, columns=RESULT_COLUMNS, pinned=True)
+        res = eng.replay(hb, NOW, base_index=base_index, columns=RESULT_COLUMNS, pinned=True, exchange=exchange)
         e1.record()
         e1.synchronize()
         if it >= args.warmup:

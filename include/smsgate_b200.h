@@ -194,6 +194,16 @@ int smsgate_dedup_apply(smsgate_ctx* ctx, int64_t n, int64_t base_index, int64_t
  * total_bytes = h_offsets[n].  Needs smsgate_reserve() to have covered n. */
 int smsgate_replay_host(smsgate_ctx* ctx, const uint8_t* h_bytes, const int64_t* h_offsets, int64_t n,
                         int64_t now_packed, int64_t base_index, const smsgate_outputs* h_out);
+/* The same call in two halves, for a multi-GPU replay that has to run the global
+ * dedup exchange on the device-resident columns in between: _begin queues the
+ * chunked copy-in, stages 1-3 and the copy-out of every column except survivor /
+ * first_seen / last_idx and returns without waiting; smsgate_device_view gives the
+ * device columns of the pending batch; _finish copies the three dedup columns out
+ * and synchronises.  Host buffers should be pinned for the copies to overlap. */
+int smsgate_replay_host_begin(smsgate_ctx* ctx, const uint8_t* h_bytes, const int64_t* h_offsets, int64_t n,
+                              int64_t now_packed, int64_t base_index, const smsgate_outputs* h_out);
+int smsgate_device_view(smsgate_ctx* ctx, int64_t n, smsgate_outputs* d_out);
+int smsgate_replay_host_finish(smsgate_ctx* ctx, const smsgate_outputs* h_out);
 
 /* ---- upsert-by-msg_id for callers that must not allocate -------------------
  * No counterpart in the reference (it has no device memory to manage).

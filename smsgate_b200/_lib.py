@@ -76,6 +76,9 @@ def lib():
         "smsgate_dedup": (i32, [vp, i64, i64, C.POINTER(Outputs)]),
         "smsgate_replay_device": (i32, [vp, vp, vp, i64, i64, i64, C.POINTER(Outputs)]),
         "smsgate_replay_host": (i32, [vp, vp, vp, i64, i64, i64, C.POINTER(Outputs)]),
+        "smsgate_replay_host_begin": (i32, [vp, vp, vp, i64, i64, i64, C.POINTER(Outputs)]),
+        "smsgate_device_view": (i32, [vp, i64, C.POINTER(Outputs)]),
+        "smsgate_replay_host_finish": (i32, [vp, C.POINTER(Outputs)]),
         "smsgate_dedup_export": (i32, [vp, i64, i64, i32, C.POINTER(Outputs), vp, vp, vp]),
         "smsgate_reserve_merge": (i32, [vp, i64]),
         "smsgate_dedup_merge": (i32, [vp, i64, vp, vp]),

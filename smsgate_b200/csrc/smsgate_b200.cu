@@ -488,6 +488,12 @@ struct smsgate_ctx {
     int device = 0;
     cudaStream_t stream = nullptr;
     bool own_stream = false;
+    // smsgate_replay_host overlaps host->device copies, kernels and device->host copies chunk by chunk
+    cudaStream_t s_h2d = nullptr, s_d2h = nullptr;
+    static const int MAX_CHUNKS = 16;
+    cudaEvent_t ev_in[MAX_CHUNKS] = {nullptr}, ev_k[MAX_CHUNKS] = {nullptr};
+    cudaEvent_t ev_start = nullptr, ev_dedup = nullptr, ev_done = nullptr;
+    int64_t host_n = 0, host_total = 0;      // batch of the pending smsgate_replay_host_begin
     int sm_count = 148;
     std::string err;
     int64_t launches = 0;
@@ -576,6 +582,15 @@ extern "C" int smsgate_create(int device, void* cuda_stream, smsgate_ctx** out) 
     }
     ctx->sm_count = prop.multiProcessorCount;
     ctx->stream = (cudaStream_t)cuda_stream;          // NULL is CUDA's default stream
+    if ((e = cudaStreamCreateWithFlags(&ctx->s_h2d, cudaStreamNonBlocking)) != cudaSuccess) return bail("cudaStreamCreate", e);
+    if ((e = cudaStreamCreateWithFlags(&ctx->s_d2h, cudaStreamNonBlocking)) != cudaSuccess) return bail("cudaStreamCreate", e);
+    for (int k = 0; k < smsgate_ctx::MAX_CHUNKS; ++k) {
+        if ((e = cudaEventCreateWithFlags(&ctx->ev_in[k], cudaEventDisableTiming)) != cudaSuccess) return bail("cudaEventCreate", e);
+        if ((e = cudaEventCreateWithFlags(&ctx->ev_k[k], cudaEventDisableTiming)) != cudaSuccess) return bail("cudaEventCreate", e);
+    }
+    if ((e = cudaEventCreateWithFlags(&ctx->ev_start, cudaEventDisableTiming)) != cudaSuccess) return bail("cudaEventCreate", e);
+    if ((e = cudaEventCreateWithFlags(&ctx->ev_dedup, cudaEventDisableTiming)) != cudaSuccess) return bail("cudaEventCreate", e);
+    if ((e = cudaEventCreateWithFlags(&ctx->ev_done, cudaEventDisableTiming)) != cudaSuccess) return bail("cudaEventCreate", e);
     DeviceTables* h = new DeviceTables();
     sg_fill_tables(h);
     if ((e = cudaMalloc(&ctx->d_tables, sizeof(DeviceTables))) != cudaSuccess) { delete h; return bail("cudaMalloc tables", e); }
@@ -613,6 +628,15 @@ extern "C" void smsgate_destroy(smsgate_ctx* ctx) {
     free_scratch(ctx);
     cudaFree(ctx->mg_owner); cudaFree(ctx->mg_first); cudaFree(ctx->mg_last); cudaFree(ctx->mg_slot_of);
     cudaFree(ctx->d_tables);
+    if (ctx->s_h2d) { cudaStreamSynchronize(ctx->s_h2d); cudaStreamDestroy(ctx->s_h2d); }
+    if (ctx->s_d2h) { cudaStreamSynchronize(ctx->s_d2h); cudaStreamDestroy(ctx->s_d2h); }
+    for (int k = 0; k < smsgate_ctx::MAX_CHUNKS; ++k) {
+        if (ctx->ev_in[k]) cudaEventDestroy(ctx->ev_in[k]);
+        if (ctx->ev_k[k]) cudaEventDestroy(ctx->ev_k[k]);
+    }
+    if (ctx->ev_start) cudaEventDestroy(ctx->ev_start);
+    if (ctx->ev_dedup) cudaEventDestroy(ctx->ev_dedup);
+    if (ctx->ev_done) cudaEventDestroy(ctx->ev_done);
     if (ctx->own_stream) cudaStreamDestroy(ctx->stream);
     delete ctx;
 }
@@ -847,10 +871,30 @@ static void carve_slab(uint8_t* slab, int64_t n, uint8_t* fixed, smsgate_outputs
     d->fixed_bytes = fixed;
 }
 
-extern "C" int smsgate_replay_host(smsgate_ctx* ctx, const uint8_t* h_bytes, const int64_t* h_offsets, int64_t n,
-                                   int64_t now_packed, int64_t base_index, const smsgate_outputs* h_out) {
+// column pointers shifted to message `lo` (fixed_bytes is addressed by absolute byte offsets and stays)
+static smsgate_outputs shift_columns(const smsgate_outputs& d, int64_t lo) {
+    smsgate_outputs o = d;
+#define SH(col, w) if (o.col) o.col = o.col + lo * (w)
+    SH(msg_id, 20); SH(cache_key, 32); SH(flags, 1); SH(body_date, 1); SH(fixed_len, 1); SH(slot, 1); SH(status, 1);
+    SH(amount_coef, 1); SH(balance_coef, 1); SH(amount_exp, 1); SH(balance_exp, 1); SH(dec_flags, 1); SH(date, 1);
+    SH(card, 16); SH(card_len, 1); SH(survivor, 1); SH(first_seen, 1); SH(last_idx, 1);
+#undef SH
+    return o;
+}
+
+extern "C" int smsgate_device_view(smsgate_ctx* ctx, int64_t n, smsgate_outputs* d_out) {
+    if (!ctx || !d_out) return SMSGATE_E_ARG;
+    if (n < 0 || n > ctx->cap_msgs) return fail(ctx, SMSGATE_E_STATE, "device_view: n exceeds the reserved scratch");
+    carve_slab(ctx->s_out, n, ctx->s_fixed, d_out);
+    return SMSGATE_OK;
+}
+
+extern "C" int smsgate_replay_host_begin(smsgate_ctx* ctx, const uint8_t* h_bytes, const int64_t* h_offsets, int64_t n,
+                                         int64_t now_packed, int64_t base_index, const smsgate_outputs* h_out) {
     if (!ctx) return SMSGATE_E_ARG;
     if (n < 0 || !h_out || (n > 0 && (!h_offsets))) return fail(ctx, SMSGATE_E_ARG, "replay_host: NULL argument");
+    ctx->host_n = 0;
+    ctx->host_total = 0;
     if (n == 0) return SMSGATE_OK;
     const int64_t first = h_offsets[0], total = h_offsets[n];
     if (first != 0) return fail(ctx, SMSGATE_E_ARG, "replay_host: offsets[0] must be 0");
@@ -858,24 +902,84 @@ extern "C" int smsgate_replay_host(smsgate_ctx* ctx, const uint8_t* h_bytes, con
     if (n > ctx->cap_msgs || total > ctx->cap_bytes)
         return fail(ctx, SMSGATE_E_STATE, "replay_host: batch larger than smsgate_reserve() sized the scratch for");
     CUDA_TRY(ctx, cudaSetDevice(ctx->device));
-    cudaStream_t st = ctx->stream;
-    CUDA_TRY(ctx, cudaMemcpyAsync(ctx->s_offsets, h_offsets, (size_t)(n + 1) * 8, cudaMemcpyHostToDevice, st));
-    if (total) CUDA_TRY(ctx, cudaMemcpyAsync(ctx->s_bytes, h_bytes, (size_t)total, cudaMemcpyHostToDevice, st));
+    cudaStream_t st = ctx->stream, sin = ctx->s_h2d, sout = ctx->s_d2h;
     smsgate_outputs d;
     carve_slab(ctx->s_out, n, ctx->s_fixed, &d);
-    int rc = smsgate_replay_device(ctx, ctx->s_bytes, ctx->s_offsets, n, now_packed, base_index, &d);
-    if (rc) return rc;
-#define BACK(col, bytes) \
-    if (h_out->col) CUDA_TRY(ctx, cudaMemcpyAsync(h_out->col, d.col, (size_t)(bytes), cudaMemcpyDeviceToHost, st))
-    BACK(msg_id, n * 20); BACK(cache_key, n * 32); BACK(flags, n); BACK(body_date, n * 4); BACK(fixed_len, n * 4);
-    BACK(slot, n * 4); BACK(status, n); BACK(amount_coef, n * 8); BACK(balance_coef, n * 8); BACK(amount_exp, n * 4);
-    BACK(balance_exp, n * 4); BACK(dec_flags, n); BACK(date, n * 8); BACK(card, n * 16); BACK(card_len, n);
-    BACK(survivor, n); BACK(first_seen, n); BACK(last_idx, n * 8);
-    if (h_out->fixed_bytes && total) BACK(fixed_bytes, total);
+    // chunks of >= 64 Ki messages, at most MAX_CHUNKS: copy-in of chunk c+1 and copy-out of chunk c-1
+    // overlap the kernels of chunk c (PCIe is full duplex; the copies dominate the end-to-end time)
+    int nchunks = (int)((n + 65535) / 65536);
+    if (nchunks > smsgate_ctx::MAX_CHUNKS) nchunks = smsgate_ctx::MAX_CHUNKS;
+    if (nchunks < 1) nchunks = 1;
+    const int64_t per = (n + nchunks - 1) / nchunks;
+    // nothing of this call may start before what the caller queued on its stream earlier
+    CUDA_TRY(ctx, cudaEventRecord(ctx->ev_start, st));
+    CUDA_TRY(ctx, cudaStreamWaitEvent(sin, ctx->ev_start, 0));
+    CUDA_TRY(ctx, cudaStreamWaitEvent(sout, ctx->ev_start, 0));
+    for (int c = 0; c < nchunks; ++c) {
+        const int64_t lo = c * per, hi = (lo + per < n) ? lo + per : n;
+        if (lo >= hi) { nchunks = c; break; }
+        const int64_t b0 = h_offsets[lo], b1 = h_offsets[hi];
+        CUDA_TRY(ctx, cudaMemcpyAsync(ctx->s_offsets + lo, h_offsets + lo, (size_t)(hi - lo + 1) * 8, cudaMemcpyHostToDevice, sin));
+        if (b1 > b0) CUDA_TRY(ctx, cudaMemcpyAsync(ctx->s_bytes + b0, h_bytes + b0, (size_t)(b1 - b0), cudaMemcpyHostToDevice, sin));
+        CUDA_TRY(ctx, cudaEventRecord(ctx->ev_in[c], sin));
+    }
+    for (int c = 0; c < nchunks; ++c) {
+        const int64_t lo = c * per, hi = (lo + per < n) ? lo + per : n;
+        const int64_t m = hi - lo;
+        CUDA_TRY(ctx, cudaStreamWaitEvent(st, ctx->ev_in[c], 0));
+        const smsgate_outputs dc = shift_columns(d, lo);
+        int rc = smsgate_scan_keys(ctx, ctx->s_bytes, ctx->s_offsets + lo, m, &dc);
+        if (rc) return rc;
+        rc = smsgate_join_route(ctx, m, now_packed, &dc);
+        if (rc) return rc;
+        CUDA_TRY(ctx, cudaEventRecord(ctx->ev_k[c], st));
+        CUDA_TRY(ctx, cudaStreamWaitEvent(sout, ctx->ev_k[c], 0));
+#define BACK(col, w) \
+    if (h_out->col) CUDA_TRY(ctx, cudaMemcpyAsync(h_out->col + lo * (w), d.col + lo * (w), (size_t)(m * (w)) * sizeof(*d.col), cudaMemcpyDeviceToHost, sout))
+        BACK(msg_id, 20); BACK(cache_key, 32); BACK(flags, 1); BACK(body_date, 1); BACK(fixed_len, 1); BACK(slot, 1);
+        BACK(status, 1); BACK(amount_coef, 1); BACK(balance_coef, 1); BACK(amount_exp, 1); BACK(balance_exp, 1);
+        BACK(dec_flags, 1); BACK(date, 1); BACK(card, 16); BACK(card_len, 1);
 #undef BACK
-    CUDA_TRY(ctx, cudaStreamSynchronize(st));
-    CUDA_TRY(ctx, cudaGetLastError());
+        if (h_out->fixed_bytes) {
+            const int64_t b0 = h_offsets[lo], b1 = h_offsets[hi];
+            if (b1 > b0) CUDA_TRY(ctx, cudaMemcpyAsync(h_out->fixed_bytes + b0, d.fixed_bytes + b0, (size_t)(b1 - b0), cudaMemcpyDeviceToHost, sout));
+        }
+    }
+    int rc = smsgate_dedup(ctx, n, base_index, &d);
+    if (rc) return rc;
+    ctx->host_n = n;
+    ctx->host_total = total;
     return SMSGATE_OK;
+}
+
+extern "C" int smsgate_replay_host_finish(smsgate_ctx* ctx, const smsgate_outputs* h_out) {
+    if (!ctx || !h_out) return SMSGATE_E_ARG;
+    const int64_t n = ctx->host_n;
+    if (n == 0) return SMSGATE_OK;
+    CUDA_TRY(ctx, cudaSetDevice(ctx->device));
+    cudaStream_t st = ctx->stream, sout = ctx->s_d2h;
+    smsgate_outputs d;
+    carve_slab(ctx->s_out, n, ctx->s_fixed, &d);
+    CUDA_TRY(ctx, cudaEventRecord(ctx->ev_dedup, st));
+    CUDA_TRY(ctx, cudaStreamWaitEvent(sout, ctx->ev_dedup, 0));
+    if (h_out->survivor) CUDA_TRY(ctx, cudaMemcpyAsync(h_out->survivor, d.survivor, (size_t)n, cudaMemcpyDeviceToHost, sout));
+    if (h_out->first_seen) CUDA_TRY(ctx, cudaMemcpyAsync(h_out->first_seen, d.first_seen, (size_t)n, cudaMemcpyDeviceToHost, sout));
+    if (h_out->last_idx) CUDA_TRY(ctx, cudaMemcpyAsync(h_out->last_idx, d.last_idx, (size_t)n * 8, cudaMemcpyDeviceToHost, sout));
+    // the caller's stream is complete only when the copy-out stream is
+    CUDA_TRY(ctx, cudaEventRecord(ctx->ev_done, sout));
+    CUDA_TRY(ctx, cudaStreamWaitEvent(st, ctx->ev_done, 0));
+    CUDA_TRY(ctx, cudaStreamSynchronize(st));
+    CUDA_TRY(ctx, cudaStreamSynchronize(ctx->s_h2d));
+    CUDA_TRY(ctx, cudaGetLastError());
+    ctx->host_n = 0;
+    return SMSGATE_OK;
+}
+
+extern "C" int smsgate_replay_host(smsgate_ctx* ctx, const uint8_t* h_bytes, const int64_t* h_offsets, int64_t n,
+                                   int64_t now_packed, int64_t base_index, const smsgate_outputs* h_out) {
+    const int rc = smsgate_replay_host_begin(ctx, h_bytes, h_offsets, n, now_packed, base_index, h_out);
+    if (rc) return rc;
+    return smsgate_replay_host_finish(ctx, h_out);
 }
 
 // ================================================================== global dedup across GPUs

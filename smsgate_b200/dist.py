@@ -85,9 +85,11 @@ class GlobalDedup:
         return t
 
     def run(self, cols: dict, base_index: int) -> None:
+        self.run_outputs(self.engine._dev_outputs(cols), cols["status"].numel(), base_index)
+
+    def run_outputs(self, out: "L.Outputs", n: int, base_index: int) -> None:
+        """Same, on a raw `smsgate_outputs` of device pointers (e.g. smsgate_device_view)."""
         eng, lib, torch = self.engine, L.lib(), self.torch
-        n = cols["status"].numel()
-        out = eng._dev_outputs(cols)
         l0 = eng.launch_count
         L.check(eng._ctx, lib.smsgate_dedup_export(eng._ctx, n, int(base_index), self.plan.world, C.byref(out),
                                                    self.records.data_ptr(), self.rec_slot.data_ptr(),

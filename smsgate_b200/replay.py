@@ -221,9 +221,11 @@ class ReplayEngine:
     ALL_COLUMNS = tuple(name for name, _, _ in L.COLUMNS)
 
     def replay(self, batch: Batch, now: _dt.datetime, base_index: int = 0,
-               columns: Optional[Sequence[str]] = None, pinned: bool = False) -> ReplayResult:
+               columns: Optional[Sequence[str]] = None, pinned: bool = False, exchange=None) -> ReplayResult:
         """Replay a host-resident batch end to end (host->device copy, three
-        kernel stages, device->host copy of the requested columns)."""
+        kernel stages, device->host copy of the requested columns).  With
+        `exchange` (a dist.GlobalDedup) the batch is this rank's shard and the
+        dedup verdicts are made global before they are copied out."""
         n = batch.n
         total = int(batch.body_offsets[-1]) if n else 0
         self.reserve(max(n, 1), max(total, 1))
@@ -232,8 +234,16 @@ class ReplayEngine:
         out = L.Outputs(**{k: (v.ctypes.data if v.size else None) for k, v in cols.items()})
         body = np.ascontiguousarray(batch.body_bytes)
         offs = np.ascontiguousarray(batch.body_offsets, dtype=np.int64)
-        L.check(self._ctx, self._lib.smsgate_replay_host(self._ctx, _np_ptr(body), _np_ptr(offs), n,
-                                                         pack_datetime(now), int(base_index), C.byref(out)))
+        if exchange is None:
+            L.check(self._ctx, self._lib.smsgate_replay_host(self._ctx, _np_ptr(body), _np_ptr(offs), n,
+                                                             pack_datetime(now), int(base_index), C.byref(out)))
+        else:
+            L.check(self._ctx, self._lib.smsgate_replay_host_begin(self._ctx, _np_ptr(body), _np_ptr(offs), n,
+                                                                   pack_datetime(now), int(base_index), C.byref(out)))
+            view = L.Outputs()
+            L.check(self._ctx, self._lib.smsgate_device_view(self._ctx, n, C.byref(view)))
+            exchange.run_outputs(view, n, int(base_index))
+            L.check(self._ctx, self._lib.smsgate_replay_host_finish(self._ctx, C.byref(out)))
         return ReplayResult(batch, cols, self.table, base_index)
 
     # -- device-pointer stages (torch tensors) -------------------------------
