@@ -218,8 +218,8 @@ def run_ours(args, rank, world, local_rank):
 
     exchange = None
     if world > 1:
-        from smsgate_b200.dist import GlobalDedup
-        exchange = GlobalDedup(eng, dist, n)
+        from smsgate_b200.dist import make_global_dedup
+        exchange = make_global_dedup(eng, dist, n, prefer_p2p=not args.nccl_exchange)
 
     # ---- resident inputs / outputs
     h_bytes = torch.from_numpy(batch.body_bytes.copy()).pin_memory()
@@ -313,7 +313,7 @@ def run_ours(args, rank, world, local_rank):
         "vs_baseline": None, "dtype": "u8/u32/int64", "data": "synthetic",
         "config": {"workload": workload_name(n), "msgs_per_gpu": n, "mean_body_bytes": round(mean_len, 1),
                    "cache_entries": len(backup.cache), "l2": "512 MiB buffer written between timed steps",
-                   "parallelism": f"shard-by-index x{world}" + (", all-to-all by msg_id prefix" if world > 1 else "")},
+                   "parallelism": f"shard-by-index x{world}" + (f", {type(exchange).__name__} exchange by msg_id prefix" if world > 1 else "")},
         "clocks": clocks,
         "e2e": {"value": world * n / (e2e * 1e-3), "unit": UNIT, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
                 "ms_per_step": e2e},
@@ -341,6 +341,7 @@ def main():
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--msgs", type=int, default=N_PER_GPU, help="messages per GPU (default: configs[1])")
     ap.add_argument("--cpu-sample", type=int, default=60_000)
+    ap.add_argument("--nccl-exchange", action="store_true", help="use the NCCL all-to-all exchange instead of peer memory")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3) if args.impl == "ours" else args.warmup
     rank = int(os.environ.get("RANK", "0"))

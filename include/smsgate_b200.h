@@ -187,6 +187,34 @@ int smsgate_dedup_merge(smsgate_ctx* ctx, int64_t n_recv, const uint8_t* d_recor
 int smsgate_dedup_apply(smsgate_ctx* ctx, int64_t n, int64_t base_index, int64_t n_rec, const int32_t* d_rec_slot,
                         const int64_t* d_verdicts, const smsgate_outputs* out);
 
+/* ---- the same exchange over peer memory (NVLink P2P) ------------------------
+ * One process per GPU; every rank maps every other rank's inbox, arrival counters and
+ * verdict arrays (e.g. through torch.distributed._symmetric_memory) and passes the
+ * mapped pointers in `smsgate_p2p`.  smsgate_p2p_scatter stores the export records
+ * straight into the owners' inboxes (one remote atomic per destination reserves the
+ * range), smsgate_p2p_merge stores a verdict straight into the home rank's gfl array
+ * whenever another rank's copy of the key changes it, smsgate_p2p_resolve rewrites
+ * survivor / first_seen / last_idx.
+ * The caller puts a cross-GPU barrier between scatter and merge and between merge and
+ * resolve; nothing is copied through host memory and no count is exchanged.
+ * `parity` alternates 0/1 from one batch to the next (two arrival counters). */
+#define SMSGATE_P2P_RECORD_BYTES 48
+typedef struct smsgate_p2p {
+    int32_t world, rank;
+    uint8_t* inbox[SMSGATE_MAX_WORLD];    /* [capacity * SMSGATE_P2P_RECORD_BYTES] per rank */
+    int32_t* in_count[SMSGATE_MAX_WORLD]; /* [2] per rank, zero before the first batch */
+    int64_t* gfl[SMSGATE_MAX_WORLD];      /* [2 * (pow2 >= 2 * max batch)] per rank: {first, last} per local slot, 16-byte aligned */
+    int64_t capacity;                     /* records per inbox; world * max batch never overflows */
+} smsgate_p2p;
+/* Size the owner-side table for inboxes of `capacity` records.  Allocates. */
+int smsgate_p2p_reserve(smsgate_ctx* ctx, int64_t capacity);
+int smsgate_p2p_scatter(smsgate_ctx* ctx, int64_t n, int64_t base_index, int parity, const smsgate_outputs* out,
+                        const smsgate_p2p* p);
+int smsgate_p2p_merge(smsgate_ctx* ctx, int parity, const smsgate_p2p* p);
+/* h_overflow (optional, host): set to 1 if an inbox ever overflowed; passing it synchronises. */
+int smsgate_p2p_resolve(smsgate_ctx* ctx, int64_t n, int64_t base_index, const smsgate_outputs* out,
+                        const smsgate_p2p* p, int* h_overflow);
+
 /* ---- the replay, host buffers --------------------------------------------
  * What `_iter_sms` -> worker -> parse_sms_llm -> pb_writer do for a whole
  * backup, called with the batch in host memory: copies in, runs the three

@@ -26,6 +26,7 @@ DEC_OK, DEC_SYNTAX, DEC_OVERFLOW = 0, 1, 2
 DEDUP_STATIC_MAX = 1 << 20
 MAX_WORLD = 64
 RECORD_BYTES = 32
+P2P_RECORD_BYTES = 48
 E_LIMIT = -5
 
 # (column name, numpy dtype string, elements per message)
@@ -40,6 +41,13 @@ COLUMNS = (
 
 class Outputs(C.Structure):
     _fields_ = [(name, C.c_void_p) for name, _, _ in COLUMNS]
+
+
+class P2P(C.Structure):
+    """struct smsgate_p2p"""
+    _fields_ = [("world", C.c_int32), ("rank", C.c_int32),
+                ("inbox", C.c_void_p * 64), ("in_count", C.c_void_p * 64),
+                ("gfl", C.c_void_p * 64), ("capacity", C.c_int64)]
 
 
 class LibraryMissing(RuntimeError):
@@ -83,6 +91,10 @@ def lib():
         "smsgate_reserve_merge": (i32, [vp, i64]),
         "smsgate_dedup_merge": (i32, [vp, i64, vp, vp]),
         "smsgate_dedup_apply": (i32, [vp, i64, i64, i64, vp, vp, C.POINTER(Outputs)]),
+        "smsgate_p2p_reserve": (i32, [vp, i64]),
+        "smsgate_p2p_scatter": (i32, [vp, i64, i64, i32, C.POINTER(Outputs), C.POINTER(P2P)]),
+        "smsgate_p2p_merge": (i32, [vp, i32, C.POINTER(P2P)]),
+        "smsgate_p2p_resolve": (i32, [vp, i64, i64, C.POINTER(Outputs), C.POINTER(P2P), vp]),
         "smsgate_dedup_static": (i32, [i32, vp, i64, i64, vp, vp, vp, vp, vp, C.c_char_p, i32]),
     }
     for name, (res, args) in sigs.items():

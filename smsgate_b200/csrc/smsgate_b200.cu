@@ -513,6 +513,12 @@ struct smsgate_ctx {
     uint64_t dd_cap = 0;
     int64_t *d_gfirst = nullptr, *d_glast = nullptr;   // [dd_cap] global first / last index per local slot
     int* d_counts = nullptr;                            // [SMSGATE_MAX_WORLD] export counters / cursors
+    int* d_cursor = nullptr;                            // [SMSGATE_MAX_WORLD] peer-exchange cursors
+    // peer-memory exchange (smsgate_p2p_reserve)
+    int64_t p2p_capacity = 0;
+    struct P2PSlot* p2p_table = nullptr;
+    int32_t* p2p_slot_of = nullptr;
+    int* p2p_overflow = nullptr;
     // owner-side merge table (smsgate_reserve_merge)
     int64_t mg_records = 0;
     uint64_t mg_cap = 0;
@@ -612,8 +618,8 @@ static void free_cache(smsgate_ctx* c) {
 }
 static void free_scratch(smsgate_ctx* c) {
     cudaFree(c->d_owner); cudaFree(c->d_first); cudaFree(c->d_last); cudaFree(c->d_slot_of);
-    cudaFree(c->d_gfirst); cudaFree(c->d_glast); cudaFree(c->d_counts);
-    c->d_gfirst = c->d_glast = nullptr; c->d_counts = nullptr;
+    cudaFree(c->d_gfirst); cudaFree(c->d_glast); cudaFree(c->d_counts); cudaFree(c->d_cursor);
+    c->d_gfirst = c->d_glast = nullptr; c->d_counts = nullptr; c->d_cursor = nullptr;
     cudaFree(c->s_bytes); cudaFree(c->s_offsets); cudaFree(c->s_out); cudaFree(c->s_fixed);
     c->d_owner = c->d_first = c->d_last = c->d_slot_of = nullptr;
     c->s_bytes = nullptr; c->s_offsets = nullptr; c->s_out = nullptr; c->s_fixed = nullptr;
@@ -627,6 +633,7 @@ extern "C" void smsgate_destroy(smsgate_ctx* ctx) {
     free_cache(ctx);
     free_scratch(ctx);
     cudaFree(ctx->mg_owner); cudaFree(ctx->mg_first); cudaFree(ctx->mg_last); cudaFree(ctx->mg_slot_of);
+    cudaFree(ctx->p2p_table); cudaFree(ctx->p2p_slot_of); cudaFree(ctx->p2p_overflow);
     cudaFree(ctx->d_tables);
     if (ctx->s_h2d) { cudaStreamSynchronize(ctx->s_h2d); cudaStreamDestroy(ctx->s_h2d); }
     if (ctx->s_d2h) { cudaStreamSynchronize(ctx->s_d2h); cudaStreamDestroy(ctx->s_d2h); }
@@ -660,6 +667,7 @@ extern "C" int smsgate_reserve(smsgate_ctx* ctx, int64_t max_msgs, int64_t max_b
     CUDA_TRY(ctx, cudaMalloc(&ctx->d_gfirst, cap * 8));
     CUDA_TRY(ctx, cudaMalloc(&ctx->d_glast, cap * 8));
     CUDA_TRY(ctx, cudaMalloc(&ctx->d_counts, sizeof(int) * SMSGATE_MAX_WORLD));
+    CUDA_TRY(ctx, cudaMalloc(&ctx->d_cursor, sizeof(int) * SMSGATE_MAX_WORLD));
     CUDA_TRY(ctx, cudaMalloc(&ctx->s_bytes, (size_t)max_bytes + 64));
     CUDA_TRY(ctx, cudaMalloc(&ctx->s_fixed, (size_t)max_bytes + 64));
     CUDA_TRY(ctx, cudaMalloc(&ctx->s_offsets, (size_t)(max_msgs + 1) * 8));
@@ -1002,26 +1010,47 @@ __device__ __forceinline__ int key_owner(const uint8_t* k, int world) {
     return (int)(((uint64_t)p * (uint64_t)world) >> 32);
 }
 
-// pass 1: count representatives (the message that claimed its slot) per destination
+// pass 1: count representatives (the message that claimed its slot) per destination.
+// Counts are gathered per block in shared memory first: with 2-8 destinations a
+// global atomic per record would serialise on a handful of addresses.
 __global__ void __launch_bounds__(256)
 k_export_count(int64_t n, const uint8_t* __restrict__ msg_id, DedupScratch D, int world, int* __restrict__ counts) {
+    __shared__ int hist[SMSGATE_MAX_WORLD];
+    if (threadIdx.x < SMSGATE_MAX_WORLD) hist[threadIdx.x] = 0;
+    __syncthreads();
     const int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
-    if (i >= n) return;
-    const int32_t sl = D.slot_of[i];
-    if (sl < 0 || D.owner[sl] != (int32_t)i) return;
-    atomicAdd(&counts[key_owner(msg_id + i * 20, world)], 1);
+    if (i < n) {
+        const int32_t sl = D.slot_of[i];
+        if (sl >= 0 && D.owner[sl] == (int32_t)i) atomicAdd(&hist[key_owner(msg_id + i * 20, world)], 1);
+    }
+    __syncthreads();
+    if (threadIdx.x < world && hist[threadIdx.x]) atomicAdd(&counts[threadIdx.x], hist[threadIdx.x]);
 }
-// pass 2: scatter the records into destination-contiguous order
+// pass 2: scatter the records into destination-contiguous order (one global atomic per block and destination)
 __global__ void __launch_bounds__(256)
 k_export_scatter(int64_t n, int64_t base_index, const uint8_t* __restrict__ msg_id, DedupScratch D, int world,
                  int* __restrict__ cursor, KeyRecord* __restrict__ records, int32_t* __restrict__ rec_slot) {
+    __shared__ int hist[SMSGATE_MAX_WORLD];
+    __shared__ int base[SMSGATE_MAX_WORLD];
+    if (threadIdx.x < SMSGATE_MAX_WORLD) hist[threadIdx.x] = 0;
+    __syncthreads();
     const int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
-    if (i >= n) return;
-    const int32_t sl = D.slot_of[i];
-    if (sl < 0 || D.owner[sl] != (int32_t)i) return;
-    const uint8_t* k = msg_id + i * 20;
-    const int r = atomicAdd(&cursor[key_owner(k, world)], 1);
-    const uint32_t* kw = reinterpret_cast<const uint32_t*>(k);
+    int32_t sl = -1;
+    int dest = 0, local = 0;
+    if (i < n) {
+        sl = D.slot_of[i];
+        if (sl >= 0 && D.owner[sl] != (int32_t)i) sl = -1;
+        if (sl >= 0) {
+            dest = key_owner(msg_id + i * 20, world);
+            local = atomicAdd(&hist[dest], 1);
+        }
+    }
+    __syncthreads();
+    if (threadIdx.x < world && hist[threadIdx.x]) base[threadIdx.x] = atomicAdd(&cursor[threadIdx.x], hist[threadIdx.x]);
+    __syncthreads();
+    if (sl < 0) return;
+    const int r = base[dest] + local;
+    const uint32_t* kw = reinterpret_cast<const uint32_t*>(msg_id + i * 20);
     const uint64_t f = (uint64_t)(base_index + D.first[sl]), l = (uint64_t)(base_index + D.last[sl]);
     KeyRecord rec;
     rec.key[0] = kw[0]; rec.key[1] = kw[1]; rec.key[2] = kw[2]; rec.key[3] = kw[3]; rec.key[4] = kw[4];
@@ -1188,6 +1217,263 @@ extern "C" int smsgate_dedup_apply(smsgate_ctx* ctx, int64_t n, int64_t base_ind
                                                                  ctx->d_glast, out->survivor, out->first_seen,
                                                                  out->last_idx);
     ctx->launches += 1;
+    CUDA_TRY(ctx, cudaGetLastError());
+    return SMSGATE_OK;
+}
+
+// ================================================================== the same exchange over peer memory
+// One process per GPU, every rank's inbox / counters / verdict arrays mapped into
+// every other rank (NVLink peer access; the Python layer gets the mappings from
+// torch's symmetric memory).  The export kernel stores its records straight into
+// the owner's inbox, the owner's merge stores each verdict straight back into the
+// home rank's per-slot arrays: no count exchange, no host synchronisation, no
+// staging copies; the only cross-GPU synchronisation is two barriers.
+struct __align__(16) P2PRecord {          // three 16-byte stores over NVLink
+    uint32_t key[5];
+    uint32_t first_lo;
+    uint32_t last_lo;
+    uint16_t first_hi;
+    uint16_t last_hi;
+    uint32_t home_slot;
+    uint32_t src_rank;
+    uint32_t pad[2];
+};
+static_assert(sizeof(P2PRecord) == SMSGATE_P2P_RECORD_BYTES, "peer records are 48 bytes");
+
+struct __align__(32) P2PSlot {
+    int32_t owner;               // record index that claimed the slot, -1 = empty
+    int32_t pad;
+    unsigned long long first;    // min global first index
+    unsigned long long last;     // max global last index
+    unsigned long long pad2;
+};
+
+struct P2PView {                 // smsgate_p2p, by value, for the kernels
+    int world, rank;
+    P2PRecord* inbox[SMSGATE_MAX_WORLD];
+    int32_t* in_count[SMSGATE_MAX_WORLD];
+    longlong2* gfl[SMSGATE_MAX_WORLD];    // per local slot {global first, global last}
+    int64_t capacity;
+};
+
+// one thread per destination: reserve a contiguous range in the owner's inbox with ONE remote atomic
+__global__ void k_p2p_reserve(P2PView P, int parity, const int* __restrict__ counts, int* __restrict__ cursor,
+                              int* __restrict__ overflow) {
+    const int w = threadIdx.x;
+    if (w == 0) P.in_count[P.rank][parity ^ 1] = 0;      // the counter of the step after this one
+    if (w >= P.world) return;
+    const int c = counts[w];
+    int base = 0;
+    if (c > 0) {
+        base = atomicAdd_system(&P.in_count[w][parity], c);
+        if ((int64_t)base + c > P.capacity) { atomicExch(overflow, 1); base = -1; }
+    }
+    cursor[w] = base;
+}
+
+__global__ void __launch_bounds__(256)
+k_p2p_scatter(int64_t n, int64_t base_index, const uint8_t* __restrict__ msg_id, DedupScratch D, P2PView P,
+              int* __restrict__ cursor) {
+    __shared__ int hist[SMSGATE_MAX_WORLD];
+    __shared__ int base[SMSGATE_MAX_WORLD];
+    if (threadIdx.x < SMSGATE_MAX_WORLD) hist[threadIdx.x] = 0;
+    __syncthreads();
+    const int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+    int32_t sl = -1;
+    int dest = 0, local = 0;
+    if (i < n) {
+        sl = D.slot_of[i];
+        if (sl >= 0 && D.owner[sl] != (int32_t)i) sl = -1;
+        if (sl >= 0) {
+            dest = key_owner(msg_id + i * 20, P.world);
+            local = atomicAdd(&hist[dest], 1);
+        }
+    }
+    __syncthreads();
+    if (threadIdx.x < P.world && hist[threadIdx.x]) {
+        const int b = cursor[threadIdx.x];                 // -1 after an overflow: drop
+        base[threadIdx.x] = b < 0 ? -1 : atomicAdd(&cursor[threadIdx.x], hist[threadIdx.x]);
+    }
+    __syncthreads();
+    if (sl < 0 || base[dest] < 0) return;
+    const uint32_t* kw = reinterpret_cast<const uint32_t*>(msg_id + i * 20);
+    const uint64_t f = (uint64_t)(base_index + D.first[sl]), l = (uint64_t)(base_index + D.last[sl]);
+    P2PRecord rec;
+    rec.key[0] = kw[0]; rec.key[1] = kw[1]; rec.key[2] = kw[2]; rec.key[3] = kw[3]; rec.key[4] = kw[4];
+    rec.first_lo = (uint32_t)f; rec.last_lo = (uint32_t)l;
+    rec.first_hi = (uint16_t)(f >> 32); rec.last_hi = (uint16_t)(l >> 32);
+    rec.home_slot = (uint32_t)sl;
+    rec.src_rank = (uint32_t)P.rank;
+    rec.pad[0] = rec.pad[1] = 0;
+    // what this rank knows already; the owner only writes back when another rank changes it
+    P.gfl[P.rank][sl] = make_longlong2((long long)f, (long long)l);
+    const uint4* src = reinterpret_cast<const uint4*>(&rec);
+    uint4* dst = reinterpret_cast<uint4*>(&P.inbox[dest][base[dest] + local]);   // peer stores over NVLink when dest != rank
+    dst[0] = src[0]; dst[1] = src[1]; dst[2] = src[2];
+}
+
+__device__ __forceinline__ uint64_t p2p_table_mask(int count) {
+    uint64_t want = (uint64_t)(count > 8 ? count : 8) * 2, cap = 16;
+    while (cap < want) cap <<= 1;
+    return cap - 1;
+}
+__global__ void __launch_bounds__(256)
+k_p2p_clear(const int32_t* __restrict__ count_ptr, P2PSlot* __restrict__ table) {
+    const uint64_t cap = p2p_table_mask(*count_ptr) + 1;
+    for (uint64_t s = blockIdx.x * (uint64_t)blockDim.x + threadIdx.x; s < cap; s += (uint64_t)gridDim.x * blockDim.x) {
+        P2PSlot e;
+        e.owner = -1; e.pad = 0; e.first = ~0ull; e.last = 0; e.pad2 = 0;
+        table[s] = e;
+    }
+}
+__global__ void __launch_bounds__(256)
+k_p2p_insert(const int32_t* __restrict__ count_ptr, const P2PRecord* __restrict__ recs, P2PSlot* __restrict__ table,
+             int32_t* __restrict__ slot_of) {
+    const int count = *count_ptr;
+    const uint64_t mask = p2p_table_mask(count);
+    for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < count; i += (int64_t)gridDim.x * blockDim.x) {
+        const P2PRecord r = recs[i];
+        uint64_t pos = (((uint64_t)r.key[1] << 32) | r.key[0]) & mask;
+        for (;;) {
+            int prev = table[pos].owner;
+            if (prev == -1) prev = atomicCAS(&table[pos].owner, -1, (int)i);
+            if (prev == -1 || prev == (int)i) break;
+            const P2PRecord o = recs[prev];
+            if (o.key[0] == r.key[0] && o.key[1] == r.key[1] && o.key[2] == r.key[2] && o.key[3] == r.key[3] &&
+                o.key[4] == r.key[4]) break;
+            pos = (pos + 1) & mask;
+        }
+        atomicMin(&table[pos].first, ((unsigned long long)r.first_hi << 32) | r.first_lo);
+        atomicMax(&table[pos].last, ((unsigned long long)r.last_hi << 32) | r.last_lo);
+        slot_of[i] = (int32_t)pos;
+    }
+}
+__global__ void __launch_bounds__(256)
+k_p2p_verdict(const int32_t* __restrict__ count_ptr, const P2PRecord* __restrict__ recs,
+              const P2PSlot* __restrict__ table, const int32_t* __restrict__ slot_of, P2PView P) {
+    const int count = *count_ptr;
+    for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < count; i += (int64_t)gridDim.x * blockDim.x) {
+        const P2PSlot e = table[slot_of[i]];
+        const P2PRecord r = recs[i];
+        const unsigned long long f = ((unsigned long long)r.first_hi << 32) | r.first_lo;
+        const unsigned long long l = ((unsigned long long)r.last_hi << 32) | r.last_lo;
+        // only a key that another rank also holds changes the home rank's view: one 16-byte peer store
+        if (e.first != f || e.last != l) P.gfl[r.src_rank][r.home_slot] = make_longlong2((long long)e.first, (long long)e.last);
+    }
+}
+
+__global__ void __launch_bounds__(256)
+k_p2p_resolve(int64_t n, int64_t base_index, const int32_t* __restrict__ slot_of, const longlong2* __restrict__ gfl,
+              uint8_t* __restrict__ survivor, uint8_t* __restrict__ first_seen, int64_t* __restrict__ last_idx) {
+    const int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const int32_t sl = slot_of[i];
+    uint8_t sv = 0, fs = 0;
+    int64_t li = -1;
+    if (sl >= 0) {
+        const longlong2 v = gfl[sl];
+        const int64_t g = base_index + i;
+        li = v.y;
+        sv = (li == g);
+        fs = (v.x == g);
+    }
+    if (survivor) survivor[i] = sv;
+    if (first_seen) first_seen[i] = fs;
+    if (last_idx) last_idx[i] = li;
+}
+
+static int p2p_view(smsgate_ctx* ctx, const smsgate_p2p* p, P2PView* v) {
+    if (!p || p->world < 1 || p->world > SMSGATE_MAX_WORLD || p->rank < 0 || p->rank >= p->world || p->capacity < 1)
+        return fail(ctx, SMSGATE_E_ARG, "p2p: bad descriptor");
+    v->world = p->world; v->rank = p->rank; v->capacity = p->capacity;
+    for (int w = 0; w < p->world; ++w) {
+        if (!p->inbox[w] || !p->in_count[w] || !p->gfl[w]) return fail(ctx, SMSGATE_E_ARG, "p2p: NULL peer pointer");
+        v->inbox[w] = reinterpret_cast<P2PRecord*>(p->inbox[w]);
+        v->in_count[w] = p->in_count[w];
+        v->gfl[w] = reinterpret_cast<longlong2*>(p->gfl[w]);
+    }
+    return SMSGATE_OK;
+}
+
+extern "C" int smsgate_p2p_reserve(smsgate_ctx* ctx, int64_t capacity) {
+    if (!ctx) return SMSGATE_E_ARG;
+    if (capacity < 0 || capacity > 0x40000000ll) return fail(ctx, SMSGATE_E_LIMIT, "p2p_reserve: at most 2^30 records");
+    if (capacity <= ctx->p2p_capacity) return SMSGATE_OK;
+    CUDA_TRY(ctx, cudaSetDevice(ctx->device));
+    CUDA_TRY(ctx, cudaStreamSynchronize(ctx->stream));
+    cudaFree(ctx->p2p_table); cudaFree(ctx->p2p_slot_of); cudaFree(ctx->p2p_overflow);
+    ctx->p2p_table = nullptr; ctx->p2p_slot_of = nullptr; ctx->p2p_overflow = nullptr; ctx->p2p_capacity = 0;
+    const uint64_t cap = pow2_at_least((uint64_t)(capacity > 8 ? capacity : 8) * 2);
+    CUDA_TRY(ctx, cudaMalloc(&ctx->p2p_table, cap * sizeof(P2PSlot)));
+    CUDA_TRY(ctx, cudaMalloc(&ctx->p2p_slot_of, (size_t)(capacity + 1) * 4));
+    CUDA_TRY(ctx, cudaMalloc(&ctx->p2p_overflow, 4));
+    CUDA_TRY(ctx, cudaMemset(ctx->p2p_overflow, 0, 4));
+    ctx->p2p_capacity = capacity;
+    return SMSGATE_OK;
+}
+
+extern "C" int smsgate_p2p_scatter(smsgate_ctx* ctx, int64_t n, int64_t base_index, int parity,
+                                   const smsgate_outputs* out, const smsgate_p2p* p) {
+    if (!ctx) return SMSGATE_E_ARG;
+    P2PView V;
+    int rc = p2p_view(ctx, p, &V);
+    if (rc) return rc;
+    if (n < 0 || !out || (n > 0 && !out->msg_id)) return fail(ctx, SMSGATE_E_ARG, "p2p_scatter: bad argument");
+    if (n > ctx->cap_msgs) return fail(ctx, SMSGATE_E_STATE, "p2p_scatter: run smsgate_dedup on this batch first");
+    if (!ctx->p2p_overflow) return fail(ctx, SMSGATE_E_STATE, "p2p_scatter: call smsgate_p2p_reserve first");
+    CUDA_TRY(ctx, cudaSetDevice(ctx->device));
+    cudaStream_t st = ctx->stream;
+    uint64_t cap = pow2_at_least((uint64_t)(n > 8 ? n : 8) * 2);
+    if (cap > ctx->dd_cap) cap = ctx->dd_cap;
+    DedupScratch D{ctx->d_owner, ctx->d_first, ctx->d_last, ctx->d_slot_of, cap - 1};
+    int* counts = ctx->d_counts;                       // [0, MAX_WORLD): counts, then cursors
+    CUDA_TRY(ctx, cudaMemsetAsync(counts, 0, sizeof(int) * SMSGATE_MAX_WORLD, st));
+    const unsigned grid = (unsigned)((n + 255) / 256);
+    if (n > 0) k_export_count<<<grid, 256, 0, st>>>(n, out->msg_id, D, V.world, counts);
+    k_p2p_reserve<<<1, SMSGATE_MAX_WORLD, 0, st>>>(V, parity & 1, counts, ctx->d_cursor, ctx->p2p_overflow);
+    if (n > 0) k_p2p_scatter<<<grid, 256, 0, st>>>(n, base_index, out->msg_id, D, V, ctx->d_cursor);
+    ctx->launches += n > 0 ? 3 : 1;
+    CUDA_TRY(ctx, cudaGetLastError());
+    return SMSGATE_OK;
+}
+
+extern "C" int smsgate_p2p_merge(smsgate_ctx* ctx, int parity, const smsgate_p2p* p) {
+    if (!ctx) return SMSGATE_E_ARG;
+    P2PView V;
+    int rc = p2p_view(ctx, p, &V);
+    if (rc) return rc;
+    if (V.capacity > ctx->p2p_capacity) return fail(ctx, SMSGATE_E_STATE, "p2p_merge: inbox larger than smsgate_p2p_reserve() sized the table for");
+    CUDA_TRY(ctx, cudaSetDevice(ctx->device));
+    cudaStream_t st = ctx->stream;
+    const int32_t* cnt = V.in_count[V.rank] + (parity & 1);
+    const unsigned grid = (unsigned)ctx->sm_count * 8;
+    k_p2p_clear<<<grid, 256, 0, st>>>(cnt, ctx->p2p_table);
+    k_p2p_insert<<<grid, 256, 0, st>>>(cnt, V.inbox[V.rank], ctx->p2p_table, ctx->p2p_slot_of);
+    k_p2p_verdict<<<grid, 256, 0, st>>>(cnt, V.inbox[V.rank], ctx->p2p_table, ctx->p2p_slot_of, V);
+    ctx->launches += 3;
+    CUDA_TRY(ctx, cudaGetLastError());
+    return SMSGATE_OK;
+}
+
+extern "C" int smsgate_p2p_resolve(smsgate_ctx* ctx, int64_t n, int64_t base_index, const smsgate_outputs* out,
+                                   const smsgate_p2p* p, int* h_overflow) {
+    if (!ctx) return SMSGATE_E_ARG;
+    P2PView V;
+    int rc = p2p_view(ctx, p, &V);
+    if (rc) return rc;
+    if (n < 0 || !out) return fail(ctx, SMSGATE_E_ARG, "p2p_resolve: bad argument");
+    if (n > ctx->cap_msgs) return fail(ctx, SMSGATE_E_STATE, "p2p_resolve: run smsgate_dedup on this batch first");
+    CUDA_TRY(ctx, cudaSetDevice(ctx->device));
+    cudaStream_t st = ctx->stream;
+    if (n > 0) {
+        k_p2p_resolve<<<(unsigned)((n + 255) / 256), 256, 0, st>>>(n, base_index, ctx->d_slot_of, V.gfl[V.rank],
+                                                                   out->survivor, out->first_seen, out->last_idx);
+        ctx->launches += 1;
+    }
+    if (h_overflow) {       // optional: costs a synchronisation
+        CUDA_TRY(ctx, cudaMemcpyAsync(h_overflow, ctx->p2p_overflow, 4, cudaMemcpyDeviceToHost, st));
+        CUDA_TRY(ctx, cudaStreamSynchronize(st));
+    }
     CUDA_TRY(ctx, cudaGetLastError());
     return SMSGATE_OK;
 }

@@ -110,3 +110,75 @@ class GlobalDedup:
         self.bytes_sent += n_rec * L.RECORD_BYTES + n_recv * 16
         self.last_counts = (send_counts, recv_counts)
         self.last_launches = eng.launch_count - l0
+
+
+class GlobalDedupP2P:
+    """The same global dedup with the exchange fused into the kernels: records and
+    verdicts are stored straight into the peers' memory over NVLink (buffers mapped
+    with torch's symmetric memory), with two cross-GPU barriers and no host
+    synchronisation per batch.  Every rank must use the same `n_max`."""
+
+    def __init__(self, engine, dist, n_max: int, group=None):
+        import torch
+        import torch.distributed._symmetric_memory as symm_mem
+        self.engine = engine
+        self.torch = torch
+        group = group if group is not None else dist.group.WORLD
+        self.world = dist.get_world_size(group)
+        self.rank = dist.get_rank(group)
+        dev = torch.device("cuda", engine.device)
+        n_max = max(int(n_max), 1)
+        self.capacity = self.world * n_max
+        cap_slots = 16
+        while cap_slots < 2 * max(n_max, 8):
+            cap_slots <<= 1
+        # one symmetric allocation per buffer kind; rendezvous gives every rank's mapping
+        self._inbox = symm_mem.empty(self.capacity * L.P2P_RECORD_BYTES, dtype=torch.uint8, device=dev)
+        self._count = symm_mem.empty(16, dtype=torch.int32, device=dev)
+        self._gfl = symm_mem.empty(2 * cap_slots, dtype=torch.int64, device=dev)
+        self._count.zero_()
+        torch.cuda.synchronize()
+        self._h = [symm_mem.rendezvous(t, group) for t in (self._inbox, self._count, self._gfl)]
+        self.desc = L.P2P()
+        self.desc.world, self.desc.rank, self.desc.capacity = self.world, self.rank, self.capacity
+        for w in range(self.world):
+            self.desc.inbox[w] = self._h[0].buffer_ptrs[w]
+            self.desc.in_count[w] = self._h[1].buffer_ptrs[w]
+            self.desc.gfl[w] = self._h[2].buffer_ptrs[w]
+        L.check(engine._ctx, L.lib().smsgate_p2p_reserve(engine._ctx, self.capacity))
+        self._h[1].barrier(channel=0)          # every rank's counters are zero before anyone scatters
+        self.step = 0
+        self.launches = 0
+        self.bytes_sent = 0
+
+    def run(self, cols: dict, base_index: int) -> None:
+        self.run_outputs(self.engine._dev_outputs(cols), cols["status"].numel(), base_index)
+
+    def run_outputs(self, out: "L.Outputs", n: int, base_index: int) -> None:
+        eng, lib = self.engine, L.lib()
+        parity = self.step & 1
+        L.check(eng._ctx, lib.smsgate_p2p_scatter(eng._ctx, n, int(base_index), parity, C.byref(out), C.byref(self.desc)))
+        self._h[1].barrier(channel=0)          # all records have landed in their owners' inboxes
+        L.check(eng._ctx, lib.smsgate_p2p_merge(eng._ctx, parity, C.byref(self.desc)))
+        self._h[1].barrier(channel=1)          # all verdicts have landed in their home arrays
+        L.check(eng._ctx, lib.smsgate_p2p_resolve(eng._ctx, n, int(base_index), C.byref(out), C.byref(self.desc), None))
+        self.step += 1
+
+    def overflowed(self) -> bool:
+        """True if an inbox ever overflowed (some rank exceeded n_max).  Synchronises."""
+        flag = C.c_int(0)
+        out = L.Outputs()
+        L.check(self.engine._ctx, L.lib().smsgate_p2p_resolve(self.engine._ctx, 0, 0, C.byref(out), C.byref(self.desc),
+                                                              C.byref(flag)))
+        return bool(flag.value)
+
+
+def make_global_dedup(engine, dist, n_max: int, prefer_p2p: bool = True):
+    """GlobalDedupP2P when peer mappings are available, else the NCCL all-to-all path."""
+    if prefer_p2p:
+        try:
+            return GlobalDedupP2P(engine, dist, n_max)
+        except Exception as e:       # no symmetric memory in this build / topology: fall back to NCCL
+            import warnings
+            warnings.warn(f"peer-memory exchange unavailable ({e!r}); using the NCCL all-to-all path")
+    return GlobalDedup(engine, dist, n_max)

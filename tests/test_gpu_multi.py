@@ -90,11 +90,11 @@ def test_ranks_emulated_on_one_gpu(world):
     assert np.array_equal(np.concatenate(got_l), want_l)
 
 
-def _nccl_worker(rank, world, port, n_per, q):
+def _nccl_worker(rank, world, port, n_per, q, p2p=False):
     import torch
     import torch.distributed as dist
 
-    from smsgate_b200.dist import GlobalDedup
+    from smsgate_b200.dist import GlobalDedup, GlobalDedupP2P
     from smsgate_b200.replay import ReplayEngine
     os.environ["MASTER_ADDR"] = "127.0.0.1"
     os.environ["MASTER_PORT"] = str(port)
@@ -110,9 +110,13 @@ def _nccl_worker(rank, world, port, n_per, q):
         d_off = torch.from_numpy(b.body_offsets.copy()).cuda()
         c = eng.device_columns(b.n, d_bytes.numel())
         eng.reserve(b.n, d_bytes.numel())
-        eng.replay_device(d_bytes, d_off, NOW, c, base_index=lo)
-        GlobalDedup(eng, dist, b.n).run(c, lo)
+        ex = (GlobalDedupP2P if p2p else GlobalDedup)(eng, dist, b.n)
+        for _ in range(3 if p2p else 1):                 # several batches: counters alternate, inboxes are reused
+            eng.replay_device(d_bytes, d_off, NOW, c, base_index=lo)
+            ex.run(c, lo)
         torch.cuda.synchronize()
+        if p2p:
+            assert not ex.overflowed()
         q.put((rank, c["survivor"].cpu().numpy(), c["first_seen"].cpu().numpy(), c["last_idx"].cpu().numpy()))
         eng.close()
     finally:
@@ -120,16 +124,17 @@ def _nccl_worker(rank, world, port, n_per, q):
 
 
 @pytest.mark.timeout(600)
-def test_two_ranks_over_nccl():
+@pytest.mark.parametrize("p2p,world", [(False, 2), (True, 2), (True, 1)])
+def test_ranks_over_nccl_or_peer_memory(p2p, world):
     import torch
-    if torch.cuda.device_count() < 2:
+    if torch.cuda.device_count() < world:
         pytest.skip("needs two GPUs")
     import torch.multiprocessing as mp
-    world, n_per = 2, 20000
+    n_per = 20000
     ctx = mp.get_context("spawn")
     q = ctx.Queue()
     s = socket.socket(); s.bind(("127.0.0.1", 0)); port = s.getsockname()[1]; s.close()
-    procs = [ctx.Process(target=_nccl_worker, args=(r, world, port, n_per, q)) for r in range(world)]
+    procs = [ctx.Process(target=_nccl_worker, args=(r, world, port, n_per, q, p2p)) for r in range(world)]
     for p in procs:
         p.start()
     res = sorted((q.get(timeout=500) for _ in range(world)), key=lambda t: t[0])
