@@ -104,6 +104,21 @@ static int32_t sg_body_date_at(const uint8_t* m, int len, int lead, int ncp, con
     uint64_t vals = 0;                                // 4 bits per code point, position k at bits 4k
     uint32_t ascm = 0;                                // bit k: code point k is ASCII
     int p = lead;
+    if (lead >= ncp - 1) {
+        // common case: the ncp bytes ending at `lead` are all ASCII, i.e. they ARE the match
+        bool all_ascii = true;
+        for (int k = 0; k < ncp; ++k) all_ascii = all_ascii && (m[lead - k] < 0x80);
+        if (all_ascii) {
+            for (int k = 0; k < ncp; ++k) {
+                const uint32_t c = m[lead - (ncp - 1) + k];
+                const uint32_t dv = (c >= '0' && c <= '9') ? c - '0' : 15u;
+                vals |= (uint64_t)dv << (4 * k);
+            }
+            ascm = (1u << ncp) - 1;
+            p = -1;
+        }
+    }
+    if (p >= 0)
     for (int k = ncp - 1; k >= 0; --k) {
         uint32_t cp;
         sg_utf8_decode(m + p, len - p, &cp);

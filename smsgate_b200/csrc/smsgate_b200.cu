@@ -57,7 +57,7 @@ constexpr int K1_THREADS = 128;           // 4 warps
 constexpr int K1_TILE = 256;              // messages per tile: every thread owns one short and one long body
 constexpr int K1_STAGE = 36 * 1024;       // staged body bytes per CTA tile (4 CTAs per SM)
 constexpr int K1_PAD = 32;                // slack read by the unaligned word reader
-constexpr int K1_BUCKETS = 64;            // length buckets of 16 bytes for the in-tile sort
+constexpr int K1_BUCKETS = 128;           // length buckets of 8 bytes for the in-tile sort
 
 struct __align__(16) K1Smem {
     DeviceTables tab;
@@ -207,24 +207,27 @@ k_scan_keys(const uint8_t* __restrict__ bytes, const int64_t* __restrict__ offse
                     S.m_off[loc] = (int)(my_lo[h] - base);
                     S.m_len[loc] = len;
                     S.m_flen[loc] = len;
-                    int k = len >> 4;
+                    int k = len >> 3;
                     k = k < K1_BUCKETS - 1 ? k : K1_BUCKETS - 1;
                     key[h] = k;
                     atomicAdd(&S.hist[k], 1);
                 }
             }
             __syncthreads();
-            if (tid < 32) {
-                const int a = S.hist[2 * tid], b = S.hist[2 * tid + 1];
-                int incl = a + b;
+            if (tid < 32) {                                  // exclusive scan of the 128 bucket counts, 4 per lane
+                const int a = S.hist[4 * tid], b = S.hist[4 * tid + 1], c = S.hist[4 * tid + 2], d4 = S.hist[4 * tid + 3];
+                const int sum = a + b + c + d4;
+                int incl = sum;
 #pragma unroll
                 for (int d = 1; d < 32; d <<= 1) {
                     const int v = __shfl_up_sync(0xffffffffu, incl, d);
                     if (tid >= d) incl += v;
                 }
-                const int excl = incl - (a + b);
-                S.cursor[2 * tid] = excl;
-                S.cursor[2 * tid + 1] = excl + a;
+                const int excl = incl - sum;
+                S.cursor[4 * tid] = excl;
+                S.cursor[4 * tid + 1] = excl + a;
+                S.cursor[4 * tid + 2] = excl + a + b;
+                S.cursor[4 * tid + 3] = excl + a + b + c;
             }
             __syncthreads();
 #pragma unroll
