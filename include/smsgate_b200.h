@@ -139,6 +139,36 @@ int smsgate_decimal_batch(smsgate_ctx* ctx, int64_t n, const int32_t* h_offsets,
 int smsgate_strict_date_batch(smsgate_ctx* ctx, int64_t n, const int32_t* h_offsets, const uint8_t* h_bytes,
                               int64_t* h_packed);
 
+/* ---- the legacy offline replay (host buffers in and out) --------------------
+ * process_cached.process_sms_from_cache (process_cached.py:210-268) for n source-cache
+ * bodies at once: strip (:233), OTP filter on body.upper() (:236), the debit pattern
+ * TRANSACTION_RE via parse_transaction_message (:98-120, :150-177), else the credit
+ * pattern CREDIT_PAYMENT_RE via parse_credit_message (:122-135, :180-204), `_to_decimal`
+ * -> float (:141-143) and the SHA-256 of the stripped body that keys the result caches
+ * (:254).  Both patterns run on the GPU in a backtracking matcher that tries
+ * alternatives in the order Python's `re` does. */
+#define SMSGATE_LEG_SKIPPED_OTP 0 /* status "skipped_otp" */
+#define SMSGATE_LEG_DEBIT 1       /* "processed", goes to the purchase cache */
+#define SMSGATE_LEG_CREDIT 2      /* "processed", goes to the credit cache */
+#define SMSGATE_LEG_FAILED 3      /* "failed_to_parse" */
+#define SMSGATE_LEG_F_BUDGET 0x01  /* matcher budget (4 M steps / 128 pending choices) ran out: treat as failed */
+#define SMSGATE_LEG_F_INEXACT 0x02 /* amount or balance beyond 2^53 / 22 fraction digits: float only approximate */
+#define SMSGATE_LEG_GROUPS 10
+/* group numbers inside caps[]: debit 1 merchant 2 city 3 address 4 date 5 time 6 card 7 amount 8 currency 9 balance;
+ * credit 1 type 2 date 3 time 4 card 5 amount 6 currency 7 balance */
+typedef struct smsgate_legacy_outputs {
+    uint8_t* status;    /* [n] SMSGATE_LEG_* */
+    uint8_t* lflags;    /* [n] SMSGATE_LEG_F_* */
+    int32_t* strip;     /* [n*2] byte span of body.strip() inside the body */
+    int32_t* caps;      /* [n*2*SMSGATE_LEG_GROUPS] byte spans of the groups inside the stripped body, already
+                           trimmed where the reference calls .strip(); -1 = group did not take part */
+    double* amount;     /* [n] float(_to_decimal(amount)) */
+    double* balance;    /* [n] */
+    uint8_t* body_hash; /* [n*32] SHA-256 of the stripped body */
+} smsgate_legacy_outputs;
+int smsgate_legacy_parse(smsgate_ctx* ctx, int64_t n, const int64_t* h_offsets, const uint8_t* h_bytes,
+                         const smsgate_legacy_outputs* h_out);
+
 /* ---- the replay stages, device pointers ----------------------------------- */
 /* Stage 1 — keys and scans: msg_id (watcher.py:45), worker skip filter
  * (worker.py:112-121), parser OTP filter (gemini_parser.py:198-200), clean +

@@ -422,6 +422,136 @@ def gen_replay(ref, n, seed, **kw):
             "upserts": upserts, "first": inserted_first}
 
 
+# ---------------------------------------------------------------- legacy regex path
+def legacy_bodies():
+    b1 = ("APPROVED PURCHASE DB SALE: TEST LLC, MOSKOW, TEST STR. 29, 24 AREA,06.05.25 14:23,card ***0018. "
+          "Amount:52.00 USD, Balance:1842.74 USD")
+    b2 = "APPROVED PURCHASE DB SALE: TEST, MOSKOW,06.05.25 15:11,card ***0018. Amount:3460.00 USD, Balance:1800.74 USD"
+    cr = "CREDIT PAYMENT: 10.06.25 12:00, card ***7538. Amount:100,000.00 AMD, Balance:491,469.09 AMD"
+    t = [b1, b2, cr,
+         "DEBIT ACCOUNT\n27,252.00 AMD\n4083***7538,\nAMERIABANK API GATE, AM\n10.06.2025 20:51\nBALANCE: 391,469.09 AMD",
+         "APPROVED PURCHASE DB INTERNET: SHOP 1, YEREVAN, ABOVYAN 12, 06.05.25 14:23,card ***0018. Amount:1,234.50 AMD, Balance:7.000,00 AMD",
+         "PURCH.COMPLETION.DB INTERNET: SHOP, YEREVAN, 06/05/2025 14:23, card ***0018. Amount:5 usd, Balance:6",
+         "purchase: shop, yerevan, addr, 06-05-25 14:23, CARD ***0018. amount:5 usd, balance:6",
+         "SALE: A,B,C,06.05.25 14:23,card ***0018. Amount:1 USD, Balance:2",
+         "SALE: A, YEREVAN,06.05.25 14:23,card ***0018. Amount:1 USD, Balance:2",
+         "SALE: A, YEREVAN, ,06.05.25 14:23,card ***0018. Amount:1 USD, Balance:2",
+         "SALE:  , YEREVAN, x,06.05.25 14:23,card ***0018. Amount:1 USD, Balance:2",
+         "SALE: ,X, y,06.05.25 14:23,card ***0018. Amount:1 USD, Balance:2",
+         "SALE:\n A\n,\n B,06.05.25\n14:23,\ncard\n***0018.\nAmount:\n1 USD,\nBalance:\n2",
+         "xxSALE: A, B,06.05.25 14:23,card ***0018. Amount:1 USD, Balance:2 trailing text",
+         "SALE: A, B,06.05.25 14:23,card ***0018. Amount:1.2.3 USD, Balance:2",
+         "SALE: A, B,06.05.25 14:23,card ***0018. Amount:1 USD, Balance:2.3.4",
+         "SALE: A, B,06.05.25 14:23,card ***0018. Amount:, USD, Balance:2",
+         "SALE: A, B,06.05.25 14:23,card ***0018. Amount:. USD, Balance:2",
+         "SALE: A, B,06.05.25 14:23,card ***0018. Amount:1,000,000.555 USD, Balance:123456789012345.67",
+         "SALE: A, B,06.05.25 14:23,card ***0018. Amount:١٢.٥ USD, Balance:１２",
+         "SALE: A, B,٠٦.05.25 14:23,card ***٠٠١٨. Amount:1 USÐ, Balance:2",
+         "SALE: A, B,06.05.25 14:23,card ***0018. Amount:1 U_1, Balance:2",
+         "SALE: A, B,06.05.25 14:23,card ***0018. Amount:1 US, Balance:2",
+         "SALE: A, B,06.05.25 14:23,card ***0018. Amount:1 USDX, Balance:2",
+         "SALE: A, B,06.05.20251 14:23,card ***0018. Amount:1 USD, Balance:2",
+         "SALE: A, B,06.05.2025 14:23,card ***0018. Amount:1 USD, Balance:2",
+         "SALE: A, B,06.05.202 14:23,card ***0018. Amount:1 USD, Balance:2",
+         "SALE: A, B,06.05.2 14:23,card ***0018. Amount:1 USD, Balance:2",
+         "ſALE: A, B,06.05.25 14:23,card ***0018. Amount:1 USD, Balance:2",
+         "SALE: A, B,06.05.25 14:23,card ***0018. Amount:1 USD, Balance:2\n",
+         "PURCHAſE DB İNTERNET: A, B,06.05.25 14:23,card ***0018. Amount:1 USD, Balance:2",
+         "PURCHASE DB ıNTERNET: A, B,06.05.25 14:23,card ***0018. Amount:1 USD, Balance:2",
+         "PURCHASE DB  INTERNET : A, B,06.05.25 14:23,card ***0018. Amount:1 USD, Balance:2",
+         "PURCHASE SALE: A, B,06.05.25 14:23,card ***0018. Amount:1 USD, Balance:2",
+         "SALE: A: B, SALE: C, D,06.05.25 14:23,card ***0018. Amount:1 USD, Balance:2",
+         "SALE: A, B,06.05.25 14:23,card ***0018. Amount:1 USD, Balance:2 SALE: E, F,07.05.25 15:00,card ***0019. Amount:3 EUR, Balance:4",
+         "SALE: A, B, 01.01.25 x,06.05.25 14:23,card ***0018. Amount:1 USD, Balance:2",
+         "SALE: A, B,06.05.25 14:23 ,card ***0018. Amount:1 USD, Balance:2",
+         "SALE: A, B,06.05.25  14:23,  card   ***0018.   Amount:   1   USD,   Balance:   2",
+         "SALE: A, B,06.05.25 14:23,card **0018. Amount:1 USD, Balance:2",
+         "SALE: A, B,06.05.25 14:23,card ****0018. Amount:1 USD, Balance:2",
+         "SALE: A, B,06.05.25 14:23,card ***00189. Amount:1 USD, Balance:2",
+         "SALE:A,B,06.05.25 14:23,card ***0018.Amount:1 USD,Balance:2",
+         "SALE:  A , B ,06.05.25 14:23,card ***0018. Amount:1 USD, Balance:2",
+         "", " ", "\n", "SALE:", "SALE: ,", "OTP SALE: A, B,06.05.25 14:23,card ***0018. Amount:1 USD, Balance:2",
+         "pass=1", "code: 5", "oſp", "ﬆ", "CODE :",
+         # credit
+         "ACCOUNT REPLENISHMENT: 06.05.25 14:23, card ***0018. Amount:1,000.00 AMD, Balance:2,000.00 AMD",
+         "ACCOUNT REPLENISHMENT: 06.05.25 14:23, card ***0018. Amount:1,000.00 AMD, Balance:2,000.00 AMD\n",
+         "ACCOUNT REPLENISHMENT: 06.05.25 14:23, card ***0018. Amount:1,000.00 AMD, Balance:2,000.00 AMD\n\n",
+         "ACCOUNT REPLENISHMENT: 06.05.25 14:23, card ***0018. Amount:1,000.00 AMD, Balance:2,000.00 AMD x",
+         "line one\nACCOUNT REPLENISHMENT: 06.05.25 14:23, card ***0018. Amount:1,000.00 AMD, Balance:2,000.00 AMD",
+         "a.b ACCOUNT REPLENISHMENT: 06.05.25 14:23, card ***0018. Amount:1 AMD, Balance:2 AMD",
+         "a.b_c 9: 06.05.25 14:23, card ***0018. Amount:1 AMD, Balance:2 AMD",
+         ": 06.05.25 14:23, card ***0018. Amount:1 AMD, Balance:2 AMD",
+         "x : 06.05.25 14:23, card ***0018. Amount:1 AMD, Balance:2 AMD",
+         "Пополнение счета: 06.05.25 14:23, card ***0018. Amount:1 AMD, Balance:2 руб",
+         "T1: 06.05.25 14:23, T2: 07.05.25 15:24, card ***0018. Amount:1 AMD, Balance:2 AMD",
+         "TYPE: 06.05.2025 14:23, card ***0018. Amount:1.5.5 AMD, Balance:2 AMD",
+         "TYPE: 06.05.25 14:23, card ***0018. Amount:1 AMD, Balance:2 AMD AMD",
+         "TYPE: 06.05.25 14:23, card ***0018. Amount:1 AMD, Balance:2  AMD  ",
+         "TYPE: 06.05.25 14:23, card ***0018. Amount:1 AMD, Balance:2 AM",
+         "TYPE: 06.05.25 14:23, card ***0018. Amount:1 AMD, Balance:2AMD",
+         "credit payment: 10.06.25 12:00, card ***7538. amount:100,000.00 amd, balance:491,469.09 amd",
+         ]
+    rnd = random.Random(11)
+    pieces = ["SALE", "PURCHASE", " DB ", "INTERNET", ":", ": ", ", ", ",", "YEREVAN", "A", "shop 7", "06.05.25", "06.05.2025",
+              " 14:23", "14:23", ",card ***0018.", "card ***0018", ". ", " Amount:", "Amount: ", "1,234.50", "5", " USD", "AMD",
+              ", Balance:", "Balance:", "2", "\n", " ", "x", "TYPE", "9", ".", "***", "٥", " "]
+    for _ in range(500):
+        t.append("".join(rnd.choice(pieces) for _ in range(rnd.randint(2, 22))))
+    # well-formed shapes with random fields
+    for i in range(120):
+        sep = rnd.choice([".", "/", "-"])
+        d = f"{rnd.randint(1,28):02d}{sep}{rnd.randint(1,12):02d}{sep}{rnd.choice(['25','2025','202'])}"
+        kw = rnd.choice(["PURCHASE", "SALE", "PURCHASE DB INTERNET", "PURCH.COMPLETION.DB INTERNET", "Purchase", "sale"])
+        city = rnd.choice(["YEREVAN, ", "Yerevan, ", "GYUMRI, ", ""])
+        addr = rnd.choice(["ABOVYAN 12", "", "A, B, C", " "])
+        amt = rnd.choice(["1", "52.00", "1,234.56", "1.234,56", "7.000,00", "0.10", "99999999.99", "12345678901234567", "1,2,3"])
+        t.append(f"APPROVED {kw}: M{i} LLC, {city}{addr},{d} {rnd.randint(0,23):02d}:{rnd.randint(0,59):02d},card ***{rnd.randint(0,9999):04d}. "
+                 f"Amount:{amt} {rnd.choice(['USD','amd','EUR'])}, Balance:{rnd.choice(['1842.74','0','1,000,000.01'])} USD")
+        t.append(f"{rnd.choice(['ACCOUNT REPLENISHMENT','C2C','Refund 1'])}: {d} 12:00, card ***{rnd.randint(0,9999):04d}. "
+                 f"Amount:{amt} AMD, Balance:491,469.09 AMD")
+    return t
+
+
+def _legacy_dump(d):
+    if d is None:
+        return None
+    import struct
+    out = dict(d)
+    for k in ("amount", "balance"):
+        out[k] = "%016x" % struct.unpack("<Q", struct.pack("<d", d[k]))[0]
+    return out
+
+
+def gen_legacy(ref):
+    import logging
+    logging.disable(logging.CRITICAL)
+    pc = ref.process_cached
+    cases = []
+    for b in legacy_bodies():
+        cases.append({"body": b, "debit": _legacy_dump(pc.parse_transaction_message(b)),
+                      "credit": _legacy_dump(pc.parse_credit_message(b))})
+    # the whole of process_sms_from_cache on a small source cache, through real diskcache directories
+    import diskcache
+    tmp = tempfile.mkdtemp()
+    src, deb, cre = (os.path.join(tmp, n) for n in ("src", "deb", "cre"))
+    bodies = legacy_bodies()[:140]
+    with diskcache.Cache(src) as c:
+        for i, b in enumerate(bodies):
+            c.set(str(1707900000000 + i), {"address": "BANK", "date": str(1707900000000 + i), "body": b})
+        c.set("already", {"body": bodies[0], "status": "processed"})
+        c.set("nobody", {"address": "X"})
+    pc.process_sms_from_cache(src, deb, cre)
+    with diskcache.Cache(src) as c:
+        statuses = {k: c.get(k).get("status") for k in c}
+    def dump_cache(path):
+        with diskcache.Cache(path) as c:
+            return {k: dict(_legacy_dump({kk: vv for kk, vv in c.get(k).items() if kk not in ("msg_id", "original_body")}),
+                            msg_id=c.get(k)["msg_id"], original_body=c.get(k)["original_body"]) for k in c}
+    logging.disable(logging.NOTSET)
+    return {"cases": cases, "process": {"bodies": bodies, "statuses": statuses, "debit": dump_cache(deb),
+                                        "credit": dump_cache(cre)}}
+
+
 def main():
     os.makedirs(OUT, exist_ok=True)
     ref = Reference(tempfile.mkdtemp())
@@ -435,6 +565,7 @@ def main():
         dump("keys.json", gen_keys(ref))
         dump("parse_matrix.json", gen_matrix(ref))
         dump("iter_sms.json", gen_iter_sms(ref))
+        dump("legacy.json", gen_legacy(ref))
         dump("replay_plain.json", gen_replay(ref, 400, 0x5EED + 1, dup_frac=0.1))
         dump("replay_mixed.json", gen_replay(ref, 500, 0x5EED + 5, mixed_locale=True, miss_frac=0.3,
                                              dup_frac=0.2, hot_key_zipf=1.2))

@@ -23,6 +23,8 @@ DLQ_STATUSES = (ST_CACHE_MISS, ST_UNMATCHED, ST_FUTURE_DATE, ST_FAILED_EXC)
 E_IS_DICT, E_HAS_TXN, E_SCHEMA_OK, E_CARD_STR, E_MERCHANT = 0x1, 0x2, 0x4, 0x8, 0x10
 E_DATE_STRICT, E_DATE_HOST, E_DATE_NOBODY, E_DATE_TZ, E_DATE_KEY = 0x20, 0x40, 0x80, 0x100, 0x200
 DEC_OK, DEC_SYNTAX, DEC_OVERFLOW = 0, 1, 2
+LEG_SKIPPED_OTP, LEG_DEBIT, LEG_CREDIT, LEG_FAILED = 0, 1, 2, 3
+LEG_F_BUDGET, LEG_F_INEXACT, LEG_GROUPS = 1, 2, 10
 DEDUP_STATIC_MAX = 1 << 20
 MAX_WORLD = 64
 RECORD_BYTES = 32
@@ -41,6 +43,11 @@ COLUMNS = (
 
 class Outputs(C.Structure):
     _fields_ = [(name, C.c_void_p) for name, _, _ in COLUMNS]
+
+
+class LegacyOutputs(C.Structure):
+    """struct smsgate_legacy_outputs"""
+    _fields_ = [(n, C.c_void_p) for n in ("status", "lflags", "strip", "caps", "amount", "balance", "body_hash")]
 
 
 class P2P(C.Structure):
@@ -79,6 +86,7 @@ def lib():
         "smsgate_cache_size": (i64, [vp]),
         "smsgate_decimal_batch": (i32, [vp, i64, vp, vp, vp, vp, vp]),
         "smsgate_strict_date_batch": (i32, [vp, i64, vp, vp, vp]),
+        "smsgate_legacy_parse": (i32, [vp, i64, vp, vp, C.POINTER(LegacyOutputs)]),
         "smsgate_scan_keys": (i32, [vp, vp, vp, i64, C.POINTER(Outputs)]),
         "smsgate_join_route": (i32, [vp, i64, i64, C.POINTER(Outputs)]),
         "smsgate_dedup": (i32, [vp, i64, i64, C.POINTER(Outputs)]),

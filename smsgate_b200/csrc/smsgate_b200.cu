@@ -21,6 +21,7 @@
 
 #include "../../include/smsgate_b200.h"
 #include "join_core.cuh"
+#include "legacy_core.cuh"
 #include "scan_core.cuh"
 
 // ------------------------------------------------------------------ PTX helpers (TMA 1-D bulk copy + mbarrier)
@@ -486,6 +487,27 @@ __global__ void k_strict_date_batch(int64_t n, const int32_t* __restrict__ offse
     packed[i] = sg_parse_strict_datetime(bytes + offsets[i], offsets[i + 1] - offsets[i]);
 }
 
+// ------------------------------------------------------------------ legacy offline replay (process_cached.py)
+struct LegacyOut {
+    uint8_t* status; uint8_t* lflags; int32_t* strip; int32_t* caps; double* amount; double* balance; uint8_t* body_hash;
+};
+__global__ void __launch_bounds__(128)
+k_legacy_parse(int64_t n, const int64_t* __restrict__ offsets, const uint8_t* __restrict__ bytes, LegacyTables L,
+               LegacyOut out) {
+    const int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const LegacyResult r = sg_legacy_process(bytes + offsets[i], (int)(offsets[i + 1] - offsets[i]), L);
+    out.status[i] = (uint8_t)r.status;
+    out.lflags[i] = (uint8_t)r.lflags;
+    out.strip[2 * i] = r.strip_lo;
+    out.strip[2 * i + 1] = r.strip_hi;
+    for (int k = 0; k < 2 * RX_MAX_GROUPS; ++k) out.caps[i * 2 * RX_MAX_GROUPS + k] = r.caps[k];
+    out.amount[i] = r.amount;
+    out.balance[i] = r.balance;
+    uint32_t* h = reinterpret_cast<uint32_t*>(out.body_hash + i * 32);
+    for (int k = 0; k < 8; ++k) h[k] = __byte_perm(r.digest[k], 0, 0x0123);
+}
+
 // ================================================================== host side / C ABI
 struct smsgate_ctx {
     int device = 0;
@@ -501,6 +523,8 @@ struct smsgate_ctx {
     std::string err;
     int64_t launches = 0;
     DeviceTables* d_tables = nullptr;
+    uint8_t* d_legacy = nullptr;            // regex programs + Unicode tables of the legacy path, one slab
+    LegacyTables legacy;
     // cache
     int64_t cache_m = 0;
     uint8_t* c_keys = nullptr;
@@ -606,6 +630,24 @@ extern "C" int smsgate_create(int device, void* cuda_stream, smsgate_ctx** out) 
     e = cudaMemcpy(ctx->d_tables, h, sizeof(DeviceTables), cudaMemcpyHostToDevice);
     delete h;
     if (e != cudaSuccess) return bail("cudaMemcpy tables", e);
+    {   // legacy-path tables: one slab, 16-byte aligned pieces
+        const size_t sz[6] = {sizeof(H_RX_DEBIT), sizeof(H_RX_CREDIT), sizeof(H_RX_WORD_LO), sizeof(H_RX_WORD_HI),
+                              sizeof(H_RX_CI_EXC), sizeof(H_LEG_OTP_NEXT)};
+        const void* src[6] = {H_RX_DEBIT, H_RX_CREDIT, H_RX_WORD_LO, H_RX_WORD_HI, H_RX_CI_EXC, H_LEG_OTP_NEXT};
+        size_t off[6], total = 0;
+        for (int k = 0; k < 6; ++k) { off[k] = total; total += (sz[k] + 15) & ~(size_t)15; }
+        if ((e = cudaMalloc(&ctx->d_legacy, total)) != cudaSuccess) return bail("cudaMalloc legacy tables", e);
+        for (int k = 0; k < 6; ++k)
+            if ((e = cudaMemcpy(ctx->d_legacy + off[k], src[k], sz[k], cudaMemcpyHostToDevice)) != cudaSuccess)
+                return bail("cudaMemcpy legacy tables", e);
+        ctx->legacy.debit = reinterpret_cast<const uint32_t*>(ctx->d_legacy + off[0]);
+        ctx->legacy.credit = reinterpret_cast<const uint32_t*>(ctx->d_legacy + off[1]);
+        ctx->legacy.word_lo = reinterpret_cast<const uint32_t*>(ctx->d_legacy + off[2]);
+        ctx->legacy.word_hi = reinterpret_cast<const uint32_t*>(ctx->d_legacy + off[3]);
+        ctx->legacy.ci_exc = reinterpret_cast<const uint32_t*>(ctx->d_legacy + off[4]);
+        ctx->legacy.otp_next = ctx->d_legacy + off[5];
+        ctx->legacy.scan.t = ctx->d_tables;
+    }
     if ((e = cudaFuncSetAttribute(k_scan_keys, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(K1Smem))) != cudaSuccess)
         return bail("cudaFuncSetAttribute(k_scan_keys)", e);
     *out = ctx;
@@ -637,6 +679,7 @@ extern "C" void smsgate_destroy(smsgate_ctx* ctx) {
     free_scratch(ctx);
     cudaFree(ctx->mg_owner); cudaFree(ctx->mg_first); cudaFree(ctx->mg_last); cudaFree(ctx->mg_slot_of);
     cudaFree(ctx->p2p_table); cudaFree(ctx->p2p_slot_of); cudaFree(ctx->p2p_overflow);
+    cudaFree(ctx->d_legacy);
     cudaFree(ctx->d_tables);
     if (ctx->s_h2d) { cudaStreamSynchronize(ctx->s_h2d); cudaStreamDestroy(ctx->s_h2d); }
     if (ctx->s_d2h) { cudaStreamSynchronize(ctx->s_d2h); cudaStreamDestroy(ctx->s_d2h); }
@@ -784,6 +827,58 @@ done:
     cudaFree(d_off); cudaFree(d_b); cudaFree(d_p);
     return rc;
 #undef HB_TRY
+}
+
+extern "C" int smsgate_legacy_parse(smsgate_ctx* ctx, int64_t n, const int64_t* h_offsets, const uint8_t* h_bytes,
+                                    const smsgate_legacy_outputs* h_out) {
+    if (!ctx) return SMSGATE_E_ARG;
+    if (n < 0 || !h_out || (n > 0 && (!h_offsets || !h_out->status || !h_out->lflags || !h_out->strip || !h_out->caps ||
+                                      !h_out->amount || !h_out->balance || !h_out->body_hash)))
+        return fail(ctx, SMSGATE_E_ARG, "legacy_parse: NULL array");
+    if (n == 0) return SMSGATE_OK;
+    CUDA_TRY(ctx, cudaSetDevice(ctx->device));
+    const int64_t nb = h_offsets[n] - h_offsets[0];
+    if (nb < 0 || (nb > 0 && !h_bytes)) return fail(ctx, SMSGATE_E_ARG, "legacy_parse: bad offsets");
+    cudaStream_t st = ctx->stream;
+    uint8_t* slab = nullptr;
+    const size_t per = 1 + 1 + 8 + 8 * RX_MAX_GROUPS + 8 + 8 + 32;
+    const size_t need = (size_t)(n + 1) * 8 + (size_t)nb + 64 + (size_t)n * per + 8 * 256;
+    int rc = SMSGATE_OK;
+    cudaError_t e;
+#define LG_TRY(expr) if ((e = (expr)) != cudaSuccess) { rc = fail(ctx, SMSGATE_E_CUDA, std::string(#expr) + ": " + cudaGetErrorString(e)); goto done; }
+    LG_TRY(cudaMalloc(&slab, need));
+    {
+        uint8_t* p = slab;
+        auto take = [&](size_t b) { uint8_t* q = p; p += (b + 255) & ~(size_t)255; return q; };
+        int64_t* d_off = (int64_t*)take((size_t)(n + 1) * 8);
+        uint8_t* d_bytes = take((size_t)nb + 64);
+        LegacyOut o;
+        o.amount = (double*)take((size_t)n * 8);
+        o.balance = (double*)take((size_t)n * 8);
+        o.strip = (int32_t*)take((size_t)n * 8);
+        o.caps = (int32_t*)take((size_t)n * 8 * RX_MAX_GROUPS);
+        o.body_hash = take((size_t)n * 32);
+        o.status = take((size_t)n);
+        o.lflags = take((size_t)n);
+        LG_TRY(cudaMemcpyAsync(d_off, h_offsets, (size_t)(n + 1) * 8, cudaMemcpyHostToDevice, st));
+        if (nb) LG_TRY(cudaMemcpyAsync(d_bytes, h_bytes + h_offsets[0], (size_t)nb, cudaMemcpyHostToDevice, st));
+        // the kernel indexes bytes with the caller's absolute offsets
+        k_legacy_parse<<<(unsigned)((n + 127) / 128), 128, 0, st>>>(n, d_off, d_bytes - h_offsets[0], ctx->legacy, o);
+        ctx->launches += 1;
+        LG_TRY(cudaMemcpyAsync(h_out->status, o.status, (size_t)n, cudaMemcpyDeviceToHost, st));
+        LG_TRY(cudaMemcpyAsync(h_out->lflags, o.lflags, (size_t)n, cudaMemcpyDeviceToHost, st));
+        LG_TRY(cudaMemcpyAsync(h_out->strip, o.strip, (size_t)n * 8, cudaMemcpyDeviceToHost, st));
+        LG_TRY(cudaMemcpyAsync(h_out->caps, o.caps, (size_t)n * 8 * RX_MAX_GROUPS, cudaMemcpyDeviceToHost, st));
+        LG_TRY(cudaMemcpyAsync(h_out->amount, o.amount, (size_t)n * 8, cudaMemcpyDeviceToHost, st));
+        LG_TRY(cudaMemcpyAsync(h_out->balance, o.balance, (size_t)n * 8, cudaMemcpyDeviceToHost, st));
+        LG_TRY(cudaMemcpyAsync(h_out->body_hash, o.body_hash, (size_t)n * 32, cudaMemcpyDeviceToHost, st));
+        LG_TRY(cudaStreamSynchronize(st));
+        LG_TRY(cudaGetLastError());
+    }
+done:
+    cudaFree(slab);
+    return rc;
+#undef LG_TRY
 }
 
 // ---- stages

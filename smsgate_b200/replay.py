@@ -246,6 +246,10 @@ class ReplayEngine:
             L.check(self._ctx, self._lib.smsgate_replay_host_finish(self._ctx, C.byref(out)))
         return ReplayResult(batch, cols, self.table, base_index)
 
+    def msg_ids(self, batch: Batch) -> np.ndarray:
+        """SHA-1(body) of every message: the XML idempotency key (watcher.py:45).  uint8 [n, 20]."""
+        return self.replay(batch, _dt.datetime(1, 1, 1), columns=("msg_id",)).cols["msg_id"]
+
     # -- device-pointer stages (torch tensors) -------------------------------
     def device_columns(self, n: int, total: int, want: Optional[Sequence[str]] = None) -> dict:
         import torch

@@ -1,0 +1,78 @@
+"""XML backup ingestion: the host side of `_iter_sms` (services/xml_watcher/watcher.py:35-54)
+and of `parse_and_cache_sms` (read_xml.py:9-54).
+
+The XML text itself is parsed on the host with the same parser the reference
+uses (ElementTree / expat), so entity and character-reference decoding and
+attribute whitespace normalisation are identical by construction; what moves to
+the GPU is the per-message work (SHA-1 `msg_id`, and everything downstream).
+A GPU tokenizer for the `<sms …/>` elements is the first "next" row of SURVEY §8(f).
+"""
+from __future__ import annotations
+
+import datetime as _dt
+import xml.etree.ElementTree as ET
+from pathlib import Path
+from typing import Iterable, Optional, Union
+
+import numpy as np
+
+from .batch import Batch
+from .models import RawSMS
+
+
+def read_backup(xml_path: Union[str, Path]) -> Batch:
+    """Top-level <sms> elements of a backup as one ragged batch, in document order.
+    Raises what the reference raises: ET.ParseError for malformed XML, ValueError
+    for a non-integer `date` (watcher.py:37-44)."""
+    root = ET.parse(xml_path).getroot()                       # watcher.py:37-38
+    bodies, senders, dates = [], [], []
+    for elem in root.findall("sms"):                          # :40  (nested <sms> under <mms> are not direct children)
+        bodies.append(elem.get("body", ""))                   # :41
+        dates.append(int(elem.get("date", "0")))              # :42
+        senders.append(elem.get("address", ""))               # :44
+    return Batch.from_strings(bodies, senders, dates)
+
+
+def iso_utc(date_ms: int) -> str:
+    """RawSMS.date of an XML message (watcher.py:43, :52)."""
+    return _dt.datetime.fromtimestamp(date_ms / 1_000, tz=_dt.timezone.utc).isoformat()
+
+
+def iter_sms(xml_path: Union[str, Path], engine) -> Iterable[RawSMS]:
+    """Drop-in for `_iter_sms`: same RawSMS objects in the same order, `msg_id` =
+    SHA-1(body) computed on the GPU for the whole file at once.  A message that
+    fails RawSMS validation (empty body or sender) raises at that message, after
+    the earlier ones were yielded, like the reference's generator."""
+    batch = read_backup(xml_path)
+    if batch.n == 0:
+        return
+    ids = engine.msg_ids(batch)
+    for i in range(batch.n):
+        yield RawSMS(source="xml", device_id="xml_backup", msg_id=ids[i].tobytes().hex(), sender=batch.senders[i],
+                     date=iso_utc(int(batch.date_ms[i])), body=batch.body(i))
+
+
+def parse_and_cache_sms(xml_file: str, cache_dir: str) -> Optional[int]:
+    """read_xml.parse_and_cache_sms (read_xml.py:9-54): every top-level <sms> goes into the
+    DiskCache under its `date` attribute (later duplicates overwrite, :41); elements without
+    `date` are skipped (:43-44); a missing or malformed file is reported, not raised (:48-51).
+    Returns the number of stored messages (the reference only prints it)."""
+    from diskcache import Cache
+    cache = Cache(cache_dir, fanout_cache=True)               # :19 (the kwarg is stored as a setting, as in the reference)
+    stored = None
+    try:
+        root = ET.parse(xml_file).getroot()                   # :25-26
+        stored = 0
+        for elem in root.findall("sms"):                      # :32
+            data = elem.attrib                                # :34
+            key = data.get("date")                            # :37
+            if key:
+                cache.set(key, data)                          # :41
+                stored += 1
+    except FileNotFoundError:
+        print(f"XML file not found: {xml_file}")
+    except ET.ParseError:
+        print("could not parse the XML file")
+    finally:
+        cache.close()
+    return stored

@@ -69,3 +69,15 @@ def join_route(scan_cols, table, now_packed):
                         _p(cols["balance_exp"]), _p(cols["dec_flags"]), _p(cols["date"]), _p(cols["card"]),
                         _p(cols["card_len"]))
     return cols
+
+
+def legacy(bodies):
+    data, offsets = ragged_from_strings(bodies)
+    n = len(bodies)
+    cols = dict(status=np.zeros(n, np.uint8), lflags=np.zeros(n, np.uint8), strip=np.zeros((n, 2), np.int32),
+                caps=np.full((n, 20), -1, np.int32), amount=np.zeros(n, np.float64), balance=np.zeros(n, np.float64),
+                body_hash=np.zeros((n, 32), np.uint8))
+    data = np.concatenate([data, np.zeros(16, np.uint8)])
+    lib().hc_legacy(C.c_int64(n), _p(offsets), _p(data), _p(cols["status"]), _p(cols["lflags"]), _p(cols["strip"]),
+                    _p(cols["caps"]), _p(cols["amount"]), _p(cols["balance"]), _p(cols["body_hash"]))
+    return cols

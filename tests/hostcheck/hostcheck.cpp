@@ -10,6 +10,7 @@
 #include <vector>
 
 #include "join_core.cuh"
+#include "legacy_core.cuh"
 #include "scan_core.cuh"
 
 static ScanTables host_tables() {
@@ -98,6 +99,23 @@ extern "C" int hc_join_route(int64_t n, const uint8_t* cache_key, const uint8_t*
         date[i] = r.date;
         memcpy(card + i * 16, r.card, 16);
         card_len[i] = (uint8_t)r.card_bytes;
+    }
+    return 0;
+}
+
+extern "C" int hc_legacy(int64_t n, const int64_t* offsets, const uint8_t* bytes, uint8_t* status, uint8_t* lflags,
+                         int32_t* strip, int32_t* caps, double* amount, double* balance, uint8_t* body_hash) {
+    LegacyTables L;
+    L.debit = H_RX_DEBIT; L.credit = H_RX_CREDIT; L.word_lo = H_RX_WORD_LO; L.word_hi = H_RX_WORD_HI;
+    L.ci_exc = H_RX_CI_EXC; L.otp_next = (const uint8_t*)H_LEG_OTP_NEXT;
+    L.scan = host_tables();
+    for (int64_t i = 0; i < n; ++i) {
+        LegacyResult r = sg_legacy_process(bytes + offsets[i], (int)(offsets[i + 1] - offsets[i]), L);
+        status[i] = (uint8_t)r.status; lflags[i] = (uint8_t)r.lflags;
+        strip[2 * i] = r.strip_lo; strip[2 * i + 1] = r.strip_hi;
+        for (int k = 0; k < 2 * RX_MAX_GROUPS; ++k) caps[i * 2 * RX_MAX_GROUPS + k] = r.caps[k];
+        amount[i] = r.amount; balance[i] = r.balance;
+        put_be(body_hash + i * 32, r.digest, 8);
     }
     return 0;
 }

@@ -1,0 +1,109 @@
+"""Legacy offline replay and XML ingestion through the C ABI on the GPU."""
+import json
+import os
+import random
+import struct
+import xml.etree.ElementTree as ET
+
+import numpy as np
+import pytest
+
+from oracle import legacy_oracle as LO
+from smsgate_b200 import _lib as L
+from smsgate_b200 import legacy, synth, xml_ingest
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.fixture(scope="module")
+def engine():
+    from smsgate_b200.replay import ReplayEngine
+    eng = ReplayEngine(0)
+    yield eng
+    eng.close()
+
+
+def _bits(d):
+    if d is None:
+        return None
+    out = dict(d)
+    for k in ("amount", "balance"):
+        out[k] = "%016x" % struct.unpack("<Q", struct.pack("<d", d[k]))[0]
+    return out
+
+
+def _check(res, bodies):
+    for i, b in enumerate(bodies):
+        st, text, digest, parsed = LO.process_body(b)
+        fl = int(res.cols["lflags"][i])
+        assert not fl & L.LEG_F_BUDGET, b
+        assert res.stripped(i) == text and res.body_hash_hex(i) == digest.hex(), b
+        assert int(res.cols["status"][i]) == st, b
+        if parsed is not None and not fl & L.LEG_F_INEXACT:
+            assert _bits(res.parsed(i)) == _bits(parsed), b
+
+
+def test_legacy_golden_and_fuzz(engine, golden):
+    bodies = [c["body"] for c in golden("legacy.json")["cases"]]
+    rnd = random.Random(5)
+    base = ("APPROVED PURCHASE DB SALE: TEST LLC, YEREVAN, TEST STR. 29, 24 AREA,06.05.25 14:23,card ***0018. "
+            "Amount:52.00 USD, Balance:1842.74 USD")
+    for _ in range(3000):
+        s = list(base)
+        for _ in range(rnd.randint(1, 4)):
+            k = rnd.randrange(len(s))
+            s[k] = rnd.choice(" ,.:*\n9aAſ٥")
+        bodies.append("".join(s))
+    _check(legacy.parse_bodies(engine, bodies), bodies)
+
+
+def test_legacy_on_synthetic_backup(engine):
+    backup = synth.generate(20000, seed=77, mixed_locale=True)
+    _check(legacy.parse_bodies(engine, backup.bodies), backup.bodies)
+
+
+def test_process_sms_from_cache_matches_reference_run(engine, golden, tmp_path):
+    import diskcache
+    g = golden("legacy.json")["process"]
+    src, deb, cre = (str(tmp_path / n) for n in ("src", "deb", "cre"))
+    with diskcache.Cache(src) as c:
+        for i, b in enumerate(g["bodies"]):
+            c.set(str(1707900000000 + i), {"address": "BANK", "date": str(1707900000000 + i), "body": b})
+        c.set("already", {"body": g["bodies"][0], "status": "processed"})
+        c.set("nobody", {"address": "X"})
+    stats = legacy.process_sms_from_cache(engine, src, deb, cre)
+    with diskcache.Cache(src) as c:
+        assert {k: c.get(k).get("status") for k in c} == g["statuses"]
+    for path, want in ((deb, g["debit"]), (cre, g["credit"])):
+        with diskcache.Cache(path) as c:
+            got = {k: dict(_bits({kk: vv for kk, vv in c.get(k).items() if kk not in ("msg_id", "original_body")}),
+                           msg_id=c.get(k)["msg_id"], original_body=c.get(k)["original_body"]) for k in c}
+        assert got == want
+    assert stats["skipped"] == 1 + sum(1 for v in g["statuses"].values() if v == "skipped_otp")
+    assert stats["failed"] == sum(1 for v in g["statuses"].values() if v == "failed_to_parse")
+
+
+def test_iter_sms_golden(engine, golden, tmp_path):
+    for c in golden("iter_sms.json"):
+        p = tmp_path / (c["name"] + ".xml")
+        p.write_text(c["xml"], encoding="utf-8", newline="")
+        if "error" in c:
+            with pytest.raises(Exception) as ei:
+                list(xml_ingest.iter_sms(p, engine))
+            assert type(ei.value).__name__ == c["error"], c["name"]
+        else:
+            rows = [r.model_dump() for r in xml_ingest.iter_sms(p, engine)]
+            assert rows == c["rows"], c["name"]
+
+
+def test_parse_and_cache_sms(tmp_path):
+    import diskcache
+    backup = synth.generate(300, seed=3)
+    xml = tmp_path / "b.xml"
+    synth.write_xml(str(xml), backup)
+    n = xml_ingest.parse_and_cache_sms(str(xml), str(tmp_path / "cache"))
+    assert n == 300
+    with diskcache.Cache(str(tmp_path / "cache")) as c:
+        assert len(c) == 300
+        assert c.get(str(backup.date_ms[7]))["body"] == backup.bodies[7].replace("\n", "\n")
+    assert xml_ingest.parse_and_cache_sms(str(tmp_path / "missing.xml"), str(tmp_path / "c2")) is None
