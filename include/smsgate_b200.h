@@ -66,7 +66,8 @@ extern "C" {
 #define SMSGATE_E_DATE_TZ 0x0100
 #define SMSGATE_E_DATE_KEY 0x0200
 
-/* dec_flags[] layout: bits 0-1 amount error, 2-3 balance error, bit 4 amount sign, bit 5 balance sign */
+/* dec_flags[] layout: bits 0-1 amount error, 2-3 balance error, bit 4 amount sign, bit 5 balance sign,
+ * bit 6 / bit 7: amount / balance does not fit Numeric(14,2) (more than 12 integer digits) */
 #define SMSGATE_DEC_OK 0
 #define SMSGATE_DEC_SYNTAX 1   /* parse_ambiguous_decimal raises ValueError */
 #define SMSGATE_DEC_OVERFLOW 2 /* |coefficient| > INT64_MAX: representation limit of this library */
@@ -97,6 +98,9 @@ typedef struct smsgate_outputs {
     uint8_t* survivor;    /* [n] 1 = last occurrence of its msg_id among upserts: the record that survives */
     uint8_t* first_seen;  /* [n] 1 = first occurrence: an insert rather than a patch */
     int64_t* last_idx;    /* [n] global index of the surviving occurrence, -1 if the message is not upserted */
+    int64_t* amount_cents;  /* [n] |amount| as a Numeric(14,2) column stores it (db/models.py:21): two decimals, halves
+                               away from zero; sign is dec_flags bit 4 */
+    int64_t* balance_cents; /* [n] same for the balance (db/models.py:27), sign in dec_flags bit 5 */
 } smsgate_outputs;
 
 /* ---- lifecycle ---------------------------------------------------------- */

@@ -307,6 +307,8 @@ class MessageOutcome:
     parsed: Optional[Parsed] = None
     amount: tuple = (0, 0, 0, 0)          # decimal_triplet of the cached amount string
     balance: tuple = (0, 0, 0, 0)
+    amount_cents: tuple = (False, 0)      # numeric_14_2 of the same strings
+    balance_cents: tuple = (False, 0)
 
 
 def copy_resp(v: Any) -> Any:
@@ -330,6 +332,8 @@ def replay_one(body: str, sender: str, raw_date: str, cache, now: _dt.datetime,
     if isinstance(resp0, dict):
         out.amount = decimal_triplet(str(resp0.get("amount")))
         out.balance = decimal_triplet(str(resp0.get("balance")))
+        out.amount_cents = numeric_14_2(str(resp0.get("amount")))
+        out.balance_cents = numeric_14_2(str(resp0.get("balance")))
     if out.worker_skip:                                           # worker.py:112-126
         return out
     if out.parser_otp:                                            # gemini_parser.py:198-200
@@ -410,3 +414,17 @@ def replay(bodies, senders, raw_dates, cache, now: _dt.datetime) -> ReplayResult
 def iso_utc_from_ms(date_ms: int) -> str:
     """RawSMS.date for XML input (services/xml_watcher/watcher.py:42-43,52)."""
     return _dt.datetime.fromtimestamp(date_ms / 1_000, tz=_dt.timezone.utc).isoformat()
+
+
+def numeric_14_2(text: str):
+    """What a Numeric(14,2) column keeps of parse_ambiguous_decimal(text) (db/models.py:21,27):
+    (overflow, |cents|).  PostgreSQL rounds numeric halves away from zero and rejects more than
+    12 integer digits.  Derived from PostgreSQL's documented behaviour; no reference code runs it."""
+    from decimal import ROUND_HALF_UP
+    err, sign, coef, exp = decimal_triplet(text)
+    if err == DEC_ERR_OVERFLOW:
+        return (True, 0)
+    if err != DEC_OK:
+        return (False, 0)
+    cents = int((Decimal((0, tuple(map(int, str(coef))), exp))).quantize(Decimal("0.01"), rounding=ROUND_HALF_UP) * 100)
+    return (True, 0) if cents > 99_999_999_999_999 else (False, cents)

@@ -38,6 +38,7 @@ COLUMNS = (
     ("amount_coef", "i8", 1), ("balance_coef", "i8", 1), ("amount_exp", "i4", 1), ("balance_exp", "i4", 1),
     ("dec_flags", "u1", 1), ("date", "i8", 1), ("card", "u1", 16), ("card_len", "u1", 1),
     ("survivor", "u1", 1), ("first_seen", "u1", 1), ("last_idx", "i8", 1),
+    ("amount_cents", "i8", 1), ("balance_cents", "i8", 1),
 )
 
 

@@ -142,6 +142,34 @@ SG_HD void sg_normalise_card(const uint8_t* s, int len, uint8_t out16[16], int* 
     *nbytes = nb;
 }
 
+// What Postgres stores in a Numeric(14,2) column (db/models.py:21,27): the value rounded to two
+// decimals, halves away from zero; more than 12 integer digits is a numeric overflow (the
+// reference swallows that error, services/pb_writer/upsert.py:32-33).  Returns |cents|, sets
+// *overflow.  Derived from PostgreSQL's documented numeric rounding, not from reference code.
+SG_HD int64_t sg_numeric_14_2(const DecResult& d, bool* overflow) {
+    *overflow = false;
+    if (d.err != SG_DEC_OK) { *overflow = d.err == SG_DEC_OVERFLOW; return 0; }
+    uint64_t c = (uint64_t)d.coef;
+    const int e = d.exp;                       // <= 0
+    if (e >= -2) {
+        for (int k = 0; k < 2 + e; ++k) {
+            if (c > 99999999999999ull) { *overflow = true; return 0; }
+            c *= 10;
+        }
+    } else {
+        const int k = -e - 2;                  // digits to drop
+        if (k > 19) c = 0;                     // coef < 10^19: rounds to zero
+        else {
+            uint64_t div = 1;
+            for (int j = 0; j < k; ++j) div *= 10;          // k <= 19 fits uint64
+            const uint64_t q = c / div, r = c % div;
+            c = q + ((r >= div - r) ? 1 : 0);               // 2r >= div without overflow
+        }
+    }
+    if (c > 99999999999999ull) { *overflow = true; return 0; }
+    return (int64_t)c;
+}
+
 struct EntryView {              // one cache entry as the loader laid it out
     const uint8_t* amount; int amount_len;
     const uint8_t* balance; int balance_len;
@@ -157,6 +185,8 @@ struct RouteResult {
     int64_t date;               // packed datetime, 0 when none
     uint8_t card[16];
     int card_bytes;
+    int64_t amount_cents, balance_cents;    // |value| as stored by Numeric(14,2)
+    uint32_t cents_overflow;                // bit 0 amount, bit 1 balance
 };
 
 // worker.py:112-189 + gemini_parser.py:224-247 + writer.py:65-84 for one
@@ -168,6 +198,8 @@ SG_HD RouteResult sg_route(uint32_t mflags, int32_t body_date, bool hit, const E
     r.balance = r.amount;
     r.date = 0;
     r.card_bytes = 0;
+    r.amount_cents = r.balance_cents = 0;
+    r.cents_overflow = 0;
     for (int k = 0; k < 16; ++k) r.card[k] = 0;
     int card_cps = 0;
     bool fail = false;
@@ -176,6 +208,11 @@ SG_HD RouteResult sg_route(uint32_t mflags, int32_t body_date, bool hit, const E
         // canonical amounts are reported for every hit, whatever the routing says
         r.amount = sg_parse_decimal(e.amount, e.amount_len);
         r.balance = sg_parse_decimal(e.balance, e.balance_len);
+        bool ov = false;
+        r.amount_cents = sg_numeric_14_2(r.amount, &ov);
+        r.cents_overflow |= ov ? 1u : 0u;
+        r.balance_cents = sg_numeric_14_2(r.balance, &ov);
+        r.cents_overflow |= ov ? 2u : 0u;
         if (e.eflags & SG_E_CARD_STR) sg_normalise_card(e.card, e.card_len, r.card, &card_cps, &r.card_bytes);
         // --- date (gemini_parser.py:226-230)
         int64_t dt = 0;

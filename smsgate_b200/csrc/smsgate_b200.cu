@@ -353,6 +353,8 @@ struct JoinOut {
     int64_t* date;
     uint8_t* card;
     uint8_t* card_len;
+    int64_t* amount_cents;
+    int64_t* balance_cents;
 };
 
 __global__ void __launch_bounds__(256)
@@ -404,7 +406,10 @@ k_join_route(int64_t n, const uint8_t* __restrict__ cache_key, const uint8_t* __
     if (out.amount_exp) out.amount_exp[i] = r.amount.exp;
     if (out.balance_exp) out.balance_exp[i] = r.balance.exp;
     if (out.dec_flags)
-        out.dec_flags[i] = (uint8_t)(r.amount.err | (r.balance.err << 2) | (r.amount.sign << 4) | (r.balance.sign << 5));
+        out.dec_flags[i] = (uint8_t)(r.amount.err | (r.balance.err << 2) | (r.amount.sign << 4) | (r.balance.sign << 5) |
+                                     (r.cents_overflow << 6));
+    if (out.amount_cents) out.amount_cents[i] = r.amount_cents;
+    if (out.balance_cents) out.balance_cents[i] = r.balance_cents;
     if (out.date) out.date[i] = r.date;
     if (out.card) {
         uint4 c;
@@ -695,7 +700,7 @@ extern "C" void smsgate_destroy(smsgate_ctx* ctx) {
 }
 
 // bytes of the output slab per message (smsgate_replay_host): see carve_slab()
-static const int64_t SLAB_PER_MSG = 20 + 32 + 1 + 4 + 4 + 4 + 1 + 8 + 8 + 4 + 4 + 1 + 8 + 16 + 1 + 1 + 1 + 8;
+static const int64_t SLAB_PER_MSG = 20 + 32 + 1 + 4 + 4 + 4 + 1 + 8 + 8 + 4 + 4 + 1 + 8 + 16 + 1 + 1 + 1 + 8 + 8 + 8;
 
 extern "C" int smsgate_reserve(smsgate_ctx* ctx, int64_t max_msgs, int64_t max_bytes) {
     if (!ctx) return SMSGATE_E_ARG;
@@ -717,7 +722,7 @@ extern "C" int smsgate_reserve(smsgate_ctx* ctx, int64_t max_msgs, int64_t max_b
     CUDA_TRY(ctx, cudaMalloc(&ctx->s_bytes, (size_t)max_bytes + 64));
     CUDA_TRY(ctx, cudaMalloc(&ctx->s_fixed, (size_t)max_bytes + 64));
     CUDA_TRY(ctx, cudaMalloc(&ctx->s_offsets, (size_t)(max_msgs + 1) * 8));
-    CUDA_TRY(ctx, cudaMalloc(&ctx->s_out, (size_t)(max_msgs + 16) * SLAB_PER_MSG + 4096));
+    CUDA_TRY(ctx, cudaMalloc(&ctx->s_out, (size_t)(max_msgs + 16) * SLAB_PER_MSG + 65536));
     ctx->dd_cap = cap;
     ctx->cap_msgs = max_msgs;
     ctx->cap_bytes = max_bytes;
@@ -909,7 +914,7 @@ extern "C" int smsgate_join_route(smsgate_ctx* ctx, int64_t n, int64_t now_packe
     CacheView C{ctx->c_keys, ctx->c_table, ctx->c_cap ? ctx->c_cap - 1 : 0, ctx->c_val_offsets, ctx->c_val_bytes,
                 ctx->c_eflags, ctx->c_date_packed, ctx->cache_m};
     JoinOut jo{out->slot, out->status, out->amount_coef, out->balance_coef, out->amount_exp, out->balance_exp,
-               out->dec_flags, out->date, out->card, out->card_len};
+               out->dec_flags, out->date, out->card, out->card_len, out->amount_cents, out->balance_cents};
     k_join_route<<<(unsigned)((n + 255) / 256), 256, 0, ctx->stream>>>(n, out->cache_key, out->flags, out->body_date,
                                                                         now_packed, C, jo);
     ctx->launches += 1;
@@ -960,6 +965,8 @@ static void carve_slab(uint8_t* slab, int64_t n, uint8_t* fixed, smsgate_outputs
     d->balance_coef = (int64_t*)take((size_t)n * 8);
     d->date = (int64_t*)take((size_t)n * 8);
     d->last_idx = (int64_t*)take((size_t)n * 8);
+    d->amount_cents = (int64_t*)take((size_t)n * 8);
+    d->balance_cents = (int64_t*)take((size_t)n * 8);
     d->cache_key = take((size_t)n * 32);
     d->msg_id = take((size_t)n * 20);
     d->card = take((size_t)n * 16);
@@ -984,6 +991,7 @@ static smsgate_outputs shift_columns(const smsgate_outputs& d, int64_t lo) {
     SH(msg_id, 20); SH(cache_key, 32); SH(flags, 1); SH(body_date, 1); SH(fixed_len, 1); SH(slot, 1); SH(status, 1);
     SH(amount_coef, 1); SH(balance_coef, 1); SH(amount_exp, 1); SH(balance_exp, 1); SH(dec_flags, 1); SH(date, 1);
     SH(card, 16); SH(card_len, 1); SH(survivor, 1); SH(first_seen, 1); SH(last_idx, 1);
+    SH(amount_cents, 1); SH(balance_cents, 1);
 #undef SH
     return o;
 }
@@ -1044,7 +1052,7 @@ extern "C" int smsgate_replay_host_begin(smsgate_ctx* ctx, const uint8_t* h_byte
     if (h_out->col) CUDA_TRY(ctx, cudaMemcpyAsync(h_out->col + lo * (w), d.col + lo * (w), (size_t)(m * (w)) * sizeof(*d.col), cudaMemcpyDeviceToHost, sout))
         BACK(msg_id, 20); BACK(cache_key, 32); BACK(flags, 1); BACK(body_date, 1); BACK(fixed_len, 1); BACK(slot, 1);
         BACK(status, 1); BACK(amount_coef, 1); BACK(balance_coef, 1); BACK(amount_exp, 1); BACK(balance_exp, 1);
-        BACK(dec_flags, 1); BACK(date, 1); BACK(card, 16); BACK(card_len, 1);
+        BACK(dec_flags, 1); BACK(date, 1); BACK(card, 16); BACK(card_len, 1); BACK(amount_cents, 1); BACK(balance_cents, 1);
 #undef BACK
         if (h_out->fixed_bytes) {
             const int64_t b0 = h_offsets[lo], b1 = h_offsets[hi];

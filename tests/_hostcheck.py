@@ -59,7 +59,8 @@ def join_route(scan_cols, table, now_packed):
     cols = dict(slot=np.zeros(n, np.int32), status=np.zeros(n, np.uint8), amount_coef=np.zeros(n, np.int64),
                 balance_coef=np.zeros(n, np.int64), amount_exp=np.zeros(n, np.int32),
                 balance_exp=np.zeros(n, np.int32), dec_flags=np.zeros(n, np.uint8), date=np.zeros(n, np.int64),
-                card=np.zeros((n, 16), np.uint8), card_len=np.zeros(n, np.uint8))
+                card=np.zeros((n, 16), np.uint8), card_len=np.zeros(n, np.uint8),
+                amount_cents=np.zeros(n, np.int64), balance_cents=np.zeros(n, np.int64))
     keys = np.ascontiguousarray(table.keys)
     vb = np.concatenate([table.val_bytes, np.zeros(16, np.uint8)])
     lib().hc_join_route(C.c_int64(n), _p(scan_cols["cache_key"]), _p(scan_cols["flags"]), _p(scan_cols["body_date"]),
@@ -67,7 +68,7 @@ def join_route(scan_cols, table, now_packed):
                         _p(table.eflags), _p(table.date_packed), _p(cols["slot"]), _p(cols["status"]),
                         _p(cols["amount_coef"]), _p(cols["balance_coef"]), _p(cols["amount_exp"]),
                         _p(cols["balance_exp"]), _p(cols["dec_flags"]), _p(cols["date"]), _p(cols["card"]),
-                        _p(cols["card_len"]))
+                        _p(cols["card_len"]), _p(cols["amount_cents"]), _p(cols["balance_cents"]))
     return cols
 
 

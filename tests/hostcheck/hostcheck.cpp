@@ -74,7 +74,7 @@ extern "C" int hc_join_route(int64_t n, const uint8_t* cache_key, const uint8_t*
                              const uint8_t* val_bytes, const uint16_t* eflags, const int64_t* date_packed,
                              int32_t* slot, uint8_t* status, int64_t* amount_coef, int64_t* balance_coef,
                              int32_t* amount_exp, int32_t* balance_exp, uint8_t* dec_flags, int64_t* date,
-                             uint8_t* card, uint8_t* card_len) {
+                             uint8_t* card, uint8_t* card_len, int64_t* amount_cents, int64_t* balance_cents) {
     std::unordered_map<std::string, int> idx;
     for (int64_t e = 0; e < m; ++e) idx.emplace(std::string((const char*)keys + e * 32, 32), (int)e);
     for (int64_t i = 0; i < n; ++i) {
@@ -95,7 +95,9 @@ extern "C" int hc_join_route(int64_t n, const uint8_t* cache_key, const uint8_t*
         slot[i] = e; status[i] = (uint8_t)r.status;
         amount_coef[i] = r.amount.coef; balance_coef[i] = r.balance.coef;
         amount_exp[i] = r.amount.exp; balance_exp[i] = r.balance.exp;
-        dec_flags[i] = (uint8_t)(r.amount.err | (r.balance.err << 2) | (r.amount.sign << 4) | (r.balance.sign << 5));
+        dec_flags[i] = (uint8_t)(r.amount.err | (r.balance.err << 2) | (r.amount.sign << 4) | (r.balance.sign << 5) |
+                                 (r.cents_overflow << 6));
+        amount_cents[i] = r.amount_cents; balance_cents[i] = r.balance_cents;
         date[i] = r.date;
         memcpy(card + i * 16, r.card, 16);
         card_len[i] = (uint8_t)r.card_bytes;

@@ -126,3 +126,25 @@ def test_replay_against_reference_run(golden, name):
             assert int(jr["amount_coef"][i]) == int(p["amount"][1]) and int(jr["amount_exp"][i]) == p["amount"][2]
             assert int(jr["balance_coef"][i]) == int(p["balance"][1]) and int(jr["balance_exp"][i]) == p["balance"][2]
             assert jr["card"][i, :int(jr["card_len"][i])].tobytes().decode() == p["card"]
+
+
+def test_numeric_14_2_storage_rounding():
+    texts = ["0", "0.005", "0.0049999", "0.015", "1.005", "2.675", "52.00", "1,234.565", "999999999999.994",
+             "999999999999.995", "1000000000000", "123456789012345678", "12345678901234567890", "0.00000000000000000001",
+             "5", "5.5", "-2.675", "79.825,895", "0.994999999999999999", "abc", ""]
+    import random
+    rnd = random.Random(9)
+    for _ in range(2000):
+        texts.append("".join(rnd.choice("0123456789") for _ in range(rnd.randint(1, 16))) + "." +
+                     "".join(rnd.choice("0123456789") for _ in range(rnd.randint(0, 6))))
+    bodies = [f"body {i}" for i in range(len(texts))]
+    sc = H.scan(bodies)
+    cache = {sc["cache_key"][i].tobytes().hex(): dict(txn_type="debit", date="06.05.25 14:23", amount=t, currency="usd",
+                                                      card="1234", merchant="M", city=None, address=None, balance=t)
+             for i, t in enumerate(texts)}
+    jr = H.join_route(sc, _table(cache), gemini_cache.pack_datetime(dt.datetime(2026, 1, 1)))
+    for i, t in enumerate(texts):
+        ov, cents = O.numeric_14_2(t)
+        fl = int(jr["dec_flags"][i])
+        assert bool(fl & 0x40) == ov and bool(fl & 0x80) == ov, t
+        assert int(jr["amount_cents"][i]) == cents and int(jr["balance_cents"][i]) == cents, t

@@ -141,6 +141,8 @@ def _compare_with_oracle(res, backup, now):
                 assert (fl >> sh) & 3 == want[0], (i, w)
                 if want[0] == 0:
                     assert ((fl >> sg) & 1, int(res.cols[w + "_coef"][i]), int(res.cols[w + "_exp"][i])) == want[1:]
+            assert (bool(fl & 0x40), int(res.amount_cents[i])) == o.amount_cents, i
+            assert (bool(fl & 0x80), int(res.balance_cents[i])) == o.balance_cents, i
         if o.parsed is not None and o.status != O.ST_FAILED_EXC:
             assert int(res.date[i]) == O.pack_datetime(o.parsed.date), i
             assert res.fixed_body(i) == o.fixed
@@ -202,7 +204,7 @@ def test_stage_calls_match_fused_replay(engine):
     torch.cuda.synchronize()
     for name in ("msg_id", "cache_key", "flags", "body_date", "fixed_len", "slot", "status", "amount_coef",
                  "balance_coef", "amount_exp", "balance_exp", "dec_flags", "date", "card", "card_len", "survivor",
-                 "first_seen", "last_idx"):
+                 "first_seen", "last_idx", "amount_cents", "balance_cents"):
         assert np.array_equal(cols[name].cpu().numpy(), ref.cols[name]), name
     assert int(ref.last_idx.max()) >= 1000
 
