@@ -37,6 +37,8 @@ extern "C" {
 #define SMSGATE_E_NOMEM (-3)
 #define SMSGATE_E_STATE (-4)
 #define SMSGATE_E_LIMIT (-5)
+#define SMSGATE_E_XML (-6)         /* the document is not well-formed: what ElementTree reports as ParseError */
+#define SMSGATE_E_UNSUPPORTED (-7) /* well-formedness undecided: a construct outside the supported XML dialect */
 
 /* flags[] bits written by the scan */
 #define SMSGATE_F_WORKER_SKIP 0x01 /* services/parser_worker/worker.py:112-121 */
@@ -142,6 +144,31 @@ int smsgate_decimal_batch(smsgate_ctx* ctx, int64_t n, const int32_t* h_offsets,
  * string needs the reference's strptime/dateutil chain on the host. */
 int smsgate_strict_date_batch(smsgate_ctx* ctx, int64_t n, const int32_t* h_offsets, const uint8_t* h_bytes,
                               int64_t* h_packed);
+
+/* ---- XML backup -> ragged batch on the GPU -----------------------------------
+ * Replaces, for a whole backup file at once, `ET.parse(path)` + `root.findall("sms")` +
+ * `elem.get("body" / "date" / "address")` + `int(date)` of `_iter_sms`
+ * (services/xml_watcher/watcher.py:37-44; the same loop in read_xml.py:25-37).
+ * smsgate_xml_scan takes the file bytes (host memory), tokenizes and validates them on the
+ * GPU and reports how many top-level <sms> elements there are and how many bytes their decoded
+ * body / address attributes take; smsgate_xml_emit then writes the batch into caller-owned
+ * device buffers: body_offsets[n+1] + body_bytes (exactly the input of smsgate_scan_keys),
+ * sender_offsets[n+1] + sender_bytes, date_ms[n] and mflags[n].  The scan keeps its
+ * intermediate state in the context until emit or smsgate_xml_release.
+ * Dialect: UTF-8, declaration / processing instructions, comments without '<', elements
+ * nested at most 64 deep, at most 64 attributes per element, the five predefined entities
+ * and numeric character references.  SMSGATE_E_XML = not well-formed (err_pos = byte
+ * offset); SMSGATE_E_UNSUPPORTED = DOCTYPE / CDATA / another encoding / '<' in a comment:
+ * hand the file to a general parser. */
+#define SMSGATE_XML_HAS_BODY 0x01    /* the element has a body attribute (else elem.get gives "") */
+#define SMSGATE_XML_HAS_ADDRESS 0x02
+#define SMSGATE_XML_DATE_BAD 0x04    /* int(date) raises ValueError */
+#define SMSGATE_XML_DATE_BIG 0x08    /* int(date) is valid but beyond int64 */
+int smsgate_xml_scan(smsgate_ctx* ctx, const uint8_t* h_xml, int64_t nbytes, int64_t* n_out, int64_t* body_bytes,
+                     int64_t* sender_bytes, int64_t* err_pos);
+int smsgate_xml_emit(smsgate_ctx* ctx, uint8_t* d_body_bytes, int64_t* d_body_offsets, uint8_t* d_sender_bytes,
+                     int64_t* d_sender_offsets, int64_t* d_date_ms, uint8_t* d_mflags);
+int smsgate_xml_release(smsgate_ctx* ctx);
 
 /* ---- the legacy offline replay (host buffers in and out) --------------------
  * process_cached.process_sms_from_cache (process_cached.py:210-268) for n source-cache

@@ -30,6 +30,8 @@ MAX_WORLD = 64
 RECORD_BYTES = 32
 P2P_RECORD_BYTES = 48
 E_LIMIT = -5
+E_XML, E_UNSUPPORTED = -6, -7
+XML_HAS_BODY, XML_HAS_ADDRESS, XML_DATE_BAD, XML_DATE_BIG = 1, 2, 4, 8
 
 # (column name, numpy dtype string, elements per message)
 COLUMNS = (
@@ -87,6 +89,9 @@ def lib():
         "smsgate_cache_size": (i64, [vp]),
         "smsgate_decimal_batch": (i32, [vp, i64, vp, vp, vp, vp, vp]),
         "smsgate_strict_date_batch": (i32, [vp, i64, vp, vp, vp]),
+        "smsgate_xml_scan": (i32, [vp, vp, i64, vp, vp, vp, vp]),
+        "smsgate_xml_emit": (i32, [vp, vp, vp, vp, vp, vp, vp]),
+        "smsgate_xml_release": (i32, [vp]),
         "smsgate_legacy_parse": (i32, [vp, i64, vp, vp, C.POINTER(LegacyOutputs)]),
         "smsgate_scan_keys": (i32, [vp, vp, vp, i64, C.POINTER(Outputs)]),
         "smsgate_join_route": (i32, [vp, i64, i64, C.POINTER(Outputs)]),

@@ -524,6 +524,14 @@ struct smsgate_ctx {
     cudaEvent_t ev_in[MAX_CHUNKS] = {nullptr}, ev_k[MAX_CHUNKS] = {nullptr};
     cudaEvent_t ev_start = nullptr, ev_dedup = nullptr, ev_done = nullptr;
     int64_t host_n = 0, host_total = 0;      // batch of the pending smsgate_replay_host_begin
+    // pending XML extraction (smsgate_xml_scan .. smsgate_xml_emit)
+    uint8_t* xml_slab = nullptr;
+    int64_t xml_n = 0, xml_T = 0, xml_nx = 0;
+    const uint8_t* xml_x = nullptr;
+    int64_t *xml_tag_pos = nullptr, *xml_end = nullptr, *xml_sms_tag = nullptr, *xml_body_off = nullptr, *xml_sender_off = nullptr,
+            *xml_date_ms = nullptr;
+    int32_t *xml_name_off = nullptr, *xml_name_len = nullptr;
+    uint8_t *xml_kind = nullptr, *xml_mflags = nullptr;
     int sm_count = 148;
     std::string err;
     int64_t launches = 0;
@@ -581,6 +589,8 @@ static uint64_t pow2_at_least(uint64_t x) {
     while (p < x) p <<= 1;
     return p;
 }
+
+#include "xml_extract.cuh"
 
 extern "C" int smsgate_abi_version(void) { return SMSGATE_ABI_VERSION; }
 
@@ -685,6 +695,7 @@ extern "C" void smsgate_destroy(smsgate_ctx* ctx) {
     cudaFree(ctx->mg_owner); cudaFree(ctx->mg_first); cudaFree(ctx->mg_last); cudaFree(ctx->mg_slot_of);
     cudaFree(ctx->p2p_table); cudaFree(ctx->p2p_slot_of); cudaFree(ctx->p2p_overflow);
     cudaFree(ctx->d_legacy);
+    cudaFree(ctx->xml_slab);
     cudaFree(ctx->d_tables);
     if (ctx->s_h2d) { cudaStreamSynchronize(ctx->s_h2d); cudaStreamDestroy(ctx->s_h2d); }
     if (ctx->s_d2h) { cudaStreamSynchronize(ctx->s_d2h); cudaStreamDestroy(ctx->s_d2h); }
@@ -884,6 +895,197 @@ done:
     cudaFree(slab);
     return rc;
 #undef LG_TRY
+}
+
+// ---- XML extraction
+// exclusive prefix sum of n int32 values into n + 1 int64 values (out[n] = total); tmp holds ceil(n/1024)+1 int64
+static void xml_scan_i32(cudaStream_t st, const int32_t* in, int64_t n, int64_t* tmp, int64_t* out) {
+    const int64_t nb = (n + SCAN_ITEMS - 1) / SCAN_ITEMS;
+    k_scan_sums<<<(unsigned)nb, 256, 0, st>>>(in, n, tmp);
+    k_scan_top<<<1, 1024, 0, st>>>(tmp, nb, nullptr);
+    k_scan_apply<<<(unsigned)nb, 256, 0, st>>>(in, n, tmp, out);
+}
+
+extern "C" int smsgate_xml_release(smsgate_ctx* ctx) {
+    if (!ctx) return SMSGATE_E_ARG;
+    if (ctx->xml_slab) {
+        cudaSetDevice(ctx->device);
+        cudaStreamSynchronize(ctx->stream);
+        cudaFree(ctx->xml_slab);
+        cudaFree((void*)ctx->xml_x);
+    }
+    ctx->xml_slab = nullptr;
+    ctx->xml_x = nullptr;
+    ctx->xml_n = ctx->xml_T = ctx->xml_nx = 0;
+    return SMSGATE_OK;
+}
+
+extern "C" int smsgate_xml_scan(smsgate_ctx* ctx, const uint8_t* h_xml, int64_t nbytes, int64_t* n_out,
+                                int64_t* body_bytes, int64_t* sender_bytes, int64_t* err_pos) {
+    if (!ctx) return SMSGATE_E_ARG;
+    if (nbytes < 0 || !n_out || !body_bytes || !sender_bytes || (nbytes > 0 && !h_xml))
+        return fail(ctx, SMSGATE_E_ARG, "xml_scan: bad argument");
+    smsgate_xml_release(ctx);
+    *n_out = *body_bytes = *sender_bytes = 0;
+    if (err_pos) *err_pos = -1;
+    if (nbytes == 0) { if (err_pos) *err_pos = 0; return fail(ctx, SMSGATE_E_XML, "xml: no element found"); }
+    CUDA_TRY(ctx, cudaSetDevice(ctx->device));
+    cudaStream_t st = ctx->stream;
+    const int64_t nchunks = (nbytes + XML_CHUNK - 1) / XML_CHUNK;
+    // stage A: the document and the '<' positions
+    uint8_t* d_x = nullptr;
+    int32_t* d_cnt = nullptr;
+    int64_t *d_off = nullptr, *d_tmp = nullptr;
+    int rc = SMSGATE_OK;
+    cudaError_t e;
+    int64_t T = 0, n = 0, nblocks = 0, tot_body = 0, tot_sender = 0;
+    unsigned long long h_err = ~0ull;
+    int h_roots = 0;
+    uint8_t* slab = nullptr;
+#define XT(expr) if ((e = (expr)) != cudaSuccess) { rc = fail(ctx, SMSGATE_E_CUDA, std::string(#expr) + ": " + cudaGetErrorString(e)); goto done; }
+    XT(cudaMalloc(&d_x, (size_t)nbytes + 64));
+    XT(cudaMalloc(&d_cnt, (size_t)nchunks * 4));
+    XT(cudaMalloc(&d_off, (size_t)(nchunks + 1) * 8));
+    XT(cudaMalloc(&d_tmp, (size_t)(nbytes / SCAN_ITEMS + 1024) * 8));
+    XT(cudaMemcpyAsync(d_x, h_xml, (size_t)nbytes, cudaMemcpyHostToDevice, st));
+    XT(cudaMemsetAsync(d_x + nbytes, 0, 64, st));
+    k_xml_count_lt<<<(unsigned)nchunks, 256, 0, st>>>(d_x, nbytes, d_cnt);
+    xml_scan_i32(st, d_cnt, nchunks, d_tmp, d_off);
+    XT(cudaMemcpyAsync(&T, d_off + nchunks, 8, cudaMemcpyDeviceToHost, st));
+    XT(cudaStreamSynchronize(st));
+    ctx->launches += 4;
+    if (T == 0) { if (err_pos) *err_pos = 0; rc = fail(ctx, SMSGATE_E_XML, "xml: not well-formed (no markup)"); goto done; }
+    {
+        // one slab for everything sized by T
+        auto al = [](size_t b) { return (b + 255) & ~(size_t)255; };
+        const size_t need = al((T + 1) * 8) * 5 + al(T * 4) * 5 + al(T) + al((T + 1) * 8) * 2 + 4096;
+        XT(cudaMalloc(&slab, need));
+        uint8_t* p = slab;
+        auto take = [&](size_t b) { uint8_t* q = p; p += al(b); return q; };
+        int64_t* tag_pos = (int64_t*)take((T + 1) * 8);
+        int64_t* tag_end = (int64_t*)take((T + 1) * 8);
+        int64_t* depth = (int64_t*)take((T + 1) * 8);
+        int64_t* sel_off = (int64_t*)take((T + 1) * 8);
+        int64_t* blk_off = (int64_t*)take((T + 1) * 8);
+        int32_t* name_off = (int32_t*)take(T * 4);
+        int32_t* name_len = (int32_t*)take(T * 4);
+        int32_t* delta = (int32_t*)take(T * 4);
+        int32_t* is_sms = (int32_t*)take(T * 4);
+        int32_t* is_block = (int32_t*)take(T * 4);
+        uint8_t* kind = take(T);
+        int64_t* sms_tag = (int64_t*)take((T + 1) * 8);
+        int64_t* blocks = (int64_t*)take((T + 1) * 8);
+        unsigned long long* d_err = (unsigned long long*)take(16);
+        int* d_roots = (int*)take(16);
+        XT(cudaMemsetAsync(d_err, 0xFF, 8, st));
+        XT(cudaMemsetAsync(d_roots, 0, 4, st));
+        k_xml_write_lt<<<(unsigned)nchunks, 256, 0, st>>>(d_x, nbytes, d_off, tag_pos);
+        XmlTags G{tag_pos, tag_end, name_off, name_len, kind, delta, is_sms, is_block};
+        const unsigned gt = (unsigned)((T + 127) / 128);
+        k_xml_parse_tags<<<gt, 128, 0, st>>>(d_x, nbytes, T, G, d_err);
+        xml_scan_i32(st, delta, T, d_tmp, depth);
+        k_xml_structure<<<gt, 128, 0, st>>>(d_x, nbytes, T, G, depth, d_err, d_roots);
+        xml_scan_i32(st, is_sms, T, d_tmp, sel_off);
+        xml_scan_i32(st, is_block, T, d_tmp, blk_off);
+        k_xml_compact<<<(unsigned)((T + 255) / 256), 256, 0, st>>>(T, is_sms, sel_off, sms_tag);
+        k_xml_compact<<<(unsigned)((T + 255) / 256), 256, 0, st>>>(T, is_block, blk_off, blocks);
+        XT(cudaMemcpyAsync(&n, sel_off + T, 8, cudaMemcpyDeviceToHost, st));
+        XT(cudaMemcpyAsync(&nblocks, blk_off + T, 8, cudaMemcpyDeviceToHost, st));
+        XT(cudaStreamSynchronize(st));
+        k_xml_match_names<<<1, 32, 0, st>>>(d_x, G, blocks, nblocks, d_err);
+        XT(cudaMemcpyAsync(&h_err, d_err, 8, cudaMemcpyDeviceToHost, st));
+        XT(cudaMemcpyAsync(&h_roots, d_roots, 4, cudaMemcpyDeviceToHost, st));
+        XT(cudaStreamSynchronize(st));
+        ctx->launches += 16;
+        if (h_err != ~0ull) {
+            if (err_pos) *err_pos = (int64_t)(h_err >> 2);
+            const bool unsup = (h_err & 3) == XML_UNSUPPORTED;
+            rc = fail(ctx, unsup ? SMSGATE_E_UNSUPPORTED : SMSGATE_E_XML,
+                      std::string(unsup ? "xml: construct outside the supported dialect at byte " : "xml: not well-formed at byte ") +
+                          std::to_string((long long)(h_err >> 2)));
+            goto done;
+        }
+        if (h_roots != 1) { if (err_pos) *err_pos = 0; rc = fail(ctx, SMSGATE_E_XML, "xml: not exactly one root element"); goto done; }
+        // stage B: per-message sizes, offsets
+        uint8_t* slab2 = nullptr;
+        const size_t need2 = al((n + 1) * 4) * 2 + al((n + 1) * 8) * 3 + al(n + 1) + 1024;
+        XT(cudaMalloc(&slab2, need2 + need));            // what smsgate_xml_emit needs outlives this call
+        ctx->xml_slab = slab2;
+        {
+            uint8_t* q = slab2;
+            auto take2 = [&](size_t b) { uint8_t* r = q; q += al(b); return r; };
+            int32_t* body_len = (int32_t*)take2((n + 1) * 4);
+            int32_t* sender_len = (int32_t*)take2((n + 1) * 4);
+            int64_t* date_ms = (int64_t*)take2((n + 1) * 8);
+            int64_t* body_off = (int64_t*)take2((n + 1) * 8);
+            int64_t* sender_off = (int64_t*)take2((n + 1) * 8);
+            uint8_t* mflags = take2(n + 1);
+            // carry over the tag arrays emit needs
+            int64_t* k_pos = (int64_t*)take2((T + 1) * 8);
+            int64_t* k_end = (int64_t*)take2((T + 1) * 8);
+            int64_t* k_sms = (int64_t*)take2((n + 1) * 8);
+            int32_t* k_noff = (int32_t*)take2(T * 4);
+            int32_t* k_nlen = (int32_t*)take2(T * 4);
+            uint8_t* k_kind = take2(T);
+            XT(cudaMemcpyAsync(k_pos, tag_pos, T * 8, cudaMemcpyDeviceToDevice, st));
+            XT(cudaMemcpyAsync(k_end, tag_end, T * 8, cudaMemcpyDeviceToDevice, st));
+            XT(cudaMemcpyAsync(k_sms, sms_tag, (n > 0 ? n : 1) * 8, cudaMemcpyDeviceToDevice, st));
+            XT(cudaMemcpyAsync(k_noff, name_off, T * 4, cudaMemcpyDeviceToDevice, st));
+            XT(cudaMemcpyAsync(k_nlen, name_len, T * 4, cudaMemcpyDeviceToDevice, st));
+            XT(cudaMemcpyAsync(k_kind, kind, T, cudaMemcpyDeviceToDevice, st));
+            XmlTags K{k_pos, k_end, k_noff, k_nlen, k_kind, nullptr, nullptr, nullptr};
+            XmlSms S{body_len, sender_len, date_ms, mflags};
+            if (n > 0) {
+                k_xml_sms_sizes<<<(unsigned)((n + 127) / 128), 128, 0, st>>>(d_x, n, k_sms, K, ctx->d_tables, S);
+                xml_scan_i32(st, body_len, n, d_tmp, body_off);
+                xml_scan_i32(st, sender_len, n, d_tmp, sender_off);
+                XT(cudaMemcpyAsync(&tot_body, body_off + n, 8, cudaMemcpyDeviceToHost, st));
+                XT(cudaMemcpyAsync(&tot_sender, sender_off + n, 8, cudaMemcpyDeviceToHost, st));
+                ctx->launches += 7;
+            }
+            XT(cudaStreamSynchronize(st));
+            XT(cudaGetLastError());
+            ctx->xml_n = n; ctx->xml_T = T; ctx->xml_nx = nbytes;
+            ctx->xml_tag_pos = k_pos; ctx->xml_end = k_end; ctx->xml_sms_tag = k_sms; ctx->xml_name_off = k_noff;
+            ctx->xml_name_len = k_nlen; ctx->xml_kind = k_kind; ctx->xml_body_off = body_off; ctx->xml_sender_off = sender_off;
+            ctx->xml_date_ms = date_ms; ctx->xml_mflags = mflags;
+            // the document stays resident for emit: park it behind the slab pointer bookkeeping
+            ctx->xml_x = d_x;
+            d_x = nullptr;
+        }
+        *n_out = n; *body_bytes = tot_body; *sender_bytes = tot_sender;
+    }
+done:
+    cudaFree(slab); cudaFree(d_cnt); cudaFree(d_off); cudaFree(d_tmp); cudaFree(d_x);
+    if (rc) { cudaFree(ctx->xml_slab); ctx->xml_slab = nullptr; ctx->xml_n = 0; }
+    return rc;
+#undef XT
+}
+
+extern "C" int smsgate_xml_emit(smsgate_ctx* ctx, uint8_t* d_body_bytes, int64_t* d_body_offsets, uint8_t* d_sender_bytes,
+                                int64_t* d_sender_offsets, int64_t* d_date_ms, uint8_t* d_mflags) {
+    if (!ctx) return SMSGATE_E_ARG;
+    if (!ctx->xml_slab) return fail(ctx, SMSGATE_E_STATE, "xml_emit: no pending smsgate_xml_scan");
+    const int64_t n = ctx->xml_n;
+    if (!d_body_offsets || !d_sender_offsets || !d_date_ms || !d_mflags) return fail(ctx, SMSGATE_E_ARG, "xml_emit: NULL array");
+    CUDA_TRY(ctx, cudaSetDevice(ctx->device));
+    cudaStream_t st = ctx->stream;
+    if (n > 0) {
+        XmlTags K{ctx->xml_tag_pos, ctx->xml_end, ctx->xml_name_off, ctx->xml_name_len, ctx->xml_kind, nullptr, nullptr, nullptr};
+        k_xml_sms_emit<<<(unsigned)((n + 127) / 128), 128, 0, st>>>(ctx->xml_x, n, ctx->xml_sms_tag, K, ctx->xml_body_off,
+                                                                    ctx->xml_sender_off, d_body_bytes, d_sender_bytes);
+        ctx->launches += 1;
+        CUDA_TRY(ctx, cudaMemcpyAsync(d_body_offsets, ctx->xml_body_off, (size_t)(n + 1) * 8, cudaMemcpyDeviceToDevice, st));
+        CUDA_TRY(ctx, cudaMemcpyAsync(d_sender_offsets, ctx->xml_sender_off, (size_t)(n + 1) * 8, cudaMemcpyDeviceToDevice, st));
+        CUDA_TRY(ctx, cudaMemcpyAsync(d_date_ms, ctx->xml_date_ms, (size_t)n * 8, cudaMemcpyDeviceToDevice, st));
+        CUDA_TRY(ctx, cudaMemcpyAsync(d_mflags, ctx->xml_mflags, (size_t)n, cudaMemcpyDeviceToDevice, st));
+    } else {
+        CUDA_TRY(ctx, cudaMemsetAsync(d_body_offsets, 0, 8, st));
+        CUDA_TRY(ctx, cudaMemsetAsync(d_sender_offsets, 0, 8, st));
+    }
+    CUDA_TRY(ctx, cudaStreamSynchronize(st));
+    CUDA_TRY(ctx, cudaGetLastError());
+    return smsgate_xml_release(ctx);
 }
 
 // ---- stages

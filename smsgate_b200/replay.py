@@ -25,6 +25,11 @@ from .gemini_cache import CacheTable, build_table, pack_datetime, unpack_datetim
 from .models import BrokenMessage, ParsedSMS
 
 
+class UnsupportedXML(RuntimeError):
+    """The backup uses an XML construct outside the dialect the GPU tokenizer covers
+    (DOCTYPE, CDATA, a non-UTF-8 encoding, '<' inside a comment)."""
+
+
 class CacheMiss(RuntimeError):
     """The body is not in the Gemini response cache; the reference would call
     Gemini here (libs/gemini_parser.py:210-222), which is out of scope offline."""
@@ -245,6 +250,35 @@ class ReplayEngine:
             exchange.run_outputs(view, n, int(base_index))
             L.check(self._ctx, self._lib.smsgate_replay_host_finish(self._ctx, C.byref(out)))
         return ReplayResult(batch, cols, self.table, base_index)
+
+    def xml_extract(self, data) -> dict:
+        """Tokenize an XML backup (bytes / uint8 array) on the GPU.  Returns device tensors
+        body_bytes, body_offsets, sender_bytes, sender_offsets, date_ms, mflags (+ n).
+        Raises xml.etree.ElementTree.ParseError where ElementTree would, UnsupportedXML for
+        constructs outside the dialect."""
+        import torch
+        import xml.etree.ElementTree as ET
+        buf = np.frombuffer(data, dtype=np.uint8) if not isinstance(data, np.ndarray) else data
+        n, nb, ns, pos = C.c_int64(0), C.c_int64(0), C.c_int64(0), C.c_int64(-1)
+        rc = self._lib.smsgate_xml_scan(self._ctx, _np_ptr(buf) if buf.size else None, int(buf.size), C.byref(n),
+                                        C.byref(nb), C.byref(ns), C.byref(pos))
+        if rc == L.E_XML:
+            raise ET.ParseError(f"not well-formed near byte {pos.value}")
+        if rc == L.E_UNSUPPORTED:
+            raise UnsupportedXML((self._lib.smsgate_last_error(self._ctx) or b"").decode())
+        L.check(self._ctx, rc)
+        dev = torch.device("cuda", self.device)
+        out = dict(n=n.value,
+                   body_bytes=torch.empty(nb.value + 64, dtype=torch.uint8, device=dev),
+                   body_offsets=torch.empty(n.value + 1, dtype=torch.int64, device=dev),
+                   sender_bytes=torch.empty(ns.value + 64, dtype=torch.uint8, device=dev),
+                   sender_offsets=torch.empty(n.value + 1, dtype=torch.int64, device=dev),
+                   date_ms=torch.empty(max(n.value, 1), dtype=torch.int64, device=dev),
+                   mflags=torch.empty(max(n.value, 1), dtype=torch.uint8, device=dev))
+        L.check(self._ctx, self._lib.smsgate_xml_emit(self._ctx, out["body_bytes"].data_ptr(), out["body_offsets"].data_ptr(),
+                                                      out["sender_bytes"].data_ptr(), out["sender_offsets"].data_ptr(),
+                                                      out["date_ms"].data_ptr(), out["mflags"].data_ptr()))
+        return out
 
     def msg_ids(self, batch: Batch) -> np.ndarray:
         """SHA-1(body) of every message: the XML idempotency key (watcher.py:45).  uint8 [n, 20]."""

@@ -82,3 +82,19 @@ def legacy(bodies):
     lib().hc_legacy(C.c_int64(n), _p(offsets), _p(data), _p(cols["status"]), _p(cols["lflags"]), _p(cols["strip"]),
                     _p(cols["caps"]), _p(cols["amount"]), _p(cols["balance"]), _p(cols["body_hash"]))
     return cols
+
+
+def xml_extract(data: bytes):
+    """(code, bodies, senders, date_ms, mflags) from the CPU build of the XML tokenizer logic."""
+    x = np.frombuffer(data + b"\0" * 16, dtype=np.uint8)
+    nx = len(data)
+    cap = nx + 16
+    n = C.c_int64(0)
+    bb, sb = np.zeros(cap, np.uint8), np.zeros(cap, np.uint8)
+    bo, so, dm = np.zeros(cap // 8 + 2, np.int64), np.zeros(cap // 8 + 2, np.int64), np.zeros(cap // 8 + 2, np.int64)
+    mf = np.zeros(cap // 8 + 2, np.uint8)
+    rc = lib().hc_xml_extract(_p(x), C.c_int64(nx), C.byref(n), _p(bb), _p(bo), _p(sb), _p(so), _p(dm), _p(mf))
+    k = n.value
+    bodies = [bb[bo[i]:bo[i + 1]].tobytes().decode() for i in range(k)]
+    senders = [sb[so[i]:so[i + 1]].tobytes().decode() for i in range(k)]
+    return rc, bodies, senders, dm[:k].tolist(), mf[:k].tolist()

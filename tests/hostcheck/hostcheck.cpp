@@ -12,6 +12,7 @@
 #include "join_core.cuh"
 #include "legacy_core.cuh"
 #include "scan_core.cuh"
+#include "xml_core.cuh"
 
 static ScanTables host_tables() {
     static DeviceTables tab;
@@ -119,5 +120,89 @@ extern "C" int hc_legacy(int64_t n, const int64_t* offsets, const uint8_t* bytes
         amount[i] = r.amount; balance[i] = r.balance;
         put_be(body_hash + i * 32, r.digest, 8);
     }
+    return 0;
+}
+
+// Sequential stand-in for the XML extraction kernels (xml_extract.cuh): same per-tag functions,
+// same checks, in document order.  Returns 0 ok, 1 malformed, 2 unsupported; *n = messages.
+extern "C" int hc_xml_extract(const uint8_t* x, int64_t nx, int64_t* n_out, uint8_t* body_bytes, int64_t* body_off,
+                              uint8_t* sender_bytes, int64_t* sender_off, int64_t* date_ms, uint8_t* mflags) {
+    const ScanTables ST = host_tables();
+    std::vector<int64_t> pos;
+    for (int64_t i = 0; i < nx; ++i) if (x[i] == '<') pos.push_back(i);
+    const int64_t T = (int64_t)pos.size();
+    *n_out = 0;
+    if (T == 0) return 1;
+    std::vector<XmlTag> tags(T);
+    int worst = 0;
+    int64_t worst_pos = nx + 1;
+    auto report = [&](int64_t p, int code) { if (p < worst_pos) { worst_pos = p; worst = code; } };
+    for (int64_t t = 0; t < T; ++t) {
+        tags[t] = xml_parse_tag(x, nx, pos[t], t + 1 < T ? pos[t + 1] : nx);
+        if (tags[t].err) report(pos[t], tags[t].err);
+    }
+    std::vector<int64_t> depth(T + 1, 0);
+    for (int64_t t = 0; t < T; ++t) depth[t + 1] = depth[t] + (tags[t].kind == XT_OPEN ? 1 : tags[t].kind == XT_CLOSE ? -1 : 0);
+    int roots = 0;
+    std::vector<int64_t> sms, stack;
+    for (int64_t t = 0; t < T; ++t) {
+        const int kind = tags[t].kind;
+        if (kind == XT_CLOSE && depth[t] <= 0) report(pos[t], XML_MALFORMED);
+        if ((kind == XT_OPEN || kind == XT_SELFCLOSE) && depth[t] == 0) ++roots;
+        if ((kind == XT_OPEN || kind == XT_SELFCLOSE) && depth[t] == 1 && tags[t].name_len == 3 &&
+            memcmp(x + pos[t] + tags[t].name_off, "sms", 3) == 0) sms.push_back(t);
+        const int64_t a = tags[t].end + 1, b = t + 1 < T ? pos[t + 1] : nx;
+        if (a < b && xml_check_text(x, a, b, depth[t + 1] == 0) != XML_OK) report(a, XML_MALFORMED);
+        if (t == 0) {
+            int64_t p = 0;
+            if (pos[0] >= 3 && x[0] == 0xEF && x[1] == 0xBB && x[2] == 0xBF) p = 3;
+            if (xml_check_text(x, p, pos[0], true) != XML_OK) report(p, XML_MALFORMED);
+        }
+        if (xml_misplaced_decl(x, pos[t], tags[t].end, kind)) report(pos[t], XML_MALFORMED);
+        if (t == T - 1 && depth[t + 1] != 0) report(nx, XML_MALFORMED);
+        if (!tags[t].err && kind == XT_OPEN) stack.push_back(t);
+        if (!tags[t].err && kind == XT_CLOSE) {
+            if (stack.empty()) report(pos[t], XML_MALFORMED);
+            else {
+                const int64_t o = stack.back(); stack.pop_back();
+                const int64_t a0 = pos[o] + tags[o].name_off, b0 = pos[t] + tags[t].name_off;
+                if (!xml_span_eq(x, a0, a0 + tags[o].name_len, b0, b0 + tags[t].name_len)) report(pos[t], XML_MALFORMED);
+            }
+        }
+    }
+    if (worst) return worst;
+    if (roots != 1) return 1;
+    int64_t bo = 0, so = 0;
+    for (size_t i = 0; i < sms.size(); ++i) {
+        const int64_t t = sms[i], lim = tags[t].end + 1;
+        int64_t p = pos[t] + tags[t].name_off + tags[t].name_len;
+        bool first = true;
+        uint32_t fl = 0;
+        int64_t bl = 0, sl = 0, dms = 0;
+        for (;;) {
+            XmlAttr a;
+            const int r = xml_next_attr(x, &p, lim, &a, first);
+            if (r <= 0) break;
+            first = false;
+            if (xml_span_is(x, a.name, a.name_end, "body", 4)) { xml_attr_value(x, a.val, lim, a.quote, body_bytes + bo, &bl); fl |= 1; }
+            else if (xml_span_is(x, a.name, a.name_end, "address", 7)) { xml_attr_value(x, a.val, lim, a.quote, sender_bytes + so, &sl); fl |= 2; }
+            else if (xml_span_is(x, a.name, a.name_end, "date", 4)) {
+                int64_t dl = 0;
+                xml_attr_value(x, a.val, lim, a.quote, nullptr, &dl);
+                uint8_t buf[96];
+                if (dl > 96) fl |= 4;
+                else {
+                    xml_attr_value(x, a.val, lim, a.quote, buf, &dl);
+                    const int ok = xml_python_int(buf, (int)dl, ST.t->digit_run_start, ST.t->digit_run_len, &dms);
+                    if (ok == 0) fl |= 4;
+                    if (ok == 2) fl |= 8;
+                }
+            }
+        }
+        body_off[i] = bo; sender_off[i] = so; date_ms[i] = dms; mflags[i] = (uint8_t)fl;
+        bo += bl; so += sl;
+    }
+    body_off[sms.size()] = bo; sender_off[sms.size()] = so;
+    *n_out = (int64_t)sms.size();
     return 0;
 }

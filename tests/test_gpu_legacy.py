@@ -107,3 +107,57 @@ def test_parse_and_cache_sms(tmp_path):
         assert len(c) == 300
         assert c.get(str(backup.date_ms[7]))["body"] == backup.bodies[7].replace("\n", "\n")
     assert xml_ingest.parse_and_cache_sms(str(tmp_path / "missing.xml"), str(tmp_path / "c2")) is None
+
+
+def test_xml_tokenizer_on_gpu_matches_elementtree(engine):
+    """smsgate_xml_scan / _emit against ElementTree on the shared documents (synthetic backups, the
+    SMS Backup & Restore prolog, malformed and out-of-dialect files, 1 500 mutated documents)."""
+    import xml.etree.ElementTree as ET
+
+    from smsgate_b200.replay import UnsupportedXML
+    from tests._xml_cases import documents
+    from tests.test_xml_logic_on_cpu import compare
+    n_unsup = 0
+    docs = documents()
+    for data in docs:
+        try:
+            d = engine.xml_extract(data)
+        except ET.ParseError:
+            res = (1, [], [], [], [])
+        except UnsupportedXML:
+            res = (2, [], [], [], [])
+        else:
+            n = d["n"]
+            off, soff = d["body_offsets"].cpu().numpy(), d["sender_offsets"].cpu().numpy()
+            bb, sb = d["body_bytes"].cpu().numpy(), d["sender_bytes"].cpu().numpy()
+            res = (0, [bb[off[i]:off[i + 1]].tobytes().decode() for i in range(n)],
+                   [sb[soff[i]:soff[i + 1]].tobytes().decode() for i in range(n)],
+                   d["date_ms"].cpu().numpy()[:n].tolist(), d["mflags"].cpu().numpy()[:n].tolist())
+        n_unsup += compare(res, data) == "unsupported"
+    assert n_unsup < len(docs) * 0.2
+
+
+def test_xml_to_replay_on_device(engine, tmp_path):
+    """A 50 000-message backup: XML bytes -> GPU tokenizer -> replay kernels without the bodies ever
+    visiting the host, equal to the host-parsed replay."""
+    import datetime as dt
+
+    import torch
+
+    from smsgate_b200.batch import Batch
+    now = dt.datetime(2026, 1, 1)
+    backup = synth.generate(50000, seed=8, mixed_locale=True, dup_frac=0.1)
+    p = tmp_path / "big.xml"
+    synth.write_xml(str(p), backup)
+    engine.load_cache(backup.cache)
+    host = engine.replay(xml_ingest.read_backup(p), now)
+    d = engine.xml_extract(np.fromfile(str(p), dtype=np.uint8))
+    assert d["n"] == 50000
+    total = int(d["body_offsets"][-1])
+    cols = engine.device_columns(d["n"], total)
+    engine.reserve(d["n"], total)
+    engine.replay_device(d["body_bytes"], d["body_offsets"], now, cols)
+    torch.cuda.synchronize()
+    for name in ("msg_id", "cache_key", "status", "survivor", "amount_coef", "date"):
+        assert np.array_equal(cols[name].cpu().numpy(), host.cols[name]), name
+    assert np.array_equal(d["date_ms"].cpu().numpy(), np.array(backup.date_ms))
