@@ -487,7 +487,45 @@ SG_HD void sg_sha1_sha256(const uint8_t* m, int len, uint32_t h1[5], uint32_t h2
     }
 }
 
+// One walk over a byte string feeding SHA-1 (mode bit 0) and / or SHA-256 (mode bit 1); a digest whose bit
+// is clear is left untouched.  The scan kernel has exactly one inlined copy of this loop and runs it once
+// for an untouched body (mode 3) and twice for a rewritten one (mode 1 before the rewrite, mode 2 after):
+// the hashing code is most of the kernel's instruction footprint, and one copy stays in the instruction cache.
+SG_HD void sg_hash_pass(const uint8_t* m, int len, uint32_t mode, uint32_t h1[5], uint32_t h2[8]) {
+    if (mode & 1u) {
+        h1[0] = 0x67452301u; h1[1] = 0xEFCDAB89u; h1[2] = 0x98BADCFEu; h1[3] = 0x10325476u; h1[4] = 0xC3D2E1F0u;
+    }
+    if (mode & 2u) {
+        h2[0] = 0x6a09e667u; h2[1] = 0xbb67ae85u; h2[2] = 0x3c6ef372u; h2[3] = 0xa54ff53au;
+        h2[4] = 0x510e527fu; h2[5] = 0x9b05688cu; h2[6] = 0x1f83d9abu; h2[7] = 0x5be0cd19u;
+    }
+    WordReader R;
+    R.init(m);
+    const int nblk = sg_sha_blocks(len), nwords = nblk * 16;
+#if defined(__CUDACC__)
+#pragma unroll 1
+#endif
+    for (int blk = 0; blk < nblk; ++blk) {
+        uint32_t w[16], v[16];
+        if ((blk + 1) * 64 <= len) {
+#pragma unroll
+            for (int j = 0; j < 16; ++j) w[j] = R.be(blk * 16 + j);
+        } else {
+#pragma unroll
+            for (int j = 0; j < 16; ++j) w[j] = sg_padded_word(R, len, blk * 16 + j, nwords);
+        }
+#pragma unroll
+        for (int j = 0; j < 16; ++j) v[j] = w[j];
+        if (mode & 1u) sg_sha1_compress(h1, w);
+        if (mode & 2u) sg_sha256_compress(h2, v);
+    }
+}
+
 #if defined(__CUDACC__)
 __host__ __device__ __noinline__
 #endif
 static void sg_sha256_outofline(const uint8_t* m, int len, uint32_t h[8]) { sg_sha256(m, len, h); }
+#if defined(__CUDACC__)
+__host__ __device__ __noinline__
+#endif
+static void sg_sha1_outofline(const uint8_t* m, int len, uint32_t h[5]) { sg_sha1(m, len, h); }

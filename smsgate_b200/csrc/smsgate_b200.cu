@@ -66,12 +66,13 @@ struct __align__(16) K1Smem {
     uint64_t mbar;
     int32_t m_off[K1_TILE];               // start of message t inside `stage`
     int32_t m_len[K1_TILE];               // body length
-    int32_t m_flen[K1_TILE];              // fixed_body length
     int32_t hist[K1_BUCKETS];
     int32_t cursor[K1_BUCKETS];
     uint16_t order[K1_TILE];              // tile-local message ids sorted by length bucket
-    uint16_t modlist[K1_TILE];            // messages whose body the clean/mask step changes
-    int32_t nmod;
+    uint16_t work[K1_TILE];               // hashing order: rewritten bodies first, each group longest first
+    uint8_t mod[K1_TILE];                 // 1 = the clean/mask step changes this body
+    int32_t pcnt[2 * K1_THREADS / 32];    // per warp and half: rewritten | untouched << 16
+    int32_t next;                         // next 32-message chunk to hash
 };
 
 struct ScanOut {
@@ -83,14 +84,16 @@ struct ScanOut {
     uint8_t* fixed_bytes;
 };
 
-__device__ __forceinline__ void k1_store_id(const ScanOut& o, int64_t i, const uint32_t h1[5], const ScanResult& sr) {
+__device__ __forceinline__ void k1_store_scan(const ScanOut& o, int64_t i, const ScanResult& sr) {
+    if (o.flags) o.flags[i] = (uint8_t)sr.flags;
+    if (o.body_date) o.body_date[i] = sr.body_date;
+}
+__device__ __forceinline__ void k1_store_id(const ScanOut& o, int64_t i, const uint32_t h1[5]) {
     if (o.msg_id) {
         uint32_t* p = (uint32_t*)(o.msg_id + i * 20);
 #pragma unroll
         for (int k = 0; k < 5; ++k) p[k] = __byte_perm(h1[k], 0, 0x0123);
     }
-    if (o.flags) o.flags[i] = (uint8_t)sr.flags;
-    if (o.body_date) o.body_date[i] = sr.body_date;
 }
 __device__ __forceinline__ void k1_store_key(const ScanOut& o, int64_t i, const uint32_t h2[8], int flen) {
     if (o.cache_key) {
@@ -111,7 +114,7 @@ __device__ __noinline__ void k1_giant(const uint8_t* bytes, int64_t lo, int64_t 
     const int len = (int)(hi - lo);
     ScanResult sr = sg_scan_body(m, len, T);
     uint32_t h1[5], h2[8];
-    sg_sha1(m, len, h1);
+    sg_sha1_outofline(m, len, h1);
     int flen = len;
     const uint8_t* fm = m;
     if ((sr.flags & SG_F_MODIFIED) && out.fixed_bytes) {
@@ -121,7 +124,8 @@ __device__ __noinline__ void k1_giant(const uint8_t* bytes, int64_t lo, int64_t 
         fm = w;
     }
     sg_sha256_outofline(fm, flen, h2);
-    k1_store_id(out, msg, h1, sr);
+    k1_store_scan(out, msg, sr);
+    k1_store_id(out, msg, h1);
     k1_store_key(out, msg, h2, flen);
 }
 
@@ -171,7 +175,7 @@ k_scan_keys(const uint8_t* __restrict__ bytes, const int64_t* __restrict__ offse
                 nfit += fits[h] ? 1 : 0;
             }
             if (tid < K1_BUCKETS) S.hist[tid] = 0;
-            if (tid == 0) S.nmod = 0;
+            if (tid == 0) S.next = 0;
             // the first half is a prefix of the tile, so the count of fitting messages is exact
             // only if the second half is counted after the first: do two block-wide counts
             const int cnt0 = __syncthreads_count(fits[0]);
@@ -207,7 +211,6 @@ k_scan_keys(const uint8_t* __restrict__ bytes, const int64_t* __restrict__ offse
                     const int len = (int)(my_hi[h] - my_lo[h]);
                     S.m_off[loc] = (int)(my_lo[h] - base);
                     S.m_len[loc] = len;
-                    S.m_flen[loc] = len;
                     int k = len >> 3;
                     k = k < K1_BUCKETS - 1 ? k : K1_BUCKETS - 1;
                     key[h] = k;
@@ -242,48 +245,98 @@ k_scan_keys(const uint8_t* __restrict__ bytes, const int64_t* __restrict__ offse
             }
             __syncthreads();
 
-            // thread `tid` owns rank tid (short half) and rank cnt-1-tid (long half): every warp gets one
-            // group of short and one group of long bodies, so warps finish each phase at about the same time
+            // ---- phase S: the scans.  Thread `tid` owns rank tid (short half) and rank cnt-1-tid (long half):
+            //      every warp gets one group of short and one group of long bodies.
             const int half = (cnt + 1) >> 1;
             int rk[2];
             rk[0] = tid < half ? tid : -1;
             rk[1] = tid < cnt - half ? cnt - 1 - tid : -1;
-            // ---- phase A: scans, then SHA-1 and SHA-256 of the body in one walk.  For the bodies that
-            //      clean/mask changes the SHA-256 is discarded and redone in phase B.
 #pragma unroll 1
             for (int h = 0; h < 2; ++h) {
                 if (rk[h] < 0) continue;
                 const int t = S.order[rk[h]];
-                const uint8_t* m = S.stage + S.m_off[t];
-                const int len = S.m_len[t];
-                const ScanResult sr = sg_scan_body(m, len, T);
+                const ScanResult sr = sg_scan_body(S.stage + S.m_off[t], S.m_len[t], T);
+                k1_store_scan(out, s + t, sr);
+                S.mod[t] = (sr.flags & SG_F_MODIFIED) ? 1 : 0;
+            }
+            __syncthreads();
+            // ---- hashing order: the bodies clean/mask changes first (they cost SHA-1 + rewrite + SHA-256 of
+            //      the result), then the untouched ones (both digests in one walk), each group longest first,
+            //      so that a 32-message chunk is one kind of work and the dearest chunks start first
+            const int lane = tid & 31, wrp = tid >> 5;
+            int wt[2];
+            uint32_t balM[2], balU[2];
+#pragma unroll
+            for (int h = 0; h < 2; ++h) {
+                const int q = tid + h * K1_THREADS;
+                const bool valid = q < cnt;
+                wt[h] = valid ? S.order[cnt - 1 - q] : 0;
+                const bool isM = valid && S.mod[wt[h]];
+                balM[h] = __ballot_sync(0xffffffffu, isM);
+                balU[h] = __ballot_sync(0xffffffffu, valid && !isM);
+                if (lane == 0) S.pcnt[h * (K1_THREADS / 32) + wrp] = __popc(balM[h]) | (__popc(balU[h]) << 16);
+            }
+            __syncthreads();
+            int nM = 0;
+            {
+                int pre[2] = {0, 0};
+#pragma unroll
+                for (int k = 0; k < 2 * K1_THREADS / 32; ++k) {
+                    const int c = S.pcnt[k];
+                    if (k < wrp) pre[0] += c;
+                    if (k < K1_THREADS / 32 + wrp) pre[1] += c;
+                    nM += c & 0xFFFF;
+                }
+                const uint32_t lt = (1u << lane) - 1u;
+#pragma unroll
+                for (int h = 0; h < 2; ++h) {
+                    const int q = tid + h * K1_THREADS;
+                    if (q < cnt) {
+                        const bool isM = (balM[h] >> lane) & 1u;
+                        const int pos = isM ? (pre[h] & 0xFFFF) + __popc(balM[h] & lt)
+                                            : nM + (pre[h] >> 16) + __popc(balU[h] & lt);
+                        S.work[pos] = (uint16_t)wt[h];
+                    }
+                }
+            }
+            __syncthreads();
+            // ---- phase H: warps pull chunks until none is left
+            const int nchM = (nM + 31) >> 5, nchU = (cnt - nM + 31) >> 5;
+#pragma unroll 1
+            for (;;) {
+                int c = 0;
+                if (lane == 0) c = atomicAdd(&S.next, 1);
+                c = __shfl_sync(0xffffffffu, c, 0);
+                if (c >= nchM + nchU) break;
+                const bool isM = c < nchM;
+                const int idx = isM ? c * 32 + lane : nM + (c - nchM) * 32 + lane;
+                const bool act = idx < (isM ? nM : cnt);
+                const int t = act ? S.work[idx] : 0;
+                const int off = S.m_off[t];
+                const int len = act ? S.m_len[t] : 0;
+                uint8_t* m = S.stage + off;
                 uint32_t h1[5], h2[8];
-                sg_sha1_sha256(m, len, h1, h2);
-                k1_store_id(out, s + t, h1, sr);
-                if (sr.flags & SG_F_MODIFIED) S.modlist[atomicAdd(&S.nmod, 1)] = (uint16_t)t;
-                else k1_store_key(out, s + t, h2, len);
-            }
-            __syncthreads();
-            // ---- phase B: clean + mask in place and SHA-256 of the result, compacted onto the first lanes
-            const int nmod = S.nmod;
-            for (int j = tid; j < nmod; j += K1_THREADS) {
-                const int u = S.modlist[j];
-                uint8_t* m = S.stage + S.m_off[u];
-                const int flen = sg_rewrite_fixed(m, S.m_len[u], T);
-                S.m_flen[u] = flen;
-                uint32_t h2[8];
-                sg_sha256_outofline(m, flen, h2);
-                k1_store_key(out, s + u, h2, flen);
-            }
-            __syncthreads();
-            // ---- phase 4: rewritten bodies -> fixed_bytes at their original offsets, one warp per body
-            if (out.fixed_bytes) {
-                for (int j = tid >> 5; j < nmod; j += K1_THREADS / 32) {
-                    const int u = S.modlist[j];
-                    const int fl = S.m_flen[u];
-                    const uint8_t* src = S.stage + S.m_off[u];
-                    uint8_t* dst = out.fixed_bytes + base + S.m_off[u];
-                    for (int k = tid & 31; k < fl; k += 32) dst[k] = src[k];
+                int cur = len;
+                const int npass = isM ? 2 : 1;
+#pragma unroll 1
+                for (int pass = 0; pass < npass; ++pass) {   // one copy of the hashing loop, see sg_hash_pass
+                    const uint32_t mode = isM ? (pass ? 2u : 1u) : 3u;
+                    if (pass && act) cur = sg_rewrite_fixed(m, len, T);
+                    if (act) sg_hash_pass(m, cur, mode, h1, h2);
+                }
+                if (act) {
+                    k1_store_id(out, s + t, h1);
+                    k1_store_key(out, s + t, h2, cur);
+                }
+                if (isM && out.fixed_bytes) {                // rewritten bodies -> fixed_bytes at their old offsets
+                    __syncwarp();
+                    const int live = min(32, nM - c * 32);
+                    for (int j = 0; j < live; ++j) {
+                        const int o = __shfl_sync(0xffffffffu, off, j), fl = __shfl_sync(0xffffffffu, cur, j);
+                        const uint8_t* src = S.stage + o;
+                        uint8_t* dst = out.fixed_bytes + base + o;
+                        for (int k = lane; k < fl; k += 32) dst[k] = src[k];
+                    }
                 }
             }
             __syncthreads();
