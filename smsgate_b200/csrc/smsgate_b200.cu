@@ -54,9 +54,10 @@ __device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
 }
 
 // ------------------------------------------------------------------ stage 1: keys + scans
-constexpr int K1_THREADS = 128;           // 4 warps
-constexpr int K1_TILE = 256;              // messages per tile: every thread owns one short and one long body
-constexpr int K1_STAGE = 36 * 1024;       // staged body bytes per CTA tile (4 CTAs per SM)
+constexpr int K1_THREADS = 640;           // 4 warps
+constexpr int K1_CTAS_PER_SM = 1;
+constexpr int K1_TILE = 1280;              // messages per tile: every thread owns one short and one long body
+constexpr int K1_STAGE = 176 * 1024;       // staged body bytes per CTA tile (4 CTAs per SM)
 constexpr int K1_PAD = 32;                // slack read by the unaligned word reader
 constexpr int K1_BUCKETS = 128;           // length buckets of 8 bytes for the in-tile sort
 
@@ -129,7 +130,7 @@ __device__ __noinline__ void k1_giant(const uint8_t* bytes, int64_t lo, int64_t 
     k1_store_key(out, msg, h2, flen);
 }
 
-__global__ void __launch_bounds__(K1_THREADS, 4)
+__global__ void __launch_bounds__(K1_THREADS, K1_CTAS_PER_SM)
 k_scan_keys(const uint8_t* __restrict__ bytes, const int64_t* __restrict__ offsets, int64_t n,
             const DeviceTables* __restrict__ gtab, ScanOut out) {
     extern __shared__ __align__(16) uint8_t smem_raw[];
@@ -150,10 +151,13 @@ k_scan_keys(const uint8_t* __restrict__ bytes, const int64_t* __restrict__ offse
     T.t = &S.tab;
 
     uint32_t parity = 0;
-    const int64_t ntiles = (n + K1_TILE - 1) / K1_TILE;
-    for (int64_t tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
-        const int64_t t0 = tile * K1_TILE;
-        const int64_t t1 = (t0 + K1_TILE < n) ? t0 + K1_TILE : n;
+    // every CTA takes an equal contiguous share of the messages and walks it in equal tiles of at most
+    // K1_TILE: all CTAs do the same number of tiles, no tail wave
+    const int64_t r0 = n * (int64_t)blockIdx.x / gridDim.x, r1 = n * ((int64_t)blockIdx.x + 1) / gridDim.x;
+    const int64_t nt = (r1 - r0 + K1_TILE - 1) / K1_TILE;
+    const int64_t per = nt ? (r1 - r0 + nt - 1) / nt : 1;
+    for (int64_t t0 = r0; t0 < r1; t0 += per) {
+        const int64_t t1 = (t0 + per < r1) ? t0 + per : r1;
         int64_t s = t0;
         while (s < t1) {
             // ---- how many messages starting at s fit the staging buffer (offsets are monotone: a prefix)
@@ -1151,7 +1155,7 @@ extern "C" int smsgate_scan_keys(smsgate_ctx* ctx, const uint8_t* d_bytes, const
     CUDA_TRY(ctx, cudaSetDevice(ctx->device));
     ScanOut so{out->msg_id, out->cache_key, out->flags, out->body_date, out->fixed_len, out->fixed_bytes};
     const int64_t ntiles = (n + K1_TILE - 1) / K1_TILE;
-    const int64_t maxgrid = (int64_t)ctx->sm_count * 4;
+    const int64_t maxgrid = (int64_t)ctx->sm_count * K1_CTAS_PER_SM;
     const unsigned grid = (unsigned)(ntiles < maxgrid ? ntiles : maxgrid);
     k_scan_keys<<<grid, K1_THREADS, sizeof(K1Smem), ctx->stream>>>(d_bytes, d_offsets, n, ctx->d_tables, so);
     ctx->launches += 1;
