@@ -274,14 +274,14 @@ def run_ours(args, rank, world, local_rank):
         torch.cuda.synchronize()
         e0, e1 = ev(), ev()
         e0.record()
-        res = eng.replay(hb, NOW, base_index=base_index, columns=RESULT_COLUMNS, pinned=True, exchange=exchange)
+        res = eng.replay_records(hb, NOW, base_index=base_index, pinned=True, exchange=exchange)
         e1.record()
         e1.synchronize()
         if it >= args.warmup:
             e2e_ms.append(e0.elapsed_time(e1))
     clocks = sampler.stop() if rank == 0 else None
     h2d = total + 8 * (n + 1)
-    d2h = int(sum(v.nbytes for v in res.cols.values()))
+    d2h = int(res.cols.nbytes)          # one 64-byte record + one 8-byte dedup verdict per message
     upserts_local = int((res.status == 0).sum())
 
     # ---- max over ranks

@@ -105,6 +105,19 @@ typedef struct smsgate_outputs {
     int64_t* balance_cents; /* [n] same for the balance (db/models.py:27), sign in dec_flags bit 5 */
 } smsgate_outputs;
 
+/* The result of one message as one 64-byte record (smsgate_replay_host_records): the same values as
+ * the columns of the same names in smsgate_outputs.  The fields a consumer of the reference's
+ * parse_sms_llm / upsert path needs per message travel together, which is also how they are read. */
+typedef struct smsgate_record {
+    uint8_t msg_id[20];
+    uint8_t status, flags, dec_flags, card_len;
+    int32_t slot;
+    int32_t amount_exp, balance_exp;
+    int32_t body_date;
+    int64_t amount_coef, balance_coef;
+    int64_t date;
+} smsgate_record;
+
 /* ---- lifecycle ---------------------------------------------------------- */
 int smsgate_abi_version(void);
 /* Create a context on CUDA device `device`.  cuda_stream is the cudaStream_t
@@ -283,6 +296,13 @@ int smsgate_p2p_resolve(smsgate_ctx* ctx, int64_t n, int64_t base_index, const s
  * total_bytes = h_offsets[n].  Needs smsgate_reserve() to have covered n. */
 int smsgate_replay_host(smsgate_ctx* ctx, const uint8_t* h_bytes, const int64_t* h_offsets, int64_t n,
                         int64_t now_packed, int64_t base_index, const smsgate_outputs* h_out);
+
+/* Diagnostics, no counterpart in the reference: where the time of the last smsgate_replay_host()
+ * went.  Fills ms[] with GPU times relative to the start of that call: ms[0..c) = host->device copy
+ * of chunk k complete, ms[c..2c) = kernels of chunk k complete, ms[2c] = dedup complete,
+ * ms[2c+1] = last byte stored to the host buffers.  Returns c (the number of chunks) or a negative
+ * SMSGATE_E_* code; `capacity` must be at least 2c+2 (34 is always enough). */
+int smsgate_replay_host_timeline(smsgate_ctx* ctx, float* ms, int capacity);
 /* The same call in two halves, for a multi-GPU replay that has to run the global
  * dedup exchange on the device-resident columns in between: _begin queues the
  * chunked copy-in, stages 1-3 and the copy-out of every column except survivor /
@@ -293,6 +313,18 @@ int smsgate_replay_host_begin(smsgate_ctx* ctx, const uint8_t* h_bytes, const in
                               int64_t now_packed, int64_t base_index, const smsgate_outputs* h_out);
 int smsgate_device_view(smsgate_ctx* ctx, int64_t n, smsgate_outputs* d_out);
 int smsgate_replay_host_finish(smsgate_ctx* ctx, const smsgate_outputs* h_out);
+
+/* smsgate_replay_host with packed results: h_records[n] receives one smsgate_record per message and
+ * h_verdict[n] the dedup verdict of message i as one integer: -1 when the message is not upserted, else
+ * (last_idx << 2) | (first_seen << 1) | survivor.  Same work, same values as smsgate_replay_host; the
+ * difference is the transport: one device->host transfer per chunk instead of one per column and chunk,
+ * which is what the end-to-end time is sensitive to.  The _begin / _finish halves are for the multi-GPU
+ * exchange, as above.  No counterpart in the reference (it has no batch API). */
+int smsgate_replay_host_records(smsgate_ctx* ctx, const uint8_t* h_bytes, const int64_t* h_offsets, int64_t n,
+                                int64_t now_packed, int64_t base_index, smsgate_record* h_records, int64_t* h_verdict);
+int smsgate_replay_host_records_begin(smsgate_ctx* ctx, const uint8_t* h_bytes, const int64_t* h_offsets, int64_t n,
+                                      int64_t now_packed, int64_t base_index, smsgate_record* h_records);
+int smsgate_replay_host_records_finish(smsgate_ctx* ctx, int64_t* h_verdict);
 
 /* ---- upsert-by-msg_id for callers that must not allocate -------------------
  * No counterpart in the reference (it has no device memory to manage).

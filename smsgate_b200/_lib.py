@@ -44,6 +44,13 @@ COLUMNS = (
 )
 
 
+# struct smsgate_record as a numpy structured dtype (64 bytes, no padding)
+RECORD_FIELDS = [("msg_id", "u1", (20,)), ("status", "u1"), ("flags", "u1"), ("dec_flags", "u1"), ("card_len", "u1"),
+                 ("slot", "<i4"), ("amount_exp", "<i4"), ("balance_exp", "<i4"), ("body_date", "<i4"),
+                 ("amount_coef", "<i8"), ("balance_coef", "<i8"), ("date", "<i8")]
+RECORD_BYTES_OUT = 64
+
+
 class Outputs(C.Structure):
     _fields_ = [(name, C.c_void_p) for name, _, _ in COLUMNS]
 
@@ -98,6 +105,10 @@ def lib():
         "smsgate_dedup": (i32, [vp, i64, i64, C.POINTER(Outputs)]),
         "smsgate_replay_device": (i32, [vp, vp, vp, i64, i64, i64, C.POINTER(Outputs)]),
         "smsgate_replay_host": (i32, [vp, vp, vp, i64, i64, i64, C.POINTER(Outputs)]),
+        "smsgate_replay_host_records": (i32, [vp, vp, vp, i64, i64, i64, vp, vp]),
+        "smsgate_replay_host_records_begin": (i32, [vp, vp, vp, i64, i64, i64, vp]),
+        "smsgate_replay_host_records_finish": (i32, [vp, vp]),
+        "smsgate_replay_host_timeline": (i32, [vp, C.POINTER(C.c_float), i32]),
         "smsgate_replay_host_begin": (i32, [vp, vp, vp, i64, i64, i64, C.POINTER(Outputs)]),
         "smsgate_device_view": (i32, [vp, i64, C.POINTER(Outputs)]),
         "smsgate_replay_host_finish": (i32, [vp, C.POINTER(Outputs)]),

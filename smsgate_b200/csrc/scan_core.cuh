@@ -433,9 +433,9 @@ SG_HD void sg_sha256_compress(uint32_t h[8], uint32_t w[16]) {
             }
             const uint32_t S1 = sg_rotr(e, 6) ^ sg_rotr(e, 11) ^ sg_rotr(e, 25);
             const uint32_t ch = (e & f) ^ (~e & g);
-            const uint32_t t1 = hh + S1 + ch + SG_K256[r + j] + wi;
             const uint32_t S0 = sg_rotr(a, 2) ^ sg_rotr(a, 13) ^ sg_rotr(a, 22);
             const uint32_t mj = (a & b) ^ (a & c) ^ (b & c);
+            const uint32_t t1 = hh + S1 + ch + SG_K256[r + j] + wi;
             const uint32_t t2 = S0 + mj;
             hh = g; g = f; f = e; e = d + t1; d = c; c = b; b = a; a = t1 + t2;
         }

@@ -17,6 +17,7 @@
 #include <string.h>
 #include <mutex>
 #include <new>
+#include <cstdlib>
 #include <string>
 
 #include "../../include/smsgate_b200.h"
@@ -337,9 +338,18 @@ k_scan_keys(const uint8_t* __restrict__ bytes, const int64_t* __restrict__ offse
                     const int live = min(32, nM - c * 32);
                     for (int j = 0; j < live; ++j) {
                         const int o = __shfl_sync(0xffffffffu, off, j), fl = __shfl_sync(0xffffffffu, cur, j);
+                        // stage and fixed_bytes + base are both 16-byte aligned: same word phase on both sides
                         const uint8_t* src = S.stage + o;
                         uint8_t* dst = out.fixed_bytes + base + o;
-                        for (int k = lane; k < fl; k += 32) dst[k] = src[k];
+                        const bool words = (((uintptr_t)dst ^ (uintptr_t)src) & 3) == 0;
+                        const int head = words ? min(fl, (4 - (o & 3)) & 3) : fl;
+                        for (int k = lane; k < head; k += 32) dst[k] = src[k];
+                        const int nw = (fl - head) >> 2;
+                        for (int k = lane; k < nw; k += 32)
+                            *reinterpret_cast<uint32_t*>(dst + head + 4 * k) =
+                                *reinterpret_cast<const uint32_t*>(src + head + 4 * k);
+                        const int done = head + 4 * nw;
+                        if (lane < fl - done) dst[done + lane] = src[done + lane];
                     }
                 }
             }
@@ -492,8 +502,8 @@ __device__ __forceinline__ bool id20_equal(const uint8_t* a, const uint8_t* b) {
 }
 
 __global__ void __launch_bounds__(256)
-k_dedup_insert(int64_t n, const uint8_t* __restrict__ msg_id, const uint8_t* __restrict__ status, DedupScratch D) {
-    const int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+k_dedup_insert(int64_t i0, int64_t n, const uint8_t* __restrict__ msg_id, const uint8_t* __restrict__ status, DedupScratch D) {
+    const int64_t i = i0 + blockIdx.x * (int64_t)blockDim.x + threadIdx.x;   // messages [i0, n) of the batch
     if (i >= n) return;
     if (status[i] != SG_ST_UPSERT) {
         D.slot_of[i] = -1;
@@ -581,6 +591,7 @@ struct smsgate_ctx {
     cudaEvent_t ev_in[MAX_CHUNKS] = {nullptr}, ev_k[MAX_CHUNKS] = {nullptr};
     cudaEvent_t ev_start = nullptr, ev_dedup = nullptr, ev_done = nullptr;
     int64_t host_n = 0, host_total = 0;      // batch of the pending smsgate_replay_host_begin
+    int host_chunks = 0;                     // chunks of the last smsgate_replay_host_begin (timeline)
     // pending XML extraction (smsgate_xml_scan .. smsgate_xml_emit)
     uint8_t* xml_slab = nullptr;
     int64_t xml_n = 0, xml_T = 0, xml_nx = 0;
@@ -626,6 +637,8 @@ struct smsgate_ctx {
     int64_t* s_offsets = nullptr;
     uint8_t* s_out = nullptr;     // one slab carved into the output columns
     uint8_t* s_fixed = nullptr;
+    smsgate_record* s_records = nullptr;   // packed results of smsgate_replay_host_records
+    int64_t* s_verdict = nullptr;
 };
 
 static thread_local std::string g_create_error;
@@ -690,12 +703,12 @@ extern "C" int smsgate_create(int device, void* cuda_stream, smsgate_ctx** out) 
     if ((e = cudaStreamCreateWithFlags(&ctx->s_h2d, cudaStreamNonBlocking)) != cudaSuccess) return bail("cudaStreamCreate", e);
     if ((e = cudaStreamCreateWithFlags(&ctx->s_d2h, cudaStreamNonBlocking)) != cudaSuccess) return bail("cudaStreamCreate", e);
     for (int k = 0; k < smsgate_ctx::MAX_CHUNKS; ++k) {
-        if ((e = cudaEventCreateWithFlags(&ctx->ev_in[k], cudaEventDisableTiming)) != cudaSuccess) return bail("cudaEventCreate", e);
-        if ((e = cudaEventCreateWithFlags(&ctx->ev_k[k], cudaEventDisableTiming)) != cudaSuccess) return bail("cudaEventCreate", e);
+        if ((e = cudaEventCreate(&ctx->ev_in[k])) != cudaSuccess) return bail("cudaEventCreate", e);
+        if ((e = cudaEventCreate(&ctx->ev_k[k])) != cudaSuccess) return bail("cudaEventCreate", e);
     }
-    if ((e = cudaEventCreateWithFlags(&ctx->ev_start, cudaEventDisableTiming)) != cudaSuccess) return bail("cudaEventCreate", e);
-    if ((e = cudaEventCreateWithFlags(&ctx->ev_dedup, cudaEventDisableTiming)) != cudaSuccess) return bail("cudaEventCreate", e);
-    if ((e = cudaEventCreateWithFlags(&ctx->ev_done, cudaEventDisableTiming)) != cudaSuccess) return bail("cudaEventCreate", e);
+    if ((e = cudaEventCreate(&ctx->ev_start)) != cudaSuccess) return bail("cudaEventCreate", e);
+    if ((e = cudaEventCreate(&ctx->ev_dedup)) != cudaSuccess) return bail("cudaEventCreate", e);
+    if ((e = cudaEventCreate(&ctx->ev_done)) != cudaSuccess) return bail("cudaEventCreate", e);
     DeviceTables* h = new DeviceTables();
     sg_fill_tables(h);
     if ((e = cudaMalloc(&ctx->d_tables, sizeof(DeviceTables))) != cudaSuccess) { delete h; return bail("cudaMalloc tables", e); }
@@ -737,9 +750,9 @@ static void free_scratch(smsgate_ctx* c) {
     cudaFree(c->d_owner); cudaFree(c->d_first); cudaFree(c->d_last); cudaFree(c->d_slot_of);
     cudaFree(c->d_gfirst); cudaFree(c->d_glast); cudaFree(c->d_counts); cudaFree(c->d_cursor);
     c->d_gfirst = c->d_glast = nullptr; c->d_counts = nullptr; c->d_cursor = nullptr;
-    cudaFree(c->s_bytes); cudaFree(c->s_offsets); cudaFree(c->s_out); cudaFree(c->s_fixed);
+    cudaFree(c->s_bytes); cudaFree(c->s_offsets); cudaFree(c->s_out); cudaFree(c->s_fixed); cudaFree(c->s_records); cudaFree(c->s_verdict);
     c->d_owner = c->d_first = c->d_last = c->d_slot_of = nullptr;
-    c->s_bytes = nullptr; c->s_offsets = nullptr; c->s_out = nullptr; c->s_fixed = nullptr;
+    c->s_bytes = nullptr; c->s_offsets = nullptr; c->s_out = nullptr; c->s_fixed = nullptr; c->s_records = nullptr; c->s_verdict = nullptr;
     c->cap_msgs = c->cap_bytes = 0; c->dd_cap = 0;
 }
 
@@ -791,6 +804,8 @@ extern "C" int smsgate_reserve(smsgate_ctx* ctx, int64_t max_msgs, int64_t max_b
     CUDA_TRY(ctx, cudaMalloc(&ctx->s_fixed, (size_t)max_bytes + 64));
     CUDA_TRY(ctx, cudaMalloc(&ctx->s_offsets, (size_t)(max_msgs + 1) * 8));
     CUDA_TRY(ctx, cudaMalloc(&ctx->s_out, (size_t)(max_msgs + 16) * SLAB_PER_MSG + 65536));
+    CUDA_TRY(ctx, cudaMalloc(&ctx->s_records, (size_t)(max_msgs + 1) * sizeof(smsgate_record)));
+    CUDA_TRY(ctx, cudaMalloc(&ctx->s_verdict, (size_t)(max_msgs + 1) * 8));
     ctx->dd_cap = cap;
     ctx->cap_msgs = max_msgs;
     ctx->cap_bytes = max_bytes;
@@ -1154,9 +1169,10 @@ extern "C" int smsgate_scan_keys(smsgate_ctx* ctx, const uint8_t* d_bytes, const
     if (n == 0) return SMSGATE_OK;
     CUDA_TRY(ctx, cudaSetDevice(ctx->device));
     ScanOut so{out->msg_id, out->cache_key, out->flags, out->body_date, out->fixed_len, out->fixed_bytes};
-    const int64_t ntiles = (n + K1_TILE - 1) / K1_TILE;
+    // one CTA per SM as soon as there are 64 messages for each: a small batch is latency, not throughput
+    const int64_t want = (n + 63) / 64;
     const int64_t maxgrid = (int64_t)ctx->sm_count * K1_CTAS_PER_SM;
-    const unsigned grid = (unsigned)(ntiles < maxgrid ? ntiles : maxgrid);
+    const unsigned grid = (unsigned)(want < maxgrid ? want : maxgrid);
     k_scan_keys<<<grid, K1_THREADS, sizeof(K1Smem), ctx->stream>>>(d_bytes, d_offsets, n, ctx->d_tables, so);
     ctx->launches += 1;
     CUDA_TRY(ctx, cudaGetLastError());
@@ -1181,6 +1197,18 @@ extern "C" int smsgate_join_route(smsgate_ctx* ctx, int64_t n, int64_t now_packe
     return SMSGATE_OK;
 }
 
+// An empty dedup table for a batch of n messages (power of two >= 2n) inside the reserved arrays.
+static int dedup_prepare(smsgate_ctx* ctx, int64_t n, DedupScratch* D) {
+    uint64_t cap = pow2_at_least((uint64_t)(n > 8 ? n : 8) * 2);
+    if (cap > ctx->dd_cap) cap = ctx->dd_cap;
+    cudaStream_t st = ctx->stream;
+    CUDA_TRY(ctx, cudaMemsetAsync(ctx->d_owner, 0xFF, cap * 4, st));
+    CUDA_TRY(ctx, cudaMemsetAsync(ctx->d_first, 0x7F, cap * 4, st));
+    CUDA_TRY(ctx, cudaMemsetAsync(ctx->d_last, 0xFF, cap * 4, st));
+    *D = DedupScratch{ctx->d_owner, ctx->d_first, ctx->d_last, ctx->d_slot_of, cap - 1};
+    return SMSGATE_OK;
+}
+
 extern "C" int smsgate_dedup(smsgate_ctx* ctx, int64_t n, int64_t base_index, const smsgate_outputs* out) {
     if (!ctx) return SMSGATE_E_ARG;
     if (n < 0 || !out) return fail(ctx, SMSGATE_E_ARG, "dedup: NULL argument");
@@ -1188,16 +1216,12 @@ extern "C" int smsgate_dedup(smsgate_ctx* ctx, int64_t n, int64_t base_index, co
     if (!out->msg_id || !out->status) return fail(ctx, SMSGATE_E_ARG, "dedup needs the msg_id and status columns");
     if (n > ctx->cap_msgs) return fail(ctx, SMSGATE_E_STATE, "dedup: batch larger than smsgate_reserve() sized the scratch for");
     CUDA_TRY(ctx, cudaSetDevice(ctx->device));
-    // table sized for this batch (power of two >= 2n) inside the reserved arrays
-    uint64_t cap = pow2_at_least((uint64_t)(n > 8 ? n : 8) * 2);
-    if (cap > ctx->dd_cap) cap = ctx->dd_cap;
     cudaStream_t st = ctx->stream;
-    CUDA_TRY(ctx, cudaMemsetAsync(ctx->d_owner, 0xFF, cap * 4, st));
-    CUDA_TRY(ctx, cudaMemsetAsync(ctx->d_first, 0x7F, cap * 4, st));
-    CUDA_TRY(ctx, cudaMemsetAsync(ctx->d_last, 0xFF, cap * 4, st));
-    DedupScratch D{ctx->d_owner, ctx->d_first, ctx->d_last, ctx->d_slot_of, cap - 1};
+    DedupScratch D;
+    const int prc = dedup_prepare(ctx, n, &D);
+    if (prc) return prc;
     const unsigned grid = (unsigned)((n + 255) / 256);
-    k_dedup_insert<<<grid, 256, 0, st>>>(n, out->msg_id, out->status, D);
+    k_dedup_insert<<<grid, 256, 0, st>>>(0, n, out->msg_id, out->status, D);
     k_dedup_resolve<<<grid, 256, 0, st>>>(n, base_index, D, out->survivor, out->first_seen, out->last_idx);
     ctx->launches += 2;
     CUDA_TRY(ctx, cudaGetLastError());
@@ -1262,10 +1286,41 @@ extern "C" int smsgate_device_view(smsgate_ctx* ctx, int64_t n, smsgate_outputs*
     return SMSGATE_OK;
 }
 
-extern "C" int smsgate_replay_host_begin(smsgate_ctx* ctx, const uint8_t* h_bytes, const int64_t* h_offsets, int64_t n,
-                                         int64_t now_packed, int64_t base_index, const smsgate_outputs* h_out) {
+// ---- packed results.  The host call returns ~10 columns; copied back chunk by chunk that is ~10 small
+// transfers per chunk, and on PCIe the set-up time of small device->host copies both exceeds their transfer
+// time and slows the concurrent copy-in down.  smsgate_replay_host_records returns the same values as one
+// 64-byte record per message instead: one transfer per chunk.
+static_assert(sizeof(smsgate_record) == 64, "smsgate_record is 64 bytes");
+__global__ void __launch_bounds__(256)
+k_pack_records(int64_t lo, int64_t hi, const smsgate_outputs d, smsgate_record* __restrict__ rec) {
+    const int64_t i = lo + blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+    if (i >= hi) return;
+    const uint32_t* id = reinterpret_cast<const uint32_t*>(d.msg_id + i * 20);
+    const uint32_t small = (uint32_t)d.status[i] | ((uint32_t)d.flags[i] << 8) | ((uint32_t)d.dec_flags[i] << 16) |
+                           ((uint32_t)d.card_len[i] << 24);
+    const int64_t ac = d.amount_coef[i], bc = d.balance_coef[i], dt = d.date[i];
+    uint4* o = reinterpret_cast<uint4*>(rec + i);
+    o[0] = make_uint4(id[0], id[1], id[2], id[3]);
+    o[1] = make_uint4(id[4], small, (uint32_t)d.slot[i], (uint32_t)d.amount_exp[i]);
+    o[2] = make_uint4((uint32_t)d.balance_exp[i], (uint32_t)d.body_date[i], (uint32_t)ac, (uint32_t)((uint64_t)ac >> 32));
+    o[3] = make_uint4((uint32_t)bc, (uint32_t)((uint64_t)bc >> 32), (uint32_t)dt, (uint32_t)((uint64_t)dt >> 32));
+}
+__global__ void __launch_bounds__(256)
+k_pack_verdict(int64_t n, const uint8_t* __restrict__ survivor, const uint8_t* __restrict__ first_seen,
+               const int64_t* __restrict__ last_idx, int64_t* __restrict__ verdict) {
+    const int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const int64_t l = last_idx[i];
+    verdict[i] = l < 0 ? -1 : ((l << 2) | ((int64_t)(first_seen[i] & 1) << 1) | (int64_t)(survivor[i] & 1));
+}
+
+static int replay_host_begin_impl(smsgate_ctx* ctx, const uint8_t* h_bytes, const int64_t* h_offsets, int64_t n,
+                                  int64_t now_packed, int64_t base_index, const smsgate_outputs* h_cols,
+                                  smsgate_record* h_records) {
     if (!ctx) return SMSGATE_E_ARG;
-    if (n < 0 || !h_out || (n > 0 && (!h_offsets))) return fail(ctx, SMSGATE_E_ARG, "replay_host: NULL argument");
+    static const smsgate_outputs no_columns = {};
+    const smsgate_outputs* h_out = h_cols ? h_cols : &no_columns;
+    if (n < 0 || (!h_cols && !h_records) || (n > 0 && (!h_offsets))) return fail(ctx, SMSGATE_E_ARG, "replay_host: NULL argument");
     ctx->host_n = 0;
     ctx->host_total = 0;
     if (n == 0) return SMSGATE_OK;
@@ -1278,63 +1333,106 @@ extern "C" int smsgate_replay_host_begin(smsgate_ctx* ctx, const uint8_t* h_byte
     cudaStream_t st = ctx->stream, sin = ctx->s_h2d, sout = ctx->s_d2h;
     smsgate_outputs d;
     carve_slab(ctx->s_out, n, ctx->s_fixed, &d);
-    // chunks of >= 64 Ki messages, at most MAX_CHUNKS: copy-in of chunk c+1 and copy-out of chunk c-1
-    // overlap the kernels of chunk c (PCIe is full duplex; the copies dominate the end-to-end time)
-    int nchunks = (int)((n + 65535) / 65536);
-    if (nchunks > smsgate_ctx::MAX_CHUNKS) nchunks = smsgate_ctx::MAX_CHUNKS;
-    if (nchunks < 1) nchunks = 1;
-    const int64_t per = (n + nchunks - 1) / nchunks;
+    // Chunks: copy-in of chunk c+1 and copy-out of chunk c-1 overlap the kernels of chunk c (PCIe is full
+    // duplex and the copies, not the kernels, are what the end-to-end time is made of).  Every copy has a
+    // few microseconds of set-up, so chunks are large where that is free - each takes a fifth of what is
+    // left - and small only at the end, where the size of the last chunk is what remains to be done after
+    // the last input byte has arrived.
+    int64_t bound[smsgate_ctx::MAX_CHUNKS + 1];
+    int nchunks = 0;
+    {
+        const int64_t min_chunk = 65536;
+        int64_t lo = 0;
+        bound[0] = 0;
+        while (lo < n) {
+            const int64_t rem = n - lo;
+            int64_t sz = rem / 5 > min_chunk ? rem / 5 : min_chunk;
+            if (nchunks == smsgate_ctx::MAX_CHUNKS - 1 || rem - sz < min_chunk / 2) sz = rem;
+            lo += sz;
+            bound[++nchunks] = lo;
+        }
+    }
     // nothing of this call may start before what the caller queued on its stream earlier
     CUDA_TRY(ctx, cudaEventRecord(ctx->ev_start, st));
     CUDA_TRY(ctx, cudaStreamWaitEvent(sin, ctx->ev_start, 0));
     CUDA_TRY(ctx, cudaStreamWaitEvent(sout, ctx->ev_start, 0));
     for (int c = 0; c < nchunks; ++c) {
-        const int64_t lo = c * per, hi = (lo + per < n) ? lo + per : n;
-        if (lo >= hi) { nchunks = c; break; }
+        const int64_t lo = bound[c], hi = bound[c + 1];
         const int64_t b0 = h_offsets[lo], b1 = h_offsets[hi];
         CUDA_TRY(ctx, cudaMemcpyAsync(ctx->s_offsets + lo, h_offsets + lo, (size_t)(hi - lo + 1) * 8, cudaMemcpyHostToDevice, sin));
         if (b1 > b0) CUDA_TRY(ctx, cudaMemcpyAsync(ctx->s_bytes + b0, h_bytes + b0, (size_t)(b1 - b0), cudaMemcpyHostToDevice, sin));
         CUDA_TRY(ctx, cudaEventRecord(ctx->ev_in[c], sin));
     }
+    // the dedup table takes each chunk's keys as soon as they exist; only the verdicts wait for the end
+    DedupScratch D;
+    int rc = dedup_prepare(ctx, n, &D);
+    if (rc) return rc;
+    int64_t back_lo = 0;                                // results of [back_lo, ...) are still on the device
     for (int c = 0; c < nchunks; ++c) {
-        const int64_t lo = c * per, hi = (lo + per < n) ? lo + per : n;
+        const int64_t lo = bound[c], hi = bound[c + 1];
         const int64_t m = hi - lo;
         CUDA_TRY(ctx, cudaStreamWaitEvent(st, ctx->ev_in[c], 0));
         const smsgate_outputs dc = shift_columns(d, lo);
-        int rc = smsgate_scan_keys(ctx, ctx->s_bytes, ctx->s_offsets + lo, m, &dc);
+        rc = smsgate_scan_keys(ctx, ctx->s_bytes, ctx->s_offsets + lo, m, &dc);
         if (rc) return rc;
         rc = smsgate_join_route(ctx, m, now_packed, &dc);
         if (rc) return rc;
+        k_dedup_insert<<<(unsigned)((m + 255) / 256), 256, 0, st>>>(lo, hi, d.msg_id, d.status, D);
+        ctx->launches += 1;
+        CUDA_TRY(ctx, cudaGetLastError());
+        if (h_records) {
+            k_pack_records<<<(unsigned)((m + 255) / 256), 256, 0, st>>>(lo, hi, d, ctx->s_records);
+            ctx->launches += 1;
+            CUDA_TRY(ctx, cudaGetLastError());
+        }
         CUDA_TRY(ctx, cudaEventRecord(ctx->ev_k[c], st));
+        // Results go back in few, large transfers (a quarter of the batch at a time): every column is its own
+        // copy, small copies are mostly set-up time and they also slow the copy-in down.  Only the last two
+        // chunks go back one by one, so that little is left to do after the last kernel.
+        if (c < nchunks - 2 && (hi - back_lo) * 4 < n) continue;
         CUDA_TRY(ctx, cudaStreamWaitEvent(sout, ctx->ev_k[c], 0));
+        const int64_t glo = back_lo, gm = hi - back_lo;
+        back_lo = hi;
+        if (h_records)
+            CUDA_TRY(ctx, cudaMemcpyAsync(h_records + glo, ctx->s_records + glo, (size_t)gm * sizeof(smsgate_record), cudaMemcpyDeviceToHost, sout));
 #define BACK(col, w) \
-    if (h_out->col) CUDA_TRY(ctx, cudaMemcpyAsync(h_out->col + lo * (w), d.col + lo * (w), (size_t)(m * (w)) * sizeof(*d.col), cudaMemcpyDeviceToHost, sout))
+    if (h_out->col) CUDA_TRY(ctx, cudaMemcpyAsync(h_out->col + glo * (w), d.col + glo * (w), (size_t)(gm * (w)) * sizeof(*d.col), cudaMemcpyDeviceToHost, sout))
         BACK(msg_id, 20); BACK(cache_key, 32); BACK(flags, 1); BACK(body_date, 1); BACK(fixed_len, 1); BACK(slot, 1);
         BACK(status, 1); BACK(amount_coef, 1); BACK(balance_coef, 1); BACK(amount_exp, 1); BACK(balance_exp, 1);
         BACK(dec_flags, 1); BACK(date, 1); BACK(card, 16); BACK(card_len, 1); BACK(amount_cents, 1); BACK(balance_cents, 1);
 #undef BACK
         if (h_out->fixed_bytes) {
-            const int64_t b0 = h_offsets[lo], b1 = h_offsets[hi];
+            const int64_t b0 = h_offsets[glo], b1 = h_offsets[hi];
             if (b1 > b0) CUDA_TRY(ctx, cudaMemcpyAsync(h_out->fixed_bytes + b0, d.fixed_bytes + b0, (size_t)(b1 - b0), cudaMemcpyDeviceToHost, sout));
         }
     }
-    int rc = smsgate_dedup(ctx, n, base_index, &d);
-    if (rc) return rc;
+    k_dedup_resolve<<<(unsigned)((n + 255) / 256), 256, 0, st>>>(n, base_index, D, d.survivor, d.first_seen, d.last_idx);
+    ctx->launches += 1;
+    CUDA_TRY(ctx, cudaGetLastError());
     ctx->host_n = n;
     ctx->host_total = total;
+    ctx->host_chunks = nchunks;
     return SMSGATE_OK;
 }
 
-extern "C" int smsgate_replay_host_finish(smsgate_ctx* ctx, const smsgate_outputs* h_out) {
-    if (!ctx || !h_out) return SMSGATE_E_ARG;
+static int replay_host_finish_impl(smsgate_ctx* ctx, const smsgate_outputs* h_cols, int64_t* h_verdict) {
+    if (!ctx || (!h_cols && !h_verdict)) return SMSGATE_E_ARG;
+    static const smsgate_outputs no_columns = {};
+    const smsgate_outputs* h_out = h_cols ? h_cols : &no_columns;
     const int64_t n = ctx->host_n;
     if (n == 0) return SMSGATE_OK;
     CUDA_TRY(ctx, cudaSetDevice(ctx->device));
     cudaStream_t st = ctx->stream, sout = ctx->s_d2h;
     smsgate_outputs d;
     carve_slab(ctx->s_out, n, ctx->s_fixed, &d);
+    if (h_verdict) {
+        k_pack_verdict<<<(unsigned)((n + 255) / 256), 256, 0, st>>>(n, d.survivor, d.first_seen, d.last_idx, ctx->s_verdict);
+        ctx->launches += 1;
+        CUDA_TRY(ctx, cudaGetLastError());
+    }
     CUDA_TRY(ctx, cudaEventRecord(ctx->ev_dedup, st));
     CUDA_TRY(ctx, cudaStreamWaitEvent(sout, ctx->ev_dedup, 0));
+    if (h_verdict) CUDA_TRY(ctx, cudaMemcpyAsync(h_verdict, ctx->s_verdict, (size_t)n * 8, cudaMemcpyDeviceToHost, sout));
     if (h_out->survivor) CUDA_TRY(ctx, cudaMemcpyAsync(h_out->survivor, d.survivor, (size_t)n, cudaMemcpyDeviceToHost, sout));
     if (h_out->first_seen) CUDA_TRY(ctx, cudaMemcpyAsync(h_out->first_seen, d.first_seen, (size_t)n, cudaMemcpyDeviceToHost, sout));
     if (h_out->last_idx) CUDA_TRY(ctx, cudaMemcpyAsync(h_out->last_idx, d.last_idx, (size_t)n * 8, cudaMemcpyDeviceToHost, sout));
@@ -1346,6 +1444,47 @@ extern "C" int smsgate_replay_host_finish(smsgate_ctx* ctx, const smsgate_output
     CUDA_TRY(ctx, cudaGetLastError());
     ctx->host_n = 0;
     return SMSGATE_OK;
+}
+
+extern "C" int smsgate_replay_host_begin(smsgate_ctx* ctx, const uint8_t* h_bytes, const int64_t* h_offsets, int64_t n,
+                                         int64_t now_packed, int64_t base_index, const smsgate_outputs* h_out) {
+    if (!h_out) return ctx ? fail(ctx, SMSGATE_E_ARG, "replay_host: NULL argument") : SMSGATE_E_ARG;
+    return replay_host_begin_impl(ctx, h_bytes, h_offsets, n, now_packed, base_index, h_out, nullptr);
+}
+extern "C" int smsgate_replay_host_finish(smsgate_ctx* ctx, const smsgate_outputs* h_out) {
+    if (!h_out) return SMSGATE_E_ARG;
+    return replay_host_finish_impl(ctx, h_out, nullptr);
+}
+extern "C" int smsgate_replay_host_records_begin(smsgate_ctx* ctx, const uint8_t* h_bytes, const int64_t* h_offsets,
+                                                 int64_t n, int64_t now_packed, int64_t base_index,
+                                                 smsgate_record* h_records) {
+    if (!h_records) return ctx ? fail(ctx, SMSGATE_E_ARG, "replay_host_records: NULL argument") : SMSGATE_E_ARG;
+    return replay_host_begin_impl(ctx, h_bytes, h_offsets, n, now_packed, base_index, nullptr, h_records);
+}
+extern "C" int smsgate_replay_host_records_finish(smsgate_ctx* ctx, int64_t* h_verdict) {
+    if (!h_verdict) return SMSGATE_E_ARG;
+    return replay_host_finish_impl(ctx, nullptr, h_verdict);
+}
+extern "C" int smsgate_replay_host_records(smsgate_ctx* ctx, const uint8_t* h_bytes, const int64_t* h_offsets, int64_t n,
+                                           int64_t now_packed, int64_t base_index, smsgate_record* h_records,
+                                           int64_t* h_verdict) {
+    const int rc = smsgate_replay_host_records_begin(ctx, h_bytes, h_offsets, n, now_packed, base_index, h_records);
+    if (rc) return rc;
+    return smsgate_replay_host_records_finish(ctx, h_verdict);
+}
+
+extern "C" int smsgate_replay_host_timeline(smsgate_ctx* ctx, float* ms, int capacity) {
+    if (!ctx || !ms) return SMSGATE_E_ARG;
+    const int nc = ctx->host_chunks;
+    if (capacity < 2 * nc + 2) return fail(ctx, SMSGATE_E_ARG, "replay_host_timeline: capacity too small");
+    CUDA_TRY(ctx, cudaSetDevice(ctx->device));
+    for (int c = 0; c < nc; ++c) {
+        CUDA_TRY(ctx, cudaEventElapsedTime(&ms[c], ctx->ev_start, ctx->ev_in[c]));
+        CUDA_TRY(ctx, cudaEventElapsedTime(&ms[nc + c], ctx->ev_start, ctx->ev_k[c]));
+    }
+    CUDA_TRY(ctx, cudaEventElapsedTime(&ms[2 * nc], ctx->ev_start, ctx->ev_dedup));
+    CUDA_TRY(ctx, cudaEventElapsedTime(&ms[2 * nc + 1], ctx->ev_start, ctx->ev_done));
+    return nc;
 }
 
 extern "C" int smsgate_replay_host(smsgate_ctx* ctx, const uint8_t* h_bytes, const int64_t* h_offsets, int64_t n,
@@ -1918,7 +2057,7 @@ extern "C" int smsgate_dedup_static(int device, void* cuda_stream, int64_t n, in
         (e = cudaMemsetAsync(D.last, 0xFF, cap * 4, st)) != cudaSuccess)
         return static_fail(errbuf, errbuf_len, SMSGATE_E_CUDA, "cudaMemsetAsync", cudaGetErrorString(e));
     const unsigned grid = (unsigned)((n + 255) / 256);
-    k_dedup_insert<<<grid, 256, 0, st>>>(n, d_msg_id, d_status, D);
+    k_dedup_insert<<<grid, 256, 0, st>>>(0, n, d_msg_id, d_status, D);
     k_dedup_resolve<<<grid, 256, 0, st>>>(n, base_index, D, d_survivor, d_first_seen, d_last_idx);
     if ((e = cudaGetLastError()) != cudaSuccess)
         return static_fail(errbuf, errbuf_len, SMSGATE_E_CUDA, "kernel launch", cudaGetErrorString(e));

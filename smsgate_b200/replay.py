@@ -39,6 +39,45 @@ def _np_ptr(a: Optional[np.ndarray]):
     return None if a is None else a.ctypes.data_as(C.c_void_p)
 
 
+class _RecordColumns:
+    """The `cols` mapping of a ReplayResult that came back as packed records
+    (smsgate_replay_host_records): record fields are strided views, the three
+    dedup columns are decoded from the verdict integers on first use."""
+
+    def __init__(self, records: np.ndarray, verdict: np.ndarray):
+        self.records = records
+        self.verdict = verdict
+        self._decoded: dict = {}
+
+    _VERDICT = ("survivor", "first_seen", "last_idx")
+
+    def keys(self):
+        return tuple(self.records.dtype.names) + self._VERDICT
+
+    def __iter__(self):
+        return iter(self.keys())
+
+    def __contains__(self, name) -> bool:
+        return name in self.records.dtype.names or name in self._VERDICT
+
+    def __getitem__(self, name):
+        if name in self.records.dtype.names:
+            return self.records[name]
+        if name not in self._VERDICT:
+            raise KeyError(name)
+        if name not in self._decoded:
+            v = self.verdict
+            up = v >= 0
+            self._decoded["survivor"] = (up & ((v & 1) != 0)).astype(np.uint8)
+            self._decoded["first_seen"] = (up & ((v & 2) != 0)).astype(np.uint8)
+            self._decoded["last_idx"] = np.where(up, v >> 2, -1).astype(np.int64)
+        return self._decoded[name]
+
+    @property
+    def nbytes(self) -> int:
+        return int(self.records.nbytes + self.verdict.nbytes)
+
+
 class ReplayResult:
     """Columns of one replayed batch (numpy, host) + lazy ParsedSMS views."""
 
@@ -224,6 +263,43 @@ class ReplayEngine:
         return cols
 
     ALL_COLUMNS = tuple(name for name, _, _ in L.COLUMNS)
+
+    def replay_records(self, batch: Batch, now: _dt.datetime, base_index: int = 0, pinned: bool = True,
+                       exchange=None) -> ReplayResult:
+        """`replay` with the results returned as one 64-byte record per message plus one verdict integer
+        (smsgate_replay_host_records): one device->host transfer per chunk instead of one per column, which
+        is what the end-to-end time depends on.  The ReplayResult reads the same either way."""
+        n = batch.n
+        total = int(batch.body_offsets[-1]) if n else 0
+        self.reserve(max(n, 1), max(total, 1))
+        dtype = np.dtype(L.RECORD_FIELDS)
+        assert dtype.itemsize == L.RECORD_BYTES_OUT
+        if pinned:
+            import torch
+            key = ("records", n)
+            t = self._pinned.get(key)
+            if t is None:
+                t = (torch.empty(max(n, 1) * L.RECORD_BYTES_OUT, dtype=torch.uint8, pin_memory=True),
+                     torch.empty(max(n, 1), dtype=torch.int64, pin_memory=True))
+                self._pinned[key] = t
+            rec_buf, verdict_buf = t[0].numpy().view(dtype), t[1].numpy()
+        else:
+            rec_buf, verdict_buf = np.zeros(max(n, 1), dtype=dtype), np.zeros(max(n, 1), dtype=np.int64)
+        rec, verdict = rec_buf[:n], verdict_buf[:n]
+        body = np.ascontiguousarray(batch.body_bytes)
+        offs = np.ascontiguousarray(batch.body_offsets, dtype=np.int64)
+        rp, vp = rec_buf.ctypes.data, verdict_buf.ctypes.data      # never NULL, also for an empty shard
+        if exchange is None:
+            L.check(self._ctx, self._lib.smsgate_replay_host_records(self._ctx, _np_ptr(body), _np_ptr(offs), n,
+                                                                     pack_datetime(now), int(base_index), rp, vp))
+        else:
+            L.check(self._ctx, self._lib.smsgate_replay_host_records_begin(self._ctx, _np_ptr(body), _np_ptr(offs), n,
+                                                                           pack_datetime(now), int(base_index), rp))
+            view = L.Outputs()
+            L.check(self._ctx, self._lib.smsgate_device_view(self._ctx, n, C.byref(view)))
+            exchange.run_outputs(view, n, int(base_index))
+            L.check(self._ctx, self._lib.smsgate_replay_host_records_finish(self._ctx, vp))
+        return ReplayResult(batch, _RecordColumns(rec, verdict), self.table, base_index)
 
     def replay(self, batch: Batch, now: _dt.datetime, base_index: int = 0,
                columns: Optional[Sequence[str]] = None, pinned: bool = False, exchange=None) -> ReplayResult:

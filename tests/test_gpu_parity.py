@@ -209,6 +209,36 @@ def test_stage_calls_match_fused_replay(engine):
     assert int(ref.last_idx.max()) >= 1000
 
 
+def test_pinned_buffers_match_pageable(engine):
+    """Pinned host buffers take the store-to-host kernel, pageable ones the copy engine: same columns,
+    for a batch large enough to be split into chunks and with odd chunk boundaries."""
+    backup = synth.generate(150_001, seed=31, dup_frac=0.2, mixed_locale=True, miss_frac=0.1)
+    engine.load_cache(backup.cache)
+    batch = Batch.from_strings(backup.bodies, backup.senders, backup.date_ms)
+    a = engine.replay(batch, NOW, base_index=7)
+    b = engine.replay(batch, NOW, base_index=7, pinned=True)
+    for name in a.cols:
+        assert np.array_equal(np.asarray(a.cols[name]), np.asarray(b.cols[name])), name
+    for i in (0, 1, 77_777, 150_000):
+        assert a.fixed_body(i) == b.fixed_body(i) == O.fixed_body(backup.bodies[i])
+
+
+def test_packed_records_match_columns(engine):
+    """smsgate_replay_host_records returns the values of smsgate_replay_host, record by record."""
+    backup = synth.generate(150_001, seed=32, dup_frac=0.3, mixed_locale=True, miss_frac=0.1)
+    engine.load_cache(backup.cache)
+    batch = Batch.from_strings(backup.bodies, backup.senders, backup.date_ms)
+    a = engine.replay(batch, NOW, base_index=5)
+    for pinned in (True, False):
+        b = engine.replay_records(batch, NOW, base_index=5, pinned=pinned)
+        for name in b.cols.keys():
+            assert np.array_equal(np.asarray(a.cols[name]), np.asarray(b.cols[name])), name
+        assert b.msg_id_hex(150_000) == a.msg_id_hex(150_000)
+        assert np.array_equal(b.survivor_indices(), a.survivor_indices())
+    empty = engine.replay_records(Batch.from_strings([], [], []), NOW)
+    assert empty.n == 0 and len(empty.cols["status"]) == 0
+
+
 def test_full_size_properties(engine):
     """BASELINE.json config 2 size (1 M messages, 100 % hit for non-OTP bodies):
     properties that do not need the oracle at full size, plus a 2 000-message
