@@ -230,6 +230,18 @@ int smsgate_join_route(smsgate_ctx* ctx, int64_t n, int64_t now_packed, const sm
  * last occurrence of a msg_id survives, the first one is the insert.  Reads
  * msg_id, status; writes survivor, first_seen, last_idx (= base_index + local). */
 int smsgate_dedup(smsgate_ctx* ctx, int64_t n, int64_t base_index, const smsgate_outputs* out);
+/* Device-source keys.  d_md5[n*16] = MD5(UTF-8 body) of every message: the msg_id the
+ * API gateway assigns, get_md5_hash (libs/models.py:97-109) as called at services/api_gateway/main.py:113.
+ * Device pointers; d_bytes needs 8 readable bytes past the last body, d_md5 16-byte alignment. */
+int smsgate_device_keys(smsgate_ctx* ctx, const uint8_t* d_bytes, const int64_t* d_offsets, int64_t n, uint8_t* d_md5);
+/* Bodies the reference stores twice because the two sources key them differently (SHA-1 of the body for
+ * XML, services/xml_watcher/watcher.py:45; MD5 for device messages, main.py:113): d_match[i] = index of
+ * the first of the n_xml XML messages whose body equals device message i's, or -1.  Bodies are compared
+ * through their SHA-1 (the msg_id column of smsgate_scan_keys on either batch).  Uses the dedup scratch:
+ * n_xml must fit smsgate_reserve().  No counterpart in the reference (it never notices). */
+int smsgate_cross_source(smsgate_ctx* ctx, int64_t n_xml, const uint8_t* d_xml_sha1, int64_t n_dev,
+                         const uint8_t* d_dev_sha1, int32_t* d_match);
+
 /* All three stages on one batch. */
 int smsgate_replay_device(smsgate_ctx* ctx, const uint8_t* d_bytes, const int64_t* d_offsets, int64_t n,
                           int64_t now_packed, int64_t base_index, const smsgate_outputs* out);

@@ -326,6 +326,14 @@ struct WordReader {
         base = (const uint32_t*)(m - mis);
         shift = mis * 8;
     }
+    SG_HD uint32_t le(int j) const {
+        const uint32_t lo = base[j], hi = base[j + 1];
+#ifdef __CUDA_ARCH__
+        return __funnelshift_r(lo, hi, shift);
+#else
+        return shift ? ((lo >> shift) | (hi << (32 - shift))) : lo;
+#endif
+    }
     SG_HD uint32_t be(int j) const {
         const uint32_t lo = base[j], hi = base[j + 1];
 #ifdef __CUDA_ARCH__
@@ -392,6 +400,63 @@ SG_HD void sg_sha1(const uint8_t* m, int len, uint32_t h[5]) {
             for (int j = 0; j < 16; ++j) w[j] = sg_padded_word(R, len, blk * 16 + j, nwords);
         }
         sg_sha1_compress(h, w);
+    }
+}
+
+// ---------------------------------------------------------------------------
+// MD5 (RFC 1321): the idempotency key of a device-sourced message,
+// hashlib.md5(message.encode('utf-8')).hexdigest() (libs/models.py:97-109, used at
+// services/api_gateway/main.py:113).  Little-endian words straight from the bytes.
+// ---------------------------------------------------------------------------
+#define SG_MD5_K_INIT { \
+    0xd76aa478u, 0xe8c7b756u, 0x242070dbu, 0xc1bdceeeu, 0xf57c0fafu, 0x4787c62au, 0xa8304613u, 0xfd469501u, \
+    0x698098d8u, 0x8b44f7afu, 0xffff5bb1u, 0x895cd7beu, 0x6b901122u, 0xfd987193u, 0xa679438eu, 0x49b40821u, \
+    0xf61e2562u, 0xc040b340u, 0x265e5a51u, 0xe9b6c7aau, 0xd62f105du, 0x02441453u, 0xd8a1e681u, 0xe7d3fbc8u, \
+    0x21e1cde6u, 0xc33707d6u, 0xf4d50d87u, 0x455a14edu, 0xa9e3e905u, 0xfcefa3f8u, 0x676f02d9u, 0x8d2a4c8au, \
+    0xfffa3942u, 0x8771f681u, 0x6d9d6122u, 0xfde5380cu, 0xa4beea44u, 0x4bdecfa9u, 0xf6bb4b60u, 0xbebfbc70u, \
+    0x289b7ec6u, 0xeaa127fau, 0xd4ef3085u, 0x04881d05u, 0xd9d4d039u, 0xe6db99e5u, 0x1fa27cf8u, 0xc4ac5665u, \
+    0xf4292244u, 0x432aff97u, 0xab9423a7u, 0xfc93a039u, 0x655b59c3u, 0x8f0ccc92u, 0xffeff47du, 0x85845dd1u, \
+    0x6fa87e4fu, 0xfe2ce6e0u, 0xa3014314u, 0x4e0811a1u, 0xf7537e82u, 0xbd3af235u, 0x2ad7d2bbu, 0xeb86d391u}
+
+// word j of the MD5-padded message (0x80, zeros, 64-bit little-endian bit length), branch-free like
+// sg_padded_word but little-endian: the first message byte is the LOW byte of word 0
+SG_HD uint32_t sg_md5_word(const WordReader& R, int len, int j, int nwords) {
+    const int k = len - j * 4;
+    const uint32_t raw = R.le(j);
+    const uint32_t kk = (uint32_t)(k < 0 ? 0 : (k > 4 ? 4 : k));
+    const uint32_t keep = kk == 0 ? 0u : (0xFFFFFFFFu >> (32 - 8 * kk));
+    uint32_t w = raw & keep;
+    if (k >= 0 && k < 4) w |= 0x80u << (8 * kk);
+    if (j == nwords - 2) w |= (uint32_t)len << 3;
+    if (j == nwords - 1) w |= (uint32_t)len >> 29;
+    return w;
+}
+
+SG_HD void sg_md5(const uint8_t* m, int len, uint32_t h[4]) {
+    const uint32_t K[64] = SG_MD5_K_INIT;
+    const int S[16] = {7, 12, 17, 22, 5, 9, 14, 20, 4, 11, 16, 23, 6, 10, 15, 21};
+    h[0] = 0x67452301u; h[1] = 0xefcdab89u; h[2] = 0x98badcfeu; h[3] = 0x10325476u;
+    WordReader R;
+    R.init(m);
+    const int nblk = sg_sha_blocks(len), nwords = nblk * 16;   // same padding rule as SHA: 1 + 8 bytes
+    for (int blk = 0; blk < nblk; ++blk) {
+        uint32_t w[16];
+#pragma unroll
+        for (int j = 0; j < 16; ++j) w[j] = sg_md5_word(R, len, blk * 16 + j, nwords);
+        uint32_t a = h[0], b = h[1], c = h[2], d = h[3];
+#pragma unroll
+        for (int i = 0; i < 64; ++i) {
+            uint32_t f;
+            int g;
+            if (i < 16) { f = (b & c) | (~b & d); g = i; }
+            else if (i < 32) { f = (d & b) | (~d & c); g = (5 * i + 1) & 15; }
+            else if (i < 48) { f = b ^ c ^ d; g = (3 * i + 5) & 15; }
+            else { f = c ^ (b | ~d); g = (7 * i) & 15; }
+            const uint32_t t = a + f + K[i] + w[g];
+            a = d; d = c; c = b;
+            b = b + sg_rotl(t, S[(i >> 4) * 4 + (i & 3)]);
+        }
+        h[0] += a; h[1] += b; h[2] += c; h[3] += d;
     }
 }
 

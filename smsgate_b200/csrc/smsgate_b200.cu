@@ -505,7 +505,7 @@ __global__ void __launch_bounds__(256)
 k_dedup_insert(int64_t i0, int64_t n, const uint8_t* __restrict__ msg_id, const uint8_t* __restrict__ status, DedupScratch D) {
     const int64_t i = i0 + blockIdx.x * (int64_t)blockDim.x + threadIdx.x;   // messages [i0, n) of the batch
     if (i >= n) return;
-    if (status[i] != SG_ST_UPSERT) {
+    if (status && status[i] != SG_ST_UPSERT) {              // status == NULL: every message takes part
         D.slot_of[i] = -1;
         return;
     }
@@ -557,6 +557,40 @@ __global__ void k_strict_date_batch(int64_t n, const int32_t* __restrict__ offse
     const int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
     if (i >= n) return;
     packed[i] = sg_parse_strict_datetime(bytes + offsets[i], offsets[i + 1] - offsets[i]);
+}
+
+// ------------------------------------------------------------------ device-source keys
+// MD5 of every body: the msg_id the API gateway gives a device-sourced message.  One thread per message
+// straight from global memory (this is not on the bulk XML path: 64 rounds per block, no staging).
+__global__ void __launch_bounds__(256)
+k_md5_keys(const uint8_t* __restrict__ bytes, const int64_t* __restrict__ offsets, int64_t n, uint8_t* __restrict__ md5) {
+    const int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const int64_t lo = offsets[i];
+    uint32_t h[4];
+    sg_md5(bytes + lo, (int)(offsets[i + 1] - lo), h);
+    *reinterpret_cast<uint4*>(md5 + i * 16) = make_uint4(h[0], h[1], h[2], h[3]);
+}
+// Which device-sourced messages carry a body that the XML backup also holds?  The reference keys the two
+// sources differently (MD5 vs SHA-1 of the same body), so such a body ends up stored twice.  The XML side's
+// SHA-1s are in the dedup table (k_dedup_insert with status == NULL); this probes it with the SHA-1 of each
+// device-sourced body and reports the first XML message with the same body, or -1.
+__global__ void __launch_bounds__(256)
+k_xsrc_probe(int64_t n_dev, const uint8_t* __restrict__ dev_sha1, const uint8_t* __restrict__ xml_sha1, DedupScratch D,
+             int32_t* __restrict__ match) {
+    const int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+    if (i >= n_dev) return;
+    const uint8_t* k = dev_sha1 + i * 20;
+    const uint32_t* kw = reinterpret_cast<const uint32_t*>(k);
+    uint64_t pos = (((uint64_t)kw[1] << 32) | kw[0]) & D.mask;
+    int32_t found = -1;
+    for (;;) {
+        const int owner = D.owner[pos];
+        if (owner == -1) break;
+        if (id20_equal(xml_sha1 + (int64_t)owner * 20, k)) { found = D.first[pos]; break; }
+        pos = (pos + 1) & D.mask;
+    }
+    match[i] = found;
 }
 
 // ------------------------------------------------------------------ legacy offline replay (process_cached.py)
@@ -1223,6 +1257,42 @@ extern "C" int smsgate_dedup(smsgate_ctx* ctx, int64_t n, int64_t base_index, co
     const unsigned grid = (unsigned)((n + 255) / 256);
     k_dedup_insert<<<grid, 256, 0, st>>>(0, n, out->msg_id, out->status, D);
     k_dedup_resolve<<<grid, 256, 0, st>>>(n, base_index, D, out->survivor, out->first_seen, out->last_idx);
+    ctx->launches += 2;
+    CUDA_TRY(ctx, cudaGetLastError());
+    return SMSGATE_OK;
+}
+
+extern "C" int smsgate_device_keys(smsgate_ctx* ctx, const uint8_t* d_bytes, const int64_t* d_offsets, int64_t n,
+                                   uint8_t* d_md5) {
+    if (!ctx) return SMSGATE_E_ARG;
+    if (n < 0 || (n > 0 && (!d_bytes || !d_offsets || !d_md5))) return fail(ctx, SMSGATE_E_ARG, "device_keys: NULL argument");
+    if (((uintptr_t)d_md5 & 15) != 0) return fail(ctx, SMSGATE_E_ARG, "device_keys: md5 must be 16-byte aligned");
+    if (n == 0) return SMSGATE_OK;
+    CUDA_TRY(ctx, cudaSetDevice(ctx->device));
+    k_md5_keys<<<(unsigned)((n + 255) / 256), 256, 0, ctx->stream>>>(d_bytes, d_offsets, n, d_md5);
+    ctx->launches += 1;
+    CUDA_TRY(ctx, cudaGetLastError());
+    return SMSGATE_OK;
+}
+
+extern "C" int smsgate_cross_source(smsgate_ctx* ctx, int64_t n_xml, const uint8_t* d_xml_sha1, int64_t n_dev,
+                                    const uint8_t* d_dev_sha1, int32_t* d_match) {
+    if (!ctx) return SMSGATE_E_ARG;
+    if (n_xml < 0 || n_dev < 0 || (n_xml > 0 && !d_xml_sha1) || (n_dev > 0 && (!d_dev_sha1 || !d_match)))
+        return fail(ctx, SMSGATE_E_ARG, "cross_source: NULL argument");
+    if (n_dev == 0) return SMSGATE_OK;
+    if (n_xml > ctx->cap_msgs) return fail(ctx, SMSGATE_E_STATE, "cross_source: more XML messages than smsgate_reserve() sized the scratch for");
+    CUDA_TRY(ctx, cudaSetDevice(ctx->device));
+    cudaStream_t st = ctx->stream;
+    if (n_xml == 0 || !ctx->d_owner) {
+        CUDA_TRY(ctx, cudaMemsetAsync(d_match, 0xFF, (size_t)n_dev * 4, st));
+        return SMSGATE_OK;
+    }
+    DedupScratch D;
+    const int rc = dedup_prepare(ctx, n_xml, &D);
+    if (rc) return rc;
+    k_dedup_insert<<<(unsigned)((n_xml + 255) / 256), 256, 0, st>>>(0, n_xml, d_xml_sha1, nullptr, D);
+    k_xsrc_probe<<<(unsigned)((n_dev + 255) / 256), 256, 0, st>>>(n_dev, d_dev_sha1, d_xml_sha1, D, d_match);
     ctx->launches += 2;
     CUDA_TRY(ctx, cudaGetLastError());
     return SMSGATE_OK;

@@ -180,3 +180,52 @@ def open_diskcache(path: str) -> Mapping[str, Any]:
     """The on-disk cache as the reference opens it (diskcache 5.6.3, pickled dicts)."""
     import diskcache
     return diskcache.Cache(path)
+
+
+# diskcache 5.6.3 storage modes (core.py: MODE_RAW .. MODE_PICKLE)
+_MODE_RAW, _MODE_BINARY, _MODE_TEXT, _MODE_PICKLE = 1, 2, 3, 4
+
+
+def read_diskcache_sqlite(path: str, now: Optional[float] = None) -> dict:
+    """the whole `.gemini_cache` in ONE query instead of two queries + one unpickle per
+    probe (libs/gemini_parser.py:208-209 through diskcache.Cache.__contains__ / __getitem__).
+
+    Reads diskcache's SQLite file directly — table `Cache(rowid, key, raw, store_time, expire_time,
+    access_time, access_count, tag, size, mode, filename, value)` — and returns `{key: value}` in rowid
+    order (diskcache's iteration order) for exactly the entries `key in cache` would answer True for:
+    string keys (stored as TEXT with raw = 1) whose expire_time is NULL or in the future.  Values are
+    decoded by mode the way `Disk.fetch` does: inline pickles, raw values, and pickles / blobs that
+    diskcache moved to files because they exceed 32 KiB.  The file is opened read-only."""
+    import os
+    import pickle
+    import sqlite3
+    import time
+    db = os.path.join(path, "cache.db")
+    if not os.path.exists(db):
+        raise FileNotFoundError(db)
+    now = time.time() if now is None else now
+    con = sqlite3.connect(f"file:{db}?mode=ro", uri=True, timeout=60)
+    try:
+        rows = con.execute(
+            "SELECT key, mode, filename, value FROM Cache "
+            "WHERE raw = 1 AND typeof(key) = 'text' AND (expire_time IS NULL OR expire_time > ?) ORDER BY rowid",
+            (now,)).fetchall()
+    finally:
+        con.close()
+    out = {}
+    loads = pickle.loads
+    for key, mode, filename, value in rows:
+        if mode == _MODE_PICKLE and filename is None:
+            out[key] = loads(value)
+        elif mode == _MODE_RAW:
+            out[key] = bytes(value) if isinstance(value, (bytes, memoryview)) else value
+        elif mode == _MODE_PICKLE:
+            with open(os.path.join(path, filename), "rb") as f:
+                out[key] = pickle.load(f)
+        elif mode == _MODE_BINARY:
+            with open(os.path.join(path, filename), "rb") as f:
+                out[key] = f.read()
+        elif mode == _MODE_TEXT:
+            with open(os.path.join(path, filename), "r", encoding="UTF-8") as f:
+                out[key] = f.read()
+    return out

@@ -216,6 +216,11 @@ class ReplayEngine:
 
     # -- cache -------------------------------------------------------------
     def load_cache(self, cache: "Mapping[str, Any] | CacheTable") -> CacheTable:
+        if isinstance(cache, (str, bytes)) or hasattr(cache, "__fspath__"):
+            # a `.gemini_cache` directory: one SQL query over diskcache's file (gemini_cache.read_diskcache_sqlite)
+            import os
+            from .gemini_cache import read_diskcache_sqlite
+            cache = read_diskcache_sqlite(os.fspath(cache))
         table = cache if isinstance(cache, CacheTable) else build_table(cache, self.strict_date_batch)
         keys = np.ascontiguousarray(table.keys)
         L.check(self._ctx, self._lib.smsgate_cache_load(
@@ -383,6 +388,39 @@ class ReplayEngine:
         out = self._dev_outputs(cols)
         L.check(self._ctx, self._lib.smsgate_scan_keys(self._ctx, d_bytes.data_ptr(), d_offsets.data_ptr(), n,
                                                        C.byref(out)))
+
+    def device_keys(self, d_bytes, d_offsets):
+        """MD5 of every body (device tensors in, uint8 [n, 16] device tensor out): the msg_id
+        `get_md5_hash` gives a device-sourced message (libs/models.py:97-109, api_gateway/main.py:113)."""
+        import torch
+        n = d_offsets.numel() - 1
+        out = torch.empty((max(n, 1), 16), dtype=torch.uint8, device=d_bytes.device)
+        L.check(self._ctx, self._lib.smsgate_device_keys(self._ctx, d_bytes.data_ptr(), d_offsets.data_ptr(), n,
+                                                         out.data_ptr()))
+        return out[:n]
+
+    def msg_ids_device(self, bodies: Sequence[str]) -> list:
+        """`get_md5_hash` over a list of bodies (hex strings), computed on the GPU."""
+        import torch
+        b = Batch.from_strings(bodies, None, None)
+        dev = torch.device("cuda", self.device)
+        d_bytes = torch.zeros(b.body_bytes.size + 64, dtype=torch.uint8, device=dev)
+        d_bytes[:b.body_bytes.size] = torch.from_numpy(np.ascontiguousarray(b.body_bytes)).to(dev)
+        d_off = torch.from_numpy(np.ascontiguousarray(b.body_offsets, dtype=np.int64)).to(dev)
+        out = self.device_keys(d_bytes, d_off).cpu().numpy()
+        return [row.tobytes().hex() for row in out]
+
+    def cross_source(self, d_xml_sha1, d_dev_sha1):
+        """For every device-sourced message (rows of d_dev_sha1, the SHA-1 of its body) the index of the
+        first XML message with the same body (rows of d_xml_sha1), or -1: the bodies the reference stores
+        twice because it keys the two sources differently."""
+        import torch
+        n_xml, n_dev = d_xml_sha1.shape[0], d_dev_sha1.shape[0]
+        self.reserve(max(n_xml, 1), 1)
+        match = torch.empty(max(n_dev, 1), dtype=torch.int32, device=d_dev_sha1.device)
+        L.check(self._ctx, self._lib.smsgate_cross_source(self._ctx, n_xml, d_xml_sha1.data_ptr(), n_dev,
+                                                          d_dev_sha1.data_ptr(), match.data_ptr()))
+        return match[:n_dev]
 
     def join_route(self, n: int, now: _dt.datetime, cols: dict) -> None:
         out = self._dev_outputs(cols)

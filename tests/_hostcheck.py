@@ -36,6 +36,15 @@ def scan(bodies):
     return cols
 
 
+def md5(bodies):
+    data, offsets = ragged_from_strings(bodies)
+    n = len(bodies)
+    out = np.zeros((n, 16), np.uint8)
+    data = np.concatenate([data, np.zeros(16, np.uint8)])
+    lib().hc_md5(_p(data), _p(offsets), C.c_int64(n), _p(out))
+    return out
+
+
 def decimal(strings):
     data, offsets = ragged_from_strings(strings, np.int32)
     n = len(strings)

@@ -3,6 +3,7 @@
 // so that `pytest -m "not gpu"` can check the device logic, bit for bit, against
 // the oracle and the golden vectors in a container without a GPU.  The shipped
 // library (libsmsgate_b200.so) has no CPU path; this file is not part of it.
+#include <cstring>
 #include <stdint.h>
 #include <string.h>
 #include <string>
@@ -52,6 +53,15 @@ extern "C" int hc_scan_keys(const uint8_t* bytes, const int64_t* offsets, int64_
         body_date[i] = sr.body_date;
         fixed_len[i] = flen;
         memcpy(fixed_bytes + offsets[i], m, flen);
+    }
+    return 0;
+}
+
+extern "C" int hc_md5(const uint8_t* bytes, const int64_t* offsets, int64_t n, uint8_t* md5) {
+    for (int64_t i = 0; i < n; ++i) {
+        uint32_t h[4];
+        sg_md5(bytes + offsets[i], (int)(offsets[i + 1] - offsets[i]), h);
+        memcpy(md5 + i * 16, h, 16);
     }
     return 0;
 }

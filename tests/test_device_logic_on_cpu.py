@@ -33,6 +33,20 @@ def test_scan_matches_reference_vectors(golden):
         assert int(cols["body_date"][i]) == want, c["body"]
 
 
+def test_device_key_md5_matches_reference_vectors(golden):
+    """get_md5_hash (libs/models.py:97-109): the reference's own outputs, then every padding boundary."""
+    import hashlib
+    cases = golden("keys.json")
+    got = H.md5([c["body"] for c in cases])
+    for i, c in enumerate(cases):
+        assert got[i].tobytes().hex() == c["md5"], c["body"]
+    edge = ["", "a", "x" * 55, "y" * 56, "z" * 57, "q" * 63, "r" * 64, "s" * 65, "t" * 119, "u" * 120, "v" * 121,
+            "\u043f\u0440\u0438\u0432\u0435\u0442 " * 40, "w" * 1000]
+    got = H.md5(edge)
+    for i, b in enumerate(edge):
+        assert got[i].tobytes() == hashlib.md5(b.encode()).digest() == O.msg_id_device(b), len(b)
+
+
 def test_decimals_match_reference_vectors(golden):
     rows = golden("decimals.json")
     coef, exp, flags = H.decimal([r[0] for r in rows])

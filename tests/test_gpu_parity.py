@@ -239,6 +239,35 @@ def test_packed_records_match_columns(engine):
     assert empty.n == 0 and len(empty.cols["status"]) == 0
 
 
+def test_device_keys_and_cross_source(engine, golden):
+    """MD5 device keys against the reference's vectors and the oracle, and the report of bodies that the
+    reference stores twice (same body seen from the XML backup and from a device)."""
+    import torch
+    cases = golden("keys.json")
+    assert engine.msg_ids_device([c["body"] for c in cases]) == [c["md5"] for c in cases]
+    backup = synth.generate(30_000, seed=41, mixed_locale=True)
+    got = engine.msg_ids_device(backup.bodies)
+    assert got == [O.msg_id_device(b).hex() for b in backup.bodies]
+    # device batch: every third XML body again (in another order) plus bodies the backup does not hold
+    rng = np.random.Generator(np.random.PCG64(7))
+    again = [int(i) for i in rng.permutation(len(backup.bodies))[:10_000]]
+    other = synth.generate(5_000, seed=42).bodies
+    dev_bodies = [backup.bodies[i] for i in again] + other
+    xml_set = {}
+    for i, b in enumerate(backup.bodies):
+        xml_set.setdefault(b, i)
+    want = np.array([xml_set.get(b, -1) for b in dev_bodies], np.int32)
+
+    def sha1_rows(bodies):
+        return torch.from_numpy(np.frombuffer(b"".join(O.msg_id_xml(b) for b in bodies), np.uint8)
+                                .reshape(len(bodies), 20).copy()).cuda()
+    match = engine.cross_source(sha1_rows(backup.bodies), sha1_rows(dev_bodies)).cpu().numpy()
+    assert np.array_equal(match, want)
+    assert (match >= 0).sum() >= 10_000
+    empty = engine.cross_source(sha1_rows(backup.bodies)[:0], sha1_rows(dev_bodies)).cpu().numpy()
+    assert np.all(empty == -1)
+
+
 def test_full_size_properties(engine):
     """BASELINE.json config 2 size (1 M messages, 100 % hit for non-OTP bodies):
     properties that do not need the oracle at full size, plus a 2 000-message
