@@ -277,8 +277,8 @@ int smsgate_dedup_apply(smsgate_ctx* ctx, int64_t n, int64_t base_index, int64_t
  * One process per GPU; every rank maps every other rank's inbox, arrival counters and
  * verdict arrays (e.g. through torch.distributed._symmetric_memory) and passes the
  * mapped pointers in `smsgate_p2p`.  smsgate_p2p_scatter stores the export records
- * straight into the owners' inboxes (one remote atomic per destination reserves the
- * range), smsgate_p2p_merge stores a verdict straight into the home rank's gfl array
+ * straight into the owners' inboxes (one remote atomic per block and destination reserves
+ * the range), smsgate_p2p_merge stores a verdict straight into the home rank's gfl array
  * whenever another rank's copy of the key changes it, smsgate_p2p_resolve rewrites
  * survivor / first_seen / last_idx.
  * The caller puts a cross-GPU barrier between scatter and merge and between merge and
@@ -291,12 +291,24 @@ typedef struct smsgate_p2p {
     int32_t* in_count[SMSGATE_MAX_WORLD]; /* [2] per rank, zero before the first batch */
     int64_t* gfl[SMSGATE_MAX_WORLD];      /* [2 * (pow2 >= 2 * max batch)] per rank: {first, last} per local slot, 16-byte aligned */
     int64_t capacity;                     /* records per inbox; world * max batch never overflows */
+    /* prefilter (optional, bitmap_words = 0 switches it off): only keys that two or more ranks hold are exchanged */
+    uint32_t* stage[SMSGATE_MAX_WORLD];   /* [world * (bitmap_words / world + 12)] words per rank: staged bitmap slices */
+    uint32_t* collide[SMSGATE_MAX_WORLD]; /* [bitmap_words] words per rank: bits set on two or more ranks */
+    int64_t bitmap_words;                 /* power of two in [64, 2^26]; about 16 bits per key of the whole job is plenty */
 } smsgate_p2p;
 /* Size the owner-side table for inboxes of `capacity` records.  Allocates. */
 int smsgate_p2p_reserve(smsgate_ctx* ctx, int64_t capacity);
 int smsgate_p2p_scatter(smsgate_ctx* ctx, int64_t n, int64_t base_index, int parity, const smsgate_outputs* out,
                         const smsgate_p2p* p);
 int smsgate_p2p_merge(smsgate_ctx* ctx, int parity, const smsgate_p2p* p);
+/* The prefilter, run before smsgate_p2p_scatter when the descriptor carries bitmaps: _filter_push marks this
+ * rank's keys in a bitmap and stores slice w of it into rank w's staging area; [barrier]; _filter_reduce turns
+ * the staged slices into "held by two or more ranks" and stores that slice into every rank's `collide`;
+ * [barrier]; smsgate_p2p_scatter then sends only keys whose bit is set.  False positives cost a record, there
+ * are no false negatives.  _reserve_filter allocates this rank's private bitmap. */
+int smsgate_p2p_reserve_filter(smsgate_ctx* ctx, int64_t bitmap_words);
+int smsgate_p2p_filter_push(smsgate_ctx* ctx, int64_t n, const smsgate_outputs* out, const smsgate_p2p* p);
+int smsgate_p2p_filter_reduce(smsgate_ctx* ctx, const smsgate_p2p* p);
 /* h_overflow (optional, host): set to 1 if an inbox ever overflowed; passing it synchronises. */
 int smsgate_p2p_resolve(smsgate_ctx* ctx, int64_t n, int64_t base_index, const smsgate_outputs* out,
                         const smsgate_p2p* p, int* h_overflow);

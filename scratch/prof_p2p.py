@@ -23,6 +23,14 @@ for it in range(8):
     eng.replay_device(d_bytes, d_off, NOW, cols, base_index=rank*n)
     out=eng._dev_outputs(cols); parity=ex.step&1
     torch.cuda.synchronize(); dist.barrier(); torch.cuda.synchronize()
+    ea=ev()
+    L.check(eng._ctx, lib.smsgate_p2p_filter_push(eng._ctx, n, C.byref(out), C.byref(ex.desc)))
+    eb=ev()
+    ex._h[1].barrier(channel=0)
+    ec=ev()
+    L.check(eng._ctx, lib.smsgate_p2p_filter_reduce(eng._ctx, C.byref(ex.desc)))
+    ed=ev()
+    ex._h[1].barrier(channel=1)
     e0=ev()
     L.check(eng._ctx, lib.smsgate_p2p_scatter(eng._ctx, n, rank*n, parity, C.byref(out), C.byref(ex.desc)))
     e1=ev()
@@ -36,5 +44,6 @@ for it in range(8):
     e5=ev()
     ex.step+=1
     torch.cuda.synchronize()
-    if rank==0 and it>=4: print('scatter %.0f bar %.0f merge %.0f bar %.0f resolve %.0f us'%tuple(a.elapsed_time(b_)*1e3 for a,b_ in [(e0,e1),(e1,e2),(e2,e3),(e3,e4),(e4,e5)]))
+    if rank==0 and it>=4: print('push %.0f bar %.0f reduce %.0f bar %.0f scatter %.0f bar %.0f merge %.0f bar %.0f resolve %.0f | total %.0f us'%tuple(a.elapsed_time(b_)*1e3 for a,b_ in [(ea,eb),(eb,ec),(ec,ed),(ed,e0),(e0,e1),(e1,e2),(e2,e3),(e3,e4),(e4,e5),(ea,e5)]))
+if rank==0: print('inbox count', int(ex._count[0]), int(ex._count[1]))
 dist.destroy_process_group()

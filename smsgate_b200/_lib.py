@@ -64,7 +64,8 @@ class P2P(C.Structure):
     """struct smsgate_p2p"""
     _fields_ = [("world", C.c_int32), ("rank", C.c_int32),
                 ("inbox", C.c_void_p * 64), ("in_count", C.c_void_p * 64),
-                ("gfl", C.c_void_p * 64), ("capacity", C.c_int64)]
+                ("gfl", C.c_void_p * 64), ("capacity", C.c_int64),
+                ("stage", C.c_void_p * 64), ("collide", C.c_void_p * 64), ("bitmap_words", C.c_int64)]
 
 
 class LibraryMissing(RuntimeError):
@@ -119,6 +120,9 @@ def lib():
         "smsgate_dedup_merge": (i32, [vp, i64, vp, vp]),
         "smsgate_dedup_apply": (i32, [vp, i64, i64, i64, vp, vp, C.POINTER(Outputs)]),
         "smsgate_p2p_reserve": (i32, [vp, i64]),
+        "smsgate_p2p_reserve_filter": (i32, [vp, i64]),
+        "smsgate_p2p_filter_push": (i32, [vp, i64, C.POINTER(Outputs), C.POINTER(P2P)]),
+        "smsgate_p2p_filter_reduce": (i32, [vp, C.POINTER(P2P)]),
         "smsgate_p2p_scatter": (i32, [vp, i64, i64, i32, C.POINTER(Outputs), C.POINTER(P2P)]),
         "smsgate_p2p_merge": (i32, [vp, i32, C.POINTER(P2P)]),
         "smsgate_p2p_resolve": (i32, [vp, i64, i64, C.POINTER(Outputs), C.POINTER(P2P), vp]),

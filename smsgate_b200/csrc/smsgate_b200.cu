@@ -661,6 +661,8 @@ struct smsgate_ctx {
     struct P2PSlot* p2p_table = nullptr;
     int32_t* p2p_slot_of = nullptr;
     int* p2p_overflow = nullptr;
+    uint32_t* p2p_bits = nullptr;                       // this rank's key bitmap (prefilter)
+    int64_t p2p_bits_words = 0;
     // owner-side merge table (smsgate_reserve_merge)
     int64_t mg_records = 0;
     uint64_t mg_cap = 0;
@@ -797,7 +799,7 @@ extern "C" void smsgate_destroy(smsgate_ctx* ctx) {
     free_cache(ctx);
     free_scratch(ctx);
     cudaFree(ctx->mg_owner); cudaFree(ctx->mg_first); cudaFree(ctx->mg_last); cudaFree(ctx->mg_slot_of);
-    cudaFree(ctx->p2p_table); cudaFree(ctx->p2p_slot_of); cudaFree(ctx->p2p_overflow);
+    cudaFree(ctx->p2p_table); cudaFree(ctx->p2p_slot_of); cudaFree(ctx->p2p_overflow); cudaFree(ctx->p2p_bits);
     cudaFree(ctx->d_legacy);
     cudaFree(ctx->xml_slab);
     cudaFree(ctx->d_tables);
@@ -1828,26 +1830,67 @@ struct P2PView {                 // smsgate_p2p, by value, for the kernels
     int32_t* in_count[SMSGATE_MAX_WORLD];
     longlong2* gfl[SMSGATE_MAX_WORLD];    // per local slot {global first, global last}
     int64_t capacity;
+    uint32_t* stage[SMSGATE_MAX_WORLD];   // prefilter: staged bitmap slices, one region per sending rank
+    uint32_t* collide[SMSGATE_MAX_WORLD]; // prefilter: bits set on two or more ranks
+    int64_t bitmap_words;                 // 0 = no prefilter
 };
 
-// one thread per destination: reserve a contiguous range in the owner's inbox with ONE remote atomic
-__global__ void k_p2p_reserve(P2PView P, int parity, const int* __restrict__ counts, int* __restrict__ cursor,
-                              int* __restrict__ overflow) {
-    const int w = threadIdx.x;
-    if (w == 0) P.in_count[P.rank][parity ^ 1] = 0;      // the counter of the step after this one
-    if (w >= P.world) return;
-    const int c = counts[w];
-    int base = 0;
-    if (c > 0) {
-        base = atomicAdd_system(&P.in_count[w][parity], c);
-        if ((int64_t)base + c > P.capacity) { atomicExch(overflow, 1); base = -1; }
-    }
-    cursor[w] = base;
+// ---- prefilter.  Only a key that occurs on two or more ranks needs the exchange; for every other key the
+// local dedup already holds the global answer.  Each rank marks its keys in a bitmap (32 bits of the SHA-1
+// that neither the table hash nor the owner prefix use), the bitmap is cut into one slice per rank, every
+// rank stores slice w into rank w's staging area, rank w ORs/ANDs the slices into "seen on >= 2 ranks" and
+// stores that slice back into everybody's `collide` bitmap.  A set bit can be a false positive (that key
+// is exchanged for nothing), never a false negative.  Cost: two bitmaps over NVLink instead of one 48-byte
+// record per distinct key - for a batch without cross-rank duplicates almost nothing is left to exchange.
+__device__ __forceinline__ int64_t slice_lo(int64_t words, int w, int world) { return (words * w / world) & ~(int64_t)3; }
+__device__ __forceinline__ int64_t slice_cap(int64_t words, int world) { return ((words + world - 1) / world + 8) & ~(int64_t)3; }
+__device__ __forceinline__ uint32_t key_bit(const uint8_t* key, int64_t words) {
+    return reinterpret_cast<const uint32_t*>(key)[2] & (uint32_t)(words * 32 - 1);
 }
 
 __global__ void __launch_bounds__(256)
-k_p2p_scatter(int64_t n, int64_t base_index, const uint8_t* __restrict__ msg_id, DedupScratch D, P2PView P,
-              int* __restrict__ cursor) {
+k_bits_build(int64_t n, const uint8_t* __restrict__ msg_id, const int32_t* __restrict__ slot_of, uint32_t* __restrict__ bits,
+             int64_t words) {
+    const int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+    if (i >= n || slot_of[i] < 0) return;                 // every upsert marks its key; duplicates mark the same bit
+    const uint32_t h = key_bit(msg_id + i * 20, words);
+    atomicOr(&bits[h >> 5], 1u << (h & 31));
+}
+__global__ void __launch_bounds__(256)
+k_bits_push(const uint32_t* __restrict__ bits, P2PView P) {
+    const int64_t nq = P.bitmap_words >> 2, cap = slice_cap(P.bitmap_words, P.world);
+    for (int64_t q = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; q < nq; q += (int64_t)gridDim.x * blockDim.x) {
+        const int64_t j = q << 2;
+        int w = (int)(j * P.world / P.bitmap_words);      // slice of word j (boundaries are rounded down to 4)
+        while (w + 1 < P.world && j >= slice_lo(P.bitmap_words, w + 1, P.world)) ++w;
+        while (w > 0 && j < slice_lo(P.bitmap_words, w, P.world)) --w;
+        const uint4 v = *reinterpret_cast<const uint4*>(bits + j);
+        *reinterpret_cast<uint4*>(P.stage[w] + P.rank * cap + (j - slice_lo(P.bitmap_words, w, P.world))) = v;   // peer store
+    }
+}
+__global__ void __launch_bounds__(256)
+k_bits_reduce(P2PView P) {
+    const int64_t lo = slice_lo(P.bitmap_words, P.rank, P.world);
+    const int64_t hi = P.rank + 1 == P.world ? P.bitmap_words : slice_lo(P.bitmap_words, P.rank + 1, P.world);
+    const int64_t cap = slice_cap(P.bitmap_words, P.world), nq = (hi - lo) >> 2;
+    const uint32_t* mine = P.stage[P.rank];
+    for (int64_t q = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; q < nq; q += (int64_t)gridDim.x * blockDim.x) {
+        uint4 one = make_uint4(0, 0, 0, 0), two = make_uint4(0, 0, 0, 0);
+        for (int r = 0; r < P.world; ++r) {
+            const uint4 x = *reinterpret_cast<const uint4*>(mine + r * cap + (q << 2));
+            two.x |= one.x & x.x; two.y |= one.y & x.y; two.z |= one.z & x.z; two.w |= one.w & x.w;
+            one.x |= x.x; one.y |= x.y; one.z |= x.z; one.w |= x.w;
+        }
+        for (int r = 0; r < P.world; ++r) *reinterpret_cast<uint4*>(P.collide[r] + lo + (q << 2)) = two;   // peer stores
+    }
+}
+
+// Records of this rank's distinct keys go straight into their owners' inboxes.  A block counts its records
+// per destination in shared memory and reserves its ranges with one remote atomic per destination; with the
+// prefilter only keys whose bit is set in `collide` are sent at all.
+__global__ void __launch_bounds__(256)
+k_p2p_scatter(int64_t n, int64_t base_index, int parity, const uint8_t* __restrict__ msg_id, DedupScratch D, P2PView P,
+              const uint32_t* __restrict__ collide, int* __restrict__ overflow) {
     __shared__ int hist[SMSGATE_MAX_WORLD];
     __shared__ int base[SMSGATE_MAX_WORLD];
     if (threadIdx.x < SMSGATE_MAX_WORLD) hist[threadIdx.x] = 0;
@@ -1855,9 +1898,20 @@ k_p2p_scatter(int64_t n, int64_t base_index, const uint8_t* __restrict__ msg_id,
     const int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
     int32_t sl = -1;
     int dest = 0, local = 0;
+    uint64_t f = 0, l = 0;
     if (i < n) {
         sl = D.slot_of[i];
         if (sl >= 0 && D.owner[sl] != (int32_t)i) sl = -1;
+        if (sl >= 0) {
+            f = (uint64_t)(base_index + D.first[sl]);
+            l = (uint64_t)(base_index + D.last[sl]);
+            // what this rank knows already; the owner only writes back when another rank changes it
+            P.gfl[P.rank][sl] = make_longlong2((long long)f, (long long)l);
+            if (collide) {
+                const uint32_t h = key_bit(msg_id + i * 20, P.bitmap_words);
+                if (!((collide[h >> 5] >> (h & 31)) & 1u)) sl = -1;          // no other rank can hold this key
+            }
+        }
         if (sl >= 0) {
             dest = key_owner(msg_id + i * 20, P.world);
             local = atomicAdd(&hist[dest], 1);
@@ -1865,13 +1919,14 @@ k_p2p_scatter(int64_t n, int64_t base_index, const uint8_t* __restrict__ msg_id,
     }
     __syncthreads();
     if (threadIdx.x < P.world && hist[threadIdx.x]) {
-        const int b = cursor[threadIdx.x];                 // -1 after an overflow: drop
-        base[threadIdx.x] = b < 0 ? -1 : atomicAdd(&cursor[threadIdx.x], hist[threadIdx.x]);
+        const int c = hist[threadIdx.x];
+        int b = atomicAdd_system(&P.in_count[threadIdx.x][parity], c);       // remote when the owner is a peer
+        if ((int64_t)b + c > P.capacity) { atomicExch(overflow, 1); b = -1; }
+        base[threadIdx.x] = b;
     }
     __syncthreads();
     if (sl < 0 || base[dest] < 0) return;
     const uint32_t* kw = reinterpret_cast<const uint32_t*>(msg_id + i * 20);
-    const uint64_t f = (uint64_t)(base_index + D.first[sl]), l = (uint64_t)(base_index + D.last[sl]);
     P2PRecord rec;
     rec.key[0] = kw[0]; rec.key[1] = kw[1]; rec.key[2] = kw[2]; rec.key[3] = kw[3]; rec.key[4] = kw[4];
     rec.first_lo = (uint32_t)f; rec.last_lo = (uint32_t)l;
@@ -1879,21 +1934,23 @@ k_p2p_scatter(int64_t n, int64_t base_index, const uint8_t* __restrict__ msg_id,
     rec.home_slot = (uint32_t)sl;
     rec.src_rank = (uint32_t)P.rank;
     rec.pad[0] = rec.pad[1] = 0;
-    // what this rank knows already; the owner only writes back when another rank changes it
-    P.gfl[P.rank][sl] = make_longlong2((long long)f, (long long)l);
     const uint4* src = reinterpret_cast<const uint4*>(&rec);
     uint4* dst = reinterpret_cast<uint4*>(&P.inbox[dest][base[dest] + local]);   // peer stores over NVLink when dest != rank
     dst[0] = src[0]; dst[1] = src[1]; dst[2] = src[2];
 }
 
+__device__ __forceinline__ int p2p_count(const int32_t* count_ptr, int64_t capacity) {
+    const int c = *count_ptr;                   // a refused reservation still advanced the counter
+    return (int64_t)c > capacity ? (int)capacity : c;
+}
 __device__ __forceinline__ uint64_t p2p_table_mask(int count) {
     uint64_t want = (uint64_t)(count > 8 ? count : 8) * 2, cap = 16;
     while (cap < want) cap <<= 1;
     return cap - 1;
 }
 __global__ void __launch_bounds__(256)
-k_p2p_clear(const int32_t* __restrict__ count_ptr, P2PSlot* __restrict__ table) {
-    const uint64_t cap = p2p_table_mask(*count_ptr) + 1;
+k_p2p_clear(const int32_t* __restrict__ count_ptr, int64_t capacity, P2PSlot* __restrict__ table) {
+    const uint64_t cap = p2p_table_mask(p2p_count(count_ptr, capacity)) + 1;
     for (uint64_t s = blockIdx.x * (uint64_t)blockDim.x + threadIdx.x; s < cap; s += (uint64_t)gridDim.x * blockDim.x) {
         P2PSlot e;
         e.owner = -1; e.pad = 0; e.first = ~0ull; e.last = 0; e.pad2 = 0;
@@ -1901,9 +1958,9 @@ k_p2p_clear(const int32_t* __restrict__ count_ptr, P2PSlot* __restrict__ table) 
     }
 }
 __global__ void __launch_bounds__(256)
-k_p2p_insert(const int32_t* __restrict__ count_ptr, const P2PRecord* __restrict__ recs, P2PSlot* __restrict__ table,
-             int32_t* __restrict__ slot_of) {
-    const int count = *count_ptr;
+k_p2p_insert(const int32_t* __restrict__ count_ptr, int64_t capacity, const P2PRecord* __restrict__ recs,
+             P2PSlot* __restrict__ table, int32_t* __restrict__ slot_of) {
+    const int count = p2p_count(count_ptr, capacity);
     const uint64_t mask = p2p_table_mask(count);
     for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < count; i += (int64_t)gridDim.x * blockDim.x) {
         const P2PRecord r = recs[i];
@@ -1924,8 +1981,10 @@ k_p2p_insert(const int32_t* __restrict__ count_ptr, const P2PRecord* __restrict_
 }
 __global__ void __launch_bounds__(256)
 k_p2p_verdict(const int32_t* __restrict__ count_ptr, const P2PRecord* __restrict__ recs,
-              const P2PSlot* __restrict__ table, const int32_t* __restrict__ slot_of, P2PView P) {
-    const int count = *count_ptr;
+              const P2PSlot* __restrict__ table, const int32_t* __restrict__ slot_of, P2PView P, int parity) {
+    const int count = p2p_count(count_ptr, P.capacity);
+    // the arrival counter of the NEXT batch: nobody scatters into it before the barrier that follows this kernel
+    if (blockIdx.x == 0 && threadIdx.x == 0) P.in_count[P.rank][parity ^ 1] = 0;
     for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < count; i += (int64_t)gridDim.x * blockDim.x) {
         const P2PSlot e = table[slot_of[i]];
         const P2PRecord r = recs[i];
@@ -1966,6 +2025,16 @@ static int p2p_view(smsgate_ctx* ctx, const smsgate_p2p* p, P2PView* v) {
         v->in_count[w] = p->in_count[w];
         v->gfl[w] = reinterpret_cast<longlong2*>(p->gfl[w]);
     }
+    v->bitmap_words = p->bitmap_words;
+    if (p->bitmap_words) {
+        if (p->bitmap_words < 64 || (p->bitmap_words & (p->bitmap_words - 1)) || p->bitmap_words > (1ll << 26))
+            return fail(ctx, SMSGATE_E_ARG, "p2p: bitmap_words must be a power of two in [64, 2^26]");
+        for (int w = 0; w < p->world; ++w) {
+            if (!p->stage[w] || !p->collide[w]) return fail(ctx, SMSGATE_E_ARG, "p2p: NULL prefilter pointer");
+            v->stage[w] = p->stage[w];
+            v->collide[w] = p->collide[w];
+        }
+    }
     return SMSGATE_OK;
 }
 
@@ -2000,14 +2069,58 @@ extern "C" int smsgate_p2p_scatter(smsgate_ctx* ctx, int64_t n, int64_t base_ind
     uint64_t cap = pow2_at_least((uint64_t)(n > 8 ? n : 8) * 2);
     if (cap > ctx->dd_cap) cap = ctx->dd_cap;
     DedupScratch D{ctx->d_owner, ctx->d_first, ctx->d_last, ctx->d_slot_of, cap - 1};
-    int* counts = ctx->d_counts;                       // [0, MAX_WORLD): counts, then cursors
-    CUDA_TRY(ctx, cudaMemsetAsync(counts, 0, sizeof(int) * SMSGATE_MAX_WORLD, st));
-    const unsigned grid = (unsigned)((n + 255) / 256);
-    if (n > 0) k_export_count<<<grid, 256, 0, st>>>(n, out->msg_id, D, V.world, counts);
-    k_p2p_reserve<<<1, SMSGATE_MAX_WORLD, 0, st>>>(V, parity & 1, counts, ctx->d_cursor, ctx->p2p_overflow);
-    if (n > 0) k_p2p_scatter<<<grid, 256, 0, st>>>(n, base_index, out->msg_id, D, V, ctx->d_cursor);
-    ctx->launches += n > 0 ? 3 : 1;
+    if (n > 0) {
+        k_p2p_scatter<<<(unsigned)((n + 255) / 256), 256, 0, st>>>(n, base_index, parity & 1, out->msg_id, D, V,
+                                                                   V.bitmap_words ? V.collide[V.rank] : nullptr,
+                                                                   ctx->p2p_overflow);
+        ctx->launches += 1;
+    }
     CUDA_TRY(ctx, cudaGetLastError());
+    return SMSGATE_OK;
+}
+
+extern "C" int smsgate_p2p_filter_push(smsgate_ctx* ctx, int64_t n, const smsgate_outputs* out, const smsgate_p2p* p) {
+    if (!ctx) return SMSGATE_E_ARG;
+    P2PView V;
+    int rc = p2p_view(ctx, p, &V);
+    if (rc) return rc;
+    if (!V.bitmap_words) return fail(ctx, SMSGATE_E_ARG, "p2p_filter_push: the descriptor has no prefilter bitmaps");
+    if (n < 0 || !out || (n > 0 && !out->msg_id)) return fail(ctx, SMSGATE_E_ARG, "p2p_filter_push: bad argument");
+    if (n > ctx->cap_msgs) return fail(ctx, SMSGATE_E_STATE, "p2p_filter_push: run smsgate_dedup on this batch first");
+    if (V.bitmap_words > ctx->p2p_bits_words) return fail(ctx, SMSGATE_E_STATE, "p2p_filter_push: call smsgate_p2p_reserve_filter first");
+    CUDA_TRY(ctx, cudaSetDevice(ctx->device));
+    cudaStream_t st = ctx->stream;
+    CUDA_TRY(ctx, cudaMemsetAsync(ctx->p2p_bits, 0, (size_t)V.bitmap_words * 4, st));
+    if (n > 0) k_bits_build<<<(unsigned)((n + 255) / 256), 256, 0, st>>>(n, out->msg_id, ctx->d_slot_of, ctx->p2p_bits, V.bitmap_words);
+    k_bits_push<<<(unsigned)ctx->sm_count * 4, 256, 0, st>>>(ctx->p2p_bits, V);
+    ctx->launches += n > 0 ? 2 : 1;
+    CUDA_TRY(ctx, cudaGetLastError());
+    return SMSGATE_OK;
+}
+
+extern "C" int smsgate_p2p_filter_reduce(smsgate_ctx* ctx, const smsgate_p2p* p) {
+    if (!ctx) return SMSGATE_E_ARG;
+    P2PView V;
+    int rc = p2p_view(ctx, p, &V);
+    if (rc) return rc;
+    if (!V.bitmap_words) return fail(ctx, SMSGATE_E_ARG, "p2p_filter_reduce: the descriptor has no prefilter bitmaps");
+    CUDA_TRY(ctx, cudaSetDevice(ctx->device));
+    k_bits_reduce<<<(unsigned)ctx->sm_count * 2, 256, 0, ctx->stream>>>(V);
+    ctx->launches += 1;
+    CUDA_TRY(ctx, cudaGetLastError());
+    return SMSGATE_OK;
+}
+
+extern "C" int smsgate_p2p_reserve_filter(smsgate_ctx* ctx, int64_t bitmap_words) {
+    if (!ctx) return SMSGATE_E_ARG;
+    if (bitmap_words < 0 || bitmap_words > (1ll << 26)) return fail(ctx, SMSGATE_E_LIMIT, "p2p_reserve_filter: at most 2^26 words");
+    if (bitmap_words <= ctx->p2p_bits_words) return SMSGATE_OK;
+    CUDA_TRY(ctx, cudaSetDevice(ctx->device));
+    CUDA_TRY(ctx, cudaStreamSynchronize(ctx->stream));
+    cudaFree(ctx->p2p_bits);
+    ctx->p2p_bits = nullptr; ctx->p2p_bits_words = 0;
+    CUDA_TRY(ctx, cudaMalloc(&ctx->p2p_bits, (size_t)bitmap_words * 4));
+    ctx->p2p_bits_words = bitmap_words;
     return SMSGATE_OK;
 }
 
@@ -2021,9 +2134,9 @@ extern "C" int smsgate_p2p_merge(smsgate_ctx* ctx, int parity, const smsgate_p2p
     cudaStream_t st = ctx->stream;
     const int32_t* cnt = V.in_count[V.rank] + (parity & 1);
     const unsigned grid = (unsigned)ctx->sm_count * 8;
-    k_p2p_clear<<<grid, 256, 0, st>>>(cnt, ctx->p2p_table);
-    k_p2p_insert<<<grid, 256, 0, st>>>(cnt, V.inbox[V.rank], ctx->p2p_table, ctx->p2p_slot_of);
-    k_p2p_verdict<<<grid, 256, 0, st>>>(cnt, V.inbox[V.rank], ctx->p2p_table, ctx->p2p_slot_of, V);
+    k_p2p_clear<<<grid, 256, 0, st>>>(cnt, V.capacity, ctx->p2p_table);
+    k_p2p_insert<<<grid, 256, 0, st>>>(cnt, V.capacity, V.inbox[V.rank], ctx->p2p_table, ctx->p2p_slot_of);
+    k_p2p_verdict<<<grid, 256, 0, st>>>(cnt, V.inbox[V.rank], ctx->p2p_table, ctx->p2p_slot_of, V, parity & 1);
     ctx->launches += 3;
     CUDA_TRY(ctx, cudaGetLastError());
     return SMSGATE_OK;

@@ -118,7 +118,7 @@ class GlobalDedupP2P:
     with torch's symmetric memory), with two cross-GPU barriers and no host
     synchronisation per batch.  Every rank must use the same `n_max`."""
 
-    def __init__(self, engine, dist, n_max: int, group=None):
+    def __init__(self, engine, dist, n_max: int, group=None, prefilter: bool = True):
         import torch
         import torch.distributed._symmetric_memory as symm_mem
         self.engine = engine
@@ -137,15 +137,32 @@ class GlobalDedupP2P:
         self._count = symm_mem.empty(16, dtype=torch.int32, device=dev)
         self._gfl = symm_mem.empty(2 * cap_slots, dtype=torch.int64, device=dev)
         self._count.zero_()
+        bufs = [self._inbox, self._count, self._gfl]
+        # prefilter bitmaps: about 16 bits per key of the whole job (a false positive only costs one record)
+        self.bitmap_words = 0
+        if prefilter and self.world > 1:
+            words = 64
+            while words * 32 < 16 * n_max * self.world and words < (1 << 26):
+                words <<= 1
+            self.bitmap_words = words
+            self._stage = symm_mem.empty(self.world * (words // self.world + 12), dtype=torch.int32, device=dev)
+            self._collide = symm_mem.empty(words, dtype=torch.int32, device=dev)
+            bufs += [self._stage, self._collide]
         torch.cuda.synchronize()
-        self._h = [symm_mem.rendezvous(t, group) for t in (self._inbox, self._count, self._gfl)]
+        self._h = [symm_mem.rendezvous(t, group) for t in bufs]
         self.desc = L.P2P()
         self.desc.world, self.desc.rank, self.desc.capacity = self.world, self.rank, self.capacity
+        self.desc.bitmap_words = self.bitmap_words
         for w in range(self.world):
             self.desc.inbox[w] = self._h[0].buffer_ptrs[w]
             self.desc.in_count[w] = self._h[1].buffer_ptrs[w]
             self.desc.gfl[w] = self._h[2].buffer_ptrs[w]
+            if self.bitmap_words:
+                self.desc.stage[w] = self._h[3].buffer_ptrs[w]
+                self.desc.collide[w] = self._h[4].buffer_ptrs[w]
         L.check(engine._ctx, L.lib().smsgate_p2p_reserve(engine._ctx, self.capacity))
+        if self.bitmap_words:
+            L.check(engine._ctx, L.lib().smsgate_p2p_reserve_filter(engine._ctx, self.bitmap_words))
         self._h[1].barrier(channel=0)          # every rank's counters are zero before anyone scatters
         self.step = 0
         self.launches = 0
@@ -157,6 +174,11 @@ class GlobalDedupP2P:
     def run_outputs(self, out: "L.Outputs", n: int, base_index: int) -> None:
         eng, lib = self.engine, L.lib()
         parity = self.step & 1
+        if self.bitmap_words:
+            L.check(eng._ctx, lib.smsgate_p2p_filter_push(eng._ctx, n, C.byref(out), C.byref(self.desc)))
+            self._h[1].barrier(channel=0)      # every rank's bitmap slices have landed at their owners
+            L.check(eng._ctx, lib.smsgate_p2p_filter_reduce(eng._ctx, C.byref(self.desc)))
+            self._h[1].barrier(channel=1)      # every rank holds the complete collision bitmap
         L.check(eng._ctx, lib.smsgate_p2p_scatter(eng._ctx, n, int(base_index), parity, C.byref(out), C.byref(self.desc)))
         self._h[1].barrier(channel=0)          # all records have landed in their owners' inboxes
         L.check(eng._ctx, lib.smsgate_p2p_merge(eng._ctx, parity, C.byref(self.desc)))

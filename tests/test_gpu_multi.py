@@ -90,7 +90,7 @@ def test_ranks_emulated_on_one_gpu(world):
     assert np.array_equal(np.concatenate(got_l), want_l)
 
 
-def _nccl_worker(rank, world, port, n_per, q, p2p=False):
+def _nccl_worker(rank, world, port, n_per, q, p2p=False, prefilter=True):
     import torch
     import torch.distributed as dist
 
@@ -110,7 +110,7 @@ def _nccl_worker(rank, world, port, n_per, q, p2p=False):
         d_off = torch.from_numpy(b.body_offsets.copy()).cuda()
         c = eng.device_columns(b.n, d_bytes.numel())
         eng.reserve(b.n, d_bytes.numel())
-        ex = (GlobalDedupP2P if p2p else GlobalDedup)(eng, dist, b.n)
+        ex = GlobalDedupP2P(eng, dist, b.n, prefilter=prefilter) if p2p else GlobalDedup(eng, dist, b.n)
         for _ in range(3 if p2p else 1):                 # several batches: counters alternate, inboxes are reused
             eng.replay_device(d_bytes, d_off, NOW, c, base_index=lo)
             ex.run(c, lo)
@@ -124,8 +124,8 @@ def _nccl_worker(rank, world, port, n_per, q, p2p=False):
 
 
 @pytest.mark.timeout(600)
-@pytest.mark.parametrize("p2p,world", [(False, 2), (True, 2), (True, 1)])
-def test_ranks_over_nccl_or_peer_memory(p2p, world):
+@pytest.mark.parametrize("p2p,world,prefilter", [(False, 2, False), (True, 2, True), (True, 2, False), (True, 1, True)])
+def test_ranks_over_nccl_or_peer_memory(p2p, world, prefilter):
     import torch
     if torch.cuda.device_count() < world:
         pytest.skip("needs two GPUs")
@@ -134,7 +134,7 @@ def test_ranks_over_nccl_or_peer_memory(p2p, world):
     ctx = mp.get_context("spawn")
     q = ctx.Queue()
     s = socket.socket(); s.bind(("127.0.0.1", 0)); port = s.getsockname()[1]; s.close()
-    procs = [ctx.Process(target=_nccl_worker, args=(r, world, port, n_per, q, p2p)) for r in range(world)]
+    procs = [ctx.Process(target=_nccl_worker, args=(r, world, port, n_per, q, p2p, prefilter)) for r in range(world)]
     for p in procs:
         p.start()
     res = sorted((q.get(timeout=500) for _ in range(world)), key=lambda t: t[0])
