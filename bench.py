@@ -201,6 +201,9 @@ def run_ours(args, rank, world, local_rank):
     from smsgate_b200.batch import Batch
     from smsgate_b200.replay import ReplayEngine
 
+    # pinned staging buffers next to the GPU: bind before anything is allocated (smsgate_b200/numa.py)
+    from smsgate_b200.numa import bind_to_gpu
+    bound = bind_to_gpu(local_rank)
     torch.cuda.set_device(local_rank)
     dist = None
     if world > 1:
@@ -306,13 +309,16 @@ def run_ours(args, rank, world, local_rank):
     except Exception:
         pass
     cpu_cores = 1
-    cpu_val, cpu_ms, cpu_n = cpu_arm(backup, args.cpu_sample, cpu_cores, 1, 0)
+    cpu_val = cpu_n = None
+    if world == 1:                     # the CPU baseline is reported at N=1 only
+        cpu_val, cpu_ms, cpu_n = cpu_arm(backup, args.cpu_sample, cpu_cores, 1, 0)
     line = {
         "metric": METRIC, "value": world * n / (step * 1e-3), "unit": UNIT, "n_gpus": world, "steps": args.steps,
         "warmup": args.warmup, "ms_per_step": step, "higher_is_better": True, "scaling": "weak",
         "vs_baseline": None, "dtype": "u8/u32/int64", "data": "synthetic",
         "config": {"workload": workload_name(n), "msgs_per_gpu": n, "mean_body_bytes": round(mean_len, 1),
                    "cache_entries": len(backup.cache), "l2": "512 MiB buffer written between timed steps",
+                   "host_cpus_bound": (len(bound) if bound else None),
                    "parallelism": f"shard-by-index x{world}" + (f", {type(exchange).__name__} exchange by msg_id prefix" if world > 1 else "")},
         "clocks": clocks,
         "e2e": {"value": world * n / (e2e * 1e-3), "unit": UNIT, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
@@ -323,9 +329,9 @@ def run_ours(args, rank, world, local_rank):
                      "kernel_ms": k1, "kernel_share_of_step": k1 / step,
                      "note": "SHA-1 + SHA-256 rounds make this kernel integer-ALU bound, not HBM bound (DESIGN.md)",
                      "path_algorithmic_gbs": n * (mean_len + 229) / (step * 1e-3) / 1e9},
-        "cpu_baseline": {"value": cpu_val, "unit": UNIT, "cores": cpu_cores, "kind": "port",
-                         "sample": f"{cpu_n} messages of the same workload, bodies in memory, oracle port with a "
-                                   f"diskcache-backed response cache, single process"},
+        "cpu_baseline": ({"value": cpu_val, "unit": UNIT, "cores": cpu_cores, "kind": "port",
+                          "sample": f"{cpu_n} messages of the same workload, bodies in memory, oracle port with a "
+                                    f"diskcache-backed response cache, single process"} if world == 1 else None),
         "upserts_per_gpu": upserts_local,
     }
     print(json.dumps(line), flush=True)

@@ -157,6 +157,12 @@ int smsgate_decimal_batch(smsgate_ctx* ctx, int64_t n, const int32_t* h_offsets,
  * string needs the reference's strptime/dateutil chain on the host. */
 int smsgate_strict_date_batch(smsgate_ctx* ctx, int64_t n, const int32_t* h_offsets, const uint8_t* h_bytes,
                               int64_t* h_packed);
+/* `_dt_str(date, time_)` of save_to_pocketbase.py:34-43 over a ragged batch of the strings
+ * f"{date} {time_}": packed datetime (same packing as smsgate_outputs.date) of the first of the six
+ * formats %d.%m.%Y, %d/%m/%Y, %d-%m-%Y, %d.%m.%y, %d/%m/%y, %d-%m-%y (+ " %H:%M") that
+ * datetime.strptime accepts, 0 where it returns None.  Host arrays; allocates temporaries. */
+int smsgate_dt_str_batch(smsgate_ctx* ctx, int64_t n, const int32_t* h_offsets, const uint8_t* h_bytes,
+                         int64_t* h_packed);
 
 /* ---- XML backup -> ragged batch on the GPU -----------------------------------
  * Replaces, for a whole backup file at once, `ET.parse(path)` + `root.findall("sms")` +

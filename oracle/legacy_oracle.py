@@ -92,3 +92,38 @@ def process_body(body: Optional[str]):
 
 def f64_bits(x: float) -> int:
     return struct.unpack("<Q", struct.pack("<d", x))[0]
+
+
+# ---------------------------------------------------------------------------
+# save_to_pocketbase.py:34-78 — the PocketBase record builders of the legacy caches.  (The module cannot be
+# imported: its line 17 `from pocketbase import ` is a syntax error in the reference itself.  The golden
+# vectors are produced by oracle/gen_golden_pb.py from the text of lines 34-78 executed as they stand.)
+# ---------------------------------------------------------------------------
+def dt_str(date, time_):                                             # :34-43
+    from datetime import datetime
+    for fmt in ("%d.%m.%Y", "%d/%m/%Y", "%d-%m-%Y", "%d.%m.%y", "%d/%m/%y", "%d-%m-%y"):
+        try:
+            dt = datetime.strptime(f"{date} {time_}", f"{fmt} %H:%M")
+            return dt.strftime("%Y-%m-%d %H:%M:%S")
+        except ValueError:
+            continue
+    return None
+
+
+def build_sms_data(record):                                          # :46-62
+    pb_dt = dt_str(record.get("date", ""), record.get("time", ""))
+    if not pb_dt:
+        return None
+    return {"merchant": record.get("merchant"), "city": record.get("city"), "address": record.get("address"),
+            "datetime": pb_dt, "card": record.get("card"), "amount": str(record.get("amount", 0.0)),
+            "currency": record.get("currency"), "balance": str(record.get("balance", 0.0)),
+            "msg_id": record.get("msg_id"), "original_body": record.get("original_body")}
+
+
+def build_transactions(record):                                      # :65-78
+    pb_dt = dt_str(record.get("date", ""), record.get("time", ""))
+    if not pb_dt:
+        return None
+    return {"transaction_id": record.get("msg_id"), "transaction_type": record.get("type", record.get("direction")),
+            "amount": record.get("amount"), "currency": record.get("currency"), "balance_after": record.get("balance"),
+            "timestamp": pb_dt, "status": "parsed"}

@@ -97,6 +97,7 @@ def lib():
         "smsgate_cache_size": (i64, [vp]),
         "smsgate_decimal_batch": (i32, [vp, i64, vp, vp, vp, vp, vp]),
         "smsgate_strict_date_batch": (i32, [vp, i64, vp, vp, vp]),
+        "smsgate_dt_str_batch": (i32, [vp, i64, vp, vp, vp]),
         "smsgate_xml_scan": (i32, [vp, vp, i64, vp, vp, vp, vp]),
         "smsgate_xml_emit": (i32, [vp, vp, vp, vp, vp, vp, vp]),
         "smsgate_xml_release": (i32, [vp]),

@@ -7,9 +7,9 @@ from typing import Iterable, Optional, Sequence
 import numpy as np
 
 
-def ragged_from_strings(strings: Sequence[str], offset_dtype=np.int64):
+def ragged_from_strings(strings: Sequence[str], offset_dtype=np.int64, errors: str = "strict"):
     """UTF-8 encode and concatenate.  Returns (bytes uint8[total], offsets[n+1])."""
-    enc = [s.encode("utf-8") for s in strings]
+    enc = [s.encode("utf-8", errors) for s in strings]
     offsets = np.zeros(len(enc) + 1, dtype=offset_dtype)
     if enc:
         np.cumsum(np.fromiter((len(b) for b in enc), dtype=np.int64, count=len(enc)), out=offsets[1:])

@@ -267,3 +267,121 @@ SG_HD LegacyResult sg_legacy_process(const uint8_t* body, int len, const LegacyT
     }
     return r;
 }
+
+// ---------------------------------------------------------------------------
+// save_to_pocketbase.py:34-43, `_dt_str(date, time_)`: datetime.strptime(f"{date} {time_}", f"{fmt} %H:%M")
+// for fmt in %d.%m.%Y, %d/%m/%Y, %d-%m-%Y, %d.%m.%y, %d/%m/%y, %d-%m-%y; the first that parses wins.
+// CPython turns such a format into the regular expression (Lib/_strptime.py, TimeRE)
+//     (3[0-1]|[1-2]\d|0[1-9]|[1-9]| [1-9]) SEP (1[0-2]|0[1-9]|[1-9]) SEP (\d\d\d\d | \d\d) \s+
+//     (2[0-3]|[0-1]\d|\d) : ([0-5]\d|\d)
+// matches it at the start of the string (first alternative first, backtracking), demands that the match
+// ends where the string ends, converts the groups with int() and builds a datetime (calendar validity,
+// year >= 1; %y pivots at 69).  \d and \s are the Unicode classes, the bracketed digits are ASCII.
+// Returns the packed datetime, 0 where every format raises.
+// ---------------------------------------------------------------------------
+struct DtCursor {
+    const uint8_t* s;
+    int len;
+    const ScanTables* T;
+    // code point at byte offset p: returns its length in bytes (0 at the end), *cp the code point
+    SG_HD int at(int p, uint32_t* cp) const {
+        if (p >= len) return 0;
+        return sg_utf8_decode(s + p, len - p, cp);
+    }
+    // a \d at p: digit value or -1; *nb the bytes it occupies
+    SG_HD int digit(int p, int* nb) const {
+        uint32_t cp;
+        *nb = at(p, &cp);
+        if (*nb == 0) return -1;
+        return sg_digit_value(cp, T->t->digit_run_start, T->t->digit_run_len);
+    }
+    SG_HD int ascii(int p) const { return p < len ? (int)s[p] : -1; }
+};
+
+// the alternatives of one numeric field, tried in the regular expression's order; alternative `k` of
+// field `f` matched at `p` -> value and end offset, or false
+SG_HD bool sg_dt_alt(const DtCursor& C, int field, int k, int p, int* val, int* end) {
+    const int c0 = C.ascii(p), c1 = C.ascii(p + 1);
+    int nb, d;
+    switch (field) {
+        case 0:     // %d
+            if (k == 0) { if (c0 == '3' && (c1 == '0' || c1 == '1')) { *val = 30 + c1 - '0'; *end = p + 2; return true; } return false; }
+            if (k == 1) { if (c0 == '1' || c0 == '2') { d = C.digit(p + 1, &nb); if (d >= 0) { *val = (c0 - '0') * 10 + d; *end = p + 1 + nb; return true; } } return false; }
+            if (k == 2) { if (c0 == '0' && c1 >= '1' && c1 <= '9') { *val = c1 - '0'; *end = p + 2; return true; } return false; }
+            if (k == 3) { if (c0 >= '1' && c0 <= '9') { *val = c0 - '0'; *end = p + 1; return true; } return false; }
+            if (k == 4) { if (c0 == ' ' && c1 >= '1' && c1 <= '9') { *val = c1 - '0'; *end = p + 2; return true; } return false; }
+            return false;
+        case 1:     // %m
+            if (k == 0) { if (c0 == '1' && c1 >= '0' && c1 <= '2') { *val = 10 + c1 - '0'; *end = p + 2; return true; } return false; }
+            if (k == 1) { if (c0 == '0' && c1 >= '1' && c1 <= '9') { *val = c1 - '0'; *end = p + 2; return true; } return false; }
+            if (k == 2) { if (c0 >= '1' && c0 <= '9') { *val = c0 - '0'; *end = p + 1; return true; } return false; }
+            return false;
+        case 2:     // %H
+            if (k == 0) { if (c0 == '2' && c1 >= '0' && c1 <= '3') { *val = 20 + c1 - '0'; *end = p + 2; return true; } return false; }
+            if (k == 1) { if (c0 == '0' || c0 == '1') { d = C.digit(p + 1, &nb); if (d >= 0) { *val = (c0 - '0') * 10 + d; *end = p + 1 + nb; return true; } } return false; }
+            if (k == 2) { d = C.digit(p, &nb); if (d >= 0) { *val = d; *end = p + nb; return true; } return false; }
+            return false;
+        default:    // %M
+            if (k == 0) { if (c0 >= '0' && c0 <= '5') { d = C.digit(p + 1, &nb); if (d >= 0) { *val = (c0 - '0') * 10 + d; *end = p + 1 + nb; return true; } } return false; }
+            if (k == 1) { d = C.digit(p, &nb); if (d >= 0) { *val = d; *end = p + nb; return true; } return false; }
+            return false;
+    }
+}
+
+// one format: separator `sep`, `ydigits` 4 (%Y) or 2 (%y).  The first complete match of the regular
+// expression in backtracking order decides; returns the packed datetime or 0.
+SG_HD int64_t sg_dt_try(const DtCursor& C, int sep, int ydigits) {
+    for (int kd = 0; kd < 5; ++kd) {
+        int day, p1;
+        if (!sg_dt_alt(C, 0, kd, 0, &day, &p1) || C.ascii(p1) != sep) continue;
+        for (int km = 0; km < 3; ++km) {
+            int mon, p2;
+            if (!sg_dt_alt(C, 1, km, p1 + 1, &mon, &p2) || C.ascii(p2) != sep) continue;
+            int year = 0, p3 = p2 + 1;
+            bool ok = true;
+            for (int k = 0; k < ydigits; ++k) {
+                int nb;
+                const int d = C.digit(p3, &nb);
+                if (d < 0) { ok = false; break; }
+                year = year * 10 + d;
+                p3 += nb;
+            }
+            if (!ok) continue;
+            int p4 = p3;                                   // \s+ (greedy; the hour starts with a digit, so
+            for (;;) {                                     //  giving white space back never helps)
+                uint32_t cp;
+                const int nb = C.at(p4, &cp);
+                if (nb == 0 || !sg_is_space(cp)) break;
+                p4 += nb;
+            }
+            if (p4 == p3) continue;
+            for (int kh = 0; kh < 3; ++kh) {
+                int hour, p5;
+                if (!sg_dt_alt(C, 2, kh, p4, &hour, &p5) || C.ascii(p5) != ':') continue;
+                for (int kn = 0; kn < 2; ++kn) {
+                    int minute, p6;
+                    if (!sg_dt_alt(C, 3, kn, p5 + 1, &minute, &p6)) continue;
+                    // re.match found its match: everything after this is strptime's own checking
+                    if (p6 != C.len) return 0;                                  // "unconverted data remains"
+                    if (ydigits == 2) year += (year < 69) ? 2000 : 1900;
+                    if (year < 1) return 0;                                     // datetime.MINYEAR
+                    if (day > sg_days_in_month(year, mon)) return 0;
+                    return sg_pack_datetime(year, mon, day, hour, minute, 0, 0);
+                }
+            }
+        }
+    }
+    return 0;
+}
+
+SG_HD int64_t sg_dt_str(const uint8_t* s, int len, const ScanTables& T) {
+    DtCursor C;
+    C.s = s; C.len = len; C.T = &T;
+    const int seps[3] = {'.', '/', '-'};
+    for (int yd = 4; yd >= 2; yd -= 2)
+        for (int k = 0; k < 3; ++k) {
+            const int64_t v = sg_dt_try(C, seps[k], yd);
+            if (v) return v;
+        }
+    return 0;
+}

@@ -593,6 +593,15 @@ k_xsrc_probe(int64_t n_dev, const uint8_t* __restrict__ dev_sha1, const uint8_t*
     match[i] = found;
 }
 
+__global__ void k_dt_str_batch(int64_t n, const int32_t* __restrict__ offsets, const uint8_t* __restrict__ bytes,
+                               const DeviceTables* __restrict__ tab, int64_t* packed) {
+    const int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    ScanTables T;
+    T.t = tab;
+    packed[i] = sg_dt_str(bytes + offsets[i], offsets[i + 1] - offsets[i], T);
+}
+
 // ------------------------------------------------------------------ legacy offline replay (process_cached.py)
 struct LegacyOut {
     uint8_t* status; uint8_t* lflags; int32_t* strip; int32_t* caps; double* amount; double* balance; uint8_t* body_hash;
@@ -943,6 +952,32 @@ extern "C" int smsgate_strict_date_batch(smsgate_ctx* ctx, int64_t n, const int3
     HB_TRY(cudaMemcpyAsync(d_off, h_offsets, (size_t)(n + 1) * 4, cudaMemcpyHostToDevice, st));
     if (nb) HB_TRY(cudaMemcpyAsync(d_b, h_bytes, (size_t)nb, cudaMemcpyHostToDevice, st));
     k_strict_date_batch<<<(unsigned)((n + 255) / 256), 256, 0, st>>>(n, d_off, d_b, d_p);
+    ctx->launches += 1;
+    HB_TRY(cudaMemcpyAsync(h_packed, d_p, (size_t)n * 8, cudaMemcpyDeviceToHost, st));
+    HB_TRY(cudaStreamSynchronize(st));
+    HB_TRY(cudaGetLastError());
+done:
+    cudaFree(d_off); cudaFree(d_b); cudaFree(d_p);
+    return rc;
+}
+
+extern "C" int smsgate_dt_str_batch(smsgate_ctx* ctx, int64_t n, const int32_t* h_offsets, const uint8_t* h_bytes,
+                                         int64_t* h_packed) {
+    if (!ctx) return SMSGATE_E_ARG;
+    if (n < 0 || (n > 0 && (!h_offsets || !h_packed))) return fail(ctx, SMSGATE_E_ARG, "dt_str_batch: NULL array");
+    if (n == 0) return SMSGATE_OK;
+    CUDA_TRY(ctx, cudaSetDevice(ctx->device));
+    const int64_t nb = h_offsets[n];
+    int32_t* d_off = nullptr; uint8_t* d_b = nullptr; int64_t* d_p = nullptr;
+    cudaStream_t st = ctx->stream;
+    int rc = SMSGATE_OK;
+    cudaError_t e;
+    HB_TRY(cudaMalloc(&d_off, (size_t)(n + 1) * 4));
+    HB_TRY(cudaMalloc(&d_b, (size_t)nb + 16));
+    HB_TRY(cudaMalloc(&d_p, (size_t)n * 8));
+    HB_TRY(cudaMemcpyAsync(d_off, h_offsets, (size_t)(n + 1) * 4, cudaMemcpyHostToDevice, st));
+    if (nb) HB_TRY(cudaMemcpyAsync(d_b, h_bytes, (size_t)nb, cudaMemcpyHostToDevice, st));
+    k_dt_str_batch<<<(unsigned)((n + 255) / 256), 256, 0, st>>>(n, d_off, d_b, ctx->d_tables, d_p);
     ctx->launches += 1;
     HB_TRY(cudaMemcpyAsync(h_packed, d_p, (size_t)n * 8, cudaMemcpyDeviceToHost, st));
     HB_TRY(cudaStreamSynchronize(st));

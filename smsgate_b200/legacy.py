@@ -125,3 +125,61 @@ def process_sms_from_cache(engine, source_dir: str, purchase_dest_dir: str, cred
                 stats["failed"] += 1
             source.set(key, data)                                         # :263
     return stats
+
+
+# ---------------------------------------------------------------------------
+# save_to_pocketbase.py:34-78 — PocketBase record builders over the legacy caches, in bulk
+# ---------------------------------------------------------------------------
+def dt_str_batch(engine, pairs: Sequence[tuple]) -> list:
+    """`_dt_str(date, time_)` (save_to_pocketbase.py:34-43) for a list of (date, time_) pairs: the six
+    strptime formats are evaluated on the GPU (smsgate_dt_str_batch), the text is laid out here the way
+    `strftime("%Y-%m-%d %H:%M:%S")` does on glibc (the year is not zero-padded)."""
+    import ctypes as C
+
+    import numpy as np
+
+    from . import _lib as L
+    from .batch import ragged_from_strings
+    from .gemini_cache import unpack_datetime
+    strings = [f"{d} {t}" for d, t in pairs]
+    if not strings:
+        return []
+    data, offsets = ragged_from_strings(strings, np.int32, errors="surrogatepass")
+    packed = np.zeros(len(strings), dtype=np.int64)
+    data = np.concatenate([data, np.zeros(16, np.uint8)])
+    L.check(engine._ctx, L.lib().smsgate_dt_str_batch(engine._ctx, len(strings), offsets.ctypes.data_as(C.c_void_p),
+                                                      data.ctypes.data_as(C.c_void_p),
+                                                      packed.ctypes.data_as(C.c_void_p)))
+    out = []
+    for p in packed:
+        if p == 0:
+            out.append(None)
+        else:
+            d = unpack_datetime(int(p))
+            out.append(f"{d.year}-{d.month:02d}-{d.day:02d} {d.hour:02d}:{d.minute:02d}:00")
+    return out
+
+
+def build_sms_data(engine, records: Sequence[Dict[str, Any]]) -> list:
+    """`_build_sms_data` (save_to_pocketbase.py:46-62) for every record of the purchase cache: the payload
+    for the `sms_data` collection, or None where the date does not parse."""
+    dts = dt_str_batch(engine, [(r.get("date", ""), r.get("time", "")) for r in records])
+    out = []
+    for r, pb_dt in zip(records, dts):
+        out.append(None if not pb_dt else {
+            "merchant": r.get("merchant"), "city": r.get("city"), "address": r.get("address"), "datetime": pb_dt,
+            "card": r.get("card"), "amount": str(r.get("amount", 0.0)), "currency": r.get("currency"),
+            "balance": str(r.get("balance", 0.0)), "msg_id": r.get("msg_id"), "original_body": r.get("original_body")})
+    return out
+
+
+def build_transactions(engine, records: Sequence[Dict[str, Any]]) -> list:
+    """`_build_transactions` (save_to_pocketbase.py:65-78) for every record of the credit cache."""
+    dts = dt_str_batch(engine, [(r.get("date", ""), r.get("time", "")) for r in records])
+    out = []
+    for r, pb_dt in zip(records, dts):
+        out.append(None if not pb_dt else {
+            "transaction_id": r.get("msg_id"), "transaction_type": r.get("type", r.get("direction")),
+            "amount": r.get("amount"), "currency": r.get("currency"), "balance_after": r.get("balance"),
+            "timestamp": pb_dt, "status": "parsed"})
+    return out

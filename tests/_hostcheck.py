@@ -63,6 +63,14 @@ def strict_date(strings):
     return out
 
 
+def dt_str(strings):
+    data, offsets = ragged_from_strings(strings, np.int32)
+    out = np.zeros(len(strings), np.int64)
+    data = np.concatenate([data, np.zeros(16, np.uint8)])
+    lib().hc_dt_str(C.c_int64(len(strings)), _p(offsets), _p(data), _p(out))
+    return out
+
+
 def join_route(scan_cols, table, now_packed):
     n = len(scan_cols["flags"])
     cols = dict(slot=np.zeros(n, np.int32), status=np.zeros(n, np.uint8), amount_coef=np.zeros(n, np.int64),

@@ -80,6 +80,12 @@ extern "C" int hc_strict_date(int64_t n, const int32_t* offsets, const uint8_t* 
     return 0;
 }
 
+extern "C" int hc_dt_str(int64_t n, const int32_t* offsets, const uint8_t* bytes, int64_t* packed) {
+    const ScanTables T = host_tables();
+    for (int64_t i = 0; i < n; ++i) packed[i] = sg_dt_str(bytes + offsets[i], offsets[i + 1] - offsets[i], T);
+    return 0;
+}
+
 extern "C" int hc_join_route(int64_t n, const uint8_t* cache_key, const uint8_t* flags, const int32_t* body_date,
                              int64_t now_packed, int64_t m, const uint8_t* keys, const int32_t* val_offsets,
                              const uint8_t* val_bytes, const uint16_t* eflags, const int64_t* date_packed,

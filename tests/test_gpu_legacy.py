@@ -161,3 +161,14 @@ def test_xml_to_replay_on_device(engine, tmp_path):
     for name in ("msg_id", "cache_key", "status", "survivor", "amount_coef", "date"):
         assert np.array_equal(cols[name].cpu().numpy(), host.cols[name]), name
     assert np.array_equal(d["date_ms"].cpu().numpy(), np.array(backup.date_ms))
+
+
+def test_pb_builders_match_reference_vectors(engine, golden):
+    """save_to_pocketbase.py:34-78 in bulk: `_dt_str` on the GPU, the payload dicts around it."""
+    from smsgate_b200 import legacy
+    g = golden("pb_builders.json")
+    got = legacy.dt_str_batch(engine, [(d, t) for d, t, _ in g["dt_str"]])
+    assert got == [w for _, _, w in g["dt_str"]]
+    assert legacy.build_sms_data(engine, [r for r, _ in g["sms_data"]]) == [w for _, w in g["sms_data"]]
+    assert legacy.build_transactions(engine, [r for r, _ in g["transactions"]]) == [w for _, w in g["transactions"]]
+    assert legacy.dt_str_batch(engine, []) == []

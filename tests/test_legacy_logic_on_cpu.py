@@ -106,3 +106,31 @@ def test_differential_fuzz_against_re():
                 s[k] = rnd.choice(" ,.:*\n9aA")
         bodies.append("".join(s))
     check_against_oracle(_res(bodies), bodies)
+
+
+def test_dt_str_matches_reference_vectors(golden):
+    """save_to_pocketbase.py:34-43 executed from the reference's text (oracle/gen_golden_pb.py) against the
+    device function compiled for the CPU and against the oracle restatement."""
+    from oracle import legacy_oracle as LO
+    from smsgate_b200.gemini_cache import unpack_datetime
+    from tests import _hostcheck as H
+    g = golden("pb_builders.json")["dt_str"]
+    packed = H.dt_str([f"{d} {t}" for d, t, _ in g])
+    for (d, t, want), p in zip(g, packed):
+        assert LO.dt_str(d, t) == want, (d, t)
+        if p == 0:
+            got = None
+        else:
+            x = unpack_datetime(int(p))
+            got = f"{x.year}-{x.month:02d}-{x.day:02d} {x.hour:02d}:{x.minute:02d}:00"
+        assert got == want, (d, t)
+    assert sum(1 for _, _, w in g if w) > 500 and sum(1 for _, _, w in g if not w) > 300
+
+
+def test_pb_builders_oracle_matches_reference_vectors(golden):
+    from oracle import legacy_oracle as LO
+    g = golden("pb_builders.json")
+    for r, want in g["sms_data"]:
+        assert LO.build_sms_data(r) == want
+    for r, want in g["transactions"]:
+        assert LO.build_transactions(r) == want
