@@ -27,10 +27,16 @@ SG_HD DecResult sg_parse_decimal(const uint8_t* s, int len) {
     int last_dot = -1, last_comma = -1, n_dot = 0, n_comma = 0;
     bool any = false;
     for (int i = 0; i < len;) {
+        const uint32_t b = s[i];
+        if (b < 0x80) {                                    // ASCII: no decoding, white space is 9-13 and 28-32
+            if (b == '.') { last_dot = i; ++n_dot; }
+            else if (b == ',') { last_comma = i; ++n_comma; }
+            if (!((b >= 9 && b <= 13) || (b >= 0x1C && b <= 0x20))) any = true;
+            ++i;
+            continue;
+        }
         uint32_t cp;
         const int n = sg_utf8_decode(s + i, len - i, &cp);
-        if (cp == '.') { last_dot = i; ++n_dot; }
-        else if (cp == ',') { last_comma = i; ++n_comma; }
         if (!sg_is_space(cp)) any = true;
         i += n;
     }
@@ -55,7 +61,8 @@ SG_HD DecResult sg_parse_decimal(const uint8_t* s, int len) {
         if (c == point_char && point >= 0) is_point = all_of_kind ? true : (i == point);
         if (c >= '0' && c <= '9') {
             const uint32_t d = c - '0';
-            if (coef > (0xFFFFFFFFFFFFFFFFull - d) / 10) overflow = true;
+            // coef * 10 + d would pass 2^64 - 1 = 1844674407370955161 * 10 + 5
+            if (coef > 1844674407370955161ull - (d > 5 ? 1u : 0u)) overflow = true;
             coef = coef * 10 + d;
             if (seen_point) ++frac;
             seen_digit = true; seen_any = true;

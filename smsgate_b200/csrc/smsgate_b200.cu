@@ -424,7 +424,10 @@ struct JoinOut {
     int64_t* balance_cents;
 };
 
-__global__ void __launch_bounds__(256)
+#ifndef K2_MIN_BLOCKS
+#define K2_MIN_BLOCKS 6      // 40 registers: six CTAs per SM hide the probe latency best (measured 1 / 6 / 8)
+#endif
+__global__ void __launch_bounds__(256, K2_MIN_BLOCKS)
 k_join_route(int64_t n, const uint8_t* __restrict__ cache_key, const uint8_t* __restrict__ flags,
              const int32_t* __restrict__ body_date, int64_t now_packed, CacheView C, JoinOut out) {
     const int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
