@@ -247,8 +247,7 @@ def run_ours(args, rank, world, local_rank):
         e0.record()
         eng.scan_keys(d_bytes, d_offs, cols)
         e1.record()
-        eng.join_route(n, NOW, cols)
-        eng.dedup(n, base_index, cols)
+        eng.join_route_dedup(n, NOW, base_index, cols)  # stages 2 + 3 as smsgate_replay_device runs them
         if exchange is not None:
             exchange.run(cols, base_index)
         e2.record()

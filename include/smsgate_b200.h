@@ -236,6 +236,11 @@ int smsgate_join_route(smsgate_ctx* ctx, int64_t n, int64_t now_packed, const sm
  * last occurrence of a msg_id survives, the first one is the insert.  Reads
  * msg_id, status; writes survivor, first_seen, last_idx (= base_index + local). */
 int smsgate_dedup(smsgate_ctx* ctx, int64_t n, int64_t base_index, const smsgate_outputs* out);
+/* Stages 2 and 3 in one call (what smsgate_replay_device runs after stage 1): the join kernel inserts each
+ * upsert into the dedup table as it routes it.  Same columns, same values as smsgate_join_route followed by
+ * smsgate_dedup. */
+int smsgate_join_route_dedup(smsgate_ctx* ctx, int64_t n, int64_t now_packed, int64_t base_index,
+                             const smsgate_outputs* out);
 /* Device-source keys.  d_md5[n*16] = MD5(UTF-8 body) of every message: the msg_id the
  * API gateway assigns, get_md5_hash (libs/models.py:97-109) as called at services/api_gateway/main.py:113.
  * Device pointers; d_bytes needs 8 readable bytes past the last body, d_md5 16-byte alignment. */

@@ -105,6 +105,7 @@ def lib():
         "smsgate_scan_keys": (i32, [vp, vp, vp, i64, C.POINTER(Outputs)]),
         "smsgate_join_route": (i32, [vp, i64, i64, C.POINTER(Outputs)]),
         "smsgate_dedup": (i32, [vp, i64, i64, C.POINTER(Outputs)]),
+        "smsgate_join_route_dedup": (i32, [vp, i64, i64, i64, C.POINTER(Outputs)]),
         "smsgate_device_keys": (i32, [vp, vp, vp, i64, vp]),
         "smsgate_cross_source": (i32, [vp, i64, vp, i64, vp, vp]),
         "smsgate_replay_device": (i32, [vp, vp, vp, i64, i64, i64, C.POINTER(Outputs)]),

@@ -424,12 +424,44 @@ struct JoinOut {
     int64_t* balance_cents;
 };
 
+// ------------------------------------------------------------------ dedup (upsert-by-msg_id)
+struct DedupScratch {
+    int32_t* owner;    // [cap] local index of the message that claimed the slot, -1 = empty
+    int32_t* first;    // [cap] min local index with this key
+    int32_t* last;     // [cap] max local index with this key
+    int32_t* slot_of;  // [n]   slot of message i, -1 = not an upsert
+    uint64_t mask;
+};
+
+__device__ __forceinline__ bool id20_equal(const uint8_t* a, const uint8_t* b) {
+    const uint32_t* x = reinterpret_cast<const uint32_t*>(a);
+    const uint32_t* y = reinterpret_cast<const uint32_t*>(b);
+    return x[0] == y[0] && x[1] == y[1] && x[2] == y[2] && x[3] == y[3] && x[4] == y[4];
+}
+
+// claim / find the slot of message i's key and fold i into the slot's first / last occurrence
+__device__ __forceinline__ void dedup_insert_one(int64_t i, const uint8_t* __restrict__ msg_id, const DedupScratch& D) {
+    const uint8_t* k = msg_id + i * 20;
+    const uint32_t* kw = reinterpret_cast<const uint32_t*>(k);
+    uint64_t pos = (((uint64_t)kw[1] << 32) | kw[0]) & D.mask;
+    for (;;) {
+        int prev = D.owner[pos];
+        if (prev == -1) prev = atomicCAS(&D.owner[pos], -1, (int)i);
+        if (prev == -1 || prev == (int)i || id20_equal(msg_id + (int64_t)prev * 20, k)) break;
+        pos = (pos + 1) & D.mask;
+    }
+    atomicMin(&D.first[pos], (int)i);
+    atomicMax(&D.last[pos], (int)i);
+    D.slot_of[i] = (int32_t)pos;
+}
+
 #ifndef K2_MIN_BLOCKS
 #define K2_MIN_BLOCKS 6      // 40 registers: six CTAs per SM hide the probe latency best (measured 1 / 6 / 8)
 #endif
 __global__ void __launch_bounds__(256, K2_MIN_BLOCKS)
 k_join_route(int64_t n, const uint8_t* __restrict__ cache_key, const uint8_t* __restrict__ flags,
-             const int32_t* __restrict__ body_date, int64_t now_packed, CacheView C, JoinOut out) {
+             const int32_t* __restrict__ body_date, int64_t now_packed, CacheView C, JoinOut out,
+             DedupScratch D, int64_t dedup_i0, const uint8_t* __restrict__ dedup_ids) {
     const int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
     if (i >= n) return;
     const uint4* kp = reinterpret_cast<const uint4*>(cache_key + i * 32);
@@ -487,23 +519,15 @@ k_join_route(int64_t n, const uint8_t* __restrict__ cache_key, const uint8_t* __
         *reinterpret_cast<uint4*>(out.card + i * 16) = c;
     }
     if (out.card_len) out.card_len[i] = (uint8_t)r.card_bytes;
+    // fused upsert-table insert (the whole-path calls): message i of this launch is message dedup_i0 + i of
+    // the batch the table was cleared for; saves a launch and a second pass over msg_id / status
+    if (D.owner) {
+        if (r.status == SG_ST_UPSERT) dedup_insert_one(dedup_i0 + i, dedup_ids, D);
+        else D.slot_of[dedup_i0 + i] = -1;
+    }
 }
 
-// ------------------------------------------------------------------ dedup (upsert-by-msg_id)
-struct DedupScratch {
-    int32_t* owner;    // [cap] local index of the message that claimed the slot, -1 = empty
-    int32_t* first;    // [cap] min local index with this key
-    int32_t* last;     // [cap] max local index with this key
-    int32_t* slot_of;  // [n]   slot of message i, -1 = not an upsert
-    uint64_t mask;
-};
-
-__device__ __forceinline__ bool id20_equal(const uint8_t* a, const uint8_t* b) {
-    const uint32_t* x = reinterpret_cast<const uint32_t*>(a);
-    const uint32_t* y = reinterpret_cast<const uint32_t*>(b);
-    return x[0] == y[0] && x[1] == y[1] && x[2] == y[2] && x[3] == y[3] && x[4] == y[4];
-}
-
+// ------------------------------------------------------------------ dedup (upsert-by-msg_id): kernels
 __global__ void __launch_bounds__(256)
 k_dedup_insert(int64_t i0, int64_t n, const uint8_t* __restrict__ msg_id, const uint8_t* __restrict__ status, DedupScratch D) {
     const int64_t i = i0 + blockIdx.x * (int64_t)blockDim.x + threadIdx.x;   // messages [i0, n) of the batch
@@ -512,18 +536,7 @@ k_dedup_insert(int64_t i0, int64_t n, const uint8_t* __restrict__ msg_id, const 
         D.slot_of[i] = -1;
         return;
     }
-    const uint8_t* k = msg_id + i * 20;
-    const uint32_t* kw = reinterpret_cast<const uint32_t*>(k);
-    uint64_t pos = (((uint64_t)kw[1] << 32) | kw[0]) & D.mask;
-    for (;;) {
-        int prev = D.owner[pos];
-        if (prev == -1) prev = atomicCAS(&D.owner[pos], -1, (int)i);
-        if (prev == -1 || prev == (int)i || id20_equal(msg_id + (int64_t)prev * 20, k)) break;
-        pos = (pos + 1) & D.mask;
-    }
-    atomicMin(&D.first[pos], (int)i);
-    atomicMax(&D.last[pos], (int)i);
-    D.slot_of[i] = (int32_t)pos;
+    dedup_insert_one(i, msg_id, D);
 }
 
 __global__ void __launch_bounds__(256)
@@ -1253,7 +1266,8 @@ extern "C" int smsgate_scan_keys(smsgate_ctx* ctx, const uint8_t* d_bytes, const
     return SMSGATE_OK;
 }
 
-extern "C" int smsgate_join_route(smsgate_ctx* ctx, int64_t n, int64_t now_packed, const smsgate_outputs* out) {
+static int join_route_impl(smsgate_ctx* ctx, int64_t n, int64_t now_packed, const smsgate_outputs* out,
+                           const DedupScratch* D, int64_t dedup_i0, const uint8_t* dedup_ids) {
     if (!ctx) return SMSGATE_E_ARG;
     if (n < 0 || !out) return fail(ctx, SMSGATE_E_ARG, "join_route: NULL argument");
     if (n == 0) return SMSGATE_OK;
@@ -1264,11 +1278,17 @@ extern "C" int smsgate_join_route(smsgate_ctx* ctx, int64_t n, int64_t now_packe
                 ctx->c_eflags, ctx->c_date_packed, ctx->cache_m};
     JoinOut jo{out->slot, out->status, out->amount_coef, out->balance_coef, out->amount_exp, out->balance_exp,
                out->dec_flags, out->date, out->card, out->card_len, out->amount_cents, out->balance_cents};
+    const DedupScratch none{nullptr, nullptr, nullptr, nullptr, 0};
     k_join_route<<<(unsigned)((n + 255) / 256), 256, 0, ctx->stream>>>(n, out->cache_key, out->flags, out->body_date,
-                                                                        now_packed, C, jo);
+                                                                        now_packed, C, jo, D ? *D : none, dedup_i0,
+                                                                        dedup_ids);
     ctx->launches += 1;
     CUDA_TRY(ctx, cudaGetLastError());
     return SMSGATE_OK;
+}
+
+extern "C" int smsgate_join_route(smsgate_ctx* ctx, int64_t n, int64_t now_packed, const smsgate_outputs* out) {
+    return join_route_impl(ctx, n, now_packed, out, nullptr, 0, nullptr);
 }
 
 // An empty dedup table for a batch of n messages (power of two >= 2n) inside the reserved arrays.
@@ -1338,13 +1358,33 @@ extern "C" int smsgate_cross_source(smsgate_ctx* ctx, int64_t n_xml, const uint8
     return SMSGATE_OK;
 }
 
+// stages 2 and 3 in one call: the upsert table is cleared first, the join kernel inserts as it routes, one
+// pass resolves - one launch and one pass over msg_id / status less than smsgate_join_route + smsgate_dedup
+extern "C" int smsgate_join_route_dedup(smsgate_ctx* ctx, int64_t n, int64_t now_packed, int64_t base_index,
+                                        const smsgate_outputs* out) {
+    if (!ctx) return SMSGATE_E_ARG;
+    if (n < 0 || !out) return fail(ctx, SMSGATE_E_ARG, "join_route_dedup: NULL argument");
+    if (n == 0) return SMSGATE_OK;
+    if (!out->msg_id || !out->status) return fail(ctx, SMSGATE_E_ARG, "join_route_dedup needs the msg_id and status columns");
+    if (n > ctx->cap_msgs) return fail(ctx, SMSGATE_E_STATE, "join_route_dedup: batch larger than smsgate_reserve() sized the scratch for");
+    CUDA_TRY(ctx, cudaSetDevice(ctx->device));
+    DedupScratch D;
+    int rc = dedup_prepare(ctx, n, &D);
+    if (rc) return rc;
+    rc = join_route_impl(ctx, n, now_packed, out, &D, 0, out->msg_id);
+    if (rc) return rc;
+    k_dedup_resolve<<<(unsigned)((n + 255) / 256), 256, 0, ctx->stream>>>(n, base_index, D, out->survivor, out->first_seen,
+                                                                          out->last_idx);
+    ctx->launches += 1;
+    CUDA_TRY(ctx, cudaGetLastError());
+    return SMSGATE_OK;
+}
+
 extern "C" int smsgate_replay_device(smsgate_ctx* ctx, const uint8_t* d_bytes, const int64_t* d_offsets, int64_t n,
                                      int64_t now_packed, int64_t base_index, const smsgate_outputs* out) {
-    int rc = smsgate_scan_keys(ctx, d_bytes, d_offsets, n, out);
+    const int rc = smsgate_scan_keys(ctx, d_bytes, d_offsets, n, out);
     if (rc) return rc;
-    rc = smsgate_join_route(ctx, n, now_packed, out);
-    if (rc) return rc;
-    return smsgate_dedup(ctx, n, base_index, out);
+    return smsgate_join_route_dedup(ctx, n, now_packed, base_index, out);
 }
 
 // carve the context's device slab into the output columns (alignment: widest first)
@@ -1485,11 +1525,8 @@ static int replay_host_begin_impl(smsgate_ctx* ctx, const uint8_t* h_bytes, cons
         const smsgate_outputs dc = shift_columns(d, lo);
         rc = smsgate_scan_keys(ctx, ctx->s_bytes, ctx->s_offsets + lo, m, &dc);
         if (rc) return rc;
-        rc = smsgate_join_route(ctx, m, now_packed, &dc);
+        rc = join_route_impl(ctx, m, now_packed, &dc, &D, lo, d.msg_id);    // routes and inserts into the upsert table
         if (rc) return rc;
-        k_dedup_insert<<<(unsigned)((m + 255) / 256), 256, 0, st>>>(lo, hi, d.msg_id, d.status, D);
-        ctx->launches += 1;
-        CUDA_TRY(ctx, cudaGetLastError());
         if (h_records) {
             k_pack_records<<<(unsigned)((m + 255) / 256), 256, 0, st>>>(lo, hi, d, ctx->s_records);
             ctx->launches += 1;

@@ -405,7 +405,7 @@ class ReplayEngine:
         b = Batch.from_strings(bodies, None, None)
         dev = torch.device("cuda", self.device)
         d_bytes = torch.zeros(b.body_bytes.size + 64, dtype=torch.uint8, device=dev)
-        d_bytes[:b.body_bytes.size] = torch.from_numpy(np.ascontiguousarray(b.body_bytes)).to(dev)
+        d_bytes[:b.body_bytes.size] = torch.from_numpy(np.array(b.body_bytes, copy=True)).to(dev)
         d_off = torch.from_numpy(np.ascontiguousarray(b.body_offsets, dtype=np.int64)).to(dev)
         out = self.device_keys(d_bytes, d_off).cpu().numpy()
         return [row.tobytes().hex() for row in out]
@@ -425,6 +425,12 @@ class ReplayEngine:
     def join_route(self, n: int, now: _dt.datetime, cols: dict) -> None:
         out = self._dev_outputs(cols)
         L.check(self._ctx, self._lib.smsgate_join_route(self._ctx, n, pack_datetime(now), C.byref(out)))
+
+    def join_route_dedup(self, n: int, now: _dt.datetime, base_index: int, cols: dict) -> None:
+        """Stages 2 and 3 in one call (the join kernel inserts into the upsert table as it routes)."""
+        out = self._dev_outputs(cols)
+        L.check(self._ctx, self._lib.smsgate_join_route_dedup(self._ctx, n, pack_datetime(now), int(base_index),
+                                                              C.byref(out)))
 
     def dedup(self, n: int, base_index: int, cols: dict) -> None:
         out = self._dev_outputs(cols)

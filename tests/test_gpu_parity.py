@@ -207,6 +207,17 @@ def test_stage_calls_match_fused_replay(engine):
                  "first_seen", "last_idx", "amount_cents", "balance_cents"):
         assert np.array_equal(cols[name].cpu().numpy(), ref.cols[name]), name
     assert int(ref.last_idx.max()) >= 1000
+    # stages 2 + 3 fused, and the whole path in one call: the same columns again
+    for mode in ("fused", "whole"):
+        cols2 = engine.device_columns(batch.n, d_bytes.numel())
+        if mode == "fused":
+            engine.scan_keys(d_bytes, d_off, cols2)
+            engine.join_route_dedup(batch.n, NOW, 1000, cols2)
+        else:
+            engine.replay_device(d_bytes, d_off, NOW, cols2, base_index=1000)
+        torch.cuda.synchronize()
+        for name in ("msg_id", "slot", "status", "amount_coef", "date", "survivor", "first_seen", "last_idx", "amount_cents"):
+            assert np.array_equal(cols2[name].cpu().numpy(), ref.cols[name]), (mode, name)
 
 
 def test_pinned_buffers_match_pageable(engine):
