@@ -105,20 +105,28 @@ static int32_t sg_body_date_at(const uint8_t* m, int len, int lead, int ncp, con
     uint32_t ascm = 0;                                // bit k: code point k is ASCII
     int p = lead;
     if (lead >= ncp - 1) {
-        // common case: the ncp bytes ending at `lead` are all ASCII, i.e. they ARE the match
-        bool all_ascii = true;
-        for (int k = 0; k < ncp; ++k) all_ascii = all_ascii && (m[lead - k] < 0x80);
-        if (all_ascii) {
-            for (int k = 0; k < ncp; ++k) {
-                const uint32_t c = m[lead - (ncp - 1) + k];
-                const uint32_t dv = (c >= '0' && c <= '9') ? c - '0' : 15u;
-                vals |= (uint64_t)dv << (4 * k);
+        // common case: the ncp bytes ending at `lead` are all ASCII, i.e. they ARE the match - digits at
+        // 0,1,3,4,6.. and '.' at 2 and 5 are what the automaton matched: read the values straight off
+        const uint8_t* q = m + lead - (ncp - 1);
+        uint32_t any = q[0] | q[1] | q[2] | q[3] | q[4] | q[5] | q[6] | q[7];
+        if (ncp == 10) any |= q[8] | q[9];
+        if (!(any & 0x80u)) {
+            const int d0 = q[0] - '0', d1 = q[1] - '0', m0 = q[3] - '0', m1 = q[4] - '0';
+            const bool day_ok = (d0 == 3 && d1 <= 1) || d0 == 1 || d0 == 2 || (d0 == 0 && d1 >= 1);
+            const bool mon_ok = (m0 == 1 && m1 <= 2) || (m0 == 0 && m1 >= 1);
+            if (!day_ok || !mon_ok) return 0;
+            const int day = d0 * 10 + d1, mon = m0 * 10 + m1;
+            int year = (q[6] - '0') * 10 + (q[7] - '0');
+            if (ncp == 10) {
+                year = year * 100 + (q[8] - '0') * 10 + (q[9] - '0');
+                if (year < 1) return 0;               // datetime.MINYEAR
+            } else {
+                year += (year < 69) ? 2000 : 1900;    // %y pivot (POSIX / _strptime)
             }
-            ascm = (1u << ncp) - 1;
-            p = -1;
+            if (day > sg_days_in_month(year, mon)) return 0;
+            return (year << 9) | (mon << 5) | day;
         }
     }
-    if (p >= 0)
     for (int k = ncp - 1; k >= 0; --k) {
         uint32_t cp;
         sg_utf8_decode(m + p, len - p, &cp);
