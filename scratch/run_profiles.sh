@@ -1,4 +1,5 @@
 set -x
+python -c "import __graft_entry__ as g; g.smoke()" > gpurun_out/smoke.log 2>&1; tail -n 1 gpurun_out/smoke.log
 python -m pytest tests -m gpu -x -q 2>&1 | tail -n 5 > gpurun_out/tests_gpu.log
 python bench.py > gpurun_out/bench1.json 2> gpurun_out/bench1.err || exit 1
 python bench.py --steps 3 --warmup 3 > gpurun_out/b_small.log 2>&1 || exit 1
