@@ -172,12 +172,21 @@ def test_edges_empty_ragged_giant(engine):
     rng = np.random.Generator(np.random.PCG64(5))
     alphabet = np.array(list("ABCDEFGHIJKLMNOPQRSTUVWXYZ 0123456789.:*,"))
     bodies = ["", "a", ""]
-    for ln in list(range(0, 200)) + [255, 256, 257, 1000, 4095, 4096, 4097, 44 * 1024 - 1, 44 * 1024, 44 * 1024 + 1]:
+    stage = 176 * 1024                                   # K1_STAGE: the scan kernel's staging buffer
+    for ln in list(range(0, 200)) + [255, 256, 257, 1000, 4095, 4096, 4097, 44 * 1024, stage - 17, stage - 16,
+                                     stage - 1, stage, stage + 1, stage + 16]:
         bodies.append("".join(rng.choice(alphabet, ln)))
-    giant = "4083***7538 " + "".join(rng.choice(alphabet, 120_000)) + " 1111•••2222 OTP "
-    bodies += [giant, "tail after giant", giant[:50_000], "x" * 45_000 + "Daily limit exceeded: 10.06.2025"]
-    # 300 x 400 B bodies: a full tile of these overflows the 44 KB stage -> sub-batches
-    bodies += ["".join(rng.choice(alphabet, 400)) + str(i) for i in range(300)]
+    giant = "4083***7538 " + "".join(rng.choice(alphabet, 400_000)) + " 1111\u2022\u2022\u20222222 OTP\u00a0"
+    bodies += [giant, "tail after giant", giant[:50_000], "x" * 200_000 + "Daily limit exceeded: 10.06.2025"]
+    # 700 x 4 KB bodies: a CTA's share of these (>= 64 messages) overflows the 176 KB stage -> sub-batches,
+    # some of them rewritten (card form / bullet) so that the in-place rewrite runs inside a sub-batch too
+    for i in range(700):
+        b = "".join(rng.choice(alphabet, 4000)) + str(i)
+        if i % 5 == 0:
+            b = b[:1000] + " 4083***7538 " + b[1000:]
+        if i % 7 == 0:
+            b = b[:3000] + "\u2022\u00a0" + b[3000:]
+        bodies.append(b)
     cache = {O.cache_key(O.fixed_body(b)).hex(): dict(synth_resp) for b, synth_resp in
              ((b, dict(txn_type="debit", date="06.05.25 14:23", amount="1,00", currency="usd", card="1234",
                        merchant="M", city=None, address=None, balance="2")) for b in bodies[::3])}
