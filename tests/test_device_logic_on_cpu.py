@@ -162,3 +162,22 @@ def test_numeric_14_2_storage_rounding():
         fl = int(jr["dec_flags"][i])
         assert bool(fl & 0x40) == ov and bool(fl & 0x80) == ov, t
         assert int(jr["amount_cents"][i]) == cents and int(jr["balance_cents"][i]) == cents, t
+
+
+def test_scan_fuzz_against_oracle():
+    """Adversarial bodies (tests/_fuzz.py): every scan output of the device code equals the oracle's."""
+    from tests._fuzz import bodies
+    bs = [b for b in bodies(6000, 81)]
+    cols = H.scan(bs)
+    off = cols["offsets"]
+    for i, b in enumerate(bs):
+        fl = int(cols["flags"][i])
+        assert cols["msg_id"][i].tobytes() == O.msg_id_xml(b), repr(b)
+        assert bool(fl & L.F_WORKER_SKIP) == O.worker_skip(b), repr(b)
+        assert bool(fl & L.F_PARSER_OTP) == O.parser_otp(b), repr(b)
+        fixed = O.fixed_body(b)
+        a = int(off[i])
+        got = cols["fixed_bytes"][a:a + int(cols["fixed_len"][i])].tobytes().decode() if fl & L.F_MODIFIED else b
+        assert got == fixed and bool(fl & L.F_MODIFIED) == (fixed != b), repr(b)
+        assert cols["cache_key"][i].tobytes() == O.cache_key(fixed), repr(b)
+        assert int(cols["body_date"][i]) == O.pack_date(O.body_date(b)), repr(b)

@@ -288,6 +288,24 @@ def test_device_keys_and_cross_source(engine, golden):
     assert np.all(empty == -1)
 
 
+def test_scan_fuzz_against_oracle(engine):
+    """Adversarial bodies (tests/_fuzz.py) through the scan kernel: keys, filters, rewrite, body date."""
+    from tests._fuzz import bodies
+    bs = bodies(40_000, 82)
+    engine.load_cache({})
+    res = engine.replay(Batch.from_strings(bs, ["B"] * len(bs), range(len(bs))), NOW)
+    want_ids = np.frombuffer(b"".join(O.msg_id_xml(b) for b in bs), np.uint8).reshape(len(bs), 20)
+    assert np.array_equal(res.msg_id, want_ids)
+    fixed = [O.fixed_body(b) for b in bs]
+    assert np.array_equal(res.cache_key, np.frombuffer(b"".join(O.cache_key(f) for f in fixed), np.uint8).reshape(len(bs), 32))
+    assert np.array_equal((res.flags & L.F_WORKER_SKIP) != 0, np.array([O.worker_skip(b) for b in bs]))
+    assert np.array_equal((res.flags & L.F_PARSER_OTP) != 0, np.array([O.parser_otp(b) for b in bs]))
+    assert np.array_equal((res.flags & L.F_MODIFIED) != 0, np.array([f != b for f, b in zip(fixed, bs)]))
+    assert np.array_equal(res.body_date, np.array([O.pack_date(O.body_date(b)) for b in bs], np.int32))
+    for i in range(0, len(bs), 7):
+        assert res.fixed_body(i) == fixed[i], repr(bs[i])
+
+
 def test_full_size_properties(engine):
     """BASELINE.json config 2 size (1 M messages, 100 % hit for non-OTP bodies):
     properties that do not need the oracle at full size, plus a 2 000-message
