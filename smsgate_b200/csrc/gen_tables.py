@@ -96,11 +96,23 @@ def aho(needles, alphabet):
     return dense, out
 
 
-def build_ci():
-    alphabet = sorted(set("".join(CI_NEEDLES)))
+# The scan kernel's first pass runs ONE upper-case automaton whose needles are the worker's keywords plus the
+# upper-cased form of every case-sensitive needle that is not among them: a body in which no such needle
+# occurs after upper-casing cannot contain a case-sensitive needle either, so the case-sensitive automaton
+# only has to run over the few bodies this automaton flags.
+CI2_EXTRA = [n.upper() for n in CS_PARSER + [CS_WORKER] if n.upper() not in CI_NEEDLES]
+
+
+def ci_alphabet():
+    return sorted(set("".join(CI_NEEDLES + CI2_EXTRA)))
+
+
+def build_ci(needles=None):
+    needles = CI_NEEDLES if needles is None else needles
+    alphabet = ci_alphabet()
     cls = {ch: i + 2 for i, ch in enumerate(alphabet)}      # 0 = OTHER, 1 = KEEP (continuation byte)
     assert len(cls) + 2 <= STRIDE
-    dense, out = aho(CI_NEEDLES, alphabet)
+    dense, out = aho(needles, alphabet)
     n = len(dense)
     ACC = n                                                # absorbing
     table = [[0] * STRIDE for _ in range(n + 1)]
@@ -221,6 +233,8 @@ def lead_len(b):
 
 def main():
     ci, ci_cls, CI_ACC = build_ci()
+    ci2, ci2_cls, CI2_ACC = build_ci(CI_NEEDLES + CI2_EXTRA)
+    assert ci2_cls == ci_cls
     cs, cs_cls, CS_N, CS_ACC = build_cs()
     dm, dm_n, dm_first_b, dm_first_a, dm_has_card = build_dm()
     runs = digit_runs()
@@ -258,6 +272,7 @@ def main():
         w("// GENERATED by gen_tables.py - do not edit.\n#pragma once\n#include <stdint.h>\n\n")
         w(f"#define SCAN_STRIDE {STRIDE}\n#define DM_STRIDE {DM_STRIDE}\n")
         w(f"#define CI_STATES {len(ci)}\n#define CI_ROW_BYTES {CI_ROW}\n#define CI_ACCEPT_OFF {CI_ACC * CI_ROW}\n")
+        w(f"#define CI2_STATES {len(ci2)}\n#define CI2_ACCEPT_OFF {CI2_ACC * CI_ROW}\n")
         w(f"#define CS_STATES {len(cs)}\n#define CS_ROW_BYTES {CS_ROW}\n#define CS_DAILY_OFF {CS_N * CS_ROW}\n"
           f"#define CS_ACCEPT_OFF {CS_ACC * CS_ROW}\n")
         w(f"#define DM_STATES {dm_n}\n#define DM_ROW_BYTES {DM_ROW}\n#define DM_FIRST_B_OFF {dm_first_b * DM_ROW}\n"
@@ -279,6 +294,7 @@ def main():
 
         arr("H_BYTE_CLASS", "uint32_t", [cls_word])
         arr("H_CI_NEXT", "uint16_t", [[v * CI_ROW for v in r] for r in ci])
+        arr("H_CI2_NEXT", "uint16_t", [[v * CI_ROW for v in r] for r in ci2])
         arr("H_CS_NEXT", "uint16_t", [[v * CS_ROW for v in r] for r in cs])
         arr("H_DM_NEXT", "uint16_t", [[v * DM_ROW for v in r] for r in dm])
         arr("H_DM_HAS_CARD", "uint8_t", [dm_has_card])
@@ -286,6 +302,7 @@ def main():
         arr("H_DIGIT_RUN_START", "uint32_t", [[a for a, _ in runs]])
         arr("H_DIGIT_RUN_LEN", "uint8_t", [[n for _, n in runs]])
         arr("H_CARD_KMP", "uint8_t", kmp("dddd***dddd", ["o", "d", ".", "*"]))
+    print("CI2 states", len(ci2), "extra needles", CI2_EXTRA)
     print("CI states", len(ci), "CS states", len(cs), "DM states", dm_n, "first_b", dm_first_b, "first_a", dm_first_a,
           "special leads", sorted(hex(b) for b in special_leads))
 

@@ -11,6 +11,7 @@ struct DeviceTables {
     uint32_t digit_run_start[N_DIGIT_RUNS];
     uint16_t ci_next[CI_STATES * SCAN_STRIDE];   // byte offset of the next row
     uint16_t cs_next[CS_STATES * SCAN_STRIDE];
+    uint16_t ci2_next[CI2_STATES * SCAN_STRIDE]; // first-pass automaton: worker needles + upper-cased case-sensitive ones
     uint16_t dm_next[DM_STATES * DM_STRIDE];
     uint8_t dm_has_card[DM_STATES];
     uint8_t digit_run_len[N_DIGIT_RUNS];
@@ -23,6 +24,7 @@ inline void sg_fill_tables(DeviceTables* h) {
     for (int k = 0; k < N_DIGIT_RUNS; ++k) { h->digit_run_start[k] = H_DIGIT_RUN_START[k]; h->digit_run_len[k] = H_DIGIT_RUN_LEN[k]; }
     for (int k = 0; k < CI_STATES * SCAN_STRIDE; ++k) h->ci_next[k] = H_CI_NEXT[k];
     for (int k = 0; k < CS_STATES * SCAN_STRIDE; ++k) h->cs_next[k] = H_CS_NEXT[k];
+    for (int k = 0; k < CI2_STATES * SCAN_STRIDE; ++k) h->ci2_next[k] = H_CI2_NEXT[k];
     for (int k = 0; k < DM_STATES * DM_STRIDE; ++k) h->dm_next[k] = H_DM_NEXT[k];
     for (int k = 0; k < DM_STATES; ++k) h->dm_has_card[k] = H_DM_HAS_CARD[k];
     for (int k = 0; k < 48; ++k) h->card_kmp[k] = H_CARD_KMP[k];
@@ -35,6 +37,7 @@ struct ScanTables {
 #define T_BYTE_CLASS(T) ((T).t->byte_class)
 #define T_CI(T) (reinterpret_cast<const uint8_t*>((T).t->ci_next))
 #define T_CS(T) (reinterpret_cast<const uint8_t*>((T).t->cs_next))
+#define T_CI2(T) (reinterpret_cast<const uint8_t*>((T).t->ci2_next))
 #define T_DM(T) (reinterpret_cast<const uint8_t*>((T).t->dm_next))
 
 // one automaton step: tables hold the byte offset of the next row, classes come pre-multiplied by 2
@@ -71,9 +74,9 @@ SG_HD int sg_upper_special(uint32_t cp, uint32_t cls[3]) {
         case 0x1E9A: cls[0] = CI_CLS_A; cls[1] = CI_CLS_OTHER; return 2;           // ẚ
         case 0xFB00: cls[0] = CI_CLS_F; cls[1] = CI_CLS_F; return 2;               // ﬀ
         case 0xFB01: cls[0] = CI_CLS_F; cls[1] = CI_CLS_I; return 2;               // ﬁ
-        case 0xFB02: cls[0] = CI_CLS_F; cls[1] = CI_CLS_OTHER; return 2;           // ﬂ (L is in no needle)
+        case 0xFB02: cls[0] = CI_CLS_F; cls[1] = CI_CLS_L; return 2;               // ﬂ
         case 0xFB03: cls[0] = CI_CLS_F; cls[1] = CI_CLS_F; cls[2] = CI_CLS_I; return 3;      // ﬃ
-        case 0xFB04: cls[0] = CI_CLS_F; cls[1] = CI_CLS_F; cls[2] = CI_CLS_OTHER; return 3;  // ﬄ
+        case 0xFB04: cls[0] = CI_CLS_F; cls[1] = CI_CLS_F; cls[2] = CI_CLS_L; return 3;      // ﬄ
         case 0xFB05: cls[0] = CI_CLS_S; cls[1] = CI_CLS_T; return 2;               // ﬅ
         case 0xFB06: cls[0] = CI_CLS_S; cls[1] = CI_CLS_T; return 2;               // ﬆ
         default: return 0;
@@ -173,29 +176,39 @@ SG_HD void sg_scan_event(ScanState& st, int i) {
     else st.dm_event = DM_FIRST_A_OFF;
 }
 
+// The scan comes in two forms.  FULL runs all three automata and yields every flag.  FIRST is the scan
+// kernel's first pass: instead of the worker's upper-case automaton AND the case-sensitive one it steps a
+// single upper-case automaton (worker needles + the upper-cased case-sensitive needles, CI2 in
+// gen_tables.py) plus the date / card automaton.  If that automaton never accepts, no needle of either
+// kind occurs (a case-sensitive occurrence upper-cases into an occurrence of its upper-cased form) and
+// both filter flags are 0; if it accepts, the body is flagged SG_F_MAYBE and a FULL scan decides.  Only
+// ~5 % of real bodies are flagged, so the common byte costs two table steps instead of three.
+
 // One byte, any value.  A special lead byte (may upper-case into ASCII, be a
 // Unicode digit, U+00A0 or U+2022) is decoded and its symbols fed explicitly;
 // continuation bytes keep the CI / DM state, other lead bytes reset it.
+template <bool FIRST>
 #if defined(__CUDACC__)
 __host__ __device__ __noinline__
 #endif
 static ScanState sg_scan_byte_careful(const uint8_t* m, int len, int i, const ScanTables T, ScanState st) {
+    const uint8_t* ci_tab = FIRST ? T_CI2(T) : T_CI(T);
     const uint32_t cw = T_BYTE_CLASS(T)[m[i]];
-    st.cs = sg_step(T_CS(T), st.cs, sg_byte(cw, 1));
+    if (!FIRST) st.cs = sg_step(T_CS(T), st.cs, sg_byte(cw, 1));
     if ((int32_t)cw < 0) {
         uint32_t cp;
         sg_utf8_decode(m + i, len - i, &cp);
         uint32_t up[3];
         const int nu = sg_upper_special(cp, up);
-        if (nu == 0) st.ci = sg_step(T_CI(T), st.ci, CI_CLS_OTHER);
-        for (int k = 0; k < nu; ++k) st.ci = sg_step(T_CI(T), st.ci, up[k]);
+        if (nu == 0) st.ci = sg_step(ci_tab, st.ci, CI_CLS_OTHER);
+        for (int k = 0; k < nu; ++k) st.ci = sg_step(ci_tab, st.ci, up[k]);
         uint32_t dcls = DM_CLS_OTHER;
         if (cp == 0x2022) { dcls = DM_CLS_STAR; st.modified = 1; }
         else if (cp == 0xA0) st.modified = 1;
         else if (sg_digit_value(cp, T.t->digit_run_start, T.t->digit_run_len) >= 0) dcls = DM_CLS_DIGIT;
         st.dm = sg_step(T_DM(T), st.dm, dcls);
     } else {
-        st.ci = sg_step(T_CI(T), st.ci, sg_byte(cw, 0));
+        st.ci = sg_step(ci_tab, st.ci, sg_byte(cw, 0));
         st.dm = sg_step(T_DM(T), st.dm, sg_byte(cw, 2));
     }
     if (st.dm >= st.dm_event) sg_scan_event(st, i);
@@ -206,8 +219,10 @@ static ScanState sg_scan_byte_careful(const uint8_t* m, int len, int i, const Sc
 // detection (is fixed_body different?) and the first hits of the two body
 // date forms.  worker.py:112-121, gemini_parser.py:198-203, :73-100, :131.
 // Aligned 4-byte words that are pure ASCII take the branch-free fast path (three
-// table steps per byte); every other byte goes through sg_scan_byte_careful.
-SG_HD ScanResult sg_scan_body(const uint8_t* m, int len, const ScanTables& T) {
+// table steps per byte, two in the FIRST form); every other byte goes through sg_scan_byte_careful.
+template <bool FIRST>
+SG_HD ScanResult sg_scan_body_t(const uint8_t* m, int len, const ScanTables& T) {
+    const uint8_t* ci_tab = FIRST ? T_CI2(T) : T_CI(T);
     ScanState st;
     st.ci = st.cs = st.dm = 0;
     st.dm_event = DM_FIRST_B_OFF;
@@ -215,12 +230,12 @@ SG_HD ScanResult sg_scan_body(const uint8_t* m, int len, const ScanTables& T) {
     st.modified = 0;
     int i = 0;
     const int head = (int)((4 - ((uintptr_t)m & 3)) & 3);
-    for (; i < len && i < head; ++i) st = sg_scan_byte_careful(m, len, i, T, st);
+    for (; i < len && i < head; ++i) st = sg_scan_byte_careful<FIRST>(m, len, i, T, st);
     for (; i + 4 <= len; i += 4) {
         const uint32_t w4 = *reinterpret_cast<const uint32_t*>(m + i);
         if (w4 & 0x80808080u) {
 #pragma unroll 1
-            for (int k = 0; k < 4; ++k) st = sg_scan_byte_careful(m, len, i + k, T, st);
+            for (int k = 0; k < 4; ++k) st = sg_scan_byte_careful<FIRST>(m, len, i + k, T, st);
             continue;
         }
         uint32_t ci = st.ci, cs = st.cs, dm = st.dm;
@@ -228,8 +243,8 @@ SG_HD ScanResult sg_scan_body(const uint8_t* m, int len, const ScanTables& T) {
 #pragma unroll
         for (int k = 0; k < 4; ++k) {
             const uint32_t cw = T_BYTE_CLASS(T)[sg_byte(w4, k)];
-            ci = sg_step(T_CI(T), ci, sg_byte(cw, 0));
-            cs = sg_step(T_CS(T), cs, sg_byte(cw, 1));
+            ci = sg_step(ci_tab, ci, sg_byte(cw, 0));
+            if (!FIRST) cs = sg_step(T_CS(T), cs, sg_byte(cw, 1));
             dm = sg_step(T_DM(T), dm, sg_byte(cw, 2));
         }
         st.ci = ci; st.cs = cs;
@@ -242,20 +257,39 @@ SG_HD ScanResult sg_scan_body(const uint8_t* m, int len, const ScanTables& T) {
             }
         } else st.dm = dm;
     }
-    for (; i < len; ++i) st = sg_scan_byte_careful(m, len, i, T, st);
+    for (; i < len; ++i) st = sg_scan_byte_careful<FIRST>(m, len, i, T, st);
 
     ScanResult r;
     r.flags = 0;
-    const bool parser_hit = st.cs == CS_ACCEPT_OFF;
-    const bool daily = st.cs >= CS_DAILY_OFF;              // includes the parser-hit state
-    if (st.ci == CI_ACCEPT_OFF || daily) r.flags |= SG_F_WORKER_SKIP;
-    if (parser_hit) r.flags |= SG_F_PARSER_OTP;
+    if (FIRST) {
+        if (st.ci == CI2_ACCEPT_OFF) r.flags |= SG_F_MAYBE;
+    } else {
+        const bool parser_hit = st.cs == CS_ACCEPT_OFF;
+        const bool daily = st.cs >= CS_DAILY_OFF;              // includes the parser-hit state
+        if (st.ci == CI_ACCEPT_OFF || daily) r.flags |= SG_F_WORKER_SKIP;
+        if (parser_hit) r.flags |= SG_F_PARSER_OTP;
+    }
     if (st.modified || T.t->dm_has_card[st.dm / DM_ROW_BYTES]) r.flags |= SG_F_MODIFIED;
     int32_t bd = 0;
     if (st.posA >= 0) bd = sg_body_date_at(m, len, st.posA, 10, T);
     if (bd == 0 && st.posB >= 0) bd = sg_body_date_at(m, len, st.posB, 8, T);
     r.body_date = bd;
     if (bd) r.flags |= SG_F_BODY_DATE;
+    return r;
+}
+SG_HD ScanResult sg_scan_body(const uint8_t* m, int len, const ScanTables& T) { return sg_scan_body_t<false>(m, len, T); }
+SG_HD ScanResult sg_scan_first(const uint8_t* m, int len, const ScanTables& T) { return sg_scan_body_t<true>(m, len, T); }
+// the two filter flags of a body the first pass flagged (kept out of line: it runs for few bodies)
+#if defined(__CUDACC__)
+__host__ __device__ __noinline__
+#endif
+static uint32_t sg_scan_filters(const uint8_t* m, int len, const ScanTables T) {
+    return sg_scan_body_t<false>(m, len, T).flags & (SG_F_WORKER_SKIP | SG_F_PARSER_OTP);
+}
+// both passes one after the other, as the scan kernel composes them
+SG_HD ScanResult sg_scan_two_pass(const uint8_t* m, int len, const ScanTables& T) {
+    ScanResult r = sg_scan_first(m, len, T);
+    if (r.flags & SG_F_MAYBE) r.flags = (r.flags & ~(uint32_t)SG_F_MAYBE) | sg_scan_filters(m, len, T);
     return r;
 }
 

@@ -19,6 +19,7 @@
 #define SG_F_PARSER_OTP  0x02   // libs/gemini_parser.py:198-200
 #define SG_F_MODIFIED    0x04   // fixed_body != body (libs/gemini_parser.py:202-203)
 #define SG_F_BODY_DATE   0x08   // fix_broken_datetime finds a usable date (libs/gemini_parser.py:73-100)
+#define SG_F_MAYBE       0x80   // internal to the scan kernel, never stored: the first pass saw a needle's upper-cased form
 
 // status codes (status[] output of the join/route kernel)
 #define SG_ST_UPSERT 0

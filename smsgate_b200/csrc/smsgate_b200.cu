@@ -55,10 +55,16 @@ __device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
 }
 
 // ------------------------------------------------------------------ stage 1: keys + scans
-constexpr int K1_THREADS = 640;           // 4 warps
+#ifndef K1_THREADS_N
+#define K1_THREADS_N 640
+#endif
+constexpr int K1_THREADS = K1_THREADS_N;   // 20 warps: one CTA per SM
 constexpr int K1_CTAS_PER_SM = 1;
-constexpr int K1_TILE = 1280;              // messages per tile: every thread owns one short and one long body
-constexpr int K1_STAGE = 176 * 1024;       // staged body bytes per CTA tile (4 CTAs per SM)
+constexpr int K1_TILE = 2 * K1_THREADS;      // messages per tile: every thread owns one short and one long body
+#ifndef K1_STAGE_KB
+#define K1_STAGE_KB 176
+#endif
+constexpr int K1_STAGE = K1_STAGE_KB * 1024;  // staged body bytes per tile
 constexpr int K1_PAD = 32;                // slack read by the unaligned word reader
 constexpr int K1_BUCKETS = 128;           // length buckets of 8 bytes for the in-tile sort
 
@@ -72,9 +78,11 @@ struct __align__(16) K1Smem {
     int32_t cursor[K1_BUCKETS];
     uint16_t order[K1_TILE];              // tile-local message ids sorted by length bucket
     uint16_t work[K1_TILE];               // hashing order: rewritten bodies first, each group longest first
-    uint8_t mod[K1_TILE];                 // 1 = the clean/mask step changes this body
+    uint8_t mod[K1_TILE];                 // first-pass flags of the body (SG_F_MODIFIED, SG_F_MAYBE, ...)
+    uint16_t rlist[K1_TILE];              // bodies the first pass flagged and clean/mask leaves alone: filter re-scan
     int32_t pcnt[2 * K1_THREADS / 32];    // per warp and half: rewritten | untouched << 16
     int32_t next;                         // next 32-message chunk to hash
+    int32_t nr;                           // entries of rlist
 };
 
 struct ScanOut {
@@ -180,7 +188,7 @@ k_scan_keys(const uint8_t* __restrict__ bytes, const int64_t* __restrict__ offse
                 nfit += fits[h] ? 1 : 0;
             }
             if (tid < K1_BUCKETS) S.hist[tid] = 0;
-            if (tid == 0) S.next = 0;
+            if (tid == 0) { S.next = 0; S.nr = 0; }
             // the first half is a prefix of the tile, so the count of fitting messages is exact
             // only if the second half is counted after the first: do two block-wide counts
             const int cnt0 = __syncthreads_count(fits[0]);
@@ -260,9 +268,12 @@ k_scan_keys(const uint8_t* __restrict__ bytes, const int64_t* __restrict__ offse
             for (int h = 0; h < 2; ++h) {
                 if (rk[h] < 0) continue;
                 const int t = S.order[rk[h]];
-                const ScanResult sr = sg_scan_body(S.stage + S.m_off[t], S.m_len[t], T);
+                // first pass (scan_core.cuh): two automata; the few flagged bodies get their filter flags later
+                ScanResult sr = sg_scan_first(S.stage + S.m_off[t], S.m_len[t], T);
+                S.mod[t] = (uint8_t)sr.flags;
+                if ((sr.flags & SG_F_MAYBE) && !(sr.flags & SG_F_MODIFIED)) S.rlist[atomicAdd(&S.nr, 1)] = (uint16_t)t;
+                sr.flags &= ~(uint32_t)SG_F_MAYBE;
                 k1_store_scan(out, s + t, sr);
-                S.mod[t] = (sr.flags & SG_F_MODIFIED) ? 1 : 0;
             }
             __syncthreads();
             // ---- hashing order: the bodies clean/mask changes first (they cost SHA-1 + rewrite + SHA-256 of
@@ -276,7 +287,7 @@ k_scan_keys(const uint8_t* __restrict__ bytes, const int64_t* __restrict__ offse
                 const int q = tid + h * K1_THREADS;
                 const bool valid = q < cnt;
                 wt[h] = valid ? S.order[cnt - 1 - q] : 0;
-                const bool isM = valid && S.mod[wt[h]];
+                const bool isM = valid && (S.mod[wt[h]] & SG_F_MODIFIED);
                 balM[h] = __ballot_sync(0xffffffffu, isM);
                 balU[h] = __ballot_sync(0xffffffffu, valid && !isM);
                 if (lane == 0) S.pcnt[h * (K1_THREADS / 32) + wrp] = __popc(balM[h]) | (__popc(balU[h]) << 16);
@@ -307,12 +318,24 @@ k_scan_keys(const uint8_t* __restrict__ bytes, const int64_t* __restrict__ offse
             __syncthreads();
             // ---- phase H: warps pull chunks until none is left
             const int nchM = (nM + 31) >> 5, nchU = (cnt - nM + 31) >> 5;
+            const int nR = S.nr, nchR = (nR + 31) >> 5;
 #pragma unroll 1
             for (;;) {
                 int c = 0;
                 if (lane == 0) c = atomicAdd(&S.next, 1);
                 c = __shfl_sync(0xffffffffu, c, 0);
-                if (c >= nchM + nchU) break;
+                if (c >= nchM + nchU + nchR) break;
+                if (c >= nchM + nchU) {
+                    // filter re-scan of flagged bodies that are not rewritten (those that are re-scan themselves
+                    // below, before the rewrite destroys the original): the stored flags gain the two filter bits
+                    const int idx = (c - nchM - nchU) * 32 + lane;
+                    if (idx < nR) {
+                        const int t = S.rlist[idx];
+                        const uint32_t fl = (S.mod[t] & ~(uint32_t)SG_F_MAYBE) | sg_scan_filters(S.stage + S.m_off[t], S.m_len[t], T);
+                        if (out.flags) out.flags[s + t] = (uint8_t)fl;
+                    }
+                    continue;
+                }
                 const bool isM = c < nchM;
                 const int idx = isM ? c * 32 + lane : nM + (c - nchM) * 32 + lane;
                 const bool act = idx < (isM ? nM : cnt);
@@ -326,7 +349,13 @@ k_scan_keys(const uint8_t* __restrict__ bytes, const int64_t* __restrict__ offse
 #pragma unroll 1
                 for (int pass = 0; pass < npass; ++pass) {   // one copy of the hashing loop, see sg_hash_pass
                     const uint32_t mode = isM ? (pass ? 2u : 1u) : 3u;
-                    if (pass && act) cur = sg_rewrite_fixed(m, len, T);
+                    if (pass && act) {
+                        if (S.mod[t] & SG_F_MAYBE) {         // flagged AND rewritten (rare): filters first, on the original
+                            const uint32_t fl = (S.mod[t] & ~(uint32_t)SG_F_MAYBE) | sg_scan_filters(m, len, T);
+                            if (out.flags) out.flags[s + t] = (uint8_t)fl;
+                        }
+                        cur = sg_rewrite_fixed(m, len, T);
+                    }
                     if (act) sg_hash_pass(m, cur, mode, h1, h2);
                 }
                 if (act) {

@@ -30,8 +30,9 @@ def scan(bodies):
                 flags=np.zeros(n, np.uint8), body_date=np.zeros(n, np.int32), fixed_len=np.zeros(n, np.int32),
                 fixed_bytes=np.zeros(max(len(data), 1), np.uint8))
     data = np.concatenate([data, np.zeros(16, np.uint8)])
-    lib().hc_scan_keys(_p(data), _p(offsets), C.c_int64(n), _p(cols["msg_id"]), _p(cols["cache_key"]),
-                       _p(cols["flags"]), _p(cols["body_date"]), _p(cols["fixed_len"]), _p(cols["fixed_bytes"]))
+    rc = lib().hc_scan_keys(_p(data), _p(offsets), C.c_int64(n), _p(cols["msg_id"]), _p(cols["cache_key"]),
+                            _p(cols["flags"]), _p(cols["body_date"]), _p(cols["fixed_len"]), _p(cols["fixed_bytes"]))
+    assert rc == 0, f"first pass + full pass disagree with the full pass at body {-100 - rc}: {bodies[-100 - rc]!r}"
     cols["offsets"] = offsets
     return cols
 

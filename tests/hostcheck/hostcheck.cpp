@@ -41,7 +41,10 @@ extern "C" int hc_scan_keys(const uint8_t* bytes, const int64_t* offsets, int64_
         buf.assign((size_t)len + 3 + 16, 0xEE);
         uint8_t* m = buf.data() + (offsets[i] & 3) + ((4 - ((uintptr_t)buf.data() & 3)) & 3);
         memcpy(m, bytes + offsets[i], len);
-        ScanResult sr = sg_scan_body(m, len, T);
+        // the scan kernel's composition (first pass, full pass for flagged bodies) must equal the full pass
+        ScanResult sr = sg_scan_two_pass(m, len, T);
+        const ScanResult full = sg_scan_body(m, len, T);
+        if (sr.flags != full.flags || sr.body_date != full.body_date) return -100 - (int)i;
         uint32_t h1[5], h2[8];
         sg_sha1(m, len, h1);
         int flen = len;
