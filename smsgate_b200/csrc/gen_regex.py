@@ -167,7 +167,7 @@ def main():
     # OTP filter of process_cached.py:236 on body.upper(): same alphabet / class ids as the worker filter
     sys.path.insert(0, HERE)
     import gen_tables as G
-    alphabet = sorted(set("".join(G.CI_NEEDLES)))
+    alphabet = G.ci_alphabet()
     cls = {ch: i + 2 for i, ch in enumerate(alphabet)}
     dense, out = G.aho(["OTP", "PASS=", "CODE:"], alphabet)
     n = len(dense)
