@@ -180,7 +180,7 @@ def main():
     otp[n] = [n] * G.STRIDE
     row = G.STRIDE * 2
 
-    with open(os.path.join(HERE, "regex_tables.h"), "w") as f:
+    with open(os.path.join(os.environ.get("SMSGATE_GEN_OUT") or HERE, "regex_tables.h"), "w") as f:
         w = f.write
         w("// GENERATED by gen_regex.py - do not edit.\n#pragma once\n#include <stdint.h>\n\n")
         for name, v in OPS.items():

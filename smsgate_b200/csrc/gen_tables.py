@@ -266,7 +266,7 @@ def main():
             sp = 1 if b in special_leads else 0
         cls_word.append((cic * 2) | (csc * 2) << 8 | (dmc * 2) << 16 | sp << 31)
 
-    here = os.path.dirname(os.path.abspath(__file__))
+    here = os.environ.get("SMSGATE_GEN_OUT") or os.path.dirname(os.path.abspath(__file__))
     with open(os.path.join(here, "scan_tables.h"), "w") as f:
         w = f.write
         w("// GENERATED by gen_tables.py - do not edit.\n#pragma once\n#include <stdint.h>\n\n")
