@@ -10,11 +10,12 @@ One "step" = one pass of the whole hot path (keys + scans, cache join + amounts
 BASELINE.json configs[1] per GPU: 1 M synthetic bank-notification SMS, every
 non-OTP body present in the loaded Gemini response cache (weak scaling: each
 rank replays its own 1 M shard; msg_ids are globally deduplicated through the
-all-to-all by key-hash prefix when N > 1).
+peer-memory exchange by key-hash prefix when N > 1, smsgate_b200/dist.py).
 
 Prints ONE JSON line (rank 0).  `value` = messages/s with the batch resident in
-HBM; `e2e` = the same through the host-buffer C-ABI call (pinned host memory
-in, result columns back out, copies inside the timed region).
+HBM; `e2e` = the same through the host-buffer C-ABI call
+(smsgate_replay_host_records: pinned host memory in, one 64-byte result record
+and one dedup verdict per message back out, copies inside the timed region).
 """
 from __future__ import annotations
 
