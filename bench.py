@@ -303,9 +303,11 @@ def run_ours(args, rank, world, local_rank):
     peak, peak_src = measured_peak_hbm()
     achieved = k1_bytes / (k1 * 1e-3) / 1e9
     traffic = None
+    prof = {}
     try:
         with open(os.path.join(ROOT, "profiles", "k_scan_keys_traffic.json")) as f:
-            traffic = json.load(f).get("dram_bytes_per_launch")
+            prof = json.load(f)
+            traffic = prof.get("dram_bytes_per_launch")
     except Exception:
         pass
     cpu_cores = 1
@@ -327,7 +329,11 @@ def run_ours(args, rank, world, local_rank):
         "roofline": {"bound": "hbm", "kernel": "k_scan_keys", "achieved": achieved, "peak": peak, "unit": "GB/s",
                      "frac": achieved / peak, "traffic": traffic, "peak_source": peak_src,
                      "kernel_ms": k1, "kernel_share_of_step": k1 / step,
-                     "note": "SHA-1 + SHA-256 rounds make this kernel integer-ALU bound, not HBM bound (DESIGN.md)",
+                     "note": "SHA-1 + SHA-256 rounds make this kernel integer-ALU bound, not HBM bound (DESIGN.md); "
+                             "alu_pipe_busy_pct / issue_slots_busy_pct are the ncu figures of the same kernel "
+                             "(profiles/, one capture per change), the ceiling it actually runs against",
+                     "alu_pipe_busy_pct": prof.get("alu_pipe_busy_pct"),
+                     "issue_slots_busy_pct": prof.get("issue_slots_busy_pct"),
                      "path_algorithmic_gbs": n * (mean_len + 229) / (step * 1e-3) / 1e9},
         "cpu_baseline": ({"value": cpu_val, "unit": UNIT, "cores": cpu_cores, "kind": "port",
                           "sample": f"{cpu_n} messages of the same workload, bodies in memory, oracle port with a "

@@ -45,7 +45,13 @@ def main():
             u = units[i].lower()
             return v * {"byte": 1, "kbyte": 1e3, "mbyte": 1e6, "gbyte": 1e9}[u]
         t = val("dram__bytes_read.sum") + val("dram__bytes_write.sum")
-        json.dump({"kernel": r[name_i].split("(")[0], "dram_bytes_per_launch": t, "source": rep}, open(sys.argv[3], "w"))
+        def num(k):
+            return float(r[hdr.index(k)].replace(",", "")) if k in hdr else None
+        json.dump({"kernel": r[name_i].split("(")[0], "dram_bytes_per_launch": t, "source": rep,
+                   "alu_pipe_busy_pct": num("sm__inst_executed_pipe_alu.avg.pct_of_peak_sustained_active"),
+                   "issue_slots_busy_pct": num("smsp__issue_active.avg.pct_of_peak_sustained_active"),
+                   "warp_instructions": num("smsp__inst_executed.sum"),
+                   "ncu_duration_us": num("gpu__time_duration.sum")}, open(sys.argv[3], "w"))
     print("\n".join(lines[:40]))
 
 
