@@ -3,14 +3,19 @@
 // point launches kernels or fails with an error code.
 //
 // Kernels
-//   k_scan_keys     one thread per message over a shared-memory tile that a
-//                   single cp.async.bulk (TMA 1-D) copy stages per CTA: skip
-//                   filters, body date, clean+mask rewrite, SHA-1, SHA-256.
-//                   Integer-ALU bound (SHA rounds), see DESIGN.md.
+//   k_scan_keys     one 640-thread CTA per SM over tiles that a single cp.async.bulk
+//                   (TMA 1-D) copy stages in shared memory: skip filters, body date,
+//                   clean+mask rewrite, SHA-1, SHA-256.  Integer-ALU bound, see DESIGN.md.
 //   k_cache_build   inserts the cache entries into an open-addressing table.
-//   k_join_route    probe + decimal canonicalisation + date/card + routing.
+//   k_join_route    probe + decimal canonicalisation + date/card + routing (+ the
+//                   upsert-table insert when called from the whole-path entries).
 //   k_dedup_insert / k_dedup_resolve   upsert-by-msg_id.
-//   k_decimal_batch / k_strict_date_batch   the two batch helpers.
+//   k_export_* / k_merge_* / k_apply_*   global dedup through an all-to-all (NCCL).
+//   k_bits_* / k_p2p_*                   the same through NVLink peer memory.
+//   k_legacy_parse, k_dt_str_batch       the legacy offline replay and its record builders.
+//   k_xml_* (xml_extract.cuh)            XML backup tokenizer.
+//   k_md5_keys, k_xsrc_probe             device-source keys, cross-source report.
+//   k_decimal_batch / k_strict_date_batch / k_pack_records / k_pack_verdict   helpers.
 #include <cuda_runtime.h>
 #include <stdint.h>
 #include <stdio.h>
@@ -214,7 +219,7 @@ k_scan_keys(const uint8_t* __restrict__ bytes, const int64_t* __restrict__ offse
                 const int64_t tail0 = (bulk_end > base) ? bulk_end : base;
                 if (tid < 16 && tail0 + tid < hi) S.stage[tail0 - base + tid] = bytes[tail0 + tid];
             }
-            // ---- while the copy is in flight: sort the tile's messages by length (16-byte buckets) so that
+            // ---- while the copy is in flight: sort the tile's messages by length (8-byte buckets) so that
             //      the 32 lanes of a warp walk bodies of about the same length and SHA block count
             int key[2] = {0, 0};
 #pragma unroll
@@ -1907,7 +1912,8 @@ extern "C" int smsgate_dedup_apply(smsgate_ctx* ctx, int64_t n, int64_t base_ind
 // torch's symmetric memory).  The export kernel stores its records straight into
 // the owner's inbox, the owner's merge stores each verdict straight back into the
 // home rank's per-slot arrays: no count exchange, no host synchronisation, no
-// staging copies; the only cross-GPU synchronisation is two barriers.
+// staging copies; the only cross-GPU synchronisation is two barriers (plus two for the
+// optional bitmap prefilter that keeps keys held by one rank only out of the exchange).
 struct __align__(16) P2PRecord {          // three 16-byte stores over NVLink
     uint32_t key[5];
     uint32_t first_lo;

@@ -115,7 +115,8 @@ class GlobalDedup:
 class GlobalDedupP2P:
     """The same global dedup with the exchange fused into the kernels: records and
     verdicts are stored straight into the peers' memory over NVLink (buffers mapped
-    with torch's symmetric memory), with two cross-GPU barriers and no host
+    with torch's symmetric memory), with four cross-GPU barriers (two for the
+    bitmap prefilter, two for the records and their verdicts) and no host
     synchronisation per batch.  Every rank must use the same `n_max`."""
 
     def __init__(self, engine, dist, n_max: int, group=None, prefilter: bool = True):
