@@ -195,6 +195,28 @@ def test_edges_empty_ragged_giant(engine):
     _compare_with_oracle(res, backup, NOW)
 
 
+def test_long_cache_value_strings(engine):
+    """Cached amount / balance / date strings far longer than real ones (padding, 90-digit numbers): same
+    results as the oracle, also mixed with ordinary entries in one batch."""
+    bodies = ["PURCHASE: SHOP %d, CITY, 06.05.25 14:23, card ***%04d. Amount:%d.00 USD, Balance:5.00 USD" % (i, i, i)
+              for i in range(600)]
+    cache = {}
+    for i, b in enumerate(bodies):
+        v = dict(txn_type="debit", date="06.05.25 14:23", amount="%d,50" % i, currency="usd", card="1234***%04d" % i,
+                 merchant="M", city=None, address=None, balance="2")
+        if i % 3 == 0:
+            v["amount"] = " " * 70 + "1 234,5"                    # 77 bytes of amount
+        if i % 3 == 1:
+            v["balance"] = "9" * 19 + "." + "0" * 70              # overflows int64
+        if i % 5 == 0:
+            v["date"] = "  10.06.2025 20:51" + " " * 60           # host-resolved date, long text
+        cache[O.cache_key(O.fixed_body(b)).hex()] = v
+    res = _run(engine, bodies, cache)
+    backup = synth.Backup(bodies=bodies, senders=["BANK"] * len(bodies), date_ms=list(range(len(bodies))), cache=cache)
+    _compare_with_oracle(res, backup, NOW)
+    assert (res.status == L.ST_UPSERT).sum() > 100
+
+
 def test_stage_calls_match_fused_replay(engine):
     """scan_keys / join_route / dedup called one by one on device tensors give
     the same columns as replay_host."""
