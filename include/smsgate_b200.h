@@ -381,7 +381,7 @@ int smsgate_replay_host_records_finish(smsgate_ctx* ctx, int64_t* h_verdict);
  *   - the built-in table takes about 28 MiB on every GPU that loads the library,
  *     for the life of the process;
  *   - the first call on a given device looks up the table's device address
- *     (cudaGetSymbolAddress); make that first call outside any stream capture;
+ *     (cudaGetSymbolAddress), once per device;
  *   - all calls on one device share the table: each call resets the part it
  *     uses, and two calls whose GPU work overlaps (different streams, different
  *     threads) corrupt each other - serialise them;
