@@ -170,6 +170,24 @@ class ReplayResult:
         """msg_id hex -> ParsedSMS of the record that remains after the replay."""
         return {self.msg_id_hex(int(i)): self.parsed(int(i)) for i in self.survivor_indices()}
 
+    def parsed_payloads(self) -> list:
+        """The `sms.parsed` payloads of the surviving records, in replay order: what `publish_parsed_sms`
+        puts on the wire, `sms.model_dump_json().encode('utf-8')` (libs/nats_utils.py:127, worker.py:183)."""
+        return [self.parsed(int(i)).model_dump_json().encode("utf-8") for i in self.survivor_indices()]
+
+    def pocketbase_records(self) -> list:
+        """The record dict `upsert_parsed_sms` sends to PocketBase for every surviving record
+        (libs/pocketbase.py:296-309), in replay order."""
+        out = []
+        for i in self.survivor_indices():
+            p = self.parsed(int(i))
+            out.append({
+                "msg_id": p.msg_id, "original_body": p.raw_body, "sender": p.sender,
+                "datetime": p.date.isoformat(), "card": p.card, "amount": str(p.amount), "currency": p.currency,
+                "balance": str(p.balance) if p.balance is not None else None, "merchant": p.merchant,
+                "address": p.address, "city": p.city, "txn_type": p.txn_type})
+        return out
+
 
 class ReplayEngine:
     def __init__(self, device: int = 0, use_torch_stream: bool = True):

@@ -328,6 +328,32 @@ def test_scan_fuzz_against_oracle(engine):
         assert res.fixed_body(i) == fixed[i], repr(bs[i])
 
 
+def test_wire_formats_of_the_survivors(engine):
+    """The `sms.parsed` JSON payloads and the PocketBase record dicts of the surviving records equal what
+    the oracle's parsed objects serialise to (libs/nats_utils.py:127, libs/pocketbase.py:296-309)."""
+    import json
+    backup = synth.generate(3000, seed=91, dup_frac=0.3, mixed_locale=True, miss_frac=0.1)
+    engine.load_cache(backup.cache)
+    res = engine.replay(Batch.from_strings(backup.bodies, backup.senders, backup.date_ms), NOW)
+    ora = O.replay(backup.bodies, backup.senders, [O.iso_utc_from_ms(m) for m in backup.date_ms], backup.cache, NOW)
+    surv = [i for i, s in enumerate(ora.survivor) if s]
+    payloads, records = res.parsed_payloads(), res.pocketbase_records()
+    assert len(payloads) == len(records) == len(surv) > 500
+    for k, i in enumerate(surv):
+        p = ora.outcomes[i].parsed
+        got = json.loads(payloads[k])
+        assert got["msg_id"] == p.msg_id and got["raw_body"] == p.raw_body and got["sender"] == p.sender
+        assert got["date"] == p.date.isoformat() and got["amount"] == str(p.amount) and got["balance"] == str(p.balance)
+        assert got["txn_type"] == p.txn_type and got["card"] == p.card and got["merchant"] == p.merchant
+        assert got["currency"] == p.currency and got["address"] == p.address and got["city"] == p.city
+        assert got["device_id"] == "xml_backup" and got["parser_version"] == "llm-0.2.0"
+        r = records[k]
+        assert r == {"msg_id": p.msg_id, "original_body": p.raw_body, "sender": p.sender, "datetime": p.date.isoformat(),
+                     "card": p.card, "amount": str(p.amount), "currency": p.currency, "balance": str(p.balance),
+                     "merchant": p.merchant, "address": p.address, "city": p.city, "txn_type": r["txn_type"]}
+        assert str(getattr(r["txn_type"], "value", r["txn_type"])) == p.txn_type
+
+
 def test_full_size_properties(engine):
     """BASELINE.json config 2 size (1 M messages, 100 % hit for non-OTP bodies):
     properties that do not need the oracle at full size, plus a 2 000-message
