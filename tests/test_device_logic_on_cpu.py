@@ -181,3 +181,78 @@ def test_scan_fuzz_against_oracle():
         assert got == fixed and bool(fl & L.F_MODIFIED) == (fixed != b), repr(b)
         assert cols["cache_key"][i].tobytes() == O.cache_key(fixed), repr(b)
         assert int(cols["body_date"][i]) == O.pack_date(O.body_date(b)), repr(b)
+
+
+def test_decimal_fuzz_against_oracle():
+    """Random amount-like strings (both separators, every kind of white space, signs, letters, digits of
+    other scripts, 0 to 24 characters): parse_ambiguous_decimal's result, exponent and sign included, and
+    the Numeric(14,2) rounding derived from it."""
+    import random
+    rng = random.Random(17)
+    alphabet = "0123456789" * 3 + "..,,  -\u00a0\u202f\u2009\t\nE+eAMD$\u0665\uff11"
+    strings = ["".join(rng.choice(alphabet) for _ in range(rng.choice([0, 1, 2, 3, 5, 8, 12, 18, 24])))
+               for _ in range(30000)]
+    coef, exp, flags = H.decimal(strings)
+    for i, t in enumerate(strings):
+        want = O.decimal_triplet(t)
+        err = int(flags[i]) & 3
+        assert err == want[0], repr(t)
+        if err == 0:
+            assert ((int(flags[i]) >> 4) & 1, int(coef[i]), int(exp[i])) == want[1:], repr(t)
+
+
+def test_route_fuzz_against_oracle():
+    """Cache entries mutated at random (keys dropped, values of the wrong type, cards / dates / amounts of every
+    odd shape the reference's parse_sms_llm has an opinion on) against bodies with and without a body date:
+    status, date, card and amounts of the device logic equal the oracle's restatement of the hit branch."""
+    import random
+    rng = random.Random(23)
+    now = dt.datetime(2026, 1, 1)
+    pool = {
+        "txn_type": ["debit", "credit", "otp", "unknown", "DEBIT", "refund", None, 5],
+        "date": ["06.05.25 14:23", "10.06.2025 20:51", "31.02.25 10:00", "6.5.25 4:3", "06.05.25  14:23", "yesterday", "",
+                 "2025-06-10T20:51:00", "2025-06-10T20:51:00+04:00", "01.01.27 00:00", "12/31/2030", None, 1717000000,
+                 "06.05.25 14:23 ", "06.05.25 24:00", "June 10, 2025 8pm"],
+        "amount": ["52.00", "1,234.56", "1.234,56", "79 825,89", "-5.00", "abc", "", None, 12.5, 7, "1e5", "5-",
+                   "99999999999999999999", "0.005", "1,5", -3, "١٢"],
+        "currency": ["USD", "usd", None, "", 5],
+        "card": ["1234", "4083***7538", "**18", "*** 7538", "12 34 56", "", None, 1234, "١٢٣٤٥", "ab", "a\u00e9\u00ef\u00f6\u00fc\u00df"],
+        "merchant": ["SHOP", "", None, 0],
+        "city": ["YEREVAN", None],
+        "address": ["null", "MAIN STR 1", None, ""],
+        "balance": ["1842.74", "-10", None, "x", "0", 3.5, "1.000.000"],
+    }
+    bodies, entries = [], []
+    for i in range(4000):
+        body = rng.choice(["PAYMENT %d 06.05.25 14:23 done", "PAYMENT %d on 10.06.2025", "PAYMENT %d no date here",
+                           "PAYMENT %d 31.02.2025 then 01.03.25", "PAYMENT %d 4083***7538 12.12.2030"]) % i
+        v = {k: rng.choice(vals) for k, vals in pool.items()}
+        if rng.random() < 0.6:                        # mostly sane entries with one or two odd fields
+            v.update(txn_type="debit", date="06.05.25 14:23", amount="52.00", currency="usd", card="4083***7538",
+                     merchant="SHOP", city=None, address="null", balance="1842.74")
+            for k in rng.sample(list(pool), rng.choice([0, 1, 1, 2])):
+                v[k] = rng.choice(pool[k])
+        for k in list(v):
+            if rng.random() < 0.03:
+                del v[k]
+        if rng.random() < 0.02:
+            v = rng.choice([None, "a string", 5, ["list"]])
+        bodies.append(body)
+        entries.append(v)
+    sc = H.scan(bodies)
+    cache = {sc["cache_key"][i].tobytes().hex(): entries[i] for i in range(len(bodies))}
+    jr = H.join_route(sc, _table(cache), gemini_cache.pack_datetime(now))
+    seen = set()
+    for i, b in enumerate(bodies):
+        o = O.replay_one(b, "BANK", "2024-02-14T09:00:00+00:00", cache, now)
+        assert int(jr["status"][i]) == o.status, (i, entries[i], b)
+        seen.add(o.status)
+        if o.parsed is not None and o.status != O.ST_FAILED_EXC:
+            assert int(jr["date"][i]) == O.pack_datetime(o.parsed.date), (i, entries[i], b)
+            assert jr["card"][i, :int(jr["card_len"][i])].tobytes().decode() == o.parsed.card, (i, entries[i])
+            fl = int(jr["dec_flags"][i])
+            for w, sh, sg, want in (("amount", 0, 4, o.amount), ("balance", 2, 5, o.balance)):
+                assert (fl >> sh) & 3 == want[0], (i, w, entries[i])
+                if want[0] == 0:
+                    assert ((fl >> sg) & 1, int(jr[w + "_coef"][i]), int(jr[w + "_exp"][i])) == want[1:], (i, w, entries[i])
+    assert {O.ST_UPSERT, O.ST_PARSED_NO_MERCHANT, O.ST_UNMATCHED, O.ST_BROKEN, O.ST_FUTURE_DATE, O.ST_FAILED_EXC} <= seen
