@@ -71,7 +71,13 @@ constexpr int K1_TILE = 2 * K1_THREADS;      // messages per tile: every thread 
 #endif
 constexpr int K1_STAGE = K1_STAGE_KB * 1024;  // staged body bytes per tile
 constexpr int K1_PAD = 32;                // slack read by the unaligned word reader
-constexpr int K1_BUCKETS = 128;           // length buckets of 8 bytes for the in-tile sort
+#ifndef K1_BUCKET_SHIFT
+#define K1_BUCKET_SHIFT 2
+#endif
+#ifndef K1_BUCKETS_N
+#define K1_BUCKETS_N 256
+#endif
+constexpr int K1_BUCKETS = K1_BUCKETS_N;   // length buckets of 4 bytes for the in-tile sort; a multiple of 32
 
 struct __align__(16) K1Smem {
     DeviceTables tab;
@@ -192,7 +198,7 @@ k_scan_keys(const uint8_t* __restrict__ bytes, const int64_t* __restrict__ offse
                 }
                 nfit += fits[h] ? 1 : 0;
             }
-            if (tid < K1_BUCKETS) S.hist[tid] = 0;
+            for (int k = tid; k < K1_BUCKETS; k += K1_THREADS) S.hist[k] = 0;
             if (tid == 0) { S.next = 0; S.nr = 0; }
             // the first half is a prefix of the tile, so the count of fitting messages is exact
             // only if the second half is counted after the first: do two block-wide counts
@@ -219,7 +225,7 @@ k_scan_keys(const uint8_t* __restrict__ bytes, const int64_t* __restrict__ offse
                 const int64_t tail0 = (bulk_end > base) ? bulk_end : base;
                 if (tid < 16 && tail0 + tid < hi) S.stage[tail0 - base + tid] = bytes[tail0 + tid];
             }
-            // ---- while the copy is in flight: sort the tile's messages by length (8-byte buckets) so that
+            // ---- while the copy is in flight: sort the tile's messages by length (4-byte buckets) so that
             //      the 32 lanes of a warp walk bodies of about the same length and SHA block count
             int key[2] = {0, 0};
 #pragma unroll
@@ -229,27 +235,27 @@ k_scan_keys(const uint8_t* __restrict__ bytes, const int64_t* __restrict__ offse
                     const int len = (int)(my_hi[h] - my_lo[h]);
                     S.m_off[loc] = (int)(my_lo[h] - base);
                     S.m_len[loc] = len;
-                    int k = len >> 3;
+                    int k = len >> K1_BUCKET_SHIFT;
                     k = k < K1_BUCKETS - 1 ? k : K1_BUCKETS - 1;
                     key[h] = k;
                     atomicAdd(&S.hist[k], 1);
                 }
             }
             __syncthreads();
-            if (tid < 32) {                                  // exclusive scan of the 128 bucket counts, 4 per lane
-                const int a = S.hist[4 * tid], b = S.hist[4 * tid + 1], c = S.hist[4 * tid + 2], d4 = S.hist[4 * tid + 3];
-                const int sum = a + b + c + d4;
+            if (tid < 32) {                                  // exclusive scan of the bucket counts, K1_BUCKETS / 32 per lane
+                constexpr int PER = K1_BUCKETS / 32;
+                int c[PER], sum = 0;
+#pragma unroll
+                for (int k = 0; k < PER; ++k) { c[k] = S.hist[PER * tid + k]; sum += c[k]; }
                 int incl = sum;
 #pragma unroll
                 for (int d = 1; d < 32; d <<= 1) {
                     const int v = __shfl_up_sync(0xffffffffu, incl, d);
                     if (tid >= d) incl += v;
                 }
-                const int excl = incl - sum;
-                S.cursor[4 * tid] = excl;
-                S.cursor[4 * tid + 1] = excl + a;
-                S.cursor[4 * tid + 2] = excl + a + b;
-                S.cursor[4 * tid + 3] = excl + a + b + c;
+                int run = incl - sum;
+#pragma unroll
+                for (int k = 0; k < PER; ++k) { S.cursor[PER * tid + k] = run; run += c[k]; }
             }
             __syncthreads();
 #pragma unroll
