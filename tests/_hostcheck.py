@@ -32,6 +32,7 @@ def scan(bodies):
     data = np.concatenate([data, np.zeros(16, np.uint8)])
     rc = lib().hc_scan_keys(_p(data), _p(offsets), C.c_int64(n), _p(cols["msg_id"]), _p(cols["cache_key"]),
                             _p(cols["flags"]), _p(cols["body_date"]), _p(cols["fixed_len"]), _p(cols["fixed_bytes"]))
+    assert rc > -200000, f"sg_hash_pass disagrees with the plain digests (code {rc})"
     assert rc == 0, f"first pass + full pass disagree with the full pass at body {-100 - rc}: {bodies[-100 - rc]!r}"
     cols["offsets"] = offsets
     return cols

@@ -47,9 +47,18 @@ extern "C" int hc_scan_keys(const uint8_t* bytes, const int64_t* offsets, int64_
         if (sr.flags != full.flags || sr.body_date != full.body_date) return -100 - (int)i;
         uint32_t h1[5], h2[8];
         sg_sha1(m, len, h1);
+        // the kernel's hashing loop (sg_hash_pass, one copy, three modes) must agree with the plain digests
+        uint32_t p1[5], p2[8], q1[5] = {1, 2, 3, 4, 5}, q2[8];
+        sg_hash_pass(m, len, 3u, p1, p2);                       // untouched body: both digests in one walk
+        sg_hash_pass(m, len, 1u, q1, q2);                       // rewritten body, first pass: SHA-1 only
+        uint32_t o2[8];
+        sg_sha256(m, len, o2);
+        if (memcmp(p1, h1, 20) || memcmp(q1, h1, 20) || memcmp(p2, o2, 32)) return -200000 - (int)i;
         int flen = len;
         if (sr.flags & SG_F_MODIFIED) flen = sg_rewrite_fixed(m, len, T);
         sg_sha256(m, flen, h2);
+        sg_hash_pass(m, flen, 2u, q1, q2);                      // second pass: SHA-256 only, SHA-1 left alone
+        if (memcmp(q2, h2, 32) || memcmp(q1, h1, 20)) return -300000 - (int)i;
         put_be(msg_id + i * 20, h1, 5);
         put_be(cache_key + i * 32, h2, 8);
         flags[i] = (uint8_t)sr.flags;
