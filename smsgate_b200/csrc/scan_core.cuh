@@ -234,9 +234,18 @@ SG_HD ScanResult sg_scan_body_t(const uint8_t* m, int len, const ScanTables& T) 
     for (; i + 4 <= len; i += 4) {
         const uint32_t w4 = *reinterpret_cast<const uint32_t*>(m + i);
         if (w4 & 0x80808080u) {
+            // A high byte that is not a special lead (bit 31 of its class word) is stepped from the class
+            // table exactly as sg_scan_byte_careful's else-branch does: continuation bytes keep the CI / DM
+            // state, ordinary leads feed OTHER.  Cyrillic, Armenian, Greek ... words therefore stay in the
+            // branch-free loop; only a word holding a lead that may upper-case into ASCII, start a Unicode
+            // digit, U+00A0 or U+2022 is taken byte by byte.
+            const uint32_t any = T_BYTE_CLASS(T)[sg_byte(w4, 0)] | T_BYTE_CLASS(T)[sg_byte(w4, 1)] |
+                                 T_BYTE_CLASS(T)[sg_byte(w4, 2)] | T_BYTE_CLASS(T)[sg_byte(w4, 3)];
+            if ((int32_t)any < 0) {
 #pragma unroll 1
-            for (int k = 0; k < 4; ++k) st = sg_scan_byte_careful<FIRST>(m, len, i + k, T, st);
-            continue;
+                for (int k = 0; k < 4; ++k) st = sg_scan_byte_careful<FIRST>(m, len, i + k, T, st);
+                continue;
+            }
         }
         uint32_t ci = st.ci, cs = st.cs, dm = st.dm;
         const uint32_t dm_before = dm;
@@ -309,6 +318,18 @@ SG_HD int sg_rewrite_fixed(uint8_t* m, int len, const ScanTables& T) {
             ++r;
             cls = sg_byte(T_BYTE_CLASS(T)[b], 2) >> 1;   // DM class ids 0 other, 1 digit, 2 '.', 3 '*'
         } else {
+            if ((int32_t)T_BYTE_CLASS(T)[b] >= 0 && b >= 0xC2 && b <= 0xF4) {
+                // a lead that starts neither U+00A0, U+2022 nor a Unicode digit: one OTHER symbol, copied as is
+                int n = (b >= 0xF0) ? 4 : (b >= 0xE0) ? 3 : 2;
+                bool ok = n <= len - r;
+                for (int j = 1; ok && j < n; ++j) ok = (m[r + j] & 0xC0) == 0x80;
+                if (!ok) n = 1;                       // malformed: one byte, as sg_utf8_decode reports it
+                for (int j = 0; j < n; ++j) m[w + j] = m[r + j];
+                w += n;
+                r += n;
+                k = T.t->card_kmp[k * 4 + KMP_CLS_OTHER];
+                continue;
+            }
             uint32_t cp;
             const int n = sg_utf8_decode(m + r, len - r, &cp);
             if (cp == 0xA0) { m[w++] = ' '; cls = KMP_CLS_OTHER; }

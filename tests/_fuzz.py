@@ -12,7 +12,10 @@ PIECES = ["OTP", "otp", "Otp", "CODE:", "code:", "PASS:", "PASS=", "pass=", "NOT
           " ", " ", "\n", ".", ":", "=", "06.05.25", "10.06.2025", "31.02.2024", "29.02.24", "00.01.2024",
           "1٢.0١.2025", "١٢.01.2025", "12.01.٢٠٢٥", "99.99.99", "1.1.2025",
           "01.13.2025", "32.01.25", "0", "7", "42", "2025", "A", "z", "я", "€", "\U0001F600", "O", "T", "P",
-          "C", "OD", "E:", "PAS", "S:", "Dai", "ly limit", " exceeded"]
+          "C", "OD", "E:", "PAS", "S:", "Dai", "ly limit", " exceeded",
+          # scripts whose lead bytes are not special (they stay in the scan's word loop), next to needles and forms
+          "Покупка", "Баланс", "отп", "ОТП", "Գնում", "ΑΓΟΡΑ", "中文", "日本", "é", "Ü", "ö", "я1", "1я",
+          "я06.05.25", "06.05.25я", "я4083***7538я", "OTя", "OяTP", "Ωcode:", "ЖPASS=Ж"]
 
 
 def bodies(n, seed):
