@@ -28,7 +28,7 @@
 extern "C" {
 #endif
 
-#define SMSGATE_ABI_VERSION 1
+#define SMSGATE_ABI_VERSION 2
 
 /* error codes */
 #define SMSGATE_OK 0
@@ -130,6 +130,14 @@ const char* smsgate_last_error(const smsgate_ctx* ctx);
 /* Size the context's scratch (dedup table, staging for the host call) for
  * batches of up to max_msgs messages / max_bytes body bytes.  Allocates. */
 int smsgate_reserve(smsgate_ctx* ctx, int64_t max_msgs, int64_t max_bytes);
+/* Queue everything this context does from now on onto another cudaStream_t of its device.  The caller
+ * orders the streams (events): this is how a multi-GPU replay runs the dedup exchange of batch k on a
+ * side stream while the keys kernel of batch k+1 runs on the main one (smsgate_b200/dist.py).
+ * No reference counterpart (the reference is single-threaded asyncio, services/xml_watcher/watcher.py:78). */
+int smsgate_set_stream(smsgate_ctx* ctx, void* cuda_stream);
+/* How many CTAs smsgate_scan_keys may use: 0 = one per SM (default).  Fewer leaves SMs for kernels of
+ * another stream (the exchange above) while the keys kernel, which otherwise fills every SM, runs. */
+int smsgate_set_scan_ctas(smsgate_ctx* ctx, int ctas);
 /* Kernels launched by this context since creation (for bench accounting). */
 int64_t smsgate_launch_count(const smsgate_ctx* ctx);
 
@@ -146,6 +154,12 @@ int64_t smsgate_launch_count(const smsgate_ctx* ctx);
 int smsgate_cache_load(smsgate_ctx* ctx, int64_t m, const uint8_t* h_keys, const int32_t* h_val_offsets,
                        const uint8_t* h_val_bytes, const uint16_t* h_eflags, const int64_t* h_date_packed);
 int64_t smsgate_cache_size(const smsgate_ctx* ctx);
+/* Let `ctx` probe the table `owner` loaded instead of loading its own copy (two contexts on one GPU that
+ * keep two batches in flight, see smsgate_set_stream).  `owner` must outlive the sharing and must not
+ * reload its cache while `ctx` uses it; a later smsgate_cache_load / _cache_share on `ctx` ends the sharing.
+ * Replaces the same reference code as smsgate_cache_load: one `.gemini_cache` per process
+ * (libs/gemini_parser.py:33). */
+int smsgate_cache_share(smsgate_ctx* ctx, const smsgate_ctx* owner);
 
 /* ---- batch helpers (host buffers in and out) ----------------------------- */
 /* libs.decimal_utils.parse_ambiguous_decimal over n strings (libs/decimal_utils.py:4-63).
@@ -306,6 +320,8 @@ typedef struct smsgate_p2p {
     uint32_t* stage[SMSGATE_MAX_WORLD];   /* [world * (bitmap_words / world + 12)] words per rank: staged bitmap slices */
     uint32_t* collide[SMSGATE_MAX_WORLD]; /* [bitmap_words] words per rank: bits set on two or more ranks */
     int64_t bitmap_words;                 /* power of two in [64, 2^26]; about 16 bits per key of the whole job is plenty */
+    int64_t gfl_slots;                    /* slots every gfl array holds (a pair of int64 each); a batch whose table would
+                                             need more is refused with SMSGATE_E_LIMIT instead of storing out of bounds */
 } smsgate_p2p;
 /* Size the owner-side table for inboxes of `capacity` records.  Allocates. */
 int smsgate_p2p_reserve(smsgate_ctx* ctx, int64_t capacity);
@@ -360,6 +376,13 @@ int smsgate_replay_host_records(smsgate_ctx* ctx, const uint8_t* h_bytes, const 
 int smsgate_replay_host_records_begin(smsgate_ctx* ctx, const uint8_t* h_bytes, const int64_t* h_offsets, int64_t n,
                                       int64_t now_packed, int64_t base_index, smsgate_record* h_records);
 int smsgate_replay_host_records_finish(smsgate_ctx* ctx, int64_t* h_verdict);
+/* Columns of the LAST smsgate_replay_host* batch that the packed record does not carry (card, cache_key,
+ * fixed_len, fixed_bytes, amount_cents, balance_cents) or any other column, copied to the non-NULL host
+ * pointers of h_out on request: the device keeps every column of a batch until the next replay or reserve
+ * on this context.  n must be that batch's size; SMSGATE_E_STATE when the batch is gone.  Synchronises.
+ * This is what lets `parse_sms_llm`-style materialisation (libs/gemini_parser.py:249-266) work on a result
+ * that came back as records. */
+int smsgate_fetch_columns(smsgate_ctx* ctx, int64_t n, const smsgate_outputs* h_out);
 
 /* ---- upsert-by-msg_id for callers that must not allocate -------------------
  * No counterpart in the reference (it has no device memory to manage).
@@ -378,10 +401,17 @@ int smsgate_replay_host_records_finish(smsgate_ctx* ctx, int64_t* h_verdict);
  *   - at most SMSGATE_DEDUP_STATIC_MAX messages per call; a larger n is refused
  *     with SMSGATE_E_LIMIT and a message in errbuf (split the batch, or use
  *     smsgate_dedup with smsgate_reserve);
- *   - the built-in table takes about 28 MiB on every GPU that loads the library,
+ *   - the built-in table takes 20 MiB on every GPU that loads the library,
  *     for the life of the process;
- *   - the first call on a given device looks up the table's device address
- *     (cudaGetSymbolAddress), once per device;
+ *   - the first call on a given device does the set-up for that device: it
+ *     looks up the table's device address (cudaGetSymbolAddress), once.  Make
+ *     that first call before any stream capture begins on the device;
+ *   - the call makes `device` the calling thread's current CUDA device and
+ *     leaves it so; cuda_stream must be a stream of that device (NULL = its
+ *     default stream);
+ *   - it only queues work: the table reset and the two kernels run on
+ *     cuda_stream and the outputs are complete once that stream has reached
+ *     them (synchronise the stream, or order later work on it, before reading);
  *   - all calls on one device share the table: each call resets the part it
  *     uses, and two calls whose GPU work overlaps (different streams, different
  *     threads) corrupt each other - serialise them;

@@ -11,7 +11,7 @@ import os
 _HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(_HERE, "libsmsgate_b200.so")
 
-ABI_VERSION = 1
+ABI_VERSION = 2
 
 # flags / status / entry flags — mirror the header
 F_WORKER_SKIP, F_PARSER_OTP, F_MODIFIED, F_BODY_DATE = 0x01, 0x02, 0x04, 0x08
@@ -65,7 +65,8 @@ class P2P(C.Structure):
     _fields_ = [("world", C.c_int32), ("rank", C.c_int32),
                 ("inbox", C.c_void_p * 64), ("in_count", C.c_void_p * 64),
                 ("gfl", C.c_void_p * 64), ("capacity", C.c_int64),
-                ("stage", C.c_void_p * 64), ("collide", C.c_void_p * 64), ("bitmap_words", C.c_int64)]
+                ("stage", C.c_void_p * 64), ("collide", C.c_void_p * 64), ("bitmap_words", C.c_int64),
+                ("gfl_slots", C.c_int64)]
 
 
 class LibraryMissing(RuntimeError):
@@ -95,6 +96,9 @@ def lib():
         "smsgate_launch_count": (i64, [vp]),
         "smsgate_cache_load": (i32, [vp, i64, vp, vp, vp, vp, vp]),
         "smsgate_cache_size": (i64, [vp]),
+        "smsgate_cache_share": (i32, [vp, vp]),
+        "smsgate_set_stream": (i32, [vp, vp]),
+        "smsgate_set_scan_ctas": (i32, [vp, i32]),
         "smsgate_decimal_batch": (i32, [vp, i64, vp, vp, vp, vp, vp]),
         "smsgate_strict_date_batch": (i32, [vp, i64, vp, vp, vp]),
         "smsgate_dt_str_batch": (i32, [vp, i64, vp, vp, vp]),
@@ -113,6 +117,7 @@ def lib():
         "smsgate_replay_host_records": (i32, [vp, vp, vp, i64, i64, i64, vp, vp]),
         "smsgate_replay_host_records_begin": (i32, [vp, vp, vp, i64, i64, i64, vp]),
         "smsgate_replay_host_records_finish": (i32, [vp, vp]),
+        "smsgate_fetch_columns": (i32, [vp, i64, C.POINTER(Outputs)]),
         "smsgate_replay_host_timeline": (i32, [vp, C.POINTER(C.c_float), i32]),
         "smsgate_replay_host_begin": (i32, [vp, vp, vp, i64, i64, i64, C.POINTER(Outputs)]),
         "smsgate_device_view": (i32, [vp, i64, C.POINTER(Outputs)]),

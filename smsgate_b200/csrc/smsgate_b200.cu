@@ -438,13 +438,40 @@ __global__ void k_cache_fix_fp(const uint8_t* __restrict__ keys, int2* __restric
     if (e >= 0) table[p].y = (int)key_fp(keys + (int64_t)e * 32);
 }
 
+// Per cache entry, next to the table: where its four strings start, how long each is and the loader's
+// flags, in ONE 16-byte record - a hit reads one sector here instead of one each from val_offsets (20 bytes
+// straddling two), eflags and date_packed.  A length of 0xFFFF means "look it up in val_offsets" (a field
+// of 64 KiB or more); date_packed is read only for the entries whose flags say it is used.
+struct __align__(16) CacheSide {
+    int32_t val_off;
+    uint16_t eflags;
+    uint16_t len[4];     // str(amount), str(balance), date, card
+    uint16_t pad;
+};
+static_assert(sizeof(CacheSide) == 16, "one side record is 16 bytes");
+
+__global__ void k_cache_side(int64_t m, const int32_t* __restrict__ val_offsets, const uint16_t* __restrict__ eflags,
+                             CacheSide* __restrict__ side) {
+    const int64_t e = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+    if (e >= m) return;
+    const int32_t* o = val_offsets + e * 4;
+    CacheSide sd;
+    sd.val_off = o[0];
+    sd.eflags = eflags[e];
+    bool wide = false;
+    for (int k = 0; k < 4; ++k) wide |= (o[k + 1] - o[k]) >= 0xFFFF;
+    for (int k = 0; k < 4; ++k) sd.len[k] = wide ? (uint16_t)0xFFFF : (uint16_t)(o[k + 1] - o[k]);
+    sd.pad = 0;
+    side[e] = sd;
+}
+
 struct CacheView {
     const uint8_t* keys;
     const int2* table;
     uint64_t mask;
     const int32_t* val_offsets;
     const uint8_t* val_bytes;
-    const uint16_t* eflags;
+    const CacheSide* side;
     const int64_t* date_packed;
     int64_t m;
 };
@@ -465,13 +492,16 @@ struct JoinOut {
 };
 
 // ------------------------------------------------------------------ dedup (upsert-by-msg_id)
+// One 8-byte slot per key: {first, last} = lowest / highest local index of the messages that carry it.
+// `first` doubles as the slot's key: any message holding the key identifies it, so no separate owner word
+// is needed, and the CAS that claims a slot, the atomicMin and the atomicMax all land in one 32-byte sector.
+// Empty = all bits set (first = 0xFFFFFFFF as unsigned, last = -1), so one memset clears the table.
 struct DedupScratch {
-    int32_t* owner;    // [cap] local index of the message that claimed the slot, -1 = empty
-    int32_t* first;    // [cap] min local index with this key
-    int32_t* last;     // [cap] max local index with this key
+    int2* tab;         // [cap] x = first (unsigned, 0xFFFFFFFF = empty), y = last
     int32_t* slot_of;  // [n]   slot of message i, -1 = not an upsert
     uint64_t mask;
 };
+constexpr unsigned DD_EMPTY = 0xFFFFFFFFu;
 
 __device__ __forceinline__ bool id20_equal(const uint8_t* a, const uint8_t* b) {
     const uint32_t* x = reinterpret_cast<const uint32_t*>(a);
@@ -484,14 +514,16 @@ __device__ __forceinline__ void dedup_insert_one(int64_t i, const uint8_t* __res
     const uint8_t* k = msg_id + i * 20;
     const uint32_t* kw = reinterpret_cast<const uint32_t*>(k);
     uint64_t pos = (((uint64_t)kw[1] << 32) | kw[0]) & D.mask;
+    bool claimed = false;
     for (;;) {
-        int prev = D.owner[pos];
-        if (prev == -1) prev = atomicCAS(&D.owner[pos], -1, (int)i);
-        if (prev == -1 || prev == (int)i || id20_equal(msg_id + (int64_t)prev * 20, k)) break;
+        const unsigned prev = atomicCAS(reinterpret_cast<unsigned*>(&D.tab[pos].x), DD_EMPTY, (unsigned)i);
+        if (prev == DD_EMPTY) { claimed = true; break; }
+        // `prev` is some message with this slot's key (a concurrent atomicMin only swaps it for another one)
+        if (prev == (unsigned)i || id20_equal(msg_id + (int64_t)prev * 20, k)) break;
         pos = (pos + 1) & D.mask;
     }
-    atomicMin(&D.first[pos], (int)i);
-    atomicMax(&D.last[pos], (int)i);
+    if (!claimed) atomicMin(reinterpret_cast<unsigned*>(&D.tab[pos].x), (unsigned)i);
+    atomicMax(&D.tab[pos].y, (int)i);
     D.slot_of[i] = (int32_t)pos;
 }
 
@@ -507,6 +539,7 @@ k_join_route(int64_t n, const uint8_t* __restrict__ cache_key, const uint8_t* __
     const uint4* kp = reinterpret_cast<const uint4*>(cache_key + i * 32);
     const uint4 k0 = kp[0], k1 = kp[1];
     int e = -1;
+    uint4 sdw = make_uint4(0, 0, 0, 0);
     if (C.m > 0) {
         uint64_t pos = (((uint64_t)k0.y << 32) | k0.x) & C.mask;
         const int fp = (int)k0.z;
@@ -516,6 +549,7 @@ k_join_route(int64_t n, const uint8_t* __restrict__ cache_key, const uint8_t* __
             if (sl.y == fp) {
                 const uint4* a = reinterpret_cast<const uint4*>(C.keys + (int64_t)sl.x * 32);
                 const uint4 a0 = a[0], a1 = a[1];
+                sdw = *reinterpret_cast<const uint4*>(C.side + sl.x);      // in flight together with the key
                 if (a0.x == k0.x && a0.y == k0.y && a0.z == k0.z && a0.w == k0.w && a1.x == k1.x && a1.y == k1.y &&
                     a1.z == k1.z && a1.w == k1.w) {
                     e = sl.x;
@@ -531,14 +565,19 @@ k_join_route(int64_t n, const uint8_t* __restrict__ cache_key, const uint8_t* __
     ev.eflags = 0;
     ev.date_packed = 0;
     if (e >= 0) {
-        const int32_t* o = C.val_offsets + (int64_t)e * 4;
-        const int32_t o0 = o[0], o1 = o[1], o2 = o[2], o3 = o[3], o4 = o[4];
-        ev.amount = C.val_bytes + o0; ev.amount_len = o1 - o0;
-        ev.balance = C.val_bytes + o1; ev.balance_len = o2 - o1;
-        ev.date = C.val_bytes + o2; ev.date_len = o3 - o2;
-        ev.card = C.val_bytes + o3; ev.card_len = o4 - o3;
-        ev.eflags = C.eflags[e];
-        ev.date_packed = C.date_packed[e];
+        // side record: x = val_off, y = eflags | len[0] << 16, z = len[1] | len[2] << 16, w = len[3]
+        int32_t o0 = (int32_t)sdw.x, l0 = (int32_t)(sdw.y >> 16), l1 = (int32_t)(sdw.z & 0xFFFF),
+                l2 = (int32_t)(sdw.z >> 16), l3 = (int32_t)(sdw.w & 0xFFFF);
+        if (l0 == 0xFFFF) {                              // a field of 64 KiB or more: the full offsets
+            const int32_t* o = C.val_offsets + (int64_t)e * 4;
+            o0 = o[0]; l0 = o[1] - o[0]; l1 = o[2] - o[1]; l2 = o[3] - o[2]; l3 = o[4] - o[3];
+        }
+        ev.amount = C.val_bytes + o0; ev.amount_len = l0;
+        ev.balance = ev.amount + l0; ev.balance_len = l1;
+        ev.date = ev.balance + l1; ev.date_len = l2;
+        ev.card = ev.date + l2; ev.card_len = l3;
+        ev.eflags = sdw.y & 0xFFFF;
+        if (ev.eflags & (SG_E_DATE_HOST | SG_E_DATE_NOBODY)) ev.date_packed = C.date_packed[e];
     }
     const RouteResult r = sg_route(flags[i], body_date[i], e >= 0, ev, now_packed);
     if (out.slot) out.slot[i] = e;
@@ -561,7 +600,7 @@ k_join_route(int64_t n, const uint8_t* __restrict__ cache_key, const uint8_t* __
     if (out.card_len) out.card_len[i] = (uint8_t)r.card_bytes;
     // fused upsert-table insert (the whole-path calls): message i of this launch is message dedup_i0 + i of
     // the batch the table was cleared for; saves a launch and a second pass over msg_id / status
-    if (D.owner) {
+    if (D.tab) {
         if (r.status == SG_ST_UPSERT) dedup_insert_one(dedup_i0 + i, dedup_ids, D);
         else D.slot_of[dedup_i0 + i] = -1;
     }
@@ -588,7 +627,8 @@ k_dedup_resolve(int64_t n, int64_t base_index, DedupScratch D, uint8_t* __restri
     uint8_t sv = 0, fs = 0;
     int64_t li = -1;
     if (sl >= 0) {
-        const int32_t l = D.last[sl], f = D.first[sl];
+        const int2 fl = D.tab[sl];
+        const int32_t l = fl.y, f = fl.x;
         sv = (l == (int32_t)i);
         fs = (f == (int32_t)i);
         li = base_index + l;
@@ -641,9 +681,9 @@ k_xsrc_probe(int64_t n_dev, const uint8_t* __restrict__ dev_sha1, const uint8_t*
     uint64_t pos = (((uint64_t)kw[1] << 32) | kw[0]) & D.mask;
     int32_t found = -1;
     for (;;) {
-        const int owner = D.owner[pos];
-        if (owner == -1) break;
-        if (id20_equal(xml_sha1 + (int64_t)owner * 20, k)) { found = D.first[pos]; break; }
+        const int first = D.tab[pos].x;                  // lowest XML index with the slot's key, -1 = empty
+        if (first == -1) break;
+        if (id20_equal(xml_sha1 + (int64_t)first * 20, k)) { found = first; break; }
         pos = (pos + 1) & D.mask;
     }
     match[i] = found;
@@ -691,6 +731,7 @@ struct smsgate_ctx {
     cudaEvent_t ev_start = nullptr, ev_dedup = nullptr, ev_done = nullptr;
     int64_t host_n = 0, host_total = 0;      // batch of the pending smsgate_replay_host_begin
     int host_chunks = 0;                     // chunks of the last smsgate_replay_host_begin (timeline)
+    int64_t view_n = 0, view_total = 0;      // batch whose columns are still in s_out / s_fixed (smsgate_fetch_columns)
     // pending XML extraction (smsgate_xml_scan .. smsgate_xml_emit)
     uint8_t* xml_slab = nullptr;
     int64_t xml_n = 0, xml_T = 0, xml_nx = 0;
@@ -700,6 +741,8 @@ struct smsgate_ctx {
     int32_t *xml_name_off = nullptr, *xml_name_len = nullptr;
     uint8_t *xml_kind = nullptr, *xml_mflags = nullptr;
     int sm_count = 148;
+    int scan_ctas = 0;                       // CTAs of k_scan_keys, 0 = one per SM (smsgate_set_scan_ctas)
+    bool cache_shared = false;               // the cache arrays belong to another context (smsgate_cache_share)
     std::string err;
     int64_t launches = 0;
     DeviceTables* d_tables = nullptr;
@@ -713,10 +756,12 @@ struct smsgate_ctx {
     int32_t* c_val_offsets = nullptr;
     uint8_t* c_val_bytes = nullptr;
     uint16_t* c_eflags = nullptr;
+    CacheSide* c_side = nullptr;
     int64_t* c_date_packed = nullptr;
     // scratch sized by reserve()
     int64_t cap_msgs = 0, cap_bytes = 0;
-    int32_t *d_owner = nullptr, *d_first = nullptr, *d_last = nullptr, *d_slot_of = nullptr;
+    int2* d_dtab = nullptr;                             // [dd_cap] upsert table slots {first, last}
+    int32_t* d_slot_of = nullptr;
     uint64_t dd_cap = 0;
     int64_t *d_gfirst = nullptr, *d_glast = nullptr;   // [dd_cap] global first / last index per local slot
     int* d_counts = nullptr;                            // [SMSGATE_MAX_WORLD] export counters / cursors
@@ -841,18 +886,24 @@ extern "C" int smsgate_create(int device, void* cuda_stream, smsgate_ctx** out) 
 }
 
 static void free_cache(smsgate_ctx* c) {
+    if (c->cache_shared) {
+        c->c_keys = nullptr; c->c_table = nullptr; c->c_val_offsets = nullptr; c->c_val_bytes = nullptr;
+        c->c_eflags = nullptr; c->c_date_packed = nullptr; c->c_side = nullptr;
+        c->cache_m = 0; c->c_cap = 0; c->cache_shared = false;
+        return;
+    }
     cudaFree(c->c_keys); cudaFree(c->c_table); cudaFree(c->c_val_offsets); cudaFree(c->c_val_bytes);
-    cudaFree(c->c_eflags); cudaFree(c->c_date_packed);
+    cudaFree(c->c_eflags); cudaFree(c->c_date_packed); cudaFree(c->c_side);
     c->c_keys = nullptr; c->c_table = nullptr; c->c_val_offsets = nullptr; c->c_val_bytes = nullptr;
-    c->c_eflags = nullptr; c->c_date_packed = nullptr;
+    c->c_eflags = nullptr; c->c_date_packed = nullptr; c->c_side = nullptr;
     c->cache_m = 0; c->c_cap = 0;
 }
 static void free_scratch(smsgate_ctx* c) {
-    cudaFree(c->d_owner); cudaFree(c->d_first); cudaFree(c->d_last); cudaFree(c->d_slot_of);
+    cudaFree(c->d_dtab); cudaFree(c->d_slot_of);
     cudaFree(c->d_gfirst); cudaFree(c->d_glast); cudaFree(c->d_counts); cudaFree(c->d_cursor);
     c->d_gfirst = c->d_glast = nullptr; c->d_counts = nullptr; c->d_cursor = nullptr;
     cudaFree(c->s_bytes); cudaFree(c->s_offsets); cudaFree(c->s_out); cudaFree(c->s_fixed); cudaFree(c->s_records); cudaFree(c->s_verdict);
-    c->d_owner = c->d_first = c->d_last = c->d_slot_of = nullptr;
+    c->d_dtab = nullptr; c->d_slot_of = nullptr;
     c->s_bytes = nullptr; c->s_offsets = nullptr; c->s_out = nullptr; c->s_fixed = nullptr; c->s_records = nullptr; c->s_verdict = nullptr;
     c->cap_msgs = c->cap_bytes = 0; c->dd_cap = 0;
 }
@@ -861,12 +912,12 @@ extern "C" void smsgate_destroy(smsgate_ctx* ctx) {
     if (!ctx) return;
     cudaSetDevice(ctx->device);
     cudaStreamSynchronize(ctx->stream);
+    smsgate_xml_release(ctx);                            // a scan that was never emitted still holds the document
     free_cache(ctx);
     free_scratch(ctx);
     cudaFree(ctx->mg_owner); cudaFree(ctx->mg_first); cudaFree(ctx->mg_last); cudaFree(ctx->mg_slot_of);
     cudaFree(ctx->p2p_table); cudaFree(ctx->p2p_slot_of); cudaFree(ctx->p2p_overflow); cudaFree(ctx->p2p_bits);
     cudaFree(ctx->d_legacy);
-    cudaFree(ctx->xml_slab);
     cudaFree(ctx->d_tables);
     if (ctx->s_h2d) { cudaStreamSynchronize(ctx->s_h2d); cudaStreamDestroy(ctx->s_h2d); }
     if (ctx->s_d2h) { cudaStreamSynchronize(ctx->s_d2h); cudaStreamDestroy(ctx->s_d2h); }
@@ -892,10 +943,9 @@ extern "C" int smsgate_reserve(smsgate_ctx* ctx, int64_t max_msgs, int64_t max_b
     if (max_msgs <= ctx->cap_msgs && max_bytes <= ctx->cap_bytes) return SMSGATE_OK;
     CUDA_TRY(ctx, cudaStreamSynchronize(ctx->stream));
     free_scratch(ctx);
+    ctx->view_n = ctx->view_total = 0;
     const uint64_t cap = pow2_at_least((uint64_t)(max_msgs > 8 ? max_msgs : 8) * 2);
-    CUDA_TRY(ctx, cudaMalloc(&ctx->d_owner, cap * 4));
-    CUDA_TRY(ctx, cudaMalloc(&ctx->d_first, cap * 4));
-    CUDA_TRY(ctx, cudaMalloc(&ctx->d_last, cap * 4));
+    CUDA_TRY(ctx, cudaMalloc(&ctx->d_dtab, cap * sizeof(int2)));
     CUDA_TRY(ctx, cudaMalloc(&ctx->d_slot_of, (size_t)(max_msgs + 1) * 4));
     CUDA_TRY(ctx, cudaMalloc(&ctx->d_gfirst, cap * 8));
     CUDA_TRY(ctx, cudaMalloc(&ctx->d_glast, cap * 8));
@@ -932,6 +982,7 @@ extern "C" int smsgate_cache_load(smsgate_ctx* ctx, int64_t m, const uint8_t* h_
     CUDA_TRY(ctx, cudaMalloc(&ctx->c_val_bytes, (size_t)vbytes + 16));
     CUDA_TRY(ctx, cudaMalloc(&ctx->c_eflags, (size_t)m * 2));
     CUDA_TRY(ctx, cudaMalloc(&ctx->c_date_packed, (size_t)m * 8));
+    CUDA_TRY(ctx, cudaMalloc(&ctx->c_side, (size_t)m * sizeof(CacheSide)));
     cudaStream_t st = ctx->stream;
     CUDA_TRY(ctx, cudaMemcpyAsync(ctx->c_keys, h_keys, (size_t)m * 32, cudaMemcpyHostToDevice, st));
     CUDA_TRY(ctx, cudaMemcpyAsync(ctx->c_val_offsets, h_val_offsets, (size_t)(4 * m + 1) * 4, cudaMemcpyHostToDevice, st));
@@ -944,7 +995,8 @@ extern "C" int smsgate_cache_load(smsgate_ctx* ctx, int64_t m, const uint8_t* h_
     CUDA_TRY(ctx, cudaMemsetAsync(d_dup, 0, 4, st));
     k_cache_build<<<(unsigned)((m + 255) / 256), 256, 0, st>>>(ctx->c_keys, m, ctx->c_table, cap - 1, d_dup);
     k_cache_fix_fp<<<(unsigned)((cap + 255) / 256), 256, 0, st>>>(ctx->c_keys, ctx->c_table, cap);
-    ctx->launches += 2;
+    k_cache_side<<<(unsigned)((m + 255) / 256), 256, 0, st>>>(m, ctx->c_val_offsets, ctx->c_eflags, ctx->c_side);
+    ctx->launches += 3;
     int dup = 0;
     CUDA_TRY(ctx, cudaMemcpyAsync(&dup, d_dup, 4, cudaMemcpyDeviceToHost, st));
     CUDA_TRY(ctx, cudaStreamSynchronize(st));
@@ -956,6 +1008,33 @@ extern "C" int smsgate_cache_load(smsgate_ctx* ctx, int64_t m, const uint8_t* h_
     }
     ctx->cache_m = m;
     ctx->c_cap = cap;
+    return SMSGATE_OK;
+}
+
+extern "C" int smsgate_cache_share(smsgate_ctx* ctx, const smsgate_ctx* owner) {
+    if (!ctx || !owner || ctx == owner) return ctx ? fail(ctx, SMSGATE_E_ARG, "cache_share: bad argument") : SMSGATE_E_ARG;
+    if (owner->device != ctx->device) return fail(ctx, SMSGATE_E_ARG, "cache_share: the contexts are on different devices");
+    if (owner->cache_shared) return fail(ctx, SMSGATE_E_ARG, "cache_share: share with the context that loaded the cache");
+    CUDA_TRY(ctx, cudaSetDevice(ctx->device));
+    CUDA_TRY(ctx, cudaStreamSynchronize(ctx->stream));
+    free_cache(ctx);
+    ctx->c_keys = owner->c_keys; ctx->c_table = owner->c_table; ctx->c_val_offsets = owner->c_val_offsets;
+    ctx->c_val_bytes = owner->c_val_bytes; ctx->c_eflags = owner->c_eflags; ctx->c_date_packed = owner->c_date_packed;
+    ctx->c_side = owner->c_side; ctx->cache_m = owner->cache_m; ctx->c_cap = owner->c_cap;
+    ctx->cache_shared = owner->cache_m > 0;
+    return SMSGATE_OK;
+}
+
+extern "C" int smsgate_set_stream(smsgate_ctx* ctx, void* cuda_stream) {
+    if (!ctx) return SMSGATE_E_ARG;
+    ctx->stream = (cudaStream_t)cuda_stream;
+    return SMSGATE_OK;
+}
+
+extern "C" int smsgate_set_scan_ctas(smsgate_ctx* ctx, int ctas) {
+    if (!ctx) return SMSGATE_E_ARG;
+    if (ctas < 0 || ctas > ctx->sm_count) return fail(ctx, SMSGATE_E_ARG, "set_scan_ctas: between 0 (default) and the SM count");
+    ctx->scan_ctas = ctas;
     return SMSGATE_OK;
 }
 
@@ -1298,7 +1377,7 @@ extern "C" int smsgate_scan_keys(smsgate_ctx* ctx, const uint8_t* d_bytes, const
     ScanOut so{out->msg_id, out->cache_key, out->flags, out->body_date, out->fixed_len, out->fixed_bytes};
     // one CTA per SM as soon as there are 64 messages for each: a small batch is latency, not throughput
     const int64_t want = (n + 63) / 64;
-    const int64_t maxgrid = (int64_t)ctx->sm_count * K1_CTAS_PER_SM;
+    const int64_t maxgrid = ctx->scan_ctas > 0 ? ctx->scan_ctas : (int64_t)ctx->sm_count * K1_CTAS_PER_SM;
     const unsigned grid = (unsigned)(want < maxgrid ? want : maxgrid);
     k_scan_keys<<<grid, K1_THREADS, sizeof(K1Smem), ctx->stream>>>(d_bytes, d_offsets, n, ctx->d_tables, so);
     ctx->launches += 1;
@@ -1315,10 +1394,10 @@ static int join_route_impl(smsgate_ctx* ctx, int64_t n, int64_t now_packed, cons
         return fail(ctx, SMSGATE_E_ARG, "join_route needs the cache_key, flags and body_date columns of stage 1");
     CUDA_TRY(ctx, cudaSetDevice(ctx->device));
     CacheView C{ctx->c_keys, ctx->c_table, ctx->c_cap ? ctx->c_cap - 1 : 0, ctx->c_val_offsets, ctx->c_val_bytes,
-                ctx->c_eflags, ctx->c_date_packed, ctx->cache_m};
+                ctx->c_side, ctx->c_date_packed, ctx->cache_m};
     JoinOut jo{out->slot, out->status, out->amount_coef, out->balance_coef, out->amount_exp, out->balance_exp,
                out->dec_flags, out->date, out->card, out->card_len, out->amount_cents, out->balance_cents};
-    const DedupScratch none{nullptr, nullptr, nullptr, nullptr, 0};
+    const DedupScratch none{nullptr, nullptr, 0};
     k_join_route<<<(unsigned)((n + 255) / 256), 256, 0, ctx->stream>>>(n, out->cache_key, out->flags, out->body_date,
                                                                         now_packed, C, jo, D ? *D : none, dedup_i0,
                                                                         dedup_ids);
@@ -1336,10 +1415,8 @@ static int dedup_prepare(smsgate_ctx* ctx, int64_t n, DedupScratch* D) {
     uint64_t cap = pow2_at_least((uint64_t)(n > 8 ? n : 8) * 2);
     if (cap > ctx->dd_cap) cap = ctx->dd_cap;
     cudaStream_t st = ctx->stream;
-    CUDA_TRY(ctx, cudaMemsetAsync(ctx->d_owner, 0xFF, cap * 4, st));
-    CUDA_TRY(ctx, cudaMemsetAsync(ctx->d_first, 0x7F, cap * 4, st));
-    CUDA_TRY(ctx, cudaMemsetAsync(ctx->d_last, 0xFF, cap * 4, st));
-    *D = DedupScratch{ctx->d_owner, ctx->d_first, ctx->d_last, ctx->d_slot_of, cap - 1};
+    CUDA_TRY(ctx, cudaMemsetAsync(ctx->d_dtab, 0xFF, cap * sizeof(int2), st));
+    *D = DedupScratch{ctx->d_dtab, ctx->d_slot_of, cap - 1};
     return SMSGATE_OK;
 }
 
@@ -1384,7 +1461,7 @@ extern "C" int smsgate_cross_source(smsgate_ctx* ctx, int64_t n_xml, const uint8
     if (n_xml > ctx->cap_msgs) return fail(ctx, SMSGATE_E_STATE, "cross_source: more XML messages than smsgate_reserve() sized the scratch for");
     CUDA_TRY(ctx, cudaSetDevice(ctx->device));
     cudaStream_t st = ctx->stream;
-    if (n_xml == 0 || !ctx->d_owner) {
+    if (n_xml == 0 || !ctx->d_dtab) {
         CUDA_TRY(ctx, cudaMemsetAsync(d_match, 0xFF, (size_t)n_dev * 4, st));
         return SMSGATE_OK;
     }
@@ -1513,6 +1590,7 @@ static int replay_host_begin_impl(smsgate_ctx* ctx, const uint8_t* h_bytes, cons
     if (n < 0 || (!h_cols && !h_records) || (n > 0 && (!h_offsets))) return fail(ctx, SMSGATE_E_ARG, "replay_host: NULL argument");
     ctx->host_n = 0;
     ctx->host_total = 0;
+    ctx->view_n = ctx->view_total = 0;
     if (n == 0) return SMSGATE_OK;
     const int64_t first = h_offsets[0], total = h_offsets[n];
     if (first != 0) return fail(ctx, SMSGATE_E_ARG, "replay_host: offsets[0] must be 0");
@@ -1599,6 +1677,8 @@ static int replay_host_begin_impl(smsgate_ctx* ctx, const uint8_t* h_bytes, cons
     ctx->host_n = n;
     ctx->host_total = total;
     ctx->host_chunks = nchunks;
+    ctx->view_n = n;
+    ctx->view_total = total;
     return SMSGATE_OK;
 }
 
@@ -1660,6 +1740,28 @@ extern "C" int smsgate_replay_host_records(smsgate_ctx* ctx, const uint8_t* h_by
     return smsgate_replay_host_records_finish(ctx, h_verdict);
 }
 
+extern "C" int smsgate_fetch_columns(smsgate_ctx* ctx, int64_t n, const smsgate_outputs* h_out) {
+    if (!ctx || !h_out) return SMSGATE_E_ARG;
+    if (n <= 0 || n != ctx->view_n || ctx->host_n != 0)
+        return fail(ctx, SMSGATE_E_STATE, "fetch_columns: the device no longer holds the columns of that batch "
+                                          "(a later replay or reserve replaced them, or the call is still pending)");
+    CUDA_TRY(ctx, cudaSetDevice(ctx->device));
+    cudaStream_t st = ctx->stream;
+    smsgate_outputs d;
+    carve_slab(ctx->s_out, n, ctx->s_fixed, &d);
+#define FETCH(col, w) \
+    if (h_out->col) CUDA_TRY(ctx, cudaMemcpyAsync(h_out->col, d.col, (size_t)(n * (w)) * sizeof(*d.col), cudaMemcpyDeviceToHost, st))
+    FETCH(msg_id, 20); FETCH(cache_key, 32); FETCH(flags, 1); FETCH(body_date, 1); FETCH(fixed_len, 1); FETCH(slot, 1);
+    FETCH(status, 1); FETCH(amount_coef, 1); FETCH(balance_coef, 1); FETCH(amount_exp, 1); FETCH(balance_exp, 1);
+    FETCH(dec_flags, 1); FETCH(date, 1); FETCH(card, 16); FETCH(card_len, 1); FETCH(survivor, 1); FETCH(first_seen, 1);
+    FETCH(last_idx, 1); FETCH(amount_cents, 1); FETCH(balance_cents, 1);
+#undef FETCH
+    if (h_out->fixed_bytes && ctx->view_total > 0)
+        CUDA_TRY(ctx, cudaMemcpyAsync(h_out->fixed_bytes, d.fixed_bytes, (size_t)ctx->view_total, cudaMemcpyDeviceToHost, st));
+    CUDA_TRY(ctx, cudaStreamSynchronize(st));
+    return SMSGATE_OK;
+}
+
 extern "C" int smsgate_replay_host_timeline(smsgate_ctx* ctx, float* ms, int capacity) {
     if (!ctx || !ms) return SMSGATE_E_ARG;
     const int nc = ctx->host_chunks;
@@ -1712,7 +1814,7 @@ k_export_count(int64_t n, const uint8_t* __restrict__ msg_id, DedupScratch D, in
     const int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
     if (i < n) {
         const int32_t sl = D.slot_of[i];
-        if (sl >= 0 && D.owner[sl] == (int32_t)i) atomicAdd(&hist[key_owner(msg_id + i * 20, world)], 1);
+        if (sl >= 0 && D.tab[sl].x == (int32_t)i) atomicAdd(&hist[key_owner(msg_id + i * 20, world)], 1);
     }
     __syncthreads();
     if (threadIdx.x < world && hist[threadIdx.x]) atomicAdd(&counts[threadIdx.x], hist[threadIdx.x]);
@@ -1727,10 +1829,11 @@ k_export_scatter(int64_t n, int64_t base_index, const uint8_t* __restrict__ msg_
     __syncthreads();
     const int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
     int32_t sl = -1;
+    int2 fl = make_int2(0, 0);
     int dest = 0, local = 0;
     if (i < n) {
         sl = D.slot_of[i];
-        if (sl >= 0 && D.owner[sl] != (int32_t)i) sl = -1;
+        if (sl >= 0 && (fl = D.tab[sl]).x != (int32_t)i) sl = -1;   // one record per key: its first message sends it
         if (sl >= 0) {
             dest = key_owner(msg_id + i * 20, world);
             local = atomicAdd(&hist[dest], 1);
@@ -1742,7 +1845,7 @@ k_export_scatter(int64_t n, int64_t base_index, const uint8_t* __restrict__ msg_
     if (sl < 0) return;
     const int r = base[dest] + local;
     const uint32_t* kw = reinterpret_cast<const uint32_t*>(msg_id + i * 20);
-    const uint64_t f = (uint64_t)(base_index + D.first[sl]), l = (uint64_t)(base_index + D.last[sl]);
+    const uint64_t f = (uint64_t)(base_index + fl.x), l = (uint64_t)(base_index + fl.y);
     KeyRecord rec;
     rec.key[0] = kw[0]; rec.key[1] = kw[1]; rec.key[2] = kw[2]; rec.key[3] = kw[3]; rec.key[4] = kw[4];
     rec.first_lo = (uint32_t)f; rec.last_lo = (uint32_t)l;
@@ -1829,7 +1932,7 @@ extern "C" int smsgate_dedup_export(smsgate_ctx* ctx, int64_t n, int64_t base_in
     cudaStream_t st = ctx->stream;
     uint64_t cap = pow2_at_least((uint64_t)(n > 8 ? n : 8) * 2);
     if (cap > ctx->dd_cap) cap = ctx->dd_cap;
-    DedupScratch D{ctx->d_owner, ctx->d_first, ctx->d_last, ctx->d_slot_of, cap - 1};
+    DedupScratch D{ctx->d_dtab, ctx->d_slot_of, cap - 1};
     const unsigned grid = (unsigned)((n + 255) / 256);
     CUDA_TRY(ctx, cudaMemsetAsync(ctx->d_counts, 0, sizeof(int) * SMSGATE_MAX_WORLD, st));
     k_export_count<<<grid, 256, 0, st>>>(n, out->msg_id, D, world, ctx->d_counts);
@@ -2013,14 +2116,15 @@ k_p2p_scatter(int64_t n, int64_t base_index, int parity, const uint8_t* __restri
     __syncthreads();
     const int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
     int32_t sl = -1;
+    int2 fl = make_int2(0, 0);
     int dest = 0, local = 0;
     uint64_t f = 0, l = 0;
     if (i < n) {
         sl = D.slot_of[i];
-        if (sl >= 0 && D.owner[sl] != (int32_t)i) sl = -1;
+        if (sl >= 0 && (fl = D.tab[sl]).x != (int32_t)i) sl = -1;   // one record per key: its first message sends it
         if (sl >= 0) {
-            f = (uint64_t)(base_index + D.first[sl]);
-            l = (uint64_t)(base_index + D.last[sl]);
+            f = (uint64_t)(base_index + fl.x);
+            l = (uint64_t)(base_index + fl.y);
             // what this rank knows already; the owner only writes back when another rank changes it
             P.gfl[P.rank][sl] = make_longlong2((long long)f, (long long)l);
             if (collide) {
@@ -2184,7 +2288,13 @@ extern "C" int smsgate_p2p_scatter(smsgate_ctx* ctx, int64_t n, int64_t base_ind
     cudaStream_t st = ctx->stream;
     uint64_t cap = pow2_at_least((uint64_t)(n > 8 ? n : 8) * 2);
     if (cap > ctx->dd_cap) cap = ctx->dd_cap;
-    DedupScratch D{ctx->d_owner, ctx->d_first, ctx->d_last, ctx->d_slot_of, cap - 1};
+    if (n > 0 && (p->gfl_slots <= 0 || cap > (uint64_t)p->gfl_slots))
+        return fail(ctx, SMSGATE_E_LIMIT, "p2p_scatter: the batch needs " + std::to_string((unsigned long long)cap) +
+                                              " verdict slots, the descriptor's gfl arrays hold " +
+                                              std::to_string((long long)p->gfl_slots));
+    if (n > 0 && n > p->capacity / p->world)
+        return fail(ctx, SMSGATE_E_LIMIT, "p2p_scatter: the batch exceeds capacity / world messages per rank");
+    DedupScratch D{ctx->d_dtab, ctx->d_slot_of, cap - 1};
     if (n > 0) {
         k_p2p_scatter<<<(unsigned)((n + 255) / 256), 256, 0, st>>>(n, base_index, parity & 1, out->msg_id, D, V,
                                                                    V.bitmap_words ? V.collide[V.rank] : nullptr,
@@ -2290,11 +2400,11 @@ extern "C" int smsgate_p2p_resolve(smsgate_ctx* ctx, int64_t n, int64_t base_ind
 // them the hash table that k_dedup_insert / k_dedup_resolve need lives in the
 // file-scope array below instead of in a context's cudaMalloc'ed scratch.
 // The price: every GPU that loads this library carries the array
-// (SG_STATIC_BYTES, about 28 MiB) until the process exits, and a batch is
+// (SG_STATIC_BYTES, 20 MiB) until the process exits, and a batch is
 // limited to SMSGATE_DEDUP_STATIC_MAX messages.
 constexpr int64_t SG_STATIC_MAX_N = SMSGATE_DEDUP_STATIC_MAX;              // 1 Mi messages
 constexpr uint64_t SG_STATIC_CAP = 2ull * SMSGATE_DEDUP_STATIC_MAX;        // table slots (power of two)
-constexpr uint64_t SG_STATIC_WORDS = 3 * SG_STATIC_CAP + SG_STATIC_MAX_N;  // owner | first | last | slot_of
+constexpr uint64_t SG_STATIC_WORDS = 2 * SG_STATIC_CAP + SG_STATIC_MAX_N;  // slots {first, last} | slot_of
 constexpr uint64_t SG_STATIC_BYTES = SG_STATIC_WORDS * 4;
 static_assert((SG_STATIC_CAP & (SG_STATIC_CAP - 1)) == 0, "table capacity must be a power of two");
 static_assert(SG_STATIC_BYTES <= (32ull << 20), "the built-in table is meant to stay modest (<= 32 MiB per GPU)");
@@ -2345,15 +2455,11 @@ extern "C" int smsgate_dedup_static(int device, void* cuda_stream, int64_t n, in
     cudaStream_t st = (cudaStream_t)cuda_stream;
     const uint64_t cap = pow2_at_least((uint64_t)(n > 8 ? n : 8) * 2);       // <= SG_STATIC_CAP
     DedupScratch D;
-    D.owner = base;
-    D.first = base + SG_STATIC_CAP;
-    D.last = base + 2 * SG_STATIC_CAP;
-    D.slot_of = base + 3 * SG_STATIC_CAP;
+    D.tab = reinterpret_cast<int2*>(base);
+    D.slot_of = base + 2 * SG_STATIC_CAP;
     D.mask = cap - 1;
-    // the array still holds the previous call's table: reset the part this call uses
-    if ((e = cudaMemsetAsync(D.owner, 0xFF, cap * 4, st)) != cudaSuccess ||
-        (e = cudaMemsetAsync(D.first, 0x7F, cap * 4, st)) != cudaSuccess ||
-        (e = cudaMemsetAsync(D.last, 0xFF, cap * 4, st)) != cudaSuccess)
+    // the array still holds the previous call's table: reset the part this call uses (all bits set = empty)
+    if ((e = cudaMemsetAsync(D.tab, 0xFF, cap * sizeof(int2), st)) != cudaSuccess)
         return static_fail(errbuf, errbuf_len, SMSGATE_E_CUDA, "cudaMemsetAsync", cudaGetErrorString(e));
     const unsigned grid = (unsigned)((n + 255) / 256);
     k_dedup_insert<<<grid, 256, 0, st>>>(0, n, d_msg_id, d_status, D);
