@@ -68,6 +68,7 @@ class GlobalDedup:
         self.torch = torch
         dev = torch.device("cuda", engine.device)
         self.plan = ExchangePlan(dist, device=dev, group=group)
+        self.n_max = max(int(n_max), 1)
         self.records = torch.empty((max(n_max, 1), L.RECORD_BYTES), dtype=torch.uint8, device=dev)
         self.rec_slot = torch.empty(max(n_max, 1), dtype=torch.int32, device=dev)
         self.h_counts = np.zeros(self.plan.world, dtype=np.int64)
@@ -90,6 +91,8 @@ class GlobalDedup:
     def run_outputs(self, out: "L.Outputs", n: int, base_index: int) -> None:
         """Same, on a raw `smsgate_outputs` of device pointers (e.g. smsgate_device_view)."""
         eng, lib, torch = self.engine, L.lib(), self.torch
+        if n > self.n_max:
+            raise ValueError(f"shard of {n} messages exceeds the n_max={self.n_max} this exchange was sized for")
         l0 = eng.launch_count
         L.check(eng._ctx, lib.smsgate_dedup_export(eng._ctx, n, int(base_index), self.plan.world, C.byref(out),
                                                    self.records.data_ptr(), self.rec_slot.data_ptr(),
@@ -109,7 +112,13 @@ class GlobalDedup:
         self.launches += 0          # the context counts its own launches
         self.bytes_sent += n_rec * L.RECORD_BYTES + n_recv * 16
         self.last_counts = (send_counts, recv_counts)
+        self._last_received = n_recv
         self.last_launches = eng.launch_count - l0
+
+
+    def last_received(self) -> int:
+        """Records this rank received as owner during the last run."""
+        return int(getattr(self, "_last_received", 0))
 
 
 class GlobalDedupP2P:
@@ -154,6 +163,8 @@ class GlobalDedupP2P:
         self.desc = L.P2P()
         self.desc.world, self.desc.rank, self.desc.capacity = self.world, self.rank, self.capacity
         self.desc.bitmap_words = self.bitmap_words
+        self.desc.gfl_slots = cap_slots
+        self.n_max = n_max
         for w in range(self.world):
             self.desc.inbox[w] = self._h[0].buffer_ptrs[w]
             self.desc.in_count[w] = self._h[1].buffer_ptrs[w]
@@ -174,6 +185,8 @@ class GlobalDedupP2P:
 
     def run_outputs(self, out: "L.Outputs", n: int, base_index: int) -> None:
         eng, lib = self.engine, L.lib()
+        if n > self.n_max:
+            raise ValueError(f"shard of {n} messages exceeds the n_max={self.n_max} this exchange was sized for")
         parity = self.step & 1
         if self.bitmap_words:
             L.check(eng._ctx, lib.smsgate_p2p_filter_push(eng._ctx, n, C.byref(out), C.byref(self.desc)))
@@ -186,6 +199,13 @@ class GlobalDedupP2P:
         self._h[1].barrier(channel=1)          # all verdicts have landed in their home arrays
         L.check(eng._ctx, lib.smsgate_p2p_resolve(eng._ctx, n, int(base_index), C.byref(out), C.byref(self.desc), None))
         self.step += 1
+
+    def last_received(self) -> int:
+        """Records that arrived in this rank's inbox during the last run (synchronises)."""
+        if self.step == 0:
+            return 0
+        self.torch.cuda.synchronize()
+        return int(self._count[(self.step - 1) & 1].item())
 
     def overflowed(self) -> bool:
         """True if an inbox ever overflowed (some rank exceeded n_max).  Synchronises."""
@@ -205,3 +225,96 @@ def make_global_dedup(engine, dist, n_max: int, prefer_p2p: bool = True):
             import warnings
             warnings.warn(f"peer-memory exchange unavailable ({e!r}); using the NCCL all-to-all path")
     return GlobalDedup(engine, dist, n_max)
+
+
+class OverlappedReplay:
+    """Device-resident replay of a STREAM of batches on one rank with the global dedup exchange of batch k
+    running under the keys kernel of batch k+1.
+
+    The exchange is a chain of small latency-bound kernels and cross-GPU barriers that depends on the whole
+    batch's keys, so inside one batch nothing can hide it; across batches everything can.  Two contexts
+    ("lanes") alternate: each owns its dedup scratch, its output columns and its peer-memory buffers and
+    shares the one response cache (smsgate_cache_share).  Lane work is queued on `main` (high priority:
+    smsgate_scan_keys, smsgate_join_route_dedup), its exchange on `side` (low priority) behind an event; a
+    lane is reused only after its previous exchange has finished.  `reserve_sms` SMs are kept free of the keys
+    kernel (smsgate_set_scan_ctas) so that the side stream's kernels find room while it runs.
+
+    The reference has no counterpart: its upsert is one synchronous HTTP/SQL round trip per message
+    (libs/pocketbase.py:168-200, services/pb_writer/upsert.py:19-31)."""
+
+    def __init__(self, engine, dist, n_max: int, prefer_p2p: bool = True, reserve_sms: int = 8, lanes: int = 2):
+        import torch
+
+        from .replay import ReplayEngine
+        self.torch = torch
+        dev = engine.device
+        lo, hi = torch.cuda.Stream.priority_range()          # (lowest priority, highest priority)
+        self.main = torch.cuda.Stream(device=dev, priority=hi)
+        self.side = torch.cuda.Stream(device=dev, priority=lo)
+        self.engines = [engine]
+        for _ in range(lanes - 1):
+            e = ReplayEngine(dev)
+            e.share_cache_of(engine)
+            self.engines.append(e)
+        sm = torch.cuda.get_device_properties(dev).multi_processor_count
+        self.exchanges = []
+        for e in self.engines:
+            e.set_scan_ctas(max(1, sm - reserve_sms) if reserve_sms > 0 else 0)
+            self.exchanges.append(make_global_dedup(e, dist, n_max, prefer_p2p=prefer_p2p) if dist is not None else None)
+        torch.cuda.synchronize(dev)
+        for e in self.engines:
+            e.set_stream(self.main)
+        self.joined = [torch.cuda.Event() for _ in self.engines]
+        self.done = [torch.cuda.Event() for _ in self.engines]
+        self.k = 0
+
+    def refresh_cache(self) -> None:
+        """After the first engine reloaded its cache: the other lanes follow."""
+        for e in self.engines[1:]:
+            e.share_cache_of(self.engines[0])
+
+    def reserve(self, n: int, total: int) -> None:
+        for e in self.engines:
+            e.reserve(n, total)
+
+    def submit(self, d_bytes, d_offs, cols, n: int, now, base_index: int, scan_events=None) -> int:
+        """Queue one batch on the next lane (`cols` must be a column set used by that lane only).
+        Returns the lane."""
+        torch = self.torch
+        lane = self.k % len(self.engines)
+        eng, ex = self.engines[lane], self.exchanges[lane]
+        with torch.cuda.stream(self.main):
+            self.main.wait_event(self.done[lane])            # the lane's previous exchange read these columns
+            if scan_events is not None:
+                scan_events[0].record(self.main)
+            eng.scan_keys(d_bytes, d_offs, cols)
+            if scan_events is not None:
+                scan_events[1].record(self.main)
+            eng.join_route_dedup(n, now, base_index, cols)
+            self.joined[lane].record(self.main)
+        if ex is not None:
+            with torch.cuda.stream(self.side):
+                self.side.wait_event(self.joined[lane])
+                eng.set_stream(self.side)
+                try:
+                    ex.run(cols, base_index)
+                finally:
+                    eng.set_stream(self.main)
+                self.done[lane].record(self.side)
+        else:
+            self.done[lane].record(self.main)
+        self.k += 1
+        return lane
+
+    def drain(self) -> None:
+        self.main.synchronize()
+        self.side.synchronize()
+
+    @property
+    def launch_count(self) -> int:
+        return sum(e.launch_count for e in self.engines)
+
+    def close(self) -> None:
+        self.drain()
+        for e in self.engines[1:]:
+            e.close()

@@ -44,25 +44,47 @@ class _RecordColumns:
     (smsgate_replay_host_records): record fields are strided views, the three
     dedup columns are decoded from the verdict integers on first use."""
 
-    def __init__(self, records: np.ndarray, verdict: np.ndarray):
+    def __init__(self, records: np.ndarray, verdict: np.ndarray, engine=None, generation: int = 0, total: int = 0):
         self.records = records
         self.verdict = verdict
         self._decoded: dict = {}
+        self._engine = engine            # for the columns the record does not carry (fetched on first use)
+        self._generation = generation
+        self._total = total
+        self._fetched: dict = {}
 
     _VERDICT = ("survivor", "first_seen", "last_idx")
+    _ON_DEVICE = ("card", "cache_key", "fixed_len", "fixed_bytes", "amount_cents", "balance_cents")
 
     def keys(self):
-        return tuple(self.records.dtype.names) + self._VERDICT
+        return tuple(self.records.dtype.names) + self._VERDICT + self._ON_DEVICE
 
     def __iter__(self):
         return iter(self.keys())
 
     def __contains__(self, name) -> bool:
-        return name in self.records.dtype.names or name in self._VERDICT
+        return name in self.records.dtype.names or name in self._VERDICT or name in self._ON_DEVICE
+
+    def _fetch(self, name):
+        """A column the 64-byte record leaves out: still on the device until the engine's next replay."""
+        if name not in self._fetched:
+            eng = self._engine
+            if eng is None or eng._generation != self._generation:
+                raise RuntimeError(f"column {name!r} of this result was left on the device and a later replay has "
+                                   "replaced it; read it (or call ReplayResult.detach()) before replaying again, "
+                                   "or use ReplayEngine.replay(columns=...)")
+            if len(self.records) == 0:
+                self._fetched.update(eng._host_columns(0, 0, self._ON_DEVICE, pinned=False))
+            else:
+                self._fetched.update(eng._fetch_columns(len(self.records), self._total,
+                                                        [c for c in self._ON_DEVICE if c not in self._fetched]))
+        return self._fetched[name]
 
     def __getitem__(self, name):
         if name in self.records.dtype.names:
             return self.records[name]
+        if name in self._ON_DEVICE:
+            return self._fetch(name)
         if name not in self._VERDICT:
             raise KeyError(name)
         if name not in self._decoded:
@@ -76,6 +98,15 @@ class _RecordColumns:
     @property
     def nbytes(self) -> int:
         return int(self.records.nbytes + self.verdict.nbytes)
+
+    def detach(self) -> None:
+        """Own copies of everything: the records and verdicts alias the engine's pinned staging buffer and
+        the remaining columns live on the device, both only until the engine's next replay."""
+        for name in self._ON_DEVICE:
+            self._fetch(name)
+        self.records = self.records.copy()
+        self.verdict = self.verdict.copy()
+        self._decoded = {}
 
 
 class ReplayResult:
@@ -155,6 +186,13 @@ class ReplayResult:
             merchant=v.get("merchant"), city=v.get("city"), address="" if address == "null" else address,
             balance=self.decimal("balance", i), parser_version="llm-0.2.0")
 
+    def detach(self) -> "ReplayResult":
+        """Make the result independent of the engine (see _RecordColumns.detach); a no-op for `replay`
+        without pinned buffers."""
+        if hasattr(self.cols, "detach"):
+            self.cols.detach()
+        return self
+
     def status_counts(self) -> dict:
         c = np.bincount(self.cols["status"], minlength=8)
         return {L.STATUS_NAMES[k]: int(c[k]) for k in range(8)}
@@ -206,6 +244,8 @@ class ReplayEngine:
             raise L.SmsgateError(rc, (self._lib.smsgate_last_error(None) or b"").decode())
         self.table: Optional[CacheTable] = None
         self._pinned: dict = {}
+        self._generation = 0             # bumped by every host-buffer replay (stale-result detection)
+        self.host_fallbacks = 0          # XML files handed to ElementTree because of their dialect (xml_ingest)
 
     # -- lifecycle ---------------------------------------------------------
     def close(self):
@@ -275,12 +315,13 @@ class ReplayEngine:
             if pinned:
                 import torch
                 tdt = {"u1": torch.uint8, "i4": torch.int32, "i8": torch.int64}[dt]
-                key = (name, shape)
-                t = self._pinned.get(key)
-                if t is None:
-                    t = torch.empty(shape, dtype=tdt, pin_memory=True)
-                    self._pinned[key] = t
-                cols[name] = t.numpy()
+                # one grow-only page-locked buffer per column: valid until the next pinned replay
+                need = int(np.prod(shape))
+                t = self._pinned.get(name)
+                if t is None or t.numel() < need:
+                    t = torch.empty(max(need, 1), dtype=tdt, pin_memory=True)
+                    self._pinned[name] = t
+                cols[name] = t.numpy()[:need].reshape(shape)
             else:
                 cols[name] = np.zeros(shape, dtype=np.dtype(dt))
         return cols
@@ -291,20 +332,26 @@ class ReplayEngine:
                        exchange=None) -> ReplayResult:
         """`replay` with the results returned as one 64-byte record per message plus one verdict integer
         (smsgate_replay_host_records): one device->host transfer per chunk instead of one per column, which
-        is what the end-to-end time depends on.  The ReplayResult reads the same either way."""
+        is what the end-to-end time depends on.  The ReplayResult reads the same either way: the columns the
+        record leaves out (card, cache_key, fixed_len, fixed_bytes, *_cents) stay on the device and are
+        fetched on first use.  With `pinned` the arrays alias this engine's page-locked staging buffer: the
+        result is valid until the next replay on this engine; `result.detach()` makes it independent."""
         n = batch.n
         total = int(batch.body_offsets[-1]) if n else 0
         self.reserve(max(n, 1), max(total, 1))
         dtype = np.dtype(L.RECORD_FIELDS)
         assert dtype.itemsize == L.RECORD_BYTES_OUT
+        self._generation += 1
         if pinned:
+            # ONE grow-only page-locked staging buffer per engine: the returned arrays alias it and stay
+            # valid until the next replay_records(pinned=True) on this engine (ReplayResult.detach() copies)
             import torch
-            key = ("records", n)
-            t = self._pinned.get(key)
-            if t is None:
-                t = (torch.empty(max(n, 1) * L.RECORD_BYTES_OUT, dtype=torch.uint8, pin_memory=True),
-                     torch.empty(max(n, 1), dtype=torch.int64, pin_memory=True))
-                self._pinned[key] = t
+            t = self._pinned.get("records")
+            if t is None or t[1].numel() < max(n, 1):
+                cap = max(n, 1) if t is None else max(n, 2 * t[1].numel())
+                t = (torch.empty(cap * L.RECORD_BYTES_OUT, dtype=torch.uint8, pin_memory=True),
+                     torch.empty(cap, dtype=torch.int64, pin_memory=True))
+                self._pinned["records"] = t
             rec_buf, verdict_buf = t[0].numpy().view(dtype), t[1].numpy()
         else:
             rec_buf, verdict_buf = np.zeros(max(n, 1), dtype=dtype), np.zeros(max(n, 1), dtype=np.int64)
@@ -322,7 +369,26 @@ class ReplayEngine:
             L.check(self._ctx, self._lib.smsgate_device_view(self._ctx, n, C.byref(view)))
             exchange.run_outputs(view, n, int(base_index))
             L.check(self._ctx, self._lib.smsgate_replay_host_records_finish(self._ctx, vp))
-        return ReplayResult(batch, _RecordColumns(rec, verdict), self.table, base_index)
+        return ReplayResult(batch, _RecordColumns(rec, verdict, self, self._generation, total), self.table, base_index)
+
+    def _fetch_columns(self, n: int, total: int, names: Sequence[str]) -> dict:
+        """Columns of the last host-buffer batch that are still on the device (smsgate_fetch_columns)."""
+        cols = self._host_columns(n, total, tuple(names), pinned=False)
+        out = L.Outputs(**{k: (v.ctypes.data if v.size else None) for k, v in cols.items()})
+        L.check(self._ctx, self._lib.smsgate_fetch_columns(self._ctx, n, C.byref(out)))
+        return cols
+
+    def set_stream(self, stream) -> None:
+        """Queue this engine's work on another torch stream from now on (smsgate_set_stream)."""
+        L.check(self._ctx, self._lib.smsgate_set_stream(self._ctx, C.c_void_p(stream.cuda_stream)))
+
+    def set_scan_ctas(self, ctas: int) -> None:
+        L.check(self._ctx, self._lib.smsgate_set_scan_ctas(self._ctx, int(ctas)))
+
+    def share_cache_of(self, other: "ReplayEngine") -> None:
+        """Probe `other`'s loaded response cache instead of loading a second copy (smsgate_cache_share)."""
+        L.check(self._ctx, self._lib.smsgate_cache_share(self._ctx, other._ctx))
+        self.table = other.table
 
     def replay(self, batch: Batch, now: _dt.datetime, base_index: int = 0,
                columns: Optional[Sequence[str]] = None, pinned: bool = False, exchange=None) -> ReplayResult:
@@ -333,6 +399,7 @@ class ReplayEngine:
         n = batch.n
         total = int(batch.body_offsets[-1]) if n else 0
         self.reserve(max(n, 1), max(total, 1))
+        self._generation += 1
         want = tuple(columns) if columns is not None else self.ALL_COLUMNS
         cols = self._host_columns(n, total, want, pinned)
         out = L.Outputs(**{k: (v.ctypes.data if v.size else None) for k, v in cols.items()})

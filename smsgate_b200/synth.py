@@ -211,3 +211,78 @@ def write_xml(path: str, backup: Backup) -> None:
             f.write(f'  <sms protocol="0" address="{xml_escape_attr(sender)}" date="{ms}" type="1" '
                     f'body="{xml_escape_attr(body)}" read="1" />\n')
         f.write("</smses>\n")
+
+
+# --------------------------------------------------------------------------- multi-GPU workload shapes
+def _owner_of_sha1(body: str, world: int) -> int:
+    """Rank that owns the body's msg_id in the global dedup: range partition of the SHA-1's top 32 bits
+    (same formula as key_owner() in the kernels and dist.owner_of_prefix)."""
+    p = int.from_bytes(hashlib.sha1(body.encode("utf-8")).digest()[:4], "big")
+    return (p * world) >> 32
+
+
+def shard_with_cross_duplicates(n: int, rank: int, world: int, *, dup_frac: float = 0.10, seed: int = 0x5EED,
+                                pool_size: Optional[int] = None) -> Backup:
+    """Rank `rank`'s shard of BASELINE.json configs[2]: n messages, `dup_frac` of them copies of bodies that
+    live in a pool COMMON to all ranks (same seed everywhere), placed at random positions - so about
+    dup_frac of the whole job are duplicates spread across shards.  The rest is the rank's own stream."""
+    n_dup = int(round(n * dup_frac))
+    own = generate(n - n_dup, seed=seed + 7919 * rank)
+    pool = generate(pool_size or max(n_dup, 1000), seed=seed + 104729)
+    rng = np.random.Generator(np.random.PCG64(seed + 31 * rank + 1))
+    pick = rng.integers(0, len(pool.bodies), n_dup)
+    pos = rng.permutation(n)
+    bodies = [None] * n
+    kinds = [None] * n
+    for j, p in enumerate(pos[:n - n_dup]):
+        bodies[p] = own.bodies[j]
+        kinds[p] = own.kinds[j]
+    for j, p in enumerate(pos[n - n_dup:]):
+        bodies[p] = pool.bodies[pick[j]]
+        kinds[p] = pool.kinds[pick[j]]
+    cache = dict(own.cache)
+    cache.update(pool.cache)
+    senders = ["BANK" if (i % 5) else "AMERIABANK" for i in range(n)]
+    date_ms = [1_707_900_000_000 + 1000 * (rank * n + i) for i in range(n)]
+    return Backup(bodies=bodies, senders=senders, date_ms=date_ms, cache=cache, kinds=kinds)
+
+
+def shard_skewed(n: int, rank: int, world: int, *, dup_frac: float = 0.5, zipf: float = 1.2,
+                 hot_owner_frac: float = 0.5, seed: int = 0x5EED) -> Backup:
+    """Rank `rank`'s shard of BASELINE.json configs[3]: `dup_frac` of the messages are
+    duplicates drawn Zipf(`zipf`) from a distinct set COMMON to all ranks (hot keys repeat on every rank),
+    and `hot_owner_frac` of the rank's own distinct bodies are re-drawn until their msg_id prefix belongs to
+    owner rank 0, so rank 0's inbox receives several times what the others do."""
+    n_dup = int(round(n * dup_frac))
+    n_own = n - n_dup
+    own = generate(n_own, seed=seed + 7919 * rank + 3)
+    common = generate(max(n_dup // 4, 1000), seed=seed + 15485863)
+    rng = np.random.Generator(np.random.PCG64(seed + 57 * rank + 2))
+    cache = dict(common.cache)
+    bodies_own = list(own.bodies)
+    n_hot = int(round(n_own * hot_owner_frac)) if world > 1 else 0
+    for j in range(n_hot):
+        body = bodies_own[j]
+        resp = own.cache.get(reference_cache_key(body))
+        k = 0
+        cand = body
+        while _owner_of_sha1(cand, world) != 0:
+            k += 1
+            cand = f"{body} ref{k}"
+        bodies_own[j] = cand
+        if resp is not None:
+            cache[reference_cache_key(cand)] = resp
+    for j in range(n_hot, n_own):
+        key = reference_cache_key(bodies_own[j])
+        if key in own.cache:
+            cache[key] = own.cache[key]
+    src = np.minimum(rng.zipf(zipf, n_dup) - 1, len(common.bodies) - 1)
+    pos = rng.permutation(n)
+    bodies = [None] * n
+    for j, p in enumerate(pos[:n_own]):
+        bodies[p] = bodies_own[j]
+    for j, p in enumerate(pos[n_own:]):
+        bodies[p] = common.bodies[src[j]]
+    senders = ["BANK" if (i % 5) else "AMERIABANK" for i in range(n)]
+    date_ms = [1_707_900_000_000 + 1000 * (rank * n + i) for i in range(n)]
+    return Backup(bodies=bodies, senders=senders, date_ms=date_ms, cache=cache, kinds=[])
