@@ -146,3 +146,131 @@ def test_ranks_over_nccl_or_peer_memory(p2p, world, prefilter):
     assert np.array_equal(np.concatenate([r[1] for r in res]) != 0, np.array(ora.survivor))
     assert np.array_equal(np.concatenate([r[2] for r in res]) != 0, np.array(ora.first_seen))
     assert np.array_equal(np.concatenate([r[3] for r in res]), np.array(ora.last_idx, np.int64))
+
+
+class _EmulatedPeers:
+    """`world` ranks of the peer-memory exchange on ONE GPU: every rank is its own context on cuda:0,
+    the "peer" pointers of the smsgate_p2p descriptor are plain device tensors of the other contexts,
+    and since all contexts share one stream a cross-GPU barrier is simply the order of the calls.
+    Drives k_bits_build/_push/_reduce and k_p2p_scatter/_clear/_insert/_verdict/_resolve exactly as
+    dist.GlobalDedupP2P.run_outputs does."""
+
+    def __init__(self, engines, n_max, prefilter):
+        import torch
+        self.engines, self.world = engines, len(engines)
+        world = self.world
+        self.capacity = world * n_max
+        cap_slots = 16
+        while cap_slots < 2 * max(n_max, 8):
+            cap_slots <<= 1
+        dev = "cuda"
+        self.inbox = [torch.zeros(self.capacity * L.P2P_RECORD_BYTES, dtype=torch.uint8, device=dev) for _ in range(world)]
+        self.count = [torch.zeros(16, dtype=torch.int32, device=dev) for _ in range(world)]
+        self.gfl = [torch.zeros(2 * cap_slots, dtype=torch.int64, device=dev) for _ in range(world)]
+        self.words = 0
+        if prefilter:
+            words = 64
+            while words * 32 < 16 * n_max * world:
+                words <<= 1
+            self.words = words
+            self.stage = [torch.zeros(world * (words // world + 12), dtype=torch.int32, device=dev) for _ in range(world)]
+            self.collide = [torch.zeros(words, dtype=torch.int32, device=dev) for _ in range(world)]
+        self.desc = []
+        lib = L.lib()
+        for r, eng in enumerate(engines):
+            d = L.P2P()
+            d.world, d.rank, d.capacity, d.bitmap_words, d.gfl_slots = world, r, self.capacity, self.words, cap_slots
+            for w in range(world):
+                d.inbox[w] = self.inbox[w].data_ptr()
+                d.in_count[w] = self.count[w].data_ptr()
+                d.gfl[w] = self.gfl[w].data_ptr()
+                if self.words:
+                    d.stage[w] = self.stage[w].data_ptr()
+                    d.collide[w] = self.collide[w].data_ptr()
+            L.check(eng._ctx, lib.smsgate_p2p_reserve(eng._ctx, self.capacity))
+            if self.words:
+                L.check(eng._ctx, lib.smsgate_p2p_reserve_filter(eng._ctx, self.words))
+            self.desc.append(d)
+        self.step = 0
+
+    def run(self, outs, ns, bases):
+        lib, parity = L.lib(), self.step & 1
+        E, D = self.engines, self.desc
+        rng = range(self.world)
+        if self.words:
+            for r in rng:
+                L.check(E[r]._ctx, lib.smsgate_p2p_filter_push(E[r]._ctx, ns[r], C.byref(outs[r]), C.byref(D[r])))
+            for r in rng:
+                L.check(E[r]._ctx, lib.smsgate_p2p_filter_reduce(E[r]._ctx, C.byref(D[r])))
+        for r in rng:
+            L.check(E[r]._ctx, lib.smsgate_p2p_scatter(E[r]._ctx, ns[r], bases[r], parity, C.byref(outs[r]), C.byref(D[r])))
+        for r in rng:
+            L.check(E[r]._ctx, lib.smsgate_p2p_merge(E[r]._ctx, parity, C.byref(D[r])))
+        for r in rng:
+            L.check(E[r]._ctx, lib.smsgate_p2p_resolve(E[r]._ctx, ns[r], bases[r], C.byref(outs[r]), C.byref(D[r]), None))
+        self.step += 1
+
+    def overflowed(self):
+        flag = C.c_int(0)
+        out = L.Outputs()
+        any_over = False
+        for r, eng in enumerate(self.engines):
+            L.check(eng._ctx, L.lib().smsgate_p2p_resolve(eng._ctx, 0, 0, C.byref(out), C.byref(self.desc[r]), C.byref(flag)))
+            any_over |= bool(flag.value)
+        return any_over
+
+
+@pytest.mark.parametrize("world,prefilter,ragged", [(2, True, False), (3, True, True), (8, True, False),
+                                                    (2, False, False), (5, False, True)])
+def test_peer_memory_exchange_emulated_on_one_gpu(world, prefilter, ragged):
+    """The default multi-GPU data plane (bitmap prefilter + peer stores) against the oracle's global
+    upsert, several batches in a row (the arrival counters alternate, inboxes and bitmaps are reused),
+    with shards of unequal size when `ragged` (one of them empty)."""
+    import torch
+
+    from smsgate_b200.replay import ReplayEngine
+    n_per = 3000
+    sizes = [n_per] * world
+    if ragged:
+        sizes = [max(0, n_per - 700 * r) for r in range(world)]
+        sizes[-1] = 0
+    engines = [ReplayEngine(0) for _ in range(world)]
+    try:
+        peers = _EmulatedPeers(engines, n_per, prefilter)
+        base0 = (1 << 33) + 5
+        for batch_no, seed in enumerate((700 + world, 900 + world, 1100 + world)):
+            backup = synth.generate(sum(sizes), seed=seed, dup_frac=(0.5, 0.1, 0.0)[batch_no],
+                                    hot_key_zipf=(1.2, None, None)[batch_no], miss_frac=0.05)
+            ora = _global_oracle(backup)
+            cols, outs, bases = [], [], []
+            lo = 0
+            for r, eng in enumerate(engines):
+                hi = lo + sizes[r]
+                eng.load_cache(backup.cache)
+                b = Batch.from_strings(backup.bodies[lo:hi], backup.senders[lo:hi], backup.date_ms[lo:hi])
+                d_bytes = torch.zeros(b.body_bytes.size + 64, dtype=torch.uint8, device="cuda")
+                d_bytes[:b.body_bytes.size] = torch.from_numpy(b.body_bytes.copy()).cuda()
+                d_off = torch.from_numpy(b.body_offsets.copy()).cuda()
+                c = eng.device_columns(max(b.n, 1), d_bytes.numel())
+                eng.reserve(n_per, d_bytes.numel())
+                eng.replay_device(d_bytes, d_off, NOW, c, base_index=base0 + lo)
+                cols.append(c); outs.append(eng._dev_outputs(c)); bases.append(base0 + lo)
+                lo = hi
+            peers.run(outs, sizes, bases)
+            torch.cuda.synchronize()
+            got_s = np.concatenate([cols[r]["survivor"][:sizes[r]].cpu().numpy() for r in range(world)])
+            got_f = np.concatenate([cols[r]["first_seen"][:sizes[r]].cpu().numpy() for r in range(world)])
+            got_l = np.concatenate([cols[r]["last_idx"][:sizes[r]].cpu().numpy() for r in range(world)])
+            assert np.array_equal(got_s != 0, np.array(ora.survivor)), batch_no
+            assert np.array_equal(got_f != 0, np.array(ora.first_seen)), batch_no
+            want_l = np.array([(-1 if x < 0 else base0 + x) for x in ora.last_idx], np.int64)
+            assert np.array_equal(got_l, want_l), batch_no
+        assert not peers.overflowed()
+        # a shard beyond what the verdict arrays were sized for is refused, not written out of bounds
+        small = L.P2P.from_buffer_copy(peers.desc[0])
+        small.gfl_slots = 16
+        rc = L.lib().smsgate_p2p_scatter(engines[0]._ctx, sizes[0], 0, 0, C.byref(outs[0]), C.byref(small))
+        assert rc == L.E_LIMIT
+    finally:
+        for eng in engines:
+            eng.close()

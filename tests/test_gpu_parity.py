@@ -281,6 +281,35 @@ def test_packed_records_match_columns(engine):
     assert empty.n == 0 and len(empty.cols["status"]) == 0
 
 
+def test_record_result_materialises_like_column_result(engine):
+    """A result that came back as packed records hands out the same ParsedSMS objects, payloads and
+    exceptions as the column result: the columns the record leaves out are fetched from the device on
+    first use, a stale result says so instead of reading another batch's data, detach() keeps it."""
+    from smsgate_b200.replay import CacheMiss
+    backup = synth.generate(6_000, seed=77, dup_frac=0.3, mixed_locale=True, miss_frac=0.2)
+    engine.load_cache(backup.cache)
+    batch = Batch.from_strings(backup.bodies, backup.senders, backup.date_ms)
+    a = engine.replay(batch, NOW)
+    ua, pa, ra = a.upserts(), a.parsed_payloads(), a.pocketbase_records()
+    b = engine.replay_records(batch, NOW)
+    assert b.upserts() == ua and b.parsed_payloads() == pa and b.pocketbase_records() == ra
+    assert any("CARD:" in p.raw_body for p in ua.values())            # masked cards are in the batch
+    miss = int(np.nonzero(a.status == L.ST_CACHE_MISS)[0][0])
+    with pytest.raises(CacheMiss) as e1:
+        a.parsed(miss)
+    with pytest.raises(CacheMiss) as e2:
+        b.parsed(miss)
+    assert str(e1.value) == str(e2.value)
+    # same-size batch again: the earlier result's pinned arrays are reused and its device columns are gone
+    c = engine.replay_records(batch, NOW).detach()
+    d = engine.replay_records(Batch.from_strings(backup.bodies[::-1], backup.senders, backup.date_ms), NOW)
+    d2 = engine.replay_records(batch, NOW)
+    with pytest.raises(RuntimeError, match="later replay"):
+        d.cols["card"]
+    assert c.upserts() == ua                                           # the detached one is unaffected
+    assert d2.upserts() == ua
+
+
 def test_device_keys_and_cross_source(engine, golden):
     """MD5 device keys against the reference's vectors and the oracle, and the report of bodies that the
     reference stores twice (same body seen from the XML backup and from a device)."""

@@ -46,6 +46,18 @@ def _dedup_both_ways(eng, backup, base_index):
     torch.cuda.synchronize()
     for k in want:
         assert np.array_equal(got[k].cpu().numpy(), want[k]), k       # integer verdicts: bit-exact
+    # and directly against the CPU oracle's upsert-by-msg_id over hashlib's SHA-1 of the same bodies,
+    # so that the two entry points cannot be wrong together
+    import hashlib
+
+    from oracle import replay_oracle as O
+    ids = [hashlib.sha1(b.encode("utf-8")).digest() for b in backup.bodies]
+    status = cols["status"].cpu().numpy()
+    surv, first, last, _ = O.dedup(ids, (int(s) == O.ST_UPSERT for s in status))
+    assert np.array_equal(got["survivor"].cpu().numpy() != 0, np.array(surv))
+    assert np.array_equal(got["first_seen"].cpu().numpy() != 0, np.array(first))
+    assert np.array_equal(got["last_idx"].cpu().numpy(),
+                          np.array([(-1 if x < 0 else base_index + x) for x in last], np.int64))
     return int(want["survivor"].sum())
 
 
