@@ -41,7 +41,7 @@ RESULT_COLUMNS = ("msg_id", "status", "slot", "amount_coef", "balance_coef", "am
 
 
 def workload_name(n):
-    return f"configs[1]: {n} synthetic bank-notification SMS per GPU, 100% cache hit for non-OTP bodies"
+    return WORKLOADS["hit100"].format(n=n)
 
 
 # --------------------------------------------------------------------------- clocks
@@ -194,11 +194,170 @@ def run_reference(args, rank, world):
 
 
 # --------------------------------------------------------------------------- our arm
-def run_ours(args, rank, world, local_rank):
+WORKLOADS = {
+    "hit100": "configs[1]: {n} synthetic bank-notification SMS per GPU, 100% cache hit for non-OTP bodies",
+    "dup10": "configs[2] per-GPU shape: {n} messages per GPU, 10% of the job duplicates spread across shards "
+             "(common pool), every rank its own stream otherwise",
+    "skew": "configs[3]: {n} messages per GPU, 50% duplicates Zipf(1.2) from a set common to all ranks, 50% of each "
+            "rank's distinct bodies re-drawn until msg_id prefix owner = rank 0",
+    "mixed": "configs[4]: {n} mixed-locale bodies (40% Cyrillic with NBSP / U+202F thousands and comma decimals, "
+             "10% card forms, 10% multi-part 400-1200 B), 30% cache misses routed to the DLQ set",
+}
+
+
+def make_backup(workload: str, n: int, rank: int, world: int):
+    from smsgate_b200 import synth
+    if workload == "hit100":
+        return synth.generate(n, seed=0x5EED + 2 + 7919 * rank)
+    if workload == "dup10":
+        return synth.shard_with_cross_duplicates(n, rank, world, dup_frac=0.10, seed=0x5EED + 3)
+    if workload == "skew":
+        return synth.shard_skewed(n, rank, world, seed=0x5EED + 4)
+    if workload == "mixed":
+        return synth.generate(n, seed=0x5EED + 5 + 7919 * rank, mixed_locale=True, miss_frac=0.3)
+    raise ValueError(workload)
+
+
+class Resident:
+    """One workload resident on this rank's GPU: batch in HBM, cache loaded, output columns allocated."""
+
+    def __init__(self, eng, backup, rank, ov=None):
+        import torch
+
+        from smsgate_b200.batch import Batch
+        self.backup = backup
+        self.batch = Batch.from_strings(backup.bodies, backup.senders, backup.date_ms)
+        self.n = self.batch.n
+        self.total = int(self.batch.body_offsets[-1])
+        self.base_index = rank * self.n
+        eng.load_cache(backup.cache)
+        eng.reserve(self.n, self.total)
+        if ov is not None:                              # the other lane probes the same table
+            ov.refresh_cache()
+            ov.reserve(self.n, self.total)
+        self.h_bytes = torch.from_numpy(self.batch.body_bytes.copy()).pin_memory()
+        self.h_offs = torch.from_numpy(self.batch.body_offsets.copy()).pin_memory()
+        self.d_bytes = self.h_bytes.cuda()
+        self.d_offs = self.h_offs.cuda()
+        self.cols = eng.device_columns(self.n, self.total)
+
+
+def time_resident(eng, R, exchange, steps, warmup, flush, barrier):
+    """`steps` device-resident passes of the whole path over R, one batch at a time (nothing overlapped).
+    Returns (mean step ms, mean k_scan_keys ms)."""
+    import torch
+    ev = lambda: torch.cuda.Event(enable_timing=True)  # noqa: E731
+    k1_ms, step_ms = [], []
+    for it in range(warmup + steps):
+        if it == warmup:
+            barrier()
+        flush.zero_()                                   # evict the previous step's lines from L2 (not timed)
+        e0, e1, e2 = ev(), ev(), ev()
+        e0.record()
+        eng.scan_keys(R.d_bytes, R.d_offs, R.cols)
+        e1.record()
+        eng.join_route_dedup(R.n, NOW, R.base_index, R.cols)  # stages 2 + 3 as smsgate_replay_device runs them
+        if exchange is not None:
+            exchange.run(R.cols, R.base_index)
+        e2.record()
+        e2.synchronize()
+        if it >= warmup:
+            k1_ms.append(e0.elapsed_time(e1))
+            step_ms.append(e0.elapsed_time(e2))
+    barrier()
+    return sum(step_ms) / len(step_ms), sum(k1_ms) / len(k1_ms)
+
+
+def time_overlapped(ov, R, steps, warmup, barrier, copies=3):
+    """`steps` batches through dist.OverlappedReplay, timed as ONE bracket on the device: the exchange of
+    batch k runs on the side stream under the keys kernel of batch k+1.  Inputs rotate through `copies`
+    copies (each ~ the size of L2) and outputs through the lanes' column sets, so no step finds its lines
+    in L2 and no flush sits inside the bracket.  Returns (ms per step, mean k_scan_keys ms)."""
+    import torch
+    ins = [(R.d_bytes, R.d_offs)] + [(R.d_bytes.clone(), R.d_offs.clone()) for _ in range(copies - 1)]
+    colsets = [R.cols] + [ov.engines[l].device_columns(R.n, R.total) for l in range(1, len(ov.engines))]
+    ev = lambda: torch.cuda.Event(enable_timing=True)  # noqa: E731
+    pairs = []
+
+    def go(k, timed):
+        b, o = ins[k % copies]
+        pe = (ev(), ev()) if timed else None
+        ov.submit(b, o, colsets[ov.k % len(colsets)], R.n, NOW, R.base_index, scan_events=pe)
+        if timed:
+            pairs.append(pe)
+
+    for k in range(warmup):
+        go(k, False)
+    ov.drain()
+    barrier()
+    l0 = ov.launch_count
+    start, end = ev(), ev()
+    start.record(ov.main)
+    for k in range(steps):
+        go(warmup + k, True)
+    for d in ov.done:
+        ov.main.wait_event(d)
+    end.record(ov.main)
+    ov.drain()
+    barrier()
+    time_overlapped.launches = ov.launch_count - l0
+    k1 = sum(a.elapsed_time(b) for a, b in pairs) / len(pairs)
+    return start.elapsed_time(end) / steps, k1
+
+
+def exchange_parity(eng, dist, rank, world, ex, shape: dict, n_per: int = 20_000):
+    """The multi-GPU data plane against the oracle: one GLOBAL generator call sliced by rank, replayed and
+    exchanged; msg_id / status / verdict columns gathered to rank 0 and compared with
+    oracle.replay_oracle.dedup over hashlib's SHA-1 of the same bodies.  Returns (ok, records received by
+    every rank) on rank 0, (None, None) elsewhere; exits non-zero on a mismatch."""
+    import hashlib
+
     import numpy as np
     import torch
 
     from smsgate_b200 import synth
+    from smsgate_b200.batch import Batch
+    backup = synth.generate(world * n_per, seed=0x5EED + 77, **shape)
+    lo, hi = rank * n_per, (rank + 1) * n_per
+    b = Batch.from_strings(backup.bodies[lo:hi], backup.senders[lo:hi], backup.date_ms[lo:hi])
+    eng.load_cache(backup.cache)
+    total = int(b.body_offsets[-1])
+    eng.reserve(n_per, total)
+    d_bytes = torch.zeros(total + 64, dtype=torch.uint8, device="cuda")
+    d_bytes[:total] = torch.from_numpy(b.body_bytes.copy()).cuda()
+    d_offs = torch.from_numpy(b.body_offsets.copy()).cuda()
+    cols = eng.device_columns(n_per, total + 64)
+    for _ in range(2):                                   # twice: the arrival counters alternate
+        eng.replay_device(d_bytes, d_offs, NOW, cols, base_index=lo)
+        ex.run(cols, lo)
+    torch.cuda.synchronize()
+    received = torch.tensor([ex.last_received()], dtype=torch.int64, device="cuda")
+    gathered = {}
+    for name in ("msg_id", "status", "survivor", "first_seen", "last_idx"):
+        t = cols[name][:n_per].contiguous()
+        out = [torch.empty_like(t) for _ in range(world)] if rank == 0 else None
+        dist.gather(t, out, dst=0)
+        if rank == 0:
+            gathered[name] = torch.cat(out).cpu().numpy()
+    recv_all = [torch.empty_like(received) for _ in range(world)] if rank == 0 else None
+    dist.gather(received, recv_all, dst=0)
+    if rank != 0:
+        return None, None
+    from oracle import replay_oracle as O
+    ids = [hashlib.sha1(x.encode("utf-8")).digest() for x in backup.bodies]
+    if gathered["msg_id"].tobytes() != b"".join(ids):
+        raise SystemExit("exchange parity FAILED: msg_id differs from hashlib.sha1")
+    surv, first, last, _ = O.dedup(ids, (int(s) == O.ST_UPSERT for s in gathered["status"]))
+    if not (np.array_equal(gathered["survivor"] != 0, np.array(surv)) and
+            np.array_equal(gathered["first_seen"] != 0, np.array(first)) and
+            np.array_equal(gathered["last_idx"], np.array(last, np.int64))):
+        raise SystemExit("exchange parity FAILED: global dedup verdicts differ from oracle.replay_oracle.dedup")
+    return True, [int(x.item()) for x in recv_all]
+
+
+def run_ours(args, rank, world, local_rank):
+    import torch
+
     from smsgate_b200.batch import Batch
     from smsgate_b200.replay import ReplayEngine
 
@@ -212,25 +371,7 @@ def run_ours(args, rank, world, local_rank):
         dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
 
     n = args.msgs
-    backup = synth.generate(n, seed=0x5EED + 2 + 7919 * rank)
-    batch = Batch.from_strings(backup.bodies, backup.senders, backup.date_ms)
-    total = int(batch.body_offsets[-1])
     eng = ReplayEngine(local_rank)
-    eng.load_cache(backup.cache)
-    eng.reserve(n, total)
-    base_index = rank * n
-
-    exchange = None
-    if world > 1:
-        from smsgate_b200.dist import make_global_dedup
-        exchange = make_global_dedup(eng, dist, n, prefer_p2p=not args.nccl_exchange)
-
-    # ---- resident inputs / outputs
-    h_bytes = torch.from_numpy(batch.body_bytes.copy()).pin_memory()
-    h_offs = torch.from_numpy(batch.body_offsets.copy()).pin_memory()
-    d_bytes = h_bytes.cuda()
-    d_offs = h_offs.cuda()
-    cols = eng.device_columns(n, total)
     flush = torch.empty(512 << 20, dtype=torch.uint8, device="cuda")     # > 126 MB L2
 
     def barrier():
@@ -239,38 +380,81 @@ def run_ours(args, rank, world, local_rank):
             dist.barrier()
             torch.cuda.synchronize()
 
-    ev = lambda: torch.cuda.Event(enable_timing=True)  # noqa: E731
-    k1_ms, step_ms = [], []
+    # ---- multi-GPU only: the exchange against the oracle, before anything is timed
+    parity = None
+    if world > 1:
+        from smsgate_b200.dist import make_global_dedup
+        parity = {}
+        ex_small = make_global_dedup(eng, dist, 20_000, prefer_p2p=not args.nccl_exchange)
+        for name, shape in (("dup50_zipf", dict(dup_frac=0.5, hot_key_zipf=1.2)), ("dup10", dict(dup_frac=0.1))):
+            ok, received = exchange_parity(eng, dist, rank, world, ex_small, shape)
+            parity[name] = {"ok": ok, "records_received_per_rank": received}
+        del ex_small
 
-    def one_step(timed: bool):
-        flush.zero_()                                   # evict the previous step's lines from L2 (not timed)
-        e0, e1, e2 = ev(), ev(), ev()
-        e0.record()
-        eng.scan_keys(d_bytes, d_offs, cols)
-        e1.record()
-        eng.join_route_dedup(n, NOW, base_index, cols)  # stages 2 + 3 as smsgate_replay_device runs them
+    # two batches in flight per rank: the exchange of one under the keys kernel of the next (dist.OverlappedReplay)
+    from smsgate_b200.dist import OverlappedReplay
+    ov = OverlappedReplay(eng, dist if world > 1 else None, n, prefer_p2p=not args.nccl_exchange,
+                          reserve_sms=(args.reserve_sms if world > 1 else 0))
+    torch.cuda.synchronize()
+    torch.cuda.set_stream(ov.main)                       # events, flushes and barriers below follow the engines' stream
+    exchange = ov.exchanges[0]
+
+    def allmax(vals):
+        t = torch.tensor(vals, dtype=torch.float64, device="cuda")
+        if dist is not None:
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        return [float(x) for x in t.cpu()]
+
+    def allgather_int(v):
+        t = torch.tensor([v], dtype=torch.int64, device="cuda")
+        if dist is None:
+            return [int(v)]
+        out = [torch.empty_like(t) for _ in range(world)]
+        dist.all_gather(out, t)
+        return [int(x.item()) for x in out]
+
+    # ---- the other configurations of BASELINE.json that this N can run: device-resident step only
+    extra = {}
+    extra_names = [w for w in (("dup10", "skew") if world > 1 else ("mixed",)) if w != args.workload]
+    if args.no_extra:
+        extra_names = []
+    for name in extra_names:
+        R = Resident(eng, make_backup(name, n, rank, world), rank, ov)
+        sync_step, _ = time_resident(eng, R, exchange, 3, 3, flush, barrier)
+        step, k1 = time_overlapped(ov, R, max(3, args.steps // 2), 3, barrier)
+        step, k1, sync_step = allmax([step, k1, sync_step])
+        upserts = int((R.cols["status"] == 0).sum().item())
+        survivors = int(R.cols["survivor"].sum().item())
+        firsts = int(R.cols["first_seen"].sum().item())
+        info = {"workload": WORKLOADS[name].format(n=n), "ms_per_step": step, "k_scan_keys_ms": k1,
+                "one_batch_at_a_time_ms": sync_step,
+                "value": world * n / (step * 1e-3), "unit": UNIT, "mean_body_bytes": round(R.total / R.n, 1),
+                "body_mb_per_s_per_gpu": R.total / (step * 1e-3) / 1e6,
+                "upserts_per_rank": allgather_int(upserts), "survivors_per_rank": allgather_int(survivors)}
         if exchange is not None:
-            exchange.run(cols, base_index)
-        e2.record()
-        e2.synchronize()
-        if timed:
-            k1_ms.append(e0.elapsed_time(e1))
-            step_ms.append(e0.elapsed_time(e2))
+            info["records_received_per_rank"] = allgather_int(exchange.last_received())
+            # every distinct upserted key has exactly one first and one last occurrence in the whole job
+            info["survivors_equal_firsts"] = sum(allgather_int(firsts)) == sum(info["survivors_per_rank"])
+            if not info["survivors_equal_firsts"]:
+                raise SystemExit(f"{name}: global first/last counts disagree")
+        extra[name] = info
+        del R
+        torch.cuda.empty_cache()
 
-    for _ in range(args.warmup):
-        one_step(False)
-    barrier()
+    # ---- the headline workload
+    R = Resident(eng, make_backup(args.workload, n, rank, world), rank, ov)
+    backup, total, base_index = R.backup, R.total, R.base_index
     sampler = ClockSampler(local_rank)
     if rank == 0:
         sampler.start()
-    launches0 = eng.launch_count
-    for _ in range(args.steps):
-        one_step(True)
-    barrier()
-    launches = eng.launch_count - launches0 + (exchange.launches if exchange else 0)
+    sync_step, sync_k1 = time_resident(eng, R, exchange, max(3, args.steps // 2), 3, flush, barrier)
+    step, k1 = time_overlapped(ov, R, args.steps, args.warmup, barrier)
+    launches = time_overlapped.launches
+    received = allgather_int(exchange.last_received()) if exchange is not None else None
 
-    # ---- end to end through the host-buffer C-ABI call (pinned in, result columns out)
-    hb = Batch(h_bytes.numpy(), h_offs.numpy(), backup.senders, None)
+    # ---- end to end through the host-buffer C-ABI call (pinned in, result records out)
+    ev = lambda: torch.cuda.Event(enable_timing=True)  # noqa: E731
+    hb = Batch(R.h_bytes.numpy(), R.h_offs.numpy(), backup.senders, None)
     e2e_ms = []
     for it in range(args.warmup + args.steps):
         flush.zero_()
@@ -284,15 +468,10 @@ def run_ours(args, rank, world, local_rank):
             e2e_ms.append(e0.elapsed_time(e1))
     clocks = sampler.stop() if rank == 0 else None
     h2d = total + 8 * (n + 1)
-    d2h = int(res.cols.nbytes)          # one 64-byte record + one 8-byte dedup verdict per message
+    d2h = int(res.cols.nbytes)          # result bytes copied back per step (records + verdicts)
     upserts_local = int((res.status == 0).sum())
 
-    # ---- max over ranks
-    t = torch.tensor([sum(step_ms) / len(step_ms), sum(e2e_ms) / len(e2e_ms), sum(k1_ms) / len(k1_ms)],
-                     dtype=torch.float64, device="cuda")
-    if dist is not None:
-        dist.all_reduce(t, op=dist.ReduceOp.MAX)
-    step, e2e, k1 = (float(x) for x in t.cpu())
+    step, e2e, k1, sync_step, sync_k1 = allmax([step, sum(e2e_ms) / len(e2e_ms), k1, sync_step, sync_k1])   # max over ranks
     if rank != 0:
         if dist is not None:
             dist.destroy_process_group()
@@ -318,8 +497,14 @@ def run_ours(args, rank, world, local_rank):
         "metric": METRIC, "value": world * n / (step * 1e-3), "unit": UNIT, "n_gpus": world, "steps": args.steps,
         "warmup": args.warmup, "ms_per_step": step, "higher_is_better": True, "scaling": "weak",
         "vs_baseline": None, "dtype": "u8/u32/int64", "data": "synthetic",
-        "config": {"workload": workload_name(n), "msgs_per_gpu": n, "mean_body_bytes": round(mean_len, 1),
-                   "cache_entries": len(backup.cache), "l2": "512 MiB buffer written between timed steps",
+        "config": {"workload": WORKLOADS[args.workload].format(n=n), "msgs_per_gpu": n, "mean_body_bytes": round(mean_len, 1),
+                   "cache_entries": len(backup.cache),
+                   "l2": "inputs larger than L2: 3 copies of the batch (~124 MB each) and 2 output sets rotate, so no "
+                         "step finds its lines in the 126 MB L2; no flush inside the timed bracket (the one-batch and "
+                         "e2e figures flush a 512 MiB buffer between steps instead)",
+                   "timing": "one CUDA-event bracket around all K steps on the engines' stream, max over ranks; "
+                             "batch k's dedup exchange overlaps batch k+1's keys kernel (two lanes)",
+                   "scan_sms_reserved_for_exchange": (args.reserve_sms if world > 1 else 0),
                    "host_cpus_bound": (len(bound) if bound else None),
                    "parallelism": f"shard-by-index x{world}" + (f", {type(exchange).__name__} exchange by msg_id prefix" if world > 1 else "")},
         "clocks": clocks,
@@ -330,16 +515,25 @@ def run_ours(args, rank, world, local_rank):
                      "frac": achieved / peak, "traffic": traffic, "peak_source": peak_src,
                      "kernel_ms": k1, "kernel_share_of_step": k1 / step,
                      "note": "SHA-1 + SHA-256 rounds make this kernel integer-ALU bound, not HBM bound (DESIGN.md); "
-                             "alu_pipe_busy_pct / issue_slots_busy_pct are the ncu figures of the same kernel "
-                             "(profiles/, one capture per change), the ceiling it actually runs against",
+                             "alu_pipe_busy_pct / fma_pipe_busy_pct / issue_slots_busy_pct are the ncu figures of "
+                             "the same kernel (profiles/, one capture per change), the ceiling it actually runs against",
                      "alu_pipe_busy_pct": prof.get("alu_pipe_busy_pct"),
+                     "fma_pipe_busy_pct": prof.get("fma_pipe_busy_pct"),
                      "issue_slots_busy_pct": prof.get("issue_slots_busy_pct"),
                      "path_algorithmic_gbs": n * (mean_len + 229) / (step * 1e-3) / 1e9},
         "cpu_baseline": ({"value": cpu_val, "unit": UNIT, "cores": cpu_cores, "kind": "port",
                           "sample": f"{cpu_n} messages of the same workload, bodies in memory, oracle port with a "
                                     f"diskcache-backed response cache, single process"} if world == 1 else None),
         "upserts_per_gpu": upserts_local,
+        "one_batch_at_a_time": {"ms_per_step": sync_step, "k_scan_keys_ms": sync_k1, "value": world * n / (sync_step * 1e-3),
+                                "note": "per-step CUDA events, L2 flushed between steps, nothing overlapped: the latency "
+                                        "of a single batch (round 1's `value` was measured this way)"},
+        "configs": extra,
     }
+    if world > 1:
+        line["exchange_parity"] = "ok" if all(v["ok"] for v in parity.values()) else "FAILED"
+        line["exchange_parity_cases"] = parity
+        line["exchange_records_received_per_rank"] = received
     print(json.dumps(line), flush=True)
     if dist is not None:
         dist.destroy_process_group()
@@ -354,6 +548,9 @@ def main():
     ap.add_argument("--msgs", type=int, default=N_PER_GPU, help="messages per GPU (default: configs[1])")
     ap.add_argument("--cpu-sample", type=int, default=60_000)
     ap.add_argument("--nccl-exchange", action="store_true", help="use the NCCL all-to-all exchange instead of peer memory")
+    ap.add_argument("--workload", default="hit100", choices=sorted(WORKLOADS), help="headline workload (default: configs[1])")
+    ap.add_argument("--reserve-sms", type=int, default=8, help="SMs the keys kernel leaves to the exchange stream (N>1)")
+    ap.add_argument("--no-extra", action="store_true", help="skip the `configs` object (the other BASELINE.json shapes)")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3) if args.impl == "ours" else args.warmup
     rank = int(os.environ.get("RANK", "0"))

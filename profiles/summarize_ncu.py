@@ -49,6 +49,7 @@ def main():
             return float(r[hdr.index(k)].replace(",", "")) if k in hdr else None
         json.dump({"kernel": r[name_i].split("(")[0], "dram_bytes_per_launch": t, "source": rep,
                    "alu_pipe_busy_pct": num("sm__inst_executed_pipe_alu.avg.pct_of_peak_sustained_active"),
+                   "fma_pipe_busy_pct": num("sm__inst_executed_pipe_fma.avg.pct_of_peak_sustained_active"),
                    "issue_slots_busy_pct": num("smsp__issue_active.avg.pct_of_peak_sustained_active"),
                    "warp_instructions": num("smsp__inst_executed.sum"),
                    "ncu_duration_us": num("gpu__time_duration.sum")}, open(sys.argv[3], "w"))
