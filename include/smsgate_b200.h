@@ -67,6 +67,7 @@ extern "C" {
 #define SMSGATE_E_DATE_NOBODY 0x0080
 #define SMSGATE_E_DATE_TZ 0x0100
 #define SMSGATE_E_DATE_KEY 0x0200
+#define SMSGATE_E_DATE_PHONE 0x0400 /* the cached date holds no date text: the phone's timestamp stands in (below) */
 
 /* dec_flags[] layout: bits 0-1 amount error, 2-3 balance error, bit 4 amount sign, bit 5 balance sign,
  * bit 6 / bit 7: amount / balance does not fit Numeric(14,2) (more than 12 integer digits) */
@@ -232,6 +233,15 @@ typedef struct smsgate_legacy_outputs {
 } smsgate_legacy_outputs;
 int smsgate_legacy_parse(smsgate_ctx* ctx, int64_t n, const int64_t* h_offsets, const uint8_t* h_bytes,
                          const smsgate_legacy_outputs* h_out);
+/* The same kernel doing what the reference's single-message functions do: parse_transaction_message
+ * (process_cached.py:150-177) = NO_STRIP | NO_OTP | NO_CREDIT, parse_credit_message (:180-204) =
+ * NO_STRIP | NO_OTP | NO_DEBIT - one pattern, applied to the message as given.  mode 0 = smsgate_legacy_parse. */
+#define SMSGATE_LEG_MODE_NO_STRIP 0x1
+#define SMSGATE_LEG_MODE_NO_OTP 0x2
+#define SMSGATE_LEG_MODE_NO_DEBIT 0x4
+#define SMSGATE_LEG_MODE_NO_CREDIT 0x8
+int smsgate_legacy_parse_mode(smsgate_ctx* ctx, int64_t n, const int64_t* h_offsets, const uint8_t* h_bytes,
+                              uint32_t mode, const smsgate_legacy_outputs* h_out);
 
 /* ---- the replay stages, device pointers ----------------------------------- */
 /* Stage 1 — keys and scans: msg_id (watcher.py:45), worker skip filter
@@ -245,6 +255,13 @@ int smsgate_scan_keys(smsgate_ctx* ctx, const uint8_t* d_bytes, const int64_t* d
  * cache_key, flags, body_date; writes slot, status, amount_*, balance_*,
  * dec_flags, date, card, card_len.  now_packed is the frozen `datetime.now()`. */
 int smsgate_join_route(smsgate_ctx* ctx, int64_t n, int64_t now_packed, const smsgate_outputs* out);
+/* Messages that carry a unix timestamp in raw.date (device-sourced messages, re-parsed DLQ entries): when the
+ * cached date holds no date text, parse_sms_llm falls back to parse_unix_timestamp(int(raw.date),
+ * tz="Asia/Yerevan", aware=False) (libs/gemini_parser.py:227-229, :139-188).  d_phone_dt[n] = that naive
+ * datetime, packed like smsgate_outputs.date, or 0 where int(raw.date) / the conversion raises; the pointer is
+ * used by every later smsgate_join_route / smsgate_join_route_dedup on this context until it is reset with
+ * NULL.  Without it (XML replay: raw.date is ISO text, int() raises) such messages end as UNMATCHED. */
+int smsgate_set_phone_dates(smsgate_ctx* ctx, const int64_t* d_phone_dt);
 /* Stage 3 — upsert-by-msg_id (libs/pocketbase.py:168-200,
  * services/pb_writer/upsert.py:19-31): among messages with status UPSERT the
  * last occurrence of a msg_id survives, the first one is the insert.  Reads

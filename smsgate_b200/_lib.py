@@ -21,10 +21,11 @@ STATUS_NAMES = ("UPSERT", "PARSED_NO_MERCHANT", "SKIPPED_FILTER", "CACHE_MISS", 
                 "FUTURE_DATE", "FAILED_EXC")
 DLQ_STATUSES = (ST_CACHE_MISS, ST_UNMATCHED, ST_FUTURE_DATE, ST_FAILED_EXC)
 E_IS_DICT, E_HAS_TXN, E_SCHEMA_OK, E_CARD_STR, E_MERCHANT = 0x1, 0x2, 0x4, 0x8, 0x10
-E_DATE_STRICT, E_DATE_HOST, E_DATE_NOBODY, E_DATE_TZ, E_DATE_KEY = 0x20, 0x40, 0x80, 0x100, 0x200
+E_DATE_STRICT, E_DATE_HOST, E_DATE_NOBODY, E_DATE_TZ, E_DATE_KEY, E_DATE_PHONE = 0x20, 0x40, 0x80, 0x100, 0x200, 0x400
 DEC_OK, DEC_SYNTAX, DEC_OVERFLOW = 0, 1, 2
 LEG_SKIPPED_OTP, LEG_DEBIT, LEG_CREDIT, LEG_FAILED = 0, 1, 2, 3
 LEG_F_BUDGET, LEG_F_INEXACT, LEG_GROUPS = 1, 2, 10
+LEG_MODE_NO_STRIP, LEG_MODE_NO_OTP, LEG_MODE_NO_DEBIT, LEG_MODE_NO_CREDIT = 1, 2, 4, 8
 DEDUP_STATIC_MAX = 1 << 20
 MAX_WORLD = 64
 RECORD_BYTES = 32
@@ -99,6 +100,7 @@ def lib():
         "smsgate_cache_share": (i32, [vp, vp]),
         "smsgate_set_stream": (i32, [vp, vp]),
         "smsgate_set_scan_ctas": (i32, [vp, i32]),
+        "smsgate_set_phone_dates": (i32, [vp, vp]),
         "smsgate_decimal_batch": (i32, [vp, i64, vp, vp, vp, vp, vp]),
         "smsgate_strict_date_batch": (i32, [vp, i64, vp, vp, vp]),
         "smsgate_dt_str_batch": (i32, [vp, i64, vp, vp, vp]),
@@ -106,6 +108,7 @@ def lib():
         "smsgate_xml_emit": (i32, [vp, vp, vp, vp, vp, vp, vp]),
         "smsgate_xml_release": (i32, [vp]),
         "smsgate_legacy_parse": (i32, [vp, i64, vp, vp, C.POINTER(LegacyOutputs)]),
+        "smsgate_legacy_parse_mode": (i32, [vp, i64, vp, vp, C.c_uint32, C.POINTER(LegacyOutputs)]),
         "smsgate_scan_keys": (i32, [vp, vp, vp, i64, C.POINTER(Outputs)]),
         "smsgate_join_route": (i32, [vp, i64, i64, C.POINTER(Outputs)]),
         "smsgate_dedup": (i32, [vp, i64, i64, C.POINTER(Outputs)]),

@@ -198,7 +198,11 @@ struct RouteResult {
 
 // worker.py:112-189 + gemini_parser.py:224-247 + writer.py:65-84 for one
 // message whose cache probe has already been done (`hit`, entry `e`).
-SG_HD RouteResult sg_route(uint32_t mflags, int32_t body_date, bool hit, const EntryView& e, int64_t now_packed) {
+// `phone_dt`: for a message whose raw.date is a unix timestamp (device-sourced / DLQ messages), the naive
+// Asia/Yerevan datetime parse_unix_timestamp(int(raw.date)) gives (gemini_parser.py:139-188), packed; 0 when
+// int(raw.date) or the conversion raises (always the case for XML messages: raw.date is ISO text there).
+SG_HD RouteResult sg_route(uint32_t mflags, int32_t body_date, bool hit, const EntryView& e, int64_t now_packed,
+                           int64_t phone_dt = 0) {
     RouteResult r;
     r.status = SG_ST_SKIPPED_FILTER;
     r.amount.coef = 0; r.amount.exp = 0; r.amount.err = 0; r.amount.sign = 0;
@@ -226,6 +230,7 @@ SG_HD RouteResult sg_route(uint32_t mflags, int32_t body_date, bool hit, const E
         bool has_dt = false;
         if (e.eflags & SG_E_DATE_STRICT) { dt = sg_parse_strict_datetime(e.date, e.date_len); has_dt = dt > 0; }
         else if (e.eflags & SG_E_DATE_HOST) { dt = e.date_packed; has_dt = true; }
+        else if ((e.eflags & SG_E_DATE_PHONE) && phone_dt > 0) { dt = phone_dt; has_dt = true; }   // :227-229
         if (has_dt) {
             if (body_date) r.date = sg_replace_date(dt, body_date);
             else { r.date = dt; tz_aware = (e.eflags & SG_E_DATE_TZ) != 0; }

@@ -222,19 +222,26 @@ SG_HD bool sg_legacy_numbers(const uint8_t* t, const int* caps, int g_amount, in
     return true;
 }
 
-SG_HD LegacyResult sg_legacy_process(const uint8_t* body, int len, const LegacyTables& L) {
+// `mode` = 0 is process_sms_from_cache's per-entry work (process_cached.py:233-261).  The bits select what
+// the reference's single-message functions do instead: parse_transaction_message / parse_credit_message
+// (process_cached.py:150-204) apply ONE pattern to the message as given - no strip(), no OTP filter.
+#define LEG_MODE_NO_STRIP 0x1
+#define LEG_MODE_NO_OTP 0x2
+#define LEG_MODE_NO_DEBIT 0x4
+#define LEG_MODE_NO_CREDIT 0x8
+SG_HD LegacyResult sg_legacy_process(const uint8_t* body, int len, const LegacyTables& L, uint32_t mode = 0) {
     LegacyResult r;
     r.status = LEG_FAILED; r.lflags = 0; r.amount = 0; r.balance = 0;
     for (int k = 0; k < 2 * RX_MAX_GROUPS; ++k) r.caps[k] = -1;
     int lo = 0, hi = len;
-    sg_strip_span(body, &lo, &hi);                                       // process_cached.py:233
+    if (!(mode & LEG_MODE_NO_STRIP)) sg_strip_span(body, &lo, &hi);      // process_cached.py:233
     r.strip_lo = lo; r.strip_hi = hi;
     const uint8_t* t = body + lo;
     const int tl = hi - lo;
     sg_sha256(t, tl, r.digest);                                          // :254 (computed for every body)
     // OTP / PASS= / CODE: in body_text.upper() (:236)
     uint32_t st = 0;
-    for (int i = 0; i < tl; ++i) {
+    for (int i = 0; i < tl && !(mode & LEG_MODE_NO_OTP); ++i) {
         const uint32_t cw = T_BYTE_CLASS(L.scan)[t[i]];
         if ((int32_t)cw < 0) {
             uint32_t cp, up[3];
@@ -246,7 +253,7 @@ SG_HD LegacyResult sg_legacy_process(const uint8_t* body, int len, const LegacyT
     }
     if (st == LEG_OTP_ACCEPT_OFF) { r.status = LEG_SKIPPED_OTP; return r; }
     int caps[2 * RX_MAX_GROUPS];
-    int m = sg_rx_exec(L.debit, t, tl, caps, L);                         // :243 parse_transaction_message
+    int m = (mode & LEG_MODE_NO_DEBIT) ? 0 : sg_rx_exec(L.debit, t, tl, caps, L);   // :243 parse_transaction_message
     if (m < 0) r.lflags |= LEG_F_BUDGET;
     if (m == 1 && sg_legacy_numbers(t, caps, RX_DEBIT_G_AMOUNT, RX_DEBIT_G_BALANCE, L, &r)) {
         r.status = LEG_DEBIT;
@@ -256,7 +263,7 @@ SG_HD LegacyResult sg_legacy_process(const uint8_t* body, int len, const LegacyT
         return r;
     }
     r.lflags &= ~LEG_F_INEXACT;
-    m = sg_rx_exec(L.credit, t, tl, caps, L);                            // :248 parse_credit_message
+    m = (mode & LEG_MODE_NO_CREDIT) ? 0 : sg_rx_exec(L.credit, t, tl, caps, L);     // :248 parse_credit_message
     if (m < 0) r.lflags |= LEG_F_BUDGET;
     if (m == 1 && sg_legacy_numbers(t, caps, RX_CREDIT_G_AMOUNT, RX_CREDIT_G_BALANCE, L, &r)) {
         r.status = LEG_CREDIT;

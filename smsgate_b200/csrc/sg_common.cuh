@@ -42,6 +42,7 @@
 #define SG_E_DATE_NOBODY  0x0080  // no datetime object, but pydantic accepts the raw value when the body has no date
 #define SG_E_DATE_TZ      0x0100  // that datetime is timezone-aware
 #define SG_E_DATE_KEY     0x0200  // 'date' key present
+#define SG_E_DATE_PHONE   0x0400  // dateutil: "String does not contain a date" -> the phone's timestamp, int(raw.date) (gemini_parser.py:227-229)
 
 // decimal result flags: bits 0-1 amount error, 2-3 balance error, 4 amount sign, 5 balance sign
 #define SG_DEC_OK 0

@@ -533,7 +533,8 @@ __device__ __forceinline__ void dedup_insert_one(int64_t i, const uint8_t* __res
 __global__ void __launch_bounds__(256, K2_MIN_BLOCKS)
 k_join_route(int64_t n, const uint8_t* __restrict__ cache_key, const uint8_t* __restrict__ flags,
              const int32_t* __restrict__ body_date, int64_t now_packed, CacheView C, JoinOut out,
-             DedupScratch D, int64_t dedup_i0, const uint8_t* __restrict__ dedup_ids) {
+             DedupScratch D, int64_t dedup_i0, const uint8_t* __restrict__ dedup_ids,
+             const int64_t* __restrict__ phone_dt) {
     const int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
     if (i >= n) return;
     const uint4* kp = reinterpret_cast<const uint4*>(cache_key + i * 32);
@@ -579,7 +580,8 @@ k_join_route(int64_t n, const uint8_t* __restrict__ cache_key, const uint8_t* __
         ev.eflags = sdw.y & 0xFFFF;
         if (ev.eflags & (SG_E_DATE_HOST | SG_E_DATE_NOBODY)) ev.date_packed = C.date_packed[e];
     }
-    const RouteResult r = sg_route(flags[i], body_date[i], e >= 0, ev, now_packed);
+    const RouteResult r = sg_route(flags[i], body_date[i], e >= 0, ev, now_packed,
+                                   phone_dt ? phone_dt[dedup_i0 + i] : 0);   // dedup_i0: this launch's first message in the batch
     if (out.slot) out.slot[i] = e;
     if (out.status) out.status[i] = (uint8_t)r.status;
     if (out.amount_coef) out.amount_coef[i] = r.amount.coef;
@@ -704,10 +706,10 @@ struct LegacyOut {
 };
 __global__ void __launch_bounds__(128)
 k_legacy_parse(int64_t n, const int64_t* __restrict__ offsets, const uint8_t* __restrict__ bytes, LegacyTables L,
-               LegacyOut out) {
+               LegacyOut out, uint32_t mode) {
     const int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
     if (i >= n) return;
-    const LegacyResult r = sg_legacy_process(bytes + offsets[i], (int)(offsets[i + 1] - offsets[i]), L);
+    const LegacyResult r = sg_legacy_process(bytes + offsets[i], (int)(offsets[i + 1] - offsets[i]), L, mode);
     out.status[i] = (uint8_t)r.status;
     out.lflags[i] = (uint8_t)r.lflags;
     out.strip[2 * i] = r.strip_lo;
@@ -742,6 +744,7 @@ struct smsgate_ctx {
     uint8_t *xml_kind = nullptr, *xml_mflags = nullptr;
     int sm_count = 148;
     int scan_ctas = 0;                       // CTAs of k_scan_keys, 0 = one per SM (smsgate_set_scan_ctas)
+    const int64_t* phone_dt = nullptr;       // per-message phone timestamps for the next join (smsgate_set_phone_dates)
     bool cache_shared = false;               // the cache arrays belong to another context (smsgate_cache_share)
     std::string err;
     int64_t launches = 0;
@@ -1031,6 +1034,12 @@ extern "C" int smsgate_set_stream(smsgate_ctx* ctx, void* cuda_stream) {
     return SMSGATE_OK;
 }
 
+extern "C" int smsgate_set_phone_dates(smsgate_ctx* ctx, const int64_t* d_phone_dt) {
+    if (!ctx) return SMSGATE_E_ARG;
+    ctx->phone_dt = d_phone_dt;
+    return SMSGATE_OK;
+}
+
 extern "C" int smsgate_set_scan_ctas(smsgate_ctx* ctx, int ctas) {
     if (!ctx) return SMSGATE_E_ARG;
     if (ctas < 0 || ctas > ctx->sm_count) return fail(ctx, SMSGATE_E_ARG, "set_scan_ctas: between 0 (default) and the SM count");
@@ -1125,7 +1134,13 @@ done:
 
 extern "C" int smsgate_legacy_parse(smsgate_ctx* ctx, int64_t n, const int64_t* h_offsets, const uint8_t* h_bytes,
                                     const smsgate_legacy_outputs* h_out) {
+    return smsgate_legacy_parse_mode(ctx, n, h_offsets, h_bytes, 0, h_out);
+}
+
+extern "C" int smsgate_legacy_parse_mode(smsgate_ctx* ctx, int64_t n, const int64_t* h_offsets, const uint8_t* h_bytes,
+                                         uint32_t mode, const smsgate_legacy_outputs* h_out) {
     if (!ctx) return SMSGATE_E_ARG;
+    if (mode > 0xF) return fail(ctx, SMSGATE_E_ARG, "legacy_parse: unknown mode bits");
     if (n < 0 || !h_out || (n > 0 && (!h_offsets || !h_out->status || !h_out->lflags || !h_out->strip || !h_out->caps ||
                                       !h_out->amount || !h_out->balance || !h_out->body_hash)))
         return fail(ctx, SMSGATE_E_ARG, "legacy_parse: NULL array");
@@ -1157,7 +1172,7 @@ extern "C" int smsgate_legacy_parse(smsgate_ctx* ctx, int64_t n, const int64_t* 
         LG_TRY(cudaMemcpyAsync(d_off, h_offsets, (size_t)(n + 1) * 8, cudaMemcpyHostToDevice, st));
         if (nb) LG_TRY(cudaMemcpyAsync(d_bytes, h_bytes + h_offsets[0], (size_t)nb, cudaMemcpyHostToDevice, st));
         // the kernel indexes bytes with the caller's absolute offsets
-        k_legacy_parse<<<(unsigned)((n + 127) / 128), 128, 0, st>>>(n, d_off, d_bytes - h_offsets[0], ctx->legacy, o);
+        k_legacy_parse<<<(unsigned)((n + 127) / 128), 128, 0, st>>>(n, d_off, d_bytes - h_offsets[0], ctx->legacy, o, mode);
         ctx->launches += 1;
         LG_TRY(cudaMemcpyAsync(h_out->status, o.status, (size_t)n, cudaMemcpyDeviceToHost, st));
         LG_TRY(cudaMemcpyAsync(h_out->lflags, o.lflags, (size_t)n, cudaMemcpyDeviceToHost, st));
@@ -1400,7 +1415,8 @@ static int join_route_impl(smsgate_ctx* ctx, int64_t n, int64_t now_packed, cons
     const DedupScratch none{nullptr, nullptr, 0};
     k_join_route<<<(unsigned)((n + 255) / 256), 256, 0, ctx->stream>>>(n, out->cache_key, out->flags, out->body_date,
                                                                         now_packed, C, jo, D ? *D : none, dedup_i0,
-                                                                        dedup_ids);
+                                                                        dedup_ids,
+                                                                        ctx->phone_dt);
     ctx->launches += 1;
     CUDA_TRY(ctx, cudaGetLastError());
     return SMSGATE_OK;

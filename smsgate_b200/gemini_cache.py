@@ -173,6 +173,8 @@ def _apply_host_date(kind: str, obj, e: int, date_packed: np.ndarray, host_dates
         if obj.tzinfo is not None:
             f |= L.E_DATE_TZ
         return f
+    if kind == "rawdate":
+        return L.E_DATE_PHONE
     return 0
 
 

@@ -73,7 +73,7 @@ def dt_str(strings):
     return out
 
 
-def join_route(scan_cols, table, now_packed):
+def join_route(scan_cols, table, now_packed, phone_dt=None):
     n = len(scan_cols["flags"])
     cols = dict(slot=np.zeros(n, np.int32), status=np.zeros(n, np.uint8), amount_coef=np.zeros(n, np.int64),
                 balance_coef=np.zeros(n, np.int64), amount_exp=np.zeros(n, np.int32),
@@ -87,11 +87,12 @@ def join_route(scan_cols, table, now_packed):
                         _p(table.eflags), _p(table.date_packed), _p(cols["slot"]), _p(cols["status"]),
                         _p(cols["amount_coef"]), _p(cols["balance_coef"]), _p(cols["amount_exp"]),
                         _p(cols["balance_exp"]), _p(cols["dec_flags"]), _p(cols["date"]), _p(cols["card"]),
-                        _p(cols["card_len"]), _p(cols["amount_cents"]), _p(cols["balance_cents"]))
+                        _p(cols["card_len"]), _p(cols["amount_cents"]), _p(cols["balance_cents"]),
+                        _p(np.ascontiguousarray(phone_dt, dtype=np.int64)) if phone_dt is not None else None)
     return cols
 
 
-def legacy(bodies):
+def legacy(bodies, mode=0):
     data, offsets = ragged_from_strings(bodies)
     n = len(bodies)
     cols = dict(status=np.zeros(n, np.uint8), lflags=np.zeros(n, np.uint8), strip=np.zeros((n, 2), np.int32),
@@ -99,7 +100,7 @@ def legacy(bodies):
                 body_hash=np.zeros((n, 32), np.uint8))
     data = np.concatenate([data, np.zeros(16, np.uint8)])
     lib().hc_legacy(C.c_int64(n), _p(offsets), _p(data), _p(cols["status"]), _p(cols["lflags"]), _p(cols["strip"]),
-                    _p(cols["caps"]), _p(cols["amount"]), _p(cols["balance"]), _p(cols["body_hash"]))
+                    _p(cols["caps"]), _p(cols["amount"]), _p(cols["balance"]), _p(cols["body_hash"]), C.c_uint32(mode))
     return cols
 
 

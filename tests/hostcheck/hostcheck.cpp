@@ -103,7 +103,8 @@ extern "C" int hc_join_route(int64_t n, const uint8_t* cache_key, const uint8_t*
                              const uint8_t* val_bytes, const uint16_t* eflags, const int64_t* date_packed,
                              int32_t* slot, uint8_t* status, int64_t* amount_coef, int64_t* balance_coef,
                              int32_t* amount_exp, int32_t* balance_exp, uint8_t* dec_flags, int64_t* date,
-                             uint8_t* card, uint8_t* card_len, int64_t* amount_cents, int64_t* balance_cents) {
+                             uint8_t* card, uint8_t* card_len, int64_t* amount_cents, int64_t* balance_cents,
+                             const int64_t* phone_dt) {
     std::unordered_map<std::string, int> idx;
     for (int64_t e = 0; e < m; ++e) idx.emplace(std::string((const char*)keys + e * 32, 32), (int)e);
     for (int64_t i = 0; i < n; ++i) {
@@ -120,7 +121,7 @@ extern "C" int hc_join_route(int64_t n, const uint8_t* cache_key, const uint8_t*
             ev.eflags = eflags[e];
             ev.date_packed = date_packed[e];
         }
-        RouteResult r = sg_route(flags[i], body_date[i], e >= 0, ev, now_packed);
+        RouteResult r = sg_route(flags[i], body_date[i], e >= 0, ev, now_packed, phone_dt ? phone_dt[i] : 0);
         slot[i] = e; status[i] = (uint8_t)r.status;
         amount_coef[i] = r.amount.coef; balance_coef[i] = r.balance.coef;
         amount_exp[i] = r.amount.exp; balance_exp[i] = r.balance.exp;
@@ -135,13 +136,14 @@ extern "C" int hc_join_route(int64_t n, const uint8_t* cache_key, const uint8_t*
 }
 
 extern "C" int hc_legacy(int64_t n, const int64_t* offsets, const uint8_t* bytes, uint8_t* status, uint8_t* lflags,
-                         int32_t* strip, int32_t* caps, double* amount, double* balance, uint8_t* body_hash) {
+                         int32_t* strip, int32_t* caps, double* amount, double* balance, uint8_t* body_hash,
+                         uint32_t mode) {
     LegacyTables L;
     L.debit = H_RX_DEBIT; L.credit = H_RX_CREDIT; L.word_lo = H_RX_WORD_LO; L.word_hi = H_RX_WORD_HI;
     L.ci_exc = H_RX_CI_EXC; L.otp_next = (const uint8_t*)H_LEG_OTP_NEXT;
     L.scan = host_tables();
     for (int64_t i = 0; i < n; ++i) {
-        LegacyResult r = sg_legacy_process(bytes + offsets[i], (int)(offsets[i + 1] - offsets[i]), L);
+        LegacyResult r = sg_legacy_process(bytes + offsets[i], (int)(offsets[i + 1] - offsets[i]), L, mode);
         status[i] = (uint8_t)r.status; lflags[i] = (uint8_t)r.lflags;
         strip[2 * i] = r.strip_lo; strip[2 * i + 1] = r.strip_hi;
         for (int k = 0; k < 2 * RX_MAX_GROUPS; ++k) caps[i * 2 * RX_MAX_GROUPS + k] = r.caps[k];

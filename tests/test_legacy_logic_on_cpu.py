@@ -12,8 +12,8 @@ from smsgate_b200 import legacy
 from tests import _hostcheck as H
 
 
-def _res(bodies):
-    cols = H.legacy(bodies)
+def _res(bodies, mode=0):
+    cols = H.legacy(bodies, mode)
     from smsgate_b200.batch import ragged_from_strings
     data, offsets = ragged_from_strings(bodies)
     return legacy.LegacyResult(bodies, data, offsets, cols)
@@ -63,6 +63,25 @@ def test_golden_cases(golden):
         assert st == (L.LEG_DEBIT if c["debit"] else L.LEG_CREDIT if c["credit"] else L.LEG_FAILED), c["body"]
     assert n_inexact < 40
     check_against_oracle(res, bodies)
+
+
+def test_single_message_functions_golden(golden):
+    """parse_transaction_message / parse_credit_message as the reference runs them on ONE message: the
+    pattern applied to the message as given (outer whitespace kept, no OTP filter), each on its own."""
+    cases = golden("legacy.json")["cases"]
+    bodies = [c["body"] for c in cases]
+    base = L.LEG_MODE_NO_STRIP | L.LEG_MODE_NO_OTP
+    deb, cre = _res(bodies, base | L.LEG_MODE_NO_CREDIT), _res(bodies, base | L.LEG_MODE_NO_DEBIT)
+    checked = 0
+    for i, c in enumerate(cases):
+        for res, want, ok in ((deb, c["debit"], L.LEG_DEBIT), (cre, c["credit"], L.LEG_CREDIT)):
+            assert not (int(res.cols["lflags"][i]) & L.LEG_F_BUDGET)
+            if int(res.cols["lflags"][i]) & L.LEG_F_INEXACT:
+                continue
+            got = res.parsed(i) if (c["body"] and int(res.cols["status"][i]) == ok) else None
+            assert _bits(got) == want, c["body"]
+            checked += 1
+    assert checked > 1.9 * len(cases)
 
 
 def test_process_flow_golden(golden):
