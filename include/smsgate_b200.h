@@ -53,8 +53,12 @@ extern "C" {
 #define SMSGATE_ST_CACHE_MISS 3         /* would call Gemini (libs/gemini_parser.py:210-222); offline: DLQ set */
 #define SMSGATE_ST_UNMATCHED 4          /* parse_sms_llm returned None -> sms.failed (worker.py:151-158) */
 #define SMSGATE_ST_BROKEN 5             /* BrokenMessage: acked, dropped (worker.py:136-140) */
-#define SMSGATE_ST_FUTURE_DATE 6        /* parsed.date > now -> sms.failed (worker.py:174-180) */
-#define SMSGATE_ST_FAILED_EXC 7         /* any other exception -> sms.failed (worker.py:141-149) */
+#define SMSGATE_ST_FUTURE_DATE 6        /* parsed.date > now (worker.py:174): the branch means to publish to sms.failed, but its
+                                           `msg.data.decode(...)` (:177) runs on a str and raises - run as written, the handler
+                                           dies there and nothing is published or acked (tests/golden/worker_flow.json) */
+#define SMSGATE_ST_FAILED_EXC 7         /* parse_sms_llm raised something else -> sms.failed (worker.py:141-149) */
+#define SMSGATE_ST_ESCAPED 8            /* parsed, but the date is timezone-aware: `parsed.date > datetime.now()` (worker.py:174)
+                                           raises TypeError outside every try - nothing is published or acked */
 
 /* per cache entry flags supplied by the loader (see smsgate_cache_load) */
 #define SMSGATE_E_IS_DICT 0x0001

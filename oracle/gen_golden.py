@@ -323,7 +323,7 @@ def _route(ref, filt, body, sender, raw_date, msg_id="m"):
         if parsed.date > NOW:                       # worker.py:174 with a frozen clock
             return "FUTURE_DATE", parsed
     except TypeError:
-        return "FAILED_EXC", parsed
+        return "ESCAPED", parsed
     return ("UPSERT" if parsed.merchant else "PARSED_NO_MERCHANT"), parsed   # writer.py:70
 
 

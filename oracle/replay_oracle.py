@@ -38,10 +38,11 @@ ST_SKIPPED_FILTER = 2    # worker skip-filter hit: acked, nothing published
 ST_CACHE_MISS = 3        # would call Gemini; offline replay -> DLQ set
 ST_UNMATCHED = 4         # parse_sms_llm returned None -> sms.failed
 ST_BROKEN = 5            # BrokenMessage: acked and dropped
-ST_FUTURE_DATE = 6       # parsed.date > now -> sms.failed
+ST_FUTURE_DATE = 6       # parsed.date > now: the handler then raises at worker.py:177 (.decode on a str), nothing published
 ST_FAILED_EXC = 7        # parse_sms_llm raised something else -> sms.failed
+ST_ESCAPED = 8           # aware date: the comparison at worker.py:174 raises TypeError outside every try
 
-DLQ_STATUSES = (ST_CACHE_MISS, ST_UNMATCHED, ST_FUTURE_DATE, ST_FAILED_EXC)
+DLQ_STATUSES = (ST_CACHE_MISS, ST_UNMATCHED, ST_FAILED_EXC)     # pinned by tests/golden/worker_flow.json
 
 
 # --------------------------------------------------------------------------
@@ -357,7 +358,7 @@ def replay_one(body: str, sender: str, raw_date: str, cache, now: _dt.datetime,
     try:
         future = parsed.date > now                                # worker.py:174
     except TypeError:                                             # aware vs naive: escapes
-        out.status = ST_FAILED_EXC
+        out.status = ST_ESCAPED
         return out
     if future:
         out.status = ST_FUTURE_DATE

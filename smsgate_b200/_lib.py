@@ -16,10 +16,13 @@ ABI_VERSION = 2
 # flags / status / entry flags — mirror the header
 F_WORKER_SKIP, F_PARSER_OTP, F_MODIFIED, F_BODY_DATE = 0x01, 0x02, 0x04, 0x08
 (ST_UPSERT, ST_PARSED_NO_MERCHANT, ST_SKIPPED_FILTER, ST_CACHE_MISS, ST_UNMATCHED, ST_BROKEN,
- ST_FUTURE_DATE, ST_FAILED_EXC) = range(8)
+ ST_FUTURE_DATE, ST_FAILED_EXC, ST_ESCAPED) = range(9)
 STATUS_NAMES = ("UPSERT", "PARSED_NO_MERCHANT", "SKIPPED_FILTER", "CACHE_MISS", "UNMATCHED", "BROKEN",
-                "FUTURE_DATE", "FAILED_EXC")
-DLQ_STATUSES = (ST_CACHE_MISS, ST_UNMATCHED, ST_FUTURE_DATE, ST_FAILED_EXC)
+                "FUTURE_DATE", "FAILED_EXC", "ESCAPED")
+# what actually reaches sms.failed.  FUTURE_DATE and ESCAPED do not: the reference's handler raises there
+# (worker.py:177 / :174, observed by running it: tests/golden/worker_flow.json)
+DLQ_STATUSES = (ST_CACHE_MISS, ST_UNMATCHED, ST_FAILED_EXC)
+HANDLER_RAISES = (ST_FUTURE_DATE, ST_ESCAPED)
 E_IS_DICT, E_HAS_TXN, E_SCHEMA_OK, E_CARD_STR, E_MERCHANT = 0x1, 0x2, 0x4, 0x8, 0x10
 E_DATE_STRICT, E_DATE_HOST, E_DATE_NOBODY, E_DATE_TZ, E_DATE_KEY, E_DATE_PHONE = 0x20, 0x40, 0x80, 0x100, 0x200, 0x400
 DEC_OK, DEC_SYNTAX, DEC_OVERFLOW = 0, 1, 2

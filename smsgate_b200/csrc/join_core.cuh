@@ -251,7 +251,7 @@ SG_HD RouteResult sg_route(uint32_t mflags, int32_t body_date, bool hit, const E
     if (!(e.eflags & SG_E_IS_DICT) || !(e.eflags & SG_E_HAS_TXN)) { r.status = SG_ST_FAILED_EXC; return r; }
     if (fail) { r.status = SG_ST_UNMATCHED; return r; }
     if (card_cps < 4) { r.status = SG_ST_BROKEN; return r; }                   // :246-247
-    if (tz_aware) { r.status = SG_ST_FAILED_EXC; return r; }                   // naive/aware compare raises (worker.py:174)
+    if (tz_aware) { r.status = SG_ST_ESCAPED; return r; }                      // naive/aware compare raises (worker.py:174), outside every try
     if (r.date > now_packed) { r.status = SG_ST_FUTURE_DATE; return r; }       // worker.py:174
     r.status = (e.eflags & SG_E_MERCHANT) ? SG_ST_UPSERT : SG_ST_PARSED_NO_MERCHANT;   // writer.py:70
     return r;

@@ -30,6 +30,7 @@
 #define SG_ST_BROKEN 5
 #define SG_ST_FUTURE_DATE 6
 #define SG_ST_FAILED_EXC 7
+#define SG_ST_ESCAPED 8
 
 // per cache entry flags, computed by the loader (smsgate_b200/gemini_cache.py)
 #define SG_E_IS_DICT      0x0001  // cached value is a dict

@@ -31,7 +31,9 @@ from .replay import ReplayEngine, ReplayResult
 NOT_JSON = "not_json"            # dlq_worker.py:48-53: logged, acked, nothing else
 NOT_AN_OBJECT = "not_an_object"  # payload.get(...) raises AttributeError in the reference (dlq_worker.py:60)
 NO_RAW = "no_raw"                # dlq_worker.py:61-63: "nothing to re-parse"
-INVALID_RAW = "invalid_raw"      # worker.py:99-109: RawSMS(**raw) failed -> published to sms.failed again
+INVALID_RAW = "invalid_raw"      # worker.py:99-109: RawSMS(**raw) failed.  The handler means to publish it to sms.failed
+                                 # again, but msg.data is already a str by then and `.decode` raises (:105): run as
+                                 # written, nothing is published or acked (tests/golden/worker_flow.json)
 REPLAYED = "replayed"
 
 
@@ -79,7 +81,6 @@ class DlqResult:
     row: np.ndarray                      # per payload: row in `result`, -1 if it was not replayed
     raws: List[RawSMS]                   # per replayed row
     result: Optional[ReplayResult]       # columns of the replayed rows (None when nothing was replayed)
-    needs_phone_timestamp: List[int] = field(default_factory=list)
 
     def parsed(self, r: int):
         """What `parse_sms_llm(raw)` returns / raises for replayed row r, carrying the message's own ids."""
@@ -92,23 +93,30 @@ class DlqResult:
             if self.result is not None else {}
 
 
-def reparse(engine: ReplayEngine, payloads: Sequence[Union[bytes, str]], now: _dt.datetime,
-            base_index: int = 0) -> DlqResult:
-    """Re-parse a dump of `sms.failed` in one pass.  The response cache must be loaded
-    (`engine.load_cache`).  Stage calls on device memory: keys + scans of the bodies, then the message's
-    own ids take the place of the computed key column, then join + routing and the upsert dedup."""
+def phone_datetime(raw_date: Any) -> int:
+    """`parse_unix_timestamp(int(raw.date), tz="Asia/Yerevan", aware=False)` (libs/gemini_parser.py:229,
+    :139-188) as a packed naive datetime, 0 where the reference raises (ISO text, negative, >= 1e14, out of
+    range).  Evaluated with Python's own int / float / datetime / zoneinfo, like the reference."""
+    import zoneinfo
+
+    from .gemini_cache import pack_datetime
+    try:
+        ts = float(int(raw_date))
+        if ts < 0 or ts >= 1e14:
+            return 0
+        secs = ts if ts < 1e11 else ts / 1_000
+        d = _dt.datetime.fromtimestamp(secs, tz=_dt.timezone.utc).astimezone(zoneinfo.ZoneInfo("Asia/Yerevan"))
+        return pack_datetime(d.replace(tzinfo=None))
+    except Exception:
+        return 0
+
+
+def replay_raws(engine: ReplayEngine, raws: Sequence[RawSMS], now: _dt.datetime, base_index: int = 0) -> ReplayResult:
+    """Replay messages that bring their own identity (`RawSMS` objects: DLQ entries, device-sourced
+    messages): keys + scans of the bodies on the GPU, then the messages' own ids take the place of the
+    computed key column, the phone timestamps of numeric `raw.date`s ride along for the cached dates that
+    hold no date text (libs/gemini_parser.py:227-229), then join + routing and the upsert dedup."""
     import torch
-    outcomes, errors, raws = [], [], []
-    row = np.full(len(payloads), -1, dtype=np.int64)
-    for i, p in enumerate(payloads):
-        o, raw, err = unwrap(p)
-        outcomes.append(o)
-        errors.append(err)
-        if raw is not None:
-            row[i] = len(raws)
-            raws.append(raw)
-    if not raws:
-        return DlqResult(outcomes, errors, row, raws, None)
     batch = Batch.from_strings([r.body for r in raws], [r.sender for r in raws], None)
     n = batch.n
     dev = torch.device("cuda", engine.device)
@@ -120,31 +128,34 @@ def reparse(engine: ReplayEngine, payloads: Sequence[Union[bytes, str]], now: _d
     engine.scan_keys(d_bytes, d_off, cols)
     ids = np.frombuffer(b"".join(key_bytes(r.msg_id) for r in raws), dtype=np.uint8).reshape(n, 20)
     cols["msg_id"].copy_(torch.from_numpy(ids.copy()).to(dev))
-    engine.join_route(n, now, cols)
+    phone = torch.from_numpy(np.array([phone_datetime(r.date) for r in raws], dtype=np.int64)).to(dev)
+    engine.set_phone_dates(phone)
+    try:
+        engine.join_route(n, now, cols)
+    finally:
+        engine.set_phone_dates(None)
     engine.dedup(n, base_index, cols)
     torch.cuda.synchronize(dev)
     host = {k: v.cpu().numpy() for k, v in cols.items()}
     res = ReplayResult(batch, host, engine.table, base_index)
-    # libs/gemini_parser.py:228-229: a cached date without any date text falls back to the phone's timestamp,
-    # int(raw.date).  For XML-sourced messages that raises (ISO text); for a numeric date it would not:
-    # those rows are listed, not evaluated.
-    needs = []
-    if engine.table is not None:
-        for r in range(n):
-            e = int(host["slot"][r])
-            # (an XML-sourced message with such an entry ends as UNMATCHED: int() of its ISO date raises
-            # inside the try of gemini_parser.py:224-241)
-            if e >= 0 and int(host["status"][r]) == L.ST_UNMATCHED and not (int(host["flags"][r]) & L.F_PARSER_OTP):
-                f = int(engine.table.eflags[e])
-                no_date = (f & L.E_DATE_KEY) and not (f & (L.E_DATE_STRICT | L.E_DATE_HOST | L.E_DATE_NOBODY))
-                if no_date and _intable(raws[r].date):
-                    needs.append(r)
-    return DlqResult(outcomes, errors, row, raws, res, needs)
+    res.phone_dates = phone.cpu().numpy()
+    return res
 
 
-def _intable(s: Any) -> bool:
-    try:
-        int(s)
-        return True
-    except Exception:
-        return False
+def reparse(engine: ReplayEngine, payloads: Sequence[Union[bytes, str]], now: _dt.datetime,
+            base_index: int = 0) -> DlqResult:
+    """Re-parse a dump of `sms.failed` in one pass.  The response cache must be loaded
+    (`engine.load_cache`).  What the reference does with each payload before the replay proper is decided
+    per payload on the host (`unwrap`); the replayed rows go through `replay_raws`."""
+    outcomes, errors, raws = [], [], []
+    row = np.full(len(payloads), -1, dtype=np.int64)
+    for i, p in enumerate(payloads):
+        o, raw, err = unwrap(p)
+        outcomes.append(o)
+        errors.append(err)
+        if raw is not None:
+            row[i] = len(raws)
+            raws.append(raw)
+    if not raws:
+        return DlqResult(outcomes, errors, row, raws, None)
+    return DlqResult(outcomes, errors, row, raws, replay_raws(engine, raws, now, base_index))

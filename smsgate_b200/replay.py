@@ -194,8 +194,8 @@ class ReplayResult:
         return self
 
     def status_counts(self) -> dict:
-        c = np.bincount(self.cols["status"], minlength=8)
-        return {L.STATUS_NAMES[k]: int(c[k]) for k in range(8)}
+        c = np.bincount(self.cols["status"], minlength=9)
+        return {L.STATUS_NAMES[k]: int(c[k]) for k in range(9)}
 
     def dlq_indices(self) -> np.ndarray:
         """Messages the reference would publish to sms.failed (libs/nats_utils.py:28)."""
@@ -381,6 +381,12 @@ class ReplayEngine:
     def set_stream(self, stream) -> None:
         """Queue this engine's work on another torch stream from now on (smsgate_set_stream)."""
         L.check(self._ctx, self._lib.smsgate_set_stream(self._ctx, C.c_void_p(stream.cuda_stream)))
+
+    def set_phone_dates(self, d_phone_dt) -> None:
+        """Per-message phone timestamps (int64 device tensor, packed datetimes, 0 = none) for the next
+        join_route calls; None resets (smsgate_set_phone_dates)."""
+        self._phone_keepalive = d_phone_dt
+        L.check(self._ctx, self._lib.smsgate_set_phone_dates(self._ctx, d_phone_dt.data_ptr() if d_phone_dt is not None else None))
 
     def set_scan_ctas(self, ctas: int) -> None:
         L.check(self._ctx, self._lib.smsgate_set_scan_ctas(self._ctx, int(ctas)))

@@ -38,32 +38,64 @@ def test_reparse_matches_oracle(engine):
     assert list(got.row) == rows
     assert [r.model_dump() for r in got.raws] == [r.model_dump() for r in raws]
     res = got.result
-    skip = set(got.needs_phone_timestamp)
-    assert skip == {rows[victim]}                    # numeric date + dateless cache entry: listed, not evaluated
+    # the row with a numeric date and a dateless cache entry takes the phone's timestamp (gemini_parser.py:227-229)
+    assert outs[rows[victim]].status == O.ST_UPSERT and int(res.phone_dates[rows[victim]]) > 0
     for r, o in enumerate(outs):
-        if r in skip:
-            assert o.status == O.ST_UPSERT and int(res.status[r]) == L.ST_UNMATCHED
-            continue
         assert int(res.status[r]) == o.status, r
         assert res.cache_key_hex(r) == o.cache_key.hex()
-        if o.parsed is not None and o.status != O.ST_FAILED_EXC:
+        if o.parsed is not None and o.status not in (O.ST_FAILED_EXC, O.ST_ESCAPED):
             p = got.parsed(r)
             assert p.msg_id == raws[r].msg_id and p.device_id == raws[r].device_id and p.sender == raws[r].sender
             assert p.date == o.parsed.date and p.amount == o.parsed.amount and p.raw_body == o.parsed.raw_body
-    # dedup by the messages' own ids: the verdicts of every row not touched by the skipped one
-    ids = [r.msg_id for r in raws]
-    touched = {ids[r] for r in skip}
+    # dedup by the messages' own ids
     for r in range(len(raws)):
-        if ids[r] in touched:
-            continue
         assert bool(res.survivor[r]) == surv[r], r
         assert bool(res.first_seen[r]) == first[r], r
         assert int(res.last_idx[r]) == last[r], r
-    assert sum(surv) > 50 and len(set(ids)) < len(ids)
-    ups = got.upserts()
-    assert all(k in set(ids) for k in ups)
 
 
-def test_reparse_nothing_to_do(engine):
-    got = dlq.reparse(engine, [b"junk", json.dumps({"err": "x", "entry": "y"}).encode()], NOW)
-    assert got.outcomes == [dlq.NOT_JSON, dlq.NO_RAW] and got.result is None and got.upserts() == {}
+def test_flows_match_a_run_of_the_reference_handlers(engine):
+    """tests/golden/worker_flow.json holds what the reference's own `_process_one` and `_handle_dlq_msg`
+    did with every message (acks, publishes with their payload bytes, counters, escaped exceptions).  The
+    GPU replay must report the matching status for each, and hand back byte-identical sms.parsed /
+    sms.failed payloads."""
+    from smsgate_b200.models import RawSMS
+    from tests import _flow as F
+    g, bodies, senders = F.load()
+    now = dt.datetime.fromisoformat(g["now"])
+    engine.load_cache(g["cache"])
+    # the live path: one RawSMS per message
+    rows_w = g["flows"]["worker"]
+    raws = [RawSMS(**json.loads(bytes.fromhex(r["payload_hex"]))) for r in rows_w]
+    res = dlq.replay_raws(engine, raws, now)
+    seen = set()
+    for i, row in enumerate(rows_w):
+        want = F.status_of(row, g["offline_error"])
+        assert int(res.status[i]) == want, (i, raws[i].body[:50])
+        seen.add(want)
+        pj = None
+        if want in (F.UPSERT, F.NO_MERCHANT):
+            pj = res.parsed(i, sender=raws[i].sender, device_id=raws[i].device_id, msg_id=raws[i].msg_id).model_dump_json()
+        F.check_published(row, want, pj, raws[i].model_dump())
+    assert seen == set(range(9))
+    # the dead-letter path
+    rows_d = g["flows"]["dlq"]
+    got = dlq.reparse(engine, [bytes.fromhex(r["payload_hex"]) for r in rows_d], now)
+    for i, row in enumerate(rows_d):
+        o = got.outcomes[i]
+        nothing = not row["published"] and row["counters"] == [0, 0, 0]
+        if o in (dlq.NOT_JSON, dlq.NO_RAW):
+            assert nothing and row["acks"] == 1 and row["escaped"] is None, i
+        elif o == dlq.NOT_AN_OBJECT:
+            assert nothing and row["acks"] == 0 and row["escaped"] == "AttributeError", i
+        elif o == dlq.INVALID_RAW:
+            assert nothing and row["acks"] == 0 and row["escaped"] is None, i
+        else:
+            r = int(got.row[i])
+            st = int(got.result.status[r])
+            if st in L.HANDLER_RAISES:
+                assert nothing and row["acks"] == 0 and row["escaped"] is None, i
+            else:
+                assert st == F.status_of(row, g["offline_error"]), i
+                pj = got.parsed(r).model_dump_json() if st in (F.UPSERT, F.NO_MERCHANT) else None
+                F.check_published(row, st, pj, got.raws[r].model_dump())

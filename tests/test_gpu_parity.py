@@ -69,7 +69,7 @@ def test_parse_matrix_golden(engine, golden):
         p = c["parsed"]
         if p is None:
             continue
-        if c["status"] == "FAILED_EXC":
+        if c["status"] in ("FAILED_EXC", "ESCAPED"):
             continue
         big = any(int(p[w][1]) > O.INT64_MAX for w in ("amount", "balance"))
         if big:
@@ -143,7 +143,7 @@ def _compare_with_oracle(res, backup, now):
                     assert ((fl >> sg) & 1, int(res.cols[w + "_coef"][i]), int(res.cols[w + "_exp"][i])) == want[1:]
             assert (bool(fl & 0x40), int(res.amount_cents[i])) == o.amount_cents, i
             assert (bool(fl & 0x80), int(res.balance_cents[i])) == o.balance_cents, i
-        if o.parsed is not None and o.status != O.ST_FAILED_EXC:
+        if o.parsed is not None and o.status not in (O.ST_FAILED_EXC, O.ST_ESCAPED):
             assert int(res.date[i]) == O.pack_datetime(o.parsed.date), i
             assert res.fixed_body(i) == o.fixed
             assert res.cols["card"][i, :int(res.card_len[i])].tobytes().decode() == o.parsed.card

@@ -9,7 +9,7 @@ from oracle import replay_oracle as O
 STATUS = {"UPSERT": O.ST_UPSERT, "PARSED_NO_MERCHANT": O.ST_PARSED_NO_MERCHANT,
           "SKIPPED_FILTER": O.ST_SKIPPED_FILTER, "CACHE_MISS": O.ST_CACHE_MISS,
           "UNMATCHED": O.ST_UNMATCHED, "BROKEN": O.ST_BROKEN, "FUTURE_DATE": O.ST_FUTURE_DATE,
-          "FAILED_EXC": O.ST_FAILED_EXC}
+          "FAILED_EXC": O.ST_FAILED_EXC, "ESCAPED": O.ST_ESCAPED}
 
 
 def _dec(d):
