@@ -207,6 +207,14 @@ int smsgate_xml_scan(smsgate_ctx* ctx, const uint8_t* h_xml, int64_t nbytes, int
 int smsgate_xml_emit(smsgate_ctx* ctx, uint8_t* d_body_bytes, int64_t* d_body_offsets, uint8_t* d_sender_bytes,
                      int64_t* d_sender_offsets, int64_t* d_date_ms, uint8_t* d_mflags);
 int smsgate_xml_release(smsgate_ctx* ctx);
+/* Between smsgate_xml_scan and smsgate_xml_emit / _release: EVERY attribute of every top-level <sms>, names as
+ * written and values decoded like the ones above - what `elem.attrib` holds in read_xml.parse_and_cache_sms
+ * (read_xml.py:32-41).  _attrs_sizes reports the totals; _attrs_emit fills caller-owned device buffers:
+ * attr_offsets[n+1] (message i owns attributes attr_offsets[i] .. attr_offsets[i+1], in document order),
+ * name_offsets[A+1] + name_bytes, value_offsets[A+1] + value_bytes.  Allocates temporaries in the context. */
+int smsgate_xml_attrs_sizes(smsgate_ctx* ctx, int64_t* n_attrs, int64_t* name_bytes, int64_t* value_bytes);
+int smsgate_xml_attrs_emit(smsgate_ctx* ctx, int64_t* d_attr_offsets, int64_t* d_name_offsets, uint8_t* d_name_bytes,
+                           int64_t* d_value_offsets, uint8_t* d_value_bytes);
 
 /* ---- the legacy offline replay (host buffers in and out) --------------------
  * process_cached.process_sms_from_cache (process_cached.py:210-268) for n source-cache

@@ -110,6 +110,8 @@ def lib():
         "smsgate_xml_scan": (i32, [vp, vp, i64, vp, vp, vp, vp]),
         "smsgate_xml_emit": (i32, [vp, vp, vp, vp, vp, vp, vp]),
         "smsgate_xml_release": (i32, [vp]),
+        "smsgate_xml_attrs_sizes": (i32, [vp, vp, vp, vp]),
+        "smsgate_xml_attrs_emit": (i32, [vp, vp, vp, vp, vp, vp]),
         "smsgate_legacy_parse": (i32, [vp, i64, vp, vp, C.POINTER(LegacyOutputs)]),
         "smsgate_legacy_parse_mode": (i32, [vp, i64, vp, vp, C.c_uint32, C.POINTER(LegacyOutputs)]),
         "smsgate_scan_keys": (i32, [vp, vp, vp, i64, C.POINTER(Outputs)]),

@@ -742,6 +742,9 @@ struct smsgate_ctx {
             *xml_date_ms = nullptr;
     int32_t *xml_name_off = nullptr, *xml_name_len = nullptr;
     uint8_t *xml_kind = nullptr, *xml_mflags = nullptr;
+    uint8_t* xml_attr_slab = nullptr;        // smsgate_xml_attrs_sizes .. _emit: per-message attribute offsets
+    int64_t *xml_attr_off = nullptr, *xml_attr_nbase = nullptr, *xml_attr_vbase = nullptr;
+    int64_t xml_attr_total = -1;
     int sm_count = 148;
     int scan_ctas = 0;                       // CTAs of k_scan_keys, 0 = one per SM (smsgate_set_scan_ctas)
     const int64_t* phone_dt = nullptr;       // per-message phone timestamps for the next join (smsgate_set_phone_dates)
@@ -1206,7 +1209,10 @@ extern "C" int smsgate_xml_release(smsgate_ctx* ctx) {
         cudaStreamSynchronize(ctx->stream);
         cudaFree(ctx->xml_slab);
         cudaFree((void*)ctx->xml_x);
+        cudaFree(ctx->xml_attr_slab);
     }
+    ctx->xml_attr_slab = nullptr;
+    ctx->xml_attr_total = -1;
     ctx->xml_slab = nullptr;
     ctx->xml_x = nullptr;
     ctx->xml_n = ctx->xml_T = ctx->xml_nx = 0;
@@ -1379,6 +1385,72 @@ extern "C" int smsgate_xml_emit(smsgate_ctx* ctx, uint8_t* d_body_bytes, int64_t
     CUDA_TRY(ctx, cudaStreamSynchronize(st));
     CUDA_TRY(ctx, cudaGetLastError());
     return smsgate_xml_release(ctx);
+}
+
+extern "C" int smsgate_xml_attrs_sizes(smsgate_ctx* ctx, int64_t* n_attrs, int64_t* name_bytes, int64_t* value_bytes) {
+    if (!ctx) return SMSGATE_E_ARG;
+    if (!n_attrs || !name_bytes || !value_bytes) return fail(ctx, SMSGATE_E_ARG, "xml_attrs_sizes: NULL argument");
+    if (!ctx->xml_slab) return fail(ctx, SMSGATE_E_STATE, "xml_attrs_sizes: no pending smsgate_xml_scan");
+    *n_attrs = *name_bytes = *value_bytes = 0;
+    const int64_t n = ctx->xml_n;
+    ctx->xml_attr_total = 0;
+    if (n == 0) return SMSGATE_OK;
+    CUDA_TRY(ctx, cudaSetDevice(ctx->device));
+    cudaStream_t st = ctx->stream;
+    cudaFree(ctx->xml_attr_slab);
+    ctx->xml_attr_slab = nullptr;
+    auto al = [](size_t b) { return (b + 255) & ~(size_t)255; };
+    const size_t need = al((n + 1) * 4) * 3 + al((n + 1) * 8) * 3 + al((size_t)(n / SCAN_ITEMS + 1024) * 8);
+    CUDA_TRY(ctx, cudaMalloc(&ctx->xml_attr_slab, need));
+    uint8_t* q = ctx->xml_attr_slab;
+    auto take = [&](size_t b) { uint8_t* r = q; q += al(b); return r; };
+    int32_t* cnt = (int32_t*)take((n + 1) * 4);
+    int32_t* nb = (int32_t*)take((n + 1) * 4);
+    int32_t* vb = (int32_t*)take((n + 1) * 4);
+    ctx->xml_attr_off = (int64_t*)take((n + 1) * 8);
+    ctx->xml_attr_nbase = (int64_t*)take((n + 1) * 8);
+    ctx->xml_attr_vbase = (int64_t*)take((n + 1) * 8);
+    int64_t* tmp = (int64_t*)take((size_t)(n / SCAN_ITEMS + 1024) * 8);
+    XmlTags K{ctx->xml_tag_pos, ctx->xml_end, ctx->xml_name_off, ctx->xml_name_len, ctx->xml_kind, nullptr, nullptr, nullptr};
+    k_xml_attr_sizes<<<(unsigned)((n + 127) / 128), 128, 0, st>>>(ctx->xml_x, n, ctx->xml_sms_tag, K, cnt, nb, vb);
+    xml_scan_i32(st, cnt, n, tmp, ctx->xml_attr_off);
+    xml_scan_i32(st, nb, n, tmp, ctx->xml_attr_nbase);
+    xml_scan_i32(st, vb, n, tmp, ctx->xml_attr_vbase);
+    ctx->launches += 10;
+    int64_t tot[3] = {0, 0, 0};
+    CUDA_TRY(ctx, cudaMemcpyAsync(&tot[0], ctx->xml_attr_off + n, 8, cudaMemcpyDeviceToHost, st));
+    CUDA_TRY(ctx, cudaMemcpyAsync(&tot[1], ctx->xml_attr_nbase + n, 8, cudaMemcpyDeviceToHost, st));
+    CUDA_TRY(ctx, cudaMemcpyAsync(&tot[2], ctx->xml_attr_vbase + n, 8, cudaMemcpyDeviceToHost, st));
+    CUDA_TRY(ctx, cudaStreamSynchronize(st));
+    CUDA_TRY(ctx, cudaGetLastError());
+    ctx->xml_attr_total = tot[0];
+    *n_attrs = tot[0]; *name_bytes = tot[1]; *value_bytes = tot[2];
+    return SMSGATE_OK;
+}
+
+extern "C" int smsgate_xml_attrs_emit(smsgate_ctx* ctx, int64_t* d_attr_offsets, int64_t* d_name_offsets, uint8_t* d_name_bytes,
+                                      int64_t* d_value_offsets, uint8_t* d_value_bytes) {
+    if (!ctx) return SMSGATE_E_ARG;
+    if (!ctx->xml_slab || ctx->xml_attr_total < 0) return fail(ctx, SMSGATE_E_STATE, "xml_attrs_emit: call smsgate_xml_attrs_sizes first");
+    if (!d_attr_offsets || !d_name_offsets || !d_value_offsets) return fail(ctx, SMSGATE_E_ARG, "xml_attrs_emit: NULL array");
+    const int64_t n = ctx->xml_n;
+    CUDA_TRY(ctx, cudaSetDevice(ctx->device));
+    cudaStream_t st = ctx->stream;
+    if (n == 0) {
+        CUDA_TRY(ctx, cudaMemsetAsync(d_attr_offsets, 0, 8, st));
+        CUDA_TRY(ctx, cudaMemsetAsync(d_name_offsets, 0, 8, st));
+        CUDA_TRY(ctx, cudaMemsetAsync(d_value_offsets, 0, 8, st));
+    } else {
+        XmlTags K{ctx->xml_tag_pos, ctx->xml_end, ctx->xml_name_off, ctx->xml_name_len, ctx->xml_kind, nullptr, nullptr, nullptr};
+        k_xml_attr_emit<<<(unsigned)((n + 127) / 128), 128, 0, st>>>(ctx->xml_x, n, ctx->xml_sms_tag, K, ctx->xml_attr_off,
+                                                                     ctx->xml_attr_nbase, ctx->xml_attr_vbase, d_name_offsets,
+                                                                     d_name_bytes, d_value_offsets, d_value_bytes);
+        ctx->launches += 1;
+        CUDA_TRY(ctx, cudaMemcpyAsync(d_attr_offsets, ctx->xml_attr_off, (size_t)(n + 1) * 8, cudaMemcpyDeviceToDevice, st));
+    }
+    CUDA_TRY(ctx, cudaStreamSynchronize(st));
+    CUDA_TRY(ctx, cudaGetLastError());
+    return SMSGATE_OK;
 }
 
 // ---- stages

@@ -271,3 +271,58 @@ __global__ void __launch_bounds__(128) k_xml_sms_emit(const uint8_t* __restrict_
     if (found & 1) xml_attr_value(x, body.val, lim, body.quote, body_bytes + body_off[i], &l);
     if (found & 4) xml_attr_value(x, addr.val, lim, addr.quote, sender_bytes + sender_off[i], &l);
 }
+
+// ---------------------------------------------------------------- every attribute of every <sms>
+// read_xml.parse_and_cache_sms stores `elem.attrib` - the whole attribute dict of each <sms>
+// (read_xml.py:32-41) - so that path needs all names and decoded values, not only body / address / date.
+// Same two-pass shape as above: per message counts and byte totals, prefix sums, then the emit pass.
+__global__ void __launch_bounds__(128) k_xml_attr_sizes(const uint8_t* __restrict__ x, int64_t n, const int64_t* __restrict__ sms_tag,
+                                                        XmlTags G, int32_t* __restrict__ cnt, int32_t* __restrict__ nbytes,
+                                                        int32_t* __restrict__ vbytes) {
+    const int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const int64_t t = sms_tag[i], pos = G.pos[t], lim = G.end[t] + 1;
+    int64_t p = pos + G.name_off[t] + G.name_len[t];
+    bool first = true;
+    int c = 0;
+    int64_t nb = 0, vb = 0;
+    for (;;) {
+        XmlAttr a;
+        if (xml_next_attr(x, &p, lim, &a, first) <= 0) break;      // the tag was validated by k_xml_parse_tags
+        first = false;
+        int64_t l = 0;
+        xml_attr_value(x, a.val, lim, a.quote, nullptr, &l);
+        ++c;
+        nb += a.name_end - a.name;
+        vb += l;
+    }
+    cnt[i] = c;
+    nbytes[i] = (int32_t)nb;
+    vbytes[i] = (int32_t)vb;
+}
+
+__global__ void __launch_bounds__(128) k_xml_attr_emit(const uint8_t* __restrict__ x, int64_t n, const int64_t* __restrict__ sms_tag,
+                                                       XmlTags G, const int64_t* __restrict__ attr_off,
+                                                       const int64_t* __restrict__ name_base, const int64_t* __restrict__ val_base,
+                                                       int64_t* __restrict__ name_offsets, uint8_t* __restrict__ name_bytes,
+                                                       int64_t* __restrict__ val_offsets, uint8_t* __restrict__ val_bytes) {
+    const int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const int64_t t = sms_tag[i], pos = G.pos[t], lim = G.end[t] + 1;
+    int64_t p = pos + G.name_off[t] + G.name_len[t];
+    bool first = true;
+    int64_t a_idx = attr_off[i], nw = name_base[i], vw = val_base[i];
+    for (;;) {
+        XmlAttr a;
+        if (xml_next_attr(x, &p, lim, &a, first) <= 0) break;
+        first = false;
+        name_offsets[a_idx] = nw;
+        val_offsets[a_idx] = vw;
+        for (int64_t k = a.name; k < a.name_end; ++k) name_bytes[nw++] = x[k];
+        int64_t l = 0;
+        xml_attr_value(x, a.val, lim, a.quote, val_bytes + vw, &l);
+        vw += l;
+        ++a_idx;
+    }
+    if (i == n - 1) { name_offsets[a_idx] = nw; val_offsets[a_idx] = vw; }
+}

@@ -111,11 +111,14 @@ def phone_datetime(raw_date: Any) -> int:
         return 0
 
 
-def replay_raws(engine: ReplayEngine, raws: Sequence[RawSMS], now: _dt.datetime, base_index: int = 0) -> ReplayResult:
+def replay_raws(engine: ReplayEngine, raws: Sequence[RawSMS], now: _dt.datetime, base_index: int = 0,
+                worker_filter: bool = True) -> ReplayResult:
     """Replay messages that bring their own identity (`RawSMS` objects: DLQ entries, device-sourced
     messages): keys + scans of the bodies on the GPU, then the messages' own ids take the place of the
     computed key column, the phone timestamps of numeric `raw.date`s ride along for the cached dates that
-    hold no date text (libs/gemini_parser.py:227-229), then join + routing and the upsert dedup."""
+    hold no date text (libs/gemini_parser.py:227-229), then join + routing and the upsert dedup.
+    `worker_filter=False` leaves the worker's skip filter (worker.py:112-126) out of the routing: what
+    `parse_sms_llm` does when it is called directly."""
     import torch
     batch = Batch.from_strings([r.body for r in raws], [r.sender for r in raws], None)
     n = batch.n
@@ -128,6 +131,8 @@ def replay_raws(engine: ReplayEngine, raws: Sequence[RawSMS], now: _dt.datetime,
     engine.scan_keys(d_bytes, d_off, cols)
     ids = np.frombuffer(b"".join(key_bytes(r.msg_id) for r in raws), dtype=np.uint8).reshape(n, 20)
     cols["msg_id"].copy_(torch.from_numpy(ids.copy()).to(dev))
+    if not worker_filter:
+        cols["flags"].bitwise_and_(0xFF & ~L.F_WORKER_SKIP)
     phone = torch.from_numpy(np.array([phone_datetime(r.date) for r in raws], dtype=np.int64)).to(dev)
     engine.set_phone_dates(phone)
     try:

@@ -68,8 +68,9 @@ class LegacyResult:
         return None
 
 
-def parse_bodies(engine, bodies: Sequence[Optional[str]]) -> LegacyResult:
-    """Run the legacy per-message path on the GPU for a list of bodies (None counts as "")."""
+def parse_bodies(engine, bodies: Sequence[Optional[str]], mode: int = 0) -> LegacyResult:
+    """Run the legacy per-message path on the GPU for a list of bodies (None counts as "").  mode 0 is what
+    process_sms_from_cache does per entry; the LEG_MODE_* bits give the single-message functions."""
     texts = [b or "" for b in bodies]
     data, offsets = ragged_from_strings(texts)
     n = len(texts)
@@ -77,20 +78,33 @@ def parse_bodies(engine, bodies: Sequence[Optional[str]]) -> LegacyResult:
                 caps=np.full((n, 2 * L.LEG_GROUPS), -1, np.int32), amount=np.zeros(n, np.float64),
                 balance=np.zeros(n, np.float64), body_hash=np.zeros((n, 32), np.uint8))
     out = L.LegacyOutputs(**{k: v.ctypes.data for k, v in cols.items()})
-    L.check(engine._ctx, L.lib().smsgate_legacy_parse(engine._ctx, n, offsets.ctypes.data_as(C.c_void_p),
-                                                      data.ctypes.data_as(C.c_void_p) if len(data) else None,
-                                                      C.byref(out)))
+    L.check(engine._ctx, L.lib().smsgate_legacy_parse_mode(engine._ctx, n, offsets.ctypes.data_as(C.c_void_p),
+                                                           data.ctypes.data_as(C.c_void_p) if len(data) else None,
+                                                           int(mode), C.byref(out)))
     return LegacyResult(texts, data, offsets, cols)
+
+
+def parse_one(engine, message: str, credit: bool) -> Optional[Dict[str, Any]]:
+    """parse_transaction_message / parse_credit_message (process_cached.py:150-204) for one message: ONE
+    pattern applied to the message as given - no strip(), no OTP filter, no falling through to the other
+    pattern.  An amount the float conversion cannot carry exactly raises OverflowError (representation
+    limit of the kernel: beyond 2^64 / 22 fraction digits)."""
+    if not message:
+        return None
+    mode = L.LEG_MODE_NO_STRIP | L.LEG_MODE_NO_OTP | (L.LEG_MODE_NO_DEBIT if credit else L.LEG_MODE_NO_CREDIT)
+    res = parse_bodies(engine, [message], mode)
+    want = L.LEG_CREDIT if credit else L.LEG_DEBIT
+    return res.parsed(0) if int(res.cols["status"][0]) == want else None
 
 
 def parse_transaction_message(engine, message: str) -> Optional[Dict[str, Any]]:
     """process_cached.parse_transaction_message (process_cached.py:150-177) for one message."""
-    if not message:
-        return None
-    res = parse_bodies(engine, [message])
-    # the reference applies the pattern to the message as given; the batch call strips first, which only
-    # differs for leading whitespace (the pattern is anchored with ^.*?): replay it unstripped via a guard char
-    return res.parsed(0) if int(res.cols["status"][0]) == L.LEG_DEBIT else None
+    return parse_one(engine, message, credit=False)
+
+
+def parse_credit_message(engine, message: str) -> Optional[Dict[str, Any]]:
+    """process_cached.parse_credit_message (process_cached.py:180-204) for one message."""
+    return parse_one(engine, message, credit=True)
 
 
 def process_sms_from_cache(engine, source_dir: str, purchase_dest_dir: str, credit_dest_dir: str) -> Dict[str, int]:

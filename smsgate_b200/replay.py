@@ -173,7 +173,9 @@ class ReplayResult:
             return None
         e = int(self.cols["slot"][i])
         v = self.table.values[e]
-        if st == L.ST_FAILED_EXC and not (isinstance(v, dict) and "txn_type" in v):
+        if st == L.ST_FAILED_EXC and not isinstance(v, dict):
+            raise TypeError("the cached response is not a mapping")       # resp_data['txn_type'] on a non-dict (:239)
+        if st == L.ST_FAILED_EXC and "txn_type" not in v:
             raise KeyError("txn_type")
         if sender is None:
             sender = self.batch.senders[i] if self.batch.senders is not None else ""
@@ -423,9 +425,11 @@ class ReplayEngine:
             L.check(self._ctx, self._lib.smsgate_replay_host_finish(self._ctx, C.byref(out)))
         return ReplayResult(batch, cols, self.table, base_index)
 
-    def xml_extract(self, data) -> dict:
+    def xml_extract(self, data, attrs: bool = False) -> dict:
         """Tokenize an XML backup (bytes / uint8 array) on the GPU.  Returns device tensors
-        body_bytes, body_offsets, sender_bytes, sender_offsets, date_ms, mflags (+ n).
+        body_bytes, body_offsets, sender_bytes, sender_offsets, date_ms, mflags (+ n); with `attrs`
+        also every attribute of every <sms>: attr_offsets[n+1], name_offsets / name_bytes,
+        value_offsets / value_bytes (smsgate_xml_attrs_sizes / _emit).
         Raises xml.etree.ElementTree.ParseError where ElementTree would, UnsupportedXML for
         constructs outside the dialect."""
         import torch
@@ -447,9 +451,34 @@ class ReplayEngine:
                    sender_offsets=torch.empty(n.value + 1, dtype=torch.int64, device=dev),
                    date_ms=torch.empty(max(n.value, 1), dtype=torch.int64, device=dev),
                    mflags=torch.empty(max(n.value, 1), dtype=torch.uint8, device=dev))
+        if attrs:
+            na, nnb, nvb = C.c_int64(0), C.c_int64(0), C.c_int64(0)
+            L.check(self._ctx, self._lib.smsgate_xml_attrs_sizes(self._ctx, C.byref(na), C.byref(nnb), C.byref(nvb)))
+            out.update(attr_offsets=torch.empty(n.value + 1, dtype=torch.int64, device=dev),
+                       name_offsets=torch.empty(na.value + 1, dtype=torch.int64, device=dev),
+                       name_bytes=torch.empty(nnb.value + 64, dtype=torch.uint8, device=dev),
+                       value_offsets=torch.empty(na.value + 1, dtype=torch.int64, device=dev),
+                       value_bytes=torch.empty(nvb.value + 64, dtype=torch.uint8, device=dev))
+            L.check(self._ctx, self._lib.smsgate_xml_attrs_emit(
+                self._ctx, out["attr_offsets"].data_ptr(), out["name_offsets"].data_ptr(), out["name_bytes"].data_ptr(),
+                out["value_offsets"].data_ptr(), out["value_bytes"].data_ptr()))
         L.check(self._ctx, self._lib.smsgate_xml_emit(self._ctx, out["body_bytes"].data_ptr(), out["body_offsets"].data_ptr(),
                                                       out["sender_bytes"].data_ptr(), out["sender_offsets"].data_ptr(),
                                                       out["date_ms"].data_ptr(), out["mflags"].data_ptr()))
+        return out
+
+    def xml_attribs(self, data) -> list:
+        """`[elem.attrib for elem in root.findall("sms")]` (read_xml.py:32-34) with the file tokenized and
+        every value decoded on the GPU: one dict per top-level <sms>, attributes in document order."""
+        d = self.xml_extract(data, attrs=True)
+        ao = d["attr_offsets"].cpu().numpy()
+        no, vo = d["name_offsets"].cpu().numpy(), d["value_offsets"].cpu().numpy()
+        nb = d["name_bytes"].cpu().numpy().tobytes()
+        vb = d["value_bytes"].cpu().numpy().tobytes()
+        out = []
+        for i in range(d["n"]):
+            out.append({nb[no[a]:no[a + 1]].decode("utf-8"): vb[vo[a]:vo[a + 1]].decode("utf-8")
+                        for a in range(int(ao[i]), int(ao[i + 1]))})
         return out
 
     def msg_ids(self, batch: Batch) -> np.ndarray:

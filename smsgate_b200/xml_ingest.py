@@ -44,6 +44,7 @@ def read_backup_gpu(xml_path: Union[str, Path], engine) -> Batch:
     try:
         d = engine.xml_extract(data)
     except UnsupportedXML:
+        engine.host_fallbacks += 1               # a dialect the tokenizer does not decide: ElementTree, and it is counted
         return read_backup(xml_path)
     n = d["n"]
     off = d["body_offsets"].cpu().numpy()
@@ -80,22 +81,34 @@ def iter_sms(xml_path: Union[str, Path], engine) -> Iterable[RawSMS]:
                      date=iso_utc(int(batch.date_ms[i])), body=batch.body(i))
 
 
-def parse_and_cache_sms(xml_file: str, cache_dir: str) -> Optional[int]:
-    """read_xml.parse_and_cache_sms (read_xml.py:9-54): every top-level <sms> goes into the
-    DiskCache under its `date` attribute (later duplicates overwrite, :41); elements without
-    `date` are skipped (:43-44); a missing or malformed file is reported, not raised (:48-51).
-    Returns the number of stored messages (the reference only prints it)."""
+def parse_and_cache_sms(xml_file: str, cache_dir: str, engine=None) -> Optional[int]:
+    """read_xml.parse_and_cache_sms (read_xml.py:9-54): every top-level <sms> goes into the DiskCache under
+    its `date` attribute with its WHOLE attribute dict as the value (:34-41; later duplicates overwrite);
+    elements without a `date` (or with an empty one) are skipped (:43-44); a missing or malformed file is
+    reported, not raised (:48-51).  The file is tokenized and its attributes decoded on the GPU
+    (ReplayEngine.xml_attribs); the DiskCache writes are host work - storage.  A file in an XML dialect the
+    tokenizer leaves to a general parser goes through ElementTree and is counted in engine.host_fallbacks.
+    Returns the number of stored messages (the reference only prints it), None when nothing was parsed."""
     from diskcache import Cache
+    from .replay import UnsupportedXML
     cache = Cache(cache_dir, fanout_cache=True)               # :19 (the kwarg is stored as a setting, as in the reference)
     stored = None
     try:
-        root = ET.parse(xml_file).getroot()                   # :25-26
+        if engine is None:
+            from .dropin import get_engine
+            engine = get_engine()
+        with open(xml_file, "rb") as f:                        # FileNotFoundError as ET.parse raises it (:25)
+            data = f.read()
+        try:
+            attribs = engine.xml_attribs(np.frombuffer(data, dtype=np.uint8))
+        except UnsupportedXML:
+            engine.host_fallbacks += 1
+            attribs = [elem.attrib for elem in ET.fromstring(data).findall("sms")]
         stored = 0
-        for elem in root.findall("sms"):                      # :32
-            data = elem.attrib                                # :34
-            key = data.get("date")                            # :37
+        for data_dict in attribs:                              # :32
+            key = data_dict.get("date")                        # :37
             if key:
-                cache.set(key, data)                          # :41
+                cache.set(key, data_dict)                      # :41
                 stored += 1
     except FileNotFoundError:
         print(f"XML file not found: {xml_file}")

@@ -96,17 +96,51 @@ def test_iter_sms_golden(engine, golden, tmp_path):
             assert rows == c["rows"], c["name"]
 
 
-def test_parse_and_cache_sms(tmp_path):
+def test_parse_and_cache_sms_matches_reference_run(engine, golden, tmp_path):
+    """tests/golden/read_xml.json: the DiskCache the reference's own read_xml.parse_and_cache_sms left behind
+    for each file (duplicate / missing / empty `date`, reversed attribute order, entities, a malformed file, a
+    missing file, a DOCTYPE the tokenizer hands to ElementTree).  Same keys in the same order, same dicts."""
     import diskcache
-    backup = synth.generate(300, seed=3)
-    xml = tmp_path / "b.xml"
-    synth.write_xml(str(xml), backup)
-    n = xml_ingest.parse_and_cache_sms(str(xml), str(tmp_path / "cache"))
-    assert n == 300
-    with diskcache.Cache(str(tmp_path / "cache")) as c:
-        assert len(c) == 300
-        assert c.get(str(backup.date_ms[7]))["body"] == backup.bodies[7].replace("\n", "\n")
-    assert xml_ingest.parse_and_cache_sms(str(tmp_path / "missing.xml"), str(tmp_path / "c2")) is None
+    fallbacks0 = engine.host_fallbacks
+    for c in golden("read_xml.json"):
+        xml = tmp_path / (c["name"] + ".xml")
+        cdir = tmp_path / (c["name"] + "_cache")
+        if c["xml_hex"] is not None:
+            xml.write_bytes(bytes.fromhex(c["xml_hex"]))
+        n = xml_ingest.parse_and_cache_sms(str(xml), str(cdir), engine)
+        with diskcache.Cache(str(cdir)) as cache:
+            got = [[k, cache[k]] for k in cache]
+        assert got == c["entries"], c["name"]
+        for (_, a), (_, b) in zip(got, c["entries"]):
+            assert list(a) == list(b), c["name"]                     # attribute order inside the stored dict
+        if c["name"] in ("malformed", "missing_file"):
+            assert n is None
+    assert engine.host_fallbacks == fallbacks0 + 1                   # only the DOCTYPE file left the GPU path
+
+
+def test_xml_attribs_on_gpu_match_elementtree(engine):
+    """Every attribute of every top-level <sms> (read_xml.py:34) for the tokenizer's whole document set."""
+    import xml.etree.ElementTree as ET
+
+    from smsgate_b200.replay import UnsupportedXML
+    from tests._xml_cases import documents
+    checked = 0
+    for data in documents():
+        try:
+            want = [dict(e.attrib) for e in ET.fromstring(data).findall("sms")]
+        except Exception:
+            want = None
+        try:
+            got = engine.xml_attribs(np.frombuffer(data, dtype=np.uint8))
+        except UnsupportedXML:
+            continue
+        except ET.ParseError:
+            got = None
+        assert got == want, data[:200]
+        if want:
+            assert [list(d) for d in got] == [list(d) for d in want]
+            checked += 1
+    assert checked > 500
 
 
 def test_xml_tokenizer_on_gpu_matches_elementtree(engine):
