@@ -9,7 +9,8 @@ import ctypes as C
 import os
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "libsmsgate_b200.so")
+# SMSGATE_B200_LIB: another build of the same library (kernel experiments, smsgate_b200.build.build_variant)
+LIB_PATH = os.environ.get("SMSGATE_B200_LIB") or os.path.join(_HERE, "libsmsgate_b200.so")
 
 ABI_VERSION = 2
 

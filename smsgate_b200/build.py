@@ -30,6 +30,23 @@ def _csrc_files() -> list:
            [os.path.join(ROOT, "include", "smsgate_b200.h")]
 
 
+def build_variant(name: str, defines: list) -> str:
+    """Kernel experiments: the same library compiled with extra -D flags into smsgate_b200/variants/lib<name>.so;
+    SMSGATE_B200_LIB=<path> makes _lib load it (scripts/gpu_variants.sh times them side by side)."""
+    out_dir = os.path.join(PKG, "variants")
+    os.makedirs(out_dir, exist_ok=True)
+    out = os.path.join(out_dir, f"lib{name}.so")
+    nvcc = os.environ.get("NVCC", "/usr/local/cuda/bin/nvcc")
+    cmd = [nvcc] + NVCC_FLAGS + [f"-D{d}" for d in defines] + ["-o", out, os.path.join(CSRC, "smsgate_b200.cu")]
+    res = subprocess.run(cmd, capture_output=True, text=True)
+    if res.returncode:
+        sys.stderr.write(res.stdout + res.stderr)
+        raise RuntimeError(f"nvcc failed building variant {name}")
+    with open(os.path.join(out_dir, f"{name}.ptxas.txt"), "w") as f:
+        f.write(res.stderr)
+    return out
+
+
 def build_cuda(force: bool = False, verbose: bool = False) -> str:
     srcs = _csrc_files()
     if force or _stale(LIB, srcs):

@@ -542,6 +542,38 @@ static __constant__ uint32_t c_k256[64] = SG_K256_INIT;   // constant-bank opera
 #define SG_K256 h_k256
 #endif
 
+// Rotations through the FMA pipe (variant SG_SHA256_IMAD): x * 2^(32-n) as a 64-bit product holds x >> n in
+// its high word and x << (32-n) in its low word, and the two are bit-disjoint, so rotr(x, n) = hi ^ lo.  One
+// IMAD.WIDE (fma pipe, otherwise ~8 % busy in this kernel) replaces one SHF (alu pipe, the kernel's limiter);
+// the XORs of the halves fold into 3-input LOP3s.  The multipliers sit in constant memory so that ptxas
+// cannot turn the multiplication back into a shift.
+#if defined(__CUDACC__) && defined(SG_SHA256_IMAD)
+static __constant__ uint32_t c_pow2[33] = {
+    1u << 0, 1u << 1, 1u << 2, 1u << 3, 1u << 4, 1u << 5, 1u << 6, 1u << 7, 1u << 8, 1u << 9, 1u << 10, 1u << 11,
+    1u << 12, 1u << 13, 1u << 14, 1u << 15, 1u << 16, 1u << 17, 1u << 18, 1u << 19, 1u << 20, 1u << 21, 1u << 22,
+    1u << 23, 1u << 24, 1u << 25, 1u << 26, 1u << 27, 1u << 28, 1u << 29, 1u << 30, 1u << 31, 0};
+#endif
+#if defined(__CUDA_ARCH__) && defined(SG_SHA256_IMAD)
+__device__ __forceinline__ uint2 sg_mw(uint32_t x, int n) {          // {x << (32-n), x >> n}
+    unsigned long long p;
+    asm("mul.wide.u32 %0, %1, %2;" : "=l"(p) : "r"(x), "r"(c_pow2[32 - n]));
+    return make_uint2((uint32_t)p, (uint32_t)(p >> 32));
+}
+__device__ __forceinline__ uint32_t sg_big_sigma(uint32_t x, int n0, int n1, int n2) {
+    const uint2 a = sg_mw(x, n0), b = sg_mw(x, n1), c = sg_mw(x, n2);
+    return (a.x ^ a.y ^ b.x) ^ (b.y ^ c.x ^ c.y);
+}
+__device__ __forceinline__ uint32_t sg_small_sigma(uint32_t x, int n0, int n1, int sh) {
+    const uint2 a = sg_mw(x, n0), b = sg_mw(x, n1), c = sg_mw(x, sh);
+    return (a.x ^ a.y ^ b.x) ^ (b.y ^ c.y);
+}
+#define SG_BIG_SIGMA(x, n0, n1, n2) sg_big_sigma(x, n0, n1, n2)
+#define SG_SMALL_SIGMA(x, n0, n1, sh) sg_small_sigma(x, n0, n1, sh)
+#else
+#define SG_BIG_SIGMA(x, n0, n1, n2) (sg_rotr(x, n0) ^ sg_rotr(x, n1) ^ sg_rotr(x, n2))
+#define SG_SMALL_SIGMA(x, n0, n1, sh) (sg_rotr(x, n0) ^ sg_rotr(x, n1) ^ ((x) >> (sh)))
+#endif
+
 SG_HD void sg_sha256_compress(uint32_t h[8], uint32_t w[16]) {
     // 4 x 16 rounds: the 16-round body is unrolled (static schedule indices), the outer loop is not,
     // which keeps the kernel's instruction footprint inside the instruction cache
@@ -554,14 +586,14 @@ SG_HD void sg_sha256_compress(uint32_t h[8], uint32_t w[16]) {
             if (r == 0) wi = w[j];
             else {
                 const uint32_t w15 = w[(j + 1) & 15], w2 = w[(j + 14) & 15];
-                const uint32_t s0 = sg_rotr(w15, 7) ^ sg_rotr(w15, 18) ^ (w15 >> 3);
-                const uint32_t s1 = sg_rotr(w2, 17) ^ sg_rotr(w2, 19) ^ (w2 >> 10);
+                const uint32_t s0 = SG_SMALL_SIGMA(w15, 7, 18, 3);
+                const uint32_t s1 = SG_SMALL_SIGMA(w2, 17, 19, 10);
                 wi = w[j] + s0 + w[(j + 9) & 15] + s1;
                 w[j] = wi;
             }
-            const uint32_t S1 = sg_rotr(e, 6) ^ sg_rotr(e, 11) ^ sg_rotr(e, 25);
+            const uint32_t S1 = SG_BIG_SIGMA(e, 6, 11, 25);
             const uint32_t ch = (e & f) ^ (~e & g);
-            const uint32_t S0 = sg_rotr(a, 2) ^ sg_rotr(a, 13) ^ sg_rotr(a, 22);
+            const uint32_t S0 = SG_BIG_SIGMA(a, 2, 13, 22);
             const uint32_t mj = (a & b) ^ (a & c) ^ (b & c);
             const uint32_t t1 = hh + S1 + ch + SG_K256[r + j] + wi;
             const uint32_t t2 = S0 + mj;

@@ -64,7 +64,10 @@ __device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
 #define K1_THREADS_N 640
 #endif
 constexpr int K1_THREADS = K1_THREADS_N;   // 20 warps: one CTA per SM
-constexpr int K1_CTAS_PER_SM = 1;
+#ifndef K1_CTAS_PER_SM_N
+#define K1_CTAS_PER_SM_N 1
+#endif
+constexpr int K1_CTAS_PER_SM = K1_CTAS_PER_SM_N;
 constexpr int K1_TILE = 2 * K1_THREADS;      // messages per tile: every thread owns one short and one long body
 #ifndef K1_STAGE_KB
 #define K1_STAGE_KB 176
@@ -93,6 +96,7 @@ struct __align__(16) K1Smem {
     uint16_t rlist[K1_TILE];              // bodies the first pass flagged and clean/mask leaves alone: filter re-scan
     int32_t pcnt[2 * K1_THREADS / 32];    // per warp and half: rewritten | untouched << 16
     int32_t next;                         // next 32-message chunk to hash
+    int32_t next_s;                       // next 32-message chunk to scan
     int32_t nr;                           // entries of rlist
 };
 
@@ -174,7 +178,12 @@ k_scan_keys(const uint8_t* __restrict__ bytes, const int64_t* __restrict__ offse
     // every CTA takes an equal contiguous share of the messages and walks it in equal tiles of at most
     // K1_TILE: all CTAs do the same number of tiles, no tail wave
     const int64_t r0 = n * (int64_t)blockIdx.x / gridDim.x, r1 = n * ((int64_t)blockIdx.x + 1) / gridDim.x;
-    const int64_t nt = (r1 - r0 + K1_TILE - 1) / K1_TILE;
+    // ... of at most K1_TILE messages AND about 90 % of the staging buffer in bytes (long bodies: mixed-locale and
+    // multi-part messages), so that a tile is staged in one piece instead of a full sub-batch plus a sliver
+    const int64_t nt_cnt = (r1 - r0 + K1_TILE - 1) / K1_TILE;
+    const int64_t share_bytes = r1 > r0 ? offsets[r1] - offsets[r0] : 0;
+    const int64_t nt_bytes = (share_bytes + (K1_STAGE / 10) * 9 - 1) / ((K1_STAGE / 10) * 9);
+    const int64_t nt = nt_cnt > nt_bytes ? nt_cnt : nt_bytes;
     const int64_t per = nt ? (r1 - r0 + nt - 1) / nt : 1;
     for (int64_t t0 = r0; t0 < r1; t0 += per) {
         const int64_t t1 = (t0 + per < r1) ? t0 + per : r1;
@@ -199,7 +208,7 @@ k_scan_keys(const uint8_t* __restrict__ bytes, const int64_t* __restrict__ offse
                 nfit += fits[h] ? 1 : 0;
             }
             for (int k = tid; k < K1_BUCKETS; k += K1_THREADS) S.hist[k] = 0;
-            if (tid == 0) { S.next = 0; S.nr = 0; }
+            if (tid == 0) { S.next = 0; S.next_s = 0; S.nr = 0; }
             // the first half is a prefix of the tile, so the count of fitting messages is exact
             // only if the second half is counted after the first: do two block-wide counts
             const int cnt0 = __syncthreads_count(fits[0]);
@@ -269,16 +278,19 @@ k_scan_keys(const uint8_t* __restrict__ bytes, const int64_t* __restrict__ offse
             }
             __syncthreads();
 
-            // ---- phase S: the scans.  Thread `tid` owns rank tid (short half) and rank cnt-1-tid (long half):
-            //      every warp gets one group of short and one group of long bodies.
-            const int half = (cnt + 1) >> 1;
-            int rk[2];
-            rk[0] = tid < half ? tid : -1;
-            rk[1] = tid < cnt - half ? cnt - 1 - tid : -1;
+            // ---- phase S: the scans.  Warps pull 32-message chunks of the length-sorted order, longest first:
+            //      the lanes of a warp walk bodies of about the same length, and a tile that mixes 100-byte and
+            //      1 200-byte bodies still ends with all warps busy (a fixed short+long pairing did not).
+            const int lane = tid & 31, wrp = tid >> 5;
 #pragma unroll 1
-            for (int h = 0; h < 2; ++h) {
-                if (rk[h] < 0) continue;
-                const int t = S.order[rk[h]];
+            for (;;) {
+                int c = 0;
+                if (lane == 0) c = atomicAdd(&S.next_s, 1);
+                c = __shfl_sync(0xffffffffu, c, 0);
+                if (c * 32 >= cnt) break;
+                const int r = cnt - 1 - (c * 32 + lane);
+                if (r < 0) continue;
+                const int t = S.order[r];
                 // first pass (scan_core.cuh): two automata; the few flagged bodies get their filter flags later
                 ScanResult sr = sg_scan_first(S.stage + S.m_off[t], S.m_len[t], T);
                 S.mod[t] = (uint8_t)sr.flags;
@@ -290,7 +302,6 @@ k_scan_keys(const uint8_t* __restrict__ bytes, const int64_t* __restrict__ offse
             // ---- hashing order: the bodies clean/mask changes first (they cost SHA-1 + rewrite + SHA-256 of
             //      the result), then the untouched ones (both digests in one walk), each group longest first,
             //      so that a 32-message chunk is one kind of work and the dearest chunks start first
-            const int lane = tid & 31, wrp = tid >> 5;
             int wt[2];
             uint32_t balM[2], balU[2];
 #pragma unroll
