@@ -164,6 +164,30 @@ def test_numeric_14_2_storage_rounding():
         assert int(jr["amount_cents"][i]) == cents and int(jr["balance_cents"][i]) == cents, t
 
 
+def test_numeric_14_2_against_postgres_documented_cases(golden):
+    """The Numeric(14,2) columns (db/models.py:21,27) against PostgreSQL's documented numeric behaviour
+    (tests/golden/postgres_numeric.json, sources cited there): rounding to the column's scale, ties away from
+    zero, overflow when the rounded value needs more than precision - scale integer digits.  Both the oracle
+    and the device code (compiled for the CPU) must agree with every documented case."""
+    g = golden("postgres_numeric.json")
+    rows = g["ties_away_from_zero"] + g["round_to_scale"] + g["precision"]
+    texts = [r[0] for r in rows]
+    bodies = [f"pg body {i}" for i in range(len(texts))]
+    sc = H.scan(bodies)
+    cache = {sc["cache_key"][i].tobytes().hex(): dict(txn_type="debit", date="06.05.25 14:23", amount="1", currency="usd",
+                                                      card="1234", merchant="M", city=None, address=None, balance=t)
+             for i, t in enumerate(texts)}
+    jr = H.join_route(sc, _table(cache), gemini_cache.pack_datetime(dt.datetime(2026, 1, 1)))
+    for i, (t, sign, want) in enumerate(rows):
+        ov, cents = O.numeric_14_2(t)
+        fl = int(jr["dec_flags"][i])
+        if want == "overflow":
+            assert ov and bool(fl & 0x80), t
+        else:
+            assert (ov, cents) == (False, want), t
+            assert not (fl & 0x80) and int(jr["balance_cents"][i]) == want and ((fl >> 5) & 1) == sign, t
+
+
 def test_scan_fuzz_against_oracle():
     """Adversarial bodies (tests/_fuzz.py): every scan output of the device code equals the oracle's."""
     from tests._fuzz import bodies
