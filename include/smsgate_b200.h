@@ -166,6 +166,31 @@ int64_t smsgate_cache_size(const smsgate_ctx* ctx);
  * (libs/gemini_parser.py:33). */
 int smsgate_cache_share(smsgate_ctx* ctx, const smsgate_ctx* owner);
 
+/* The reference's `.gemini_cache` directory read natively: diskcache 5.6.3's SQLite file and its pickled
+ * response dicts decoded in C++ (smsgate_b200/csrc/cache_reader.h), no Python object per entry.  Replaces
+ * `cache = diskcache.Cache(".gemini_cache")` + the per-message `cache_key in cache` / `cache[cache_key]`
+ * (libs/gemini_parser.py:33, :208-209) by one pass that yields the arrays smsgate_cache_load takes.
+ *   _open   reads <cache_dir>/cache.db (read-only); `now` = time.time() for diskcache's expiry rule
+ *   _sizes  m entries, bytes of the four device strings, bytes of the five host-side strings, keys skipped
+ *           because they are not 64 lower-case hex digits, entries the decoder leaves to the caller
+ *   _fill   keys[m*32], val_offsets[4m+1], val_bytes, eflags[m] (schema facts; date flags are the caller's:
+ *           smsgate_strict_date_entries), rowids[m], needs_host[m] (1 = decode this entry yourself, by rowid;
+ *           2 = only its date needs the reference's strptime/dateutil chain), and for building payloads on
+ *           the host text_offsets[5m+1] + text_bytes + text_kind[5m] = txn_type, currency, merchant, city,
+ *           address (kind: 0 missing, 1 None, 2 str, 3 other).  Any pointer may be NULL.
+ * Host memory only; no GPU involved. */
+typedef struct smsgate_dcache smsgate_dcache;
+int smsgate_dcache_open(const char* cache_dir, double now, smsgate_dcache** out, char* errbuf, int errbuf_len);
+int smsgate_dcache_sizes(const smsgate_dcache* h, int64_t* m, int64_t* value_bytes, int64_t* text_bytes,
+                         int64_t* skipped_keys, int64_t* needs_host);
+int smsgate_dcache_fill(const smsgate_dcache* h, uint8_t* keys, int32_t* val_offsets, uint8_t* val_bytes, uint16_t* eflags,
+                        int64_t* rowids, uint8_t* needs_host, int64_t* text_offsets, uint8_t* text_bytes, uint8_t* text_kind);
+void smsgate_dcache_close(smsgate_dcache* h);
+/* smsgate_strict_date_batch over the date string of every entry in smsgate_cache_load's layout (string 4e+2):
+ * h_packed[e] = packed datetime, or -1 (empty / not in the strict form). */
+int smsgate_strict_date_entries(smsgate_ctx* ctx, int64_t m, const int32_t* h_val_offsets, const uint8_t* h_val_bytes,
+                                int64_t* h_packed);
+
 /* ---- batch helpers (host buffers in and out) ----------------------------- */
 /* libs.decimal_utils.parse_ambiguous_decimal over n strings (libs/decimal_utils.py:4-63).
  * flags[i]: bits 0-1 SMSGATE_DEC_*, bit 4 sign. */

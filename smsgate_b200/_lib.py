@@ -105,6 +105,11 @@ def lib():
         "smsgate_set_stream": (i32, [vp, vp]),
         "smsgate_set_scan_ctas": (i32, [vp, i32]),
         "smsgate_set_phone_dates": (i32, [vp, vp]),
+        "smsgate_dcache_open": (i32, [C.c_char_p, C.c_double, C.POINTER(vp), C.c_char_p, i32]),
+        "smsgate_dcache_sizes": (i32, [vp, vp, vp, vp, vp, vp]),
+        "smsgate_dcache_fill": (i32, [vp, vp, vp, vp, vp, vp, vp, vp, vp, vp]),
+        "smsgate_dcache_close": (None, [vp]),
+        "smsgate_strict_date_entries": (i32, [vp, i64, vp, vp, vp]),
         "smsgate_decimal_batch": (i32, [vp, i64, vp, vp, vp, vp, vp]),
         "smsgate_strict_date_batch": (i32, [vp, i64, vp, vp, vp]),
         "smsgate_dt_str_batch": (i32, [vp, i64, vp, vp, vp]),

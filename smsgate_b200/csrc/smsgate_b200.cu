@@ -702,6 +702,15 @@ k_xsrc_probe(int64_t n_dev, const uint8_t* __restrict__ dev_sha1, const uint8_t*
     match[i] = found;
 }
 
+// the date string of every cache entry (string 4e+2 of the loader's layout) through the strict parser
+__global__ void k_strict_date_entries(int64_t m, const int32_t* __restrict__ val_offsets, const uint8_t* __restrict__ val_bytes,
+                                      int64_t* packed) {
+    const int64_t e = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+    if (e >= m) return;
+    const int32_t a = val_offsets[4 * e + 2], b = val_offsets[4 * e + 3];
+    packed[e] = b > a ? sg_parse_strict_datetime(val_bytes + a, b - a) : -1;
+}
+
 __global__ void k_dt_str_batch(int64_t n, const int32_t* __restrict__ offsets, const uint8_t* __restrict__ bytes,
                                const DeviceTables* __restrict__ tab, int64_t* packed) {
     const int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
@@ -824,6 +833,59 @@ static uint64_t pow2_at_least(uint64_t x) {
 }
 
 #include "xml_extract.cuh"
+#include "cache_reader.h"
+
+// ---- the on-disk response cache, read natively (cache_reader.h)
+struct smsgate_dcache {
+    sgcache::Table T;
+};
+extern "C" int smsgate_dcache_open(const char* cache_dir, double now, smsgate_dcache** out, char* errbuf, int errbuf_len) {
+    if (!cache_dir || !out) return SMSGATE_E_ARG;
+    *out = nullptr;
+    smsgate_dcache* h = new (std::nothrow) smsgate_dcache();
+    if (!h) return SMSGATE_E_NOMEM;
+    bool ok = false;
+    try {
+        ok = sgcache::read_diskcache(cache_dir, now, &h->T);
+    } catch (const std::bad_alloc&) {
+        h->T.err = "out of host memory";
+    }
+    if (!ok) {
+        if (errbuf && errbuf_len > 0) snprintf(errbuf, (size_t)errbuf_len, "%s", h->T.err.c_str());
+        delete h;
+        return SMSGATE_E_STATE;
+    }
+    *out = h;
+    return SMSGATE_OK;
+}
+extern "C" int smsgate_dcache_sizes(const smsgate_dcache* h, int64_t* m, int64_t* value_bytes, int64_t* text_bytes,
+                                    int64_t* skipped_keys, int64_t* needs_host) {
+    if (!h) return SMSGATE_E_ARG;
+    if (m) *m = h->T.m;
+    if (value_bytes) *value_bytes = (int64_t)h->T.val_bytes.size();
+    if (text_bytes) *text_bytes = (int64_t)h->T.text_bytes.size();
+    if (skipped_keys) *skipped_keys = h->T.skipped;
+    if (needs_host) *needs_host = h->T.fallbacks;
+    return SMSGATE_OK;
+}
+extern "C" int smsgate_dcache_fill(const smsgate_dcache* h, uint8_t* keys, int32_t* val_offsets, uint8_t* val_bytes,
+                                   uint16_t* eflags, int64_t* rowids, uint8_t* needs_host, int64_t* text_offsets,
+                                   uint8_t* text_bytes, uint8_t* text_kind) {
+    if (!h) return SMSGATE_E_ARG;
+    const sgcache::Table& T = h->T;
+    if (T.val_bytes.size() >= 0x7fffffffull) return SMSGATE_E_LIMIT;       // int32 offsets, as smsgate_cache_load takes them
+    if (keys && T.m) memcpy(keys, T.keys.data(), T.keys.size());
+    if (val_offsets) for (size_t k = 0; k < T.val_offsets.size(); ++k) val_offsets[k] = (int32_t)T.val_offsets[k];
+    if (val_bytes && !T.val_bytes.empty()) memcpy(val_bytes, T.val_bytes.data(), T.val_bytes.size());
+    if (eflags && T.m) memcpy(eflags, T.eflags.data(), T.eflags.size() * 2);
+    if (rowids && T.m) memcpy(rowids, T.rowids.data(), T.rowids.size() * 8);
+    if (needs_host && T.m) memcpy(needs_host, T.needs_host.data(), T.needs_host.size());
+    if (text_offsets) memcpy(text_offsets, T.text_offsets.data(), T.text_offsets.size() * 8);
+    if (text_bytes && !T.text_bytes.empty()) memcpy(text_bytes, T.text_bytes.data(), T.text_bytes.size());
+    if (text_kind && T.m) memcpy(text_kind, T.text_kind.data(), T.text_kind.size());
+    return SMSGATE_OK;
+}
+extern "C" void smsgate_dcache_close(smsgate_dcache* h) { delete h; }
 
 extern "C" int smsgate_abi_version(void) { return SMSGATE_ABI_VERSION; }
 
@@ -1112,6 +1174,32 @@ extern "C" int smsgate_strict_date_batch(smsgate_ctx* ctx, int64_t n, const int3
     k_strict_date_batch<<<(unsigned)((n + 255) / 256), 256, 0, st>>>(n, d_off, d_b, d_p);
     ctx->launches += 1;
     HB_TRY(cudaMemcpyAsync(h_packed, d_p, (size_t)n * 8, cudaMemcpyDeviceToHost, st));
+    HB_TRY(cudaStreamSynchronize(st));
+    HB_TRY(cudaGetLastError());
+done:
+    cudaFree(d_off); cudaFree(d_b); cudaFree(d_p);
+    return rc;
+}
+
+extern "C" int smsgate_strict_date_entries(smsgate_ctx* ctx, int64_t m, const int32_t* h_val_offsets, const uint8_t* h_val_bytes,
+                                           int64_t* h_packed) {
+    if (!ctx) return SMSGATE_E_ARG;
+    if (m < 0 || (m > 0 && (!h_val_offsets || !h_packed))) return fail(ctx, SMSGATE_E_ARG, "strict_date_entries: NULL array");
+    if (m == 0) return SMSGATE_OK;
+    CUDA_TRY(ctx, cudaSetDevice(ctx->device));
+    const int64_t nb = h_val_offsets[4 * m];
+    int32_t* d_off = nullptr; uint8_t* d_b = nullptr; int64_t* d_p = nullptr;
+    cudaStream_t st = ctx->stream;
+    int rc = SMSGATE_OK;
+    cudaError_t e;
+    HB_TRY(cudaMalloc(&d_off, (size_t)(4 * m + 1) * 4));
+    HB_TRY(cudaMalloc(&d_b, (size_t)nb + 16));
+    HB_TRY(cudaMalloc(&d_p, (size_t)m * 8));
+    HB_TRY(cudaMemcpyAsync(d_off, h_val_offsets, (size_t)(4 * m + 1) * 4, cudaMemcpyHostToDevice, st));
+    if (nb) HB_TRY(cudaMemcpyAsync(d_b, h_val_bytes, (size_t)nb, cudaMemcpyHostToDevice, st));
+    k_strict_date_entries<<<(unsigned)((m + 255) / 256), 256, 0, st>>>(m, d_off, d_b, d_p);
+    ctx->launches += 1;
+    HB_TRY(cudaMemcpyAsync(h_packed, d_p, (size_t)m * 8, cudaMemcpyDeviceToHost, st));
     HB_TRY(cudaStreamSynchronize(st));
     HB_TRY(cudaGetLastError());
 done:

@@ -231,3 +231,145 @@ def read_diskcache_sqlite(path: str, now: Optional[float] = None) -> dict:
             with open(os.path.join(path, filename), "r", encoding="UTF-8") as f:
                 out[key] = f.read()
     return out
+
+
+# --------------------------------------------------------------------------- native loader
+class LazyValues:
+    """`CacheTable.values` of a natively loaded cache: the response dict of entry e, unpickled from
+    `cache.db` by rowid only when somebody materialises a ParsedSMS from it (libs/gemini_parser.py:249-266
+    needs currency / merchant / city / address, which never travel to the GPU)."""
+
+    def __init__(self, path: str, rowids: np.ndarray):
+        self.path = path
+        self.rowids = rowids
+        self._con = None
+        self._memo: dict = {}
+
+    def __len__(self) -> int:
+        return len(self.rowids)
+
+    def _fetch(self, e: int):
+        import os
+        import pickle
+        import sqlite3
+        if self._con is None:
+            self._con = sqlite3.connect(f"file:{os.path.join(self.path, 'cache.db')}?mode=ro", uri=True, timeout=60)
+        mode, filename, value = self._con.execute("SELECT mode, filename, value FROM Cache WHERE rowid = ?",
+                                                  (int(self.rowids[e]),)).fetchone()
+        if mode == _MODE_PICKLE and filename is None:
+            return pickle.loads(value)
+        if mode == _MODE_RAW:
+            return bytes(value) if isinstance(value, (bytes, memoryview)) else value
+        with open(os.path.join(self.path, filename), "rb" if mode != _MODE_TEXT else "r",
+                  **({} if mode != _MODE_TEXT else {"encoding": "UTF-8"})) as f:
+            return pickle.load(f) if mode == _MODE_PICKLE else f.read()
+
+    def __getitem__(self, e: int):
+        e = int(e)
+        if e not in self._memo:
+            if len(self._memo) > 65536:
+                self._memo.clear()
+            self._memo[e] = self._fetch(e)
+        return self._memo[e]
+
+
+def read_diskcache_native(path: str, engine, now: Optional[float] = None) -> CacheTable:
+    """The whole `.gemini_cache` as a CacheTable WITHOUT a Python object per entry: the C++ reader
+    (smsgate_dcache_*, csrc/cache_reader.h) walks diskcache's SQLite file and decodes the pickled response
+    dicts into the flat arrays; the date strings are classified on the GPU (smsgate_strict_date_entries).
+    Only what the decoder declines - values kept in side files, float amounts, nested containers, dates the
+    strict parser does not take - goes through the per-entry Python code of `build_table`, and is counted in
+    `table.host_decoded`."""
+    import ctypes as C
+    import os
+    import time
+    lib = L.lib()
+    if not os.path.exists(os.path.join(path, "cache.db")):
+        raise FileNotFoundError(os.path.join(path, "cache.db"))
+    h = C.c_void_p()
+    err = C.create_string_buffer(512)
+    rc = lib.smsgate_dcache_open(os.fsencode(path), float(time.time() if now is None else now), C.byref(h), err, len(err))
+    if rc != 0:
+        raise L.SmsgateError(rc, err.value.decode("utf-8", "replace"))
+    try:
+        m, vb, tb, skipped, nhost = (C.c_int64(0) for _ in range(5))
+        lib.smsgate_dcache_sizes(h, C.byref(m), C.byref(vb), C.byref(tb), C.byref(skipped), C.byref(nhost))
+        m = m.value
+        keys = np.zeros((m, 32), np.uint8)
+        val_offsets = np.zeros(4 * m + 1, np.int32)
+        val_bytes = np.zeros(vb.value + 16, np.uint8)
+        eflags = np.zeros(m, np.uint16)
+        rowids = np.zeros(m, np.int64)
+        needs_host = np.zeros(m, np.uint8)
+        text_offsets = np.zeros(5 * m + 1, np.int64)
+        text_bytes = np.zeros(tb.value + 16, np.uint8)
+        text_kind = np.zeros(5 * m, np.uint8)
+        p = lambda a: a.ctypes.data_as(C.c_void_p)  # noqa: E731
+        L.check(None, lib.smsgate_dcache_fill(h, p(keys), p(val_offsets), p(val_bytes), p(eflags), p(rowids), p(needs_host),
+                                              p(text_offsets), p(text_bytes), p(text_kind)))
+    finally:
+        lib.smsgate_dcache_close(h)
+    values = LazyValues(path, rowids)
+    date_packed = np.zeros(m, np.int64)
+    host_dates: dict = {}
+    # entries the decoder left to Python entirely: the old per-entry code, spliced into the flat arrays
+    whole = np.nonzero(needs_host == 1)[0]
+    if len(whole):
+        sub = build_table({f"{k:064x}": values[int(e)] for k, e in enumerate(whole)}, engine.strict_date_batch)
+        val_offsets, val_bytes = _splice_values(val_offsets, val_bytes[:vb.value], whole, sub)
+        val_bytes = np.concatenate([val_bytes, np.zeros(16, np.uint8)])
+        for k, e in enumerate(whole):
+            eflags[e] = sub.eflags[k]
+            date_packed[e] = sub.date_packed[k]
+            if k in sub.host_dates:
+                host_dates[int(e)] = sub.host_dates[k]
+    # dates: the strict form on the GPU for every entry at once ...
+    if m:
+        packed = np.zeros(m, np.int64)
+        L.check(engine._ctx, lib.smsgate_strict_date_entries(engine._ctx, m, p(val_offsets), p(val_bytes), p(packed)))
+        native = needs_host != 1
+        strict = native & (packed > 0)
+        eflags[strict] |= L.E_DATE_STRICT
+        date_packed[strict] = packed[strict]
+        # ... and the reference's strptime -> dateutil -> pydantic chain for the rest that carry a date key
+        rest = np.nonzero(native & ~strict & ((eflags & L.E_DATE_KEY) != 0))[0]
+        for e in rest:
+            kind, obj = _host_date(values[int(e)]["date"])
+            eflags[e] |= _apply_host_date(kind, obj, int(e), date_packed, host_dates)
+    else:
+        rest = whole
+    t = CacheTable(keys=keys, val_offsets=val_offsets, val_bytes=val_bytes[:int(val_offsets[-1])].copy(), eflags=eflags,
+                   date_packed=date_packed, values=values, host_dates=host_dates, skipped=int(skipped.value))
+    t.host_decoded = int(len(whole))
+    t.host_dates_resolved = int(len(rest)) if m else 0
+    t.text = (text_offsets, text_bytes[:tb.value], text_kind)
+    return t
+
+
+def _splice_values(val_offsets: np.ndarray, val_bytes: np.ndarray, entries: np.ndarray, sub: CacheTable):
+    """Give the entries `entries` (whose four strings are empty in the native arrays) the strings of the
+    table `sub` built for them: one vectorised rebuild of offsets + bytes."""
+    m = (len(val_offsets) - 1) // 4
+    lens = np.diff(val_offsets.astype(np.int64))
+    sub_lens = np.diff(sub.val_offsets.astype(np.int64))
+    idx = (entries[:, None] * 4 + np.arange(4)[None, :]).ravel()
+    lens[idx] = sub_lens
+    new_off = np.zeros(4 * m + 1, np.int64)
+    np.cumsum(lens, out=new_off[1:])
+    if new_off[-1] >= 2 ** 31:
+        raise ValueError("cache value strings exceed 2 GiB")
+    out = np.zeros(int(new_off[-1]), np.uint8)
+    # native strings: copy run by run between the spliced entries (entries are few)
+    src = 0
+    prev = 0
+    for k, e in enumerate(entries):
+        a, b = int(val_offsets[4 * prev]), int(val_offsets[4 * e])
+        out[int(new_off[4 * prev]):int(new_off[4 * prev]) + (b - a)] = val_bytes[a:b]
+        sa, sb = int(sub.val_offsets[4 * k]), int(sub.val_offsets[4 * k + 4])
+        out[int(new_off[4 * e]):int(new_off[4 * e]) + (sb - sa)] = sub.val_bytes[sa:sb]
+        prev = int(e) + 1
+    a, b = int(val_offsets[4 * prev]) if prev <= m else 0, int(val_offsets[-1])
+    if prev <= m and b > a:
+        out[int(new_off[4 * prev]):int(new_off[4 * prev]) + (b - a)] = val_bytes[a:b]
+    del src
+    return new_off.astype(np.int32), out

@@ -277,10 +277,12 @@ class ReplayEngine:
     # -- cache -------------------------------------------------------------
     def load_cache(self, cache: "Mapping[str, Any] | CacheTable") -> CacheTable:
         if isinstance(cache, (str, bytes)) or hasattr(cache, "__fspath__"):
-            # a `.gemini_cache` directory: one SQL query over diskcache's file (gemini_cache.read_diskcache_sqlite)
+            # a `.gemini_cache` directory: diskcache's SQLite file and its pickles read natively, no Python
+            # object per entry (gemini_cache.read_diskcache_native; the pure-Python reader stays as
+            # gemini_cache.read_diskcache_sqlite for comparison)
             import os
-            from .gemini_cache import read_diskcache_sqlite
-            cache = read_diskcache_sqlite(os.fspath(cache))
+            from .gemini_cache import read_diskcache_native
+            cache = read_diskcache_native(os.fspath(cache), self)
         table = cache if isinstance(cache, CacheTable) else build_table(cache, self.strict_date_batch)
         keys = np.ascontiguousarray(table.keys)
         L.check(self._ctx, self._lib.smsgate_cache_load(

@@ -57,3 +57,109 @@ def test_table_from_sqlite_equals_table_from_mapping(tmp_path):
     for f in ("keys", "val_offsets", "val_bytes", "eflags", "date_packed"):
         assert np.array_equal(getattr(a, f), getattr(b, f)), f
     assert a.values == b.values and a.skipped == b.skipped
+
+
+def _extra_entries(c):
+    """Values at the edges of the native decoder's pickle subset."""
+    base = dict(txn_type="debit", date="06.05.25 14:23", amount="52.00", currency="usd", card="***0018",
+                merchant="TEST LLC", city=None, address="null", balance="1,842.74")
+    odd = {
+        "int_amount": dict(base, amount=52, balance=-7),
+        "big_int": dict(base, amount=2 ** 40, balance=2 ** 70),            # LONG1 beyond int64: Python
+        "float_amount": dict(base, amount=52.5),                           # float repr: Python
+        "bool_none": dict(base, amount=True, balance=None),
+        "shared_string": dict(base, amount="77.00", balance="77.00"[:]),   # the same object twice: BINGET
+        "no_card": {k: v for k, v in base.items() if k != "card"},
+        "card_none": dict(base, card=None),
+        "merchant_empty": dict(base, merchant=""),
+        "currency_int": dict(base, currency=5),
+        "txn_bogus": dict(base, txn_type="bogus"),
+        "extra_keys": dict(base, note="x", nested_ok=None),
+        "nested_list": dict(base, tags=["a", "b"]),                        # a container: Python
+        "nested_dict": dict(base, meta={"k": 1}),
+        "date_unicode": dict(base, date="٠٦.٠٥.٢٥ 14:23"),                 # non-ASCII date: host chain
+        "date_long": dict(base, date="x" * 40),
+        "date_int": dict(base, date=20250506),
+        "date_missing": {k: v for k, v in base.items() if k != "date"},
+        "long_merchant": dict(base, merchant="Ж" * 300),                   # BINUNICODE (4-byte length)
+        "not_a_dict": ["a", "list"],
+        "empty_dict": {},
+    }
+    amount = "99.00"
+    odd["shared_string"] = dict(base, amount=amount, balance=amount)
+    import hashlib
+    names = {}
+    for name, v in odd.items():
+        k = hashlib.sha256(name.encode()).hexdigest()
+        c[k] = v
+        names[k] = name
+    return names
+
+
+def test_native_reader_matches_python_reader(tmp_path):
+    """smsgate_dcache_* (C++: SQLite + pickle subset, no Python object per entry) against the per-entry
+    Python path, array by array, for every entry it decodes itself; what it declines is flagged, not guessed."""
+    import ctypes as C
+
+    from smsgate_b200 import _lib as L
+    c, backup = _fill(str(tmp_path))
+    names = _extra_entries(c)
+    c.close()
+
+    def no_gpu(strings):
+        return np.full(len(strings), -1, np.int64)
+    want = gemini_cache.build_table(gemini_cache.read_diskcache_sqlite(str(tmp_path)), no_gpu)
+    lib = L.lib()
+    h = C.c_void_p()
+    err = C.create_string_buffer(256)
+    assert lib.smsgate_dcache_open(str(tmp_path).encode(), time.time(), C.byref(h), err, 256) == 0, err.value
+    m, vb, tb, sk, nh = (C.c_int64(0) for _ in range(5))
+    lib.smsgate_dcache_sizes(h, C.byref(m), C.byref(vb), C.byref(tb), C.byref(sk), C.byref(nh))
+    assert m.value == want.m and sk.value == want.skipped
+    keys = np.zeros((m.value, 32), np.uint8)
+    off = np.zeros(4 * m.value + 1, np.int32)
+    vbytes = np.zeros(vb.value + 1, np.uint8)
+    eflags = np.zeros(m.value, np.uint16)
+    rowids = np.zeros(m.value, np.int64)
+    host = np.zeros(m.value, np.uint8)
+    toff = np.zeros(5 * m.value + 1, np.int64)
+    tbytes = np.zeros(tb.value + 1, np.uint8)
+    tkind = np.zeros(5 * m.value, np.uint8)
+    p = lambda a: a.ctypes.data_as(C.c_void_p)  # noqa: E731
+    assert lib.smsgate_dcache_fill(h, p(keys), p(off), p(vbytes), p(eflags), p(rowids), p(host), p(toff), p(tbytes), p(tkind)) == 0
+    lib.smsgate_dcache_close(h)
+    assert np.array_equal(keys, want.keys)                       # same entries, same (rowid) order
+    assert nh.value == int((host == 1).sum())
+    date_bits = L.E_DATE_STRICT | L.E_DATE_HOST | L.E_DATE_NOBODY | L.E_DATE_TZ | L.E_DATE_PHONE
+    by_name = {}
+    for e in range(m.value):
+        name = names.get(keys[e].tobytes().hex())
+        by_name[name] = e
+        if host[e] == 1:
+            continue
+        for k in (0, 1, 3):                                       # str(amount), str(balance), card
+            a = vbytes[off[4 * e + k]:off[4 * e + k + 1]].tobytes()
+            b = want.val_bytes[want.val_offsets[4 * e + k]:want.val_offsets[4 * e + k + 1]].tobytes()
+            assert a == b, (name, k)
+        assert int(eflags[e]) == int(want.eflags[e]) & ~date_bits, name
+        got_date = vbytes[off[4 * e + 2]:off[4 * e + 3]].tobytes()
+        if host[e] == 0:
+            assert got_date == want.val_bytes[want.val_offsets[4 * e + 2]:want.val_offsets[4 * e + 3]].tobytes(), name
+        else:
+            assert got_date == b""                                # the host chain decides this date
+        v = want.values[e]
+        for j, field in enumerate(("txn_type", "currency", "merchant", "city", "address")):
+            kind = int(tkind[5 * e + j])
+            text = tbytes[toff[5 * e + j]:toff[5 * e + j + 1]].tobytes().decode()
+            if not isinstance(v, dict) or field not in v:
+                assert kind == 0, (name, field)
+            elif v[field] is None:
+                assert kind == 1
+            elif isinstance(v[field], str):
+                assert kind == 2 and text == v[field], (name, field)
+            else:
+                assert kind not in (0, 1, 2)
+    assert {n for n, e in by_name.items() if n and host[e] == 1} == {"big_int", "float_amount", "nested_list", "nested_dict", "not_a_dict"}
+    assert {n for n, e in by_name.items() if n and host[e] == 2} == {"date_unicode", "date_long", "date_int"}
+    assert host[[e for e in range(m.value) if keys[e].tobytes().hex() == "f" * 64][0]] == 1      # value in a side file
+    assert (host == 0).sum() > 2500
