@@ -374,6 +374,8 @@ typedef struct smsgate_p2p {
     uint32_t* stage[SMSGATE_MAX_WORLD];   /* [world * (bitmap_words / world + 12)] words per rank: staged bitmap slices */
     uint32_t* collide[SMSGATE_MAX_WORLD]; /* [bitmap_words] words per rank: bits set on two or more ranks */
     int64_t bitmap_words;                 /* power of two in [64, 2^26]; about 16 bits per key of the whole job is plenty */
+    int32_t* flags[SMSGATE_MAX_WORLD];    /* [SMSGATE_MAX_WORLD] int32 per rank, zero before the first use: arrival flags of
+                                             smsgate_p2p_barrier (NULL when the caller brings its own barrier) */
     int64_t gfl_slots;                    /* slots every gfl array holds (a pair of int64 each); a batch whose table would
                                              need more is refused with SMSGATE_E_LIMIT instead of storing out of bounds */
 } smsgate_p2p;
@@ -390,7 +392,13 @@ int smsgate_p2p_merge(smsgate_ctx* ctx, int parity, const smsgate_p2p* p);
 int smsgate_p2p_reserve_filter(smsgate_ctx* ctx, int64_t bitmap_words);
 int smsgate_p2p_filter_push(smsgate_ctx* ctx, int64_t n, const smsgate_outputs* out, const smsgate_p2p* p);
 int smsgate_p2p_filter_reduce(smsgate_ctx* ctx, const smsgate_p2p* p);
-/* h_overflow (optional, host): set to 1 if an inbox ever overflowed; passing it synchronises. */
+/* The cross-GPU barrier the steps above need between them, queued on the context's stream like any kernel (no
+ * host synchronisation): every rank calls it with the same `epoch`, which must grow by one from call to call.
+ * It returns (on the GPU) once every rank's earlier stores into peer memory are visible here.  One tiny block,
+ * so it is scheduled even while another stream's kernels fill the SMs.  A rank that waits ~2 s gives up and
+ * raises the overflow flag (reported as 2 by smsgate_p2p_resolve). */
+int smsgate_p2p_barrier(smsgate_ctx* ctx, const smsgate_p2p* p, int epoch);
+/* h_overflow (optional, host): set to 1 if an inbox ever overflowed, 2 if a barrier timed out; passing it synchronises. */
 int smsgate_p2p_resolve(smsgate_ctx* ctx, int64_t n, int64_t base_index, const smsgate_outputs* out,
                         const smsgate_p2p* p, int* h_overflow);
 

@@ -71,7 +71,7 @@ class P2P(C.Structure):
                 ("inbox", C.c_void_p * 64), ("in_count", C.c_void_p * 64),
                 ("gfl", C.c_void_p * 64), ("capacity", C.c_int64),
                 ("stage", C.c_void_p * 64), ("collide", C.c_void_p * 64), ("bitmap_words", C.c_int64),
-                ("gfl_slots", C.c_int64)]
+                ("flags", C.c_void_p * 64), ("gfl_slots", C.c_int64)]
 
 
 class LibraryMissing(RuntimeError):
@@ -141,6 +141,7 @@ def lib():
         "smsgate_dedup_merge": (i32, [vp, i64, vp, vp]),
         "smsgate_dedup_apply": (i32, [vp, i64, i64, i64, vp, vp, C.POINTER(Outputs)]),
         "smsgate_p2p_reserve": (i32, [vp, i64]),
+        "smsgate_p2p_barrier": (i32, [vp, C.POINTER(P2P), i32]),
         "smsgate_p2p_reserve_filter": (i32, [vp, i64]),
         "smsgate_p2p_filter_push": (i32, [vp, i64, C.POINTER(Outputs), C.POINTER(P2P)]),
         "smsgate_p2p_filter_reduce": (i32, [vp, C.POINTER(P2P)]),

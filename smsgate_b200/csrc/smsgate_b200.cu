@@ -2239,6 +2239,7 @@ struct P2PView {                 // smsgate_p2p, by value, for the kernels
     uint32_t* stage[SMSGATE_MAX_WORLD];   // prefilter: staged bitmap slices, one region per sending rank
     uint32_t* collide[SMSGATE_MAX_WORLD]; // prefilter: bits set on two or more ranks
     int64_t bitmap_words;                 // 0 = no prefilter
+    int32_t* flags[SMSGATE_MAX_WORLD];    // per rank [SMSGATE_MAX_WORLD] arrival flags of smsgate_p2p_barrier (may be NULL)
 };
 
 // ---- prefilter.  Only a key that occurs on two or more ranks needs the exchange; for every other key the
@@ -2248,13 +2249,19 @@ struct P2PView {                 // smsgate_p2p, by value, for the kernels
 // stores that slice back into everybody's `collide` bitmap.  A set bit can be a false positive (that key
 // is exchanged for nothing), never a false negative.  Cost: two bitmaps over NVLink instead of one 48-byte
 // record per distinct key - for a batch without cross-rank duplicates almost nothing is left to exchange.
+// The peer-exchange kernels run in blocks of 128 threads with at most 32 registers each: one such block fits
+// on an SM NEXT TO the keys kernel's CTA (640 threads x 96 registers leave 4 096 registers and ~20 KB of shared
+// memory), so the exchange of batch k proceeds on every SM while the keys kernel of batch k+1 occupies them all.
+constexpr int XCH_THREADS = 128;
+constexpr int XCH_MIN_BLOCKS = 16;       // 65 536 registers / (16 x 128 threads) = 32 per thread
+
 __device__ __forceinline__ int64_t slice_lo(int64_t words, int w, int world) { return (words * w / world) & ~(int64_t)3; }
 __device__ __forceinline__ int64_t slice_cap(int64_t words, int world) { return ((words + world - 1) / world + 8) & ~(int64_t)3; }
 __device__ __forceinline__ uint32_t key_bit(const uint8_t* key, int64_t words) {
     return reinterpret_cast<const uint32_t*>(key)[2] & (uint32_t)(words * 32 - 1);
 }
 
-__global__ void __launch_bounds__(256)
+__global__ void __launch_bounds__(XCH_THREADS, XCH_MIN_BLOCKS)
 k_bits_build(int64_t n, const uint8_t* __restrict__ msg_id, const int32_t* __restrict__ slot_of, uint32_t* __restrict__ bits,
              int64_t words) {
     const int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
@@ -2262,7 +2269,7 @@ k_bits_build(int64_t n, const uint8_t* __restrict__ msg_id, const int32_t* __res
     const uint32_t h = key_bit(msg_id + i * 20, words);
     atomicOr(&bits[h >> 5], 1u << (h & 31));
 }
-__global__ void __launch_bounds__(256)
+__global__ void __launch_bounds__(XCH_THREADS, XCH_MIN_BLOCKS)
 k_bits_push(const uint32_t* __restrict__ bits, P2PView P) {
     const int64_t nq = P.bitmap_words >> 2, cap = slice_cap(P.bitmap_words, P.world);
     for (int64_t q = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; q < nq; q += (int64_t)gridDim.x * blockDim.x) {
@@ -2274,7 +2281,7 @@ k_bits_push(const uint32_t* __restrict__ bits, P2PView P) {
         *reinterpret_cast<uint4*>(P.stage[w] + P.rank * cap + (j - slice_lo(P.bitmap_words, w, P.world))) = v;   // peer store
     }
 }
-__global__ void __launch_bounds__(256)
+__global__ void __launch_bounds__(XCH_THREADS, XCH_MIN_BLOCKS)
 k_bits_reduce(P2PView P) {
     const int64_t lo = slice_lo(P.bitmap_words, P.rank, P.world);
     const int64_t hi = P.rank + 1 == P.world ? P.bitmap_words : slice_lo(P.bitmap_words, P.rank + 1, P.world);
@@ -2294,7 +2301,7 @@ k_bits_reduce(P2PView P) {
 // Records of this rank's distinct keys go straight into their owners' inboxes.  A block counts its records
 // per destination in shared memory and reserves its ranges with one remote atomic per destination; with the
 // prefilter only keys whose bit is set in `collide` are sent at all.
-__global__ void __launch_bounds__(256)
+__global__ void __launch_bounds__(XCH_THREADS, XCH_MIN_BLOCKS)
 k_p2p_scatter(int64_t n, int64_t base_index, int parity, const uint8_t* __restrict__ msg_id, DedupScratch D, P2PView P,
               const uint32_t* __restrict__ collide, int* __restrict__ overflow) {
     __shared__ int hist[SMSGATE_MAX_WORLD];
@@ -2355,7 +2362,7 @@ __device__ __forceinline__ uint64_t p2p_table_mask(int count) {
     while (cap < want) cap <<= 1;
     return cap - 1;
 }
-__global__ void __launch_bounds__(256)
+__global__ void __launch_bounds__(XCH_THREADS, XCH_MIN_BLOCKS)
 k_p2p_clear(const int32_t* __restrict__ count_ptr, int64_t capacity, P2PSlot* __restrict__ table) {
     const uint64_t cap = p2p_table_mask(p2p_count(count_ptr, capacity)) + 1;
     for (uint64_t s = blockIdx.x * (uint64_t)blockDim.x + threadIdx.x; s < cap; s += (uint64_t)gridDim.x * blockDim.x) {
@@ -2364,7 +2371,7 @@ k_p2p_clear(const int32_t* __restrict__ count_ptr, int64_t capacity, P2PSlot* __
         table[s] = e;
     }
 }
-__global__ void __launch_bounds__(256)
+__global__ void __launch_bounds__(XCH_THREADS, XCH_MIN_BLOCKS)
 k_p2p_insert(const int32_t* __restrict__ count_ptr, int64_t capacity, const P2PRecord* __restrict__ recs,
              P2PSlot* __restrict__ table, int32_t* __restrict__ slot_of) {
     const int count = p2p_count(count_ptr, capacity);
@@ -2386,7 +2393,7 @@ k_p2p_insert(const int32_t* __restrict__ count_ptr, int64_t capacity, const P2PR
         slot_of[i] = (int32_t)pos;
     }
 }
-__global__ void __launch_bounds__(256)
+__global__ void __launch_bounds__(XCH_THREADS, XCH_MIN_BLOCKS)
 k_p2p_verdict(const int32_t* __restrict__ count_ptr, const P2PRecord* __restrict__ recs,
               const P2PSlot* __restrict__ table, const int32_t* __restrict__ slot_of, P2PView P, int parity) {
     const int count = p2p_count(count_ptr, P.capacity);
@@ -2402,7 +2409,7 @@ k_p2p_verdict(const int32_t* __restrict__ count_ptr, const P2PRecord* __restrict
     }
 }
 
-__global__ void __launch_bounds__(256)
+__global__ void __launch_bounds__(XCH_THREADS, XCH_MIN_BLOCKS)
 k_p2p_resolve(int64_t n, int64_t base_index, const int32_t* __restrict__ slot_of, const longlong2* __restrict__ gfl,
               uint8_t* __restrict__ survivor, uint8_t* __restrict__ first_seen, int64_t* __restrict__ last_idx) {
     const int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
@@ -2422,6 +2429,29 @@ k_p2p_resolve(int64_t n, int64_t base_index, const int32_t* __restrict__ slot_of
     if (last_idx) last_idx[i] = li;
 }
 
+// Cross-GPU barrier from inside the stream, without a host round trip and small enough (one warp-sized block, a
+// dozen registers) to be scheduled next to anything: thread w stores `epoch` into rank w's flag for this rank
+// (a system-scope release after the fence: everything this rank's earlier kernels stored into peer memory is
+// visible before the flag is), then waits until rank w's flag for it has reached `epoch`.  Epochs only grow, the
+// flags are never reset.  The wait gives up after about two seconds and raises the overflow flag (value 2)
+// rather than hang the GPU.
+__global__ void __launch_bounds__(SMSGATE_MAX_WORLD)
+k_p2p_barrier(P2PView P, int epoch, int* __restrict__ overflow) {
+    const int w = threadIdx.x;
+    if (w >= P.world) return;
+    __threadfence_system();
+    asm volatile("st.release.sys.global.s32 [%0], %1;" ::"l"(P.flags[w] + P.rank), "r"(epoch) : "memory");
+    const int32_t* mine = P.flags[P.rank] + w;
+    const long long t0 = clock64();
+    for (;;) {
+        int v;
+        asm volatile("ld.acquire.sys.global.s32 %0, [%1];" : "=r"(v) : "l"(mine) : "memory");
+        if (v - epoch >= 0) break;
+        if (clock64() - t0 > 4000000000ll) { atomicExch(overflow, 2); break; }
+        __nanosleep(200);
+    }
+}
+
 static int p2p_view(smsgate_ctx* ctx, const smsgate_p2p* p, P2PView* v) {
     if (!p || p->world < 1 || p->world > SMSGATE_MAX_WORLD || p->rank < 0 || p->rank >= p->world || p->capacity < 1)
         return fail(ctx, SMSGATE_E_ARG, "p2p: bad descriptor");
@@ -2432,6 +2462,7 @@ static int p2p_view(smsgate_ctx* ctx, const smsgate_p2p* p, P2PView* v) {
         v->in_count[w] = p->in_count[w];
         v->gfl[w] = reinterpret_cast<longlong2*>(p->gfl[w]);
     }
+    for (int w = 0; w < p->world; ++w) v->flags[w] = p->flags[w];
     v->bitmap_words = p->bitmap_words;
     if (p->bitmap_words) {
         if (p->bitmap_words < 64 || (p->bitmap_words & (p->bitmap_words - 1)) || p->bitmap_words > (1ll << 26))
@@ -2483,7 +2514,7 @@ extern "C" int smsgate_p2p_scatter(smsgate_ctx* ctx, int64_t n, int64_t base_ind
         return fail(ctx, SMSGATE_E_LIMIT, "p2p_scatter: the batch exceeds capacity / world messages per rank");
     DedupScratch D{ctx->d_dtab, ctx->d_slot_of, cap - 1};
     if (n > 0) {
-        k_p2p_scatter<<<(unsigned)((n + 255) / 256), 256, 0, st>>>(n, base_index, parity & 1, out->msg_id, D, V,
+        k_p2p_scatter<<<(unsigned)((n + XCH_THREADS - 1) / XCH_THREADS), XCH_THREADS, 0, st>>>(n, base_index, parity & 1, out->msg_id, D, V,
                                                                    V.bitmap_words ? V.collide[V.rank] : nullptr,
                                                                    ctx->p2p_overflow);
         ctx->launches += 1;
@@ -2504,8 +2535,8 @@ extern "C" int smsgate_p2p_filter_push(smsgate_ctx* ctx, int64_t n, const smsgat
     CUDA_TRY(ctx, cudaSetDevice(ctx->device));
     cudaStream_t st = ctx->stream;
     CUDA_TRY(ctx, cudaMemsetAsync(ctx->p2p_bits, 0, (size_t)V.bitmap_words * 4, st));
-    if (n > 0) k_bits_build<<<(unsigned)((n + 255) / 256), 256, 0, st>>>(n, out->msg_id, ctx->d_slot_of, ctx->p2p_bits, V.bitmap_words);
-    k_bits_push<<<(unsigned)ctx->sm_count * 4, 256, 0, st>>>(ctx->p2p_bits, V);
+    if (n > 0) k_bits_build<<<(unsigned)((n + XCH_THREADS - 1) / XCH_THREADS), XCH_THREADS, 0, st>>>(n, out->msg_id, ctx->d_slot_of, ctx->p2p_bits, V.bitmap_words);
+    k_bits_push<<<(unsigned)ctx->sm_count * 4, XCH_THREADS, 0, st>>>(ctx->p2p_bits, V);
     ctx->launches += n > 0 ? 2 : 1;
     CUDA_TRY(ctx, cudaGetLastError());
     return SMSGATE_OK;
@@ -2518,7 +2549,22 @@ extern "C" int smsgate_p2p_filter_reduce(smsgate_ctx* ctx, const smsgate_p2p* p)
     if (rc) return rc;
     if (!V.bitmap_words) return fail(ctx, SMSGATE_E_ARG, "p2p_filter_reduce: the descriptor has no prefilter bitmaps");
     CUDA_TRY(ctx, cudaSetDevice(ctx->device));
-    k_bits_reduce<<<(unsigned)ctx->sm_count * 2, 256, 0, ctx->stream>>>(V);
+    k_bits_reduce<<<(unsigned)ctx->sm_count * 2, XCH_THREADS, 0, ctx->stream>>>(V);
+    ctx->launches += 1;
+    CUDA_TRY(ctx, cudaGetLastError());
+    return SMSGATE_OK;
+}
+
+extern "C" int smsgate_p2p_barrier(smsgate_ctx* ctx, const smsgate_p2p* p, int epoch) {
+    if (!ctx) return SMSGATE_E_ARG;
+    P2PView V;
+    int rc = p2p_view(ctx, p, &V);
+    if (rc) return rc;
+    for (int w = 0; w < V.world; ++w)
+        if (!V.flags[w]) return fail(ctx, SMSGATE_E_ARG, "p2p_barrier: the descriptor carries no flags arrays");
+    if (!ctx->p2p_overflow) return fail(ctx, SMSGATE_E_STATE, "p2p_barrier: call smsgate_p2p_reserve first");
+    CUDA_TRY(ctx, cudaSetDevice(ctx->device));
+    k_p2p_barrier<<<1, SMSGATE_MAX_WORLD, 0, ctx->stream>>>(V, epoch, ctx->p2p_overflow);
     ctx->launches += 1;
     CUDA_TRY(ctx, cudaGetLastError());
     return SMSGATE_OK;
@@ -2547,9 +2593,9 @@ extern "C" int smsgate_p2p_merge(smsgate_ctx* ctx, int parity, const smsgate_p2p
     cudaStream_t st = ctx->stream;
     const int32_t* cnt = V.in_count[V.rank] + (parity & 1);
     const unsigned grid = (unsigned)ctx->sm_count * 8;
-    k_p2p_clear<<<grid, 256, 0, st>>>(cnt, V.capacity, ctx->p2p_table);
-    k_p2p_insert<<<grid, 256, 0, st>>>(cnt, V.capacity, V.inbox[V.rank], ctx->p2p_table, ctx->p2p_slot_of);
-    k_p2p_verdict<<<grid, 256, 0, st>>>(cnt, V.inbox[V.rank], ctx->p2p_table, ctx->p2p_slot_of, V, parity & 1);
+    k_p2p_clear<<<grid, XCH_THREADS, 0, st>>>(cnt, V.capacity, ctx->p2p_table);
+    k_p2p_insert<<<grid, XCH_THREADS, 0, st>>>(cnt, V.capacity, V.inbox[V.rank], ctx->p2p_table, ctx->p2p_slot_of);
+    k_p2p_verdict<<<grid, XCH_THREADS, 0, st>>>(cnt, V.inbox[V.rank], ctx->p2p_table, ctx->p2p_slot_of, V, parity & 1);
     ctx->launches += 3;
     CUDA_TRY(ctx, cudaGetLastError());
     return SMSGATE_OK;
@@ -2566,7 +2612,7 @@ extern "C" int smsgate_p2p_resolve(smsgate_ctx* ctx, int64_t n, int64_t base_ind
     CUDA_TRY(ctx, cudaSetDevice(ctx->device));
     cudaStream_t st = ctx->stream;
     if (n > 0) {
-        k_p2p_resolve<<<(unsigned)((n + 255) / 256), 256, 0, st>>>(n, base_index, ctx->d_slot_of, V.gfl[V.rank],
+        k_p2p_resolve<<<(unsigned)((n + XCH_THREADS - 1) / XCH_THREADS), XCH_THREADS, 0, st>>>(n, base_index, ctx->d_slot_of, V.gfl[V.rank],
                                                                    out->survivor, out->first_seen, out->last_idx);
         ctx->launches += 1;
     }

@@ -147,6 +147,8 @@ class GlobalDedupP2P:
         self._count = symm_mem.empty(16, dtype=torch.int32, device=dev)
         self._gfl = symm_mem.empty(2 * cap_slots, dtype=torch.int64, device=dev)
         self._count.zero_()
+        self._flags = symm_mem.empty(L.MAX_WORLD, dtype=torch.int32, device=dev)     # smsgate_p2p_barrier arrival flags
+        self._flags.zero_()
         bufs = [self._inbox, self._count, self._gfl]
         # prefilter bitmaps: about 16 bits per key of the whole job (a false positive only costs one record)
         self.bitmap_words = 0
@@ -158,6 +160,7 @@ class GlobalDedupP2P:
             self._stage = symm_mem.empty(self.world * (words // self.world + 12), dtype=torch.int32, device=dev)
             self._collide = symm_mem.empty(words, dtype=torch.int32, device=dev)
             bufs += [self._stage, self._collide]
+        bufs.append(self._flags)
         torch.cuda.synchronize()
         self._h = [symm_mem.rendezvous(t, group) for t in bufs]
         self.desc = L.P2P()
@@ -169,14 +172,16 @@ class GlobalDedupP2P:
             self.desc.inbox[w] = self._h[0].buffer_ptrs[w]
             self.desc.in_count[w] = self._h[1].buffer_ptrs[w]
             self.desc.gfl[w] = self._h[2].buffer_ptrs[w]
+            self.desc.flags[w] = self._h[-1].buffer_ptrs[w]
             if self.bitmap_words:
                 self.desc.stage[w] = self._h[3].buffer_ptrs[w]
                 self.desc.collide[w] = self._h[4].buffer_ptrs[w]
         L.check(engine._ctx, L.lib().smsgate_p2p_reserve(engine._ctx, self.capacity))
         if self.bitmap_words:
             L.check(engine._ctx, L.lib().smsgate_p2p_reserve_filter(engine._ctx, self.bitmap_words))
-        self._h[1].barrier(channel=0)          # every rank's counters are zero before anyone scatters
+        self._h[1].barrier(channel=0)          # every rank's counters and flags are zero before anyone scatters
         self.step = 0
+        self.epoch = 0
         self.launches = 0
         self.bytes_sent = 0
 
@@ -188,15 +193,20 @@ class GlobalDedupP2P:
         if n > self.n_max:
             raise ValueError(f"shard of {n} messages exceeds the n_max={self.n_max} this exchange was sized for")
         parity = self.step & 1
+
+        def barrier():
+            # in-stream, no host round trip, one tiny block (smsgate_p2p_barrier): schedulable next to anything
+            self.epoch += 1
+            L.check(eng._ctx, lib.smsgate_p2p_barrier(eng._ctx, C.byref(self.desc), self.epoch))
         if self.bitmap_words:
             L.check(eng._ctx, lib.smsgate_p2p_filter_push(eng._ctx, n, C.byref(out), C.byref(self.desc)))
-            self._h[1].barrier(channel=0)      # every rank's bitmap slices have landed at their owners
+            barrier()                          # every rank's bitmap slices have landed at their owners
             L.check(eng._ctx, lib.smsgate_p2p_filter_reduce(eng._ctx, C.byref(self.desc)))
-            self._h[1].barrier(channel=1)      # every rank holds the complete collision bitmap
+            barrier()                          # every rank holds the complete collision bitmap
         L.check(eng._ctx, lib.smsgate_p2p_scatter(eng._ctx, n, int(base_index), parity, C.byref(out), C.byref(self.desc)))
-        self._h[1].barrier(channel=0)          # all records have landed in their owners' inboxes
+        barrier()                              # all records have landed in their owners' inboxes
         L.check(eng._ctx, lib.smsgate_p2p_merge(eng._ctx, parity, C.byref(self.desc)))
-        self._h[1].barrier(channel=1)          # all verdicts have landed in their home arrays
+        barrier()                              # all verdicts have landed in their home arrays
         L.check(eng._ctx, lib.smsgate_p2p_resolve(eng._ctx, n, int(base_index), C.byref(out), C.byref(self.desc), None))
         self.step += 1
 
@@ -213,6 +223,8 @@ class GlobalDedupP2P:
         out = L.Outputs()
         L.check(self.engine._ctx, L.lib().smsgate_p2p_resolve(self.engine._ctx, 0, 0, C.byref(out), C.byref(self.desc),
                                                               C.byref(flag)))
+        if flag.value == 2:
+            raise RuntimeError("a cross-GPU barrier of the exchange timed out (a rank fell behind by more than ~2 s)")
         return bool(flag.value)
 
 
@@ -236,13 +248,14 @@ class OverlappedReplay:
     ("lanes") alternate: each owns its dedup scratch, its output columns and its peer-memory buffers and
     shares the one response cache (smsgate_cache_share).  Lane work is queued on `main` (high priority:
     smsgate_scan_keys, smsgate_join_route_dedup), its exchange on `side` (low priority) behind an event; a
-    lane is reused only after its previous exchange has finished.  `reserve_sms` SMs are kept free of the keys
-    kernel (smsgate_set_scan_ctas) so that the side stream's kernels find room while it runs.
+    lane is reused only after its previous exchange has finished.  The exchange kernels and the in-stream barrier
+    are built to fit on an SM next to the keys kernel's CTA (128 threads, 32 registers), so they run on every SM
+    while it has them all; `reserve_sms` > 0 additionally keeps SMs free of it (smsgate_set_scan_ctas).
 
     The reference has no counterpart: its upsert is one synchronous HTTP/SQL round trip per message
     (libs/pocketbase.py:168-200, services/pb_writer/upsert.py:19-31)."""
 
-    def __init__(self, engine, dist, n_max: int, prefer_p2p: bool = True, reserve_sms: int = 8, lanes: int = 2):
+    def __init__(self, engine, dist, n_max: int, prefer_p2p: bool = True, reserve_sms: int = 0, lanes: int = 2):
         import torch
 
         from .replay import ReplayEngine

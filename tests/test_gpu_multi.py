@@ -274,3 +274,31 @@ def test_peer_memory_exchange_emulated_on_one_gpu(world, prefilter, ragged):
     finally:
         for eng in engines:
             eng.close()
+
+
+def test_in_stream_barrier_single_rank_and_timeout():
+    """smsgate_p2p_barrier: with one rank it signals and finds its own flag; a rank whose peer never arrives
+    gives up after about two seconds and reports it instead of hanging the GPU."""
+    import torch
+
+    from smsgate_b200.replay import ReplayEngine
+    with ReplayEngine(0) as eng:
+        lib = L.lib()
+        peers = _EmulatedPeers([eng], 64, False)
+        flags = torch.zeros(L.MAX_WORLD, dtype=torch.int32, device="cuda")
+        d = peers.desc[0]
+        d.flags[0] = flags.data_ptr()
+        for epoch in (1, 2, 3):
+            L.check(eng._ctx, lib.smsgate_p2p_barrier(eng._ctx, C.byref(d), epoch))
+        torch.cuda.synchronize()
+        assert int(flags[0].item()) == 3 and not peers.overflowed()
+        # two ranks, the second never calls: rank 0's wait times out
+        other = torch.zeros(L.MAX_WORLD, dtype=torch.int32, device="cuda")
+        d.world = 2
+        d.inbox[1], d.in_count[1], d.gfl[1], d.flags[1] = d.inbox[0], d.in_count[0], d.gfl[0], other.data_ptr()
+        L.check(eng._ctx, lib.smsgate_p2p_barrier(eng._ctx, C.byref(d), 4))
+        torch.cuda.synchronize()
+        flag = C.c_int(0)
+        out = L.Outputs()
+        L.check(eng._ctx, lib.smsgate_p2p_resolve(eng._ctx, 0, 0, C.byref(out), C.byref(d), C.byref(flag)))
+        assert flag.value == 2 and int(other[0].item()) == 4
