@@ -310,6 +310,42 @@ def test_record_result_materialises_like_column_result(engine):
     assert d2.upserts() == ua
 
 
+def test_native_cache_loader_equals_python_loader(engine, tmp_path):
+    """engine.load_cache(<directory>) - SQLite + pickles decoded in C++, dates classified on the GPU - builds
+    the same table, array for array, as the per-entry Python path over diskcache's own view of the cache,
+    and replays identically; the response dicts behind it are unpickled only on demand."""
+    import diskcache
+    from tests.test_cache_loader import _extra_entries
+    backup = synth.generate(8000, seed=52, mixed_locale=True, miss_frac=0.1)
+    c = diskcache.Cache(str(tmp_path))
+    with c.transact():
+        for k, v in backup.cache.items():
+            c[k] = v
+    _extra_entries(c)
+    odd_dates = ["2024-02-14 09:00:00", "14:23 06.05.2025", "", "yesterday", "2024-02-14T09:00:00+04:00", "06.05.25 14:23"]
+    some = [k for k in list(backup.cache)[:len(odd_dates)]]
+    for k, d in zip(some, odd_dates):
+        c[k] = dict(backup.cache[k], date=d)
+    c["f" * 64] = dict(backup.cache[some[0]], merchant="X" * 40_000)          # side file
+    via_diskcache = {k: c[k] for k in c if isinstance(k, str) and k in c}
+    c.close()
+    want = gemini_cache.build_table(via_diskcache, engine.strict_date_batch)
+    got = engine.load_cache(str(tmp_path))
+    for f in ("keys", "val_offsets", "val_bytes", "eflags", "date_packed"):
+        assert np.array_equal(getattr(got, f), getattr(want, f)), f
+    assert got.skipped == want.skipped and got.host_dates == want.host_dates
+    assert 0 < got.host_decoded < 10 and got.host_dates_resolved < 20
+    assert all(got.values[e] == want.values[e] for e in range(0, want.m, 97))
+    batch = Batch.from_strings(backup.bodies, backup.senders, backup.date_ms)
+    a = engine.replay(batch, NOW)
+    engine.load_cache(via_diskcache)
+    b = engine.replay(batch, NOW)
+    for name in ("status", "slot", "amount_coef", "date", "card", "survivor"):
+        assert np.array_equal(a.cols[name], b.cols[name]), name
+    engine.load_cache(str(tmp_path))
+    assert engine.replay(batch, NOW).upserts() == b.upserts()                   # materialised through LazyValues
+
+
 def test_device_keys_and_cross_source(engine, golden):
     """MD5 device keys against the reference's vectors and the oracle, and the report of bodies that the
     reference stores twice (same body seen from the XML backup and from a device)."""
