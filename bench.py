@@ -182,7 +182,8 @@ def run_reference(args, rank, world):
     value, ms, n_used = cpu_arm(backup, n_sample, cores, args.steps, args.warmup)
     sample = (f"{n_used} messages of the workload per step, bodies already in memory (no XML parse), "
               f"oracle port of worker filter + parse_sms_llm hit branch + writer gate + dict upsert, "
-              f"diskcache-backed response cache, {cores} processes")
+              f"diskcache-backed response cache, {cores} processes; the port runs at ~0.66x the speed of the reference's own "
+              f"functions on the same input (profiles/r2_cpu_units_reference_vs_port.txt)")
     line = {"impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": args.gpus,
             "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms, "higher_is_better": True,
             "scaling": "weak", "vs_baseline": None, "dtype": "u8/u32/int64", "data": "synthetic",
@@ -523,7 +524,10 @@ def run_ours(args, rank, world, local_rank):
                      "path_algorithmic_gbs": n * (mean_len + 229) / (step * 1e-3) / 1e9},
         "cpu_baseline": ({"value": cpu_val, "unit": UNIT, "cores": cpu_cores, "kind": "port",
                           "sample": f"{cpu_n} messages of the same workload, bodies in memory, oracle port with a "
-                                    f"diskcache-backed response cache, single process"} if world == 1 else None),
+                                    f"diskcache-backed response cache, single process.  Port vs the reference's own functions on "
+                                    f"configs[0] in the build container (profiles/r2_cpu_units_reference_vs_port.txt): same "
+                                    f"upsert set, the reference runs this unit at ~12.7 k msgs/s, the port at ~8.4 k - the "
+                                    f"port UNDERSTATES the CPU by about 1.5x"} if world == 1 else None),
         "upserts_per_gpu": upserts_local,
         "one_batch_at_a_time": {"ms_per_step": sync_step, "k_scan_keys_ms": sync_k1, "value": world * n / (sync_step * 1e-3),
                                 "note": "per-step CUDA events, L2 flushed between steps, nothing overlapped: the latency "
