@@ -446,6 +446,30 @@ int smsgate_replay_host_records_finish(smsgate_ctx* ctx, int64_t* h_verdict);
  * that came back as records. */
 int smsgate_fetch_columns(smsgate_ctx* ctx, int64_t n, const smsgate_outputs* h_out);
 
+/* ---- what goes downstream, in bulk -------------------------------------------
+ * For the selected messages of a replayed batch (normally the survivors), the bytes the reference would send:
+ *   mode 0  the sms.parsed payload, ParsedSMS.model_dump_json() (libs/nats_utils.py:127, services/parser_worker/worker.py:183)
+ *   mode 1  the record upsert_parsed_sms hands to PocketBase (libs/pocketbase.py:296-309), as compact JSON
+ * assembled on the host from the replay's columns (or packed records) and the natively read cache texts
+ * (smsgate_dcache_fill: text_offsets / text_bytes / text_kind) - no pydantic object per record.  Two calls:
+ * with out_bytes = NULL it only reports `needed`; then out_offsets[n_sel+1] + out_bytes[capacity] are filled and
+ * fallback[k] = 1 marks a row this code leaves to the caller (non-ASCII currency, a cache field of another type,
+ * an overflowed coefficient): its span is empty.  Host memory only. */
+typedef struct smsgate_emit_input {
+    const smsgate_record* records;   /* packed records, or NULL to use the columns below */
+    const uint8_t* msg_id; const uint8_t* status; const uint8_t* flags; const uint8_t* dec_flags; const int32_t* slot;
+    const int64_t* amount_coef; const int64_t* balance_coef; const int32_t* amount_exp; const int32_t* balance_exp;
+    const int64_t* date;
+    const uint8_t* card; const uint8_t* card_len;                 /* always columns (the record does not carry the card) */
+    const int64_t* body_offsets; const uint8_t* body_bytes;       /* the batch */
+    const int32_t* fixed_len; const uint8_t* fixed_bytes;         /* raw_body where SMSGATE_F_MODIFIED */
+    const int64_t* sender_offsets; const uint8_t* sender_bytes;   /* RawSMS.sender per message, ragged */
+    const char* device_id;                                        /* one value for the batch, NULL -> null */
+    const int64_t* text_offsets; const uint8_t* text_bytes; const uint8_t* text_kind;   /* per cache entry */
+} smsgate_emit_input;
+int smsgate_emit_json(const smsgate_emit_input* in, int mode, int64_t n_sel, const int64_t* sel, int64_t* out_offsets,
+                      uint8_t* out_bytes, int64_t capacity, uint8_t* fallback, int64_t* needed);
+
 /* ---- upsert-by-msg_id for callers that must not allocate -------------------
  * No counterpart in the reference (it has no device memory to manage).
  *

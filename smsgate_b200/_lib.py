@@ -65,6 +65,15 @@ class LegacyOutputs(C.Structure):
     _fields_ = [(n, C.c_void_p) for n in ("status", "lflags", "strip", "caps", "amount", "balance", "body_hash")]
 
 
+class EmitInput(C.Structure):
+    """struct smsgate_emit_input"""
+    _fields_ = [(n, C.c_void_p) for n in (
+        "records", "msg_id", "status", "flags", "dec_flags", "slot", "amount_coef", "balance_coef", "amount_exp",
+        "balance_exp", "date", "card", "card_len", "body_offsets", "body_bytes", "fixed_len", "fixed_bytes",
+        "sender_offsets", "sender_bytes")] + [("device_id", C.c_char_p)] + [
+        (n, C.c_void_p) for n in ("text_offsets", "text_bytes", "text_kind")]
+
+
 class P2P(C.Structure):
     """struct smsgate_p2p"""
     _fields_ = [("world", C.c_int32), ("rank", C.c_int32),
@@ -110,6 +119,7 @@ def lib():
         "smsgate_dcache_fill": (i32, [vp, vp, vp, vp, vp, vp, vp, vp, vp, vp]),
         "smsgate_dcache_close": (None, [vp]),
         "smsgate_strict_date_entries": (i32, [vp, i64, vp, vp, vp]),
+        "smsgate_emit_json": (i32, [C.POINTER(EmitInput), i32, i64, vp, vp, vp, i64, vp, vp]),
         "smsgate_decimal_batch": (i32, [vp, i64, vp, vp, vp, vp, vp]),
         "smsgate_strict_date_batch": (i32, [vp, i64, vp, vp, vp]),
         "smsgate_dt_str_batch": (i32, [vp, i64, vp, vp, vp]),

@@ -887,6 +887,37 @@ extern "C" int smsgate_dcache_fill(const smsgate_dcache* h, uint8_t* keys, int32
 }
 extern "C" void smsgate_dcache_close(smsgate_dcache* h) { delete h; }
 
+// ---- bulk emit of sms.parsed payloads / PocketBase records (emit_json.h)
+#include "emit_json.h"
+extern "C" int smsgate_emit_json(const smsgate_emit_input* in, int mode, int64_t n_sel, const int64_t* sel, int64_t* out_offsets,
+                                 uint8_t* out_bytes, int64_t capacity, uint8_t* fallback, int64_t* needed) {
+    if (!in || n_sel < 0 || (n_sel > 0 && !sel) || !out_offsets || (mode != 0 && mode != 1)) return SMSGATE_E_ARG;
+    sgemit::In I;
+    I.msg_id = in->msg_id; I.status = in->status; I.flags = in->flags; I.dec_flags = in->dec_flags; I.slot = in->slot;
+    I.amount_coef = in->amount_coef; I.balance_coef = in->balance_coef; I.amount_exp = in->amount_exp; I.balance_exp = in->balance_exp;
+    I.date = in->date; I.card = in->card; I.card_len = in->card_len; I.body_offsets = in->body_offsets; I.body_bytes = in->body_bytes;
+    I.fixed_len = in->fixed_len; I.fixed_bytes = in->fixed_bytes; I.sender_offsets = in->sender_offsets; I.sender_bytes = in->sender_bytes;
+    I.device_id = in->device_id; I.text_offsets = in->text_offsets; I.text_bytes = in->text_bytes; I.text_kind = in->text_kind;
+    I.record_stride = in->records ? (int64_t)sizeof(smsgate_record) : 0;
+    if (in->records) I.msg_id = reinterpret_cast<const uint8_t*>(in->records);
+    if (!I.msg_id || !I.card || !I.card_len || !I.body_offsets || !I.sender_offsets || !I.text_offsets || !I.text_kind ||
+        (!in->records && (!I.flags || !I.dec_flags || !I.slot || !I.amount_coef || !I.balance_coef || !I.amount_exp || !I.balance_exp || !I.date)))
+        return SMSGATE_E_ARG;
+    sgemit::Sink count{nullptr};
+    for (int64_t k = 0; k < n_sel; ++k) sgemit::emit_one(count, I, sel[k], mode);
+    if (needed) *needed = count.n;
+    if (!out_bytes) return SMSGATE_OK;                       // sizing pass
+    if (capacity < count.n) return SMSGATE_E_LIMIT;
+    sgemit::Sink w{out_bytes};
+    for (int64_t k = 0; k < n_sel; ++k) {
+        out_offsets[k] = w.n;
+        const bool ok = sgemit::emit_one(w, I, sel[k], mode);
+        if (fallback) fallback[k] = ok ? 0 : 1;
+    }
+    out_offsets[n_sel] = w.n;
+    return SMSGATE_OK;
+}
+
 extern "C" int smsgate_abi_version(void) { return SMSGATE_ABI_VERSION; }
 
 extern "C" const char* smsgate_last_error(const smsgate_ctx* ctx) {

@@ -160,9 +160,41 @@ def build_table(mapping: Mapping[str, Any], strict_date_batch) -> CacheTable:
         raise ValueError("cache value strings exceed 2 GiB")
     key_arr = (np.frombuffer(bytes.fromhex("".join(keys)), dtype=np.uint8).reshape(m, 32).copy()
                if m else np.zeros((0, 32), dtype=np.uint8))
-    return CacheTable(keys=key_arr, val_offsets=val_offsets.astype(np.int32),
-                      val_bytes=np.frombuffer(b"".join(parts), dtype=np.uint8).copy(), eflags=eflags,
-                      date_packed=date_packed, values=values, host_dates=host_dates, skipped=skipped)
+    t = CacheTable(keys=key_arr, val_offsets=val_offsets.astype(np.int32),
+                   val_bytes=np.frombuffer(b"".join(parts), dtype=np.uint8).copy(), eflags=eflags,
+                   date_packed=date_packed, values=values, host_dates=host_dates, skipped=skipped)
+    t.text = _text_arrays(values)
+    return t
+
+
+def _text_arrays(values) -> tuple:
+    """The five host-side strings of every entry (txn_type, currency, merchant, city, address) in the layout
+    smsgate_dcache_fill produces: offsets[5m+1], bytes, kind[5m] (0 missing, 1 None, 2 str, 3 other) - what the
+    bulk payload emitter (smsgate_emit_json) reads."""
+    m = len(values)
+    kind = np.zeros(5 * m, np.uint8)
+    parts = []
+    for e, v in enumerate(values):
+        for j, f in enumerate(("txn_type", "currency", "merchant", "city", "address")):
+            x = v.get(f, _MISSING) if isinstance(v, dict) else _MISSING
+            if x is _MISSING:
+                parts.append(b"")
+            elif x is None:
+                kind[5 * e + j] = 1
+                parts.append(b"")
+            elif type(x) is str:
+                kind[5 * e + j] = 2
+                parts.append(x.encode("utf-8", "surrogatepass"))
+            else:
+                kind[5 * e + j] = 3
+                parts.append(b"")
+    off = np.zeros(5 * m + 1, np.int64)
+    if parts:
+        np.cumsum(np.fromiter((len(p) for p in parts), dtype=np.int64, count=len(parts)), out=off[1:])
+    return off, np.frombuffer(b"".join(parts), dtype=np.uint8).copy(), kind
+
+
+_MISSING = object()
 
 
 def _apply_host_date(kind: str, obj, e: int, date_packed: np.ndarray, host_dates: dict) -> int:

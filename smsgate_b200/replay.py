@@ -210,10 +210,66 @@ class ReplayResult:
         """msg_id hex -> ParsedSMS of the record that remains after the replay."""
         return {self.msg_id_hex(int(i)): self.parsed(int(i)) for i in self.survivor_indices()}
 
+    def emit_json(self, indices: np.ndarray, mode: int = 0, device_id: Optional[str] = "xml_backup"):
+        """Bytes for the messages `indices`, assembled natively from the columns and the cache texts
+        (smsgate_emit_json): mode 0 = sms.parsed payloads (`ParsedSMS.model_dump_json()`), mode 1 = PocketBase
+        records as compact JSON.  Returns (offsets int64[k+1], bytes uint8, fallback uint8[k]); a row flagged in
+        `fallback` has an empty span and is rendered by the caller through pydantic."""
+        t = self.table
+        idx = np.ascontiguousarray(indices, dtype=np.int64)
+        text = getattr(t, "text", None)
+        if text is None:
+            raise RuntimeError("the loaded cache carries no text arrays (load it with ReplayEngine.load_cache)")
+        cols = self.cols
+        inp = L.EmitInput()
+        keep = []
+
+        def ptr(a):
+            a = np.ascontiguousarray(a)
+            keep.append(a)
+            return a.ctypes.data
+        if hasattr(cols, "records"):
+            inp.records = ptr(cols.records)
+        else:
+            for name in ("msg_id", "status", "flags", "dec_flags", "slot", "amount_coef", "balance_coef", "amount_exp",
+                         "balance_exp", "date"):
+                setattr(inp, name, ptr(cols[name]))
+        inp.card, inp.card_len = ptr(cols["card"]), ptr(cols["card_len"])
+        inp.body_offsets = ptr(np.asarray(self.batch.body_offsets, dtype=np.int64))
+        inp.body_bytes = ptr(self.batch.body_bytes) if self.batch.body_bytes.size else None
+        inp.fixed_len, inp.fixed_bytes = ptr(cols["fixed_len"]), (ptr(cols["fixed_bytes"]) if cols["fixed_bytes"].size else None)
+        if getattr(self, "_sender_ragged", None) is None:
+            self._sender_ragged = ragged_from_strings(self.batch.senders if self.batch.senders is not None else [""] * self.n)
+        sb, so = self._sender_ragged
+        inp.sender_offsets, inp.sender_bytes = ptr(so), (ptr(sb) if sb.size else None)
+        inp.device_id = device_id.encode("utf-8") if device_id is not None else None
+        inp.text_offsets, inp.text_bytes, inp.text_kind = ptr(text[0]), (ptr(text[1]) if text[1].size else None), ptr(text[2])
+        k = len(idx)
+        offsets = np.zeros(k + 1, np.int64)
+        fallback = np.zeros(max(k, 1), np.uint8)
+        needed = C.c_int64(0)
+        lib = L.lib()
+        rc = lib.smsgate_emit_json(C.byref(inp), mode, k, idx.ctypes.data, offsets.ctypes.data, None, 0, None, C.byref(needed))
+        if rc:
+            raise L.SmsgateError(rc, "emit_json: bad input")
+        out = np.zeros(max(needed.value, 1), np.uint8)
+        rc = lib.smsgate_emit_json(C.byref(inp), mode, k, idx.ctypes.data, offsets.ctypes.data, out.ctypes.data, out.size,
+                                   fallback.ctypes.data, C.byref(needed))
+        if rc:
+            raise L.SmsgateError(rc, "emit_json failed")
+        return offsets, out[:needed.value], fallback[:k]
+
     def parsed_payloads(self) -> list:
         """The `sms.parsed` payloads of the surviving records, in replay order: what `publish_parsed_sms`
-        puts on the wire, `sms.model_dump_json().encode('utf-8')` (libs/nats_utils.py:127, worker.py:183)."""
-        return [self.parsed(int(i)).model_dump_json().encode("utf-8") for i in self.survivor_indices()]
+        puts on the wire, `sms.model_dump_json().encode('utf-8')` (libs/nats_utils.py:127, worker.py:183).
+        Assembled as bytes by smsgate_emit_json; only rows it declines go through pydantic."""
+        idx = self.survivor_indices()
+        if getattr(self.table, "text", None) is None:
+            return [self.parsed(int(i)).model_dump_json().encode("utf-8") for i in idx]
+        off, data, fb = self.emit_json(idx, 0)
+        raw = data.tobytes()
+        return [raw[off[k]:off[k + 1]] if not fb[k] else self.parsed(int(i)).model_dump_json().encode("utf-8")
+                for k, i in enumerate(idx)]
 
     def pocketbase_records(self) -> list:
         """The record dict `upsert_parsed_sms` sends to PocketBase for every surviving record

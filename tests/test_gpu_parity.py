@@ -334,7 +334,7 @@ def test_native_cache_loader_equals_python_loader(engine, tmp_path):
     for f in ("keys", "val_offsets", "val_bytes", "eflags", "date_packed"):
         assert np.array_equal(getattr(got, f), getattr(want, f)), f
     assert got.skipped == want.skipped and got.host_dates == want.host_dates
-    assert 0 < got.host_decoded < 10 and got.host_dates_resolved < 20
+    assert 0 < got.host_decoded < 10 and got.host_dates_resolved < want.m // 4   # dates outside the strict form: the host chain, per entry
     assert all(got.values[e] == want.values[e] for e in range(0, want.m, 97))
     batch = Batch.from_strings(backup.bodies, backup.senders, backup.date_ms)
     a = engine.replay(batch, NOW)
