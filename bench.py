@@ -294,8 +294,10 @@ def time_overlapped(ov, R, steps, warmup, barrier, copies=3):
     l0 = ov.launch_count
     start, end = ev(), ev()
     start.record(ov.main)
+    h0 = time.perf_counter()
     for k in range(steps):
         go(warmup + k, True)
+    time_overlapped.host_submit_ms = (time.perf_counter() - h0) * 1e3 / steps      # host time to queue one step
     for d in ov.done:
         ov.main.wait_event(d)
     end.record(ov.main)
@@ -512,6 +514,7 @@ def run_ours(args, rank, world, local_rank):
         "e2e": {"value": world * n / (e2e * 1e-3), "unit": UNIT, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
                 "ms_per_step": e2e},
         "gpu_launches": int(launches),
+        "host_submit_ms_per_step": time_overlapped.host_submit_ms,
         "roofline": {"bound": "hbm", "kernel": "k_scan_keys", "achieved": achieved, "peak": peak, "unit": "GB/s",
                      "frac": achieved / peak, "traffic": traffic, "peak_source": peak_src,
                      "kernel_ms": k1, "kernel_share_of_step": k1 / step,

@@ -398,6 +398,15 @@ int smsgate_p2p_filter_reduce(smsgate_ctx* ctx, const smsgate_p2p* p);
  * so it is scheduled even while another stream's kernels fill the SMs.  A rank that waits ~2 s gives up and
  * raises the overflow flag (reported as 2 by smsgate_p2p_resolve). */
 int smsgate_p2p_barrier(smsgate_ctx* ctx, const smsgate_p2p* p, int epoch);
+/* Let the join kernel's fused upsert insert (smsgate_join_route_dedup, smsgate_replay_host*) mark this rank's
+ * prefilter bitmap as it goes, so that smsgate_p2p_filter_push has no pass of its own over the batch left
+ * (bitmap_words must equal the descriptor's; 0 switches it off). */
+int smsgate_p2p_fuse_filter(smsgate_ctx* ctx, int64_t bitmap_words);
+/* The whole exchange of one batch in one call: filter_push, barrier, filter_reduce, barrier (when the descriptor
+ * has bitmaps), scatter, barrier, merge, barrier, resolve - barriers numbered epoch_base+1 ....  Returns the number
+ * of barriers used (>= 0) or a negative SMSGATE_E_* code. */
+int smsgate_p2p_exchange(smsgate_ctx* ctx, int64_t n, int64_t base_index, int parity, int epoch_base,
+                         const smsgate_outputs* out, const smsgate_p2p* p);
 /* h_overflow (optional, host): set to 1 if an inbox ever overflowed, 2 if a barrier timed out; passing it synchronises. */
 int smsgate_p2p_resolve(smsgate_ctx* ctx, int64_t n, int64_t base_index, const smsgate_outputs* out,
                         const smsgate_p2p* p, int* h_overflow);

@@ -152,6 +152,8 @@ def lib():
         "smsgate_dedup_apply": (i32, [vp, i64, i64, i64, vp, vp, C.POINTER(Outputs)]),
         "smsgate_p2p_reserve": (i32, [vp, i64]),
         "smsgate_p2p_barrier": (i32, [vp, C.POINTER(P2P), i32]),
+        "smsgate_p2p_fuse_filter": (i32, [vp, i64]),
+        "smsgate_p2p_exchange": (i32, [vp, i64, i64, i32, i32, C.POINTER(Outputs), C.POINTER(P2P)]),
         "smsgate_p2p_reserve_filter": (i32, [vp, i64]),
         "smsgate_p2p_filter_push": (i32, [vp, i64, C.POINTER(Outputs), C.POINTER(P2P)]),
         "smsgate_p2p_filter_reduce": (i32, [vp, C.POINTER(P2P)]),

@@ -545,7 +545,7 @@ __global__ void __launch_bounds__(256, K2_MIN_BLOCKS)
 k_join_route(int64_t n, const uint8_t* __restrict__ cache_key, const uint8_t* __restrict__ flags,
              const int32_t* __restrict__ body_date, int64_t now_packed, CacheView C, JoinOut out,
              DedupScratch D, int64_t dedup_i0, const uint8_t* __restrict__ dedup_ids,
-             const int64_t* __restrict__ phone_dt) {
+             const int64_t* __restrict__ phone_dt, uint32_t* __restrict__ key_bits, int64_t key_bits_words) {
     const int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
     if (i >= n) return;
     const uint4* kp = reinterpret_cast<const uint4*>(cache_key + i * 32);
@@ -614,8 +614,16 @@ k_join_route(int64_t n, const uint8_t* __restrict__ cache_key, const uint8_t* __
     // fused upsert-table insert (the whole-path calls): message i of this launch is message dedup_i0 + i of
     // the batch the table was cleared for; saves a launch and a second pass over msg_id / status
     if (D.tab) {
-        if (r.status == SG_ST_UPSERT) dedup_insert_one(dedup_i0 + i, dedup_ids, D);
-        else D.slot_of[dedup_i0 + i] = -1;
+        if (r.status == SG_ST_UPSERT) {
+            dedup_insert_one(dedup_i0 + i, dedup_ids, D);
+            // multi-GPU prefilter: mark the key in this rank's bitmap right here (k_bits_build's work, same bit
+            // choice as key_bit()) instead of in another pass over msg_id / slot_of on the exchange stream
+            if (key_bits) {
+                const uint32_t h = reinterpret_cast<const uint32_t*>(dedup_ids + (dedup_i0 + i) * 20)[2] &
+                                   (uint32_t)(key_bits_words * 32 - 1);
+                atomicOr(&key_bits[h >> 5], 1u << (h & 31));
+            }
+        } else D.slot_of[dedup_i0 + i] = -1;
     }
 }
 
@@ -767,6 +775,8 @@ struct smsgate_ctx {
     int64_t xml_attr_total = -1;
     int sm_count = 148;
     int scan_ctas = 0;                       // CTAs of k_scan_keys, 0 = one per SM (smsgate_set_scan_ctas)
+    int64_t fuse_bits_words = 0;             // > 0: the join's fused insert also marks the prefilter bitmap (smsgate_p2p_fuse_filter)
+    bool bits_ready = false;                 // ... and has done so for the batch in the dedup table
     const int64_t* phone_dt = nullptr;       // per-message phone timestamps for the next join (smsgate_set_phone_dates)
     bool cache_shared = false;               // the cache arrays belong to another context (smsgate_cache_share)
     std::string err;
@@ -1618,9 +1628,12 @@ static int join_route_impl(smsgate_ctx* ctx, int64_t n, int64_t now_packed, cons
     k_join_route<<<(unsigned)((n + 255) / 256), 256, 0, ctx->stream>>>(n, out->cache_key, out->flags, out->body_date,
                                                                         now_packed, C, jo, D ? *D : none, dedup_i0,
                                                                         dedup_ids,
-                                                                        ctx->phone_dt);
+                                                                        ctx->phone_dt,
+                                                                        (D && ctx->fuse_bits_words) ? ctx->p2p_bits : nullptr,
+                                                                        ctx->fuse_bits_words);
     ctx->launches += 1;
     CUDA_TRY(ctx, cudaGetLastError());
+    if (D && ctx->fuse_bits_words > 0 && ctx->p2p_bits) ctx->bits_ready = true;
     return SMSGATE_OK;
 }
 
@@ -1634,6 +1647,9 @@ static int dedup_prepare(smsgate_ctx* ctx, int64_t n, DedupScratch* D) {
     if (cap > ctx->dd_cap) cap = ctx->dd_cap;
     cudaStream_t st = ctx->stream;
     CUDA_TRY(ctx, cudaMemsetAsync(ctx->d_dtab, 0xFF, cap * sizeof(int2), st));
+    ctx->bits_ready = false;
+    if (ctx->fuse_bits_words > 0 && ctx->p2p_bits && ctx->fuse_bits_words <= ctx->p2p_bits_words)
+        CUDA_TRY(ctx, cudaMemsetAsync(ctx->p2p_bits, 0, (size_t)ctx->fuse_bits_words * 4, st));
     *D = DedupScratch{ctx->d_dtab, ctx->d_slot_of, cap - 1};
     return SMSGATE_OK;
 }
@@ -2565,10 +2581,14 @@ extern "C" int smsgate_p2p_filter_push(smsgate_ctx* ctx, int64_t n, const smsgat
     if (V.bitmap_words > ctx->p2p_bits_words) return fail(ctx, SMSGATE_E_STATE, "p2p_filter_push: call smsgate_p2p_reserve_filter first");
     CUDA_TRY(ctx, cudaSetDevice(ctx->device));
     cudaStream_t st = ctx->stream;
-    CUDA_TRY(ctx, cudaMemsetAsync(ctx->p2p_bits, 0, (size_t)V.bitmap_words * 4, st));
-    if (n > 0) k_bits_build<<<(unsigned)((n + XCH_THREADS - 1) / XCH_THREADS), XCH_THREADS, 0, st>>>(n, out->msg_id, ctx->d_slot_of, ctx->p2p_bits, V.bitmap_words);
+    const bool fused = ctx->bits_ready && ctx->fuse_bits_words == V.bitmap_words;    // the join kernel marked the keys already
+    ctx->bits_ready = false;
+    if (!fused) {
+        CUDA_TRY(ctx, cudaMemsetAsync(ctx->p2p_bits, 0, (size_t)V.bitmap_words * 4, st));
+        if (n > 0) k_bits_build<<<(unsigned)((n + XCH_THREADS - 1) / XCH_THREADS), XCH_THREADS, 0, st>>>(n, out->msg_id, ctx->d_slot_of, ctx->p2p_bits, V.bitmap_words);
+    }
     k_bits_push<<<(unsigned)ctx->sm_count * 4, XCH_THREADS, 0, st>>>(ctx->p2p_bits, V);
-    ctx->launches += n > 0 ? 2 : 1;
+    ctx->launches += (n > 0 && !fused) ? 2 : 1;
     CUDA_TRY(ctx, cudaGetLastError());
     return SMSGATE_OK;
 }
@@ -2599,6 +2619,35 @@ extern "C" int smsgate_p2p_barrier(smsgate_ctx* ctx, const smsgate_p2p* p, int e
     ctx->launches += 1;
     CUDA_TRY(ctx, cudaGetLastError());
     return SMSGATE_OK;
+}
+
+extern "C" int smsgate_p2p_fuse_filter(smsgate_ctx* ctx, int64_t bitmap_words) {
+    if (!ctx) return SMSGATE_E_ARG;
+    if (bitmap_words < 0 || bitmap_words > ctx->p2p_bits_words)
+        return fail(ctx, SMSGATE_E_STATE, "p2p_fuse_filter: call smsgate_p2p_reserve_filter for that many words first");
+    ctx->fuse_bits_words = bitmap_words;
+    ctx->bits_ready = false;
+    return SMSGATE_OK;
+}
+
+// The whole exchange of one batch queued by ONE call (the steps are the entry points above, in the order
+// dist.GlobalDedupP2P used to issue them from Python): a multi-GPU step is launch-bound on the host otherwise.
+extern "C" int smsgate_p2p_exchange(smsgate_ctx* ctx, int64_t n, int64_t base_index, int parity, int epoch_base,
+                                    const smsgate_outputs* out, const smsgate_p2p* p) {
+    if (!ctx || !p) return SMSGATE_E_ARG;
+    int rc, e = epoch_base;
+    if (p->bitmap_words) {
+        if ((rc = smsgate_p2p_filter_push(ctx, n, out, p))) return rc;
+        if ((rc = smsgate_p2p_barrier(ctx, p, ++e))) return rc;
+        if ((rc = smsgate_p2p_filter_reduce(ctx, p))) return rc;
+        if ((rc = smsgate_p2p_barrier(ctx, p, ++e))) return rc;
+    }
+    if ((rc = smsgate_p2p_scatter(ctx, n, base_index, parity, out, p))) return rc;
+    if ((rc = smsgate_p2p_barrier(ctx, p, ++e))) return rc;
+    if ((rc = smsgate_p2p_merge(ctx, parity, p))) return rc;
+    if ((rc = smsgate_p2p_barrier(ctx, p, ++e))) return rc;
+    if ((rc = smsgate_p2p_resolve(ctx, n, base_index, out, p, nullptr))) return rc;
+    return e - epoch_base;                       // barriers used: the caller's next epoch_base is this much further
 }
 
 extern "C" int smsgate_p2p_reserve_filter(smsgate_ctx* ctx, int64_t bitmap_words) {

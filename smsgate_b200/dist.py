@@ -179,6 +179,8 @@ class GlobalDedupP2P:
         L.check(engine._ctx, L.lib().smsgate_p2p_reserve(engine._ctx, self.capacity))
         if self.bitmap_words:
             L.check(engine._ctx, L.lib().smsgate_p2p_reserve_filter(engine._ctx, self.bitmap_words))
+            # the join kernel marks the keys in the bitmap while it inserts them into the upsert table
+            L.check(engine._ctx, L.lib().smsgate_p2p_fuse_filter(engine._ctx, self.bitmap_words))
         self._h[1].barrier(channel=0)          # every rank's counters and flags are zero before anyone scatters
         self.step = 0
         self.epoch = 0
@@ -193,21 +195,12 @@ class GlobalDedupP2P:
         if n > self.n_max:
             raise ValueError(f"shard of {n} messages exceeds the n_max={self.n_max} this exchange was sized for")
         parity = self.step & 1
-
-        def barrier():
-            # in-stream, no host round trip, one tiny block (smsgate_p2p_barrier): schedulable next to anything
-            self.epoch += 1
-            L.check(eng._ctx, lib.smsgate_p2p_barrier(eng._ctx, C.byref(self.desc), self.epoch))
-        if self.bitmap_words:
-            L.check(eng._ctx, lib.smsgate_p2p_filter_push(eng._ctx, n, C.byref(out), C.byref(self.desc)))
-            barrier()                          # every rank's bitmap slices have landed at their owners
-            L.check(eng._ctx, lib.smsgate_p2p_filter_reduce(eng._ctx, C.byref(self.desc)))
-            barrier()                          # every rank holds the complete collision bitmap
-        L.check(eng._ctx, lib.smsgate_p2p_scatter(eng._ctx, n, int(base_index), parity, C.byref(out), C.byref(self.desc)))
-        barrier()                              # all records have landed in their owners' inboxes
-        L.check(eng._ctx, lib.smsgate_p2p_merge(eng._ctx, parity, C.byref(self.desc)))
-        barrier()                              # all verdicts have landed in their home arrays
-        L.check(eng._ctx, lib.smsgate_p2p_resolve(eng._ctx, n, int(base_index), C.byref(out), C.byref(self.desc), None))
+        # filter_push, barrier, filter_reduce, barrier, scatter, barrier, merge, barrier, resolve: queued by one C
+        # call (smsgate_p2p_exchange); the barriers are in-stream kernels (smsgate_p2p_barrier), no host round trip
+        used = lib.smsgate_p2p_exchange(eng._ctx, n, int(base_index), parity, self.epoch, C.byref(out), C.byref(self.desc))
+        if used < 0:
+            L.check(eng._ctx, used)
+        self.epoch += used
         self.step += 1
 
     def last_received(self) -> int:

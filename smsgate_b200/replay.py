@@ -302,6 +302,7 @@ class ReplayEngine:
             raise L.SmsgateError(rc, (self._lib.smsgate_last_error(None) or b"").decode())
         self.table: Optional[CacheTable] = None
         self._pinned: dict = {}
+        self._outputs_cache: dict = {}
         self._generation = 0             # bumped by every host-buffer replay (stale-result detection)
         self.host_fallbacks = 0          # XML files handed to ElementTree because of their dialect (xml_ingest)
 
@@ -557,9 +558,22 @@ class ReplayEngine:
             cols[name] = torch.empty(shape, dtype=tdt, device=dev)
         return cols
 
-    @staticmethod
-    def _dev_outputs(cols: dict) -> L.Outputs:
-        return L.Outputs(**{k: v.data_ptr() for k, v in cols.items()})
+    def _dev_outputs(self, cols: dict) -> L.Outputs:
+        """struct smsgate_outputs over a set of device columns; built once per column set (a step of the
+        multi-GPU pipeline makes three C calls on the same columns and is launch-bound on the host).  The
+        cache holds no reference to the tensors: an entry is valid while the dict still has the same size and
+        its first and last columns still sit at the same addresses."""
+        key = id(cols)
+        vals = list(cols.values())
+        sig = (len(vals), vals[0].data_ptr(), vals[-1].data_ptr()) if vals else (0, 0, 0)
+        hit = self._outputs_cache.get(key)
+        if hit is not None and hit[0] == sig:
+            return hit[1]
+        out = L.Outputs(**{k: v.data_ptr() for k, v in cols.items()})
+        if len(self._outputs_cache) > 16:
+            self._outputs_cache.clear()
+        self._outputs_cache[key] = (sig, out)
+        return out
 
     def scan_keys(self, d_bytes, d_offsets, cols: dict) -> None:
         n = d_offsets.numel() - 1

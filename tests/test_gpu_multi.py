@@ -190,6 +190,8 @@ class _EmulatedPeers:
             L.check(eng._ctx, lib.smsgate_p2p_reserve(eng._ctx, self.capacity))
             if self.words:
                 L.check(eng._ctx, lib.smsgate_p2p_reserve_filter(eng._ctx, self.words))
+                if world != 2:           # the join kernel marks the bitmap itself (as dist.GlobalDedupP2P sets it up)
+                    L.check(eng._ctx, lib.smsgate_p2p_fuse_filter(eng._ctx, self.words))
             self.desc.append(d)
         self.step = 0
 
