@@ -358,8 +358,9 @@ int smsgate_dedup_apply(smsgate_ctx* ctx, int64_t n, int64_t base_index, int64_t
  * mapped pointers in `smsgate_p2p`.  smsgate_p2p_scatter stores the export records
  * straight into the owners' inboxes (one remote atomic per block and destination reserves
  * the range), smsgate_p2p_merge stores a verdict straight into the home rank's gfl array
- * whenever another rank's copy of the key changes it, smsgate_p2p_resolve rewrites
- * survivor / first_seen / last_idx.
+ * whenever another rank's copy of the key changes it (and sets the slot's bit in the home rank's override
+ * bitmap), smsgate_p2p_resolve then rewrites survivor / first_seen / last_idx of exactly those messages: the
+ * columns must already hold the local verdicts (smsgate_dedup / smsgate_join_route_dedup).
  * The caller puts a cross-GPU barrier between scatter and merge and between merge and
  * resolve; nothing is copied through host memory and no count is exchanged.
  * `parity` alternates 0/1 from one batch to the next (two arrival counters). */
@@ -376,6 +377,10 @@ typedef struct smsgate_p2p {
     int64_t bitmap_words;                 /* power of two in [64, 2^26]; about 16 bits per key of the whole job is plenty */
     int32_t* flags[SMSGATE_MAX_WORLD];    /* [SMSGATE_MAX_WORLD] int32 per rank, zero before the first use: arrival flags of
                                              smsgate_p2p_barrier (NULL when the caller brings its own barrier) */
+    uint32_t* ovr[SMSGATE_MAX_WORLD];     /* [2 * ovr_words] per rank, zero before the first batch: one bit per local slot (one half
+                                             per parity) set by the owner that answered the slot with a different global first /
+                                             last; smsgate_p2p_resolve rewrites only those */
+    int64_t ovr_words;                    /* >= gfl_slots / 32 */
     int64_t gfl_slots;                    /* slots every gfl array holds (a pair of int64 each); a batch whose table would
                                              need more is refused with SMSGATE_E_LIMIT instead of storing out of bounds */
 } smsgate_p2p;
@@ -408,7 +413,7 @@ int smsgate_p2p_fuse_filter(smsgate_ctx* ctx, int64_t bitmap_words);
 int smsgate_p2p_exchange(smsgate_ctx* ctx, int64_t n, int64_t base_index, int parity, int epoch_base,
                          const smsgate_outputs* out, const smsgate_p2p* p);
 /* h_overflow (optional, host): set to 1 if an inbox ever overflowed, 2 if a barrier timed out; passing it synchronises. */
-int smsgate_p2p_resolve(smsgate_ctx* ctx, int64_t n, int64_t base_index, const smsgate_outputs* out,
+int smsgate_p2p_resolve(smsgate_ctx* ctx, int64_t n, int64_t base_index, int parity, const smsgate_outputs* out,
                         const smsgate_p2p* p, int* h_overflow);
 
 /* ---- the replay, host buffers --------------------------------------------

@@ -80,7 +80,7 @@ class P2P(C.Structure):
                 ("inbox", C.c_void_p * 64), ("in_count", C.c_void_p * 64),
                 ("gfl", C.c_void_p * 64), ("capacity", C.c_int64),
                 ("stage", C.c_void_p * 64), ("collide", C.c_void_p * 64), ("bitmap_words", C.c_int64),
-                ("flags", C.c_void_p * 64), ("gfl_slots", C.c_int64)]
+                ("flags", C.c_void_p * 64), ("ovr", C.c_void_p * 64), ("ovr_words", C.c_int64), ("gfl_slots", C.c_int64)]
 
 
 class LibraryMissing(RuntimeError):
@@ -159,7 +159,7 @@ def lib():
         "smsgate_p2p_filter_reduce": (i32, [vp, C.POINTER(P2P)]),
         "smsgate_p2p_scatter": (i32, [vp, i64, i64, i32, C.POINTER(Outputs), C.POINTER(P2P)]),
         "smsgate_p2p_merge": (i32, [vp, i32, C.POINTER(P2P)]),
-        "smsgate_p2p_resolve": (i32, [vp, i64, i64, C.POINTER(Outputs), C.POINTER(P2P), vp]),
+        "smsgate_p2p_resolve": (i32, [vp, i64, i64, i32, C.POINTER(Outputs), C.POINTER(P2P), vp]),
         "smsgate_dedup_static": (i32, [i32, vp, i64, i64, vp, vp, vp, vp, vp, C.c_char_p, i32]),
     }
     for name, (res, args) in sigs.items():

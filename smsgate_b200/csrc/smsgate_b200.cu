@@ -2287,6 +2287,8 @@ struct P2PView {                 // smsgate_p2p, by value, for the kernels
     uint32_t* collide[SMSGATE_MAX_WORLD]; // prefilter: bits set on two or more ranks
     int64_t bitmap_words;                 // 0 = no prefilter
     int32_t* flags[SMSGATE_MAX_WORLD];    // per rank [SMSGATE_MAX_WORLD] arrival flags of smsgate_p2p_barrier (may be NULL)
+    uint32_t* ovr[SMSGATE_MAX_WORLD];     // per rank [2 * ovr_words]: bit per local slot "an owner overrode this slot's verdict", one half per parity
+    int64_t ovr_words;
 };
 
 // ---- prefilter.  Only a key that occurs on two or more ranks needs the exchange; for every other key the
@@ -2366,8 +2368,6 @@ k_p2p_scatter(int64_t n, int64_t base_index, int parity, const uint8_t* __restri
         if (sl >= 0) {
             f = (uint64_t)(base_index + fl.x);
             l = (uint64_t)(base_index + fl.y);
-            // what this rank knows already; the owner only writes back when another rank changes it
-            P.gfl[P.rank][sl] = make_longlong2((long long)f, (long long)l);
             if (collide) {
                 const uint32_t h = key_bit(msg_id + i * 20, P.bitmap_words);
                 if (!((collide[h >> 5] >> (h & 31)) & 1u)) sl = -1;          // no other rank can hold this key
@@ -2452,28 +2452,33 @@ k_p2p_verdict(const int32_t* __restrict__ count_ptr, const P2PRecord* __restrict
         const unsigned long long f = ((unsigned long long)r.first_hi << 32) | r.first_lo;
         const unsigned long long l = ((unsigned long long)r.last_hi << 32) | r.last_lo;
         // only a key that another rank also holds changes the home rank's view: one 16-byte peer store
-        if (e.first != f || e.last != l) P.gfl[r.src_rank][r.home_slot] = make_longlong2((long long)e.first, (long long)e.last);
+        if (e.first != f || e.last != l) {
+            P.gfl[r.src_rank][r.home_slot] = make_longlong2((long long)e.first, (long long)e.last);
+            atomicOr_system(&P.ovr[r.src_rank][(int64_t)parity * P.ovr_words + (r.home_slot >> 5)], 1u << (r.home_slot & 31));
+        }
     }
 }
 
 __global__ void __launch_bounds__(XCH_THREADS, XCH_MIN_BLOCKS)
 k_p2p_resolve(int64_t n, int64_t base_index, const int32_t* __restrict__ slot_of, const longlong2* __restrict__ gfl,
+              uint32_t* __restrict__ ovr, int64_t ovr_words, int parity,
               uint8_t* __restrict__ survivor, uint8_t* __restrict__ first_seen, int64_t* __restrict__ last_idx) {
+    // The columns already hold this rank's local verdicts (k_dedup_resolve).  Only a key that another rank also
+    // holds AND whose global first / last differs from the local one was answered by its owner: those slots have
+    // their bit set in this parity's half of `ovr`, and only their messages are rewritten.  The other half is
+    // cleared here for the next batch (its owners write it after the next batch's barriers).
     const int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+    uint32_t* next_half = ovr + (int64_t)(parity ^ 1) * ovr_words;
+    for (int64_t w = i; w < ovr_words; w += (int64_t)gridDim.x * blockDim.x) next_half[w] = 0;
     if (i >= n) return;
     const int32_t sl = slot_of[i];
-    uint8_t sv = 0, fs = 0;
-    int64_t li = -1;
-    if (sl >= 0) {
-        const longlong2 v = gfl[sl];
-        const int64_t g = base_index + i;
-        li = v.y;
-        sv = (li == g);
-        fs = (v.x == g);
-    }
-    if (survivor) survivor[i] = sv;
-    if (first_seen) first_seen[i] = fs;
-    if (last_idx) last_idx[i] = li;
+    if (sl < 0) return;
+    if (!((ovr[(int64_t)parity * ovr_words + (sl >> 5)] >> (sl & 31)) & 1u)) return;
+    const longlong2 v = gfl[sl];
+    const int64_t g = base_index + i;
+    if (survivor) survivor[i] = (v.y == g);
+    if (first_seen) first_seen[i] = (v.x == g);
+    if (last_idx) last_idx[i] = v.y;
 }
 
 // Cross-GPU barrier from inside the stream, without a host round trip and small enough (one warp-sized block, a
@@ -2509,7 +2514,12 @@ static int p2p_view(smsgate_ctx* ctx, const smsgate_p2p* p, P2PView* v) {
         v->in_count[w] = p->in_count[w];
         v->gfl[w] = reinterpret_cast<longlong2*>(p->gfl[w]);
     }
-    for (int w = 0; w < p->world; ++w) v->flags[w] = p->flags[w];
+    for (int w = 0; w < p->world; ++w) {
+        v->flags[w] = p->flags[w];
+        if (!p->ovr[w] || p->ovr_words < 1) return fail(ctx, SMSGATE_E_ARG, "p2p: NULL override bitmap");
+        v->ovr[w] = p->ovr[w];
+    }
+    v->ovr_words = p->ovr_words;
     v->bitmap_words = p->bitmap_words;
     if (p->bitmap_words) {
         if (p->bitmap_words < 64 || (p->bitmap_words & (p->bitmap_words - 1)) || p->bitmap_words > (1ll << 26))
@@ -2557,6 +2567,8 @@ extern "C" int smsgate_p2p_scatter(smsgate_ctx* ctx, int64_t n, int64_t base_ind
         return fail(ctx, SMSGATE_E_LIMIT, "p2p_scatter: the batch needs " + std::to_string((unsigned long long)cap) +
                                               " verdict slots, the descriptor's gfl arrays hold " +
                                               std::to_string((long long)p->gfl_slots));
+    if (n > 0 && (uint64_t)p->ovr_words * 32 < cap)
+        return fail(ctx, SMSGATE_E_LIMIT, "p2p_scatter: the descriptor's override bitmaps are smaller than the batch's table");
     if (n > 0 && n > p->capacity / p->world)
         return fail(ctx, SMSGATE_E_LIMIT, "p2p_scatter: the batch exceeds capacity / world messages per rank");
     DedupScratch D{ctx->d_dtab, ctx->d_slot_of, cap - 1};
@@ -2646,7 +2658,7 @@ extern "C" int smsgate_p2p_exchange(smsgate_ctx* ctx, int64_t n, int64_t base_in
     if ((rc = smsgate_p2p_barrier(ctx, p, ++e))) return rc;
     if ((rc = smsgate_p2p_merge(ctx, parity, p))) return rc;
     if ((rc = smsgate_p2p_barrier(ctx, p, ++e))) return rc;
-    if ((rc = smsgate_p2p_resolve(ctx, n, base_index, out, p, nullptr))) return rc;
+    if ((rc = smsgate_p2p_resolve(ctx, n, base_index, parity, out, p, nullptr))) return rc;
     return e - epoch_base;                       // barriers used: the caller's next epoch_base is this much further
 }
 
@@ -2681,7 +2693,7 @@ extern "C" int smsgate_p2p_merge(smsgate_ctx* ctx, int parity, const smsgate_p2p
     return SMSGATE_OK;
 }
 
-extern "C" int smsgate_p2p_resolve(smsgate_ctx* ctx, int64_t n, int64_t base_index, const smsgate_outputs* out,
+extern "C" int smsgate_p2p_resolve(smsgate_ctx* ctx, int64_t n, int64_t base_index, int parity, const smsgate_outputs* out,
                                    const smsgate_p2p* p, int* h_overflow) {
     if (!ctx) return SMSGATE_E_ARG;
     P2PView V;
@@ -2693,6 +2705,7 @@ extern "C" int smsgate_p2p_resolve(smsgate_ctx* ctx, int64_t n, int64_t base_ind
     cudaStream_t st = ctx->stream;
     if (n > 0) {
         k_p2p_resolve<<<(unsigned)((n + XCH_THREADS - 1) / XCH_THREADS), XCH_THREADS, 0, st>>>(n, base_index, ctx->d_slot_of, V.gfl[V.rank],
+                                                                   V.ovr[V.rank], V.ovr_words, parity & 1,
                                                                    out->survivor, out->first_seen, out->last_idx);
         ctx->launches += 1;
     }

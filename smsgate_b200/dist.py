@@ -149,6 +149,9 @@ class GlobalDedupP2P:
         self._count.zero_()
         self._flags = symm_mem.empty(L.MAX_WORLD, dtype=torch.int32, device=dev)     # smsgate_p2p_barrier arrival flags
         self._flags.zero_()
+        self.ovr_words = cap_slots // 32
+        self._ovr = symm_mem.empty(2 * self.ovr_words, dtype=torch.int32, device=dev)   # override bits, one half per parity
+        self._ovr.zero_()
         bufs = [self._inbox, self._count, self._gfl]
         # prefilter bitmaps: about 16 bits per key of the whole job (a false positive only costs one record)
         self.bitmap_words = 0
@@ -160,6 +163,7 @@ class GlobalDedupP2P:
             self._stage = symm_mem.empty(self.world * (words // self.world + 12), dtype=torch.int32, device=dev)
             self._collide = symm_mem.empty(words, dtype=torch.int32, device=dev)
             bufs += [self._stage, self._collide]
+        bufs.append(self._ovr)
         bufs.append(self._flags)
         torch.cuda.synchronize()
         self._h = [symm_mem.rendezvous(t, group) for t in bufs]
@@ -167,12 +171,14 @@ class GlobalDedupP2P:
         self.desc.world, self.desc.rank, self.desc.capacity = self.world, self.rank, self.capacity
         self.desc.bitmap_words = self.bitmap_words
         self.desc.gfl_slots = cap_slots
+        self.desc.ovr_words = cap_slots // 32
         self.n_max = n_max
         for w in range(self.world):
             self.desc.inbox[w] = self._h[0].buffer_ptrs[w]
             self.desc.in_count[w] = self._h[1].buffer_ptrs[w]
             self.desc.gfl[w] = self._h[2].buffer_ptrs[w]
             self.desc.flags[w] = self._h[-1].buffer_ptrs[w]
+            self.desc.ovr[w] = self._h[-2].buffer_ptrs[w]
             if self.bitmap_words:
                 self.desc.stage[w] = self._h[3].buffer_ptrs[w]
                 self.desc.collide[w] = self._h[4].buffer_ptrs[w]
@@ -214,7 +220,7 @@ class GlobalDedupP2P:
         """True if an inbox ever overflowed (some rank exceeded n_max).  Synchronises."""
         flag = C.c_int(0)
         out = L.Outputs()
-        L.check(self.engine._ctx, L.lib().smsgate_p2p_resolve(self.engine._ctx, 0, 0, C.byref(out), C.byref(self.desc),
+        L.check(self.engine._ctx, L.lib().smsgate_p2p_resolve(self.engine._ctx, 0, 0, 0, C.byref(out), C.byref(self.desc),
                                                               C.byref(flag)))
         if flag.value == 2:
             raise RuntimeError("a cross-GPU barrier of the exchange timed out (a rank fell behind by more than ~2 s)")

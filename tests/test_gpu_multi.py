@@ -167,6 +167,7 @@ class _EmulatedPeers:
         self.inbox = [torch.zeros(self.capacity * L.P2P_RECORD_BYTES, dtype=torch.uint8, device=dev) for _ in range(world)]
         self.count = [torch.zeros(16, dtype=torch.int32, device=dev) for _ in range(world)]
         self.gfl = [torch.zeros(2 * cap_slots, dtype=torch.int64, device=dev) for _ in range(world)]
+        self.ovr = [torch.zeros(2 * (cap_slots // 32), dtype=torch.int32, device=dev) for _ in range(world)]
         self.words = 0
         if prefilter:
             words = 64
@@ -180,10 +181,12 @@ class _EmulatedPeers:
         for r, eng in enumerate(engines):
             d = L.P2P()
             d.world, d.rank, d.capacity, d.bitmap_words, d.gfl_slots = world, r, self.capacity, self.words, cap_slots
+            d.ovr_words = cap_slots // 32
             for w in range(world):
                 d.inbox[w] = self.inbox[w].data_ptr()
                 d.in_count[w] = self.count[w].data_ptr()
                 d.gfl[w] = self.gfl[w].data_ptr()
+                d.ovr[w] = self.ovr[w].data_ptr()
                 if self.words:
                     d.stage[w] = self.stage[w].data_ptr()
                     d.collide[w] = self.collide[w].data_ptr()
@@ -209,7 +212,7 @@ class _EmulatedPeers:
         for r in rng:
             L.check(E[r]._ctx, lib.smsgate_p2p_merge(E[r]._ctx, parity, C.byref(D[r])))
         for r in rng:
-            L.check(E[r]._ctx, lib.smsgate_p2p_resolve(E[r]._ctx, ns[r], bases[r], C.byref(outs[r]), C.byref(D[r]), None))
+            L.check(E[r]._ctx, lib.smsgate_p2p_resolve(E[r]._ctx, ns[r], bases[r], parity, C.byref(outs[r]), C.byref(D[r]), None))
         self.step += 1
 
     def overflowed(self):
@@ -217,7 +220,7 @@ class _EmulatedPeers:
         out = L.Outputs()
         any_over = False
         for r, eng in enumerate(self.engines):
-            L.check(eng._ctx, L.lib().smsgate_p2p_resolve(eng._ctx, 0, 0, C.byref(out), C.byref(self.desc[r]), C.byref(flag)))
+            L.check(eng._ctx, L.lib().smsgate_p2p_resolve(eng._ctx, 0, 0, 0, C.byref(out), C.byref(self.desc[r]), C.byref(flag)))
             any_over |= bool(flag.value)
         return any_over
 
@@ -297,10 +300,10 @@ def test_in_stream_barrier_single_rank_and_timeout():
         # two ranks, the second never calls: rank 0's wait times out
         other = torch.zeros(L.MAX_WORLD, dtype=torch.int32, device="cuda")
         d.world = 2
-        d.inbox[1], d.in_count[1], d.gfl[1], d.flags[1] = d.inbox[0], d.in_count[0], d.gfl[0], other.data_ptr()
+        d.inbox[1], d.in_count[1], d.gfl[1], d.ovr[1], d.flags[1] = d.inbox[0], d.in_count[0], d.gfl[0], d.ovr[0], other.data_ptr()
         L.check(eng._ctx, lib.smsgate_p2p_barrier(eng._ctx, C.byref(d), 4))
         torch.cuda.synchronize()
         flag = C.c_int(0)
         out = L.Outputs()
-        L.check(eng._ctx, lib.smsgate_p2p_resolve(eng._ctx, 0, 0, C.byref(out), C.byref(d), C.byref(flag)))
+        L.check(eng._ctx, lib.smsgate_p2p_resolve(eng._ctx, 0, 0, 0, C.byref(out), C.byref(d), C.byref(flag)))
         assert flag.value == 2 and int(other[0].item()) == 4
