@@ -271,6 +271,26 @@ class ReplayResult:
         return [raw[off[k]:off[k + 1]] if not fb[k] else self.parsed(int(i)).model_dump_json().encode("utf-8")
                 for k, i in enumerate(idx)]
 
+    def pocketbase_records_json(self) -> list:
+        """The same records as `pocketbase_records`, as compact JSON bytes assembled natively
+        (smsgate_emit_json mode 1): what a bulk import into PocketBase is fed."""
+        idx = self.survivor_indices()
+        if getattr(self.table, "text", None) is None:
+            import json
+            return [json.dumps(r, ensure_ascii=False, separators=(",", ":")).encode("utf-8") for r in self.pocketbase_records()]
+        off, data, fb = self.emit_json(idx, 1)
+        raw = data.tobytes()
+        import json
+        rec = None
+        out = []
+        for k in range(len(idx)):
+            if fb[k]:
+                rec = rec if rec is not None else self.pocketbase_records()
+                out.append(json.dumps(rec[k], ensure_ascii=False, separators=(",", ":")).encode("utf-8"))
+            else:
+                out.append(raw[off[k]:off[k + 1]])
+        return out
+
     def pocketbase_records(self) -> list:
         """The record dict `upsert_parsed_sms` sends to PocketBase for every surviving record
         (libs/pocketbase.py:296-309), in replay order."""

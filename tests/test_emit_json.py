@@ -1,0 +1,84 @@
+"""smsgate_emit_json (host C++: payload bytes assembled from the replay's columns and the cache texts) against
+what pydantic produces for the same records: `ParsedSMS.model_dump_json()` (libs/nats_utils.py:127,
+worker.py:183) byte for byte, and the PocketBase record dict (libs/pocketbase.py:296-309) as JSON.
+Runs without a GPU: the columns come from the device code compiled for the CPU (tests/hostcheck)."""
+import datetime as dt
+import json
+
+import numpy as np
+
+from smsgate_b200 import _lib as L
+from smsgate_b200 import gemini_cache, synth
+from smsgate_b200.batch import Batch
+from smsgate_b200.replay import ReplayResult
+from tests import _hostcheck as H
+
+NOW = dt.datetime(2026, 1, 1)
+
+
+def _result(bodies, senders, cache):
+    sc = H.scan(bodies)
+    table = gemini_cache.build_table(cache, H.strict_date)
+    jr = H.join_route(sc, table, gemini_cache.pack_datetime(NOW))
+    cols = dict(sc)
+    cols.pop("offsets")
+    cols.update(jr)
+    batch = Batch.from_strings(bodies, senders, range(len(bodies)))
+    return ReplayResult(batch, cols, table, 0), table
+
+
+def test_payload_bytes_equal_pydantic():
+    backup = synth.generate(4000, seed=91, mixed_locale=True, miss_frac=0.1)
+    cache = dict(backup.cache)
+    keys = list(cache)
+    # strings that need JSON escaping, non-ASCII text, odd amounts, a non-ASCII currency (left to pydantic)
+    cache[keys[0]] = dict(cache[keys[0]], merchant='A "quoted" \\\\ back\\slash', city="line\\nbreak\\ttab\\x01\\x1f", address="null")
+    cache[keys[1]] = dict(cache[keys[1]], merchant="Ереван ☕ 中文", city="", address="ул. Абовяна, 12")
+    cache[keys[2]] = dict(cache[keys[2]], amount="0.0000001", balance="-12,5")
+    cache[keys[3]] = dict(cache[keys[3]], amount="0", balance="000123.4500")
+    cache[keys[4]] = dict(cache[keys[4]], currency="руб")
+    cache[keys[5]] = dict(cache[keys[5]], currency=None, merchant="x")
+    cache[keys[6]] = dict(cache[keys[6]], currency="", city=None)
+    cache[keys[7]] = dict(cache[keys[7]], date="2024-02-14 09:00:00.250000")
+    cache[keys[0]]["city"] = "line\\nbreak\\ttab\\x01\\x1f".encode().decode("unicode_escape")
+    cache[keys[0]]["merchant"] = 'A "quoted" \\ back\\slash'
+    senders = [s if i % 9 else 'S"e\\nder ß' for i, s in enumerate(backup.senders)]
+    bodies = list(backup.bodies)
+    res, table = _result(bodies, senders, cache)
+    idx = np.nonzero(np.isin(res.cols["status"], (L.ST_UPSERT, L.ST_PARSED_NO_MERCHANT)))[0]
+    assert len(idx) > 3000
+    off, data, fb = res.emit_json(idx, 0)
+    raw = data.tobytes()
+    n_fb = 0
+    for k, i in enumerate(idx):
+        want = res.parsed(int(i)).model_dump_json().encode("utf-8")
+        if fb[k]:
+            n_fb += 1
+            assert off[k] == off[k + 1]
+            continue
+        assert raw[off[k]:off[k + 1]] == want, (int(i), raw[off[k]:off[k + 1]], want)
+    assert 1 <= n_fb <= 3                                  # the non-ASCII currency (str.upper() is Python's)
+    # the PocketBase record of the same messages
+    off, data, fb = res.emit_json(idx, 1)
+    raw = data.tobytes()
+    for k, i in enumerate(idx):
+        if fb[k]:
+            continue
+        p = res.parsed(int(i))
+        want = {"msg_id": p.msg_id, "original_body": p.raw_body, "sender": p.sender, "datetime": p.date.isoformat(),
+                "card": p.card, "amount": str(p.amount), "currency": p.currency,
+                "balance": str(p.balance) if p.balance is not None else None, "merchant": p.merchant,
+                "address": p.address, "city": p.city, "txn_type": p.txn_type.value}
+        got = json.loads(raw[off[k]:off[k + 1]])
+        assert got == want and list(got) == list(want), int(i)
+
+
+def test_survivor_payloads_use_the_native_emitter():
+    backup = synth.generate(1500, seed=92, dup_frac=0.3)
+    res, table = _result(backup.bodies, backup.senders, backup.cache)
+    from oracle import replay_oracle as O
+    surv, first, last, _ = O.dedup([bytes(r) for r in res.cols["msg_id"]], (int(s) == 0 for s in res.cols["status"]))
+    res.cols["survivor"] = np.array(surv, np.uint8)
+    got = res.parsed_payloads()
+    want = [res.parsed(int(i)).model_dump_json().encode() for i in res.survivor_indices()]
+    assert got == want and len(got) > 500
