@@ -452,6 +452,13 @@ int smsgate_replay_host_records(smsgate_ctx* ctx, const uint8_t* h_bytes, const 
 int smsgate_replay_host_records_begin(smsgate_ctx* ctx, const uint8_t* h_bytes, const int64_t* h_offsets, int64_t n,
                                       int64_t now_packed, int64_t base_index, smsgate_record* h_records);
 int smsgate_replay_host_records_finish(smsgate_ctx* ctx, int64_t* h_verdict);
+/* The same with ONE byte of verdict per message instead of eight: 0 = the message is not upserted, else
+ * 0x80 | first_seen << 1 | survivor.  The index of the surviving occurrence (last_idx) stays on the device and
+ * can be fetched on request (smsgate_fetch_columns).  8 MB less to bring back per 1 M messages, all of it after
+ * the last kernel: this is the call the end-to-end figure uses. */
+int smsgate_replay_host_records8(smsgate_ctx* ctx, const uint8_t* h_bytes, const int64_t* h_offsets, int64_t n,
+                                 int64_t now_packed, int64_t base_index, smsgate_record* h_records, uint8_t* h_verdict8);
+int smsgate_replay_host_records8_finish(smsgate_ctx* ctx, uint8_t* h_verdict8);
 /* Columns of the LAST smsgate_replay_host* batch that the packed record does not carry (card, cache_key,
  * fixed_len, fixed_bytes, amount_cents, balance_cents) or any other column, copied to the non-NULL host
  * pointers of h_out on request: the device keeps every column of a batch until the next replay or reserve

@@ -141,6 +141,8 @@ def lib():
         "smsgate_replay_host_records": (i32, [vp, vp, vp, i64, i64, i64, vp, vp]),
         "smsgate_replay_host_records_begin": (i32, [vp, vp, vp, i64, i64, i64, vp]),
         "smsgate_replay_host_records_finish": (i32, [vp, vp]),
+        "smsgate_replay_host_records8": (i32, [vp, vp, vp, i64, i64, i64, vp, vp]),
+        "smsgate_replay_host_records8_finish": (i32, [vp, vp]),
         "smsgate_fetch_columns": (i32, [vp, i64, C.POINTER(Outputs)]),
         "smsgate_replay_host_timeline": (i32, [vp, C.POINTER(C.c_float), i32]),
         "smsgate_replay_host_begin": (i32, [vp, vp, vp, i64, i64, i64, C.POINTER(Outputs)]),

@@ -1815,6 +1815,16 @@ k_pack_verdict(int64_t n, const uint8_t* __restrict__ survivor, const uint8_t* _
     verdict[i] = l < 0 ? -1 : ((l << 2) | ((int64_t)(first_seen[i] & 1) << 1) | (int64_t)(survivor[i] & 1));
 }
 
+// one byte per message instead of eight: 0x80 = the message is upserted, bit 0 survivor, bit 1 first_seen; the
+// index of the surviving occurrence stays on the device (smsgate_fetch_columns: last_idx) for whoever wants it
+__global__ void __launch_bounds__(256)
+k_pack_verdict8(int64_t n, const uint8_t* __restrict__ survivor, const uint8_t* __restrict__ first_seen,
+                const int64_t* __restrict__ last_idx, uint8_t* __restrict__ verdict) {
+    const int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    verdict[i] = last_idx[i] < 0 ? 0 : (uint8_t)(0x80 | ((first_seen[i] & 1) << 1) | (survivor[i] & 1));
+}
+
 static int replay_host_begin_impl(smsgate_ctx* ctx, const uint8_t* h_bytes, const int64_t* h_offsets, int64_t n,
                                   int64_t now_packed, int64_t base_index, const smsgate_outputs* h_cols,
                                   smsgate_record* h_records) {
@@ -1916,8 +1926,8 @@ static int replay_host_begin_impl(smsgate_ctx* ctx, const uint8_t* h_bytes, cons
     return SMSGATE_OK;
 }
 
-static int replay_host_finish_impl(smsgate_ctx* ctx, const smsgate_outputs* h_cols, int64_t* h_verdict) {
-    if (!ctx || (!h_cols && !h_verdict)) return SMSGATE_E_ARG;
+static int replay_host_finish_impl(smsgate_ctx* ctx, const smsgate_outputs* h_cols, int64_t* h_verdict, uint8_t* h_verdict8 = nullptr) {
+    if (!ctx || (!h_cols && !h_verdict && !h_verdict8)) return SMSGATE_E_ARG;
     static const smsgate_outputs no_columns = {};
     const smsgate_outputs* h_out = h_cols ? h_cols : &no_columns;
     const int64_t n = ctx->host_n;
@@ -1931,9 +1941,16 @@ static int replay_host_finish_impl(smsgate_ctx* ctx, const smsgate_outputs* h_co
         ctx->launches += 1;
         CUDA_TRY(ctx, cudaGetLastError());
     }
+    if (h_verdict8) {
+        k_pack_verdict8<<<(unsigned)((n + 255) / 256), 256, 0, st>>>(n, d.survivor, d.first_seen, d.last_idx,
+                                                                     reinterpret_cast<uint8_t*>(ctx->s_verdict));
+        ctx->launches += 1;
+        CUDA_TRY(ctx, cudaGetLastError());
+    }
     CUDA_TRY(ctx, cudaEventRecord(ctx->ev_dedup, st));
     CUDA_TRY(ctx, cudaStreamWaitEvent(sout, ctx->ev_dedup, 0));
     if (h_verdict) CUDA_TRY(ctx, cudaMemcpyAsync(h_verdict, ctx->s_verdict, (size_t)n * 8, cudaMemcpyDeviceToHost, sout));
+    if (h_verdict8) CUDA_TRY(ctx, cudaMemcpyAsync(h_verdict8, ctx->s_verdict, (size_t)n, cudaMemcpyDeviceToHost, sout));
     if (h_out->survivor) CUDA_TRY(ctx, cudaMemcpyAsync(h_out->survivor, d.survivor, (size_t)n, cudaMemcpyDeviceToHost, sout));
     if (h_out->first_seen) CUDA_TRY(ctx, cudaMemcpyAsync(h_out->first_seen, d.first_seen, (size_t)n, cudaMemcpyDeviceToHost, sout));
     if (h_out->last_idx) CUDA_TRY(ctx, cudaMemcpyAsync(h_out->last_idx, d.last_idx, (size_t)n * 8, cudaMemcpyDeviceToHost, sout));
@@ -1965,6 +1982,17 @@ extern "C" int smsgate_replay_host_records_begin(smsgate_ctx* ctx, const uint8_t
 extern "C" int smsgate_replay_host_records_finish(smsgate_ctx* ctx, int64_t* h_verdict) {
     if (!h_verdict) return SMSGATE_E_ARG;
     return replay_host_finish_impl(ctx, nullptr, h_verdict);
+}
+extern "C" int smsgate_replay_host_records8_finish(smsgate_ctx* ctx, uint8_t* h_verdict8) {
+    if (!h_verdict8) return SMSGATE_E_ARG;
+    return replay_host_finish_impl(ctx, nullptr, nullptr, h_verdict8);
+}
+extern "C" int smsgate_replay_host_records8(smsgate_ctx* ctx, const uint8_t* h_bytes, const int64_t* h_offsets, int64_t n,
+                                            int64_t now_packed, int64_t base_index, smsgate_record* h_records,
+                                            uint8_t* h_verdict8) {
+    const int rc = smsgate_replay_host_records_begin(ctx, h_bytes, h_offsets, n, now_packed, base_index, h_records);
+    if (rc) return rc;
+    return smsgate_replay_host_records8_finish(ctx, h_verdict8);
 }
 extern "C" int smsgate_replay_host_records(smsgate_ctx* ctx, const uint8_t* h_bytes, const int64_t* h_offsets, int64_t n,
                                            int64_t now_packed, int64_t base_index, smsgate_record* h_records,

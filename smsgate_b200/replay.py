@@ -87,6 +87,20 @@ class _RecordColumns:
             return self._fetch(name)
         if name not in self._VERDICT:
             raise KeyError(name)
+        if self.verdict.dtype == np.uint8:                 # one byte per message: 0x80 upserted | first_seen << 1 | survivor
+            if name == "last_idx":
+                if "last_idx" not in self._fetched:
+                    eng = self._engine
+                    if eng is None or eng._generation != self._generation:
+                        raise RuntimeError("last_idx of this result was left on the device and a later replay has replaced it")
+                    self._fetched.update(eng._fetch_columns(len(self.records), self._total, ["last_idx"])
+                                         if len(self.records) else {"last_idx": np.zeros(0, np.int64)})
+                return self._fetched["last_idx"]
+            if name not in self._decoded:
+                v = self.verdict
+                self._decoded["survivor"] = (v & 1).astype(np.uint8)
+                self._decoded["first_seen"] = ((v >> 1) & 1).astype(np.uint8)
+            return self._decoded[name]
         if name not in self._decoded:
             v = self.verdict
             up = v >= 0
@@ -104,6 +118,8 @@ class _RecordColumns:
         the remaining columns live on the device, both only until the engine's next replay."""
         for name in self._ON_DEVICE:
             self._fetch(name)
+        if self.verdict.dtype == np.uint8:
+            self["last_idx"]
         self.records = self.records.copy()
         self.verdict = self.verdict.copy()
         self._decoded = {}
@@ -410,7 +426,7 @@ class ReplayEngine:
     ALL_COLUMNS = tuple(name for name, _, _ in L.COLUMNS)
 
     def replay_records(self, batch: Batch, now: _dt.datetime, base_index: int = 0, pinned: bool = True,
-                       exchange=None) -> ReplayResult:
+                       exchange=None, compact_verdict: bool = True) -> ReplayResult:
         """`replay` with the results returned as one 64-byte record per message plus one verdict integer
         (smsgate_replay_host_records): one device->host transfer per chunk instead of one per column, which
         is what the end-to-end time depends on.  The ReplayResult reads the same either way: the columns the
@@ -436,20 +452,24 @@ class ReplayEngine:
             rec_buf, verdict_buf = t[0].numpy().view(dtype), t[1].numpy()
         else:
             rec_buf, verdict_buf = np.zeros(max(n, 1), dtype=dtype), np.zeros(max(n, 1), dtype=np.int64)
+        if compact_verdict:
+            # one byte of verdict per message (smsgate_replay_host_records8); last_idx stays on the device
+            verdict_buf = verdict_buf.view(np.uint8)
         rec, verdict = rec_buf[:n], verdict_buf[:n]
         body = np.ascontiguousarray(batch.body_bytes)
         offs = np.ascontiguousarray(batch.body_offsets, dtype=np.int64)
         rp, vp = rec_buf.ctypes.data, verdict_buf.ctypes.data      # never NULL, also for an empty shard
+        call = self._lib.smsgate_replay_host_records8 if compact_verdict else self._lib.smsgate_replay_host_records
+        finish = self._lib.smsgate_replay_host_records8_finish if compact_verdict else self._lib.smsgate_replay_host_records_finish
         if exchange is None:
-            L.check(self._ctx, self._lib.smsgate_replay_host_records(self._ctx, _np_ptr(body), _np_ptr(offs), n,
-                                                                     pack_datetime(now), int(base_index), rp, vp))
+            L.check(self._ctx, call(self._ctx, _np_ptr(body), _np_ptr(offs), n, pack_datetime(now), int(base_index), rp, vp))
         else:
             L.check(self._ctx, self._lib.smsgate_replay_host_records_begin(self._ctx, _np_ptr(body), _np_ptr(offs), n,
                                                                            pack_datetime(now), int(base_index), rp))
             view = L.Outputs()
             L.check(self._ctx, self._lib.smsgate_device_view(self._ctx, n, C.byref(view)))
             exchange.run_outputs(view, n, int(base_index))
-            L.check(self._ctx, self._lib.smsgate_replay_host_records_finish(self._ctx, vp))
+            L.check(self._ctx, finish(self._ctx, vp))
         return ReplayResult(batch, _RecordColumns(rec, verdict, self, self._generation, total), self.table, base_index)
 
     def _fetch_columns(self, n: int, total: int, names: Sequence[str]) -> dict:

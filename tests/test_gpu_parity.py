@@ -271,8 +271,9 @@ def test_packed_records_match_columns(engine):
     engine.load_cache(backup.cache)
     batch = Batch.from_strings(backup.bodies, backup.senders, backup.date_ms)
     a = engine.replay(batch, NOW, base_index=5)
-    for pinned in (True, False):
-        b = engine.replay_records(batch, NOW, base_index=5, pinned=pinned)
+    for pinned, compact in ((True, True), (False, True), (True, False), (False, False)):
+        b = engine.replay_records(batch, NOW, base_index=5, pinned=pinned, compact_verdict=compact)
+        assert b.cols.nbytes == batch.n * (64 + (1 if compact else 8))
         for name in b.cols.keys():
             assert np.array_equal(np.asarray(a.cols[name]), np.asarray(b.cols[name])), name
         assert b.msg_id_hex(150_000) == a.msg_id_hex(150_000)
