@@ -19,8 +19,11 @@ struct DecResult {
 //   then every char outside [0-9.-] is dropped and Decimal() must accept the rest,
 //   i.e. -?digits[.digits] with at least one digit (a '-' anywhere else, or a
 //   lone '.', is InvalidOperation -> ValueError).
-// Two passes over at most a few dozen bytes.
-SG_HD DecResult sg_parse_decimal(const uint8_t* s, int len) {
+// Two passes over at most a few dozen bytes: the general form (any UTF-8).
+#if defined(__CUDACC__)
+__host__ __device__ __noinline__
+#endif
+static DecResult sg_parse_decimal_general(const uint8_t* s, int len) {
     DecResult r;
     r.coef = 0; r.exp = 0; r.err = SG_DEC_OK; r.sign = 0;
     // pass 1: is there anything but whitespace; where are the last '.' and ','
@@ -77,6 +80,56 @@ SG_HD DecResult sg_parse_decimal(const uint8_t* s, int len) {
         // non-ASCII bytes) is removed by the final re.sub
     }
     if (!seen_digit) { r.err = SG_DEC_SYNTAX; r.sign = 0; return r; }
+    if (overflow || coef > 0x7FFFFFFFFFFFFFFFull) { r.err = SG_DEC_OVERFLOW; return r; }
+    r.coef = (int64_t)coef;
+    r.exp = -frac;
+    return r;
+}
+
+// The same in ONE pass for the strings that occur in practice - pure ASCII - and the general form for anything
+// else.  Which separator is the decimal point is only known at the end of the string, but nothing that is
+// accumulated on the way depends on it: the coefficient is all digits in order whichever separators are dropped,
+// and the exponent is the number of digits after the last '.' or after the last ',' (both are counted).  The
+// syntax rules of Decimal() reduce to: at least one digit; at most one '-', before every digit and before the
+// decimal point; at most one decimal point among the kept characters - which, by the reference's replacement
+// rules, fails exactly when both kinds occur and the later kind occurs more than once.
+SG_HD DecResult sg_parse_decimal(const uint8_t* s, int len) {
+    DecResult r;
+    r.coef = 0; r.exp = 0; r.err = SG_DEC_OK; r.sign = 0;
+    int n_dot = 0, n_comma = 0, last_dot = -1, last_comma = -1, after_dot = 0, after_comma = 0;
+    int first_digit = -1, minus_pos = -1, n_minus = 0;
+    bool any = false, overflow = false;
+    uint64_t coef = 0;
+    for (int i = 0; i < len; ++i) {
+        const uint32_t c = s[i];
+        if (c >= 0x80) return sg_parse_decimal_general(s, len);
+        const uint32_t d = c - '0';
+        if (d <= 9) {
+            if (coef > 1844674407370955161ull - (d > 5 ? 1u : 0u)) overflow = true;
+            coef = coef * 10 + d;
+            ++after_dot; ++after_comma;
+            if (first_digit < 0) first_digit = i;
+            any = true;
+        } else if (c == '.') { ++n_dot; last_dot = i; after_dot = 0; any = true; }
+        else if (c == ',') { ++n_comma; last_comma = i; after_comma = 0; any = true; }
+        else if (c == '-') { ++n_minus; if (minus_pos < 0) minus_pos = i; any = true; }
+        else if (!((c >= 9 && c <= 13) || (c >= 0x1C && c <= 0x20))) any = true;
+    }
+    if (!any) { r.exp = -1; return r; }                    // Decimal("0.0")
+    int point = -1, frac = 0;
+    bool two_points = false;
+    if (n_dot && n_comma) {
+        if (last_comma > last_dot) { point = last_comma; frac = after_comma; two_points = n_comma > 1; }
+        else { point = last_dot; frac = after_dot; two_points = n_dot > 1; }
+    } else if (n_comma) {
+        if (n_comma == 1) { point = last_comma; frac = after_comma; }
+    } else if (n_dot) { point = last_dot; frac = after_dot; }
+    // with both kinds present every occurrence of the later kind is a point: the '-' has to precede the FIRST of
+    // them, but then there is only one (two_points is an error anyway), so `point` is that one
+    const bool minus_bad = n_minus > 1 || (n_minus == 1 && ((first_digit >= 0 && first_digit < minus_pos) ||
+                                                            (point >= 0 && point < minus_pos)));
+    if (two_points || minus_bad || first_digit < 0) { r.err = SG_DEC_SYNTAX; return r; }
+    r.sign = n_minus ? 1u : 0u;
     if (overflow || coef > 0x7FFFFFFFFFFFFFFFull) { r.err = SG_DEC_OVERFLOW; return r; }
     r.coef = (int64_t)coef;
     r.exp = -frac;

@@ -225,6 +225,25 @@ def test_decimal_fuzz_against_oracle():
             assert ((int(flags[i]) >> 4) & 1, int(coef[i]), int(exp[i])) == want[1:], repr(t)
 
 
+def test_decimal_ascii_fuzz_against_oracle():
+    """The one-pass ASCII form of sg_parse_decimal on separator- and sign-heavy strings."""
+    import random
+    rng = random.Random(23)
+    alphabet = "0123456789" * 2 + "....,,,,---  \t+eA"
+    strings = ["".join(rng.choice(alphabet) for _ in range(rng.choice([1, 2, 3, 4, 6, 9, 14, 22])))
+               for _ in range(80000)]
+    strings += ["-", "-.", ".-", "-.5", ".-.5", "1.-2", "-1,2.3", "1,-2.3", "-,1.2", ",-1.2", "1,2,3", "1.2.3", "1,2.3,4",
+                "1.2,3.4", "--1", "-1-", "1-", " - 1", "\t-\t1 ", "18446744073709551615", "18446744073709551616",
+                "9223372036854775807", "9223372036854775808", "-9223372036854775808", "00000000000000000000001.5"]
+    coef, exp, flags = H.decimal(strings)
+    for i, t in enumerate(strings):
+        want = O.decimal_triplet(t)
+        err = int(flags[i]) & 3
+        assert err == want[0], repr(t)
+        if err == 0:
+            assert ((int(flags[i]) >> 4) & 1, int(coef[i]), int(exp[i])) == want[1:], repr(t)
+
+
 def test_route_fuzz_against_oracle():
     """Cache entries mutated at random (keys dropped, values of the wrong type, cards / dates / amounts of every
     odd shape the reference's parse_sms_llm has an opinion on) against bodies with and without a body date:
