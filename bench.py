@@ -557,7 +557,7 @@ def main():
     ap.add_argument("--nccl-exchange", action="store_true", help="use the NCCL all-to-all exchange instead of peer memory")
     ap.add_argument("--workload", default="hit100", choices=sorted(WORKLOADS), help="headline workload (default: configs[1])")
     ap.add_argument("--reserve-sms", type=int, default=0, help="SMs the keys kernel leaves to the exchange stream (N>1)")
-    ap.add_argument("--lanes", type=int, default=2, help="batches in flight per rank (dist.OverlappedReplay)")
+    ap.add_argument("--lanes", type=int, default=3, help="batches in flight per rank (dist.OverlappedReplay)")
     ap.add_argument("--no-extra", action="store_true", help="skip the `configs` object (the other BASELINE.json shapes)")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3) if args.impl == "ours" else args.warmup

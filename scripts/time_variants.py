@@ -62,11 +62,23 @@ def main():
                 if it >= 3:
                     k1.append(e0.elapsed_time(e1))
                     step.append(e0.elapsed_time(e2))
+            phases = None
+            if hasattr(L.lib(), "smsgate_debug_scan_phases"):          # -DK1_PHASE_TIMERS build: clocks per phase, summed over CTAs
+                import ctypes as C
+                buf = (C.c_ulonglong * 8)()
+                L.lib().smsgate_debug_scan_phases(None, 1)
+                eng.scan_keys(d_bytes, d_offs, cols)
+                torch.cuda.synchronize()
+                L.lib().smsgate_debug_scan_phases(buf, 0)
+                tot = float(sum(buf[:4])) or 1.0
+                phases = {k: round(buf[i] / tot, 4) for i, k in enumerate(("stage_sort", "scan", "partition", "hash"))}
+                phases["clocks_per_cta"] = tot / 148
             chk = [int(cols[c].to(torch.int64).sum().item()) for c in ("msg_id", "cache_key", "flags", "status", "survivor")]
             if ref_sum is None:
                 ref_sum = chk
             out.setdefault(wl, {})[name] = {"k_scan_keys_ms": sum(k1) / len(k1), "k_scan_keys_min_ms": min(k1),
-                                            "step_ms": sum(step) / len(step), "same_results_as_first": chk == ref_sum}
+                                            "step_ms": sum(step) / len(step), "same_results_as_first": chk == ref_sum,
+                                            "phase_share": phases}
             print(wl, name, out[wl][name], file=sys.stderr, flush=True)
             eng.close()
             del cols

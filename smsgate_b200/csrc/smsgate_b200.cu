@@ -154,6 +154,20 @@ __device__ __noinline__ void k1_giant(const uint8_t* bytes, int64_t lo, int64_t 
     k1_store_key(out, msg, h2, flen);
 }
 
+// -DK1_PHASE_TIMERS (variant build, scripts/time_variants.py): thread 0 of every CTA adds up the clocks between the
+// tile's barriers - staging + sort, scan phase, partition, hash phase - into g_k1_phase; never in the shipped build.
+#ifdef K1_PHASE_TIMERS
+__device__ unsigned long long g_k1_phase[8];
+#define K1_T(slot) do { if (tid == 0) { const long long now_ = clock64(); atomicAdd(&g_k1_phase[slot], (unsigned long long)(now_ - t_prev)); t_prev = now_; } } while (0)
+extern "C" int smsgate_debug_scan_phases(unsigned long long* h_out8, int reset) {
+    if (h_out8 && cudaMemcpyFromSymbol(h_out8, g_k1_phase, sizeof(g_k1_phase)) != cudaSuccess) return -1;
+    if (reset) { unsigned long long z[8] = {0}; if (cudaMemcpyToSymbol(g_k1_phase, z, sizeof(z)) != cudaSuccess) return -1; }
+    return 0;
+}
+#else
+#define K1_T(slot) do { } while (0)
+#endif
+
 __global__ void __launch_bounds__(K1_THREADS, K1_CTAS_PER_SM)
 k_scan_keys(const uint8_t* __restrict__ bytes, const int64_t* __restrict__ offsets, int64_t n,
             const DeviceTables* __restrict__ gtab, ScanOut out) {
@@ -175,6 +189,9 @@ k_scan_keys(const uint8_t* __restrict__ bytes, const int64_t* __restrict__ offse
     T.t = &S.tab;
 
     uint32_t parity = 0;
+#ifdef K1_PHASE_TIMERS
+    long long t_prev = clock64();
+#endif
     // every CTA takes an equal contiguous share of the messages and walks it in equal tiles of at most
     // K1_TILE: all CTAs do the same number of tiles, no tail wave
     const int64_t r0 = n * (int64_t)blockIdx.x / gridDim.x, r1 = n * ((int64_t)blockIdx.x + 1) / gridDim.x;
@@ -277,6 +294,7 @@ k_scan_keys(const uint8_t* __restrict__ bytes, const int64_t* __restrict__ offse
                 parity ^= 1;
             }
             __syncthreads();
+            K1_T(0);                                         // offsets, staging copy, sort
 
             // ---- phase S: the scans.  Warps pull 32-message chunks of the length-sorted order, longest first:
             //      the lanes of a warp walk bodies of about the same length, and a tile that mixes 100-byte and
@@ -299,6 +317,7 @@ k_scan_keys(const uint8_t* __restrict__ bytes, const int64_t* __restrict__ offse
                 k1_store_scan(out, s + t, sr);
             }
             __syncthreads();
+            K1_T(1);                                         // scan phase
             // ---- hashing order: the bodies clean/mask changes first (they cost SHA-1 + rewrite + SHA-256 of
             //      the result), then the untouched ones (both digests in one walk), each group longest first,
             //      so that a 32-message chunk is one kind of work and the dearest chunks start first
@@ -338,6 +357,7 @@ k_scan_keys(const uint8_t* __restrict__ bytes, const int64_t* __restrict__ offse
                 }
             }
             __syncthreads();
+            K1_T(2);                                         // partition
             // ---- phase H: warps pull chunks until none is left
             const int nchM = (nM + 31) >> 5, nchU = (cnt - nM + 31) >> 5;
             const int nR = S.nr, nchR = (nR + 31) >> 5;
@@ -405,6 +425,7 @@ k_scan_keys(const uint8_t* __restrict__ bytes, const int64_t* __restrict__ offse
                 }
             }
             __syncthreads();
+            K1_T(3);                                         // hash phase
             s = e;
         }
     }

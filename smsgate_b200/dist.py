@@ -243,8 +243,8 @@ class OverlappedReplay:
     running under the keys kernel of batch k+1.
 
     The exchange is a chain of small latency-bound kernels and cross-GPU barriers that depends on the whole
-    batch's keys, so inside one batch nothing can hide it; across batches everything can.  Two contexts
-    ("lanes") alternate: each owns its dedup scratch, its output columns and its peer-memory buffers and
+    batch's keys, so inside one batch nothing can hide it; across batches everything can.  A few contexts
+    ("lanes", three by default) take turns: each owns its dedup scratch, its output columns and its peer-memory buffers and
     shares the one response cache (smsgate_cache_share).  Lane work is queued on `main` (high priority:
     smsgate_scan_keys, smsgate_join_route_dedup), its exchange on `side` (low priority) behind an event; a
     lane is reused only after its previous exchange has finished.  The exchange kernels and the in-stream barrier
@@ -254,7 +254,7 @@ class OverlappedReplay:
     The reference has no counterpart: its upsert is one synchronous HTTP/SQL round trip per message
     (libs/pocketbase.py:168-200, services/pb_writer/upsert.py:19-31)."""
 
-    def __init__(self, engine, dist, n_max: int, prefer_p2p: bool = True, reserve_sms: int = 0, lanes: int = 2):
+    def __init__(self, engine, dist, n_max: int, prefer_p2p: bool = True, reserve_sms: int = 0, lanes: int = 3):
         import torch
 
         from .replay import ReplayEngine
