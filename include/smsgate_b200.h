@@ -14,8 +14,16 @@
  *   - A context is bound to one GPU and one CUDA stream and is not re-entrant;
  *     different contexts are independent.
  *   - "d_" pointers are device memory owned by the caller; "h_" pointers are
- *     host memory.  Hot calls allocate nothing: scratch lives in the context
- *     and is sized by smsgate_reserve().
+ *     host memory.
+ *   - Which calls allocate.  The replay path proper allocates NOTHING per call: smsgate_scan_keys,
+ *     smsgate_join_route, smsgate_dedup, smsgate_join_route_dedup, smsgate_replay_device, smsgate_replay_host*
+ *     (all forms), smsgate_fetch_columns, smsgate_device_keys, smsgate_cross_source, the smsgate_dedup_export /
+ *     _merge / _apply and smsgate_p2p_* exchange steps, smsgate_dedup_static - their scratch lives in the context
+ *     and is sized once by smsgate_reserve / smsgate_reserve_merge / smsgate_p2p_reserve / _reserve_filter.
+ *     Set-up and batch-helper calls DO allocate (and free) device memory inside the call: smsgate_create,
+ *     smsgate_reserve*, smsgate_cache_load, smsgate_decimal_batch, smsgate_strict_date_batch / _entries,
+ *     smsgate_dt_str_batch, smsgate_legacy_parse*, smsgate_xml_scan / _attrs_sizes.  smsgate_dcache_* and
+ *     smsgate_emit_json are host code and use host memory only.
  *   - A batch is Arrow-style: int64 offsets[n+1] + uint8 bytes[offsets[n]],
  *     UTF-8, offsets[0] may be non-zero, `bytes` must be 16-byte aligned.
  */
