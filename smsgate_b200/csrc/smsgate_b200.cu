@@ -2369,14 +2369,22 @@ k_bits_build(int64_t n, const uint8_t* __restrict__ msg_id, const int32_t* __res
 }
 __global__ void __launch_bounds__(XCH_THREADS, XCH_MIN_BLOCKS)
 k_bits_push(const uint32_t* __restrict__ bits, P2PView P) {
-    const int64_t nq = P.bitmap_words >> 2, cap = slice_cap(P.bitmap_words, P.world);
-    for (int64_t q = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; q < nq; q += (int64_t)gridDim.x * blockDim.x) {
-        const int64_t j = q << 2;
-        int w = (int)(j * P.world / P.bitmap_words);      // slice of word j (boundaries are rounded down to 4)
-        while (w + 1 < P.world && j >= slice_lo(P.bitmap_words, w + 1, P.world)) ++w;
-        while (w > 0 && j < slice_lo(P.bitmap_words, w, P.world)) --w;
-        const uint4 v = *reinterpret_cast<const uint4*>(bits + j);
-        *reinterpret_cast<uint4*>(P.stage[w] + P.rank * cap + (j - slice_lo(P.bitmap_words, w, P.world))) = v;   // peer store
+    // slice w of this rank's bitmap -> rank w's staging row for this rank.  One block-stride loop per slice, two
+    // 16-byte loads in flight per thread before the two peer stores.
+    const int64_t cap = slice_cap(P.bitmap_words, P.world);
+    for (int w = 0; w < P.world; ++w) {
+        const int64_t lo = slice_lo(P.bitmap_words, w, P.world);
+        const int64_t hi = w + 1 == P.world ? P.bitmap_words : slice_lo(P.bitmap_words, w + 1, P.world);
+        const uint4* src = reinterpret_cast<const uint4*>(bits + lo);
+        uint4* dst = reinterpret_cast<uint4*>(P.stage[w] + P.rank * cap);               // peer memory
+        const int64_t nq = (hi - lo) >> 2, step = (int64_t)gridDim.x * blockDim.x;
+        for (int64_t q = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; q < nq; q += 2 * step) {
+            uint4 v0 = src[q], v1 = make_uint4(0, 0, 0, 0);
+            const bool second = q + step < nq;
+            if (second) v1 = src[q + step];
+            dst[q] = v0;
+            if (second) dst[q + step] = v1;
+        }
     }
 }
 __global__ void __launch_bounds__(XCH_THREADS, XCH_MIN_BLOCKS)
@@ -2387,10 +2395,16 @@ k_bits_reduce(P2PView P) {
     const uint32_t* mine = P.stage[P.rank];
     for (int64_t q = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; q < nq; q += (int64_t)gridDim.x * blockDim.x) {
         uint4 one = make_uint4(0, 0, 0, 0), two = make_uint4(0, 0, 0, 0);
-        for (int r = 0; r < P.world; ++r) {
-            const uint4 x = *reinterpret_cast<const uint4*>(mine + r * cap + (q << 2));
-            two.x |= one.x & x.x; two.y |= one.y & x.y; two.z |= one.z & x.z; two.w |= one.w & x.w;
-            one.x |= x.x; one.y |= x.y; one.z |= x.z; one.w |= x.w;
+        for (int r0 = 0; r0 < P.world; r0 += 4) {                                       // four rows' loads in flight
+            uint4 x[4];
+#pragma unroll
+            for (int k = 0; k < 4; ++k)
+                x[k] = r0 + k < P.world ? *reinterpret_cast<const uint4*>(mine + (r0 + k) * cap + (q << 2)) : make_uint4(0, 0, 0, 0);
+#pragma unroll
+            for (int k = 0; k < 4; ++k) {
+                two.x |= one.x & x[k].x; two.y |= one.y & x[k].y; two.z |= one.z & x[k].z; two.w |= one.w & x[k].w;
+                one.x |= x[k].x; one.y |= x[k].y; one.z |= x[k].z; one.w |= x[k].w;
+            }
         }
         for (int r = 0; r < P.world; ++r) *reinterpret_cast<uint4*>(P.collide[r] + lo + (q << 2)) = two;   // peer stores
     }
@@ -2399,6 +2413,9 @@ k_bits_reduce(P2PView P) {
 // Records of this rank's distinct keys go straight into their owners' inboxes.  A block counts its records
 // per destination in shared memory and reserves its ranges with one remote atomic per destination; with the
 // prefilter only keys whose bit is set in `collide` are sent at all.
+constexpr int XCH_ITEMS = 4;             // messages per thread in the per-message exchange kernels: four independent loads in
+                                         // flight per thread - these kernels mostly run squeezed next to the keys kernel, one
+                                         // small block per SM, where memory parallelism per thread is all the parallelism there is
 __global__ void __launch_bounds__(XCH_THREADS, XCH_MIN_BLOCKS)
 k_p2p_scatter(int64_t n, int64_t base_index, int parity, const uint8_t* __restrict__ msg_id, DedupScratch D, P2PView P,
               const uint32_t* __restrict__ collide, int* __restrict__ overflow) {
@@ -2406,26 +2423,30 @@ k_p2p_scatter(int64_t n, int64_t base_index, int parity, const uint8_t* __restri
     __shared__ int base[SMSGATE_MAX_WORLD];
     if (threadIdx.x < SMSGATE_MAX_WORLD) hist[threadIdx.x] = 0;
     __syncthreads();
-    const int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
-    int32_t sl = -1;
-    int2 fl = make_int2(0, 0);
-    int dest = 0, local = 0;
-    uint64_t f = 0, l = 0;
-    if (i < n) {
-        sl = D.slot_of[i];
-        if (sl >= 0 && (fl = D.tab[sl]).x != (int32_t)i) sl = -1;   // one record per key: its first message sends it
-        if (sl >= 0) {
-            f = (uint64_t)(base_index + fl.x);
-            l = (uint64_t)(base_index + fl.y);
-            if (collide) {
-                const uint32_t h = key_bit(msg_id + i * 20, P.bitmap_words);
-                if (!((collide[h >> 5] >> (h & 31)) & 1u)) sl = -1;          // no other rank can hold this key
-            }
-        }
-        if (sl >= 0) {
-            dest = key_owner(msg_id + i * 20, P.world);
-            local = atomicAdd(&hist[dest], 1);
-        }
+    const int64_t i0 = (int64_t)blockIdx.x * (XCH_THREADS * XCH_ITEMS) + threadIdx.x;
+    // pass 1 (all messages, cheap): is the message an upsert whose key some other rank may hold?
+    int32_t sl[XCH_ITEMS];
+    uint32_t hb[XCH_ITEMS];
+#pragma unroll
+    for (int k = 0; k < XCH_ITEMS; ++k) {
+        const int64_t i = i0 + (int64_t)k * XCH_THREADS;
+        sl[k] = i < n ? D.slot_of[i] : -1;
+        hb[k] = (i < n && collide) ? key_bit(msg_id + i * 20, P.bitmap_words) : 0;
+    }
+    uint32_t cand = 0;
+#pragma unroll
+    for (int k = 0; k < XCH_ITEMS; ++k)
+        if (sl[k] >= 0 && (!collide || ((collide[hb[k] >> 5] >> (hb[k] & 31)) & 1u))) cand |= 1u << k;
+    // pass 2 (the few candidates): one record per key - its first message sends it
+    uint32_t dest_packed = 0;                            // 8 bits per item: the owner rank (< SMSGATE_MAX_WORLD = 64)
+#pragma unroll
+    for (int k = 0; k < XCH_ITEMS; ++k) {
+        if (!((cand >> k) & 1u)) continue;
+        const int64_t i = i0 + (int64_t)k * XCH_THREADS;
+        if (D.tab[sl[k]].x != (int32_t)i) { cand &= ~(1u << k); continue; }
+        const int dest = key_owner(msg_id + i * 20, P.world);
+        hb[k] = (uint32_t)atomicAdd(&hist[dest], 1);     // the record's place inside this block's range at that owner
+        dest_packed |= (uint32_t)dest << (8 * k);
     }
     __syncthreads();
     if (threadIdx.x < P.world && hist[threadIdx.x]) {
@@ -2435,18 +2456,26 @@ k_p2p_scatter(int64_t n, int64_t base_index, int parity, const uint8_t* __restri
         base[threadIdx.x] = b;
     }
     __syncthreads();
-    if (sl < 0 || base[dest] < 0) return;
-    const uint32_t* kw = reinterpret_cast<const uint32_t*>(msg_id + i * 20);
-    P2PRecord rec;
-    rec.key[0] = kw[0]; rec.key[1] = kw[1]; rec.key[2] = kw[2]; rec.key[3] = kw[3]; rec.key[4] = kw[4];
-    rec.first_lo = (uint32_t)f; rec.last_lo = (uint32_t)l;
-    rec.first_hi = (uint16_t)(f >> 32); rec.last_hi = (uint16_t)(l >> 32);
-    rec.home_slot = (uint32_t)sl;
-    rec.src_rank = (uint32_t)P.rank;
-    rec.pad[0] = rec.pad[1] = 0;
-    const uint4* src = reinterpret_cast<const uint4*>(&rec);
-    uint4* dst = reinterpret_cast<uint4*>(&P.inbox[dest][base[dest] + local]);   // peer stores over NVLink when dest != rank
-    dst[0] = src[0]; dst[1] = src[1]; dst[2] = src[2];
+#pragma unroll
+    for (int k = 0; k < XCH_ITEMS; ++k) {
+        if (!((cand >> k) & 1u)) continue;
+        const int dest = (int)((dest_packed >> (8 * k)) & 255u);
+        if (base[dest] < 0) continue;
+        const int64_t i = i0 + (int64_t)k * XCH_THREADS;
+        const int2 fl = D.tab[sl[k]];
+        const uint64_t f = (uint64_t)(base_index + fl.x), l = (uint64_t)(base_index + fl.y);
+        const uint32_t* kw = reinterpret_cast<const uint32_t*>(msg_id + i * 20);
+        P2PRecord rec;
+        rec.key[0] = kw[0]; rec.key[1] = kw[1]; rec.key[2] = kw[2]; rec.key[3] = kw[3]; rec.key[4] = kw[4];
+        rec.first_lo = (uint32_t)f; rec.last_lo = (uint32_t)l;
+        rec.first_hi = (uint16_t)(f >> 32); rec.last_hi = (uint16_t)(l >> 32);
+        rec.home_slot = (uint32_t)sl[k];
+        rec.src_rank = (uint32_t)P.rank;
+        rec.pad[0] = rec.pad[1] = 0;
+        const uint4* src = reinterpret_cast<const uint4*>(&rec);
+        uint4* dst = reinterpret_cast<uint4*>(&P.inbox[dest][base[dest] + (int)hb[k]]);   // peer stores over NVLink when dest != rank
+        dst[0] = src[0]; dst[1] = src[1]; dst[2] = src[2];
+    }
 }
 
 __device__ __forceinline__ int p2p_count(const int32_t* count_ptr, int64_t capacity) {
@@ -2516,18 +2545,27 @@ k_p2p_resolve(int64_t n, int64_t base_index, const int32_t* __restrict__ slot_of
     // holds AND whose global first / last differs from the local one was answered by its owner: those slots have
     // their bit set in this parity's half of `ovr`, and only their messages are rewritten.  The other half is
     // cleared here for the next batch (its owners write it after the next batch's barriers).
-    const int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+    const int64_t t = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
     uint32_t* next_half = ovr + (int64_t)(parity ^ 1) * ovr_words;
-    for (int64_t w = i; w < ovr_words; w += (int64_t)gridDim.x * blockDim.x) next_half[w] = 0;
-    if (i >= n) return;
-    const int32_t sl = slot_of[i];
-    if (sl < 0) return;
-    if (!((ovr[(int64_t)parity * ovr_words + (sl >> 5)] >> (sl & 31)) & 1u)) return;
-    const longlong2 v = gfl[sl];
-    const int64_t g = base_index + i;
-    if (survivor) survivor[i] = (v.y == g);
-    if (first_seen) first_seen[i] = (v.x == g);
-    if (last_idx) last_idx[i] = v.y;
+    for (int64_t w = t; w < ovr_words; w += (int64_t)gridDim.x * blockDim.x) next_half[w] = 0;
+    const uint32_t* half = ovr + (int64_t)parity * ovr_words;
+    const int64_t i0 = (int64_t)blockIdx.x * (XCH_THREADS * XCH_ITEMS) + threadIdx.x;
+    int32_t sl[XCH_ITEMS];
+#pragma unroll
+    for (int k = 0; k < XCH_ITEMS; ++k) {
+        const int64_t i = i0 + (int64_t)k * XCH_THREADS;
+        sl[k] = i < n ? slot_of[i] : -1;
+    }
+#pragma unroll
+    for (int k = 0; k < XCH_ITEMS; ++k) {
+        if (sl[k] < 0 || !((half[sl[k] >> 5] >> (sl[k] & 31)) & 1u)) continue;
+        const int64_t i = i0 + (int64_t)k * XCH_THREADS;
+        const longlong2 v = gfl[sl[k]];
+        const int64_t g = base_index + i;
+        if (survivor) survivor[i] = (v.y == g);
+        if (first_seen) first_seen[i] = (v.x == g);
+        if (last_idx) last_idx[i] = v.y;
+    }
 }
 
 // Cross-GPU barrier from inside the stream, without a host round trip and small enough (one warp-sized block, a
@@ -2622,7 +2660,7 @@ extern "C" int smsgate_p2p_scatter(smsgate_ctx* ctx, int64_t n, int64_t base_ind
         return fail(ctx, SMSGATE_E_LIMIT, "p2p_scatter: the batch exceeds capacity / world messages per rank");
     DedupScratch D{ctx->d_dtab, ctx->d_slot_of, cap - 1};
     if (n > 0) {
-        k_p2p_scatter<<<(unsigned)((n + XCH_THREADS - 1) / XCH_THREADS), XCH_THREADS, 0, st>>>(n, base_index, parity & 1, out->msg_id, D, V,
+        k_p2p_scatter<<<(unsigned)((n + XCH_THREADS * XCH_ITEMS - 1) / (XCH_THREADS * XCH_ITEMS)), XCH_THREADS, 0, st>>>(n, base_index, parity & 1, out->msg_id, D, V,
                                                                    V.bitmap_words ? V.collide[V.rank] : nullptr,
                                                                    ctx->p2p_overflow);
         ctx->launches += 1;
@@ -2753,7 +2791,7 @@ extern "C" int smsgate_p2p_resolve(smsgate_ctx* ctx, int64_t n, int64_t base_ind
     CUDA_TRY(ctx, cudaSetDevice(ctx->device));
     cudaStream_t st = ctx->stream;
     if (n > 0) {
-        k_p2p_resolve<<<(unsigned)((n + XCH_THREADS - 1) / XCH_THREADS), XCH_THREADS, 0, st>>>(n, base_index, ctx->d_slot_of, V.gfl[V.rank],
+        k_p2p_resolve<<<(unsigned)((n + XCH_THREADS * XCH_ITEMS - 1) / (XCH_THREADS * XCH_ITEMS)), XCH_THREADS, 0, st>>>(n, base_index, ctx->d_slot_of, V.gfl[V.rank],
                                                                    V.ovr[V.rank], V.ovr_words, parity & 1,
                                                                    out->survivor, out->first_seen, out->last_idx);
         ctx->launches += 1;

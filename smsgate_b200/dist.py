@@ -245,8 +245,8 @@ class OverlappedReplay:
     The exchange is a chain of small latency-bound kernels and cross-GPU barriers that depends on the whole
     batch's keys, so inside one batch nothing can hide it; across batches everything can.  A few contexts
     ("lanes", three by default) take turns: each owns its dedup scratch, its output columns and its peer-memory buffers and
-    shares the one response cache (smsgate_cache_share).  Lane work is queued on `main` (high priority:
-    smsgate_scan_keys, smsgate_join_route_dedup), its exchange on `side` (low priority) behind an event; a
+    shares the one response cache (smsgate_cache_share).  Lane work is queued on `main` (smsgate_scan_keys,
+    smsgate_join_route_dedup), its exchange on `side` behind an event; a
     lane is reused only after its previous exchange has finished.  The exchange kernels and the in-stream barrier
     are built to fit on an SM next to the keys kernel's CTA (128 threads, 32 registers), so they run on every SM
     while it has them all; `reserve_sms` > 0 additionally keeps SMs free of it (smsgate_set_scan_ctas).
@@ -254,15 +254,20 @@ class OverlappedReplay:
     The reference has no counterpart: its upsert is one synchronous HTTP/SQL round trip per message
     (libs/pocketbase.py:168-200, services/pb_writer/upsert.py:19-31)."""
 
-    def __init__(self, engine, dist, n_max: int, prefer_p2p: bool = True, reserve_sms: int = 0, lanes: int = 3):
+    def __init__(self, engine, dist, n_max: int, prefer_p2p: bool = True, reserve_sms: int = 0, lanes: int = 3,
+                 exchange_first: bool = True):
         import torch
 
         from .replay import ReplayEngine
         self.torch = torch
         dev = engine.device
         lo, hi = torch.cuda.Stream.priority_range()          # (lowest priority, highest priority)
-        self.main = torch.cuda.Stream(device=dev, priority=hi)
-        self.side = torch.cuda.Stream(device=dev, priority=lo)
+        # `exchange_first`: the exchange stream has the HIGHER priority.  Its kernels are tiny next to the keys kernel
+        # (tens of microseconds each at full speed); while that kernel holds every SM they trickle through the one
+        # co-resident block per SM, and at every kernel boundary of the main stream they take the freed SMs first
+        # and are done in microseconds - instead of starving behind 0.16 ms of join blocks and making the lane wait.
+        self.main = torch.cuda.Stream(device=dev, priority=lo if exchange_first else hi)
+        self.side = torch.cuda.Stream(device=dev, priority=hi if exchange_first else lo)
         self.engines = [engine]
         for _ in range(lanes - 1):
             e = ReplayEngine(dev)
