@@ -398,7 +398,7 @@ def run_ours(args, rank, world, local_rank):
     from smsgate_b200.dist import OverlappedReplay
     ov = OverlappedReplay(eng, dist if world > 1 else None, n, prefer_p2p=not args.nccl_exchange,
                           reserve_sms=(args.reserve_sms if world > 1 else 0), lanes=args.lanes,
-                          exchange_first=not args.main_first)
+                          exchange_first=not args.main_first, prefilter_bits=args.prefilter_bits)
     torch.cuda.synchronize()
     torch.cuda.set_stream(ov.main)                       # events, flushes and barriers below follow the engines' stream
     exchange = ov.exchanges[0]
@@ -508,7 +508,7 @@ def run_ours(args, rank, world, local_rank):
                          "e2e figures flush a 512 MiB buffer between steps instead)",
                    "timing": "one CUDA-event bracket around all K steps on the engines' stream, max over ranks; "
                              "batch k's dedup exchange overlaps batch k+1's keys kernel (two lanes)",
-                   "scan_sms_reserved_for_exchange": (args.reserve_sms if world > 1 else 0), "lanes": args.lanes, "exchange_stream_priority": ("low" if args.main_first else "high"),
+                   "scan_sms_reserved_for_exchange": (args.reserve_sms if world > 1 else 0), "lanes": args.lanes, "prefilter_bits_per_key": args.prefilter_bits, "exchange_stream_priority": ("low" if args.main_first else "high"),
                    "host_cpus_bound": (len(bound) if bound else None),
                    "parallelism": f"shard-by-index x{world}" + (f", {type(exchange).__name__} exchange by msg_id prefix" if world > 1 else "")},
         "clocks": clocks,
@@ -560,6 +560,7 @@ def main():
     ap.add_argument("--reserve-sms", type=int, default=0, help="SMs the keys kernel leaves to the exchange stream (N>1)")
     ap.add_argument("--lanes", type=int, default=3, help="batches in flight per rank (dist.OverlappedReplay)")
     ap.add_argument("--main-first", action="store_true", help="give the keys / join stream the higher priority (default: the exchange stream)")
+    ap.add_argument("--prefilter-bits", type=int, default=16, help="bits per key of the whole job in the exchange's bitmaps")
     ap.add_argument("--no-extra", action="store_true", help="skip the `configs` object (the other BASELINE.json shapes)")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3) if args.impl == "ours" else args.warmup

@@ -128,7 +128,7 @@ class GlobalDedupP2P:
     bitmap prefilter, two for the records and their verdicts) and no host
     synchronisation per batch.  Every rank must use the same `n_max`."""
 
-    def __init__(self, engine, dist, n_max: int, group=None, prefilter: bool = True):
+    def __init__(self, engine, dist, n_max: int, group=None, prefilter: bool = True, prefilter_bits: int = 16):
         import torch
         import torch.distributed._symmetric_memory as symm_mem
         self.engine = engine
@@ -153,11 +153,12 @@ class GlobalDedupP2P:
         self._ovr = symm_mem.empty(2 * self.ovr_words, dtype=torch.int32, device=dev)   # override bits, one half per parity
         self._ovr.zero_()
         bufs = [self._inbox, self._count, self._gfl]
-        # prefilter bitmaps: about 16 bits per key of the whole job (a false positive only costs one record)
+        # prefilter bitmaps: `prefilter_bits` bits per key of the whole job (a false positive only costs one record;
+        # the bitmaps cross NVLink twice per batch, so fewer bits trade records for bitmap traffic)
         self.bitmap_words = 0
         if prefilter and self.world > 1:
             words = 64
-            while words * 32 < 16 * n_max * self.world and words < (1 << 26):
+            while words * 32 < prefilter_bits * n_max * self.world and words < (1 << 26):
                 words <<= 1
             self.bitmap_words = words
             self._stage = symm_mem.empty(self.world * (words // self.world + 12), dtype=torch.int32, device=dev)
@@ -227,11 +228,11 @@ class GlobalDedupP2P:
         return bool(flag.value)
 
 
-def make_global_dedup(engine, dist, n_max: int, prefer_p2p: bool = True):
+def make_global_dedup(engine, dist, n_max: int, prefer_p2p: bool = True, prefilter_bits: int = 16):
     """GlobalDedupP2P when peer mappings are available, else the NCCL all-to-all path."""
     if prefer_p2p:
         try:
-            return GlobalDedupP2P(engine, dist, n_max)
+            return GlobalDedupP2P(engine, dist, n_max, prefilter_bits=prefilter_bits)
         except Exception as e:       # no symmetric memory in this build / topology: fall back to NCCL
             import warnings
             warnings.warn(f"peer-memory exchange unavailable ({e!r}); using the NCCL all-to-all path")
@@ -255,7 +256,7 @@ class OverlappedReplay:
     (libs/pocketbase.py:168-200, services/pb_writer/upsert.py:19-31)."""
 
     def __init__(self, engine, dist, n_max: int, prefer_p2p: bool = True, reserve_sms: int = 0, lanes: int = 3,
-                 exchange_first: bool = True):
+                 exchange_first: bool = True, prefilter_bits: int = 16):
         import torch
 
         from .replay import ReplayEngine
@@ -277,7 +278,8 @@ class OverlappedReplay:
         self.exchanges = []
         for e in self.engines:
             e.set_scan_ctas(max(1, sm - reserve_sms) if reserve_sms > 0 else 0)
-            self.exchanges.append(make_global_dedup(e, dist, n_max, prefer_p2p=prefer_p2p) if dist is not None else None)
+            self.exchanges.append(make_global_dedup(e, dist, n_max, prefer_p2p=prefer_p2p, prefilter_bits=prefilter_bits)
+                                  if dist is not None else None)
         torch.cuda.synchronize(dev)
         for e in self.engines:
             e.set_stream(self.main)
