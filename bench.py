@@ -282,7 +282,7 @@ def time_overlapped(ov, R, steps, warmup, barrier, copies=3):
 
     def go(k, timed):
         b, o = ins[k % copies]
-        pe = (ev(), ev()) if timed else None
+        pe = (ev(), ev(), ev()) if timed else None
         ov.submit(b, o, colsets[ov.k % len(colsets)], R.n, NOW, R.base_index, scan_events=pe)
         if timed:
             pairs.append(pe)
@@ -304,7 +304,13 @@ def time_overlapped(ov, R, steps, warmup, barrier, copies=3):
     ov.drain()
     barrier()
     time_overlapped.launches = ov.launch_count - l0
-    k1 = sum(a.elapsed_time(b) for a, b in pairs) / len(pairs)
+    k1 = sum(p[0].elapsed_time(p[1]) for p in pairs) / len(pairs)
+    # where a step of the main stream goes: keys kernel, join + upsert kernels, and the wait before the next keys
+    # kernel starts (lane reuse behind its exchange, exchange kernels taking the SMs at the boundary)
+    time_overlapped.main_stream_ms = {
+        "k_scan_keys": k1, "join_route_dedup": sum(p[1].elapsed_time(p[2]) for p in pairs) / len(pairs),
+        "between_steps": (sum(pairs[k][2].elapsed_time(pairs[k + 1][0]) for k in range(len(pairs) - 1)) / (len(pairs) - 1)
+                          if len(pairs) > 1 else 0.0)}
     return start.elapsed_time(end) / steps, k1
 
 
@@ -516,6 +522,7 @@ def run_ours(args, rank, world, local_rank):
                 "ms_per_step": e2e},
         "gpu_launches": int(launches),
         "host_submit_ms_per_step": time_overlapped.host_submit_ms,
+        "main_stream_ms_per_step": time_overlapped.main_stream_ms,
         "roofline": {"bound": "hbm", "kernel": "k_scan_keys", "achieved": achieved, "peak": peak, "unit": "GB/s",
                      "frac": achieved / peak, "traffic": traffic, "peak_source": peak_src,
                      "kernel_ms": k1, "kernel_share_of_step": k1 / step,

@@ -310,6 +310,8 @@ class OverlappedReplay:
             if scan_events is not None:
                 scan_events[1].record(self.main)
             eng.join_route_dedup(n, now, base_index, cols)
+            if scan_events is not None and len(scan_events) > 2:
+                scan_events[2].record(self.main)
             self.joined[lane].record(self.main)
         if ex is not None:
             with torch.cuda.stream(self.side):
