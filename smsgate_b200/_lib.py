@@ -113,6 +113,7 @@ def lib():
         "smsgate_cache_share": (i32, [vp, vp]),
         "smsgate_set_stream": (i32, [vp, vp]),
         "smsgate_set_scan_ctas": (i32, [vp, i32]),
+        "smsgate_set_host_pipeline": (i32, [vp, i32, i64, i32]),
         "smsgate_set_phone_dates": (i32, [vp, vp]),
         "smsgate_dcache_open": (i32, [C.c_char_p, C.c_double, C.POINTER(vp), C.c_char_p, i32]),
         "smsgate_dcache_sizes": (i32, [vp, vp, vp, vp, vp, vp]),

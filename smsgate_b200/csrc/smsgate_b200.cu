@@ -796,6 +796,8 @@ struct smsgate_ctx {
     int64_t xml_attr_total = -1;
     int sm_count = 148;
     int scan_ctas = 0;                       // CTAs of k_scan_keys, 0 = one per SM (smsgate_set_scan_ctas)
+    int host_div = 5, host_offsets_first = 0;    // smsgate_set_host_pipeline: how smsgate_replay_host* cuts the batch
+    int64_t host_min_chunk = 65536;
     int64_t fuse_bits_words = 0;             // > 0: the join's fused insert also marks the prefilter bitmap (smsgate_p2p_fuse_filter)
     bool bits_ready = false;                 // ... and has done so for the batch in the dedup table
     const int64_t* phone_dt = nullptr;       // per-message phone timestamps for the next join (smsgate_set_phone_dates)
@@ -1175,6 +1177,15 @@ extern "C" int smsgate_set_stream(smsgate_ctx* ctx, void* cuda_stream) {
 extern "C" int smsgate_set_phone_dates(smsgate_ctx* ctx, const int64_t* d_phone_dt) {
     if (!ctx) return SMSGATE_E_ARG;
     ctx->phone_dt = d_phone_dt;
+    return SMSGATE_OK;
+}
+
+extern "C" int smsgate_set_host_pipeline(smsgate_ctx* ctx, int divisor, int64_t min_chunk, int offsets_first) {
+    if (!ctx) return SMSGATE_E_ARG;
+    if (divisor < 1 || divisor > 16 || min_chunk < 1024) return fail(ctx, SMSGATE_E_ARG, "set_host_pipeline: divisor in 1..16, min_chunk >= 1024");
+    ctx->host_div = divisor;
+    ctx->host_min_chunk = min_chunk;
+    ctx->host_offsets_first = offsets_first ? 1 : 0;
     return SMSGATE_OK;
 }
 
@@ -1874,12 +1885,12 @@ static int replay_host_begin_impl(smsgate_ctx* ctx, const uint8_t* h_bytes, cons
     int64_t bound[smsgate_ctx::MAX_CHUNKS + 1];
     int nchunks = 0;
     {
-        const int64_t min_chunk = 65536;
+        const int64_t min_chunk = ctx->host_min_chunk;
         int64_t lo = 0;
         bound[0] = 0;
         while (lo < n) {
             const int64_t rem = n - lo;
-            int64_t sz = rem / 5 > min_chunk ? rem / 5 : min_chunk;
+            int64_t sz = rem / ctx->host_div > min_chunk ? rem / ctx->host_div : min_chunk;
             if (nchunks == smsgate_ctx::MAX_CHUNKS - 1 || rem - sz < min_chunk / 2) sz = rem;
             lo += sz;
             bound[++nchunks] = lo;
@@ -1889,10 +1900,13 @@ static int replay_host_begin_impl(smsgate_ctx* ctx, const uint8_t* h_bytes, cons
     CUDA_TRY(ctx, cudaEventRecord(ctx->ev_start, st));
     CUDA_TRY(ctx, cudaStreamWaitEvent(sin, ctx->ev_start, 0));
     CUDA_TRY(ctx, cudaStreamWaitEvent(sout, ctx->ev_start, 0));
+    if (ctx->host_offsets_first)                       // all offsets in ONE copy ahead of the bodies instead of one small copy per chunk
+        CUDA_TRY(ctx, cudaMemcpyAsync(ctx->s_offsets, h_offsets, (size_t)(n + 1) * 8, cudaMemcpyHostToDevice, sin));
     for (int c = 0; c < nchunks; ++c) {
         const int64_t lo = bound[c], hi = bound[c + 1];
         const int64_t b0 = h_offsets[lo], b1 = h_offsets[hi];
-        CUDA_TRY(ctx, cudaMemcpyAsync(ctx->s_offsets + lo, h_offsets + lo, (size_t)(hi - lo + 1) * 8, cudaMemcpyHostToDevice, sin));
+        if (!ctx->host_offsets_first)
+            CUDA_TRY(ctx, cudaMemcpyAsync(ctx->s_offsets + lo, h_offsets + lo, (size_t)(hi - lo + 1) * 8, cudaMemcpyHostToDevice, sin));
         if (b1 > b0) CUDA_TRY(ctx, cudaMemcpyAsync(ctx->s_bytes + b0, h_bytes + b0, (size_t)(b1 - b0), cudaMemcpyHostToDevice, sin));
         CUDA_TRY(ctx, cudaEventRecord(ctx->ev_in[c], sin));
     }
