@@ -166,15 +166,13 @@ struct ScanState {
     uint32_t ci, cs, dm;     // row byte offsets in their tables
     uint32_t dm_event;       // next date-progress threshold the DM row offset has to reach
     int posB, posA;          // offset of the byte that completed the short / long date form
-    int wordB, wordA;        // the word loop only notes WHICH word completed a form (and the state before it) ...
-    uint32_t stateB, stateA; // ... the byte is found after the loop, by all lanes of the warp together
     uint32_t modified;       // U+00A0 or U+2022 seen
 };
 
 // A date-progress event (rows are sorted by progress): rare, at most twice per body.
 SG_HD void sg_scan_event(ScanState& st, int i) {
-    if (st.posB < 0 && st.wordB < 0) st.posB = i;
-    if (st.dm >= DM_FIRST_A_OFF) { if (st.wordA < 0) st.posA = i; st.dm_event = 0xFFFFFFFFu; }
+    if (st.posB < 0) st.posB = i;
+    if (st.dm >= DM_FIRST_A_OFF) { st.posA = i; st.dm_event = 0xFFFFFFFFu; }
     else st.dm_event = DM_FIRST_A_OFF;
 }
 
@@ -229,8 +227,6 @@ SG_HD ScanResult sg_scan_body_t(const uint8_t* m, int len, const ScanTables& T) 
     st.ci = st.cs = st.dm = 0;
     st.dm_event = DM_FIRST_B_OFF;
     st.posB = st.posA = -1;
-    st.wordB = st.wordA = -1;
-    st.stateB = st.stateA = 0;
     st.modified = 0;
     int i = 0;
     const int head = (int)((4 - ((uintptr_t)m & 3)) & 3);
@@ -261,19 +257,6 @@ SG_HD ScanResult sg_scan_body_t(const uint8_t* m, int len, const ScanTables& T) 
             dm = sg_step(T_DM(T), dm, sg_byte(cw, 2));
         }
         st.ci = ci; st.cs = cs;
-#ifndef SG_OLD_EVENTS
-        if (dm >= st.dm_event) {
-            // a date form completed inside this word.  Which byte it was is found after the loop (every body has
-            // one or two such events, each at another word: handled here, lane by lane, they cost a divergent
-            // replay per event; handled after the loop all lanes of the warp do it at once)
-            if (st.posB < 0 && st.wordB < 0) { st.wordB = i; st.stateB = dm_before; }
-            if (dm >= DM_FIRST_A_OFF) {
-                if (st.posA < 0 && st.wordA < 0) { st.wordA = i; st.stateA = dm_before; }
-                st.dm_event = 0xFFFFFFFFu;
-            } else st.dm_event = DM_FIRST_A_OFF;
-        }
-        st.dm = dm;
-#else
         if (dm >= st.dm_event) {
             // a date form completed inside this word: replay its four bytes one by one for the position
             st.dm = dm_before;
@@ -282,26 +265,8 @@ SG_HD ScanResult sg_scan_body_t(const uint8_t* m, int len, const ScanTables& T) 
                 if (st.dm >= st.dm_event) sg_scan_event(st, i + k);
             }
         } else st.dm = dm;
-#endif
     }
     for (; i < len; ++i) st = sg_scan_byte_careful<FIRST>(m, len, i, T, st);
-    // the noted words: step their four bytes again from the state before them; the first byte that reaches the
-    // form's progress level is the one that completed it
-    if (st.wordB >= 0) {
-        uint32_t d = st.stateB;
-        for (int k = 0; k < 4; ++k) {
-            d = sg_step(T_DM(T), d, sg_byte(T_BYTE_CLASS(T)[m[st.wordB + k]], 2));
-            if (d >= DM_FIRST_B_OFF) { st.posB = st.wordB + k; break; }
-        }
-    }
-    if (st.wordA >= 0) {
-        uint32_t d = st.stateA;
-        for (int k = 0; k < 4; ++k) {
-            d = sg_step(T_DM(T), d, sg_byte(T_BYTE_CLASS(T)[m[st.wordA + k]], 2));
-            if (d >= DM_FIRST_A_OFF) { st.posA = st.wordA + k; break; }
-        }
-    }
-
     ScanResult r;
     r.flags = 0;
     if (FIRST) {

@@ -560,7 +560,9 @@ __device__ __forceinline__ void dedup_insert_one(int64_t i, const uint8_t* __res
 }
 
 #ifndef K2_MIN_BLOCKS
-#define K2_MIN_BLOCKS 6      // 40 registers: six CTAs per SM hide the probe latency best (measured 1 / 6 / 8)
+#define K2_MIN_BLOCKS 5      // 48 registers, no spills; 6 (40 registers) is as fast but spills 48 bytes per thread to local
+                             // memory since the one-pass decimal parser (+30 MB of DRAM writes per 1 M messages), 4 is slower
+                             // (profiles/r2i_scan_variants.json: join5 / join4 against base)
 #endif
 __global__ void __launch_bounds__(256, K2_MIN_BLOCKS)
 k_join_route(int64_t n, const uint8_t* __restrict__ cache_key, const uint8_t* __restrict__ flags,
