@@ -41,20 +41,29 @@ def _np_ptr(a: Optional[np.ndarray]):
 
 class _RecordColumns:
     """The `cols` mapping of a ReplayResult that came back as packed records
-    (smsgate_replay_host_records): record fields are strided views, the three
-    dedup columns are decoded from the verdict integers on first use."""
+    (smsgate_replay_host_records / _records8).  Three kinds of column:
+      - fields of the 64-byte record: strided views of the record array;
+      - the dedup verdicts: decoded on first use from the verdict array - one int64 per message
+        (-1, or last_idx << 2 | first_seen << 1 | survivor) or one byte per message (0, or
+        0x80 | first_seen << 1 | survivor; `last_idx` then stays on the device);
+      - what the record leaves out (card, cache_key, fixed body, cents): still on the device until the
+        engine's next replay, fetched on first use (smsgate_fetch_columns)."""
+
+    _VERDICT = ("survivor", "first_seen", "last_idx")
+    _ON_DEVICE = ("card", "cache_key", "fixed_len", "fixed_bytes", "amount_cents", "balance_cents")
 
     def __init__(self, records: np.ndarray, verdict: np.ndarray, engine=None, generation: int = 0, total: int = 0):
         self.records = records
         self.verdict = verdict
-        self._decoded: dict = {}
-        self._engine = engine            # for the columns the record does not carry (fetched on first use)
+        self._engine = engine
         self._generation = generation
         self._total = total
+        self._decoded: dict = {}
         self._fetched: dict = {}
 
-    _VERDICT = ("survivor", "first_seen", "last_idx")
-    _ON_DEVICE = ("card", "cache_key", "fixed_len", "fixed_bytes", "amount_cents", "balance_cents")
+    @property
+    def _compact(self) -> bool:
+        return self.verdict.dtype == np.uint8
 
     def keys(self):
         return tuple(self.records.dtype.names) + self._VERDICT + self._ON_DEVICE
@@ -63,63 +72,55 @@ class _RecordColumns:
         return iter(self.keys())
 
     def __contains__(self, name) -> bool:
-        return name in self.records.dtype.names or name in self._VERDICT or name in self._ON_DEVICE
+        return name in self.keys()
 
-    def _fetch(self, name):
-        """A column the 64-byte record leaves out: still on the device until the engine's next replay."""
-        if name not in self._fetched:
-            eng = self._engine
-            if eng is None or eng._generation != self._generation:
-                raise RuntimeError(f"column {name!r} of this result was left on the device and a later replay has "
-                                   "replaced it; read it (or call ReplayResult.detach()) before replaying again, "
-                                   "or use ReplayEngine.replay(columns=...)")
-            if len(self.records) == 0:
-                self._fetched.update(eng._host_columns(0, 0, self._ON_DEVICE, pinned=False))
-            else:
-                self._fetched.update(eng._fetch_columns(len(self.records), self._total,
-                                                        [c for c in self._ON_DEVICE if c not in self._fetched]))
-        return self._fetched[name]
+    def _fetch(self, names) -> None:
+        """Bring columns that were left on the device to the host (once)."""
+        names = [c for c in names if c not in self._fetched]
+        if not names:
+            return
+        eng = self._engine
+        if eng is None or eng._generation != self._generation:
+            raise RuntimeError(f"columns {names} of this result were left on the device and a later replay has "
+                               "replaced them; read them (or call ReplayResult.detach()) before replaying again, "
+                               "or use ReplayEngine.replay(columns=...)")
+        if len(self.records) == 0:
+            self._fetched.update(eng._host_columns(0, 0, tuple(names), pinned=False))
+        else:
+            self._fetched.update(eng._fetch_columns(len(self.records), self._total, names))
 
     def __getitem__(self, name):
         if name in self.records.dtype.names:
             return self.records[name]
         if name in self._ON_DEVICE:
-            return self._fetch(name)
+            self._fetch(self._ON_DEVICE)                    # all of them in one call: they are wanted together
+            return self._fetched[name]
         if name not in self._VERDICT:
             raise KeyError(name)
-        if self.verdict.dtype == np.uint8:                 # one byte per message: 0x80 upserted | first_seen << 1 | survivor
-            if name == "last_idx":
-                if "last_idx" not in self._fetched:
-                    eng = self._engine
-                    if eng is None or eng._generation != self._generation:
-                        raise RuntimeError("last_idx of this result was left on the device and a later replay has replaced it")
-                    self._fetched.update(eng._fetch_columns(len(self.records), self._total, ["last_idx"])
-                                         if len(self.records) else {"last_idx": np.zeros(0, np.int64)})
-                return self._fetched["last_idx"]
-            if name not in self._decoded:
-                v = self.verdict
-                self._decoded["survivor"] = (v & 1).astype(np.uint8)
-                self._decoded["first_seen"] = ((v >> 1) & 1).astype(np.uint8)
-            return self._decoded[name]
+        if name == "last_idx" and self._compact:
+            self._fetch(["last_idx"])
+            return self._fetched["last_idx"]
         if name not in self._decoded:
             v = self.verdict
-            up = v >= 0
-            self._decoded["survivor"] = (up & ((v & 1) != 0)).astype(np.uint8)
-            self._decoded["first_seen"] = (up & ((v & 2) != 0)).astype(np.uint8)
-            self._decoded["last_idx"] = np.where(up, v >> 2, -1).astype(np.int64)
+            if self._compact:
+                self._decoded["survivor"] = (v & 1).astype(np.uint8)
+                self._decoded["first_seen"] = ((v >> 1) & 1).astype(np.uint8)
+            else:
+                up = v >= 0
+                self._decoded["survivor"] = (up & ((v & 1) != 0)).astype(np.uint8)
+                self._decoded["first_seen"] = (up & ((v & 2) != 0)).astype(np.uint8)
+                self._decoded["last_idx"] = np.where(up, v >> 2, -1).astype(np.int64)
         return self._decoded[name]
 
     @property
     def nbytes(self) -> int:
+        """Bytes that crossed PCIe for this result (records + verdicts)."""
         return int(self.records.nbytes + self.verdict.nbytes)
 
     def detach(self) -> None:
         """Own copies of everything: the records and verdicts alias the engine's pinned staging buffer and
         the remaining columns live on the device, both only until the engine's next replay."""
-        for name in self._ON_DEVICE:
-            self._fetch(name)
-        if self.verdict.dtype == np.uint8:
-            self["last_idx"]
+        self._fetch(self._ON_DEVICE + (("last_idx",) if self._compact else ()))
         self.records = self.records.copy()
         self.verdict = self.verdict.copy()
         self._decoded = {}
