@@ -434,7 +434,8 @@ int smsgate_replay_host(smsgate_ctx* ctx, const uint8_t* h_bytes, const int64_t*
 
 /* Tuning of the host call's pipeline, no counterpart in the reference: every chunk takes 1/divisor of what is left
  * of the batch (at least min_chunk messages), and the offsets travel either with their chunk or all at once ahead
- * of the bodies.  Defaults 5, 65536, 0.  (At most 16 chunks: the last one takes the rest.) */
+ * of the bodies.  Defaults 3, 131072, 1 (the best of a sweep at 1 M messages).  At most 16 chunks: the last one takes
+ * the rest. */
 int smsgate_set_host_pipeline(smsgate_ctx* ctx, int divisor, int64_t min_chunk, int offsets_first);
 /* Diagnostics, no counterpart in the reference: where the time of the last smsgate_replay_host()
  * went.  Fills ms[] with GPU times relative to the start of that call: ms[0..c) = host->device copy

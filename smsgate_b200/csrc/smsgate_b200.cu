@@ -470,28 +470,20 @@ __global__ void k_cache_fix_fp(const uint8_t* __restrict__ keys, int2* __restric
     if (e >= 0) table[p].y = (int)key_fp(keys + (int64_t)e * 32);
 }
 
-// Per cache entry, next to the table, ONE 64-byte record: the loader's flags, the lengths of the entry's four strings
-// and - when they fit, which they do for any real response (an amount, a balance, a date, a card: ~45 bytes) - the
-// strings themselves.  A hit then costs one random access for everything the routing needs (the header load and a
-// prefetch of the second sector go out together with the key compare) instead of a chain of two: record, then strings.
-// Entries whose strings do not fit (`inline_ok` = 0) keep them in val_bytes at val_off, as before; date_packed is read
-// only for the few entries whose flags say it is used.
-#ifndef SG_NO_INLINE_STRINGS
-#define SG_INLINE_STRINGS 1
-#else
-#define SG_INLINE_STRINGS 0
-#endif
-struct __align__(64) CacheSide {
+// Per cache entry, next to the table: where its four strings start, how long each is and the loader's
+// flags, in ONE 16-byte record - a hit reads one sector here instead of one each from val_offsets (20 bytes
+// straddling two), eflags and date_packed.  A length of 0xFFFF means "look it up in val_offsets" (a field
+// of 64 KiB or more); date_packed is read only for the entries whose flags say it is used.
+struct __align__(16) CacheSide {
     int32_t val_off;
     uint16_t eflags;
-    uint16_t len[4];     // str(amount), str(balance), date, card; 0xFFFF in len[0] = "look the lengths up in val_offsets"
-    uint16_t inline_ok;  // the four strings follow, back to back
-    uint8_t text[48];
+    uint16_t len[4];     // str(amount), str(balance), date, card
+    uint16_t pad;
 };
-static_assert(sizeof(CacheSide) == 64, "one side record is 64 bytes");
+static_assert(sizeof(CacheSide) == 16, "one side record is 16 bytes");
 
-__global__ void k_cache_side(int64_t m, const int32_t* __restrict__ val_offsets, const uint8_t* __restrict__ val_bytes,
-                             const uint16_t* __restrict__ eflags, CacheSide* __restrict__ side) {
+__global__ void k_cache_side(int64_t m, const int32_t* __restrict__ val_offsets, const uint16_t* __restrict__ eflags,
+                             CacheSide* __restrict__ side) {
     const int64_t e = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
     if (e >= m) return;
     const int32_t* o = val_offsets + e * 4;
@@ -501,9 +493,7 @@ __global__ void k_cache_side(int64_t m, const int32_t* __restrict__ val_offsets,
     bool wide = false;
     for (int k = 0; k < 4; ++k) wide |= (o[k + 1] - o[k]) >= 0xFFFF;
     for (int k = 0; k < 4; ++k) sd.len[k] = wide ? (uint16_t)0xFFFF : (uint16_t)(o[k + 1] - o[k]);
-    const int total = o[4] - o[0];
-    sd.inline_ok = (SG_INLINE_STRINGS && !wide && total <= (int)sizeof(sd.text)) ? 1 : 0;
-    for (int k = 0; k < (int)sizeof(sd.text); ++k) sd.text[k] = (sd.inline_ok && k < total) ? val_bytes[o[0] + k] : 0;
+    sd.pad = 0;
     side[e] = sd;
 }
 
@@ -594,8 +584,7 @@ k_join_route(int64_t n, const uint8_t* __restrict__ cache_key, const uint8_t* __
             if (sl.y == fp) {
                 const uint4* a = reinterpret_cast<const uint4*>(C.keys + (int64_t)sl.x * 32);
                 const uint4 a0 = a[0], a1 = a[1];
-                sdw = *reinterpret_cast<const uint4*>(C.side + sl.x);      // in flight together with the key ...
-                asm volatile("prefetch.global.L1 [%0];" ::"l"(reinterpret_cast<const uint8_t*>(C.side + sl.x) + 32));   // ... and the record's second sector
+                sdw = *reinterpret_cast<const uint4*>(C.side + sl.x);      // in flight together with the key
                 if (a0.x == k0.x && a0.y == k0.y && a0.z == k0.z && a0.w == k0.w && a1.x == k1.x && a1.y == k1.y &&
                     a1.z == k1.z && a1.w == k1.w) {
                     e = sl.x;
@@ -611,16 +600,14 @@ k_join_route(int64_t n, const uint8_t* __restrict__ cache_key, const uint8_t* __
     ev.eflags = 0;
     ev.date_packed = 0;
     if (e >= 0) {
-        // side record: x = val_off, y = eflags | len[0] << 16, z = len[1] | len[2] << 16, w = len[3] | inline_ok << 16
+        // side record: x = val_off, y = eflags | len[0] << 16, z = len[1] | len[2] << 16, w = len[3]
         int32_t o0 = (int32_t)sdw.x, l0 = (int32_t)(sdw.y >> 16), l1 = (int32_t)(sdw.z & 0xFFFF),
                 l2 = (int32_t)(sdw.z >> 16), l3 = (int32_t)(sdw.w & 0xFFFF);
         if (l0 == 0xFFFF) {                              // a field of 64 KiB or more: the full offsets
             const int32_t* o = C.val_offsets + (int64_t)e * 4;
             o0 = o[0]; l0 = o[1] - o[0]; l1 = o[2] - o[1]; l2 = o[3] - o[2]; l3 = o[4] - o[3];
         }
-        // the strings: inside the record (the common case) or in val_bytes
-        ev.amount = (sdw.w >> 16) ? reinterpret_cast<const uint8_t*>(C.side + e) + 16 : C.val_bytes + o0;
-        ev.amount_len = l0;
+        ev.amount = C.val_bytes + o0; ev.amount_len = l0;
         ev.balance = ev.amount + l0; ev.balance_len = l1;
         ev.date = ev.balance + l1; ev.date_len = l2;
         ev.card = ev.date + l2; ev.card_len = l3;
@@ -811,8 +798,8 @@ struct smsgate_ctx {
     int64_t xml_attr_total = -1;
     int sm_count = 148;
     int scan_ctas = 0;                       // CTAs of k_scan_keys, 0 = one per SM (smsgate_set_scan_ctas)
-    int host_div = 5, host_offsets_first = 0;    // smsgate_set_host_pipeline: how smsgate_replay_host* cuts the batch
-    int64_t host_min_chunk = 65536;
+    int host_div = 3, host_offsets_first = 1;    // smsgate_set_host_pipeline: how smsgate_replay_host* cuts the batch
+    int64_t host_min_chunk = 131072;             // (measured best of profiles/r2k_host_pipeline_sweep.json)
     int64_t fuse_bits_words = 0;             // > 0: the join's fused insert also marks the prefilter bitmap (smsgate_p2p_fuse_filter)
     bool bits_ready = false;                 // ... and has done so for the batch in the dedup table
     const int64_t* phone_dt = nullptr;       // per-message phone timestamps for the next join (smsgate_set_phone_dates)
@@ -1153,7 +1140,7 @@ extern "C" int smsgate_cache_load(smsgate_ctx* ctx, int64_t m, const uint8_t* h_
     CUDA_TRY(ctx, cudaMemsetAsync(d_dup, 0, 4, st));
     k_cache_build<<<(unsigned)((m + 255) / 256), 256, 0, st>>>(ctx->c_keys, m, ctx->c_table, cap - 1, d_dup);
     k_cache_fix_fp<<<(unsigned)((cap + 255) / 256), 256, 0, st>>>(ctx->c_keys, ctx->c_table, cap);
-    k_cache_side<<<(unsigned)((m + 255) / 256), 256, 0, st>>>(m, ctx->c_val_offsets, ctx->c_val_bytes, ctx->c_eflags, ctx->c_side);
+    k_cache_side<<<(unsigned)((m + 255) / 256), 256, 0, st>>>(m, ctx->c_val_offsets, ctx->c_eflags, ctx->c_side);
     ctx->launches += 3;
     int dup = 0;
     CUDA_TRY(ctx, cudaMemcpyAsync(&dup, d_dup, 4, cudaMemcpyDeviceToHost, st));

@@ -490,7 +490,7 @@ class ReplayEngine:
         self._phone_keepalive = d_phone_dt
         L.check(self._ctx, self._lib.smsgate_set_phone_dates(self._ctx, d_phone_dt.data_ptr() if d_phone_dt is not None else None))
 
-    def set_host_pipeline(self, divisor: int = 5, min_chunk: int = 65536, offsets_first: bool = False) -> None:
+    def set_host_pipeline(self, divisor: int = 3, min_chunk: int = 131072, offsets_first: bool = True) -> None:
         """How the host-buffer calls cut a batch into chunks (smsgate_set_host_pipeline)."""
         L.check(self._ctx, self._lib.smsgate_set_host_pipeline(self._ctx, int(divisor), int(min_chunk), int(offsets_first)))
 
