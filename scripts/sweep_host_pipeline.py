@@ -27,8 +27,8 @@ hb = Batch(h_bytes.numpy(), h_offs.numpy(), backup.senders, None)
 flush = torch.empty(512 << 20, dtype=torch.uint8, device="cuda")
 ev = lambda: torch.cuda.Event(enable_timing=True)  # noqa: E731
 out = []
-for div, mn, first in ((5, 65536, 0), (5, 65536, 1), (4, 65536, 1), (3, 65536, 1), (6, 32768, 1), (8, 32768, 1), (4, 32768, 1),
-                       (3, 131072, 1), (2, 65536, 1), (4, 131072, 0)):
+for div, mn, first in ((5, 65536, 0), (3, 131072, 1), (3, 131072, 0), (3, 100000, 1), (3, 163840, 1), (3, 196608, 1),
+                       (4, 131072, 1), (4, 100000, 1), (2, 131072, 1), (2, 196608, 1), (5, 131072, 1), (3, 262144, 1)):
     eng.set_host_pipeline(div, mn, bool(first))
     ts = []
     for it in range(9):
