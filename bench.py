@@ -249,6 +249,7 @@ def time_resident(eng, R, exchange, steps, warmup, flush, barrier):
     import torch
     ev = lambda: torch.cuda.Event(enable_timing=True)  # noqa: E731
     k1_ms, step_ms = [], []
+    barrier()                                           # ranks build their workloads at different speeds: line up before the first exchange
     for it in range(warmup + steps):
         if it == warmup:
             barrier()
@@ -287,6 +288,7 @@ def time_overlapped(ov, R, steps, warmup, barrier, copies=3):
         if timed:
             pairs.append(pe)
 
+    barrier()
     for k in range(warmup):
         go(k, False)
     ov.drain()
@@ -336,6 +338,8 @@ def exchange_parity(eng, dist, rank, world, ex, shape: dict, n_per: int = 20_000
     d_bytes[:total] = torch.from_numpy(b.body_bytes.copy()).cuda()
     d_offs = torch.from_numpy(b.body_offsets.copy()).cuda()
     cols = eng.device_columns(n_per, total + 64)
+    torch.cuda.synchronize()
+    dist.barrier()
     for _ in range(2):                                   # twice: the arrival counters alternate
         eng.replay_device(d_bytes, d_offs, NOW, cols, base_index=lo)
         ex.run(cols, lo)

@@ -408,8 +408,9 @@ int smsgate_p2p_filter_reduce(smsgate_ctx* ctx, const smsgate_p2p* p);
 /* The cross-GPU barrier the steps above need between them, queued on the context's stream like any kernel (no
  * host synchronisation): every rank calls it with the same `epoch`, which must grow by one from call to call.
  * It returns (on the GPU) once every rank's earlier stores into peer memory are visible here.  One tiny block,
- * so it is scheduled even while another stream's kernels fill the SMs.  A rank that waits ~2 s gives up and
- * raises the overflow flag (reported as 2 by smsgate_p2p_resolve). */
+ * so it is scheduled even while another stream's kernels fill the SMs.  A rank that waits ~10 s gives up and
+ * raises the overflow flag (reported as 2 by smsgate_p2p_resolve): the ranks have to reach a barrier within that
+ * time of each other. */
 int smsgate_p2p_barrier(smsgate_ctx* ctx, const smsgate_p2p* p, int epoch);
 /* Let the join kernel's fused upsert insert (smsgate_join_route_dedup, smsgate_replay_host*) mark this rank's
  * prefilter bitmap as it goes, so that smsgate_p2p_filter_push has no pass of its own over the batch left

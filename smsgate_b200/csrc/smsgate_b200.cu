@@ -2588,8 +2588,8 @@ k_p2p_resolve(int64_t n, int64_t base_index, const int32_t* __restrict__ slot_of
 // dozen registers) to be scheduled next to anything: thread w stores `epoch` into rank w's flag for this rank
 // (a system-scope release after the fence: everything this rank's earlier kernels stored into peer memory is
 // visible before the flag is), then waits until rank w's flag for it has reached `epoch`.  Epochs only grow, the
-// flags are never reset.  The wait gives up after about two seconds and raises the overflow flag (value 2)
-// rather than hang the GPU.
+// flags are never reset.  The wait gives up after about ten seconds and raises the overflow flag (value 2)
+// rather than hang the GPU: ranks must reach a barrier within that time of each other.
 __global__ void __launch_bounds__(SMSGATE_MAX_WORLD)
 k_p2p_barrier(P2PView P, int epoch, int* __restrict__ overflow) {
     const int w = threadIdx.x;
@@ -2602,7 +2602,7 @@ k_p2p_barrier(P2PView P, int epoch, int* __restrict__ overflow) {
         int v;
         asm volatile("ld.acquire.sys.global.s32 %0, [%1];" : "=r"(v) : "l"(mine) : "memory");
         if (v - epoch >= 0) break;
-        if (clock64() - t0 > 4000000000ll) { atomicExch(overflow, 2); break; }
+        if (clock64() - t0 > 20000000000ll) { atomicExch(overflow, 2); break; }    // ~10 s at 2 GHz
         __nanosleep(200);
     }
 }

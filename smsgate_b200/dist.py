@@ -224,7 +224,7 @@ class GlobalDedupP2P:
         L.check(self.engine._ctx, L.lib().smsgate_p2p_resolve(self.engine._ctx, 0, 0, 0, C.byref(out), C.byref(self.desc),
                                                               C.byref(flag)))
         if flag.value == 2:
-            raise RuntimeError("a cross-GPU barrier of the exchange timed out (a rank fell behind by more than ~2 s)")
+            raise RuntimeError("a cross-GPU barrier of the exchange timed out (a rank fell behind by more than ~10 s)")
         return bool(flag.value)
 
 

@@ -283,7 +283,7 @@ def test_peer_memory_exchange_emulated_on_one_gpu(world, prefilter, ragged):
 
 def test_in_stream_barrier_single_rank_and_timeout():
     """smsgate_p2p_barrier: with one rank it signals and finds its own flag; a rank whose peer never arrives
-    gives up after about two seconds and reports it instead of hanging the GPU."""
+    gives up after about ten seconds and reports it instead of hanging the GPU."""
     import torch
 
     from smsgate_b200.replay import ReplayEngine
