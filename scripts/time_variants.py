@@ -1,5 +1,5 @@
 """Times builds of the library against each other on one GPU: smsgate_b200/variants/lib*.so (made by
-smsgate_b200.build.build_variant) on the hit100 and mixed workloads, keys kernel and whole step, with the L2
+smsgate_b200.build.build_variant) on the hit100 and mixed workloads (VARIANT_WORKLOADS=hit100,skew,... picks others), keys kernel and whole step, with the L2
 flushed between steps.  Every variant's key columns are compared with the first one's.
 Usage: python scripts/time_variants.py [name ...] > gpurun_out/variants.json"""
 import glob
@@ -36,7 +36,10 @@ def main():
     flush = torch.empty(512 << 20, dtype=torch.uint8, device="cuda")
     ev = lambda: torch.cuda.Event(enable_timing=True)  # noqa: E731
     out = {}
-    for wl, kw in (("hit100", dict(seed=0x5EED + 2)), ("mixed", dict(seed=0x5EED + 5, mixed_locale=True, miss_frac=0.3))):
+    known = {"hit100": dict(seed=0x5EED + 2), "mixed": dict(seed=0x5EED + 5, mixed_locale=True, miss_frac=0.3),
+             "dup10": dict(seed=0x5EED + 3, dup_frac=0.10), "skew": dict(seed=0x5EED + 4, dup_frac=0.5, hot_key_zipf=1.2)}
+    for wl in os.environ.get("VARIANT_WORKLOADS", "hit100,mixed").split(","):
+        kw = known[wl]
         backup = synth.generate(N, **kw)
         batch = Batch.from_strings(backup.bodies, backup.senders, backup.date_ms)
         total = int(batch.body_offsets[-1])
@@ -73,11 +76,11 @@ def main():
                 tot = float(sum(buf[:4])) or 1.0
                 phases = {k: round(buf[i] / tot, 4) for i, k in enumerate(("stage_sort", "scan", "partition", "hash"))}
                 phases["clocks_per_cta"] = tot / 148
-            chk = [int(cols[c].to(torch.int64).sum().item()) for c in ("msg_id", "cache_key", "flags", "status", "survivor")]
+            chk = [int(cols[c].to(torch.int64).sum().item()) for c in ("msg_id", "cache_key", "flags", "status", "survivor", "first_seen", "last_idx")]
             if ref_sum is None:
                 ref_sum = chk
             out.setdefault(wl, {})[name] = {"k_scan_keys_ms": sum(k1) / len(k1), "k_scan_keys_min_ms": min(k1),
-                                            "step_ms": sum(step) / len(step), "same_results_as_first": chk == ref_sum,
+                                            "step_ms": sum(step) / len(step), "join_dedup_ms": (sum(step) - sum(k1)) / len(step), "same_results_as_first": chk == ref_sum,
                                             "phase_share": phases}
             print(wl, name, out[wl][name], file=sys.stderr, flush=True)
             eng.close()

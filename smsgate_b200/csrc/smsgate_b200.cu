@@ -541,32 +541,64 @@ __device__ __forceinline__ bool id20_equal(const uint8_t* a, const uint8_t* b) {
     return x[0] == y[0] && x[1] == y[1] && x[2] == y[2] && x[3] == y[3] && x[4] == y[4];
 }
 
-// claim / find the slot of message i's key and fold i into the slot's first / last occurrence
-__device__ __forceinline__ void dedup_insert_one(int64_t i, const uint8_t* __restrict__ msg_id, const DedupScratch& D) {
-    const uint8_t* k = msg_id + i * 20;
+// claim / find the slot of the key at `k` for message index `lo` and fold [lo, hi] into the slot's first / last
+// occurrence; returns the slot
+__device__ __forceinline__ uint64_t dedup_fold(const uint8_t* __restrict__ k, unsigned lo, int hi,
+                                               const uint8_t* __restrict__ msg_id, const DedupScratch& D) {
     const uint32_t* kw = reinterpret_cast<const uint32_t*>(k);
     uint64_t pos = (((uint64_t)kw[1] << 32) | kw[0]) & D.mask;
-    bool claimed = false;
-    unsigned first_seen_then = DD_EMPTY;
+    unsigned first_then;
     for (;;) {
-        const unsigned prev = atomicCAS(reinterpret_cast<unsigned*>(&D.tab[pos].x), DD_EMPTY, (unsigned)i);
-        first_seen_then = prev;
-        if (prev == DD_EMPTY) { claimed = true; break; }
-        // `prev` is some message with this slot's key (a concurrent atomicMin only swaps it for another one)
-        if (prev == (unsigned)i || id20_equal(msg_id + (int64_t)prev * 20, k)) break;
+        first_then = atomicCAS(reinterpret_cast<unsigned*>(&D.tab[pos].x), DD_EMPTY, lo);
+        if (first_then == DD_EMPTY) break;
+        // `first_then` is some message with this slot's key (a concurrent atomicMin only swaps it for another one)
+        if (first_then == lo || id20_equal(msg_id + (int64_t)first_then * 20, k)) break;
         pos = (pos + 1) & D.mask;
     }
-    if (claimed) {
-        atomicMax(&D.tab[pos].y, (int)i);
+#ifdef DD_THREE_ATOMICS
+    if (first_then != DD_EMPTY) atomicMin(reinterpret_cast<unsigned*>(&D.tab[pos].x), lo);
+    atomicMax(&D.tab[pos].y, hi);
+#else
+    if (first_then == DD_EMPTY) {
+        atomicMax(&D.tab[pos].y, hi);
     } else {
         // A later occurrence of a key.  `first` only ever decreases and `last` only ever increases, so a value read
         // a moment ago is enough to tell that an atomic would change nothing: the CAS returned `first` as it was,
-        // a plain (L2) load gives `last` - hot keys (50 % Zipf duplicates put 90 000 messages on one slot) would
-        // otherwise queue three atomics each on the same eight bytes.
-        if ((unsigned)i < first_seen_then) atomicMin(reinterpret_cast<unsigned*>(&D.tab[pos].x), (unsigned)i);
-        if ((int)i > __ldcg(&D.tab[pos].y)) atomicMax(&D.tab[pos].y, (int)i);
+        // an L2 load gives `last`.  Hot keys (50 % Zipf(1.2) duplicates put 90 000 of a million messages on one slot)
+        // would otherwise queue three atomics each on the same eight bytes.
+        if (lo < first_then) atomicMin(reinterpret_cast<unsigned*>(&D.tab[pos].x), lo);
+        if (hi > __ldcg(&D.tab[pos].y)) atomicMax(&D.tab[pos].y, hi);
+    }
+#endif
+    return pos;
+}
+
+__device__ __forceinline__ void dedup_insert_one(int64_t i, const uint8_t* __restrict__ msg_id, const DedupScratch& D) {
+    const uint8_t* k = msg_id + i * 20;
+#ifdef DD_WARP_AGG
+    // Lanes of this warp that carry the same key send one of them to the table with the group's lowest and highest
+    // index.  Neighbouring messages share a key only when the key is hot, which is when the slot's atomics queue.
+    const uint32_t* kw = reinterpret_cast<const uint32_t*>(k);
+    const unsigned act = __activemask();
+    const unsigned peers = __match_any_sync(act, ((uint64_t)kw[1] << 32) | kw[0]);
+    const int leader = __ffs(peers) - 1;
+    bool same = true;                                        // the other twelve bytes, against the leader's
+#pragma unroll
+    for (int w = 2; w < 5; ++w) same &= __shfl_sync(peers, kw[w], leader) == kw[w];
+    const unsigned grp = __ballot_sync(peers, same) & peers;
+    uint64_t pos = 0;
+    if (same) {
+        const unsigned lo = __reduce_min_sync(grp, (unsigned)i);
+        const unsigned hi = __reduce_max_sync(grp, (unsigned)i);
+        if ((int)(threadIdx.x & 31) == leader) pos = dedup_fold(k, lo, (int)hi, msg_id, D);
+        pos = __shfl_sync(grp, pos, leader);
+    } else {
+        pos = dedup_fold(k, (unsigned)i, (int)i, msg_id, D);  // same first eight bytes, another key: on its own
     }
     D.slot_of[i] = (int32_t)pos;
+#else
+    D.slot_of[i] = (int32_t)dedup_fold(k, (unsigned)i, (int)i, msg_id, D);
+#endif
 }
 
 #ifndef K2_MIN_BLOCKS
