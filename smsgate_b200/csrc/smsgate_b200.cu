@@ -542,35 +542,52 @@ __device__ __forceinline__ bool id20_equal(const uint8_t* a, const uint8_t* b) {
 }
 
 // claim / find the slot of the key at `k` for message index `lo` and fold [lo, hi] into the slot's first / last
-// occurrence; returns the slot
+// occurrence; returns the slot.  One 64-bit CAS claims an empty slot with {first, last} = {lo, hi} already in place,
+// so a key seen once costs one atomic; when the slot is taken the same CAS hands back {first, last} as they were.
+// `first` only ever decreases and `last` only ever increases, so those values are enough to tell that an atomicMin /
+// atomicMax would change nothing - hot keys (50 % Zipf(1.2) duplicates put 90 000 of a million messages on one slot)
+// would otherwise queue three atomics each on the same eight bytes (profiles/r2p_dedup_variants.json).
 __device__ __forceinline__ uint64_t dedup_fold(const uint8_t* __restrict__ k, unsigned lo, int hi,
                                                const uint8_t* __restrict__ msg_id, const DedupScratch& D) {
     const uint32_t* kw = reinterpret_cast<const uint32_t*>(k);
     uint64_t pos = (((uint64_t)kw[1] << 32) | kw[0]) & D.mask;
+#ifdef DD_CAS32
     unsigned first_then;
     for (;;) {
         first_then = atomicCAS(reinterpret_cast<unsigned*>(&D.tab[pos].x), DD_EMPTY, lo);
         if (first_then == DD_EMPTY) break;
-        // `first_then` is some message with this slot's key (a concurrent atomicMin only swaps it for another one)
         if (first_then == lo || id20_equal(msg_id + (int64_t)first_then * 20, k)) break;
         pos = (pos + 1) & D.mask;
     }
-#ifdef DD_THREE_ATOMICS
-    if (first_then != DD_EMPTY) atomicMin(reinterpret_cast<unsigned*>(&D.tab[pos].x), lo);
-    atomicMax(&D.tab[pos].y, hi);
-#else
     if (first_then == DD_EMPTY) {
         atomicMax(&D.tab[pos].y, hi);
     } else {
-        // A later occurrence of a key.  `first` only ever decreases and `last` only ever increases, so a value read
-        // a moment ago is enough to tell that an atomic would change nothing: the CAS returned `first` as it was,
-        // an L2 load gives `last`.  Hot keys (50 % Zipf(1.2) duplicates put 90 000 of a million messages on one slot)
-        // would otherwise queue three atomics each on the same eight bytes.
         if (lo < first_then) atomicMin(reinterpret_cast<unsigned*>(&D.tab[pos].x), lo);
         if (hi > __ldcg(&D.tab[pos].y)) atomicMax(&D.tab[pos].y, hi);
     }
-#endif
     return pos;
+#else
+    const unsigned long long empty = ~0ull;                  // {DD_EMPTY, -1}: the table is cleared with 0xFF bytes
+    const unsigned long long mine = ((unsigned long long)(unsigned)hi << 32) | lo;      // .x = first is the low word
+    for (;;) {
+        unsigned long long* slot = reinterpret_cast<unsigned long long*>(&D.tab[pos]);
+#ifdef DD_PREREAD
+        unsigned long long cur = __ldcg(slot);
+        if (cur == empty) cur = atomicCAS(slot, empty, mine);
+#else
+        const unsigned long long cur = atomicCAS(slot, empty, mine);
+#endif
+        if (cur == empty) return pos;
+        // `first_then` is some message with this slot's key (a concurrent atomicMin only swaps it for another one)
+        const unsigned first_then = (unsigned)cur;
+        if (first_then == lo || id20_equal(msg_id + (int64_t)first_then * 20, k)) {
+            if (lo < first_then) atomicMin(reinterpret_cast<unsigned*>(&D.tab[pos].x), lo);
+            if (hi > (int)(cur >> 32)) atomicMax(&D.tab[pos].y, hi);
+            return pos;
+        }
+        pos = (pos + 1) & D.mask;
+    }
+#endif
 }
 
 __device__ __forceinline__ void dedup_insert_one(int64_t i, const uint8_t* __restrict__ msg_id, const DedupScratch& D) {
