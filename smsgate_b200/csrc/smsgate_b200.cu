@@ -541,81 +541,50 @@ __device__ __forceinline__ bool id20_equal(const uint8_t* a, const uint8_t* b) {
     return x[0] == y[0] && x[1] == y[1] && x[2] == y[2] && x[3] == y[3] && x[4] == y[4];
 }
 
-// claim / find the slot of the key at `k` for message index `lo` and fold [lo, hi] into the slot's first / last
-// occurrence; returns the slot.  One 64-bit CAS claims an empty slot with {first, last} = {lo, hi} already in place,
-// so a key seen once costs one atomic; when the slot is taken the same CAS hands back {first, last} as they were.
-// `first` only ever decreases and `last` only ever increases, so those values are enough to tell that an atomicMin /
-// atomicMax would change nothing - hot keys (50 % Zipf(1.2) duplicates put 90 000 of a million messages on one slot)
-// would otherwise queue three atomics each on the same eight bytes (profiles/r2p_dedup_variants.json).
-__device__ __forceinline__ uint64_t dedup_fold(const uint8_t* __restrict__ k, unsigned lo, int hi,
-                                               const uint8_t* __restrict__ msg_id, const DedupScratch& D) {
-    const uint32_t* kw = reinterpret_cast<const uint32_t*>(k);
-    uint64_t pos = (((uint64_t)kw[1] << 32) | kw[0]) & D.mask;
-#ifdef DD_CAS32
-    unsigned first_then;
-    for (;;) {
-        first_then = atomicCAS(reinterpret_cast<unsigned*>(&D.tab[pos].x), DD_EMPTY, lo);
-        if (first_then == DD_EMPTY) break;
-        if (first_then == lo || id20_equal(msg_id + (int64_t)first_then * 20, k)) break;
-        pos = (pos + 1) & D.mask;
-    }
-    if (first_then == DD_EMPTY) {
-        atomicMax(&D.tab[pos].y, hi);
-    } else {
-        if (lo < first_then) atomicMin(reinterpret_cast<unsigned*>(&D.tab[pos].x), lo);
-        if (hi > __ldcg(&D.tab[pos].y)) atomicMax(&D.tab[pos].y, hi);
-    }
-    return pos;
-#else
+// Claim / find the slot of message i's key and fold i into the slot's first / last occurrence.
+//  * The slot is read first; only a slot that looks free is claimed, with ONE 64-bit CAS that puts {first, last} =
+//    {i, i} in place: a key seen once costs a load and an atomic.
+//  * A taken slot's `first` is some message with the slot's key (a concurrent atomicMin only swaps it for another
+//    one), so equality is decided on the full 20 bytes of THAT message's key.
+//  * `first` only ever decreases and `last` only ever increases, so the values just read are enough to tell that an
+//    atomicMin / atomicMax would change nothing.  Hot keys (50 % Zipf(1.2) duplicates put 90 000 of a million
+//    messages on one slot) would otherwise queue a CAS and two more atomics each on the same eight bytes.
+//  * The key to compare with - this message's own when the slot looks free - is fetched BEFORE the CAS is issued:
+//    in a warp some lanes claim and others compare, the two paths run one after the other, and this way both wait
+//    for memory at the same time (DD_SERIAL_VERIFY keeps the fetch inside the comparing path).
+// Measured forms: profiles/r2p_dedup_variants.json, r2q_dedup_variants.json, r2r_dedup_variants.json.
+__device__ __forceinline__ void dedup_insert_one(int64_t i, const uint8_t* __restrict__ msg_id, const DedupScratch& D) {
+    const uint32_t* kw = reinterpret_cast<const uint32_t*>(msg_id + i * 20);
+    const uint32_t k0 = kw[0], k1 = kw[1], k2 = kw[2], k3 = kw[3], k4 = kw[4];
+    const unsigned me = (unsigned)i;
     const unsigned long long empty = ~0ull;                  // {DD_EMPTY, -1}: the table is cleared with 0xFF bytes
-    const unsigned long long mine = ((unsigned long long)(unsigned)hi << 32) | lo;      // .x = first is the low word
+    const unsigned long long mine = ((unsigned long long)me << 32) | me;                // .x = first is the low word
+    uint64_t pos = (((uint64_t)k1 << 32) | k0) & D.mask;
     for (;;) {
         unsigned long long* slot = reinterpret_cast<unsigned long long*>(&D.tab[pos]);
-#ifdef DD_PREREAD
         unsigned long long cur = __ldcg(slot);
-        if (cur == empty) cur = atomicCAS(slot, empty, mine);
+#ifdef DD_SERIAL_VERIFY
+        if (cur == empty && (cur = atomicCAS(slot, empty, mine)) == empty) break;
+        const uint32_t* ow = reinterpret_cast<const uint32_t*>(msg_id + (int64_t)(unsigned)cur * 20);
+        const uint32_t o0 = ow[0], o1 = ow[1], o2 = ow[2], o3 = ow[3], o4 = ow[4];
 #else
-        const unsigned long long cur = atomicCAS(slot, empty, mine);
+        const uint32_t* ow = reinterpret_cast<const uint32_t*>(msg_id + (int64_t)(cur == empty ? me : (unsigned)cur) * 20);
+        uint32_t o0 = ow[0], o1 = ow[1], o2 = ow[2], o3 = ow[3], o4 = ow[4];
+        if (cur == empty) {
+            cur = atomicCAS(slot, empty, mine);
+            if (cur == empty) break;
+            ow = reinterpret_cast<const uint32_t*>(msg_id + (int64_t)(unsigned)cur * 20);   // claimed in between
+            o0 = ow[0]; o1 = ow[1]; o2 = ow[2]; o3 = ow[3]; o4 = ow[4];
+        }
 #endif
-        if (cur == empty) return pos;
-        // `first_then` is some message with this slot's key (a concurrent atomicMin only swaps it for another one)
-        const unsigned first_then = (unsigned)cur;
-        if (first_then == lo || id20_equal(msg_id + (int64_t)first_then * 20, k)) {
-            if (lo < first_then) atomicMin(reinterpret_cast<unsigned*>(&D.tab[pos].x), lo);
-            if (hi > (int)(cur >> 32)) atomicMax(&D.tab[pos].y, hi);
-            return pos;
+        if ((((o0 ^ k0) | (o1 ^ k1)) | ((o2 ^ k2) | (o3 ^ k3)) | (o4 ^ k4)) == 0) {
+            if (me < (unsigned)cur) atomicMin(reinterpret_cast<unsigned*>(&D.tab[pos].x), me);
+            if ((int)me > (int)(cur >> 32)) atomicMax(&D.tab[pos].y, (int)me);
+            break;
         }
         pos = (pos + 1) & D.mask;
     }
-#endif
-}
-
-__device__ __forceinline__ void dedup_insert_one(int64_t i, const uint8_t* __restrict__ msg_id, const DedupScratch& D) {
-    const uint8_t* k = msg_id + i * 20;
-#ifdef DD_WARP_AGG
-    // Lanes of this warp that carry the same key send one of them to the table with the group's lowest and highest
-    // index.  Neighbouring messages share a key only when the key is hot, which is when the slot's atomics queue.
-    const uint32_t* kw = reinterpret_cast<const uint32_t*>(k);
-    const unsigned act = __activemask();
-    const unsigned peers = __match_any_sync(act, ((uint64_t)kw[1] << 32) | kw[0]);
-    const int leader = __ffs(peers) - 1;
-    bool same = true;                                        // the other twelve bytes, against the leader's
-#pragma unroll
-    for (int w = 2; w < 5; ++w) same &= __shfl_sync(peers, kw[w], leader) == kw[w];
-    const unsigned grp = __ballot_sync(peers, same) & peers;
-    uint64_t pos = 0;
-    if (same) {
-        const unsigned lo = __reduce_min_sync(grp, (unsigned)i);
-        const unsigned hi = __reduce_max_sync(grp, (unsigned)i);
-        if ((int)(threadIdx.x & 31) == leader) pos = dedup_fold(k, lo, (int)hi, msg_id, D);
-        pos = __shfl_sync(grp, pos, leader);
-    } else {
-        pos = dedup_fold(k, (unsigned)i, (int)i, msg_id, D);  // same first eight bytes, another key: on its own
-    }
     D.slot_of[i] = (int32_t)pos;
-#else
-    D.slot_of[i] = (int32_t)dedup_fold(k, (unsigned)i, (int)i, msg_id, D);
-#endif
 }
 
 #ifndef K2_MIN_BLOCKS
