@@ -533,7 +533,6 @@ struct DedupScratch {
     int32_t* slot_of;  // [n]   slot of message i, -1 = not an upsert
     uint64_t mask;
 };
-constexpr unsigned DD_EMPTY = 0xFFFFFFFFu;
 
 __device__ __forceinline__ bool id20_equal(const uint8_t* a, const uint8_t* b) {
     const uint32_t* x = reinterpret_cast<const uint32_t*>(a);
@@ -551,23 +550,19 @@ __device__ __forceinline__ bool id20_equal(const uint8_t* a, const uint8_t* b) {
 //    messages on one slot) would otherwise queue a CAS and two more atomics each on the same eight bytes.
 //  * The key to compare with - this message's own when the slot looks free - is fetched BEFORE the CAS is issued:
 //    in a warp some lanes claim and others compare, the two paths run one after the other, and this way both wait
-//    for memory at the same time (DD_SERIAL_VERIFY keeps the fetch inside the comparing path).
-// Measured forms: profiles/r2p_dedup_variants.json, r2q_dedup_variants.json, r2r_dedup_variants.json.
+//    for memory at the same time (measured: no difference to fetching inside the comparing path).
+// Measured forms (three atomics, 32-bit CAS + skipped atomics, 64-bit CAS, read first, one lane per key and warp):
+// profiles/r2p_dedup_variants.json, r2q_dedup_variants.json, r2r_dedup_variants.json.
 __device__ __forceinline__ void dedup_insert_one(int64_t i, const uint8_t* __restrict__ msg_id, const DedupScratch& D) {
     const uint32_t* kw = reinterpret_cast<const uint32_t*>(msg_id + i * 20);
     const uint32_t k0 = kw[0], k1 = kw[1], k2 = kw[2], k3 = kw[3], k4 = kw[4];
     const unsigned me = (unsigned)i;
-    const unsigned long long empty = ~0ull;                  // {DD_EMPTY, -1}: the table is cleared with 0xFF bytes
+    const unsigned long long empty = ~0ull;                  // {0xFFFFFFFF, -1}: the table is cleared with 0xFF bytes
     const unsigned long long mine = ((unsigned long long)me << 32) | me;                // .x = first is the low word
     uint64_t pos = (((uint64_t)k1 << 32) | k0) & D.mask;
     for (;;) {
         unsigned long long* slot = reinterpret_cast<unsigned long long*>(&D.tab[pos]);
         unsigned long long cur = __ldcg(slot);
-#ifdef DD_SERIAL_VERIFY
-        if (cur == empty && (cur = atomicCAS(slot, empty, mine)) == empty) break;
-        const uint32_t* ow = reinterpret_cast<const uint32_t*>(msg_id + (int64_t)(unsigned)cur * 20);
-        const uint32_t o0 = ow[0], o1 = ow[1], o2 = ow[2], o3 = ow[3], o4 = ow[4];
-#else
         const uint32_t* ow = reinterpret_cast<const uint32_t*>(msg_id + (int64_t)(cur == empty ? me : (unsigned)cur) * 20);
         uint32_t o0 = ow[0], o1 = ow[1], o2 = ow[2], o3 = ow[3], o4 = ow[4];
         if (cur == empty) {
@@ -576,7 +571,6 @@ __device__ __forceinline__ void dedup_insert_one(int64_t i, const uint8_t* __res
             ow = reinterpret_cast<const uint32_t*>(msg_id + (int64_t)(unsigned)cur * 20);   // claimed in between
             o0 = ow[0]; o1 = ow[1]; o2 = ow[2]; o3 = ow[3]; o4 = ow[4];
         }
-#endif
         if ((((o0 ^ k0) | (o1 ^ k1)) | ((o2 ^ k2) | (o3 ^ k3)) | (o4 ^ k4)) == 0) {
             if (me < (unsigned)cur) atomicMin(reinterpret_cast<unsigned*>(&D.tab[pos].x), me);
             if ((int)me > (int)(cur >> 32)) atomicMax(&D.tab[pos].y, (int)me);
