@@ -45,6 +45,10 @@ __device__ __forceinline__ void tma_load_1d(void* dst, const void* src, uint32_t
                  "l"(src), "r"(bytes), "r"(smem_u32(bar))
                  : "memory");
 }
+// ask L2 for [src, src + bytes) ahead of the bulk copy that will read it; src 16-byte aligned, bytes a multiple of 16
+__device__ __forceinline__ void l2_prefetch_bulk(const void* src, uint32_t bytes) {
+    asm volatile("cp.async.bulk.prefetch.L2.global [%0], %1;" ::"l"(src), "r"(bytes) : "memory");
+}
 __device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
     asm volatile(
         "{\n"
@@ -198,7 +202,8 @@ k_scan_keys(const uint8_t* __restrict__ bytes, const int64_t* __restrict__ offse
     // ... of at most K1_TILE messages AND about 90 % of the staging buffer in bytes (long bodies: mixed-locale and
     // multi-part messages), so that a tile is staged in one piece instead of a full sub-batch plus a sliver
     const int64_t nt_cnt = (r1 - r0 + K1_TILE - 1) / K1_TILE;
-    const int64_t share_bytes = r1 > r0 ? offsets[r1] - offsets[r0] : 0;
+    const int64_t offsets_end = r1 > r0 ? offsets[r1] : 0;
+    const int64_t share_bytes = r1 > r0 ? offsets_end - offsets[r0] : 0;
     const int64_t nt_bytes = (share_bytes + (K1_STAGE / 10) * 9 - 1) / ((K1_STAGE / 10) * 9);
     const int64_t nt = nt_cnt > nt_bytes ? nt_cnt : nt_bytes;
     // (full tiles of K1_TILE plus one short tile, i.e. exactly two chunks per warp and phase, measured slower:
@@ -361,6 +366,23 @@ k_scan_keys(const uint8_t* __restrict__ bytes, const int64_t* __restrict__ offse
             __syncthreads();
             K1_T(2);                                         // partition
             // ---- phase H: warps pull chunks until none is left
+#ifdef K1_L2_PREFETCH
+            // the hash phase is seven tenths of a tile and touches no global memory but its results: have L2 fetch
+            // the next tile's bytes and offsets meanwhile, so that its bulk copy and its first loads find them there
+            if (tid == 0 && e < r1) {
+                const int64_t from = hi & ~(int64_t)15;
+                int64_t want = hi - base;                                  // as many bytes again as this tile had
+                const int64_t left = (offsets_end & ~(int64_t)15) - from;
+                if (want > left) want = left;
+                want &= ~(int64_t)15;
+                if (want > 0) l2_prefetch_bulk(bytes + from, (uint32_t)want);
+                const uintptr_t o_lo = ((uintptr_t)(offsets + e) + 15) & ~(uintptr_t)15;
+                uintptr_t o_hi = (uintptr_t)(offsets + e + cnt + 2);
+                if (o_hi > (uintptr_t)(offsets + n + 1)) o_hi = (uintptr_t)(offsets + n + 1);
+                o_hi &= ~(uintptr_t)15;
+                if (o_hi > o_lo) l2_prefetch_bulk((const void*)o_lo, (uint32_t)(o_hi - o_lo));
+            }
+#endif
             const int nchM = (nM + 31) >> 5, nchU = (cnt - nM + 31) >> 5;
             const int nR = S.nr, nchR = (nR + 31) >> 5;
 #pragma unroll 1
