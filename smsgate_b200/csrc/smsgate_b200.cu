@@ -366,9 +366,10 @@ k_scan_keys(const uint8_t* __restrict__ bytes, const int64_t* __restrict__ offse
             __syncthreads();
             K1_T(2);                                         // partition
             // ---- phase H: warps pull chunks until none is left
-#ifdef K1_L2_PREFETCH
+#ifndef K1_NO_L2_PREFETCH
             // the hash phase is seven tenths of a tile and touches no global memory but its results: have L2 fetch
             // the next tile's bytes and offsets meanwhile, so that its bulk copy and its first loads find them there
+            // (0.476 vs 0.485 ms per 1 M messages, profiles/r2u_prefetch_variants.json)
             if (tid == 0 && e < r1) {
                 const int64_t from = hi & ~(int64_t)15;
                 int64_t want = hi - base;                                  // as many bytes again as this tile had
