@@ -82,3 +82,75 @@ def test_survivor_payloads_use_the_native_emitter():
     got = res.parsed_payloads()
     want = [res.parsed(int(i)).model_dump_json().encode() for i in res.survivor_indices()]
     assert got == want and len(got) > 500
+
+
+_FUZZ_ALPHABET = ['a', 'Z', '0', ' ', '"', '\\', '/', '\n', '\t', '\r', '\x00', '\x01', '\x1f', '\x7f', '\x80', '\xa0',
+                  'é', 'Я', '中', '☕', '😀', ' ', ' ', '﻿', '퟿', '', '￿', '<', '>', '&',
+                  "'", '\x08', '\x0c', '\x0b']
+
+
+def test_emitter_fuzz_against_pydantic():
+    """Random cache entries - text from an alphabet of everything JSON escapes or pydantic treats specially,
+    amounts in every shape parse_ambiguous_decimal accepts, upper-casable and non-ASCII currencies - rendered by
+    the native emitter and by pydantic.  The emitter may decline a row (non-ASCII currency: str.upper() is
+    Python's; a coefficient beyond int64), it may never differ."""
+    import random
+    rng = random.Random(0xE417)
+
+    def text(maxlen=12):
+        return ''.join(rng.choice(_FUZZ_ALPHABET) for _ in range(rng.randint(0, maxlen)))
+
+    def amount():
+        k = rng.random()
+        if k < 0.3:
+            return f"{rng.randint(0, 10 ** rng.randint(1, 12))}.{rng.randint(0, 99):02d}"
+        if k < 0.4:
+            return f"{rng.randint(0, 999)},{rng.randint(0, 999):03d}.{rng.randint(0, 9)}"
+        if k < 0.5:
+            return f"{rng.randint(0, 999)}.{rng.randint(0, 999):03d},{rng.randint(0, 99):02d}"
+        if k < 0.6:
+            return rng.choice(["0", "0.0", "-0", "0.00", ".5", "5.", "+5", "00012.50", "1e5", "", "   ", "000",
+                               "0.0000000", "1.0000000000", "999999999999999999", "9999999999999999999",
+                               "0.000000000000000001", "-0.00", "1 234,5", "1\xa0234,56"])
+        if k < 0.75:
+            return "0." + "0" * rng.randint(0, 10) + str(rng.randint(1, 999))
+        if k < 0.85:
+            return str(rng.randint(0, 10 ** 17)) + "0" * rng.randint(0, 3)
+        return f"{rng.randint(0, 99999)}.{rng.randint(0, 9999999):07d}"
+
+    backup = synth.generate(2500, seed=93)
+    cache = dict(backup.cache)
+    for key in list(cache):
+        if rng.random() < 0.8:
+            cache[key] = dict(cache[key], merchant=text() or "m", city=rng.choice([None, text(), ""]),
+                              address=rng.choice([None, text(20), "null", ""]), amount=amount(),
+                              balance=rng.choice([amount(), "-" + amount(), None]),
+                              currency=rng.choice(["amd", "USD", "eUr", "", None, "ru", "Ab1", "ß", "ı", "a b"]),
+                              txn_type=rng.choice(["debit", "credit", "otp", "unknown"]))
+    senders = [text(8) for _ in backup.senders]
+    res, table = _result(list(backup.bodies), senders, cache)
+    idx = np.nonzero(np.isin(res.cols["status"], (L.ST_UPSERT, L.ST_PARSED_NO_MERCHANT)))[0]
+    assert len(idx) > 1200
+    rendered = declined_for_a_reason = 0
+    for mode in (0, 1):
+        off, data, fb = res.emit_json(idx, mode)
+        raw = data.tobytes()
+        for k, i in enumerate(idx):
+            if fb[k]:
+                cur = res.table.values[int(res.cols["slot"][i])].get("currency")
+                over = (int(res.cols["dec_flags"][i]) & 3) == L.DEC_OVERFLOW or ((int(res.cols["dec_flags"][i]) >> 2) & 3) == L.DEC_OVERFLOW
+                assert over or (cur is not None and not cur.isascii()), (int(i), cur)
+                declined_for_a_reason += 1
+                continue
+            p = res.parsed(int(i))
+            got = raw[off[k]:off[k + 1]]
+            if mode == 0:
+                assert got == p.model_dump_json().encode("utf-8"), (int(i), got)
+            else:
+                want = {"msg_id": p.msg_id, "original_body": p.raw_body, "sender": p.sender,
+                        "datetime": p.date.isoformat(), "card": p.card, "amount": str(p.amount),
+                        "currency": p.currency, "balance": str(p.balance) if p.balance is not None else None,
+                        "merchant": p.merchant, "address": p.address, "city": p.city, "txn_type": p.txn_type.value}
+                assert json.loads(got) == want, (int(i), got)
+            rendered += 1
+    assert rendered > 1500 and declined_for_a_reason > 50
