@@ -105,6 +105,18 @@ def test_native_reader_matches_python_reader(tmp_path):
     c, backup = _fill(str(tmp_path))
     names = _extra_entries(c)
     c.close()
+    by_name, host, keys, m = _native_vs_python(tmp_path, names)
+    assert {n for n, e in by_name.items() if n and host[e] == 1} == {"big_int", "float_amount", "nested_list", "nested_dict", "not_a_dict"}
+    assert {n for n, e in by_name.items() if n and host[e] == 2} == {"date_unicode", "date_long", "date_int"}
+    assert host[[e for e in range(m) if keys[e].tobytes().hex() == "f" * 64][0]] == 1      # value in a side file
+    assert (host == 0).sum() > 2500
+
+
+def _native_vs_python(tmp_path, names):
+    """Every array the native reader fills against the per-entry Python path on the same directory."""
+    import ctypes as C
+
+    from smsgate_b200 import _lib as L
 
     def no_gpu(strings):
         return np.full(len(strings), -1, np.int64)
@@ -159,7 +171,57 @@ def test_native_reader_matches_python_reader(tmp_path):
                 assert kind == 2 and text == v[field], (name, field)
             else:
                 assert kind not in (0, 1, 2)
-    assert {n for n, e in by_name.items() if n and host[e] == 1} == {"big_int", "float_amount", "nested_list", "nested_dict", "not_a_dict"}
-    assert {n for n, e in by_name.items() if n and host[e] == 2} == {"date_unicode", "date_long", "date_int"}
-    assert host[[e for e in range(m.value) if keys[e].tobytes().hex() == "f" * 64][0]] == 1      # value in a side file
-    assert (host == 0).sum() > 2500
+    return by_name, host, keys, m.value
+
+
+def test_native_reader_fuzz_over_pickle_protocols(tmp_path):
+    """Random response dicts - every value type the decoder's subset has an opinion on, shared and repeated
+    strings, long strings, extra keys - stored by diskcache with pickle protocols 2 to 5 (a cache directory may
+    have been written by an older interpreter).  What the native reader decodes itself must equal the Python
+    path; declining an entry is always allowed."""
+    import hashlib
+    import random
+    rng = random.Random(0xCAC4E)
+    words = ["", "a", "52.00", "1,842.74", "TEST LLC", "Ереван", "☕", "x" * 255, "y" * 256, "z" * 70000, "null",
+             "06.05.25 14:23", "06.05.2025 14:23", "2025-05-06T14:23:00+04:00", "***0018", "4083***7538", "usd"]
+
+    def value():
+        k = rng.random()
+        if k < 0.55:
+            return rng.choice(words)
+        if k < 0.65:
+            return None
+        if k < 0.75:
+            return rng.choice([0, 1, -1, 255, 256, 65535, 65536, 2 ** 31 - 1, 2 ** 31, -2 ** 31, 2 ** 63 - 1, 2 ** 63, -2 ** 63, 10 ** 30])
+        if k < 0.8:
+            return rng.choice([True, False])
+        if k < 0.85:
+            return rng.choice([0.0, 12.5, -1e300, float("inf")])
+        if k < 0.9:
+            return rng.choice([b"bytes", ("t", 1), ["l"], {"d": 1}, {1, 2}, frozenset(), bytearray(b"x")])
+        return "".join(rng.choice("aЖ☕ \"\\\n0,.-") for _ in range(rng.randint(0, 30)))
+    fields = ["txn_type", "date", "amount", "currency", "card", "merchant", "city", "address", "balance"]
+    total_native = 0
+    for proto in (2, 3, 4, 5):
+        d = tmp_path / f"p{proto}"
+        c = diskcache.Cache(str(d), disk_pickle_protocol=proto)
+        names = {}
+        for j in range(400):
+            keep = [f for f in fields if rng.random() < 0.9]
+            rng.shuffle(keep)
+            shared = value()
+            v = {f: (shared if rng.random() < 0.2 else value()) for f in keep}
+            if rng.random() < 0.5:
+                v["txn_type"] = rng.choice(["debit", "credit", "otp", "unknown", "bogus"])
+            if rng.random() < 0.2:
+                v[rng.choice(["note", "x" * 300, "Ж"])] = value()
+            if rng.random() < 0.03:
+                v = rng.choice([[], "str", 5, None, (1, 2), {}])
+            name = f"p{proto}_{j}"
+            k = hashlib.sha256(name.encode()).hexdigest()
+            c[k] = v
+            names[k] = name
+        c.close()
+        by_name, host, keys, m = _native_vs_python(d, names)
+        total_native += int((host != 1).sum())
+    assert total_native > 600
