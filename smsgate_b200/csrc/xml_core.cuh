@@ -250,12 +250,11 @@ SG_HD XmlTag xml_parse_tag(const uint8_t* x, int64_t nx, int64_t pos, int64_t ne
             if (k >= close) return t;
             const int64_t v1 = k++;
             if (stage == 0 && xml_span_is(x, a0, a1, "version", 7)) {
-                // expat accepts any non-empty run of [A-Za-z0-9_.:-] as the version number
-                if (v1 == v0) return t;
+                // expat accepts any run of [A-Za-z0-9_.-] as the version number, the empty one included
                 for (int64_t c = v0; c < v1; ++c) {
                     const uint8_t ch = x[c];
                     if (!((ch >= 'a' && ch <= 'z') || (ch >= 'A' && ch <= 'Z') || (ch >= '0' && ch <= '9') || ch == '_' ||
-                          ch == '.' || ch == ':' || ch == '-')) return t;
+                          ch == '.' || ch == '-')) return t;
                 }
                 stage = 1;
             } else if (stage == 1 && xml_span_is(x, a0, a1, "encoding", 8)) {

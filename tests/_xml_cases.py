@@ -91,6 +91,11 @@ def documents():
         b"<?xml version='1.0' encoding='ISO-8859-1'?><smses><sms address='A' date='1' body='x'/></smses>",
         b"<?xml version='1.0' encoding='utf-8'?><smses><sms address='A' date='1' body='x'/></smses>",
         b" <?xml version='1.0'?><smses><sms address='A' date='1' body='x'/></smses>",
+        b"<?xml version=''?><smses><sms address='A' date='1' body='x'/></smses>",
+        b"<?xml version='1:0'?><smses><sms address='A' date='1' body='x'/></smses>",
+        b"<?xml version='Z9_.-'?><smses><sms address='A' date='1' body='x'/></smses>",
+        b"<?xml version='1.0' standalone=''?><smses><sms address='A' date='1' body='x'/></smses>",
+        b"<?xml version='1.0'encoding='utf-8'?><smses><sms address='A' date='1' body='x'/></smses>",
         b"<smses><?xml version='1.0'?><sms address='A' date='1' body='x'/></smses>",
         b"<smses><?pi data?><sms address='A' date='1' body='x'/></smses>",
         b'<a:smses xmlns:a="u"><sms address="A" date="1" body="x"/></a:smses>',
