@@ -370,6 +370,19 @@ XML_CASES = {
     "other_root_child": '<smses><call number="1"/><sms address="A" date="7" body="z"/></smses>',
     "dup_attr": '<smses><sms address="A" address="B" date="7" body="z"/></smses>',
     "cdata_text": '<smses><sms address="A" date="7" body="z">text<![CDATA[x]]></sms></smses>',
+    # _iter_sms is a generator: what it yields before it raises is part of its behaviour
+    "bad_date_after_two": '<smses><sms address="A" date="1000" body="one"/><sms address="B" date="2000" body="two"/>'
+                          '<sms address="C" date="12x" body="three"/><sms address="D" date="4000" body="four"/></smses>',
+    "empty_body_after_one": '<smses><sms address="A" date="1000" body="one"/><sms address="B" date="2000" body=""/>'
+                            '<sms address="C" date="3000" body="three"/></smses>',
+    "year_10000_after_one": '<smses><sms address="A" date="253402300799999" body="last ms of 9999"/>'
+                            '<sms address="B" date="253402300800000" body="year 10000"/></smses>',
+    "beyond_int64_after_one": '<smses><sms address="A" date="-62135596800000" body="first ms of year 1"/>'
+                              '<sms address="B" date="9223372036854775808" body="2^63"/></smses>',
+    "beyond_time_t_after_one": '<smses><sms address="A" date="1000" body="one"/>'
+                               '<sms address="B" date="100000000000000000000000" body="1e23"/></smses>',
+    "odd_int_forms": '<smses><sms address="A" date=" +1_000 " body="one"/><sms address="B" date="-0" body="two"/>'
+                     '<sms address="C" date="\u0661\u0662" body="arabic-indic twelve"/></smses>',
 }
 
 
@@ -380,12 +393,14 @@ def gen_iter_sms(ref):
         p = os.path.join(tmp, name + ".xml")
         with open(p, "w", encoding="utf-8", newline="") as f:
             f.write(text)
+        from pathlib import Path
+        rows = []                                  # with "error": what the generator yielded before it raised
         try:
-            from pathlib import Path
-            rows = [r.model_dump() for r in ref.watcher._iter_sms(Path(p))]
+            for r in ref.watcher._iter_sms(Path(p)):
+                rows.append(r.model_dump())
             out.append({"name": name, "xml": text, "rows": rows})
         except Exception as e:
-            out.append({"name": name, "xml": text, "error": type(e).__name__})
+            out.append({"name": name, "xml": text, "rows": rows, "error": type(e).__name__})
     return out
 
 

@@ -1,11 +1,13 @@
 """XML backup ingestion: the host side of `_iter_sms` (services/xml_watcher/watcher.py:35-54)
 and of `parse_and_cache_sms` (read_xml.py:9-54).
 
-The XML text itself is parsed on the host with the same parser the reference
-uses (ElementTree / expat), so entity and character-reference decoding and
-attribute whitespace normalisation are identical by construction; what moves to
-the GPU is the per-message work (SHA-1 `msg_id`, and everything downstream).
-A GPU tokenizer for the `<sms …/>` elements is the first "next" row of SURVEY §8(f).
+The file's bytes go to the GPU tokenizer (smsgate_xml_scan / _emit), which hands back
+body / address / date of every top-level <sms> already decoded - entity and character references, attribute
+white-space normalisation - and checked against ElementTree on every document the tests and the fuzz runs
+throw at it.  Two kinds of file still go through ElementTree, and both are counted in `engine.host_fallbacks`:
+a file in an XML dialect the tokenizer leaves to a general parser (DOCTYPE, CDATA, namespaces, other
+encodings), and a file with a `date` attribute the reference raises on, so that the exception and the
+messages yielded before it are exactly the reference's.
 """
 from __future__ import annotations
 
@@ -72,13 +74,45 @@ def iter_sms(xml_path: Union[str, Path], engine) -> Iterable[RawSMS]:
     SHA-1(body) computed on the GPU for the whole file at once.  A message that
     fails RawSMS validation (empty body or sender) raises at that message, after
     the earlier ones were yielded, like the reference's generator."""
-    batch = read_backup_gpu(xml_path, engine)
+    try:
+        batch = read_backup_gpu(xml_path, engine)
+    except (ValueError, OverflowError):
+        # a `date` attribute int() refuses, or one beyond int64: the reference's generator has yielded the messages
+        # in front of it by the time it raises (watcher.py:42-43 run per element)
+        engine.host_fallbacks += 1
+        yield from _iter_sms_until_bad_date(xml_path, engine)
+        return
     if batch.n == 0:
         return
     ids = engine.msg_ids(batch)
     for i in range(batch.n):
         yield RawSMS(source="xml", device_id="xml_backup", msg_id=ids[i].tobytes().hex(), sender=batch.senders[i],
                      date=iso_utc(int(batch.date_ms[i])), body=batch.body(i))
+
+
+def _iter_sms_until_bad_date(xml_path: Union[str, Path], engine) -> Iterable[RawSMS]:
+    """`_iter_sms` for a file whose dates make it raise: ElementTree element by element as the reference does
+    (watcher.py:40-44), the messages in front of the failing one yielded first (msg_ids still from the GPU), then
+    the reference's own exception from `int()` / `datetime.fromtimestamp()`."""
+    root = ET.parse(xml_path).getroot()
+    bodies, senders, dates, failure = [], [], [], None
+    for elem in root.findall("sms"):
+        try:
+            ts_ms = int(elem.get("date", "0"))                                    # :42
+            date = _dt.datetime.fromtimestamp(ts_ms / 1_000, tz=_dt.timezone.utc).isoformat()   # :43, :52
+        except Exception as e:                                # noqa: BLE001 - re-raised below, after the yields
+            failure = e
+            break
+        bodies.append(elem.get("body", ""))
+        senders.append(elem.get("address", ""))
+        dates.append(date)
+    if bodies:
+        ids = engine.msg_ids(Batch.from_strings(bodies, senders, [0] * len(bodies)))
+        for i, body in enumerate(bodies):
+            yield RawSMS(source="xml", device_id="xml_backup", msg_id=ids[i].tobytes().hex(), sender=senders[i],
+                         date=dates[i], body=body)
+    if failure is not None:
+        raise failure
 
 
 def parse_and_cache_sms(xml_file: str, cache_dir: str, engine=None) -> Optional[int]:

@@ -118,3 +118,38 @@ def xml_extract(data: bytes):
     bodies = [bb[bo[i]:bo[i + 1]].tobytes().decode() for i in range(k)]
     senders = [sb[so[i]:so[i + 1]].tobytes().decode() for i in range(k)]
     return rc, bodies, senders, dm[:k].tolist(), mf[:k].tolist()
+
+
+class HostTokenizerEngine:
+    """TEST stand-in for ReplayEngine where only the XML host logic is under test: `xml_extract` runs the
+    tokenizer compiled for the CPU (same xml_core.cuh), `msg_ids` is hashlib."""
+
+    def __init__(self):
+        self.host_fallbacks = 0
+
+    def xml_extract(self, data):
+        import xml.etree.ElementTree as ET
+
+        import torch
+
+        from smsgate_b200.batch import ragged_from_strings
+        from smsgate_b200.replay import UnsupportedXML
+        code, bodies, senders, dates, mflags = xml_extract(bytes(data))
+        if code == 2:
+            raise UnsupportedXML("outside the tokenizer's dialect")
+        if code == 1:
+            raise ET.ParseError("not well-formed")
+        bb, bo = ragged_from_strings(bodies)
+        sb, so = ragged_from_strings(senders)
+
+        def t(a, dtype):
+            a = np.array(a, dtype=dtype)
+            return torch.from_numpy(a if a.size else np.zeros(1, dtype))
+        return {"n": len(bodies), "body_offsets": t(bo, np.int64), "sender_offsets": t(so, np.int64),
+                "body_bytes": t(bb, np.uint8), "sender_bytes": t(sb, np.uint8), "mflags": t(mflags, np.uint8),
+                "date_ms": t([d if -2 ** 63 <= d < 2 ** 63 else 0 for d in dates], np.int64)}
+
+    def msg_ids(self, batch):
+        import hashlib
+        return np.array([np.frombuffer(hashlib.sha1(batch.body(i).encode("utf-8")).digest(), np.uint8)
+                         for i in range(batch.n)]).reshape(batch.n, 20)

@@ -33,3 +33,22 @@ def test_tokenizer_matches_elementtree():
     for data in docs:
         n_unsup += compare(H.xml_extract(data), data) == "unsupported"
     assert n_unsup < len(docs) * 0.2
+
+
+def test_iter_sms_host_logic_against_reference_run(golden, tmp_path):
+    """xml_ingest.iter_sms above the tokenizer (CPU build) against tests/golden/iter_sms.json, a run of the
+    reference's `_iter_sms`: the rows it yields, the exception it ends with, and the rows yielded BEFORE that
+    exception - a date `int()` refuses in the middle of a file comes after the messages in front of it."""
+    from smsgate_b200 import xml_ingest
+    engine = H.HostTokenizerEngine()
+    for c in golden("iter_sms.json"):
+        p = tmp_path / (c["name"] + ".xml")
+        p.write_text(c["xml"], encoding="utf-8", newline="")
+        rows, error = [], None
+        try:
+            for r in xml_ingest.iter_sms(p, engine):
+                rows.append(r.model_dump())
+        except Exception as e:                     # noqa: BLE001
+            error = type(e).__name__
+        assert rows == c["rows"] and error == c.get("error"), c["name"]
+    assert engine.host_fallbacks >= 4              # the files whose dates raise, and the CDATA one
