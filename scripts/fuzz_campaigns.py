@@ -9,7 +9,8 @@ Two families:
     `xml_struct` (documents generated from a grammar of odd names, attributes, references);
   * the oracle against the REFERENCE ITSELF, imported from /root/reference (build container only): `ref_units`
     (worker filter lifted from worker.py, parser filter, clean + mask, fix_broken_datetime,
-    parse_ambiguous_decimal), `ref_route` (parse_sms_llm + the worker / writer gates on random cache entries).
+    parse_ambiguous_decimal), `ref_route` (parse_sms_llm + the worker / writer gates on random cache entries),
+    `ref_iter_sms` (the `_iter_sms` generator on mutated backups: rows, exception, rows before the exception).
 Every mismatch prints a line containing MISMATCH; a clean run prints only the per-seed progress lines.
 Round 2's runs and the one finding they produced are listed in DESIGN.md section 2."""
 import datetime as dt
@@ -370,7 +371,67 @@ def ref_route(first, last):
         progress(seed, t0, messages=n, bad=bad)
 
 
-CAMPAIGNS = {"scan": scan, "route": route, "legacy": legacy, "xml": xml, "xml_struct": xml_struct,
+XML_DATES = [b"99999999999999999999999", b"253402300800000", b"253402300799999", b"-62135596800001", b"-62135596800000",
+             b"9223372036854775808", b"9223372036854775807", b"-9223372036854775808", b"-9223372036854775809", b" 5 ",
+             b"1_0", b"+7", b"\xd9\xa1\xd9\xa2", b"", b"1e3", b"0x10", b"12345678901234567890", b"9300000000000000000000",
+             b"-9300000000000000000000", b"00000000000000000000000000000000000007", b"\xef\xbc\x91"]
+
+
+def ref_iter_sms(first, last):
+    """xml_ingest.iter_sms above the CPU build of the tokenizer against the reference's _iter_sms generator: rows
+    yielded, exception type, and the rows yielded before the exception."""
+    import re
+    from pathlib import Path
+
+    import torch  # noqa: F401 - before the reference's import stubs go in
+
+    from smsgate_b200 import xml_ingest
+    from tests import _hostcheck as H
+    ref = _reference()
+    eng = H.HostTokenizerEngine()
+    path = os.path.join(tempfile.mkdtemp(prefix="smsgate_fuzz_xml_"), "a.xml")
+
+    def outcome(gen):
+        rows = []
+        try:
+            for r in gen():
+                rows.append(r.model_dump())
+            return rows, None
+        except Exception as e:                            # noqa: BLE001
+            return rows, type(e).__name__
+    t0, bad, n = time.time(), 0, 0
+    for seed in range(first, last):
+        rnd = random.Random(123000 + seed)
+        for _ in range(1500):
+            doc = bytearray(rnd.choice(XML_SEEDS))
+            for _ in range(rnd.randint(0, 3)):
+                k = rnd.randrange(len(doc))
+                op = rnd.random()
+                if op < 0.3:
+                    del doc[k]
+                elif op < 0.6:
+                    doc[k] = rnd.choice(XML_BYTES)
+                else:
+                    doc.insert(k, rnd.choice(XML_BYTES))
+            doc = bytes(doc)
+            dates = list(re.finditer(rb'date="[^"]*"', doc))
+            if dates and rnd.random() < 0.5:
+                m = rnd.choice(dates)
+                doc = doc[:m.start()] + b'date="' + rnd.choice(XML_DATES) + b'"' + doc[m.end():]
+            with open(path, "wb") as f:
+                f.write(doc)
+            with ref.quiet():
+                want = outcome(lambda: ref.watcher._iter_sms(Path(path)))
+            got = outcome(lambda: xml_ingest.iter_sms(path, eng))
+            n += 1
+            if want != got:
+                bad += 1
+                print("REFERENCE MISMATCH _iter_sms", doc[:300], "\n   reference:", str(want)[:300], "\n   drop-in:  ", str(got)[:300],
+                      flush=True)
+        progress(seed, t0, files=n, bad=bad, through_elementtree=eng.host_fallbacks)
+
+
+CAMPAIGNS = {"ref_iter_sms": ref_iter_sms, "scan": scan, "route": route, "legacy": legacy, "xml": xml, "xml_struct": xml_struct,
              "ref_units": ref_units, "ref_route": ref_route}
 
 if __name__ == "__main__":
