@@ -10,7 +10,7 @@ Two families:
   * the oracle against the REFERENCE ITSELF, imported from /root/reference (build container only): `ref_units`
     (worker filter lifted from worker.py, parser filter, clean + mask, fix_broken_datetime,
     parse_ambiguous_decimal), `ref_route` (parse_sms_llm + the worker / writer gates on random cache entries),
-    `ref_iter_sms` (the `_iter_sms` generator on mutated backups: rows, exception, rows before the exception).
+    `ref_legacy` (parse_transaction_message / parse_credit_message), `ref_iter_sms` (the `_iter_sms` generator on mutated backups: rows, exception, rows before the exception).
 Every mismatch prints a line containing MISMATCH; a clean run prints only the per-seed progress lines.
 Round 2's runs and the one finding they produced are listed in DESIGN.md section 2."""
 import datetime as dt
@@ -159,20 +159,7 @@ def legacy(first, last):
     import tests.test_legacy_logic_on_cpu as T
     t0, bad = time.time(), 0
     for seed in range(first, last):
-        rnd = random.Random(9000 + seed)
-        bodies = ["".join(rnd.choice(LEGACY_PIECES) for _ in range(rnd.randint(1, 26))) for _ in range(3000)]
-        for _ in range(3000):
-            s = list(rnd.choice(LEGACY_BASES))
-            for _ in range(rnd.randint(1, 5)):
-                k = rnd.randrange(len(s))
-                op = rnd.random()
-                if op < 0.4:
-                    del s[k]
-                elif op < 0.7:
-                    s.insert(k, s[k])
-                else:
-                    s[k] = rnd.choice(" ,.:*\n9aA\t٥é")
-            bodies.append("".join(s))
+        bodies = _legacy_bodies(random.Random(9000 + seed))
         try:
             T.check_against_oracle(T._res(bodies), bodies)
         except AssertionError as e:
@@ -371,6 +358,50 @@ def ref_route(first, last):
         progress(seed, t0, messages=n, bad=bad)
 
 
+def _legacy_bodies(rnd):
+    bodies = ["".join(rnd.choice(LEGACY_PIECES) for _ in range(rnd.randint(1, 26))) for _ in range(3000)]
+    for _ in range(3000):
+        s = list(rnd.choice(LEGACY_BASES))
+        for _ in range(rnd.randint(1, 5)):
+            k = rnd.randrange(len(s))
+            op = rnd.random()
+            if op < 0.4:
+                del s[k]
+            elif op < 0.7:
+                s.insert(k, s[k])
+            else:
+                s[k] = rnd.choice(" ,.:*\n9aA\t٥é")
+        bodies.append("".join(s))
+    return bodies
+
+
+def ref_legacy(first, last):
+    """oracle/legacy_oracle.py against process_cached.parse_transaction_message / parse_credit_message themselves."""
+    import logging
+
+    from oracle import legacy_oracle as LO
+    ref = _reference()
+    logging.disable(logging.CRITICAL)                     # the reference logs every amount it cannot convert
+    pc = ref.process_cached
+
+    def outcome(f, b):
+        try:
+            with ref.quiet():
+                return f(b)
+        except Exception as e:                            # noqa: BLE001
+            return type(e).__name__
+    t0, bad, n = time.time(), 0, 0
+    for seed in range(first, last):
+        for b in _legacy_bodies(random.Random(9000 + seed)):
+            n += 1
+            a = (outcome(pc.parse_transaction_message, b), outcome(pc.parse_credit_message, b))
+            c = (outcome(LO.parse_debit, b), outcome(LO.parse_credit, b))
+            if a != c:
+                bad += 1
+                print("REFERENCE MISMATCH legacy", repr(b)[:200], a, c, flush=True)
+        progress(seed, t0, bodies=n, bad=bad)
+
+
 XML_DATES = [b"99999999999999999999999", b"253402300800000", b"253402300799999", b"-62135596800001", b"-62135596800000",
              b"9223372036854775808", b"9223372036854775807", b"-9223372036854775808", b"-9223372036854775809", b" 5 ",
              b"1_0", b"+7", b"\xd9\xa1\xd9\xa2", b"", b"1e3", b"0x10", b"12345678901234567890", b"9300000000000000000000",
@@ -431,7 +462,7 @@ def ref_iter_sms(first, last):
         progress(seed, t0, files=n, bad=bad, through_elementtree=eng.host_fallbacks)
 
 
-CAMPAIGNS = {"ref_iter_sms": ref_iter_sms, "scan": scan, "route": route, "legacy": legacy, "xml": xml, "xml_struct": xml_struct,
+CAMPAIGNS = {"ref_iter_sms": ref_iter_sms, "ref_legacy": ref_legacy, "scan": scan, "route": route, "legacy": legacy, "xml": xml, "xml_struct": xml_struct,
              "ref_units": ref_units, "ref_route": ref_route}
 
 if __name__ == "__main__":
