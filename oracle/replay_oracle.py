@@ -317,20 +317,38 @@ def copy_resp(v: Any) -> Any:
 
 
 def replay_one(body: str, sender: str, raw_date: str, cache, now: _dt.datetime,
-               device_id: Optional[str] = "xml_backup") -> MessageOutcome:
+               device_id: Optional[str] = "xml_backup", lean: bool = False) -> MessageOutcome:
     """One message through worker -> parse_sms_llm (hit branch) -> writer gate
     (services/parser_worker/worker.py:112-189, services/pb_writer/writer.py:65-84).
-    `cache` is any mapping keyed by the 64-char hex cache key."""
+    `cache` is any mapping keyed by the 64-char hex cache key.
+
+    `lean=True` is the form bench.py TIMES as the CPU baseline: the reference's own order of work and nothing the
+    reference does not compute - the filters first, the rewrite and the cache key only for a message that gets
+    that far, no decimal triplets / Numeric(14,2) cents / body-date column (those exist for the parity checks of
+    the GPU columns).  Status, parsed record and dedup verdict are the same either way
+    (tests/test_oracle_golden.py)."""
     mid = msg_id_xml(body)
-    fixed = fixed_body(body)
-    ck = cache_key(fixed)
-    out = MessageOutcome(msg_id=mid, cache_key=ck, worker_skip=worker_skip(body),
-                         parser_otp=parser_otp(body), fixed=fixed, hit=False,
-                         status=ST_SKIPPED_FILTER, body_date=pack_date(body_date(body)))
+    if lean:
+        out = MessageOutcome(msg_id=mid, cache_key=b"", worker_skip=worker_skip(body), parser_otp=False, fixed="",
+                             hit=False, status=ST_SKIPPED_FILTER, body_date=0)
+        if out.worker_skip:                                       # worker.py:112-126
+            return out
+        out.parser_otp = parser_otp(body)                         # gemini_parser.py:198-200
+        if out.parser_otp:
+            out.status = ST_UNMATCHED
+            return out
+        out.fixed = fixed = fixed_body(body)                      # :202-203
+        out.cache_key = ck = cache_key(fixed)                     # :207
+    else:
+        fixed = fixed_body(body)
+        ck = cache_key(fixed)
+        out = MessageOutcome(msg_id=mid, cache_key=ck, worker_skip=worker_skip(body),
+                             parser_otp=parser_otp(body), fixed=fixed, hit=False,
+                             status=ST_SKIPPED_FILTER, body_date=pack_date(body_date(body)))
     hexkey = ck.hex()
     out.hit = hexkey in cache                                     # gemini_parser.py:208
     resp0 = cache[hexkey] if out.hit else None                    # :209
-    if isinstance(resp0, dict):
+    if isinstance(resp0, dict) and not lean:
         out.amount = decimal_triplet(str(resp0.get("amount")))
         out.balance = decimal_triplet(str(resp0.get("balance")))
         out.amount_cents = numeric_14_2(str(resp0.get("amount")))
@@ -404,8 +422,8 @@ def dedup(msg_ids: Iterable[bytes], eligible: Iterable[bool]):
     return survivor, first_seen, last_idx, last
 
 
-def replay(bodies, senders, raw_dates, cache, now: _dt.datetime) -> ReplayResult:
-    outs = [replay_one(b, s, d, cache, now) for b, s, d in zip(bodies, senders, raw_dates)]
+def replay(bodies, senders, raw_dates, cache, now: _dt.datetime, lean: bool = False) -> ReplayResult:
+    outs = [replay_one(b, s, d, cache, now, lean=lean) for b, s, d in zip(bodies, senders, raw_dates)]
     res = ReplayResult(outcomes=outs)
     res.survivor, res.first_seen, res.last_idx, res.upserts = dedup(
         (o.msg_id for o in outs), (o.status == ST_UPSERT for o in outs))

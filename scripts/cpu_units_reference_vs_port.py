@@ -84,7 +84,7 @@ def main():
 
     def port_b():
         with quiet():
-            res = O.replay(backup.bodies, backup.senders, [r.date for r in raws], c, NOW)
+            res = O.replay(backup.bodies, backup.senders, [r.date for r in raws], c, NOW, lean=True)
         return {o.msg_id.hex(): o for o, s in zip(res.outcomes, res.survivor) if s}
     tb_port, ups_port = best_of(port_b)
     c.close()
