@@ -4,7 +4,7 @@
  * The reference (vpuhoff/smsgate) is pure Python and has no FFI seam; its seam
  * is a handful of Python functions.  Each entry point below names the reference
  * code it stands in for (paths relative to the reference root).  The Python
- * drop-in (smsgate_b200/*.py) binds these with ctypes; INTEGRATION.md shows the
+ * drop-in (the modules of smsgate_b200/) binds these with ctypes; INTEGRATION.md shows the
  * stub a maintainer of the reference would add.
  *
  * Conventions
