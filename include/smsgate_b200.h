@@ -178,7 +178,10 @@ int smsgate_cache_share(smsgate_ctx* ctx, const smsgate_ctx* owner);
  * response dicts decoded in C++ (smsgate_b200/csrc/cache_reader.h), no Python object per entry.  Replaces
  * `cache = diskcache.Cache(".gemini_cache")` + the per-message `cache_key in cache` / `cache[cache_key]`
  * (libs/gemini_parser.py:33, :208-209) by one pass that yields the arrays smsgate_cache_load takes.
- *   _open   reads <cache_dir>/cache.db (read-only); `now` = time.time() for diskcache's expiry rule
+ *   _open   reads <cache_dir>/cache.db (read-only); `now` = time.time() for diskcache's expiry rule.  A large table
+ *           is read as up to eight rowid ranges at once, each on a read-only connection of its own (environment
+ *           variable SMSGATE_DCACHE_THREADS overrides the count; 1 = one connection); the cache is expected not
+ *           to be written while it is read
  *   _sizes  m entries, bytes of the four device strings, bytes of the five host-side strings, keys skipped
  *           because they are not 64 lower-case hex digits, entries the decoder leaves to the caller
  *   _fill   keys[m*32], val_offsets[4m+1], val_bytes, eflags[m] (schema facts; date flags are the caller's:

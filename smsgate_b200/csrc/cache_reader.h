@@ -22,7 +22,10 @@
 #include <stdint.h>
 #include <string.h>
 
+#include <mutex>
+#include <new>
 #include <string>
+#include <thread>
 #include <vector>
 
 namespace sgcache {
@@ -32,6 +35,7 @@ struct Sqlite {
     int (*open_v2)(const char*, void**, int, const char*) = nullptr;
     int (*prepare_v2)(void*, const char*, int, void**, const char**) = nullptr;
     int (*bind_double)(void*, int, double) = nullptr;
+    int (*bind_int64)(void*, int, long long) = nullptr;
     int (*step)(void*) = nullptr;
     const void* (*column_blob)(void*, int) = nullptr;
     int (*column_bytes)(void*, int) = nullptr;
@@ -52,7 +56,7 @@ struct Sqlite {
 #define SG_SYM(field, sym)                                             \
     field = reinterpret_cast<decltype(field)>(dlsym(so, sym));         \
     if (!field) { *err = std::string("libsqlite3 lacks ") + sym; return false; }
-        SG_SYM(open_v2, "sqlite3_open_v2") SG_SYM(prepare_v2, "sqlite3_prepare_v2") SG_SYM(bind_double, "sqlite3_bind_double")
+        SG_SYM(open_v2, "sqlite3_open_v2") SG_SYM(prepare_v2, "sqlite3_prepare_v2") SG_SYM(bind_double, "sqlite3_bind_double") SG_SYM(bind_int64, "sqlite3_bind_int64")
         SG_SYM(step, "sqlite3_step") SG_SYM(column_blob, "sqlite3_column_blob") SG_SYM(column_bytes, "sqlite3_column_bytes")
         SG_SYM(column_text, "sqlite3_column_text") SG_SYM(column_int64, "sqlite3_column_int64")
         SG_SYM(column_type, "sqlite3_column_type") SG_SYM(finalize, "sqlite3_finalize") SG_SYM(close, "sqlite3_close")
@@ -303,12 +307,11 @@ inline void append_entry(Table* T, const uint8_t key32[32], int64_t rowid, const
     ++T->m;
 }
 
-// Read <dir>/cache.db.  Entries: string keys (TEXT, raw = 1) of 64 lower-case hex digits whose expire_time
-// is NULL or later than `now`, in rowid order - what `key in cache` answers True for and the order
-// diskcache iterates in.
-inline bool read_diskcache(const char* dir, double now, Table* T) {
-    static Sqlite S;
-    if (!S.load(&T->err)) return false;
+// Read the rows of <dir>/cache.db whose rowid lies in [lo, hi] (lo > hi: all of them) into *T, on a connection of
+// its own.  Entries: string keys (TEXT, raw = 1) of 64 lower-case hex digits whose expire_time is NULL or later
+// than `now`, in rowid order - what `key in cache` answers True for and the order diskcache iterates in.
+// T->val_offsets holds four ENDS per entry, T->text_offsets starts with 0.
+inline bool read_rows(Sqlite& S, const char* dir, double now, long long lo, long long hi, Table* T) {
     const std::string uri = std::string("file:") + dir + "/cache.db?mode=ro";
     void* db = nullptr;
     if (S.open_v2(uri.c_str(), &db, 0x1 /*READONLY*/ | 0x40 /*URI*/, nullptr) != 0) {
@@ -318,14 +321,17 @@ inline bool read_diskcache(const char* dir, double now, Table* T) {
     }
     S.busy_timeout(db, 60000);
     void* st = nullptr;
-    const char* sql = "SELECT rowid, key, mode, filename, value FROM Cache WHERE raw = 1 AND typeof(key) = 'text' "
-                      "AND (expire_time IS NULL OR expire_time > ?) ORDER BY rowid";
-    if (S.prepare_v2(db, sql, -1, &st, nullptr) != 0) {
+    const bool ranged = lo <= hi;
+    const std::string sql = std::string("SELECT rowid, key, mode, filename, value FROM Cache WHERE raw = 1 AND typeof(key) = 'text' "
+                                        "AND (expire_time IS NULL OR expire_time > ?1)") +
+                            (ranged ? " AND rowid BETWEEN ?2 AND ?3" : "") + " ORDER BY rowid";
+    if (S.prepare_v2(db, sql.c_str(), -1, &st, nullptr) != 0) {
         T->err = std::string("not a diskcache database: ") + S.errmsg(db);
         S.close(db);
         return false;
     }
     S.bind_double(st, 1, now);
+    if (ranged) { S.bind_int64(st, 2, lo); S.bind_int64(st, 3, hi); }
     T->val_offsets.clear();
     T->text_offsets.assign(1, 0);
     int rc;
@@ -336,15 +342,14 @@ inline bool read_diskcache(const char* dir, double now, Table* T) {
         uint8_t k32[32];
         bool hex = klen == 64;
         for (int k = 0; hex && k < 32; ++k) {
-            const int hi = hexval(key[2 * k]), lo = hexval(key[2 * k + 1]);
-            hex = hi >= 0 && lo >= 0;
-            k32[k] = (uint8_t)((hi << 4) | lo);
+            const int hi4 = hexval(key[2 * k]), lo4 = hexval(key[2 * k + 1]);
+            hex = hi4 >= 0 && lo4 >= 0;
+            k32[k] = (uint8_t)((hi4 << 4) | lo4);
         }
         if (!hex) { ++T->skipped; continue; }
         const long long mode = S.column_int64(st, 2);
         const bool in_file = S.column_type(st, 3) != 5;                     // filename NOT NULL: value lives in a side file
         Decoded d;
-        bool force_host = false;
         if (mode == 4 && !in_file && S.column_type(st, 4) == 4) {           // MODE_PICKLE, inline blob
             const uint8_t* blob = static_cast<const uint8_t*>(S.column_blob(st, 4));
             d = decode_pickle(blob, (size_t)S.column_bytes(st, 4));
@@ -355,13 +360,99 @@ inline bool read_diskcache(const char* dir, double now, Table* T) {
             append_entry(T, k32, rowid, d, false);
             continue;
         }
-        force_host = true;                                                   // side files, other modes: Python's Disk.fetch
-        append_entry(T, k32, rowid, d, force_host);
+        append_entry(T, k32, rowid, d, true);                                // side files, other modes: Python's Disk.fetch
     }
     S.finalize(st);
     const bool ok = rc == 101;
     if (!ok) T->err = std::string("reading cache.db failed: ") + S.errmsg(db);
     S.close(db);
+    return ok;
+}
+
+// lowest and highest rowid of the table; false if it is empty or unreadable (the caller then reads it in one piece)
+inline bool rowid_span(Sqlite& S, const char* dir, long long* lo, long long* hi) {
+    const std::string uri = std::string("file:") + dir + "/cache.db?mode=ro";
+    void* db = nullptr;
+    if (S.open_v2(uri.c_str(), &db, 0x1 | 0x40, nullptr) != 0) {
+        if (db) S.close(db);
+        return false;
+    }
+    S.busy_timeout(db, 60000);
+    void* st = nullptr;
+    bool ok = false;
+    if (S.prepare_v2(db, "SELECT min(rowid), max(rowid) FROM Cache", -1, &st, nullptr) == 0) {
+        if (S.step(st) == 100 && S.column_type(st, 0) == 1) {
+            *lo = S.column_int64(st, 0);
+            *hi = S.column_int64(st, 1);
+            ok = true;
+        }
+        S.finalize(st);
+    }
+    S.close(db);
+    return ok;
+}
+
+template <class V>
+inline void append_vec(V* dst, const V& src) { dst->insert(dst->end(), src.begin(), src.end()); }
+
+// Read <dir>/cache.db into *T.  A large table is read as `threads` contiguous rowid ranges at once, each on its own
+// read-only connection, and the parts are joined in rowid order: SQLite's row decoding and the pickle decoding are
+// the cost (2.2 us per entry on one core), both per row.  threads <= 0: one per 64 K rows, at most 8 and at most the
+// host's cores.  The ranges are separate read transactions: the cache is expected not to be written meanwhile (a
+// bulk replay is an offline job; a writer committing between two ranges' snapshots shows in one and not the other).
+inline bool read_diskcache(const char* dir, double now, Table* T, int threads = 0) {
+    static Sqlite S;
+    static std::mutex load_mutex;
+    {
+        std::lock_guard<std::mutex> g(load_mutex);
+        if (!S.load(&T->err)) return false;
+    }
+    long long lo = 0, hi = -1;
+    if (threads != 1 && rowid_span(S, dir, &lo, &hi)) {
+        const long long span = hi - lo + 1;
+        if (threads <= 0) {
+            const unsigned hw = std::thread::hardware_concurrency();
+            long long t = span / 65536;
+            if (t > 8) t = 8;
+            if (hw && t > (long long)hw) t = hw;
+            threads = t < 1 ? 1 : (int)t;
+        }
+        if ((long long)threads > span) threads = (int)span;
+    } else threads = 1;
+    bool ok = true;
+    if (threads <= 1) {
+        ok = read_rows(S, dir, now, 0, -1, T);
+    } else {
+        std::vector<Table> parts((size_t)threads);
+        std::vector<char> oks((size_t)threads, 0);
+        std::vector<std::thread> pool;
+        const long long span = hi - lo + 1;
+        for (int t = 0; t < threads; ++t) {
+            const long long a = lo + span * t / threads, b = lo + span * (t + 1) / threads - 1;
+            pool.emplace_back([&, t, a, b] {
+                try {
+                    oks[(size_t)t] = read_rows(S, dir, now, a, b, &parts[(size_t)t]) ? 1 : 0;
+                } catch (const std::bad_alloc&) {
+                    parts[(size_t)t].err = "out of host memory";
+                }
+            });
+        }
+        for (auto& th : pool) th.join();
+        T->val_offsets.clear();
+        T->text_offsets.assign(1, 0);
+        for (int t = 0; t < threads; ++t) {
+            Table& P = parts[(size_t)t];
+            if (!oks[(size_t)t]) { ok = false; if (T->err.empty()) T->err = P.err; continue; }
+            const int64_t vbase = (int64_t)T->val_bytes.size(), tbase = (int64_t)T->text_bytes.size();
+            T->m += P.m; T->skipped += P.skipped; T->fallbacks += P.fallbacks;
+            append_vec(&T->keys, P.keys); append_vec(&T->rowids, P.rowids); append_vec(&T->eflags, P.eflags);
+            append_vec(&T->needs_host, P.needs_host); append_vec(&T->text_kind, P.text_kind);
+            append_vec(&T->val_bytes, P.val_bytes); append_vec(&T->text_bytes, P.text_bytes);
+            for (int64_t v : P.val_offsets) T->val_offsets.push_back(v + vbase);
+            for (size_t k = 1; k < P.text_offsets.size(); ++k) T->text_offsets.push_back(P.text_offsets[k] + tbase);
+            P = Table();                                    // free the part's buffers before the next one is copied
+        }
+    }
     // val_offsets were pushed as 4 per entry (ends of the four strings); turn them into 4m+1 starts/ends
     std::vector<int64_t> vo(4 * T->m + 1, 0);
     for (int64_t e = 0; e < 4 * T->m; ++e) vo[e + 1] = T->val_offsets[e];

@@ -928,7 +928,8 @@ extern "C" int smsgate_dcache_open(const char* cache_dir, double now, smsgate_dc
     if (!h) return SMSGATE_E_NOMEM;
     bool ok = false;
     try {
-        ok = sgcache::read_diskcache(cache_dir, now, &h->T);
+        const char* forced = getenv("SMSGATE_DCACHE_THREADS");           // tests force the multi-connection path on small caches
+        ok = sgcache::read_diskcache(cache_dir, now, &h->T, forced ? atoi(forced) : 0);
     } catch (const std::bad_alloc&) {
         h->T.err = "out of host memory";
     }

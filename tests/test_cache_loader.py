@@ -96,9 +96,15 @@ def _extra_entries(c):
     return names
 
 
-def test_native_reader_matches_python_reader(tmp_path):
+import pytest
+
+
+@pytest.mark.parametrize("connections", ["1", "3", "16"])
+def test_native_reader_matches_python_reader(tmp_path, monkeypatch, connections):
     """smsgate_dcache_* (C++: SQLite + pickle subset, no Python object per entry) against the per-entry
-    Python path, array by array, for every entry it decodes itself; what it declines is flagged, not guessed."""
+    Python path, array by array, for every entry it decodes itself; what it declines is flagged, not guessed.
+    Read on one connection and as 3 / 16 rowid ranges at once (what a large cache gets by default)."""
+    monkeypatch.setenv("SMSGATE_DCACHE_THREADS", connections)
     import ctypes as C
 
     from smsgate_b200 import _lib as L
@@ -174,13 +180,14 @@ def _native_vs_python(tmp_path, names):
     return by_name, host, keys, m.value
 
 
-def test_native_reader_fuzz_over_pickle_protocols(tmp_path):
+def test_native_reader_fuzz_over_pickle_protocols(tmp_path, monkeypatch):
     """Random response dicts - every value type the decoder's subset has an opinion on, shared and repeated
     strings, long strings, extra keys - stored by diskcache with pickle protocols 2 to 5 (a cache directory may
     have been written by an older interpreter).  What the native reader decodes itself must equal the Python
     path; declining an entry is always allowed."""
     import hashlib
     import random
+    monkeypatch.setenv("SMSGATE_DCACHE_THREADS", "4")
     rng = random.Random(0xCAC4E)
     words = ["", "a", "52.00", "1,842.74", "TEST LLC", "Ереван", "☕", "x" * 255, "y" * 256, "z" * 70000, "null",
              "06.05.25 14:23", "06.05.2025 14:23", "2025-05-06T14:23:00+04:00", "***0018", "4083***7538", "usd"]
