@@ -490,9 +490,10 @@ int smsgate_fetch_columns(smsgate_ctx* ctx, int64_t n, const smsgate_outputs* h_
  *   mode 1  the record upsert_parsed_sms hands to PocketBase (libs/pocketbase.py:296-309), as compact JSON
  * assembled on the host from the replay's columns (or packed records) and the natively read cache texts
  * (smsgate_dcache_fill: text_offsets / text_bytes / text_kind) - no pydantic object per record.  Two calls:
- * with out_bytes = NULL it only reports `needed`; then out_offsets[n_sel+1] + out_bytes[capacity] are filled and
+ * with out_bytes = NULL it reports `needed` (and already fills out_offsets[n_sel+1]); then out_bytes[capacity] is filled and
  * fallback[k] = 1 marks a row this code leaves to the caller (non-ASCII currency, a cache field of another type,
- * an overflowed coefficient): its span is empty.  Host memory only. */
+ * an overflowed coefficient): its span is empty.  Host memory only; rows are independent, so large selections are
+ * sized and written by up to eight host threads (environment variable SMSGATE_EMIT_THREADS overrides the count). */
 typedef struct smsgate_emit_input {
     const smsgate_record* records;   /* packed records, or NULL to use the columns below */
     const uint8_t* msg_id; const uint8_t* status; const uint8_t* flags; const uint8_t* dec_flags; const int32_t* slot;

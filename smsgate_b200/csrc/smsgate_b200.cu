@@ -986,18 +986,48 @@ extern "C" int smsgate_emit_json(const smsgate_emit_input* in, int mode, int64_t
     if (!I.msg_id || !I.card || !I.card_len || !I.body_offsets || !I.sender_offsets || !I.text_offsets || !I.text_kind ||
         (!in->records && (!I.flags || !I.dec_flags || !I.slot || !I.amount_coef || !I.balance_coef || !I.amount_exp || !I.balance_exp || !I.date)))
         return SMSGATE_E_ARG;
-    sgemit::Sink count{nullptr};
-    for (int64_t k = 0; k < n_sel; ++k) sgemit::emit_one(count, I, sel[k], mode);
-    if (needed) *needed = count.n;
-    if (!out_bytes) return SMSGATE_OK;                       // sizing pass
-    if (capacity < count.n) return SMSGATE_E_LIMIT;
-    sgemit::Sink w{out_bytes};
-    for (int64_t k = 0; k < n_sel; ++k) {
-        out_offsets[k] = w.n;
-        const bool ok = sgemit::emit_one(w, I, sel[k], mode);
-        if (fallback) fallback[k] = ok ? 0 : 1;
+    // Rows are independent: a sizing pass leaves every row's length in out_offsets[k + 1], a prefix sum turns the
+    // lengths into offsets, the emitting pass writes each row at its offset.  Both passes run on several host threads
+    // once there are enough rows (one per 32 K rows, at most 8 and at most the host's cores; environment variable
+    // SMSGATE_EMIT_THREADS overrides the count).
+    int threads = 1;
+    if (const char* forced = getenv("SMSGATE_EMIT_THREADS")) threads = atoi(forced);
+    else {
+        const unsigned hw = std::thread::hardware_concurrency();
+        int64_t t = n_sel / 32768;
+        if (t > 8) t = 8;
+        if (hw && t > (int64_t)hw) t = hw;
+        threads = (int)t;
     }
-    out_offsets[n_sel] = w.n;
+    if (threads < 1) threads = 1;
+    if ((int64_t)threads > n_sel) threads = n_sel > 0 ? (int)n_sel : 1;
+    auto in_chunks = [&](auto&& body) {                      // body(first row, one past the last row) on each thread
+        if (threads == 1) { body((int64_t)0, n_sel); return; }
+        std::vector<std::thread> pool;
+        for (int t = 0; t < threads; ++t)
+            pool.emplace_back([&, t] { body(n_sel * t / threads, n_sel * (t + 1) / threads); });
+        for (auto& th : pool) th.join();
+    };
+    out_offsets[0] = 0;
+    in_chunks([&](int64_t k0, int64_t k1) {
+        for (int64_t k = k0; k < k1; ++k) {
+            sgemit::Sink count{nullptr};
+            sgemit::emit_one(count, I, sel[k], mode);
+            out_offsets[k + 1] = count.n;
+        }
+    });
+    for (int64_t k = 0; k < n_sel; ++k) out_offsets[k + 1] += out_offsets[k];
+    const int64_t total = out_offsets[n_sel];
+    if (needed) *needed = total;
+    if (!out_bytes) return SMSGATE_OK;                       // sizing call
+    if (capacity < total) return SMSGATE_E_LIMIT;
+    in_chunks([&](int64_t k0, int64_t k1) {
+        for (int64_t k = k0; k < k1; ++k) {
+            sgemit::Sink w{out_bytes + out_offsets[k]};
+            const bool ok = sgemit::emit_one(w, I, sel[k], mode);
+            if (fallback) fallback[k] = ok ? 0 : 1;
+        }
+    });
     return SMSGATE_OK;
 }
 

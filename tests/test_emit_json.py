@@ -27,7 +27,12 @@ def _result(bodies, senders, cache):
     return ReplayResult(batch, cols, table, 0), table
 
 
-def test_payload_bytes_equal_pydantic():
+import pytest
+
+
+@pytest.mark.parametrize("threads", ["1", "5"])
+def test_payload_bytes_equal_pydantic(monkeypatch, threads):
+    monkeypatch.setenv("SMSGATE_EMIT_THREADS", threads)      # one thread / rows split over five (large batches get that by default)
     backup = synth.generate(4000, seed=91, mixed_locale=True, miss_frac=0.1)
     cache = dict(backup.cache)
     keys = list(cache)
@@ -89,12 +94,13 @@ _FUZZ_ALPHABET = ['a', 'Z', '0', ' ', '"', '\\', '/', '\n', '\t', '\r', '\x00', 
                   "'", '\x08', '\x0c', '\x0b']
 
 
-def test_emitter_fuzz_against_pydantic():
+def test_emitter_fuzz_against_pydantic(monkeypatch):
     """Random cache entries - text from an alphabet of everything JSON escapes or pydantic treats specially,
     amounts in every shape parse_ambiguous_decimal accepts, upper-casable and non-ASCII currencies - rendered by
     the native emitter and by pydantic.  The emitter may decline a row (non-ASCII currency: str.upper() is
     Python's; a coefficient beyond int64), it may never differ."""
     import random
+    monkeypatch.setenv("SMSGATE_EMIT_THREADS", "3")
     rng = random.Random(0xE417)
 
     def text(maxlen=12):
