@@ -1023,9 +1023,14 @@ extern "C" int smsgate_emit_json(const smsgate_emit_input* in, int mode, int64_t
     if (capacity < total) return SMSGATE_E_LIMIT;
     in_chunks([&](int64_t k0, int64_t k1) {
         for (int64_t k = k0; k < k1; ++k) {
-            sgemit::Sink w{out_bytes + out_offsets[k]};
-            const bool ok = sgemit::emit_one(w, I, sel[k], mode);
-            if (fallback) fallback[k] = ok ? 0 : 1;
+            // a row the sizing pass declined has an empty span and must not be started again: what it writes before
+            // it gives up would land in its neighbour's span (or past the end of the buffer)
+            const bool declined = out_offsets[k + 1] == out_offsets[k];
+            if (!declined) {
+                sgemit::Sink w{out_bytes + out_offsets[k]};
+                sgemit::emit_one(w, I, sel[k], mode);
+            }
+            if (fallback) fallback[k] = declined ? 1 : 0;
         }
     });
     return SMSGATE_OK;
