@@ -1,0 +1,135 @@
+"""The host C++ inside the library that parses bytes someone else wrote - the pickle decoder of the native cache
+reader - and the payload emitter, built with AddressSanitizer + UBSan and run on mutated / adversarial input.
+No GPU, no CUDA: the two headers are plain C++ (tests/hostcheck/asan_*.cpp include them directly)."""
+import os
+import pickle
+import random
+import shutil
+import struct
+import subprocess
+
+import numpy as np
+import pytest
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+CSRC = os.path.join(ROOT, "smsgate_b200", "csrc")
+SAN = ["-std=c++17", "-O1", "-g", "-fsanitize=address,undefined", "-fno-sanitize-recover=undefined", "-fno-omit-frame-pointer"]
+
+
+def _build(tmp_path, name):
+    gxx = shutil.which("g++")
+    if gxx is None:
+        pytest.skip("no g++")
+    exe = str(tmp_path / name)
+    res = subprocess.run([gxx] + SAN + ["-I", CSRC, "-o", exe, os.path.join(ROOT, "tests", "hostcheck", name + ".cpp"), "-ldl", "-lpthread"],
+                         capture_output=True, text=True)
+    if res.returncode and "sanitize" in res.stderr and "cannot find" in res.stderr:
+        pytest.skip("g++ has no sanitizer runtime here")
+    assert res.returncode == 0, res.stderr[-2000:]
+    return exe
+
+
+def _run(exe, arg):
+    env = dict(os.environ, ASAN_OPTIONS="detect_leaks=0:abort_on_error=0", UBSAN_OPTIONS="print_stacktrace=1")
+    res = subprocess.run([exe, arg], capture_output=True, text=True, env=env, timeout=600)
+    assert res.returncode == 0 and "ERROR: AddressSanitizer" not in res.stderr and "runtime error" not in res.stderr, res.stderr[-3000:]
+    return res.stdout
+
+
+def test_pickle_decoder_on_mutated_blobs(tmp_path):
+    rng = random.Random(0xA5A)
+    words = ["", "a", "52.00", "1,842.74", "TEST LLC", "Ереван", "☕", "x" * 255, "y" * 256, "z" * 70000,
+             "null", "06.05.25 14:23", "***0018", "usd"]
+
+    def value():
+        k = rng.random()
+        if k < 0.5:
+            return rng.choice(words)
+        if k < 0.6:
+            return None
+        if k < 0.7:
+            return rng.choice([0, 1, -1, 255, 256, 65535, 65536, 2 ** 31 - 1, 2 ** 31, -2 ** 31, 2 ** 63 - 1, 2 ** 63, -2 ** 63, 10 ** 30])
+        if k < 0.75:
+            return rng.choice([True, False])
+        if k < 0.8:
+            return rng.choice([0.0, 12.5, -1e300, float("inf")])
+        if k < 0.9:
+            return rng.choice([b"bytes", ("t", 1), ["l"], {"d": 1}, {1, 2}, frozenset(), bytearray(b"x")])
+        return "".join(rng.choice("aЖ☕ \"\\\n0,.-") for _ in range(rng.randint(0, 30)))
+    fields = ["txn_type", "date", "amount", "currency", "card", "merchant", "city", "address", "balance"]
+    path = tmp_path / "blobs.bin"
+    n = 30000
+    with open(path, "wb") as out:
+        for _ in range(n):
+            keep = [f for f in fields if rng.random() < 0.9]
+            rng.shuffle(keep)
+            shared = value()
+            v = {f: (shared if rng.random() < 0.2 else value()) for f in keep}
+            if rng.random() < 0.03:
+                v = rng.choice([[], "str", 5, None, (1, 2), {}])
+            blob = bytearray(pickle.dumps(v, protocol=rng.choice([0, 1, 2, 3, 4, 5])))
+            r = rng.random()
+            if r < 0.25:
+                blob = blob[:rng.randint(0, len(blob))]                       # cut short
+            elif r < 0.7:
+                for _ in range(rng.randint(1, 4)):
+                    if not blob:
+                        break
+                    k = rng.randrange(len(blob))
+                    op = rng.random()
+                    if op < 0.3:
+                        del blob[k]
+                    elif op < 0.7:
+                        blob[k] = rng.randrange(256)
+                    else:
+                        blob.insert(k, rng.randrange(256))
+            elif r < 0.75:
+                blob = bytearray(rng.randrange(256) for _ in range(rng.randint(0, 64)))   # noise
+            out.write(struct.pack("<I", len(blob)))
+            out.write(blob)
+    stdout = _run(_build(tmp_path, "asan_pickle"), str(path))
+    assert f"decoded {n} blobs" in stdout
+
+
+def test_emitter_writes_exactly_what_it_announced(tmp_path):
+    from smsgate_b200 import synth
+    from smsgate_b200.batch import ragged_from_strings
+    from tests import test_emit_json as T
+    rng = random.Random(0xE417)
+
+    def text(maxlen=12):
+        return ''.join(rng.choice(T._FUZZ_ALPHABET) for _ in range(rng.randint(0, maxlen)))
+    backup = synth.generate(2500, seed=2001, mixed_locale=True)
+    cache = dict(backup.cache)
+    for key in list(cache):
+        if rng.random() < 0.8:
+            cache[key] = dict(cache[key], merchant=text() or "m", city=rng.choice([None, text(), ""]),
+                              address=rng.choice([None, text(40), "null", ""]),
+                              amount=rng.choice(["52.00", "0.0000001", "1e5", "999999999999999999", "0", "-0", "1,234.5", "9" * 25,
+                                                 "0." + "0" * 17 + "1"]),
+                              balance=rng.choice(["1", "-12,5", None, "000123.4500", "0.00"]),
+                              currency=rng.choice(["amd", "USD", "", None, "ß", "a b", 5]),
+                              txn_type=rng.choice(["debit", "credit", "otp", "unknown"]))
+    senders = [text(8) for _ in backup.senders]
+    res, table = T._result(list(backup.bodies), senders, cache)
+    d = tmp_path / "cols"
+    d.mkdir()
+
+    def w(name, a, dt):
+        np.ascontiguousarray(a, dtype=dt).tofile(str(d / name))
+    w("n", [len(backup.bodies), table.m], np.int64)
+    for name, dt in (("msg_id", np.uint8), ("status", np.uint8), ("flags", np.uint8), ("dec_flags", np.uint8), ("slot", np.int32),
+                     ("amount_coef", np.int64), ("balance_coef", np.int64), ("amount_exp", np.int32), ("balance_exp", np.int32),
+                     ("date", np.int64), ("card", np.uint8), ("card_len", np.uint8), ("fixed_len", np.int32), ("fixed_bytes", np.uint8)):
+        w(name, res.cols[name], dt)
+    sb, so = ragged_from_strings(senders)
+    w("body_offsets", res.batch.body_offsets, np.int64)
+    w("body_bytes", res.batch.body_bytes, np.uint8)
+    w("sender_offsets", so, np.int64)
+    w("sender_bytes", sb, np.uint8)
+    w("text_offsets", table.text[0], np.int64)
+    w("text_bytes", table.text[1], np.uint8)
+    w("text_kind", table.text[2], np.uint8)
+    stdout = _run(_build(tmp_path, "asan_emit"), str(d))
+    rows = int(stdout.split()[1])
+    assert rows > 2000 and "MISMATCH" not in stdout
