@@ -15,6 +15,11 @@
  *     different contexts are independent.
  *   - "d_" pointers are device memory owned by the caller; "h_" pointers are
  *     host memory.
+ *   - Every d_bytes buffer (bodies, XML text) needs 8 readable bytes past its last byte: the kernels that read
+ *     a body straight from global memory (MD5 keys, the legacy path, bodies larger than the keys kernel's staging
+ *     buffer) fetch aligned 4-byte words and may touch the word after the one holding the last byte.  Buffers the
+ *     library allocates itself (the host-buffer calls) have that slack; any CUDA allocation that is not filled to
+ *     its last byte has it too.
  *   - Which calls allocate.  The replay path proper allocates NOTHING per call: smsgate_scan_keys,
  *     smsgate_join_route, smsgate_dedup, smsgate_join_route_dedup, smsgate_replay_device, smsgate_replay_host*
  *     (all forms), smsgate_fetch_columns, smsgate_device_keys, smsgate_cross_source, the smsgate_dedup_export /

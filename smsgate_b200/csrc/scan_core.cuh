@@ -502,7 +502,8 @@ SG_HD void sg_sha1(const uint8_t* m, int len, uint32_t h[5]) {
 // sg_padded_word but little-endian: the first message byte is the LOW byte of word 0
 SG_HD uint32_t sg_md5_word(const WordReader& R, int len, int j, int nwords) {
     const int k = len - j * 4;
-    const uint32_t raw = R.le(j);
+    const uint32_t raw = k > 0 ? R.le(j) : 0u;       // padding words are not read: MD5 runs straight off global memory,
+                                                     // and the caller owes only 8 readable bytes past the last body
     const uint32_t kk = (uint32_t)(k < 0 ? 0 : (k > 4 ? 4 : k));
     const uint32_t keep = kk == 0 ? 0u : (0xFFFFFFFFu >> (32 - 8 * kk));
     uint32_t w = raw & keep;
