@@ -15,7 +15,9 @@ _lib = None
 def lib():
     global _lib
     if _lib is None:
-        _lib = C.CDLL(build.build_hostcheck())
+        import os
+        # tests/test_host_cpp_sanitized.py points this at a build with AddressSanitizer + UBSan
+        _lib = C.CDLL(os.environ.get("SMSGATE_HOSTCHECK_LIB") or build.build_hostcheck())
     return _lib
 
 

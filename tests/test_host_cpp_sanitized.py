@@ -133,3 +133,55 @@ def test_emitter_writes_exactly_what_it_announced(tmp_path):
     stdout = _run(_build(tmp_path, "asan_emit"), str(d))
     rows = int(stdout.split()[1])
     assert rows > 2000 and "MISMATCH" not in stdout
+
+
+_DEVICE_LOGIC_SCRIPT = r"""
+import random, sys
+sys.path.insert(0, sys.argv[1])
+import numpy as np
+from smsgate_b200 import gemini_cache, synth
+from tests import _hostcheck as H
+from tests._fuzz import bodies
+import datetime as dt
+bs = list(bodies(4000, 4242))
+sc = H.scan(bs)                                            # keys, filters, rewrite, body date
+H.md5(bs)                                                  # MD5 straight off the byte buffer (8 bytes of slack)
+H.md5(["", "a" * 55, "b" * 56, "c" * 63, "d" * 64, "e" * 119, "f" * 120])
+rng = random.Random(7)
+alphabet = "0123456789" * 3 + "..,,  -\u00a0\u202f\u2009\t\nE+eAMD$\u0665\uff11"
+H.decimal(["".join(rng.choice(alphabet) for _ in range(rng.choice([0, 1, 2, 3, 5, 8, 12, 18, 24, 40]))) for _ in range(20000)])
+H.strict_date(["06.05.25 14:23", "", "x" * 40, "31.02.25 10:00", "06.05.25 14:2", "\u0660\u0666.05.25 14:23"] * 50)
+b = synth.generate(3000, seed=9, mixed_locale=True, miss_frac=0.2, dup_frac=0.2)
+sc = H.scan(b.bodies)
+table = gemini_cache.build_table(b.cache, H.strict_date)
+H.join_route(sc, table, gemini_cache.pack_datetime(dt.datetime(2026, 1, 1)))
+H.legacy(bs[:2000])
+H.legacy(list(b.bodies)[:1500], 3)
+from tests._xml_cases import documents
+for d in documents()[:600]:
+    H.xml_extract(d)
+print("device logic ok")
+"""
+
+
+def test_device_logic_under_sanitizers(tmp_path):
+    """The kernels' __host__ __device__ cores (scan, keys, decimals, dates, join + routing, legacy matcher, XML
+    tokenizer) compiled for the CPU with AddressSanitizer + UBSan and run on adversarial input: a read past a
+    buffer is silent on the GPU.  (This is how the MD5 kernel's reads of its padding words were found.)"""
+    gxx = shutil.which("g++")
+    if gxx is None:
+        pytest.skip("no g++")
+    lib = str(tmp_path / "libhostcheck_san.so")
+    res = subprocess.run([gxx] + SAN + ["-fPIC", "-shared", "-I", CSRC, "-o", lib, os.path.join(ROOT, "tests", "hostcheck", "hostcheck.cpp")],
+                         capture_output=True, text=True)
+    assert res.returncode == 0, res.stderr[-2000:]
+    runtimes = [subprocess.run([gxx, "-print-file-name=" + n], capture_output=True, text=True).stdout.strip()
+                for n in ("libasan.so", "libubsan.so")]
+    if not all(os.path.isabs(r) and os.path.exists(r) for r in runtimes):
+        pytest.skip("sanitizer runtimes not found")
+    import sys
+    env = dict(os.environ, LD_PRELOAD=":".join(runtimes), ASAN_OPTIONS="detect_leaks=0:abort_on_error=0",
+               UBSAN_OPTIONS="print_stacktrace=1", SMSGATE_HOSTCHECK_LIB=lib)
+    res = subprocess.run([sys.executable, "-c", _DEVICE_LOGIC_SCRIPT, ROOT], capture_output=True, text=True, env=env, timeout=900)
+    assert res.returncode == 0 and "device logic ok" in res.stdout, (res.stdout[-500:], res.stderr[-3000:])
+    assert "ERROR: AddressSanitizer" not in res.stderr and "runtime error" not in res.stderr, res.stderr[-3000:]
