@@ -10,6 +10,7 @@ from smsgate_b200 import build
 from smsgate_b200.batch import ragged_from_strings
 
 _lib = None
+SLACK = 8        # readable bytes past the last byte of a byte buffer: what include/smsgate_b200.h asks callers for
 
 
 def lib():
@@ -31,7 +32,7 @@ def scan(bodies):
     cols = dict(msg_id=np.zeros((n, 20), np.uint8), cache_key=np.zeros((n, 32), np.uint8),
                 flags=np.zeros(n, np.uint8), body_date=np.zeros(n, np.int32), fixed_len=np.zeros(n, np.int32),
                 fixed_bytes=np.zeros(max(len(data), 1), np.uint8))
-    data = np.concatenate([data, np.zeros(16, np.uint8)])
+    data = np.concatenate([data, np.zeros(SLACK, np.uint8)])
     rc = lib().hc_scan_keys(_p(data), _p(offsets), C.c_int64(n), _p(cols["msg_id"]), _p(cols["cache_key"]),
                             _p(cols["flags"]), _p(cols["body_date"]), _p(cols["fixed_len"]), _p(cols["fixed_bytes"]))
     assert rc > -200000, f"sg_hash_pass disagrees with the plain digests (code {rc})"
@@ -44,7 +45,7 @@ def md5(bodies):
     data, offsets = ragged_from_strings(bodies)
     n = len(bodies)
     out = np.zeros((n, 16), np.uint8)
-    data = np.concatenate([data, np.zeros(16, np.uint8)])
+    data = np.concatenate([data, np.zeros(SLACK, np.uint8)])
     lib().hc_md5(_p(data), _p(offsets), C.c_int64(n), _p(out))
     return out
 
@@ -53,7 +54,7 @@ def decimal(strings):
     data, offsets = ragged_from_strings(strings, np.int32)
     n = len(strings)
     coef, exp, flags = np.zeros(n, np.int64), np.zeros(n, np.int32), np.zeros(n, np.uint8)
-    data = np.concatenate([data, np.zeros(16, np.uint8)])
+    data = np.concatenate([data, np.zeros(SLACK, np.uint8)])
     lib().hc_decimal(C.c_int64(n), _p(offsets), _p(data), _p(coef), _p(exp), _p(flags))
     return coef, exp, flags
 
@@ -62,7 +63,7 @@ def strict_date(strings):
     data, offsets = ragged_from_strings(strings, np.int32)
     n = len(strings)
     out = np.zeros(n, np.int64)
-    data = np.concatenate([data, np.zeros(16, np.uint8)])
+    data = np.concatenate([data, np.zeros(SLACK, np.uint8)])
     lib().hc_strict_date(C.c_int64(n), _p(offsets), _p(data), _p(out))
     return out
 
@@ -70,7 +71,7 @@ def strict_date(strings):
 def dt_str(strings):
     data, offsets = ragged_from_strings(strings, np.int32)
     out = np.zeros(len(strings), np.int64)
-    data = np.concatenate([data, np.zeros(16, np.uint8)])
+    data = np.concatenate([data, np.zeros(SLACK, np.uint8)])
     lib().hc_dt_str(C.c_int64(len(strings)), _p(offsets), _p(data), _p(out))
     return out
 
@@ -83,7 +84,7 @@ def join_route(scan_cols, table, now_packed, phone_dt=None):
                 card=np.zeros((n, 16), np.uint8), card_len=np.zeros(n, np.uint8),
                 amount_cents=np.zeros(n, np.int64), balance_cents=np.zeros(n, np.int64))
     keys = np.ascontiguousarray(table.keys)
-    vb = np.concatenate([table.val_bytes, np.zeros(16, np.uint8)])
+    vb = np.concatenate([table.val_bytes, np.zeros(SLACK, np.uint8)])
     lib().hc_join_route(C.c_int64(n), _p(scan_cols["cache_key"]), _p(scan_cols["flags"]), _p(scan_cols["body_date"]),
                         C.c_int64(now_packed), C.c_int64(table.m), _p(keys), _p(table.val_offsets), _p(vb),
                         _p(table.eflags), _p(table.date_packed), _p(cols["slot"]), _p(cols["status"]),
@@ -100,7 +101,7 @@ def legacy(bodies, mode=0):
     cols = dict(status=np.zeros(n, np.uint8), lflags=np.zeros(n, np.uint8), strip=np.zeros((n, 2), np.int32),
                 caps=np.full((n, 20), -1, np.int32), amount=np.zeros(n, np.float64), balance=np.zeros(n, np.float64),
                 body_hash=np.zeros((n, 32), np.uint8))
-    data = np.concatenate([data, np.zeros(16, np.uint8)])
+    data = np.concatenate([data, np.zeros(SLACK, np.uint8)])
     lib().hc_legacy(C.c_int64(n), _p(offsets), _p(data), _p(cols["status"]), _p(cols["lflags"]), _p(cols["strip"]),
                     _p(cols["caps"]), _p(cols["amount"]), _p(cols["balance"]), _p(cols["body_hash"]), C.c_uint32(mode))
     return cols
