@@ -17,6 +17,8 @@
 #include <string.h>
 
 #include <string>
+#include <thread>
+#include <vector>
 
 namespace sgemit {
 
@@ -212,6 +214,56 @@ inline bool emit_one(Sink& o, const In& in, int64_t i, int mode) {
         o.lit(",\"txn_type\":"); if (!text_field(o, in, e, 0, false, false)) return bail();
         o.ch('}');
     }
+    return true;
+}
+
+// The selected rows of a batch: lengths, offsets and (with out_bytes) the bytes.  Rows are independent: a sizing pass
+// leaves every row's length in out_offsets[k + 1], a prefix sum turns the lengths into offsets, the writing pass puts
+// each row at its offset.  Both passes run on `threads` host threads (0: one per 32 K rows, at most 8 and at most the
+// host's cores).  Returns false when `capacity` is too small for the bytes (`needed` says how many).
+inline bool emit_many(const In& I, int mode, int64_t n_sel, const int64_t* sel, int64_t* out_offsets, uint8_t* out_bytes,
+                      int64_t capacity, uint8_t* fallback, int64_t* needed, int threads) {
+    if (threads <= 0) {
+        const unsigned hw = std::thread::hardware_concurrency();
+        int64_t t = n_sel / 32768;
+        if (t > 8) t = 8;
+        if (hw && t > (int64_t)hw) t = hw;
+        threads = (int)t;
+    }
+    if (threads < 1) threads = 1;
+    if ((int64_t)threads > n_sel) threads = n_sel > 0 ? (int)n_sel : 1;
+    auto in_chunks = [&](auto&& body) {                      // body(first row, one past the last row) on each thread
+        if (threads == 1) { body((int64_t)0, n_sel); return; }
+        std::vector<std::thread> pool;
+        for (int t = 0; t < threads; ++t)
+            pool.emplace_back([&, t] { body(n_sel * t / threads, n_sel * (t + 1) / threads); });
+        for (auto& th : pool) th.join();
+    };
+    out_offsets[0] = 0;
+    in_chunks([&](int64_t k0, int64_t k1) {
+        for (int64_t k = k0; k < k1; ++k) {
+            Sink count{nullptr};
+            emit_one(count, I, sel[k], mode);
+            out_offsets[k + 1] = count.n;
+        }
+    });
+    for (int64_t k = 0; k < n_sel; ++k) out_offsets[k + 1] += out_offsets[k];
+    const int64_t total = out_offsets[n_sel];
+    if (needed) *needed = total;
+    if (!out_bytes) return true;                             // sizing call
+    if (capacity < total) return false;
+    in_chunks([&](int64_t k0, int64_t k1) {
+        for (int64_t k = k0; k < k1; ++k) {
+            // a row the sizing pass declined has an empty span and must not be started again: what it writes before
+            // it gives up would land in its neighbour's span (or past the end of the buffer)
+            const bool declined = out_offsets[k + 1] == out_offsets[k];
+            if (!declined) {
+                Sink w{out_bytes + out_offsets[k]};
+                emit_one(w, I, sel[k], mode);
+            }
+            if (fallback) fallback[k] = declined ? 1 : 0;
+        }
+    });
     return true;
 }
 

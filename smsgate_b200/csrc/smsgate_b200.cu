@@ -986,54 +986,10 @@ extern "C" int smsgate_emit_json(const smsgate_emit_input* in, int mode, int64_t
     if (!I.msg_id || !I.card || !I.card_len || !I.body_offsets || !I.sender_offsets || !I.text_offsets || !I.text_kind ||
         (!in->records && (!I.flags || !I.dec_flags || !I.slot || !I.amount_coef || !I.balance_coef || !I.amount_exp || !I.balance_exp || !I.date)))
         return SMSGATE_E_ARG;
-    // Rows are independent: a sizing pass leaves every row's length in out_offsets[k + 1], a prefix sum turns the
-    // lengths into offsets, the emitting pass writes each row at its offset.  Both passes run on several host threads
-    // once there are enough rows (one per 32 K rows, at most 8 and at most the host's cores; environment variable
-    // SMSGATE_EMIT_THREADS overrides the count).
-    int threads = 1;
-    if (const char* forced = getenv("SMSGATE_EMIT_THREADS")) threads = atoi(forced);
-    else {
-        const unsigned hw = std::thread::hardware_concurrency();
-        int64_t t = n_sel / 32768;
-        if (t > 8) t = 8;
-        if (hw && t > (int64_t)hw) t = hw;
-        threads = (int)t;
-    }
-    if (threads < 1) threads = 1;
-    if ((int64_t)threads > n_sel) threads = n_sel > 0 ? (int)n_sel : 1;
-    auto in_chunks = [&](auto&& body) {                      // body(first row, one past the last row) on each thread
-        if (threads == 1) { body((int64_t)0, n_sel); return; }
-        std::vector<std::thread> pool;
-        for (int t = 0; t < threads; ++t)
-            pool.emplace_back([&, t] { body(n_sel * t / threads, n_sel * (t + 1) / threads); });
-        for (auto& th : pool) th.join();
-    };
-    out_offsets[0] = 0;
-    in_chunks([&](int64_t k0, int64_t k1) {
-        for (int64_t k = k0; k < k1; ++k) {
-            sgemit::Sink count{nullptr};
-            sgemit::emit_one(count, I, sel[k], mode);
-            out_offsets[k + 1] = count.n;
-        }
-    });
-    for (int64_t k = 0; k < n_sel; ++k) out_offsets[k + 1] += out_offsets[k];
-    const int64_t total = out_offsets[n_sel];
-    if (needed) *needed = total;
-    if (!out_bytes) return SMSGATE_OK;                       // sizing call
-    if (capacity < total) return SMSGATE_E_LIMIT;
-    in_chunks([&](int64_t k0, int64_t k1) {
-        for (int64_t k = k0; k < k1; ++k) {
-            // a row the sizing pass declined has an empty span and must not be started again: what it writes before
-            // it gives up would land in its neighbour's span (or past the end of the buffer)
-            const bool declined = out_offsets[k + 1] == out_offsets[k];
-            if (!declined) {
-                sgemit::Sink w{out_bytes + out_offsets[k]};
-                sgemit::emit_one(w, I, sel[k], mode);
-            }
-            if (fallback) fallback[k] = declined ? 1 : 0;
-        }
-    });
-    return SMSGATE_OK;
+    int threads = 0;
+    if (const char* forced = getenv("SMSGATE_EMIT_THREADS")) threads = atoi(forced) > 0 ? atoi(forced) : 1;
+    return sgemit::emit_many(I, mode, n_sel, sel, out_offsets, out_bytes, capacity, fallback, needed, threads) ? SMSGATE_OK
+                                                                                                               : SMSGATE_E_LIMIT;
 }
 
 extern "C" int smsgate_abi_version(void) { return SMSGATE_ABI_VERSION; }

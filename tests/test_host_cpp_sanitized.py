@@ -91,7 +91,8 @@ def test_pickle_decoder_on_mutated_blobs(tmp_path):
     assert f"decoded {n} blobs" in stdout
 
 
-def test_emitter_writes_exactly_what_it_announced(tmp_path):
+def _dump_replay_columns(tmp_path):
+    """Columns of a replayed batch with adversarial cache texts, one file per array, for the C++ harnesses."""
     from smsgate_b200 import synth
     from smsgate_b200.batch import ragged_from_strings
     from tests import test_emit_json as T
@@ -130,9 +131,45 @@ def test_emitter_writes_exactly_what_it_announced(tmp_path):
     w("text_offsets", table.text[0], np.int64)
     w("text_bytes", table.text[1], np.uint8)
     w("text_kind", table.text[2], np.uint8)
-    stdout = _run(_build(tmp_path, "asan_emit"), str(d))
+    return d
+
+
+def test_emitter_writes_exactly_what_it_announced(tmp_path):
+    stdout = _run(_build(tmp_path, "asan_emit"), str(_dump_replay_columns(tmp_path)))
     rows = int(stdout.split()[1])
     assert rows > 2000 and "MISMATCH" not in stdout
+
+
+def test_threaded_host_code_under_tsan(tmp_path):
+    """The cache reader on seven connections and the emitter on six threads, built with ThreadSanitizer: no data
+    race, and the same arrays / bytes as on one."""
+    import diskcache
+
+    from smsgate_b200 import synth
+    gxx = shutil.which("g++")
+    if gxx is None:
+        pytest.skip("no g++")
+    exe = str(tmp_path / "tsan_host")
+    res = subprocess.run([gxx, "-std=c++17", "-O1", "-g", "-fsanitize=thread", "-fno-omit-frame-pointer", "-I", CSRC, "-o", exe,
+                          os.path.join(ROOT, "tests", "hostcheck", "tsan_host.cpp"), "-ldl", "-lpthread"], capture_output=True, text=True)
+    if res.returncode and "cannot find" in res.stderr:
+        pytest.skip("g++ has no ThreadSanitizer runtime here")
+    assert res.returncode == 0, res.stderr[-2000:]
+    cache_dir = tmp_path / "cache"
+    c = diskcache.Cache(str(cache_dir))
+    backup = synth.generate(6000, seed=77, mixed_locale=True)
+    with c.transact():
+        for k, v in backup.cache.items():
+            c[k] = v
+        c["f" * 64] = {"txn_type": "debit", "merchant": "X" * 40_000}      # a value diskcache keeps in a side file
+        c["e" * 64] = "a plain string"
+    c.close()
+    cols = _dump_replay_columns(tmp_path)
+    res = subprocess.run([exe, str(cache_dir), str(cols)], capture_output=True, text=True, timeout=900,
+                         env=dict(os.environ, TSAN_OPTIONS="halt_on_error=0"))
+    assert res.returncode == 0, (res.stdout, res.stderr[-3000:])
+    assert "ThreadSanitizer" not in res.stderr, res.stderr[-3000:]
+    assert "one connection == seven: yes" in res.stdout and "one thread == six: yes" in res.stdout
 
 
 _DEVICE_LOGIC_SCRIPT = r"""
