@@ -96,34 +96,69 @@ def special_cache(backup):
     return cache, bend
 
 
+class Harness:
+    """The reference's two handlers, imported unmodified, behind a fake NATS: `run(handler, payload bytes)` reports
+    acks, the exception that escaped (if any), the three Prometheus counters' deltas and what was published."""
+
+    def __init__(self):
+        logging.disable(logging.CRITICAL)
+        self.ref = ref = Reference(tempfile.mkdtemp(prefix="ref_worker_"))
+        sys.path.insert(0, os.path.join(REFERENCE_ROOT, "services", "parser_worker"))     # `from metrics import ...`
+        if "redis" not in sys.modules:                       # metrics.py only names the type (absent package: stub)
+            import types
+            redis, ra = types.ModuleType("redis"), types.ModuleType("redis.asyncio")
+            ra.Redis = type("Redis", (), {})
+            redis.asyncio = ra
+            sys.modules.update({"redis": redis, "redis.asyncio": ra})
+        with ref.quiet():
+            import services.parser_worker.dlq_worker as D
+            import services.parser_worker.worker as W
+        from libs import nats_utils
+
+        class _Frozen(dt.datetime):
+            @classmethod
+            def now(cls, tz=None):
+                return NOW
+
+        W.datetime = _Frozen
+
+        async def _no_stream(nc):
+            return None
+        W.ensure_stream = _no_stream
+        D.ensure_stream = _no_stream
+        self.W, self.D = W, D
+        self.subjects = {nats_utils.SUBJECT_FAILED: "failed", nats_utils.SUBJECT_PARSED: "parsed",
+                         getattr(nats_utils, "SUBJECT_PROCESSING", "?"): "processing"}
+
+    def counters(self):
+        W = self.W
+        return [c._value.get() for c in (W.PARSED_OK, W.PARSED_SKIP, W.PARSED_FAIL)]
+
+    def run(self, coro_fn, data):
+        nc, msg = _NC(), _Msg(data)
+        before = self.counters()
+        escaped = None
+        try:
+            with self.ref.quiet():
+                asyncio.run(coro_fn(nc, msg))
+        except Exception as e:                                   # what the worker loop would die of
+            escaped = type(e).__name__
+        after = self.counters()
+        return {"acks": msg.acks, "escaped": escaped,
+                "counters": [int(a - b) for a, b in zip(after, before)],          # PARSED_OK, PARSED_SKIP, PARSED_FAIL
+                "published": [[self.subjects.get(s, s), p.decode("utf-8")] for s, p in nc.log]}
+
+    def run_dlq(self, data):
+        return self.run(lambda nc, m: self.D._handle_dlq_msg(nc, m, reparse=True), data)
+
+    def run_worker(self, data):
+        return self.run(self.W._process_one, data)
+
+
 def main():
-    logging.disable(logging.CRITICAL)
-    ref = Reference(tempfile.mkdtemp(prefix="ref_worker_"))
-    sys.path.insert(0, os.path.join(REFERENCE_ROOT, "services", "parser_worker"))     # `from metrics import ...`
-    if "redis" not in sys.modules:                       # metrics.py only names the type (absent package: stub)
-        import types
-        redis, ra = types.ModuleType("redis"), types.ModuleType("redis.asyncio")
-        ra.Redis = type("Redis", (), {})
-        redis.asyncio = ra
-        sys.modules.update({"redis": redis, "redis.asyncio": ra})
-    with ref.quiet():
-        import services.parser_worker.dlq_worker as D
-        import services.parser_worker.worker as W
-    from libs import nats_utils
-
-    class _Frozen(dt.datetime):
-        @classmethod
-        def now(cls, tz=None):
-            return NOW
-
-    W.datetime = _Frozen
-
-    async def _no_stream(nc):
-        return None
-    W.ensure_stream = _no_stream
-    D.ensure_stream = _no_stream
-    subjects = {nats_utils.SUBJECT_FAILED: "failed", nats_utils.SUBJECT_PARSED: "parsed",
-                getattr(nats_utils, "SUBJECT_PROCESSING", "?"): "processing"}
+    h = Harness()
+    ref, W, D = h.ref, h.W, h.D
+    run = h.run
 
     backup = synth.generate(160, seed=74, mixed_locale=True, miss_frac=0.1, otp_frac=0.08)
     cache, bend = special_cache(backup)
@@ -139,23 +174,6 @@ def main():
         backup.date_ms.append(1_707_900_000_000 + 1000 * (160 + k) * (10 if k % 2 else 1))
         cache[reference_cache_key(body)] = dict(base, date=date)
     ref.seed_cache(cache)
-
-    def counters():
-        return [c._value.get() for c in (W.PARSED_OK, W.PARSED_SKIP, W.PARSED_FAIL)]
-
-    def run(coro_fn, data):
-        nc, msg = _NC(), _Msg(data)
-        before = counters()
-        escaped = None
-        try:
-            with ref.quiet():
-                asyncio.run(coro_fn(nc, msg))
-        except Exception as e:                                   # what the worker loop would die of
-            escaped = type(e).__name__
-        after = counters()
-        return {"acks": msg.acks, "escaped": escaped,
-                "counters": [int(a - b) for a, b in zip(after, before)],          # PARSED_OK, PARSED_SKIP, PARSED_FAIL
-                "published": [[subjects.get(s, s), p.decode("utf-8")] for s, p in nc.log]}
 
     flows = {"dlq": [], "worker": []}
     for p in payloads(backup.bodies, backup.senders):

@@ -10,7 +10,7 @@ Two families:
   * the oracle against the REFERENCE ITSELF, imported from /root/reference (build container only): `ref_units`
     (worker filter lifted from worker.py, parser filter, clean + mask, fix_broken_datetime,
     parse_ambiguous_decimal), `ref_route` (parse_sms_llm + the worker / writer gates on random cache entries),
-    `ref_legacy` (parse_transaction_message / parse_credit_message), `ref_iter_sms` (the `_iter_sms` generator on mutated backups: rows, exception, rows before the exception).
+    `ref_dlq` (the DLQ handler and `_process_one` behind a fake NATS, damaged payloads), `ref_legacy` (parse_transaction_message / parse_credit_message), `ref_iter_sms` (the `_iter_sms` generator on mutated backups: rows, exception, rows before the exception).
 Every mismatch prints a line containing MISMATCH; a clean run prints only the per-seed progress lines.
 Round 2's runs and the one finding they produced are listed in DESIGN.md section 2."""
 import datetime as dt
@@ -402,6 +402,87 @@ def ref_legacy(first, last):
         progress(seed, t0, bodies=n, bad=bad)
 
 
+def ref_dlq(first, last):
+    """dlq_worker._handle_dlq_msg(reparse=True) and worker._process_one, run unmodified behind a fake NATS
+    (oracle/gen_golden_worker.Harness), against oracle/dlq_oracle.py on damaged and restructured DLQ payloads and on
+    live RawSMS payloads with random cache entries: acks, escaped exception, counters, published bytes."""
+    import json
+
+    import torch  # noqa: F401 - before the reference's import stubs go in
+
+    import tests.test_worker_flow_oracle as TW
+    from oracle import dlq_oracle as DO
+    from oracle import replay_oracle as O
+    from oracle.gen_golden_worker import Harness
+    from smsgate_b200 import synth
+    from tests import _flow as FL
+    h = Harness()
+    offline = "offline: Gemini is not reachable"
+    t0, bad, n = time.time(), 0, 0
+    odd_values = [None, 5, 1.5, True, [], ["x"], {}, {"a": 1}, "", "x", "1707900000000", "2024-02-14T09:00:00+00:00"]
+    for seed in range(first, last):
+        rng = random.Random(66000 + seed)
+        bodies = [rng.choice(ROUTE_BODIES) % i for i in range(300)]
+        backup = synth.generate(100, seed=500 + seed, mixed_locale=True, otp_frac=0.1)
+        bodies += list(backup.bodies)
+        cache = {}
+        for b in bodies:
+            if rng.random() < 0.85:
+                v = backup.cache.get(O.cache_key(O.fixed_body(b)).hex())
+                cache[O.cache_key(O.fixed_body(b)).hex()] = v if v is not None and rng.random() < 0.5 else random_entry(rng)
+        h.ref.seed_cache(cache)
+        for b in bodies:
+            raw = {"msg_id": hashlib.sha1(b.encode()).hexdigest(), "sender": rng.choice(["BANK", "Ж", "B 1"]), "body": b,
+                   "date": rng.choice(["2024-02-14T09:00:00+00:00", "1707900000000", "1707900000", "abc", ""]),
+                   "device_id": rng.choice(["xml_backup", None, "d1"]), "source": rng.choice(["xml", "device"])}
+            r = rng.random()
+            if r < 0.25:                                         # one field bent
+                k = rng.choice(list(raw) + ["extra"])
+                raw[k] = rng.choice(odd_values)
+            elif r < 0.32:
+                raw.pop(rng.choice(list(raw)))
+            wrap = rng.random()
+            if wrap < 0.55:
+                obj = {"reason": "unmatched", "raw": raw}
+            elif wrap < 0.62:
+                obj = {"err": "boom", "entry": raw}              # no `raw`
+            elif wrap < 0.68:
+                obj = {"raw": rng.choice([None, [raw], "text", 5, json.dumps(raw)])}
+            elif wrap < 0.72:
+                obj = rng.choice([[1, 2], "str", 5, None, [raw]])
+            else:
+                obj = raw                                        # the live shape: the RawSMS itself
+            data = json.dumps(obj, ensure_ascii=rng.random() < 0.5).encode()
+            if rng.random() < 0.06:
+                k = rng.randrange(len(data) + 1)
+                data = data[:k] + rng.choice([b"\xff", b"{", b"}", b'"', b"\x00", b""]) + data[k + rng.randint(0, 2):]
+            n += 1
+            try:
+                row = h.run_dlq(data)
+                outcomes, rows, raws, outs, _, _, _ = DO.reparse([data], cache, NOW)
+                out, rw = (outs[0], raws[0]) if rows[0] >= 0 else (None, None)
+                FL.check_dlq_row(row, outcomes[0], out, rw, offline, TW._dump_json)
+            except AssertionError as e:
+                bad += 1
+                print("REFERENCE MISMATCH dlq", data[:300], "\n   reference:", str(row)[:400], "\n   oracle:", outcomes, e, flush=True)
+            # the live path: the same message as the watcher / gateway publish it, through worker._process_one
+            try:
+                live = DO.RawSMS(**raw)
+            except Exception:                             # noqa: BLE001 - a bent field: not a message the live path sees
+                continue
+            row = h.run_worker(live.model_dump_json().encode())
+            out = O.replay_one(live.body, live.sender, live.date, cache, NOW, device_id=live.device_id)
+            try:
+                want = FL.status_of(row, offline)
+                assert out.status == want, (out.status, want)
+                pj = TW._dump_json(out.parsed, live.msg_id) if want in (FL.UPSERT, FL.NO_MERCHANT) else None
+                FL.check_published(row, want, pj, live.model_dump())
+            except AssertionError as e:
+                bad += 1
+                print("REFERENCE MISMATCH worker", raw, "\n   reference:", str(row)[:400], "\n   oracle:", out.status, e, flush=True)
+        progress(seed, t0, payloads=n, bad=bad)
+
+
 XML_DATES = [b"99999999999999999999999", b"253402300800000", b"253402300799999", b"-62135596800001", b"-62135596800000",
              b"9223372036854775808", b"9223372036854775807", b"-9223372036854775808", b"-9223372036854775809", b" 5 ",
              b"1_0", b"+7", b"\xd9\xa1\xd9\xa2", b"", b"1e3", b"0x10", b"12345678901234567890", b"9300000000000000000000",
@@ -462,7 +543,7 @@ def ref_iter_sms(first, last):
         progress(seed, t0, files=n, bad=bad, through_elementtree=eng.host_fallbacks)
 
 
-CAMPAIGNS = {"ref_iter_sms": ref_iter_sms, "ref_legacy": ref_legacy, "scan": scan, "route": route, "legacy": legacy, "xml": xml, "xml_struct": xml_struct,
+CAMPAIGNS = {"ref_dlq": ref_dlq, "ref_iter_sms": ref_iter_sms, "ref_legacy": ref_legacy, "scan": scan, "route": route, "legacy": legacy, "xml": xml, "xml_struct": xml_struct,
              "ref_units": ref_units, "ref_route": ref_route}
 
 if __name__ == "__main__":

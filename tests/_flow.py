@@ -51,3 +51,26 @@ def check_published(row, status, parsed_json, raw_dump):
         assert parsed_json == row["published"][0][1]
     elif status == UNMATCHED:
         assert json.dumps({"reason": "unmatched", "raw": raw_dump}) == row["published"][0][1]
+
+
+def check_dlq_row(row, outcome, out, raw, offline_error, dump_json):
+    """One DLQ payload: what the reference's `_handle_dlq_msg(reparse=True)` did (`row`) against the oracle's
+    reading of the same payload (`outcome` of dlq_oracle.handle; `out` / `raw` the replayed message, if any).
+    `dump_json(parsed, msg_id)` renders the sms.parsed payload."""
+    nothing = not row["published"] and row["counters"] == [0, 0, 0]
+    if outcome in ("not_json", "no_raw"):
+        assert nothing and row["acks"] == 1 and row["escaped"] is None
+    elif outcome == "not_an_object":
+        assert nothing and row["acks"] == 0 and row["escaped"] == "AttributeError"      # payload.get on a list
+    elif outcome == "invalid_raw":
+        # worker.py:101-109 means to publish the failure, but `.decode` on the already decoded str raises
+        # inside the handler and dlq_worker.py:76 swallows it: nothing happens
+        assert nothing and row["acks"] == 0 and row["escaped"] is None
+    else:
+        st = out.status
+        if st in (FUTURE, ESCAPED):
+            assert nothing and row["acks"] == 0 and row["escaped"] is None              # swallowed by dlq_worker.py:76
+        else:
+            assert st == status_of(row, offline_error)
+            pj = dump_json(out.parsed, raw.msg_id) if st in (UPSERT, NO_MERCHANT) else None
+            check_published(row, st, pj, raw.model_dump())

@@ -40,25 +40,10 @@ def test_dlq_flow_matches_reference_run():
     outcomes, rows, raws, outs, surv, first, last = DO.reparse(payloads, g["cache"], now)
     kinds = set()
     for i, row in enumerate(g["flows"]["dlq"]):
-        o = outcomes[i]
-        kinds.add(o)
-        nothing = not row["published"] and row["counters"] == [0, 0, 0]
-        if o == "not_json" or o == "no_raw":
-            assert nothing and row["acks"] == 1 and row["escaped"] is None, i
-        elif o == "not_an_object":
-            assert nothing and row["acks"] == 0 and row["escaped"] == "AttributeError", i      # payload.get on a list
-        elif o == "invalid_raw":
-            # worker.py:101-109 means to publish the failure, but `.decode` on the already decoded str raises
-            # inside the handler and dlq_worker.py:76 swallows it: nothing happens
-            assert nothing and row["acks"] == 0 and row["escaped"] is None, i
-        else:
-            st = outs[rows[i]].status
-            if st in (O.ST_FUTURE_DATE, O.ST_ESCAPED):
-                assert nothing and row["acks"] == 0 and row["escaped"] is None, i              # swallowed by dlq_worker.py:76
-            else:
-                assert st == F.status_of(row, g["offline_error"]), i
-                pj = None
-                if st in (O.ST_UPSERT, O.ST_PARSED_NO_MERCHANT):
-                    pj = _dump_json(outs[rows[i]].parsed, raws[rows[i]].msg_id)
-                F.check_published(row, st, pj, raws[rows[i]].model_dump())
+        kinds.add(outcomes[i])
+        out, raw = (outs[rows[i]], raws[rows[i]]) if rows[i] >= 0 else (None, None)
+        try:
+            F.check_dlq_row(row, outcomes[i], out, raw, g["offline_error"], _dump_json)
+        except AssertionError as e:
+            raise AssertionError(f"DLQ payload {i}: {e}") from e
     assert kinds == {"not_json", "no_raw", "not_an_object", "invalid_raw", "replayed"}
