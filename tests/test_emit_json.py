@@ -160,3 +160,27 @@ def test_emitter_fuzz_against_pydantic(monkeypatch):
                 assert json.loads(got) == want, (int(i), got)
             rendered += 1
     assert rendered > 1500 and declined_for_a_reason > 50
+
+
+def test_packed_records_give_the_same_bytes(monkeypatch):
+    """The emitter reading the 64-byte records of smsgate_replay_host_records8 (what the end-to-end call returns)
+    against the emitter reading separate columns."""
+    from smsgate_b200.replay import _RecordColumns
+    backup = synth.generate(3000, seed=94, mixed_locale=True, dup_frac=0.2)
+    res, table = _result(list(backup.bodies), list(backup.senders), backup.cache)
+    dtype = np.dtype(L.RECORD_FIELDS)
+    assert dtype.itemsize == L.RECORD_BYTES_OUT
+    records = np.zeros(len(backup.bodies), dtype=dtype)
+    for f in dtype.names:
+        if f in res.cols:
+            records[f] = res.cols[f]
+    packed = _RecordColumns(records, np.zeros(len(backup.bodies), np.uint8), engine=None)
+    packed._fetched.update({k: res.cols[k] for k in _RecordColumns._ON_DEVICE})       # as if fetched from the device
+    res_packed = ReplayResult(res.batch, packed, table, 0)
+    idx = np.nonzero(np.isin(res.cols["status"], (L.ST_UPSERT, L.ST_PARSED_NO_MERCHANT)))[0]
+    assert len(idx) > 2000
+    for threads in ("1", "4"):
+        monkeypatch.setenv("SMSGATE_EMIT_THREADS", threads)
+        for mode in (0, 1):
+            a, b = res.emit_json(idx, mode), res_packed.emit_json(idx, mode)
+            assert all(np.array_equal(x, y) for x, y in zip(a, b)), (threads, mode)
